@@ -1,0 +1,354 @@
+// engine.hpp -- host-side object behind the C ABI (include/pfbwt_b200.h).  One
+// Engine = one pfbwtf::PfParser (+ the PrefixFreeBWT built from it) living on one
+// GPU.  Mirrors the reference's operator surface for the hot path:
+//   add_fasta / finalize        include/pfparser.hpp:299-369, 484-492
+//   bwt_of_parse                include/pfparser.hpp:379-467
+//   save_parser / load_parser   include/pfbwt_io.hpp:211-249
+//   operator+=                  include/pfparser.hpp:194-263
+//   generate_bwt_lcp + writer   include/pfbwt.hpp:96-194, src/pfbwt-f.cpp:272-349
+#pragma once
+#include "host_io.hpp"
+#include "pipeline.cuh"
+#include <memory>
+
+namespace pfb {
+
+struct Segment {             // a piece of S waiting to be parsed
+    bool on_device = false;
+    DevBuf<u8> dev;          // normalised bytes (reconstructed from a loaded parse)
+    size_t host_off = 0;     // offset into Engine::raw
+    u64 len = 0;
+};
+
+struct Engine {
+    Params prm;
+    int device = 0;
+    Workspace ws;
+    StageTimes tm;
+    std::string err;
+    int last_rc = 0;
+
+    HostBytes raw;                   // record bytes + A^w padding, as read from FASTA / caller buffers
+    std::vector<Segment> segs;
+    FastaResult docs;
+    bool store_docs = false;
+    u64 pending_n = 0;               // bytes of S accumulated in segs
+
+    TextOnDevice text;
+    bool text_ready = false;
+    DeviceParse parse;
+    bool parsed = false;
+    DeviceBwt bwt;
+    bool built = false;
+    bool built_sa = false, built_rssa = false;
+
+    int fail(int rc, const std::string &m) { err = m; last_rc = rc; return rc; }
+
+    // ---- ingestion -----------------------------------------------------------
+    void push_host_segment(size_t off, u64 len) {
+        if (!len) return;
+        if (!segs.empty() && !segs.back().on_device && segs.back().host_off + segs.back().len == off) segs.back().len += len;
+        else { Segment s; s.host_off = off; s.len = len; segs.push_back(std::move(s)); }
+        pending_n += len;
+    }
+
+    int add_fasta(const std::string &path) {
+        size_t off0 = raw.n;
+        FastaResult r;
+        std::string e;
+        if (read_fasta(path, prm.w, raw, r, store_docs, 0, e)) return fail(PFB_ERR_IO, e);
+        if (prm.bits == 32 && r.total_len > 0xFFFFFFFFull)   // include/pfparser.hpp:326-332
+            return fail(PFB_ERR_TOO_LONG_32, "input too long, please use 64-bit version");
+        // doc starts are offsets in S of everything parsed so far
+        u64 base = pending_n - (u64)0;
+        for (size_t i = 0; i < r.starts.size(); ++i) docs.starts.push_back(base + (r.starts[i] - off0));
+        for (auto &nm : r.names) docs.names.push_back(nm);
+        docs.nrec += r.nrec; docs.total_len += r.total_len;
+        push_host_segment(off0, raw.n - off0);
+        invalidate();
+        return PFB_OK;
+    }
+
+    int add_records(const u8 *seq, const u64 *rec_len, u64 nrec) {
+        size_t off0 = raw.n;
+        u64 tot = 0;
+        for (u64 r = 0; r < nrec; ++r) tot += rec_len[r];
+        if (prm.bits == 32 && tot > 0xFFFFFFFFull) return fail(PFB_ERR_TOO_LONG_32, "input too long, please use 64-bit version");
+        raw.reserve(raw.n + tot + nrec * (u64)prm.w);
+        u64 src = 0;
+        for (u64 r = 0; r < nrec; ++r) {
+            raw.append(seq + src, rec_len[r]);
+            raw.append_fill('A', (size_t)prm.w);
+            src += rec_len[r];
+        }
+        docs.nrec += nrec; docs.total_len += tot;
+        push_host_segment(off0, raw.n - off0);
+        invalidate();
+        return PFB_OK;
+    }
+
+    void invalidate() { text_ready = false; parsed = false; built = false; }
+
+    // ---- text upload: T' = Dollar . S . Dollar^w, S 16-byte aligned ---------------
+    int upload_text() {
+        try {
+            const u64 n = pending_n;
+            if (n == 0) return fail(PFB_ERR_ARG, "empty input");
+            Timer timer(ws.st);
+            text.buf.alloc(16 + n + (u64)prm.w + 64);
+            text.n = n;
+            u8 *S = text.S();
+            u64 o = 0;
+            for (auto &s : segs) {
+                if (s.on_device) d2d(S + o, s.dev.get(), s.len, ws.st);
+                else h2d(S + o, raw.p + s.host_off, s.len, ws.st);
+                o += s.len;
+            }
+            u8 *Tp = text.Tp();
+            const int w = prm.w;
+            launch_for((u64)w + 1, ws.st, PFB_LAMBDA(u64 i) {
+                if (i == 0) Tp[0] = DOLLAR; else Tp[n + i] = DOLLAR;
+            });
+            // K0 normalise
+            DevBuf<u64> errpos(1);
+            dev_memset(errpos.get(), 0xff, 8, ws.st);
+            k_normalise(S, n, prm.non_acgt_to_a, errpos.get(), ws.st);
+            u64 ep = read_scalar(errpos.get(), ws.st);
+            tm.normalise = timer.stop();
+            if (ep != ~0ull) {
+                u8 c = read_scalar(S + ep, ws.st);
+                char msg[128];
+                snprintf(msg, sizeof(msg), "error, invalid character %d/%c -> %d", (int)(signed char)c, c, 5);   // include/hash.hpp:31
+                return fail(PFB_ERR_INVALID_CHAR, msg);
+            }
+            text_ready = true;
+            return PFB_OK;
+        } catch (const Error &e) { return fail(e.code, e.what()); }
+    }
+
+    // ---- finalize = parse on device ---------------------------------------------------
+    int parse_device() {
+        try {
+            if (!text_ready) { int rc = upload_text(); if (rc) return rc; }
+            parse = DeviceParse();
+            int rc = parse_text(text, prm, parse, ws, tm, err);
+            if (rc) return fail(rc, err);
+            parsed = true; built = false;
+            return PFB_OK;
+        } catch (const Error &e) { return fail(e.code, e.what()); }
+    }
+    int finalize() { return parse_device(); }
+
+    int do_parse_bwt() {
+        try {
+            if (!parsed) return fail(PFB_ERR_ARG, "parse not finalized");
+            int rc = parse_bwt(parse, prm, ws, tm, err);
+            if (rc) return fail(rc, err);
+            return PFB_OK;
+        } catch (const Error &e) { return fail(e.code, e.what()); }
+    }
+
+    int build(bool sa, bool rssa) {
+        try {
+            if (!parsed) return fail(PFB_ERR_ARG, "no parse loaded");
+            if (!parse.has_parse_bwt) { int rc = do_parse_bwt(); if (rc) return rc; }
+            bwt = DeviceBwt();
+            int rc = build_bwt(parse, prm, sa, rssa, bwt, ws, tm, err);
+            if (rc) return fail(rc, err);
+            built = true; built_sa = sa; built_rssa = rssa;
+            return PFB_OK;
+        } catch (const Error &e) { return fail(e.code, e.what()); }
+    }
+
+    // drop the text (and host staging) once the parse exists: only dict/parse are needed downstream
+    void release_text() { text.buf.release(); text_ready = false; }
+
+    // ---- copies to host -----------------------------------------------------------------
+    template <class T>
+    std::vector<T> to_host(const DevBuf<T> &b, size_t count) {
+        std::vector<T> v(count);
+        if (count) { d2h(v.data(), b.get(), count * sizeof(T), ws.st); stream_sync(ws.st); }
+        return v;
+    }
+
+    // ---- files: save_parser (include/pfbwt_io.hpp:234-249) + parse-bwt (src/pfbwt-f.cpp:229-235)
+    int save_parse(const std::string &prefix, bool with_parse_bwt, bool with_sai) {
+        try {
+            if (!parsed) return fail(PFB_ERR_ARG, "parse not finalized");
+            const int U = prm.bits / 8;
+            std::string e;
+            { auto v = to_host(parse.dict, parse.dsize); if (write_file(prefix + ".dict", v.data(), v.size(), e)) return fail(PFB_ERR_IO, e); }
+            { auto v = to_host(parse.occ, parse.Dw); auto o = widen_u32(v.data(), v.size(), U);
+              if (write_file(prefix + ".occ", o.data(), o.size(), e)) return fail(PFB_ERR_IO, e); }
+            { auto v = to_host(parse.parse, parse.P); if (write_file(prefix + ".parse", v.data(), v.size() * 4, e)) return fail(PFB_ERR_IO, e); }
+            if (store_docs) {   // include/pfbwt_io.hpp:224-231
+                FILE *f = fopen((prefix + ".docs").c_str(), "w");
+                if (!f) return fail(PFB_ERR_IO, "could not open docs file");
+                for (size_t i = 0; i < docs.starts.size(); ++i)
+                    fprintf(f, "%s %lu\n", i < docs.names.size() ? docs.names[i].c_str() : "", (unsigned long)docs.starts[i]);
+                fclose(f);
+            }
+            { FILE *f = fopen((prefix + ".n").c_str(), "w"); if (!f) return fail(PFB_ERR_IO, "could not open .n file");
+              fprintf(f, "%lu\n", (unsigned long)parse.n); fclose(f); }
+            if (with_parse_bwt) {
+                if (!parse.has_parse_bwt) return fail(PFB_ERR_ARG, "parse BWT not computed");
+                { auto v = to_host(parse.bwlast, parse.P + 1); if (write_file(prefix + ".bwlast", v.data(), v.size(), e)) return fail(PFB_ERR_IO, e); }
+                { auto v = to_host(parse.ilist, parse.P + 1); auto o = widen_u32(v.data(), v.size(), U);
+                  if (write_file(prefix + ".ilist", o.data(), o.size(), e)) return fail(PFB_ERR_IO, e); }
+                if (with_sai) { auto v = to_host(parse.bwsai, parse.P + 1); auto o = narrow_u64(v.data(), v.size(), U);
+                  if (write_file(prefix + ".bwsai", o.data(), o.size(), e)) return fail(PFB_ERR_IO, e); }
+            }
+            return PFB_OK;
+        } catch (const Error &e) { return fail(e.code, e.what()); }
+    }
+
+    // ---- load: PrefixFreeBWT ctor (include/pfbwt.hpp:64-81) / load_parser (include/pfbwt_io.hpp:211-222)
+    int load_parse(const std::string &prefix, bool with_parse_bwt, bool with_sai) {
+        try {
+            const int U = prm.bits / 8;
+            std::string e;
+            std::vector<uint8_t> dict, occ, pr;
+            if (read_file(prefix + ".dict", dict, e)) return fail(PFB_ERR_IO, "bad dict file\n");
+            if (read_file(prefix + ".parse", pr, e)) return fail(PFB_ERR_IO, "bad parse file\n");
+            if (dict.empty() || dict.back() != ENDOFDICT) return fail(PFB_ERR_IO, "bad dict file\n");
+            if (dict.size() > 0xFFFFFFF0ull) return fail(PFB_ERR_LIMIT, "dictionary larger than 2^32 bytes is not supported yet");
+            for (size_t i = 0; i + 1 < dict.size(); ++i) {
+                uint8_t c = dict[i];
+                if (!(c == 1 || c == 2 || c == '-' || c == 'A' || c == 'C' || c == 'G' || c == 'N' || c == 'T'))
+                    return fail(PFB_ERR_IO, "dict file contains a byte outside the parser's alphabet");
+            }
+            parse = DeviceParse();
+            parse.dsize = dict.size();
+            std::vector<u32> wstart;
+            wstart.push_back(0);
+            for (size_t i = 0; i + 1 < dict.size(); ++i) if (dict[i] == ENDOFWORD) wstart.push_back((u32)i + 1);
+            parse.Dw = wstart.size() - 1;
+            if (wstart.back() != dict.size() - 1) return fail(PFB_ERR_IO, "bad dict file\n");
+            parse.P = pr.size() / 4;
+            parse.dict.alloc(parse.dsize); h2d(parse.dict.get(), dict.data(), dict.size(), ws.st);
+            parse.wstart.alloc(parse.Dw + 1); h2d(parse.wstart.get(), wstart.data(), wstart.size() * 4, ws.st);
+            parse.parse.alloc(parse.P + 1);
+            h2d(parse.parse.get(), pr.data(), parse.P * 4, ws.st);
+            dev_memset(parse.parse.get() + parse.P, 0, 4, ws.st);
+            // occ: from file if present, else recount
+            std::vector<u32> occ32(parse.Dw, 0);
+            if (!read_file(prefix + ".occ", occ, e) && occ.size() == parse.Dw * (size_t)U) {
+                for (u64 d = 0; d < parse.Dw; ++d) occ32[d] = U == 4 ? ((u32 *)occ.data())[d] : (u32)((u64 *)occ.data())[d];
+            } else {
+                const u32 *p32 = (const u32 *)pr.data();
+                for (u64 k = 0; k < parse.P; ++k) { if (p32[k] < 1 || p32[k] > parse.Dw) return fail(PFB_ERR_IO, "bad parse file\n"); occ32[p32[k] - 1]++; }
+            }
+            parse.occ.alloc(parse.Dw); h2d(parse.occ.get(), occ32.data(), parse.Dw * 4, ws.st);
+            // n from <prefix>.n (src/pfbwt-f.cpp:255-270) or from the phrase lengths
+            {
+                FILE *f = fopen((prefix + ".n").c_str(), "r");
+                unsigned long nn = 0;
+                if (f && fscanf(f, "%lu", &nn) == 1) parse.n = nn;
+                else {
+                    const u32 *p32 = (const u32 *)pr.data();
+                    u64 tot = 0;
+                    for (u64 k = 0; k < parse.P; ++k) { u64 d = p32[k] - 1; tot += (u64)(wstart[d + 1] - 1 - wstart[d]) - (k ? (u64)prm.w : 0); }
+                    parse.n = tot - 1 - (u64)prm.w;
+                }
+                if (f) fclose(f);
+            }
+            stream_sync(ws.st);
+            if (with_parse_bwt) {
+                std::vector<uint8_t> bl, il, bs;
+                if (read_file(prefix + ".bwlast", bl, e) || read_file(prefix + ".ilist", il, e)) return fail(PFB_ERR_IO, e);
+                if (bl.size() != parse.P + 1 || il.size() != (parse.P + 1) * (size_t)U) return fail(PFB_ERR_IO, "bwlast/ilist size mismatch");
+                parse.bwlast.alloc(parse.P + 1); h2d(parse.bwlast.get(), bl.data(), bl.size(), ws.st);
+                std::vector<u32> il32(parse.P + 1);
+                for (u64 i = 0; i <= parse.P; ++i) il32[i] = U == 4 ? ((u32 *)il.data())[i] : (u32)((u64 *)il.data())[i];
+                parse.ilist.alloc(parse.P + 1); h2d(parse.ilist.get(), il32.data(), il32.size() * 4, ws.st);
+                if (with_sai) {
+                    if (read_file(prefix + ".bwsai", bs, e)) return fail(PFB_ERR_IO, e);
+                    if (bs.size() != (parse.P + 1) * (size_t)U) return fail(PFB_ERR_IO, "bwsai size mismatch");
+                    std::vector<u64> b64(parse.P + 1);
+                    for (u64 i = 0; i <= parse.P; ++i) b64[i] = U == 4 ? ((u32 *)bs.data())[i] : ((u64 *)bs.data())[i];
+                    parse.bwsai.alloc(parse.P + 1); h2d(parse.bwsai.get(), b64.data(), b64.size() * 8, ws.st);
+                }
+                stream_sync(ws.st);
+                parse.has_parse_bwt = true;
+            }
+            parsed = true; built = false;
+            return PFB_OK;
+        } catch (const Error &e) { return fail(e.code, e.what()); }
+    }
+
+    // ---- operator+= (include/pfparser.hpp:194-263): the result is defined as the parse of
+    // the concatenated record list, so the rhs parse is expanded back to its text on the
+    // device (phrases minus their w-byte overlaps) and queued as a device segment.
+    int append_parse_of(Engine &rhs) {
+        try {
+            if (!rhs.parsed) return fail(PFB_ERR_ARG, "rhs parse not finalized");
+            if (rhs.prm.w != prm.w) return fail(PFB_ERR_ARG, "invalid w");
+            if (rhs.prm.p != prm.p) return fail(PFB_ERR_ARG, "invalid p");
+            const DeviceParse &rp = rhs.parse;
+            const u64 P = rp.P; const int w = prm.w;
+            DevBuf<u64> clen(P + 1), coff(P + 1);
+            {
+                const u32 *pr = rp.parse.get(); const u32 *wsr = rp.wstart.get(); u64 *cl = clen.get();
+                launch_for(P + 1, ws.st, PFB_LAMBDA(u64 k) {
+                    if (k == P) { cl[k] = 0; return; }
+                    u32 d = pr[k] - 1;
+                    u64 len = wsr[d + 1] - 1 - wsr[d];
+                    cl[k] = k ? len - (u64)w : len;
+                });
+            }
+            exclusive_sum<u64, u64>(clen.get(), coff.get(), P + 1, ws.sc, ws.st);
+            u64 tlen = read_scalar(coff.get() + P, ws.st);      // |T'| = n + w + 1
+            if (tlen < (u64)w + 1) return fail(PFB_ERR_ARG, "rhs parser malformed");
+            u64 n = tlen - (u64)w - 1;
+            DevBuf<u8> tp(tlen);
+            {
+                const u32 *pr = rp.parse.get(); const u32 *wsr = rp.wstart.get(); const u8 *dict = rp.dict.get();
+                const u64 *co = coff.get(); u8 *out = tp.get();
+                launch_for(P * 32, ws.st, PFB_LAMBDA(u64 i) {
+                    u64 k = i / 32, lane = i % 32;
+                    u32 d = pr[k] - 1;
+                    u64 len = wsr[d + 1] - 1 - wsr[d];
+                    u64 skip = k ? (u64)w : 0;
+                    const u8 *src = dict + wsr[d] + skip;
+                    u8 *dst = out + co[k];
+                    for (u64 j = lane; j < len - skip; j += 32) dst[j] = src[j];
+                });
+            }
+            Segment s;
+            s.on_device = true; s.len = n;
+            s.dev.alloc(n);
+            d2d(s.dev.get(), tp.get() + 1, n, ws.st);
+            stream_sync(ws.st);
+            for (size_t i = 0; i < rhs.docs.starts.size(); ++i) docs.starts.push_back(rhs.docs.starts[i] + pending_n);
+            for (auto &nm : rhs.docs.names) docs.names.push_back(nm);
+            segs.push_back(std::move(s));
+            pending_n += n;
+            invalidate();
+            return PFB_OK;
+        } catch (const Error &e) { return fail(e.code, e.what()); }
+    }
+
+    // ---- output files: src/pfbwt-f.cpp:298-349 -------------------------------------------------
+    int write_bwt_files(const std::string &prefix, bool sa, bool rssa, const std::string &stdout_ext) {
+        try {
+            if (!built) return fail(PFB_ERR_ARG, "BWT not built");
+            std::string e;
+            const int U = prm.bits / 8;
+            auto emit = [&](const std::string &ext, const DevBuf<u8> &b, size_t bytes) -> int {
+                auto v = to_host(b, bytes);
+                if (stdout_ext == ext) { fwrite(v.data(), 1, v.size(), stdout); fflush(stdout); return 0; }
+                return write_file(prefix + "." + ext, v.data(), v.size(), e);
+            };
+            if (emit("bwt", bwt.bwt, bwt.n + 1)) return fail(PFB_ERR_IO, e);
+            if (sa) { if (!built_sa && !built_rssa) return fail(PFB_ERR_ARG, "SA not built"); if (emit("sa", bwt.sa, (bwt.n + 1) * (size_t)U)) return fail(PFB_ERR_IO, e); }
+            if (rssa) {
+                if (!built_rssa) return fail(PFB_ERR_ARG, "run-length SA not built");
+                if (emit("ssa", bwt.ssa, 2 * bwt.r * (size_t)U)) return fail(PFB_ERR_IO, e);
+                if (emit("esa", bwt.esa, 2 * bwt.r * (size_t)U)) return fail(PFB_ERR_IO, e);
+            }
+            return PFB_OK;
+        } catch (const Error &e) { return fail(e.code, e.what()); }
+    }
+};
+
+}  // namespace pfb

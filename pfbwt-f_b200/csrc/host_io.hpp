@@ -1,0 +1,188 @@
+// host_io.hpp -- host side of the drop-in boundary: FASTA/FASTQ (plain or gzip,
+// file or stdin) reader with kseq semantics (include/kseq.h:178-216 as driven by
+// PfParser::add_fasta, include/pfparser.hpp:299-337) and writers for the
+// reference's on-disk formats (include/pfbwt_io.hpp:44-82,
+// 224-249; src/pfbwt-f.cpp:229-243).
+#pragma once
+#include <zlib.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <unistd.h>
+
+namespace pfb {
+
+// growable host byte buffer (pinned when the CUDA build asks for it)
+struct HostBytes {
+    uint8_t *p = nullptr;
+    size_t n = 0, cap = 0;
+    bool pinned = false;
+    void *(*alloc_fn)(size_t) = nullptr;
+    void (*free_fn)(void *) = nullptr;
+    ~HostBytes() { release(); }
+    void release() {
+        if (p) { if (free_fn) free_fn(p); else free(p); }
+        p = nullptr; n = cap = 0;
+    }
+    void reserve(size_t c) {
+        if (c <= cap) return;
+        size_t nc = cap ? cap : (1u << 20);
+        while (nc < c) nc = nc + nc / 2 + 4096;
+        uint8_t *q = (uint8_t *)(alloc_fn ? alloc_fn(nc) : malloc(nc));
+        if (!q) { fprintf(stderr, "out of host memory\n"); exit(1); }
+        if (p) { memcpy(q, p, n); if (free_fn) free_fn(p); else free(p); }
+        p = q; cap = nc;
+    }
+    void append(const uint8_t *s, size_t len) { reserve(n + len); memcpy(p + n, s, len); n += len; }
+    void append_fill(uint8_t c, size_t len) { reserve(n + len); memset(p + n, c, len); n += len; }
+};
+
+struct FastaResult {
+    uint64_t nrec = 0;
+    uint64_t total_len = 0;                 // sum of record lengths (no padding)
+    std::vector<std::string> names;
+    std::vector<uint64_t> starts;           // doc_starts_ (include/pfparser.hpp:321-325)
+};
+
+// Appends every record's bytes followed by w filler 'A's to `out` (the 'A's are
+// the inter-record padding of include/pfparser.hpp:333-337).  `base_n` is the
+// number of text bytes already held by the parser (for doc starts).
+// Returns 0, or -1 with err set.
+inline int read_fasta(const std::string &path, int w, HostBytes &out, FastaResult &res, bool store_docs, uint64_t base_n,
+                      std::string &err) {
+    gzFile fp = path == "-" ? gzdopen(fileno(stdin), "r") : gzopen(path.c_str(), "r");
+    if (fp == NULL) { err = "failed to open file!\n"; return -1; }
+    gzbuffer(fp, 1 << 20);
+    const size_t BUFSZ = 8u << 20;
+    std::vector<uint8_t> buf(BUFSZ);
+    // state machine over the byte stream
+    enum { SEEK_HDR, NAME, COMMENT, LINE_START, SEQ_LINE, PLUS_LINE, QUAL } state = SEEK_HDR;
+    uint64_t seq_len = 0, qual_len = 0;
+    std::string name;
+    bool in_record = false;
+    auto finish_record = [&]() {
+        out.append_fill('A', (size_t)w);
+        res.total_len += seq_len;
+        res.nrec++;
+        in_record = false;
+    };
+    auto begin_record = [&]() {
+        if (store_docs) {
+            uint64_t nb = base_n + out.n;      // text bytes before this record (all already padded)
+            res.starts.push_back(nb);
+        }
+        name.clear(); seq_len = 0; qual_len = 0; in_record = true;
+    };
+    for (;;) {
+        int got = gzread(fp, buf.data(), (unsigned)BUFSZ);
+        if (got < 0) { err = "error reading input"; gzclose(fp); return -1; }
+        if (got == 0) break;
+        const uint8_t *b = buf.data();
+        size_t i = 0, e = (size_t)got;
+        while (i < e) {
+            switch (state) {
+            case SEEK_HDR: {   // kseq.h:183-187: skip to the next '>' or '@' anywhere
+                while (i < e && b[i] != '>' && b[i] != '@') ++i;
+                if (i < e) { ++i; begin_record(); state = NAME; }
+                break;
+            }
+            case NAME: {       // name = up to first whitespace
+                while (i < e && !isspace(b[i])) { if (store_docs) name.push_back((char)b[i]); ++i; }
+                if (i < e) {
+                    if (store_docs) res.names.push_back(name);
+                    state = b[i] == '\n' ? LINE_START : COMMENT;
+                    ++i;
+                }
+                break;
+            }
+            case COMMENT: {
+                const uint8_t *q = (const uint8_t *)memchr(b + i, '\n', e - i);
+                if (q) { i = (size_t)(q - b) + 1; state = LINE_START; } else i = e;
+                break;
+            }
+            case LINE_START: { // kseq.h:194-198
+                uint8_t c = b[i];
+                if (c == '>' || c == '@') { finish_record(); ++i; begin_record(); state = NAME; }
+                else if (c == '+') { ++i; state = PLUS_LINE; }
+                else if (c == '\n') { ++i; }
+                else state = SEQ_LINE;
+                break;
+            }
+            case SEQ_LINE: {
+                const uint8_t *q = (const uint8_t *)memchr(b + i, '\n', e - i);
+                size_t le = q ? (size_t)(q - b) : e;
+                out.append(b + i, le - i);
+                seq_len += le - i;
+                i = le;
+                if (q) {
+                    // kseq.h:139: a trailing '\r' is dropped when the string is longer than 1
+                    if (seq_len > 1 && out.p[out.n - 1] == '\r') { out.n--; seq_len--; }
+                    ++i; state = LINE_START;
+                }
+                break;
+            }
+            case PLUS_LINE: {  // kseq.h:207
+                const uint8_t *q = (const uint8_t *)memchr(b + i, '\n', e - i);
+                if (q) { i = (size_t)(q - b) + 1; state = seq_len ? QUAL : SEEK_HDR; if (!seq_len) finish_record(); } else i = e;
+                break;
+            }
+            case QUAL: {       // kseq.h:209: read quality lines until as long as the sequence
+                while (i < e && qual_len < seq_len) { if (b[i] != '\n') ++qual_len; ++i; }
+                if (qual_len >= seq_len) { finish_record(); state = SEEK_HDR; }
+                break;
+            }
+            }
+        }
+    }
+    if (state == NAME && store_docs && in_record) res.names.push_back(name);
+    if (in_record) {
+        if (seq_len > 1 && state == SEQ_LINE && out.p[out.n - 1] == '\r') { out.n--; seq_len--; }
+        finish_record();
+    }
+    gzclose(fp);
+    return 0;
+}
+
+// ---------------------------------------------------------------- writers --
+inline int write_file(const std::string &path, const void *data, size_t bytes, std::string &err) {
+    FILE *f = fopen(path.c_str(), "wb");
+    if (!f) { err = "could not open " + path + " for writing"; return -1; }
+    const uint8_t *p = (const uint8_t *)data;
+    size_t done = 0;
+    while (done < bytes) {
+        size_t chunk = bytes - done < (1u << 30) ? bytes - done : (1u << 30);
+        if (fwrite(p + done, 1, chunk, f) != chunk) { fclose(f); err = "could not write file " + path; return -1; }
+        done += chunk;
+    }
+    if (fclose(f)) { err = "error closing " + path; return -1; }
+    return 0;
+}
+inline int read_file(const std::string &path, std::vector<uint8_t> &out, std::string &err) {
+    FILE *f = fopen(path.c_str(), "rb");
+    if (!f) { err = "error opening " + path; return -1; }
+    fseek(f, 0, SEEK_END);
+    long sz = ftell(f);
+    fseek(f, 0, SEEK_SET);
+    out.resize((size_t)sz);
+    if (sz && fread(out.data(), 1, (size_t)sz, f) != (size_t)sz) { fclose(f); err = "error reading " + path; return -1; }
+    fclose(f);
+    return 0;
+}
+// widen u32 -> U-byte little-endian integers
+inline std::vector<uint8_t> widen_u32(const uint32_t *v, size_t n, int U) {
+    std::vector<uint8_t> o(n * (size_t)U);
+    if (U == 4) memcpy(o.data(), v, n * 4);
+    else { uint64_t *q = (uint64_t *)o.data(); for (size_t i = 0; i < n; ++i) q[i] = v[i]; }
+    return o;
+}
+inline std::vector<uint8_t> narrow_u64(const uint64_t *v, size_t n, int U) {
+    std::vector<uint8_t> o(n * (size_t)U);
+    if (U == 8) memcpy(o.data(), v, n * 8);
+    else { uint32_t *q = (uint32_t *)o.data(); for (size_t i = 0; i < n; ++i) q[i] = (uint32_t)v[i]; }
+    return o;
+}
+
+}  // namespace pfb

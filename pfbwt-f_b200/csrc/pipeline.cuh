@@ -1,0 +1,979 @@
+// pipeline.cuh -- the PFP-BWT hot path as device stages (B200-native re-design of
+// the path SURVEY.md §8(a) lists; reference file:line cited per stage).
+//
+//   parse_text()        K0-K5a : normalise, Wang-hash trigger scan, compaction,
+//                                fingerprint dedup (GPU hash table, byte-verified),
+//                                phrase sort, ranks, .dict/.occ/.parse images
+//                                (include/pfparser.hpp:299-369,484-517,595-601)
+//   parse_bwt()         K5b-c  : suffix array of the parse by prefix doubling,
+//                                bwlast / bwsai / ilist (include/pfparser.hpp:379-467)
+//   build_bwt()         K6-K9  : dictionary suffix sort by prefix doubling, group
+//                                detection, segmented emission of BWT/SA, run
+//                                boundaries (include/pfbwt.hpp:96-223,
+//                                src/pfbwt-f.cpp:298-328)
+//
+// All stages are written against prim.cuh.  Data layout: byte text T' in HBM
+// (Dollar . S . Dollar^w, S 16-byte aligned), 32-bit dictionary / parse indices,
+// 64-bit text positions.
+#pragma once
+#include "prim.cuh"
+
+namespace pfb {
+
+typedef uint8_t u8;
+typedef uint32_t u32;
+typedef uint64_t u64;
+
+enum : int {
+    PFB_OK = 0,
+    PFB_ERR_ARG = -1,
+    PFB_ERR_INVALID_CHAR = -2,
+    PFB_ERR_LIMIT = -3,
+    PFB_ERR_NOMEM = -4,
+    PFB_ERR_CUDA = -5,
+    PFB_ERR_IO = -6,
+    PFB_ERR_ONE_WORD = -7,
+    PFB_ERR_INTERNAL = -8,
+    PFB_ERR_TOO_LONG_32 = -9,
+};
+
+static const u8 DOLLAR = 2, ENDOFWORD = 1, ENDOFDICT = 0;   // include/utils.h:8-10
+
+struct Params {
+    int w = 10;
+    u64 p = 100;
+    int bits = 32;              // width of uint_t in the reference binary being replaced
+    bool non_acgt_to_a = false;
+    bool get_sai = false;
+    bool verbose = false;
+};
+
+struct StageTimes {   // milliseconds, CUDA events on the pipeline stream
+    float normalise = 0, trigger = 0, compact = 0, fingerprint = 0, dedup = 0, phrase_sort = 0, dict_build = 0,
+          parse_sa = 0, parse_bwt = 0, dict_sort = 0, groups = 0, emit = 0, runs = 0;
+    u32 dedup_attempts = 0, phrase_sort_rounds = 0, parse_sa_rounds = 0, dict_sort_rounds = 0;
+};
+
+// the device-resident parse: what PfParser holds after finalize()+bwt_of_parse()
+struct DeviceParse {
+    u64 n = 0, P = 0, Dw = 0, dsize = 0;
+    DevBuf<u8> dict;        // dsize           .dict image
+    DevBuf<u32> wstart;     // Dw+1            word start offsets in dict
+    DevBuf<u32> occ;        // Dw              .occ
+    DevBuf<u32> parse;      // P+1             .parse (+ EOS slot)
+    DevBuf<u8> last;        // P               last_
+    DevBuf<u64> sai;        // P               sai_
+    DevBuf<u8> bwlast;      // P+1
+    DevBuf<u32> ilist;      // P+1
+    DevBuf<u64> bwsai;      // P+1
+    bool has_parse_bwt = false;
+};
+
+struct DeviceBwt {
+    u64 n = 0, r = 0, easy = 0, hard = 0;
+    DevBuf<u8> bwt;         // n+1
+    DevBuf<u8> sa;          // (n+1)*U bytes, U=bits/8 (empty unless any_sa)
+    DevBuf<u8> ssa, esa;    // r pairs of U-byte ints each
+};
+
+struct Timer {
+#ifndef PFB_EMU
+    cudaEvent_t a, b;
+    pfbStream_t s;
+    Timer(pfbStream_t st) : s(st) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, s); }
+    float stop() { cudaEventRecord(b, s); cudaEventSynchronize(b); float ms = 0; cudaEventElapsedTime(&ms, a, b); cudaEventRecord(a, s); return ms; }
+    ~Timer() { cudaEventDestroy(a); cudaEventDestroy(b); }
+#else
+    Timer(pfbStream_t) {}
+    float stop() { return 0.f; }
+#endif
+};
+
+// ---------------------------------------------------------------- symbols --
+// include/hash.hpp:12-21
+PFB_HD inline u64 wang_hash(u64 key) {
+    key = (~key) + (key << 21);
+    key = key ^ (key >> 24);
+    key = (key + (key << 3)) + (key << 8);
+    key = key ^ (key >> 14);
+    key = (key + (key << 2)) + (key << 4);
+    key = key ^ (key >> 28);
+    key = key + (key << 31);
+    return key;
+}
+// seq_nt4_ntoa_table restricted to the normalised alphabet (src/utils.c:139-161):
+// A,N -> 0  C -> 1  G -> 2  T,'-' -> 3
+PFB_HD inline u32 nt_code(u8 c) {
+    u32 x = (c >> 1) & 3;       // A->0 C->1 G->3 T->2 '-'->2
+    x ^= x >> 1;                // A->0 C->1 G->2 T->3 '-'->3
+    return c == 'N' ? 0u : x;
+}
+// order-preserving 3-bit code of the 8 bytes that can occur in T'/dict:
+// 0x01<0x02<'-'<'A'<'C'<'G'<'N'<'T'  ->  0..7   (0 doubles as "past the end")
+PFB_HD inline u32 sym3(u8 c) {
+    switch (c) {
+    case 1: return 0;
+    case 2: return 1;
+    case '-': return 2;
+    case 'A': return 3;
+    case 'C': return 4;
+    case 'G': return 5;
+    case 'N': return 6;
+    case 'T': return 7;
+    default: return 0;   // EndOfDict (0x00)
+    }
+}
+
+// divisibility of a 64-bit value by a runtime constant without a division:
+// d = 2^k * d', d' odd:  d | x  <=>  ror(x * inv(d'), k) <= floor((2^64-1)/d)
+struct DivTest {
+    u64 inv = 1, lim = ~0ull;
+    u32 k = 0;
+    static DivTest make(u64 d) {
+        DivTest t;
+        u32 k = 0;
+        u64 dd = d;
+        while ((dd & 1) == 0) { dd >>= 1; ++k; }
+        u64 x = dd;   // Newton: x*dd = 1 mod 2^3 initially
+        for (int i = 0; i < 6; ++i) x *= 2 - dd * x;
+        t.inv = x; t.k = k; t.lim = ~0ull / d;
+        return t;
+    }
+    PFB_HD inline bool divides(u64 x) const {
+        u64 m = x * inv;
+        m = k ? ((m >> k) | (m << (64 - k))) : m;
+        return m <= lim;
+    }
+};
+
+// ---------------------------------------------------------------------------
+// K0  normalise the record bytes in place: toupper, optional non-ACGT -> 'A',
+//     validate against the hasher's alphabet.   (include/pfparser.hpp:337-346,
+//     include/hash.hpp:30-31).  8 bytes per thread, S is 16-byte aligned.
+// ---------------------------------------------------------------------------
+inline void k_normalise(u8 *S, u64 n, bool non_acgt_to_a, u64 *d_errpos, pfbStream_t st) {
+    u64 nwords = (n + 7) / 8;
+    launch_for(nwords, st, PFB_LAMBDA(u64 i) {
+        u64 base = i * 8;
+        u64 lim = n - base < 8 ? n - base : 8;
+        u64 x = 0;
+        if (lim == 8) x = *reinterpret_cast<const u64 *>(S + base);
+        else for (u64 j = 0; j < lim; ++j) x |= (u64)S[base + j] << (8 * j);
+        u64 y = 0;
+        for (u64 j = 0; j < lim; ++j) {
+            u32 c = (u32)(x >> (8 * j)) & 0xff;
+            if (c >= 'a' && c <= 'z') c -= 32;
+            bool acgt = (c == 'A') | (c == 'C') | (c == 'G') | (c == 'T');
+            if (non_acgt_to_a && !acgt) { c = 'A'; acgt = true; }
+            if (!(acgt | (c == 'N') | (c == '-'))) atomic_min(d_errpos, base + j);
+            y |= (u64)c << (8 * j);
+        }
+        if (lim == 8) *reinterpret_cast<u64 *>(S + base) = y;
+        else for (u64 j = 0; j < lim; ++j) S[base + j] = (u8)(y >> (8 * j));
+    });
+}
+
+// ---------------------------------------------------------------------------
+// K1  trigger bitmap: bit q of word q/32 set iff q > w and
+//     wang_hash(kmer ending at T'[q]) % p == 0          (include/pfparser.hpp:347)
+//     Tp points at T'[0]; valid q range is [w+1, n].
+// ---------------------------------------------------------------------------
+inline void k_trigger_words(const u8 *Tp, u64 n, int w, DivTest dt, u32 *trig, u32 *cnt, u64 nwords, pfbStream_t st) {
+    const u64 mask = (w >= 32) ? ~0ull : ((1ull << (2 * w)) - 1);
+    launch_for(nwords, st, PFB_LAMBDA(u64 t) {
+        u64 q0 = t * 32, q1 = q0 + 31;
+        if (q1 > n) q1 = n;
+        u64 qs = q0 < (u64)w + 1 ? (u64)w + 1 : q0;
+        u32 bits = 0;
+        if (qs <= q1) {
+            u64 kmer = 0;
+            for (u64 j = qs - (u64)w + 1; j < qs; ++j) kmer = (kmer << 2) | nt_code(Tp[j]);
+            for (u64 q = qs; q <= q1; ++q) {
+                kmer = ((kmer << 2) | nt_code(Tp[q])) & mask;
+                if (dt.divides(wang_hash(kmer))) bits |= 1u << (q - q0);
+            }
+        }
+        trig[t] = bits;
+        cnt[t] = (u32)popc32(bits);
+    });
+}
+
+// K2  scatter trigger positions -> ends[] (sorted), ends[P-1] = n+w
+inline void k_scatter_ends(const u32 *trig, const u32 *wordoff, u64 nwords, u64 *ends, u64 P, u64 n, int w, pfbStream_t st) {
+    launch_for(nwords, st, PFB_LAMBDA(u64 t) {
+        u32 bits = trig[t];
+        u64 o = wordoff[t];
+        while (bits) {
+            int b = ffs32(bits) - 1;
+            ends[o++] = t * 32 + (u64)b;
+            bits &= bits - 1;
+        }
+        if (t == 0) ends[P - 1] = n + (u64)w;
+    });
+}
+
+PFB_HD inline u64 phrase_start(const u64 *ends, u64 k, int w) { return k ? ends[k - 1] - (u64)w + 1 : 0; }
+
+// ---------------------------------------------------------------------------
+// K3  phrase fingerprints: fp_b(k) = sum_j T'[s_k+j] * B^(len-1-j)  (mod 2^64) for two
+//     odd bases.  One logical thread per 64-byte slice of T'; a slice adds its
+//     share of every phrase it overlaps with an atomicAdd, so Mbp-long phrases
+//     are spread over many threads.
+// ---------------------------------------------------------------------------
+static const u64 FP_B1 = 0x9E3779B97F4A7C15ull, FP_B2 = 0xC2B2AE3D27D4EB4Full;
+PFB_HD inline u64 pow_u64(u64 b, u64 e) {
+    u64 r = 1;
+    while (e) { if (e & 1) r *= b; b *= b; e >>= 1; }
+    return r;
+}
+inline void k_fingerprint(const u8 *Tp, u64 tlen, const u64 *ends, u64 P, int w, const u32 *wordoff, u64 nwords, u64 *fp1,
+                          u64 *fp2, pfbStream_t st) {
+    u64 nslices = (tlen + 63) / 64;
+    launch_for(nslices, st, PFB_LAMBDA(u64 c) {
+        u64 lo = c * 64, hi = lo + 63;
+        if (hi > tlen - 1) hi = tlen - 1;
+        u64 k = (lo / 32 < nwords) ? (u64)wordoff[lo / 32] : P - 1;
+        for (; k < P; ++k) {
+            u64 s = phrase_start(ends, k, w), e = ends[k];
+            if (s > hi) break;
+            u64 a = s > lo ? s : lo, b = e < hi ? e : hi;
+            u64 h1 = 0, h2 = 0;
+            for (u64 j = a; j <= b; ++j) { u64 ch = Tp[j]; h1 = h1 * FP_B1 + ch; h2 = h2 * FP_B2 + ch; }
+            u64 rem = e - b;
+            if (rem) { h1 *= pow_u64(FP_B1, rem); h2 *= pow_u64(FP_B2, rem); }
+            atomic_add(&fp1[k], h1);
+            atomic_add(&fp2[k], h2);
+        }
+    });
+}
+
+PFB_HD inline u64 mix64(u64 x) {   // splitmix64 finaliser
+    x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull;
+    x ^= x >> 27; x *= 0x94D049BB133111EBull;
+    x ^= x >> 31;
+    return x;
+}
+
+// ---------------------------------------------------------------------------
+// K4  dedup: open-addressing table keyed by a 64-bit mix of (fp1, fp2, len).
+//     The representative of a phrase is the smallest text-order index with the
+//     same key; every other occurrence is byte-verified against it (slice-wise),
+//     so a fingerprint collision can never change the output: it only sets a flag
+//     and the table is rebuilt with another seed.   Replaces the std::map insert of
+//     process_phrase (include/pfparser.hpp:595-598).
+// ---------------------------------------------------------------------------
+inline void k_ht_insert(const u64 *fp1, const u64 *fp2, const u64 *ends, u64 P, int w, u64 seed, u64 *tkey, u32 *trep,
+                        u64 tmask, u32 *slot, pfbStream_t st) {
+    launch_for(P, st, PFB_LAMBDA(u64 k) {
+        u64 len = ends[k] - phrase_start(ends, k, w) + 1;
+        u64 key = mix64(fp1[k] + seed * 0x632BE59BD9B4E019ull) ^ mix64(fp2[k] ^ (len * 0xD6E8FEB86659FD93ull) ^ seed);
+        if (key == 0) key = 1;
+        u64 h = (key >> 17) & tmask;
+        for (;;) {
+            u64 old = atomic_cas(&tkey[h], (u64)0, key);
+            if (old == 0 || old == key) {
+                atomic_min(&trep[h], (u32)k);
+                slot[k] = (u32)h;
+                break;
+            }
+            h = (h + 1) & tmask;
+        }
+    });
+}
+inline void k_verify(const u8 *Tp, u64 tlen, const u64 *ends, u64 P, int w, const u32 *wordoff, u64 nwords, const u32 *rep,
+                     u32 *d_flag, pfbStream_t st) {
+    u64 nslices = (tlen + 63) / 64;
+    launch_for(nslices, st, PFB_LAMBDA(u64 c) {
+        u64 lo = c * 64, hi = lo + 63;
+        if (hi > tlen - 1) hi = tlen - 1;
+        u64 k = (lo / 32 < nwords) ? (u64)wordoff[lo / 32] : P - 1;
+        for (; k < P; ++k) {
+            u64 s = phrase_start(ends, k, w), e = ends[k];
+            if (s > hi) break;
+            u64 r = rep[k];
+            if (r == k) continue;
+            u64 rs = phrase_start(ends, r, w), re = ends[r];
+            bool bad = (re - rs) != (e - s);
+            if (!bad) {
+                u64 a = s > lo ? s : lo, b = e < hi ? e : hi;
+                for (u64 j = a; j <= b; ++j) bad |= Tp[j] != Tp[rs + (j - s)];
+            }
+            if (bad) atomic_or(d_flag, 1u);
+        }
+    });
+}
+
+// pack `cnt` (<=21) 3-bit symbols of a string starting at p[off], total length len
+// (symbols past the end are 0), most significant symbol first.
+PFB_HD inline u64 pack_syms(const u8 *p, u64 len, u64 off, int cnt) {
+    u64 key = 0;
+    for (int j = 0; j < cnt; ++j) {
+        u64 o = off + (u64)j;
+        key = (key << 3) | (o < len ? sym3(p[o]) : 0u);
+    }
+    return key;
+}
+
+struct Workspace {
+    Scratch sc;
+    pfbStream_t st = 0;
+};
+
+// compaction helper: out positions for flagged items; returns number selected
+inline u64 scan_flags(const u8 *flags, u32 *idx, u64 n, Workspace &ws) {
+    if (n == 0) return 0;
+    exclusive_sum<u8, u32>(flags, idx, n, ws.sc, ws.st);
+    u32 last_idx = read_scalar(idx + (n - 1), ws.st);
+    u8 last_flag = read_scalar(flags + (n - 1), ws.st);
+    return (u64)last_idx + last_flag;
+}
+
+// ---------------------------------------------------------------------------
+// K5a  lexicographic sort of the distinct phrases (strcmp order,
+//      include/pfparser.hpp:494-502) by MSD rounds of packed 3-bit symbols:
+//      round 0 sorts on 21 symbols; later rounds re-sort only the members of tie
+//      groups on (dense group id, next symbols).
+//      order[r] = text-order index k of the phrase of rank r.
+// ---------------------------------------------------------------------------
+inline int sort_phrases(const u8 *Tp, const u64 *ends, int w, DevBuf<u32> &order, u64 Dw, Workspace &ws, u32 *rounds_out,
+                        std::string &err) {
+    pfbStream_t st = ws.st;
+    DevBuf<u64> key_a(Dw), key_b(Dw);
+    DevBuf<u32> val_b(Dw);
+    DevBuf<u8> flag(Dw);
+    {
+        u64 *ka = key_a.get(); const u32 *ord = order.get();
+        launch_for(Dw, st, PFB_LAMBDA(u64 j) {
+            u64 k = ord[j];
+            u64 s = phrase_start(ends, k, w);
+            ka[j] = pack_syms(Tp + s, ends[k] - s + 1, 0, 21);
+        });
+    }
+    sort_pairs(key_a, key_b, order, val_b, Dw, 0, 63, ws.sc, st);
+    {
+        const u64 *ka = key_a.get(); u8 *fl = flag.get();
+        launch_for(Dw, st, PFB_LAMBDA(u64 j) { fl[j] = (j == 0 || ka[j] != ka[j - 1]) ? 1 : 0; });
+    }
+    u64 depth = 21;
+    u32 rounds = 1;
+    DevBuf<u8> act(Dw), acthead(Dw);
+    DevBuf<u32> aidx(Dw), gidx(Dw);
+    for (;;) {
+        {
+            const u8 *fl = flag.get(); u8 *ac = act.get(); u8 *ah = acthead.get();
+            launch_for(Dw, st, PFB_LAMBDA(u64 j) {
+                bool single = fl[j] && (j + 1 == Dw || fl[j + 1]);
+                ac[j] = single ? 0 : 1;
+                ah[j] = (!single && fl[j]) ? 1 : 0;
+            });
+        }
+        u64 m = scan_flags(act.get(), aidx.get(), Dw, ws);
+        if (m == 0) break;
+        u64 G = scan_flags(acthead.get(), gidx.get(), Dw, ws);
+        int gbits = bits_for(G ? G - 1 : 0);
+        int nsym = (63 - gbits) / 3;
+        if (nsym > 21) nsym = 21;
+        if (nsym < 1) { err = "phrase sort: too many tie groups"; return PFB_ERR_INTERNAL; }
+        if (rounds > 200000) { err = "phrase sort: distinct phrases share a prefix longer than supported"; return PFB_ERR_LIMIT; }
+        DevBuf<u32> apos(m), aval(m), aval_b(m);
+        DevBuf<u64> akey(m), akey_b(m);
+        {
+            const u8 *ac = act.get(); const u8 *fl = flag.get();
+            const u32 *ai = aidx.get(); const u32 *gi = gidx.get(); const u32 *ord = order.get();
+            u32 *ap = apos.get(); u32 *av = aval.get(); u64 *ak = akey.get();
+            launch_for(Dw, st, PFB_LAMBDA(u64 j) {
+                if (!ac[j]) return;
+                u32 a = ai[j];
+                u64 gid = (u64)gi[j] + (fl[j] ? 1 : 0) - 1;
+                u64 k = ord[j];
+                u64 s = phrase_start(ends, k, w);
+                ap[a] = (u32)j; av[a] = (u32)k;
+                ak[a] = (gid << (3 * nsym)) | pack_syms(Tp + s, ends[k] - s + 1, depth, nsym);
+            });
+        }
+        sort_pairs(akey, akey_b, aval, aval_b, m, 0, gbits + 3 * nsym, ws.sc, st);
+        {
+            const u32 *ap = apos.get(); const u32 *av = aval.get(); const u64 *ak = akey.get();
+            u32 *ord = order.get(); u8 *fl = flag.get();
+            launch_for(m, st, PFB_LAMBDA(u64 a) {
+                u32 j = ap[a];
+                ord[j] = av[a];
+                fl[j] = (a == 0 || ak[a] != ak[a - 1]) ? 1 : 0;
+            });
+        }
+        depth += (u64)nsym;
+        ++rounds;
+    }
+    if (rounds_out) *rounds_out = rounds;
+    return PFB_OK;
+}
+
+// ---------------------------------------------------------------------------
+// Prefix doubling (Larsson-Sadakane numbering: rank = position of the group head
+// in sa).  On entry sa is sorted by the first h symbols, flag[j]=1 at group heads,
+// rank[i] = head position of suffix i's group.  `done(idx,h)` says whether a tied
+// suffix is already complete within h symbols (dictionary suffixes end at their
+// EndOfWord; equal complete suffixes stay one group).  Replaces sacak_int /
+// gsacak (gsa/gsacak.c:2499-2524).
+// ---------------------------------------------------------------------------
+template <class DoneFn>
+inline int prefix_doubling(DevBuf<u32> &sa, DevBuf<u32> &rank, DevBuf<u8> &flag, u64 m, u64 h, DoneFn done, Workspace &ws,
+                           u32 *rounds_out, std::string &err) {
+    pfbStream_t st = ws.st;
+    DevBuf<u8> act(m), acthead(m);
+    DevBuf<u32> aidx(m), gidx(m);
+    const int rbits = bits_for(m ? m - 1 : 0);
+    u32 rounds = 0;
+    for (;;) {
+        {
+            const u8 *fl = flag.get(); const u32 *sp = sa.get(); u8 *ac = act.get();
+            launch_for(m, st, PFB_LAMBDA(u64 j) {
+                bool single = fl[j] && (j + 1 == m || fl[j + 1]);
+                ac[j] = (single || done(sp[j], h)) ? 0 : 1;
+            });
+            // a group is active as a whole (done() is uniform over a tie group), so the
+            // first active member of a group is its head
+            u8 *ah = acthead.get();
+            launch_for(m, st, PFB_LAMBDA(u64 j) { ah[j] = (ac[j] && fl[j]) ? 1 : 0; });
+        }
+        u64 ma = scan_flags(act.get(), aidx.get(), m, ws);
+        if (ma == 0) break;
+        u64 G = scan_flags(acthead.get(), gidx.get(), m, ws);
+        int gbits = bits_for(G ? G - 1 : 0);
+        if (gbits + rbits > 64) { err = "prefix doubling: key overflow"; return PFB_ERR_INTERNAL; }
+        if (rounds > 64) { err = "prefix doubling did not converge"; return PFB_ERR_INTERNAL; }
+        DevBuf<u32> apos(ma), aval(ma), aval_b(ma);
+        DevBuf<u64> akey(ma), akey_b(ma);
+        {
+            const u8 *ac = act.get(); const u8 *fl = flag.get();
+            const u32 *ai = aidx.get(); const u32 *gi = gidx.get(); const u32 *sp = sa.get(); const u32 *rk = rank.get();
+            u32 *ap = apos.get(); u32 *av = aval.get(); u64 *ak = akey.get();
+            launch_for(m, st, PFB_LAMBDA(u64 j) {
+                if (!ac[j]) return;
+                u32 a = ai[j];
+                u64 gid = (u64)gi[j] + (fl[j] ? 1 : 0) - 1;
+                u64 i = sp[j];
+                u64 nx = i + h;
+                u64 r2 = nx < m ? (u64)rk[nx] : 0;
+                ap[a] = (u32)j; av[a] = (u32)i;
+                ak[a] = (gid << rbits) | r2;
+            });
+        }
+        sort_pairs(akey, akey_b, aval, aval_b, ma, 0, gbits + rbits, ws.sc, st);
+        DevBuf<u32> hd(ma), hd2(ma);
+        {
+            const u32 *ap = apos.get(); const u32 *av = aval.get(); const u64 *ak = akey.get();
+            u32 *sp = sa.get(); u8 *fl = flag.get(); u32 *hp = hd.get();
+            launch_for(ma, st, PFB_LAMBDA(u64 a) {
+                u32 j = ap[a];
+                sp[j] = av[a];
+                bool head = (a == 0 || ak[a] != ak[a - 1]);
+                fl[j] = head ? 1 : 0;
+                hp[a] = head ? j : 0;
+            });
+        }
+        inclusive_max(hd.get(), hd2.get(), ma, ws.sc, st);
+        {
+            const u32 *av = aval.get(); const u32 *hp = hd2.get(); u32 *rk = rank.get();
+            launch_for(ma, st, PFB_LAMBDA(u64 a) { rk[av[a]] = hp[a]; });
+        }
+        h *= 2;
+        ++rounds;
+    }
+    if (rounds_out) *rounds_out = rounds;
+    return PFB_OK;
+}
+
+// heads/ranks from sorted keys: flag[j] = key differs from predecessor,
+// rank[sa[j]] = position of the group head
+inline void ranks_from_flags(const DevBuf<u32> &sa, DevBuf<u8> &flag, DevBuf<u32> &rank, u64 m, Workspace &ws) {
+    pfbStream_t st = ws.st;
+    DevBuf<u32> hd(m), hd2(m);
+    {
+        const u8 *fl = flag.get(); u32 *hp = hd.get();
+        launch_for(m, st, PFB_LAMBDA(u64 j) { hp[j] = fl[j] ? (u32)j : 0; });
+    }
+    inclusive_max(hd.get(), hd2.get(), m, ws.sc, st);
+    {
+        const u32 *sp = sa.get(); const u32 *hp = hd2.get(); u32 *rk = rank.get();
+        launch_for(m, st, PFB_LAMBDA(u64 j) { rk[sp[j]] = hp[j]; });
+    }
+}
+
+// largest d with wstart[d] <= pos   (wstart has Dw+1 entries, wstart[Dw] = dsize-1)
+PFB_HD inline u32 word_of(const u32 *wstart, u32 Dw, u32 pos) {
+    u32 lo = 0, hi = Dw;   // answer in [lo, hi)
+    while (hi - lo > 1) {
+        u32 mid = lo + (hi - lo) / 2;
+        if (wstart[mid] <= pos) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+// ===========================================================================
+// parse_text: T' bytes already on the device and normalised
+// ===========================================================================
+struct TextOnDevice {
+    DevBuf<u8> buf;     // 16 pad | S (n) | Dollar^w | pad
+    u64 n = 0;
+    u8 *Tp() const { return buf.get() + 15; }   // T'[0] (the leading Dollar)
+    u8 *S() const { return buf.get() + 16; }
+};
+
+inline int parse_text(const TextOnDevice &T, const Params &prm, DeviceParse &out, Workspace &ws, StageTimes &tm, std::string &err) {
+    pfbStream_t st = ws.st;
+    const int w = prm.w;
+    const u64 n = T.n;
+    const u8 *Tp = T.Tp();
+    const u64 tlen = n + (u64)w + 1;
+    if (w < 1 || w > 31) { err = "window size w must be < 32!"; return PFB_ERR_ARG; }
+    if (prm.p < 1) { err = "modulus p must be >= 1"; return PFB_ERR_ARG; }
+    if (n == 0) { err = "empty input"; return PFB_ERR_ARG; }
+    Timer timer(st);
+
+    // K1 trigger bitmap ------------------------------------------------------
+    const u64 nwords = n / 32 + 1;   // bits 0..n
+    DevBuf<u32> trig(nwords), cnt(nwords), wordoff(nwords);
+    k_trigger_words(Tp, n, w, DivTest::make(prm.p), trig.get(), cnt.get(), nwords, st);
+    tm.trigger = timer.stop();
+
+    // K2 compaction ------------------------------------------------------------
+    exclusive_sum<u32, u32>(cnt.get(), wordoff.get(), nwords, ws.sc, st);
+    u64 ntrig = (u64)read_scalar(wordoff.get() + (nwords - 1), st) + read_scalar(cnt.get() + (nwords - 1), st);
+    const u64 P = ntrig + 1;
+    if (prm.bits == 32 && P > 0x7FFFFFFEull) { err = "Input containing more than 2^31-2 phrases! Please use 64 bit version"; return PFB_ERR_LIMIT; }
+    if (P > 0xFFFFFFFEull) { err = "Input containing more than 2^32-2 phrases! This is currently a hard limit"; return PFB_ERR_LIMIT; }
+    cnt.release();
+    out.sai.alloc(P);   // sai_[k] == end position of phrase k (include/pfparser.hpp:600)
+    u64 *ends = out.sai.get();
+    k_scatter_ends(trig.get(), wordoff.get(), nwords, ends, P, n, w, st);
+    trig.release();
+    out.last.alloc(P);
+    {
+        u8 *last = out.last.get();
+        launch_for(P, st, PFB_LAMBDA(u64 k) { last[k] = Tp[ends[k] - (u64)w]; });   // include/pfparser.hpp:599
+    }
+    tm.compact = timer.stop();
+
+    // K3 fingerprints ------------------------------------------------------------
+    DevBuf<u64> fp1(P), fp2(P);
+    dev_memset(fp1.get(), 0, P * 8, st);
+    dev_memset(fp2.get(), 0, P * 8, st);
+    k_fingerprint(Tp, tlen, ends, P, w, wordoff.get(), nwords, fp1.get(), fp2.get(), st);
+    tm.fingerprint = timer.stop();
+
+    // K4 dedup -------------------------------------------------------------------
+    u64 tsize = 1024;
+    while (tsize < 2 * P) tsize <<= 1;
+    DevBuf<u32> rep(P);
+    {
+        DevBuf<u64> tkey(tsize);
+        DevBuf<u32> trep(tsize), slot(P), flagbuf(1);
+        u32 attempt = 0;
+        for (;; ++attempt) {
+            if (attempt >= 8) { err = "phrase fingerprint collisions could not be resolved"; return PFB_ERR_INTERNAL; }
+            dev_memset(tkey.get(), 0, tsize * 8, st);
+            dev_memset(trep.get(), 0xff, tsize * 4, st);
+            dev_memset(flagbuf.get(), 0, 4, st);
+            k_ht_insert(fp1.get(), fp2.get(), ends, P, w, attempt, tkey.get(), trep.get(), tsize - 1, slot.get(), st);
+            {
+                const u32 *sl = slot.get(); const u32 *tr = trep.get(); u32 *rp = rep.get();
+                launch_for(P, st, PFB_LAMBDA(u64 k) { rp[k] = tr[sl[k]]; });
+            }
+            k_verify(Tp, tlen, ends, P, w, wordoff.get(), nwords, rep.get(), flagbuf.get(), st);
+            if (read_scalar(flagbuf.get(), st) == 0) break;
+        }
+        tm.dedup_attempts = attempt + 1;
+    }
+    fp1.release(); fp2.release(); wordoff.release();
+    // distinct phrases (representatives) and their occurrence counts
+    DevBuf<u32> cntk(P);
+    dev_memset(cntk.get(), 0, P * 4, st);
+    DevBuf<u32> order;
+    u64 Dw;
+    {
+        DevBuf<u8> isrep(P);
+        DevBuf<u32> didx(P);
+        const u32 *rp = rep.get(); u8 *ir = isrep.get(); u32 *ck = cntk.get();
+        launch_for(P, st, PFB_LAMBDA(u64 k) {
+            ir[k] = rp[k] == (u32)k ? 1 : 0;
+            atomic_add(&ck[rp[k]], 1u);
+        });
+        Dw = scan_flags(isrep.get(), didx.get(), P, ws);
+        order.alloc(Dw);
+        u32 *ord = order.get(); const u32 *di = didx.get();
+        launch_for(P, st, PFB_LAMBDA(u64 k) { if (ir[k]) ord[di[k]] = (u32)k; });
+    }
+    tm.dedup = timer.stop();
+
+    // K5a phrase sort --------------------------------------------------------------
+    int rc = sort_phrases(Tp, ends, w, order, Dw, ws, &tm.phrase_sort_rounds, err);
+    if (rc) return rc;
+    tm.phrase_sort = timer.stop();
+
+    // ranks, occ, dict image ---------------------------------------------------------
+    out.n = n; out.P = P; out.Dw = Dw;
+    out.parse.alloc(P + 1);
+    out.occ.alloc(Dw);
+    {
+        DevBuf<u32> rankc(P);
+        u32 *rc_ = rankc.get(); const u32 *ord = order.get(); const u32 *ck = cntk.get(); u32 *oc = out.occ.get();
+        launch_for(Dw, st, PFB_LAMBDA(u64 r) { rc_[ord[r]] = (u32)r + 1; oc[r] = ck[ord[r]]; });
+        u32 *pr = out.parse.get(); const u32 *rp = rep.get();
+        launch_for(P + 1, st, PFB_LAMBDA(u64 k) { pr[k] = k < P ? rc_[rp[k]] : 0u; });   // include/pfparser.hpp:504-517
+    }
+    rep.release(); cntk.release();
+    DevBuf<u64> wl(Dw + 1), ws64(Dw + 1);
+    {
+        u64 *wlp = wl.get(); const u32 *ord = order.get();
+        launch_for(Dw + 1, st, PFB_LAMBDA(u64 r) {
+            if (r == Dw) { wlp[r] = 0; return; }
+            u64 k = ord[r];
+            wlp[r] = ends[k] - phrase_start(ends, k, w) + 2;   // phrase + EndOfWord
+        });
+    }
+    exclusive_sum<u64, u64>(wl.get(), ws64.get(), Dw + 1, ws.sc, st);
+    u64 dsize = read_scalar(ws64.get() + Dw, st) + 1;
+    if (dsize > 0xFFFFFFF0ull) { err = "dictionary larger than 2^32 bytes is not supported yet"; return PFB_ERR_LIMIT; }
+    out.dsize = dsize;
+    out.wstart.alloc(Dw + 1);
+    out.dict.alloc(dsize);
+    {
+        const u64 *w64 = ws64.get(); u32 *wsp = out.wstart.get();
+        launch_for(Dw + 1, st, PFB_LAMBDA(u64 r) { wsp[r] = (u32)w64[r]; });
+        u8 *dict = out.dict.get(); const u32 *ord = order.get();
+        // 32 logical lanes per word copy it with unit stride (include/pfbwt_io.hpp:71-82)
+        launch_for(Dw * 32, st, PFB_LAMBDA(u64 i) {
+            u64 r = i / 32, lane = i % 32;
+            u64 k = ord[r];
+            u64 s = phrase_start(ends, k, w), len = ends[k] - s + 1;
+            u64 d0 = w64[r];
+            for (u64 j = lane; j < len; j += 32) dict[d0 + j] = Tp[s + j];
+            if (lane == 0) dict[d0 + len] = ENDOFWORD;
+            if (i == 0) dict[dsize - 1] = ENDOFDICT;
+        });
+    }
+    tm.dict_build = timer.stop();
+    return PFB_OK;
+}
+
+// ===========================================================================
+// parse_bwt: SA of parse.0, then bwlast / bwsai / ilist (include/pfparser.hpp:379-467)
+// ===========================================================================
+inline int parse_bwt(DeviceParse &pp, const Params &prm, Workspace &ws, StageTimes &tm, std::string &err) {
+    pfbStream_t st = ws.st;
+    const u64 P = pp.P, Dw = pp.Dw;
+    if (P == 1) { err = "error: only one dict word total. Re-run with a smaller p modulus"; return PFB_ERR_ONE_WORD; }
+    const u64 m = P + 1;
+    Timer timer(st);
+    DevBuf<u32> sa(m), rank(m);
+    DevBuf<u8> flag(m);
+    {
+        // initial order on two symbols: key = R[i] << sbits | R[i+1]
+        const int sbits = bits_for(Dw);
+        DevBuf<u64> key_a(m), key_b(m);
+        DevBuf<u32> val_b(m);
+        const u32 *R = pp.parse.get(); u64 *ka = key_a.get(); u32 *sp = sa.get();
+        launch_for(m, st, PFB_LAMBDA(u64 i) {
+            u64 a = R[i], b = i + 1 < m ? R[i + 1] : 0;
+            ka[i] = (a << sbits) | b;
+            sp[i] = (u32)i;
+        });
+        sort_pairs(key_a, key_b, sa, val_b, m, 0, 2 * sbits, ws.sc, st);
+        const u64 *ks = key_a.get(); u8 *fl = flag.get();
+        launch_for(m, st, PFB_LAMBDA(u64 j) { fl[j] = (j == 0 || ks[j] != ks[j - 1]) ? 1 : 0; });
+    }
+    ranks_from_flags(sa, flag, rank, m, ws);
+    int rc = prefix_doubling(sa, rank, flag, m, 2, PFB_LAMBDA(u32, u64) { return false; }, ws, &tm.parse_sa_rounds, err);
+    if (rc) return rc;
+    rank.release(); flag.release();
+    tm.parse_sa = timer.stop();
+
+    pp.bwlast.alloc(m);
+    pp.bwsai.alloc(m);
+    pp.ilist.alloc(m);
+    {
+        DevBuf<u32> bwtp(m), bwtp_b(m), il_b(m);
+        const u32 *sp = sa.get(); const u32 *R = pp.parse.get(); const u8 *last = pp.last.get(); const u64 *sai = pp.sai.get();
+        u8 *bl = pp.bwlast.get(); u64 *bs = pp.bwsai.get(); u32 *bp = bwtp.get(); u32 *il = pp.ilist.get();
+        launch_for(m, st, PFB_LAMBDA(u64 i) {     // include/pfparser.hpp:429-451
+            u64 s = sp[i];
+            il[i] = (u32)i;
+            if (s == 0) { bp[i] = 0; bl[i] = 0; bs[i] = 0; }
+            else {
+                bl[i] = s == 1 ? last[P - 1] : last[s - 2];
+                bs[i] = sai[s - 1];
+                bp[i] = R[s - 1];
+            }
+        });
+        // ilist = positions grouped by BWT(P) symbol, ascending inside a symbol
+        // (the F[]-driven counting sort of include/pfparser.hpp:452-462) = stable sort by symbol
+        sort_pairs(bwtp, bwtp_b, pp.ilist, il_b, m, 0, bits_for(Dw), ws.sc, st);
+    }
+    pp.has_parse_bwt = true;
+    tm.parse_bwt = timer.stop();
+    return PFB_OK;
+}
+
+// ===========================================================================
+// build_bwt: dict suffix sort + emission (include/pfbwt.hpp:96-223,
+// src/pfbwt-f.cpp:298-328)
+// ===========================================================================
+inline int build_bwt(const DeviceParse &pp, const Params &prm, bool want_sa, bool want_rssa, DeviceBwt &out, Workspace &ws,
+                     StageTimes &tm, std::string &err) {
+    pfbStream_t st = ws.st;
+    const u64 D = pp.dsize, Dw = pp.Dw, n = pp.n, P = pp.P;
+    const u64 w = (u64)prm.w;
+    const bool any_sa = want_sa || want_rssa;
+    const int U = prm.bits / 8;
+    if (!pp.has_parse_bwt) { err = "parse BWT (bwlast/ilist) not available"; return PFB_ERR_ARG; }
+    if (any_sa && pp.bwsai.size() == 0) { err = "bwsai not available"; return PFB_ERR_ARG; }
+    Timer timer(st);
+    const u8 *dict = pp.dict.get();
+    const u32 *wstart = pp.wstart.get();
+
+    // K6 dictionary suffix sort -----------------------------------------------------
+    DevBuf<u32> sa(D), rank(D);
+    DevBuf<u8> flag(D);
+    {
+        DevBuf<u64> key_a(D), key_b(D);
+        DevBuf<u32> val_b(D);
+        u64 *ka = key_a.get(); u32 *sp = sa.get();
+        launch_for(D, st, PFB_LAMBDA(u64 i) {
+            // 21 symbols up to and including the word's EndOfWord, then zeros
+            u64 key = 0;
+            int j = 0;
+            for (; j < 21; ++j) {
+                u64 o = i + (u64)j;
+                u32 c = o < D ? sym3(dict[o]) : 0u;
+                key = (key << 3) | c;
+                if (c == 0) { ++j; break; }
+            }
+            key <<= 3 * (21 - j);
+            ka[i] = key;
+            sp[i] = (u32)i;
+        });
+        sort_pairs(key_a, key_b, sa, val_b, D, 0, 63, ws.sc, st);
+        const u64 *ks = key_a.get(); u8 *fl = flag.get();
+        launch_for(D, st, PFB_LAMBDA(u64 j) { fl[j] = (j == 0 || ks[j] != ks[j - 1]) ? 1 : 0; });
+    }
+    ranks_from_flags(sa, flag, rank, D, ws);
+    {
+        const u32 Dw32 = (u32)Dw;
+        // a tied suffix is complete once its EndOfWord lies inside the compared prefix
+        int rc = prefix_doubling(sa, rank, flag, D, 21, PFB_LAMBDA(u32 idx, u64 h) {
+            u32 d = word_of(wstart, Dw32 + 1, idx);   // wstart[Dw] = position of EndOfDict
+            u64 sl = d < Dw32 ? (u64)(wstart[d + 1] - 1 - idx) : 0;
+            return sl < h;
+        }, ws, &tm.dict_sort_rounds, err);
+        if (rc) return rc;
+    }
+    tm.dict_sort = timer.stop();
+
+    // K7 groups, counts, offsets ------------------------------------------------------
+    // per sorted position t: word, suffix length, validity (> w), occ(word)
+    DevBuf<u32> wordv(D);
+    DevBuf<u64> cnt(D), off(D);
+    DevBuf<u32> cum(Dw + 1);    // exclusive sums of occ: ilist slots of word d = ilist[1+cum[d] ..)
+    exclusive_sum<u32, u32>(pp.occ.get(), cum.get(), Dw, ws.sc, st);
+    {
+        const u32 *occ = pp.occ.get(); u32 *cm = cum.get();
+        launch_for(1, st, PFB_LAMBDA(u64) { cm[Dw] = Dw ? cm[Dw - 1] + occ[Dw - 1] : 0; });
+    }
+    {
+        const u32 *sp = sa.get(); const u32 *occ = pp.occ.get(); u32 *wv = wordv.get(); u64 *cp = cnt.get();
+        const u32 Dw32 = (u32)Dw;
+        launch_for(D, st, PFB_LAMBDA(u64 t) {
+            u32 idx = sp[t];
+            u32 d = word_of(wstart, Dw32 + 1, idx);
+            u64 sl = d < Dw32 ? (u64)(wstart[d + 1] - 1 - idx) : 0;
+            bool valid = sl > w;                 // include/pfbwt.hpp:114
+            wv[t] = d;
+            cp[t] = valid ? (u64)occ[d] : 0;
+        });
+    }
+    exclusive_sum<u64, u64>(cnt.get(), off.get(), D, ws.sc, st);
+    {
+        u64 total = read_scalar(off.get() + (D - 1), st) + read_scalar(cnt.get() + (D - 1), st);
+        if (total != n + 1) { err = "internal: emitted positions " + std::to_string(total) + " != n+1 = " + std::to_string(n + 1); return PFB_ERR_INTERNAL; }
+    }
+    // group structure: head position of each t, per-group "chars differ" flag
+    DevBuf<u32> head(D);
+    {
+        DevBuf<u32> hd(D);
+        const u8 *fl = flag.get(); u32 *hp = hd.get();
+        launch_for(D, st, PFB_LAMBDA(u64 j) { hp[j] = fl[j] ? (u32)j : 0; });
+        inclusive_max(hd.get(), head.get(), D, ws.sc, st);
+    }
+    DevBuf<u8> gdiff(D);
+    dev_memset(gdiff.get(), 0, D, st);
+    {
+        const u32 *sp = sa.get(); const u32 *hd = head.get(); u8 *gd = gdiff.get();
+        launch_for(D, st, PFB_LAMBDA(u64 t) {
+            u32 h = hd[t];
+            if (h == (u32)t) return;
+            u32 i0 = sp[h], i1 = sp[t];
+            u8 c0 = i0 > 1 ? dict[i0 - 1] : 0, c1 = i1 > 1 ? dict[i1 - 1] : 0;   // include/pfbwt.hpp:132,140
+            if (i0 == 0 || i1 == 0) return;   // full words never share a group
+            if (c0 != c1) gd[h] = 1;
+        });
+    }
+    // classification per member: 0 = nothing to emit, 1 = easy (direct), 2 = hard (needs merge by ilist position)
+    DevBuf<u64> hcnt(D), hoff(D);
+    DevBuf<u64> stats(2);
+    dev_memset(stats.get(), 0, 16, st);
+    {
+        const u8 *fl = flag.get(); const u32 *hd = head.get(); const u8 *gd = gdiff.get(); const u64 *cp = cnt.get();
+        u64 *hc = hcnt.get(); u64 *stp = stats.get();
+        launch_for(D, st, PFB_LAMBDA(u64 t) {
+            u64 c = cp[t];
+            bool single = fl[t] && (t + 1 == D || fl[t + 1]);
+            bool hard = c && !single && (any_sa || gd[hd[t]]);   // include/pfbwt.hpp:146
+            hc[t] = hard ? c : 0;
+            if (c) atomic_add(&stp[hard ? 1 : 0], c);
+        });
+    }
+    exclusive_sum<u64, u64>(hcnt.get(), hoff.get(), D, ws.sc, st);
+    u64 nhard = read_scalar(hoff.get() + (D - 1), st) + read_scalar(hcnt.get() + (D - 1), st);
+    out.easy = read_scalar(stats.get(), st);
+    out.hard = read_scalar(stats.get() + 1, st);
+    tm.groups = timer.stop();
+
+    // K8 emission ------------------------------------------------------------------------
+    out.n = n;
+    out.bwt.alloc(n + 1);
+    if (any_sa) out.sa.alloc((n + 1) * (u64)U);
+    u8 *bwt = out.bwt.get();
+    u8 *sa_out = out.sa.get();
+    const u32 *ilist = pp.ilist.get(); const u8 *bwlast = pp.bwlast.get(); const u64 *bwsai = pp.bwsai.get();
+    const u32 *cm = cum.get();
+    {   // easy members: occurrences already ordered by ilist position
+        const u32 *sp = sa.get(); const u32 *wv = wordv.get(); const u64 *cp = cnt.get(); const u64 *hc = hcnt.get();
+        const u64 *of = off.get();
+        launch_for(D, st, PFB_LAMBDA(u64 t) {
+            u64 c = cp[t];
+            if (!c || hc[t]) return;
+            u32 idx = sp[t], d = wv[t];
+            bool full = idx == wstart[d];
+            u64 sl = (u64)(wstart[d + 1] - 1 - idx);
+            u8 pc = idx > 1 ? dict[idx - 1] : 0;
+            u64 x = of[t];
+            u32 base = 1 + cm[d];
+            for (u64 j = 0; j < c; ++j) {
+                u32 ii = ilist[base + j];
+                bwt[x + j] = full ? bwlast[ii] : pc;          // include/pfbwt.hpp:119,151
+                if (any_sa) {
+                    u64 v = bwsai[ii] - sl;
+                    if (U == 4) reinterpret_cast<u32 *>(sa_out)[x + j] = (u32)v;
+                    else reinterpret_cast<u64 *>(sa_out)[x + j] = v;
+                }
+            }
+        });
+    }
+    if (nhard) {   // hard groups: gather (dense group, ilist position) keys, one global radix sort, scatter
+        DevBuf<u8> hh(D);
+        DevBuf<u32> hgid(D);
+        {
+            const u64 *hc = hcnt.get(); const u32 *hd = head.get(); u8 *hp = hh.get();
+            launch_for(D, st, PFB_LAMBDA(u64 t) { hp[t] = (hc[t] && (hd[t] == (u32)t || !hc[hd[t]])) ? 1 : 0; });
+        }
+        // (a hard group's head is always hard itself, so the second clause never fires;
+        //  kept as a guard)  dense id of the group = number of hard heads before it
+        u64 nhg = scan_flags(hh.get(), hgid.get(), D, ws);
+        const int ibits = bits_for(P);           // ilist values are in [0, P]
+        const int gbits = bits_for(nhg ? nhg - 1 : 0);
+        if (ibits + gbits > 64) { err = "internal: hard key overflow"; return PFB_ERR_INTERNAL; }
+        DevBuf<u64> hkey(nhard), hkey_b(nhard), hval(nhard), hval_b(nhard);
+        {
+            const u32 *sp = sa.get(); const u32 *wv = wordv.get(); const u64 *hc = hcnt.get(); const u64 *ho = hoff.get();
+            const u32 *hd = head.get(); const u32 *hg = hgid.get();
+            u64 *hk = hkey.get(); u64 *hv = hval.get();
+            launch_for(D, st, PFB_LAMBDA(u64 t) {
+                u64 c = hc[t];
+                if (!c) return;
+                u32 idx = sp[t], d = wv[t];
+                u8 pc = idx > 1 ? dict[idx - 1] : 0;
+                u32 h = hd[t];
+                u64 g = hg[h];
+                u64 e = ho[t];
+                u32 base = 1 + cm[d];
+                for (u64 j = 0; j < c; ++j) {
+                    u32 ii = ilist[base + j];
+                    hk[e + j] = (g << ibits) | (u64)ii;
+                    hv[e + j] = ((u64)h << 8) | pc;
+                }
+            });
+        }
+        sort_pairs(hkey, hkey_b, hval, hval_b, nhard, 0, ibits + gbits, ws.sc, st);
+        {
+            const u64 *hk = hkey.get(); const u64 *hv = hval.get(); const u64 *ho = hoff.get(); const u64 *of = off.get();
+            const u32 *sp = sa.get(); const u32 *wv = wordv.get();
+            const u64 imask = ibits >= 64 ? ~0ull : ((1ull << ibits) - 1);
+            launch_for(nhard, st, PFB_LAMBDA(u64 e) {
+                u64 v = hv[e];
+                u32 h = (u32)(v >> 8);
+                u8 pc = (u8)(v & 0xff);
+                u32 ii = (u32)(hk[e] & imask);
+                u64 x = of[h] + (e - ho[h]);
+                bwt[x] = pc;                                           // include/pfbwt.hpp:173-178
+                if (any_sa) {
+                    u32 idx = sp[h], d = wv[h];
+                    u64 sl = (u64)(wstart[d + 1] - 1 - idx);
+                    u64 s = bwsai[ii] - sl;
+                    if (U == 4) reinterpret_cast<u32 *>(sa_out)[x] = (u32)s;
+                    else reinterpret_cast<u64 *>(sa_out)[x] = s;
+                }
+            });
+        }
+    }
+    if (any_sa) {   // src/pfbwt-f.cpp:301
+        launch_for(1, st, PFB_LAMBDA(u64) {
+            if (U == 4) reinterpret_cast<u32 *>(sa_out)[0] = (u32)n;
+            else reinterpret_cast<u64 *>(sa_out)[0] = n;
+        });
+    }
+    tm.emit = timer.stop();
+
+    // K9 run boundaries + run-length SA samples (src/pfbwt-f.cpp:304-328) -------------------
+    {
+        DevBuf<u8> rf(n + 1);
+        u8 *rp = rf.get();
+        launch_for(n + 1, st, PFB_LAMBDA(u64 x) { rp[x] = bwt[x] != (x ? bwt[x - 1] : (u8)0) ? 1 : 0; });
+        if (!want_rssa) {
+            out.r = reduce_sum<u8, u64>(rf.get(), n + 1, ws.sc, st);
+        } else {
+            DevBuf<u64> ridx(n + 1);
+            exclusive_sum<u8, u64>(rf.get(), ridx.get(), n + 1, ws.sc, st);
+            u64 r = read_scalar(ridx.get() + n, st) + read_scalar(rf.get() + n, st);
+            out.r = r;
+            out.ssa.alloc(2 * r * (u64)U);
+            out.esa.alloc(2 * r * (u64)U);
+            u8 *ssa = out.ssa.get(); u8 *esa = out.esa.get(); const u64 *ri = ridx.get();
+            launch_for(n + 1, st, PFB_LAMBDA(u64 x) {
+                if (U == 4) {
+                    const u32 *S4 = reinterpret_cast<const u32 *>(sa_out);
+                    u32 *s4 = reinterpret_cast<u32 *>(ssa); u32 *e4 = reinterpret_cast<u32 *>(esa);
+                    if (rp[x]) {
+                        u64 k = ri[x];
+                        s4[2 * k] = (u32)x; s4[2 * k + 1] = S4[x];
+                        if (x) { e4[2 * (k - 1)] = (u32)(x - 1); e4[2 * (k - 1) + 1] = S4[x - 1]; }
+                    }
+                    if (x == n) { e4[2 * (r - 1)] = (u32)n; e4[2 * (r - 1) + 1] = S4[n]; }
+                } else {
+                    const u64 *S8 = reinterpret_cast<const u64 *>(sa_out);
+                    u64 *s8 = reinterpret_cast<u64 *>(ssa); u64 *e8 = reinterpret_cast<u64 *>(esa);
+                    if (rp[x]) {
+                        u64 k = ri[x];
+                        s8[2 * k] = x; s8[2 * k + 1] = S8[x];
+                        if (x) { e8[2 * (k - 1)] = x - 1; e8[2 * (k - 1) + 1] = S8[x - 1]; }
+                    }
+                    if (x == n) { e8[2 * (r - 1)] = n; e8[2 * (r - 1) + 1] = S8[n]; }
+                }
+            });
+        }
+    }
+    tm.runs = timer.stop();
+    return PFB_OK;
+}
+
+}  // namespace pfb

@@ -1,0 +1,332 @@
+// prim.cuh -- device primitive layer of pfbwt-b200.
+//
+// Everything the pipeline does on the GPU goes through this header:
+//   * launch_for(n, f)       one logical thread per element, grid-stride kernel
+//   * launch_blocks(...)     explicit CTA-shaped kernels (hand-written kernels in
+//                            kernels.cuh use raw <<<>>> launches instead)
+//   * scans / radix sorts / compaction
+//   * DevBuf<T>              RAII device allocation
+//
+// Two builds exist.  The product build (nvcc, sm_100a) is the only thing that is
+// ever linked into libpfbwt_b200.so.  Defining PFB_EMU gives a *developer logic
+// check*: the same pipeline source is compiled by g++ with every primitive
+// executed as a serial loop, so index arithmetic can be checked against the
+// oracle on a machine without a GPU (tests/emu/, `-m "not gpu"`).  The emulator is
+// test infrastructure; it is never shipped, never linked into the library and
+// never used as a fallback -- the library fails loudly without a CUDA device.
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <utility>
+#include <vector>
+
+#ifdef PFB_EMU
+// ---------------------------------------------------------------- emulator --
+#include <algorithm>
+#include <numeric>
+#define PFB_DEV
+#define PFB_HD
+#define PFB_LAMBDA [=]
+typedef int pfbStream_t;
+#else
+// -------------------------------------------------------------------- CUDA --
+#include <cuda_runtime.h>
+#include <cub/cub.cuh>
+#define PFB_DEV __device__
+#define PFB_HD __host__ __device__
+#define PFB_LAMBDA [=] __device__
+typedef cudaStream_t pfbStream_t;
+#endif
+
+namespace pfb {
+
+struct Error : std::runtime_error {
+    int code;
+    Error(int c, const std::string &m) : std::runtime_error(m), code(c) {}
+};
+
+#ifndef PFB_EMU
+#define PFB_CUDA_CHECK(x)                                                                         \
+    do {                                                                                          \
+        cudaError_t e_ = (x);                                                                     \
+        if (e_ != cudaSuccess)                                                                    \
+            throw pfb::Error(-5, std::string("CUDA error: ") + cudaGetErrorString(e_) + " at " +  \
+                                     __FILE__ + ":" + std::to_string(__LINE__));                  \
+    } while (0)
+#endif
+
+// launch counter: every kernel launched by this library (ours + CUB's) is counted
+// so bench.py can report gpu_launches honestly.
+struct LaunchStats {
+    uint64_t own = 0;   // kernels written in this repo
+    uint64_t lib = 0;   // CUB kernels (library code)
+};
+inline LaunchStats &launch_stats() {
+    static LaunchStats s;
+    return s;
+}
+
+// ------------------------------------------------------------------ DevBuf --
+size_t &dev_bytes_live();
+size_t &dev_bytes_peak();
+
+template <class T>
+struct DevBuf {
+    T *p = nullptr;
+    size_t n = 0;
+    DevBuf() {}
+    explicit DevBuf(size_t count) { alloc(count); }
+    DevBuf(const DevBuf &) = delete;
+    DevBuf &operator=(const DevBuf &) = delete;
+    DevBuf(DevBuf &&o) noexcept : p(o.p), n(o.n) { o.p = nullptr; o.n = 0; }
+    DevBuf &operator=(DevBuf &&o) noexcept {
+        if (this != &o) { release(); p = o.p; n = o.n; o.p = nullptr; o.n = 0; }
+        return *this;
+    }
+    ~DevBuf() { release(); }
+    void alloc(size_t count) {
+        release();
+        n = count;
+        size_t bytes = (count ? count : 1) * sizeof(T);
+#ifdef PFB_EMU
+        p = (T *)malloc(bytes);
+        if (!p) throw Error(-4, "emu: out of memory");
+#else
+        cudaError_t e = cudaMalloc((void **)&p, bytes);
+        if (e != cudaSuccess) {
+            p = nullptr; n = 0;
+            throw Error(-4, std::string("device out of memory allocating ") + std::to_string(bytes) + " bytes (" +
+                                cudaGetErrorString(e) + ")");
+        }
+#endif
+        dev_bytes_live() += bytes;
+        if (dev_bytes_live() > dev_bytes_peak()) dev_bytes_peak() = dev_bytes_live();
+    }
+    void release() {
+        if (p) {
+            dev_bytes_live() -= (n ? n : 1) * sizeof(T);
+#ifdef PFB_EMU
+            free(p);
+#else
+            cudaFree(p);
+#endif
+        }
+        p = nullptr; n = 0;
+    }
+    T *get() const { return p; }
+    size_t size() const { return n; }
+    void swap(DevBuf &o) { std::swap(p, o.p); std::swap(n, o.n); }
+};
+
+// ----------------------------------------------------------------- memory ops
+inline void dev_memset(void *p, int v, size_t bytes, pfbStream_t s) {
+#ifdef PFB_EMU
+    (void)s; memset(p, v, bytes);
+#else
+    PFB_CUDA_CHECK(cudaMemsetAsync(p, v, bytes, s));
+#endif
+}
+inline void h2d(void *d, const void *h, size_t bytes, pfbStream_t s) {
+#ifdef PFB_EMU
+    (void)s; memcpy(d, h, bytes);
+#else
+    PFB_CUDA_CHECK(cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, s));
+#endif
+}
+inline void d2h(void *h, const void *d, size_t bytes, pfbStream_t s) {
+#ifdef PFB_EMU
+    (void)s; memcpy(h, d, bytes);
+#else
+    PFB_CUDA_CHECK(cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, s));
+#endif
+}
+inline void d2d(void *dst, const void *src, size_t bytes, pfbStream_t s) {
+#ifdef PFB_EMU
+    (void)s; memmove(dst, src, bytes);
+#else
+    PFB_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, s));
+#endif
+}
+inline void stream_sync(pfbStream_t s) {
+#ifdef PFB_EMU
+    (void)s;
+#else
+    PFB_CUDA_CHECK(cudaStreamSynchronize(s));
+#endif
+}
+template <class T>
+inline T read_scalar(const T *d, pfbStream_t s) {
+    T v;
+    d2h(&v, d, sizeof(T), s);
+    stream_sync(s);
+    return v;
+}
+
+// ------------------------------------------------------------------ atomics --
+#ifdef PFB_EMU
+template <class T> inline T atomic_add(T *a, T v) { T o = *a; *a = o + v; return o; }
+template <class T> inline T atomic_min(T *a, T v) { T o = *a; if (v < o) *a = v; return o; }
+template <class T> inline T atomic_max(T *a, T v) { T o = *a; if (v > o) *a = v; return o; }
+template <class T> inline T atomic_or(T *a, T v) { T o = *a; *a = o | v; return o; }
+template <class T> inline T atomic_cas(T *a, T cmp, T v) { T o = *a; if (o == cmp) *a = v; return o; }
+inline int popc32(uint32_t x) { return __builtin_popcount(x); }
+inline int ffs32(uint32_t x) { return __builtin_ffs((int)x); }
+#else
+__device__ __forceinline__ uint32_t atomic_add(uint32_t *a, uint32_t v) { return atomicAdd(a, v); }
+__device__ __forceinline__ uint64_t atomic_add(uint64_t *a, uint64_t v) {
+    return (uint64_t)atomicAdd((unsigned long long *)a, (unsigned long long)v);
+}
+__device__ __forceinline__ uint32_t atomic_min(uint32_t *a, uint32_t v) { return atomicMin(a, v); }
+__device__ __forceinline__ uint64_t atomic_min(uint64_t *a, uint64_t v) {
+    return (uint64_t)atomicMin((unsigned long long *)a, (unsigned long long)v);
+}
+__device__ __forceinline__ uint32_t atomic_max(uint32_t *a, uint32_t v) { return atomicMax(a, v); }
+__device__ __forceinline__ uint32_t atomic_or(uint32_t *a, uint32_t v) { return atomicOr(a, v); }
+__device__ __forceinline__ uint64_t atomic_cas(uint64_t *a, uint64_t cmp, uint64_t v) {
+    return (uint64_t)atomicCAS((unsigned long long *)a, (unsigned long long)cmp, (unsigned long long)v);
+}
+__device__ __forceinline__ int popc32(uint32_t x) { return __popc(x); }
+__device__ __forceinline__ int ffs32(uint32_t x) { return __ffs((int)x); }
+#endif
+
+// -------------------------------------------------------------- launch_for --
+#ifndef PFB_EMU
+template <class F>
+__global__ void __launch_bounds__(256) for_kernel(uint64_t n, F f) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) f(i);
+}
+#endif
+
+// one logical thread per i in [0,n).  Grid is capped at a multiple of the SM
+// count (148 SMs x 8 resident CTAs of 256 threads) and grid-strided beyond it.
+template <class F>
+inline void launch_for(uint64_t n, pfbStream_t s, F f) {
+    if (n == 0) return;
+#ifdef PFB_EMU
+    (void)s;
+    for (uint64_t i = 0; i < n; ++i) f(i);
+#else
+    uint64_t blocks = (n + 255) / 256;
+    const uint64_t cap = 148ull * 8ull * 4ull;
+    if (blocks > cap) blocks = cap;
+    for_kernel<<<(unsigned)blocks, 256, 0, s>>>(n, f);
+    PFB_CUDA_CHECK(cudaGetLastError());
+    launch_stats().own++;
+#endif
+}
+
+// ------------------------------------------------------------------- scans --
+struct Scratch {
+    DevBuf<uint8_t> buf;
+    void *ensure(size_t bytes) {
+        if (buf.size() < bytes) buf.alloc(bytes + bytes / 4 + 256);
+        return buf.get();
+    }
+};
+
+struct MaxOp {
+    template <class T> PFB_HD T operator()(const T &a, const T &b) const { return a > b ? a : b; }
+};
+template <class A, class B>
+struct CastOp {
+    PFB_HD B operator()(const A &a) const { return (B)a; }
+};
+
+template <class TIn, class TOut>
+inline void exclusive_sum(const TIn *in, TOut *out, uint64_t n, Scratch &sc, pfbStream_t s) {
+    if (n == 0) return;
+#ifdef PFB_EMU
+    (void)sc; (void)s;
+    TOut acc = 0;
+    for (uint64_t i = 0; i < n; ++i) { TOut v = (TOut)in[i]; out[i] = acc; acc += v; }
+#else
+    auto it = cub::TransformInputIterator<TOut, CastOp<TIn, TOut>, const TIn *>(in, CastOp<TIn, TOut>());
+    size_t bytes = 0;
+    PFB_CUDA_CHECK(cub::DeviceScan::ExclusiveSum(nullptr, bytes, it, out, (int64_t)n, s));
+    void *tmp = sc.ensure(bytes);
+    PFB_CUDA_CHECK(cub::DeviceScan::ExclusiveSum(tmp, bytes, it, out, (int64_t)n, s));
+    launch_stats().lib += 2;
+#endif
+}
+template <class T>
+inline void inclusive_max(const T *in, T *out, uint64_t n, Scratch &sc, pfbStream_t s) {
+    if (n == 0) return;
+#ifdef PFB_EMU
+    (void)sc; (void)s;
+    T acc = in[0];
+    for (uint64_t i = 0; i < n; ++i) { acc = in[i] > acc ? in[i] : acc; out[i] = acc; }
+#else
+    size_t bytes = 0;
+    PFB_CUDA_CHECK(cub::DeviceScan::InclusiveScan(nullptr, bytes, in, out, MaxOp(), (int64_t)n, s));
+    void *tmp = sc.ensure(bytes);
+    PFB_CUDA_CHECK(cub::DeviceScan::InclusiveScan(tmp, bytes, in, out, MaxOp(), (int64_t)n, s));
+    launch_stats().lib += 2;
+#endif
+}
+
+template <class TIn, class TOut>
+inline TOut reduce_sum(const TIn *in, uint64_t n, Scratch &sc, pfbStream_t s) {
+    if (n == 0) return 0;
+#ifdef PFB_EMU
+    (void)sc; (void)s;
+    TOut acc = 0;
+    for (uint64_t i = 0; i < n; ++i) acc += (TOut)in[i];
+    return acc;
+#else
+    auto it = cub::TransformInputIterator<TOut, CastOp<TIn, TOut>, const TIn *>(in, CastOp<TIn, TOut>());
+    DevBuf<TOut> out(1);
+    size_t bytes = 0;
+    PFB_CUDA_CHECK(cub::DeviceReduce::Sum(nullptr, bytes, it, out.get(), (int64_t)n, s));
+    void *tmp = sc.ensure(bytes);
+    PFB_CUDA_CHECK(cub::DeviceReduce::Sum(tmp, bytes, it, out.get(), (int64_t)n, s));
+    launch_stats().lib += 2;
+    return read_scalar(out.get(), s);
+#endif
+}
+
+// ------------------------------------------------------------- radix sorts --
+// Stable LSD radix sort of (key,value) pairs on key bits [begin_bit,end_bit).
+// Result is left in keys_a/vals_a (buffers may be swapped internally).
+template <class K, class V>
+inline void sort_pairs(DevBuf<K> &keys_a, DevBuf<K> &keys_b, DevBuf<V> &vals_a, DevBuf<V> &vals_b, uint64_t n,
+                       int begin_bit, int end_bit, Scratch &sc, pfbStream_t s) {
+    if (n <= 1) return;
+    if (end_bit <= begin_bit) return;
+#ifdef PFB_EMU
+    (void)sc; (void)s; (void)keys_b; (void)vals_b;
+    std::vector<uint64_t> perm(n);
+    std::iota(perm.begin(), perm.end(), 0);
+    const K mask = (end_bit - begin_bit >= (int)(8 * sizeof(K))) ? (K)~(K)0 : (K)((((K)1) << (end_bit - begin_bit)) - 1);
+    K *kp = keys_a.get(); V *vp = vals_a.get();
+    std::stable_sort(perm.begin(), perm.end(), [&](uint64_t a, uint64_t b) {
+        return ((kp[a] >> begin_bit) & mask) < ((kp[b] >> begin_bit) & mask);
+    });
+    std::vector<K> k2(n); std::vector<V> v2(n);
+    for (uint64_t i = 0; i < n; ++i) { k2[i] = kp[perm[i]]; v2[i] = vp[perm[i]]; }
+    memcpy(kp, k2.data(), n * sizeof(K)); memcpy(vp, v2.data(), n * sizeof(V));
+#else
+    cub::DoubleBuffer<K> dk(keys_a.get(), keys_b.get());
+    cub::DoubleBuffer<V> dv(vals_a.get(), vals_b.get());
+    size_t bytes = 0;
+    PFB_CUDA_CHECK(cub::DeviceRadixSort::SortPairs(nullptr, bytes, dk, dv, (int64_t)n, begin_bit, end_bit, s));
+    void *tmp = sc.ensure(bytes);
+    PFB_CUDA_CHECK(cub::DeviceRadixSort::SortPairs(tmp, bytes, dk, dv, (int64_t)n, begin_bit, end_bit, s));
+    launch_stats().lib += 1 + (uint64_t)((end_bit - begin_bit + 7) / 8);
+    if (dk.Current() != keys_a.get()) keys_a.swap(keys_b);
+    if (dv.Current() != vals_a.get()) vals_a.swap(vals_b);
+#endif
+}
+
+inline int bits_for(uint64_t max_value) {   // number of bits needed to represent max_value
+    int b = 1;
+    while (b < 64 && (max_value >> b)) ++b;
+    return b;
+}
+
+}  // namespace pfb

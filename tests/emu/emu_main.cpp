@@ -1,0 +1,60 @@
+// emu_main.cpp -- DEVELOPER LOGIC CHECK, TEST INFRASTRUCTURE ONLY.
+// Compiles the device pipeline (pfbwt-f_b200/csrc/pipeline.cuh, engine.hpp) with
+// -DPFB_EMU so that every launch_for / scan / sort runs as a serial host loop.
+// It lets the `-m "not gpu"` tests check the pipeline's index arithmetic against
+// the oracle on a box without a GPU.  It is NOT a fallback: nothing here is
+// linked into libpfbwt_b200.so, which fails loudly without a CUDA device.
+//
+//   pfb_emu [-w W] [-p P] [-s] [-r] [--bits 32|64] [--non-acgt-to-a] [--parse-only] [-o prefix] in.fa
+//   pfb_emu --merge [-w W] [-p P] [-s] [--bits 64] -o out pfx1 pfx2 ...
+#define PFB_EMU 1
+#include "engine.hpp"
+
+namespace pfb {
+size_t &dev_bytes_live() { static size_t v = 0; return v; }
+size_t &dev_bytes_peak() { static size_t v = 0; return v; }
+}
+
+int main(int argc, char **argv) {
+    int w = 10, p = 100, sa = 0, rssa = 0, bits = 32, ntoa = 0, parse_only = 0, merge = 0, docs = 0;
+    std::string out;
+    std::vector<std::string> in;
+    for (int i = 1; i < argc; ++i) {
+        std::string a = argv[i];
+        if (a == "-w") w = atoi(argv[++i]);
+        else if (a == "-p") p = atoi(argv[++i]);
+        else if (a == "-s") sa = 1;
+        else if (a == "-r") rssa = 1;
+        else if (a == "--bits") bits = atoi(argv[++i]);
+        else if (a == "--non-acgt-to-a") ntoa = 1;
+        else if (a == "--parse-only") parse_only = 1;
+        else if (a == "--print-docs") docs = 1;
+        else if (a == "--merge") merge = 1;
+        else if (a == "-o") out = argv[++i];
+        else in.push_back(a);
+    }
+    if (in.empty()) { fprintf(stderr, "usage: see source header\n"); return 2; }
+    pfb::Engine E;
+    E.prm.w = w; E.prm.p = (uint64_t)p; E.prm.bits = bits; E.prm.non_acgt_to_a = ntoa; E.prm.get_sai = sa || rssa;
+    E.store_docs = docs;
+    if (merge) {
+        if (out.empty()) out = "out";
+        for (auto &pfx : in) {
+            pfb::Engine R;
+            R.prm = E.prm;
+            if (R.load_parse(pfx, false, false)) { fprintf(stderr, "%s\n", R.err.c_str()); return 1; }
+            if (E.append_parse_of(R)) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }
+        }
+        if (E.finalize() || E.do_parse_bwt() || E.save_parse(out, true, sa)) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }
+        return 0;
+    }
+    if (out.empty()) out = in[0];
+    if (E.add_fasta(in[0])) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }
+    if (E.finalize() || E.do_parse_bwt() || E.save_parse(out, true, sa || rssa)) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }
+    if (parse_only) return 0;
+    if (E.build(sa, rssa) || E.write_bwt_files(out, sa, rssa, "")) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }
+    fprintf(stderr, "# easy cases: %lu, # hard cases: %lu\nn: %lu\nr: %lu\nrounds: phrase %u parse_sa %u dict %u\n",
+            (unsigned long)E.bwt.easy, (unsigned long)E.bwt.hard, (unsigned long)E.bwt.n, (unsigned long)E.bwt.r,
+            E.tm.phrase_sort_rounds, E.tm.parse_sa_rounds, E.tm.dict_sort_rounds);
+    return 0;
+}
