@@ -1,0 +1,37 @@
+# Builds libpfbwt_b200.so (sm_100a only) and the drop-in binaries pfbwt-f, pfbwt-f64, merge_pfp.
+NVCC   ?= nvcc
+CXX    ?= g++
+ARCH   := -gencode arch=compute_100a,code=sm_100a
+NVFLAGS := -std=c++17 -O3 $(ARCH) -lineinfo --extended-lambda -Xcompiler -fPIC,-Wno-deprecated-declarations \
+           -Wno-deprecated-declarations -I pfbwt-f_b200/csrc -I include
+CSRC   := pfbwt-f_b200/csrc
+LIB    := pfbwt-f_b200/libpfbwt_b200.so
+BIN    := bin
+
+all: $(LIB) $(BIN)/pfbwt-f $(BIN)/pfbwt-f64 $(BIN)/merge_pfp emu
+
+$(LIB): $(CSRC)/capi.cu $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp include/pfbwt_b200.h
+	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/capi.cu -lz -lcudart
+
+$(BIN)/pfbwt-f: pfbwt-f_b200/src/pfbwt-f.cpp $(LIB)
+	mkdir -p $(BIN)
+	$(CXX) -std=c++17 -O2 -I include -o $@ $< -Lpfbwt-f_b200 -lpfbwt_b200 -Wl,-rpath,'$$ORIGIN/../pfbwt-f_b200'
+$(BIN)/pfbwt-f64: pfbwt-f_b200/src/pfbwt-f.cpp $(LIB)
+	mkdir -p $(BIN)
+	$(CXX) -std=c++17 -O2 -DM64 -I include -o $@ $< -Lpfbwt-f_b200 -lpfbwt_b200 -Wl,-rpath,'$$ORIGIN/../pfbwt-f_b200'
+$(BIN)/merge_pfp: pfbwt-f_b200/src/merge_pfp.cpp $(LIB)
+	mkdir -p $(BIN)
+	$(CXX) -std=c++17 -O2 -I include -o $@ $< -Lpfbwt-f_b200 -lpfbwt_b200 -Wl,-rpath,'$$ORIGIN/../pfbwt-f_b200'
+
+# developer logic check (tests only; see tests/emu/emu_main.cpp)
+emu: tests/emu/pfb_emu
+tests/emu/pfb_emu: tests/emu/emu_main.cpp $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp
+	$(CXX) -std=c++17 -O2 -Wall -Wno-unused -I $(CSRC) -o $@ $< -lz
+
+oracle:
+	$(MAKE) -C oracle all
+
+clean:
+	rm -rf $(LIB) $(BIN) tests/emu/pfb_emu
+
+.PHONY: all emu oracle clean

@@ -1,0 +1,136 @@
+/* pfbwt_b200.h -- C ABI of libpfbwt_b200.so, the B200-native drop-in for the
+ * fasta -> prefix-free parse -> BWT(+SA) hot path of alshai/pfbwt-f.
+ *
+ * The reference has no C ABI of its own (only header-level C++ classes); every
+ * entry point below names the reference interface it replaces (paths relative
+ * to the reference tree).  Plain pointers and sizes only; all buffers passed in
+ * or out are HOST memory owned by the caller.  Every call is synchronous; a
+ * context is bound to one CUDA device and is not thread-safe (like the
+ * reference's classes).  There is no CPU fallback: pfb_create() fails when no
+ * CUDA device is usable.
+ *
+ * Return value of int functions: 0 on success, a negative PFB_ERR_* code on
+ * failure; pfb_last_error() then returns the message the reference would have
+ * printed before exit(1) (same wording where the reference has one).
+ */
+#ifndef PFBWT_B200_H
+#define PFBWT_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PFB_OK 0
+#define PFB_ERR_ARG (-1)
+#define PFB_ERR_INVALID_CHAR (-2)  /* include/hash.hpp:31 */
+#define PFB_ERR_LIMIT (-3)         /* include/pfparser.hpp:393-405 */
+#define PFB_ERR_NOMEM (-4)
+#define PFB_ERR_CUDA (-5)
+#define PFB_ERR_IO (-6)
+#define PFB_ERR_ONE_WORD (-7)      /* include/pfparser.hpp:390-392 */
+#define PFB_ERR_INTERNAL (-8)
+#define PFB_ERR_TOO_LONG_32 (-9)   /* include/pfparser.hpp:326-332 */
+
+typedef struct pfb_ctx pfb_ctx;
+
+/* pfbwtf::PfParserParams, include/pfparser.hpp:30-44 (same field meaning) */
+typedef struct {
+    uint32_t w;             /* window size, default 10, 1..31            */
+    uint64_t p;             /* trigger modulus, default 100              */
+    int get_sai;            /* keep sai_/bwsai (-s / -r)                 */
+    int store_docs;         /* --print-docs                              */
+    int verbose;
+    int trim_non_acgt;      /* accepted, disabled like the reference (include/pfparser.hpp:338-341) */
+    int non_acgt_to_a;      /* --non-acgt-to-a                           */
+} pfb_parse_params;
+
+/* sizes of everything a context currently holds (0 when absent) */
+typedef struct {
+    uint64_t n;             /* PfParser::get_n(), include/pfparser.hpp:529-532  */
+    uint64_t n_phrases;     /* get_parse_size()                                  */
+    uint64_t n_words;       /* distinct phrases                                  */
+    uint64_t dict_bytes;    /* size of the .dict image                           */
+    uint64_t r;             /* BWT runs (src/pfbwt-f.cpp:346)                    */
+    uint64_t easy, hard;    /* include/pfbwt.hpp:188                             */
+    int bits;               /* 32 | 64: width of uint_t in the replaced binary   */
+    int has_parse_bwt, has_bwt, has_sa, has_rssa;
+} pfb_sizes;
+
+/* per-stage device times (CUDA events, ms) and counters of the last run */
+typedef struct {
+    float normalise_ms, trigger_ms, compact_ms, fingerprint_ms, dedup_ms, phrase_sort_ms, dict_build_ms;
+    float parse_sa_ms, parse_bwt_ms, dict_sort_ms, groups_ms, emit_ms, runs_ms;
+    uint32_t dedup_attempts, phrase_sort_rounds, parse_sa_rounds, dict_sort_rounds;
+    uint64_t launches_own;  /* kernels written in this repository launched so far in this process */
+    uint64_t launches_lib;  /* library (CUB) kernels launched so far                              */
+    uint64_t dev_bytes_peak;
+} pfb_stats;
+
+/* ---- lifetime ------------------------------------------------------------ */
+/* bits = 32 replaces pfbwt-f, 64 replaces pfbwt-f64 / merge_pfp (gsa/gsacak.h:40-58). */
+pfb_ctx *pfb_create(int device, int bits);
+void pfb_destroy(pfb_ctx *);
+const char *pfb_last_error(const pfb_ctx *);
+/* message for a failed pfb_create (no context to ask) */
+const char *pfb_create_error(void);
+
+/* PfParser(PfParserParams), include/pfparser.hpp:80-84 (incl. check_w :371-376) */
+int pfb_set_params(pfb_ctx *, const pfb_parse_params *);
+
+/* ---- parse step (pfbwtf::PfParser) ------------------------------------------ */
+/* PfParser::add_fasta, include/pfparser.hpp:299-369.  path "-" = stdin; plain or gzip. */
+int pfb_add_fasta(pfb_ctx *, const char *path_or_dash);
+/* same, from host buffers: nrec records, concatenated bytes in seq, lengths in rec_len */
+int pfb_add_records(pfb_ctx *, const uint8_t *seq, const uint64_t *rec_len, uint64_t nrec);
+/* PfParser::finalize, include/pfparser.hpp:484-492: runs the parse on the device */
+int pfb_finalize(pfb_ctx *);
+/* PfParser::bwt_of_parse, include/pfparser.hpp:379-467 */
+int pfb_parse_bwt(pfb_ctx *);
+/* PfParser::operator+=, include/pfparser.hpp:194-263 (call pfb_finalize(lhs) afterwards) */
+int pfb_append(pfb_ctx *lhs, pfb_ctx *rhs);
+/* save_parser + the bwt_of_parse writer: include/pfbwt_io.hpp:234-249, src/pfbwt-f.cpp:229-243 */
+int pfb_save_parse(pfb_ctx *, const char *prefix, int with_parse_bwt, int with_sai);
+/* load_parser (include/pfbwt_io.hpp:211-222) / PrefixFreeBWT ctor (include/pfbwt.hpp:64-81) */
+int pfb_load_parse(pfb_ctx *, const char *prefix, int with_parse_bwt, int with_sai);
+
+/* ---- BWT build (pfbwtf::PrefixFreeBWT) ----------------------------------------- */
+/* PrefixFreeBWT::generate_bwt_lcp driven by run_pfbwt, include/pfbwt.hpp:96-194,
+ * src/pfbwt-f.cpp:272-349.  sa / rssa = -s / -r. */
+int pfb_build_bwt(pfb_ctx *, int sa, int rssa);
+/* the .bwt/.sa/.ssa/.esa writer of src/pfbwt-f.cpp:298-328; stdout_ext = "bwt" | "sa" | NULL (--stdout) */
+int pfb_write_bwt(pfb_ctx *, const char *prefix, int sa, int rssa, const char *stdout_ext);
+
+/* ---- getters (PfParser getters include/pfparser.hpp:469-544; copies into caller buffers) ---- */
+int pfb_get_sizes(const pfb_ctx *, pfb_sizes *);
+int pfb_get_stats(const pfb_ctx *, pfb_stats *);
+int pfb_copy_dict(pfb_ctx *, uint8_t *out /* dict_bytes */);
+int pfb_copy_occ(pfb_ctx *, void *out /* n_words * bits/8 */);
+int pfb_copy_parse(pfb_ctx *, uint32_t *out /* n_phrases */);
+int pfb_copy_last(pfb_ctx *, uint8_t *out /* n_phrases */);
+int pfb_copy_sai(pfb_ctx *, void *out /* n_phrases * bits/8 */);
+int pfb_copy_bwlast(pfb_ctx *, uint8_t *out /* n_phrases+1 */);
+int pfb_copy_ilist(pfb_ctx *, void *out /* (n_phrases+1) * bits/8 */);
+int pfb_copy_bwsai(pfb_ctx *, void *out /* (n_phrases+1) * bits/8 */);
+int pfb_copy_bwt(pfb_ctx *, uint8_t *out /* n+1 */);
+int pfb_copy_sa(pfb_ctx *, void *out /* (n+1) * bits/8 */);
+int pfb_copy_ssa(pfb_ctx *, void *out /* 2*r * bits/8 */);
+int pfb_copy_esa(pfb_ctx *, void *out /* 2*r * bits/8 */);
+/* doc table of --print-docs (include/pfbwt_io.hpp:224-231): number of docs; start offsets copied when out != NULL */
+int64_t pfb_get_docs(pfb_ctx *, uint64_t *starts_out);
+
+/* ---- measurement hooks (bench.py) -------------------------------------------------- */
+/* stage the pending records into HBM (H2D + normalise) without parsing */
+int pfb_upload_text(pfb_ctx *);
+/* whole hot path on text already resident in HBM: parse -> parse BWT -> BWT(+SA); no host copies */
+int pfb_run_resident(pfb_ctx *, int sa, int rssa);
+/* release device text / host staging once the parse exists */
+int pfb_release_text(pfb_ctx *);
+/* forget all records, parses and outputs (keeps parameters and the CUDA stream) */
+int pfb_clear(pfb_ctx *);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

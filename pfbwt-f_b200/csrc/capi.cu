@@ -1,0 +1,212 @@
+// capi.cu -- the C ABI of libpfbwt_b200.so (include/pfbwt_b200.h) over pfb::Engine.
+// Compiled by nvcc for sm_100a only; there is no host fallback in this library.
+#include "../../include/pfbwt_b200.h"
+#include "engine.hpp"
+#include <new>
+
+namespace pfb {
+size_t &dev_bytes_live() { static size_t v = 0; return v; }
+size_t &dev_bytes_peak() { static size_t v = 0; return v; }
+}
+
+struct pfb_ctx {
+    pfb::Engine eng;
+};
+
+static std::string g_create_err;
+
+static void *pinned_alloc(size_t n) {
+    void *p = nullptr;
+    if (cudaMallocHost(&p, n) != cudaSuccess) return nullptr;
+    return p;
+}
+static void pinned_free(void *p) { cudaFreeHost(p); }
+
+template <class T>
+static int copy_out(pfb_ctx *c, const pfb::DevBuf<T> &b, size_t count, void *out, bool ok, const char *what) {
+    if (!ok || b.size() < count) return c->eng.fail(PFB_ERR_ARG, std::string(what) + " not available");
+    if (!out) return c->eng.fail(PFB_ERR_ARG, "null output buffer");
+    try {
+        if (count) { pfb::d2h(out, b.get(), count * sizeof(T), c->eng.ws.st); pfb::stream_sync(c->eng.ws.st); }
+    } catch (const pfb::Error &e) { return c->eng.fail(e.code, e.what()); }
+    return PFB_OK;
+}
+// device u32 / u64 arrays leave as bits/8-byte integers
+template <class T>
+static int copy_out_uint(pfb_ctx *c, const pfb::DevBuf<T> &b, size_t count, void *out, bool ok, const char *what) {
+    if (!ok || b.size() < count) return c->eng.fail(PFB_ERR_ARG, std::string(what) + " not available");
+    if (!out) return c->eng.fail(PFB_ERR_ARG, "null output buffer");
+    const size_t U = (size_t)c->eng.prm.bits / 8;
+    try {
+        if (U == sizeof(T)) { if (count) { pfb::d2h(out, b.get(), count * sizeof(T), c->eng.ws.st); pfb::stream_sync(c->eng.ws.st); } }
+        else {
+            std::vector<T> v = c->eng.to_host(b, count);
+            if (U == 4) { uint32_t *o = (uint32_t *)out; for (size_t i = 0; i < count; ++i) o[i] = (uint32_t)v[i]; }
+            else { uint64_t *o = (uint64_t *)out; for (size_t i = 0; i < count; ++i) o[i] = (uint64_t)v[i]; }
+        }
+    } catch (const pfb::Error &e) { return c->eng.fail(e.code, e.what()); }
+    return PFB_OK;
+}
+
+extern "C" {
+
+pfb_ctx *pfb_create(int device, int bits) {
+    g_create_err.clear();
+    if (bits != 32 && bits != 64) { g_create_err = "bits must be 32 or 64"; return nullptr; }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        g_create_err = std::string("no CUDA device available (") + cudaGetErrorString(e) + "); libpfbwt_b200 has no CPU path";
+        return nullptr;
+    }
+    if (device < 0 || device >= ndev) { g_create_err = "invalid device ordinal"; return nullptr; }
+    if ((e = cudaSetDevice(device)) != cudaSuccess) { g_create_err = cudaGetErrorString(e); return nullptr; }
+    cudaDeviceProp prop;
+    cudaGetDeviceProperties(&prop, device);
+    if (prop.major < 10) {
+        g_create_err = "libpfbwt_b200 is built for sm_100a (Blackwell B200) only; found sm_" + std::to_string(prop.major) +
+                       std::to_string(prop.minor);
+        return nullptr;
+    }
+    pfb_ctx *c = new (std::nothrow) pfb_ctx();
+    if (!c) { g_create_err = "out of memory"; return nullptr; }
+    c->eng.device = device;
+    c->eng.prm.bits = bits;
+    if ((e = cudaStreamCreateWithFlags(&c->eng.ws.st, cudaStreamNonBlocking)) != cudaSuccess) {
+        g_create_err = cudaGetErrorString(e); delete c; return nullptr;
+    }
+    c->eng.raw.alloc_fn = pinned_alloc;
+    c->eng.raw.free_fn = pinned_free;
+    c->eng.raw.pinned = true;
+    return c;
+}
+
+void pfb_destroy(pfb_ctx *c) {
+    if (!c) return;
+    cudaSetDevice(c->eng.device);
+    cudaStream_t st = c->eng.ws.st;
+    cudaStreamSynchronize(st);
+    c->eng.clear();
+    c->eng.ws.sc.buf.release();
+    c->eng.raw.release();
+    cudaStreamDestroy(st);
+    delete c;
+}
+
+const char *pfb_last_error(const pfb_ctx *c) { return c ? c->eng.err.c_str() : g_create_err.c_str(); }
+const char *pfb_create_error(void) { return g_create_err.c_str(); }
+
+#define CTX_GUARD(c)                       \
+    if (!(c)) return PFB_ERR_ARG;          \
+    cudaSetDevice((c)->eng.device);
+
+int pfb_set_params(pfb_ctx *c, const pfb_parse_params *p) {
+    CTX_GUARD(c);
+    if (!p) return c->eng.fail(PFB_ERR_ARG, "null params");
+    if (p->w > 32) return c->eng.fail(PFB_ERR_ARG, "window size w must be < 32!");   // include/pfparser.hpp:371-376
+    if (p->w < 1 || p->w > 31) return c->eng.fail(PFB_ERR_ARG, "window size w must be in 1..31");
+    if (p->p < 1) return c->eng.fail(PFB_ERR_ARG, "modulus p must be >= 1");
+    if (p->non_acgt_to_a && p->trim_non_acgt)
+        return c->eng.fail(PFB_ERR_ARG, "cannot have both --non-acgt-to-a and --trim-non-acgt options enabled at same time");
+    c->eng.prm.w = (int)p->w;
+    c->eng.prm.p = p->p;
+    c->eng.prm.get_sai = p->get_sai != 0;
+    c->eng.prm.non_acgt_to_a = p->non_acgt_to_a != 0;
+    c->eng.prm.verbose = p->verbose != 0;
+    c->eng.store_docs = p->store_docs != 0;
+    return PFB_OK;
+}
+
+int pfb_add_fasta(pfb_ctx *c, const char *path) { CTX_GUARD(c); return c->eng.add_fasta(path ? path : "-"); }
+int pfb_add_records(pfb_ctx *c, const uint8_t *seq, const uint64_t *rec_len, uint64_t nrec) {
+    CTX_GUARD(c);
+    return c->eng.add_records(seq, rec_len, nrec);
+}
+int pfb_finalize(pfb_ctx *c) { CTX_GUARD(c); return c->eng.finalize(); }
+int pfb_parse_bwt(pfb_ctx *c) { CTX_GUARD(c); return c->eng.do_parse_bwt(); }
+int pfb_append(pfb_ctx *l, pfb_ctx *r) {
+    CTX_GUARD(l);
+    if (!r) return l->eng.fail(PFB_ERR_ARG, "null rhs");
+    if (r->eng.device != l->eng.device) return l->eng.fail(PFB_ERR_ARG, "contexts live on different devices");
+    cudaStreamSynchronize(r->eng.ws.st);
+    return l->eng.append_parse_of(r->eng);
+}
+int pfb_save_parse(pfb_ctx *c, const char *prefix, int with_parse_bwt, int with_sai) {
+    CTX_GUARD(c);
+    return c->eng.save_parse(prefix, with_parse_bwt != 0, with_sai != 0);
+}
+int pfb_load_parse(pfb_ctx *c, const char *prefix, int with_parse_bwt, int with_sai) {
+    CTX_GUARD(c);
+    return c->eng.load_parse(prefix, with_parse_bwt != 0, with_sai != 0);
+}
+int pfb_build_bwt(pfb_ctx *c, int sa, int rssa) { CTX_GUARD(c); return c->eng.build(sa != 0, rssa != 0); }
+int pfb_write_bwt(pfb_ctx *c, const char *prefix, int sa, int rssa, const char *stdout_ext) {
+    CTX_GUARD(c);
+    return c->eng.write_bwt_files(prefix, sa != 0, rssa != 0, stdout_ext ? stdout_ext : "");
+}
+
+int pfb_get_sizes(const pfb_ctx *c, pfb_sizes *s) {
+    if (!c || !s) return PFB_ERR_ARG;
+    const pfb::Engine &e = c->eng;
+    memset(s, 0, sizeof(*s));
+    s->bits = e.prm.bits;
+    if (e.parsed) {
+        s->n = e.parse.n; s->n_phrases = e.parse.P; s->n_words = e.parse.Dw; s->dict_bytes = e.parse.dsize;
+        s->has_parse_bwt = e.parse.has_parse_bwt;
+    }
+    if (e.built) {
+        s->r = e.bwt.r; s->easy = e.bwt.easy; s->hard = e.bwt.hard;
+        s->has_bwt = 1; s->has_sa = (e.built_sa || e.built_rssa); s->has_rssa = e.built_rssa;
+    }
+    return PFB_OK;
+}
+int pfb_get_stats(const pfb_ctx *c, pfb_stats *s) {
+    if (!c || !s) return PFB_ERR_ARG;
+    const pfb::StageTimes &t = c->eng.tm;
+    memset(s, 0, sizeof(*s));
+    s->normalise_ms = t.normalise; s->trigger_ms = t.trigger; s->compact_ms = t.compact; s->fingerprint_ms = t.fingerprint;
+    s->dedup_ms = t.dedup; s->phrase_sort_ms = t.phrase_sort; s->dict_build_ms = t.dict_build; s->parse_sa_ms = t.parse_sa;
+    s->parse_bwt_ms = t.parse_bwt; s->dict_sort_ms = t.dict_sort; s->groups_ms = t.groups; s->emit_ms = t.emit; s->runs_ms = t.runs;
+    s->dedup_attempts = t.dedup_attempts; s->phrase_sort_rounds = t.phrase_sort_rounds;
+    s->parse_sa_rounds = t.parse_sa_rounds; s->dict_sort_rounds = t.dict_sort_rounds;
+    s->launches_own = pfb::launch_stats().own; s->launches_lib = pfb::launch_stats().lib;
+    s->dev_bytes_peak = pfb::dev_bytes_peak();
+    return PFB_OK;
+}
+
+int pfb_copy_dict(pfb_ctx *c, uint8_t *o) { CTX_GUARD(c); return copy_out(c, c->eng.parse.dict, c->eng.parse.dsize, o, c->eng.parsed, "dict"); }
+int pfb_copy_occ(pfb_ctx *c, void *o) { CTX_GUARD(c); return copy_out_uint(c, c->eng.parse.occ, c->eng.parse.Dw, o, c->eng.parsed, "occ"); }
+int pfb_copy_parse(pfb_ctx *c, uint32_t *o) { CTX_GUARD(c); return copy_out(c, c->eng.parse.parse, c->eng.parse.P, o, c->eng.parsed, "parse"); }
+int pfb_copy_last(pfb_ctx *c, uint8_t *o) { CTX_GUARD(c); return copy_out(c, c->eng.parse.last, c->eng.parse.P, o, c->eng.parsed && c->eng.parse.last.size(), "last"); }
+int pfb_copy_sai(pfb_ctx *c, void *o) { CTX_GUARD(c); return copy_out_uint(c, c->eng.parse.sai, c->eng.parse.P, o, c->eng.parsed && c->eng.parse.sai.size(), "sai"); }
+int pfb_copy_bwlast(pfb_ctx *c, uint8_t *o) { CTX_GUARD(c); return copy_out(c, c->eng.parse.bwlast, c->eng.parse.P + 1, o, c->eng.parsed && c->eng.parse.has_parse_bwt, "bwlast"); }
+int pfb_copy_ilist(pfb_ctx *c, void *o) { CTX_GUARD(c); return copy_out_uint(c, c->eng.parse.ilist, c->eng.parse.P + 1, o, c->eng.parsed && c->eng.parse.has_parse_bwt, "ilist"); }
+int pfb_copy_bwsai(pfb_ctx *c, void *o) { CTX_GUARD(c); return copy_out_uint(c, c->eng.parse.bwsai, c->eng.parse.P + 1, o, c->eng.parsed && c->eng.parse.has_parse_bwt && c->eng.parse.bwsai.size(), "bwsai"); }
+int pfb_copy_bwt(pfb_ctx *c, uint8_t *o) { CTX_GUARD(c); return copy_out(c, c->eng.bwt.bwt, c->eng.bwt.n + 1, o, c->eng.built, "bwt"); }
+int pfb_copy_sa(pfb_ctx *c, void *o) {
+    CTX_GUARD(c);
+    return copy_out(c, c->eng.bwt.sa, (c->eng.bwt.n + 1) * ((size_t)c->eng.prm.bits / 8), o, c->eng.built && (c->eng.built_sa || c->eng.built_rssa), "sa");
+}
+int pfb_copy_ssa(pfb_ctx *c, void *o) { CTX_GUARD(c); return copy_out(c, c->eng.bwt.ssa, 2 * c->eng.bwt.r * ((size_t)c->eng.prm.bits / 8), o, c->eng.built && c->eng.built_rssa, "ssa"); }
+int pfb_copy_esa(pfb_ctx *c, void *o) { CTX_GUARD(c); return copy_out(c, c->eng.bwt.esa, 2 * c->eng.bwt.r * ((size_t)c->eng.prm.bits / 8), o, c->eng.built && c->eng.built_rssa, "esa"); }
+
+int64_t pfb_get_docs(pfb_ctx *c, uint64_t *starts_out) {
+    if (!c) return PFB_ERR_ARG;
+    if (starts_out) for (size_t i = 0; i < c->eng.docs.starts.size(); ++i) starts_out[i] = c->eng.docs.starts[i];
+    return (int64_t)c->eng.docs.starts.size();
+}
+
+int pfb_upload_text(pfb_ctx *c) { CTX_GUARD(c); return c->eng.upload_text(); }
+int pfb_run_resident(pfb_ctx *c, int sa, int rssa) {
+    CTX_GUARD(c);
+    if (!c->eng.text_ready) return c->eng.fail(PFB_ERR_ARG, "no text resident on the device (call pfb_upload_text)");
+    int rc = c->eng.parse_device();
+    if (rc) return rc;
+    rc = c->eng.do_parse_bwt();
+    if (rc) return rc;
+    return c->eng.build(sa != 0, rssa != 0);
+}
+int pfb_release_text(pfb_ctx *c) { CTX_GUARD(c); c->eng.release_text(); return PFB_OK; }
+int pfb_clear(pfb_ctx *c) { CTX_GUARD(c); c->eng.clear(); return PFB_OK; }
+
+}  // extern "C"

@@ -69,22 +69,50 @@ struct Engine {
         return PFB_OK;
     }
 
+    // Records handed over in caller memory go straight to HBM (one H2D per record, padding
+    // written by a kernel); many small records are staged through `raw` instead.
     int add_records(const u8 *seq, const u64 *rec_len, u64 nrec) {
-        size_t off0 = raw.n;
-        u64 tot = 0;
-        for (u64 r = 0; r < nrec; ++r) tot += rec_len[r];
-        if (prm.bits == 32 && tot > 0xFFFFFFFFull) return fail(PFB_ERR_TOO_LONG_32, "input too long, please use 64-bit version");
-        raw.reserve(raw.n + tot + nrec * (u64)prm.w);
-        u64 src = 0;
-        for (u64 r = 0; r < nrec; ++r) {
-            raw.append(seq + src, rec_len[r]);
-            raw.append_fill('A', (size_t)prm.w);
-            src += rec_len[r];
-        }
-        docs.nrec += nrec; docs.total_len += tot;
-        push_host_segment(off0, raw.n - off0);
+        try {
+            u64 tot = 0;
+            for (u64 r = 0; r < nrec; ++r) tot += rec_len[r];
+            if (prm.bits == 32 && tot > 0xFFFFFFFFull) return fail(PFB_ERR_TOO_LONG_32, "input too long, please use 64-bit version");
+            const u64 w = (u64)prm.w;
+            if (nrec > 256) {
+                size_t off0 = raw.n;
+                raw.reserve(raw.n + tot + nrec * w);
+                u64 src = 0;
+                for (u64 r = 0; r < nrec; ++r) {
+                    raw.append(seq + src, rec_len[r]);
+                    raw.append_fill('A', (size_t)w);
+                    src += rec_len[r];
+                }
+                push_host_segment(off0, raw.n - off0);
+            } else if (nrec) {
+                Segment s;
+                s.on_device = true; s.len = tot + nrec * w;
+                s.dev.alloc(s.len);
+                u64 src = 0, dst = 0;
+                for (u64 r = 0; r < nrec; ++r) {
+                    if (rec_len[r]) h2d(s.dev.get() + dst, seq + src, rec_len[r], ws.st);
+                    u8 *pad = s.dev.get() + dst + rec_len[r];
+                    launch_for(w, ws.st, PFB_LAMBDA(u64 i) { pad[i] = 'A'; });
+                    src += rec_len[r]; dst += rec_len[r] + w;
+                }
+                stream_sync(ws.st);   // caller memory may be reused after return
+                pending_n += s.len;
+                segs.push_back(std::move(s));
+            }
+            docs.nrec += nrec; docs.total_len += tot;
+            invalidate();
+            return PFB_OK;
+        } catch (const Error &e) { return fail(e.code, e.what()); }
+    }
+
+    void clear() {
+        segs.clear(); raw.n = 0; pending_n = 0; docs = FastaResult();
+        text.buf.release(); text.n = 0;
+        parse = DeviceParse(); bwt = DeviceBwt();
         invalidate();
-        return PFB_OK;
     }
 
     void invalidate() { text_ready = false; parsed = false; built = false; }

@@ -17,6 +17,7 @@
 // 64-bit text positions.
 #pragma once
 #include "prim.cuh"
+#include "../../include/pfbwt_b200.h"
 
 namespace pfb {
 
@@ -24,18 +25,7 @@ typedef uint8_t u8;
 typedef uint32_t u32;
 typedef uint64_t u64;
 
-enum : int {
-    PFB_OK = 0,
-    PFB_ERR_ARG = -1,
-    PFB_ERR_INVALID_CHAR = -2,
-    PFB_ERR_LIMIT = -3,
-    PFB_ERR_NOMEM = -4,
-    PFB_ERR_CUDA = -5,
-    PFB_ERR_IO = -6,
-    PFB_ERR_ONE_WORD = -7,
-    PFB_ERR_INTERNAL = -8,
-    PFB_ERR_TOO_LONG_32 = -9,
-};
+// error codes: PFB_OK / PFB_ERR_* from include/pfbwt_b200.h
 
 static const u8 DOLLAR = 2, ENDOFWORD = 1, ENDOFDICT = 0;   // include/utils.h:8-10
 

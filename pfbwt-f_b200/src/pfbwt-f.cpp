@@ -1,0 +1,164 @@
+// pfbwt-f / pfbwt-f64 command-line driver over libpfbwt_b200 (C ABI).  Same flags,
+// file set and stderr lines as the reference driver (src/pfbwt-f.cpp:102-182 flags,
+// :209-245 run_parser, :272-349 run_pfbwt, :351-367 main).  -DM64 builds pfbwt-f64.
+#include "pfbwt_b200.h"
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <getopt.h>
+#include <string>
+
+#ifdef M64
+static const int BITS = 64;
+#else
+static const int BITS = 32;
+#endif
+
+struct Args {
+    std::string in_fname, output, stdout_ext;
+    size_t w = 10, p = 100;
+    int sa = 0, rssa = 0, mmap = 0, parse_only = 0, trim_non_acgt = 0, non_acgt_to_a = 0, pfbwt_only = 0, verbose = 0, print_docs = 0;
+    int device = 0;
+};
+
+struct Timer {   // src/pfbwt-f.cpp:35-50
+    std::chrono::time_point<std::chrono::system_clock> start;
+    std::string msg;
+    Timer(std::string m) : msg(m) { start = std::chrono::system_clock::now(); }
+    ~Timer() {
+        std::chrono::duration<double> d = std::chrono::system_clock::now() - start;
+        fprintf(stderr, "%s%.2fs\n", msg.c_str(), d.count());
+    }
+};
+
+static void die(const char *s) { perror(s); exit(1); }   // src/utils.c:13-17
+static void die_ctx(pfb_ctx *c) { fprintf(stderr, "%s\n", pfb_last_error(c)); exit(1); }
+
+static void print_help() {
+    fprintf(stderr, "%s. use the prefix-free parsing algorithm to build a BWT for %sgenomic data (B200 build).\n\n"
+                    "usage\n    ./%s [options] <fasta file>\n\n",
+            BITS == 64 ? "pfbwt-f64" : "pfbwt-f", BITS == 64 ? "BIG " : "", BITS == 64 ? "pfbwt-f64" : "pfbwt-f");
+    fprintf(stderr,
+"results\n    BWT of input saved to <fasta file>.bwt. Header lines are excluded.\n\noptions\n"
+"    -o                  output prefix.\n"
+"    -s                  Output full suffix array to <fasta file>.sa\n"
+"    -r                  Output run-length sampled suffix arrray to <fasta file>.ssa (run-starts) and <fasta file>.esa (run-ends)\n"
+"    -w <int>            window-size for parsing [default: 10]\n"
+"    -p <int>            modulo for parsing [default: 100]\n"
+"    -m                  accepted for compatibility (workspace lives in HBM)\n"
+"    --parse-only        only produce parse (dict, occ, ilist, last, bwlast)\n"
+"    --pfbwt-only        build pfbwt from parse + parse-bwt. Requires -o to match parse files' prefix.\n"
+"    --non-acgt-to-a     convert non-ACGT characters to A\n"
+"    --print-docs        write <prefix>.docs\n"
+"    --stdout <ext>      output file ending <ext> will be stdout instead (bwt, sa)\n"
+"    --device <int>      CUDA device ordinal [default: 0]\n"
+"    -h                  print this help message\n");
+}
+
+static Args parse_args(int argc, char **argv) {
+    Args args;
+    fputs("==== Command line:", stderr);
+    for (int i = 0; i < argc; i++) fprintf(stderr, " %s", argv[i]);
+    fputs("\n", stderr);
+    static struct option lopts[] = {
+        {"parse-only", no_argument, &args.parse_only, 1},
+        {"pfbwt-only", no_argument, &args.pfbwt_only, 1},
+        {"trim-non-acgt", no_argument, &args.trim_non_acgt, 1},
+        {"non-acgt-to-a", no_argument, &args.non_acgt_to_a, 1},
+        {"print-docs", no_argument, &args.print_docs, 1},
+        {"stdout", required_argument, NULL, 'c'},
+        {"verbose", no_argument, &args.verbose, 1},
+        {"sa", no_argument, NULL, 's'},
+        {"rssa", no_argument, NULL, 'r'},
+        {"mmap", no_argument, NULL, 'm'},
+        {"output", required_argument, NULL, 'o'},
+        {"window-size", required_argument, NULL, 'w'},
+        {"mod-val", required_argument, NULL, 'p'},
+        {"device", required_argument, NULL, 'D'},
+        {0, 0, 0, 0}};
+    int c;
+    while ((c = getopt_long(argc, argv, "w:p:o:hsrfm", lopts, NULL)) != -1) {
+        switch (c) {
+        case 'f': break;   // legacy
+        case 's': args.sa = 1; break;
+        case 'r': args.rssa = 1; break;
+        case 'w': args.w = atoi(optarg); break;
+        case 'm': args.mmap = 1; break;
+        case 'p': args.p = atoi(optarg); break;
+        case 'h': print_help(); exit(0);
+        case 'o': args.output.assign(optarg); break;
+        case 'c': args.stdout_ext = optarg; break;
+        case 'D': args.device = atoi(optarg); break;
+        case '?': fprintf(stderr, "Unknown option. Use -h for help.\n"); exit(1);
+        }
+    }
+    if (argc == optind + 1) args.in_fname.assign(argv[optind]);
+    else { fprintf(stderr, "reading from stdin. Parsing might be a bit slow.\n"); args.in_fname.assign("-"); }
+    if (args.non_acgt_to_a && args.trim_non_acgt) die("cannot have both --non-acgt-to-a and --trim-non-acgt options enabled at same time");
+    if (args.in_fname == "-" && args.output == "") die("if reading from stdin, need a prefix for output files (-o, --output)");
+    if (args.in_fname != "-" && args.output == "") args.output = args.in_fname;
+    if (args.parse_only && args.pfbwt_only) die("cannot simulatneously do parse_only and pfbwt_only");
+    return args;
+}
+
+int main(int argc, char **argv) {
+    Args args = parse_args(argc, argv);
+    pfb_ctx *ctx = pfb_create(args.device, BITS);
+    if (!ctx) { fprintf(stderr, "%s\n", pfb_create_error()); return 1; }
+    pfb_parse_params pp;
+    memset(&pp, 0, sizeof(pp));
+    pp.w = (uint32_t)args.w; pp.p = args.p; pp.get_sai = args.sa || args.rssa; pp.store_docs = args.print_docs;
+    pp.verbose = args.verbose; pp.trim_non_acgt = args.trim_non_acgt; pp.non_acgt_to_a = args.non_acgt_to_a;
+    if (pfb_set_params(ctx, &pp)) die_ctx(ctx);
+    const int any_sa = args.sa || args.rssa;
+    if (!args.pfbwt_only) {   // run_parser, src/pfbwt-f.cpp:209-245
+        fprintf(stderr, "running parser...\n");
+        fprintf(stderr, "starting...\n");
+        {
+            Timer t("TASK\tparsing input\t");
+            if (pfb_add_fasta(ctx, args.in_fname.c_str())) die_ctx(ctx);
+        }
+        {
+            Timer t("TASK\tfinalizing parse, writing dict, occs, and ranks\t");
+            if (pfb_finalize(ctx)) die_ctx(ctx);
+        }
+        {
+            Timer t("TASK\tranking and bwt-ing parse and processing last-chars\t");
+            if (pfb_parse_bwt(ctx)) {
+                fprintf(stderr, "%s: Success\n", pfb_last_error(ctx));
+                exit(1);
+            }
+            if (pfb_save_parse(ctx, args.output.c_str(), 1, any_sa)) die_ctx(ctx);
+        }
+        if (args.trim_non_acgt) { FILE *f = fopen((args.output + ".ntab").c_str(), "wb"); if (f) fclose(f); }
+        pfb_release_text(ctx);
+    } else {
+        if (pfb_load_parse(ctx, args.output.c_str(), 1, any_sa)) die_ctx(ctx);
+    }
+    if (!args.parse_only) {   // run_pfbwt, src/pfbwt-f.cpp:272-349
+        fprintf(stderr, "generating BWT using pfbwt algorithm...\n");
+        fprintf(stderr, "workspace will be contained in HBM\n");
+        {
+            Timer t(any_sa ? "TASK\tgenerating final BWT w/ full and/or run-length SA\t" : "TASK\tgenerating final BWT w/o SA\t");
+            if (pfb_build_bwt(ctx, args.sa, args.rssa)) die_ctx(ctx);
+            if (pfb_write_bwt(ctx, args.output.c_str(), args.sa, args.rssa, args.stdout_ext.empty() ? NULL : args.stdout_ext.c_str())) die_ctx(ctx);
+        }
+        pfb_sizes sz;
+        pfb_get_sizes(ctx, &sz);
+        fprintf(stderr, "# easy cases: %lu, # hard cases: %lu\n", (unsigned long)sz.easy, (unsigned long)sz.hard);
+        fprintf(stderr, "n: %lu\n", (unsigned long)sz.n);
+        fprintf(stderr, "r: %lu\n", (unsigned long)sz.r);
+        fprintf(stderr, "n/r: %.3f\n", (double)sz.n / (double)sz.r);
+    }
+    if (args.verbose) {
+        pfb_stats s;
+        pfb_get_stats(ctx, &s);
+        fprintf(stderr, "GPU\tnormalise %.3f trigger %.3f compact %.3f fingerprint %.3f dedup %.3f phrase_sort %.3f dict_build %.3f "
+                        "parse_sa %.3f parse_bwt %.3f dict_sort %.3f groups %.3f emit %.3f runs %.3f ms\n",
+                s.normalise_ms, s.trigger_ms, s.compact_ms, s.fingerprint_ms, s.dedup_ms, s.phrase_sort_ms, s.dict_build_ms,
+                s.parse_sa_ms, s.parse_bwt_ms, s.dict_sort_ms, s.groups_ms, s.emit_ms, s.runs_ms);
+    }
+    pfb_destroy(ctx);
+    return 0;
+}

@@ -1,0 +1,53 @@
+"""CPU tests (-m "not gpu") of the HOST LOGIC of the device pipeline: tests/emu/pfb_emu compiles
+pfbwt-f_b200/csrc/{pipeline.cuh,engine.hpp} with every launch/scan/sort executed as a serial loop
+(developer logic check, test infrastructure only - never linked into the library) and must write
+files identical to the oracle.  The real parity tests are the `-m gpu` ones."""
+import os
+import subprocess
+import pytest
+from pfp_util import ROOT, write_fasta, random_bases, pangenome_records, nrun_records, run, exts_for, assert_same_files
+
+EMU = os.path.join(ROOT, "tests", "emu", "pfb_emu")
+
+
+@pytest.fixture(scope="module")
+def emu():
+    subprocess.run(["make", "-C", ROOT, "emu"], check=True, stdout=subprocess.DEVNULL)
+    return EMU
+
+
+CASES = [
+    ("e_rand", lambda: [("r", random_bases(150_000, 2))], 32, ["-s", "-r"]),
+    ("e_pan", lambda: pangenome_records(60_000, 6, 60, 8), 64, ["-s", "-r"]),
+    ("e_pan_nosa", lambda: pangenome_records(60_000, 6, 60, 8), 32, []),
+    ("e_nrun", lambda: nrun_records(2, 50_000, 38), 64, ["-s", "--non-acgt-to-a"]),
+    ("e_w3p5", lambda: [("a", random_bases(20_000, 3)), ("b", random_bases(0, 4)), ("c", random_bases(7, 5))], 32,
+     ["-s", "-r", "-w", "3", "-p", "5"]),
+]
+
+
+@pytest.mark.parametrize("name,gen,bits,flags", CASES, ids=[c[0] for c in CASES])
+def test_emu_matches_oracle(name, gen, bits, flags, emu, ref_bins, datadir):
+    fa = os.path.join(datadir, name + ".fa")
+    write_fasta(fa, gen(), line_width=50)
+    a, b = os.path.join(datadir, name + ".port"), os.path.join(datadir, name + ".emu")
+    run([ref_bins["pfp_oracle"], "--bits", str(bits)] + flags + ["-o", a, fa])
+    run([emu, "--bits", str(bits)] + flags + ["-o", b, fa])
+    assert_same_files(a, b, exts_for("-s" in flags, "-r" in flags))
+
+
+def test_emu_merge(emu, ref_bins, datadir):
+    recs = pangenome_records(50_000, 6, 50, 77)
+    parts = []
+    for g in range(3):
+        p = os.path.join(datadir, f"epart{g}.fa")
+        write_fasta(p, recs[2 * g:2 * g + 2], line_width=60)
+        run([emu, "--bits", "64", "--parse-only", "-s", p])
+        parts.append(p)
+    allfa = os.path.join(datadir, "eall.fa")
+    write_fasta(allfa, recs, line_width=60)
+    mono = os.path.join(datadir, "emono")
+    run([ref_bins["pfp_oracle"], "--bits", "64", "--parse-only", "-s", "-o", mono, allfa])
+    merged = os.path.join(datadir, "emerged")
+    run([emu, "--merge", "--bits", "64", "-s", "-o", merged] + parts)
+    assert_same_files(mono, merged, ["dict", "occ", "parse", "n", "bwlast", "ilist", "bwsai"])

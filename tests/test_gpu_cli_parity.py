@@ -1,0 +1,82 @@
+"""GPU parity through the drop-in binaries (bin/pfbwt-f, bin/pfbwt-f64, bin/merge_pfp, all thin
+drivers over the C ABI) against the oracle: every file the reference writes must be byte-identical.
+Oracle = unmodified reference binaries (oracle/_ref) when present, else the CPU restatement."""
+import os
+import pytest
+import numpy as np
+from pfp_util import (ROOT, write_fasta, random_bases, pangenome_records, nrun_records, run, exts_for,
+                      assert_same_files, GOLDEN)
+
+pytestmark = pytest.mark.gpu
+BIN = os.path.join(ROOT, "bin")
+
+
+def oracle_cmd(ref_bins, bits, args, out, fa):
+    name = "pfbwt-f64" if bits == 64 else "pfbwt-f"
+    if ref_bins[name]:
+        return [ref_bins[name]] + args + ["-o", out, fa]
+    return [ref_bins["pfp_oracle"], "--bits", str(bits)] + args + ["-o", out, fa]
+
+
+CASES = [
+    # name, generator, bits, flags
+    ("rand200k_sr", lambda: [("r", random_bases(200_000, 11))], 32, ["-s", "-r"]),
+    ("rand1m", lambda: [("r", random_bases(1_000_000, 1))], 32, []),
+    ("rand1m_s64", lambda: [("r", random_bases(1_000_000, 1))], 64, ["-s"]),
+    ("pan8x200k", lambda: pangenome_records(200_000, 8, 200, 7), 64, ["-s", "-r"]),
+    ("pan8x200k_nosa", lambda: pangenome_records(200_000, 8, 200, 7), 32, []),
+    ("nrun", lambda: nrun_records(3, 100_000, 38), 64, ["-s", "-r", "--non-acgt-to-a"]),
+    ("nrun_keepN", lambda: nrun_records(3, 100_000, 38), 32, ["-s"]),
+    ("w4p7", lambda: [("a", random_bases(50_000, 3)), ("b", random_bases(1, 4)), ("c", random_bases(30_000, 5))], 32,
+     ["-s", "-r", "-w", "4", "-p", "7"]),
+    ("w20p300", lambda: pangenome_records(300_000, 4, 100, 9), 64, ["-s", "-w", "20", "-p", "300"]),
+]
+
+
+@pytest.mark.parametrize("name,gen,bits,flags", CASES, ids=[c[0] for c in CASES])
+def test_cli_matches_oracle(name, gen, bits, flags, ref_bins, datadir):
+    fa = os.path.join(datadir, name + ".fa")
+    write_fasta(fa, gen(), line_width=70)
+    a, b = os.path.join(datadir, name + ".ref"), os.path.join(datadir, name + ".gpu")
+    run(oracle_cmd(ref_bins, bits, flags, a, fa))
+    run([os.path.join(BIN, "pfbwt-f64" if bits == 64 else "pfbwt-f")] + flags + ["-o", b, fa])
+    assert_same_files(a, b, exts_for("-s" in flags, "-r" in flags))
+
+
+@pytest.mark.parametrize("fa", ["single_chrom.fa", "mult_chroms.fa"])
+def test_cli_reference_fixtures(fa, ref_bins, datadir):
+    """config 1: the reference's own tests/data FASTA, pfbwt-f -w 10 -p 100 -s -r"""
+    src = os.path.join(GOLDEN, fa)
+    a, b = os.path.join(datadir, fa + ".ref"), os.path.join(datadir, fa + ".gpu")
+    run(oracle_cmd(ref_bins, 32, ["-s", "-r"], a, src))
+    run([os.path.join(BIN, "pfbwt-f"), "-s", "-r", "-o", b, src])
+    assert_same_files(a, b, exts_for(True, True))
+
+
+def test_cli_merge_matches_monolithic(ref_bins, datadir):
+    """config 5 (scaled): per-part --parse-only, merge_pfp -s --parse-bwt, --pfbwt-only == monolithic"""
+    recs = pangenome_records(150_000, 8, 150, 21)
+    parts = []
+    for g in range(4):
+        p = os.path.join(datadir, f"mpart{g}.fa")
+        write_fasta(p, recs[2 * g:2 * g + 2], line_width=60)
+        run([os.path.join(BIN, "pfbwt-f64"), "--parse-only", "-s", p])
+        parts.append(p)
+    allfa = os.path.join(datadir, "mall.fa")
+    write_fasta(allfa, recs, line_width=60)
+    mono = os.path.join(datadir, "mono")
+    run(oracle_cmd(ref_bins, 64, ["-s"], mono, allfa))
+    merged = os.path.join(datadir, "merged")
+    run([os.path.join(BIN, "merge_pfp"), "-s", "--parse-bwt", "-o", merged, "-t", "4"] + parts)
+    assert_same_files(mono, merged, ["dict", "occ", "parse", "n", "bwlast", "ilist", "bwsai"])
+    run([os.path.join(BIN, "pfbwt-f64"), "--pfbwt-only", "-s", "-o", merged])
+    assert_same_files(mono, merged, ["bwt", "sa"])
+
+
+def test_cli_invalid_char_exits_1(datadir):
+    fa = os.path.join(datadir, "bad.fa")
+    with open(fa, "w") as f:
+        f.write(">x\nACGTRACGT\n")
+    r = run([os.path.join(BIN, "pfbwt-f"), fa], check=False)
+    assert r.returncode == 1
+    assert b"error, invalid character 82/R -> 5" in r.stderr
