@@ -1,0 +1,274 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the fasta -> .bwt hot path (BASELINE.json metric:
+input bases/sec end-to-end at 1/2/4/8 B200 + fraction of the HBM roofline).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--bases B]
+
+Workload (config.workload): BASELINE.json configs[1] = synthetic uniform-random ACGT single
+sequence, -w 10 -p 100, 32-bit mode, .bwt only; 1 Gbp per GPU by default (--bases overrides, e.g.
+for quick checks).  A "step" is one pass of the whole hot path (parse -> parse BWT -> dictionary
+suffix sort -> BWT assembly) over one text.
+
+  value      bases/s with the text already resident in HBM (pfb_run_resident), all ranks summed
+  e2e        bases/s through the C ABI with HOST buffers: H2D of the record bytes from pinned
+             memory and D2H of the .bwt image inside the timed region
+  roofline   dominant stage (dictionary suffix sort): algorithmic bytes D*(1+U)
+             divided by its CUDA-event time, against MEASURED_PEAKS.json hbm_gbs
+  cpu_baseline  unmodified reference binary (oracle/_ref/pfbwt-f) on a bounded sample, 1 core
+
+--impl reference times the reference's own CPU implementation (oracle/_ref/pfbwt-f) on a bounded
+sample of the same workload (rank 0 only).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+W, PMOD = 10, 100
+LUT = np.frombuffer(b"ACGT", dtype=np.uint8)
+
+
+def gen_bases(out, seed):
+    """uniform ACGT (config 2 recipe: default_rng(seed), lut[rng.integers(0,4,...)]) into `out`."""
+    rng = np.random.default_rng(seed)
+    n = len(out)
+    step = 50_000_000
+    for s in range(0, n, step):
+        m = min(step, n - s)
+        out[s:s + m] = LUT[rng.integers(0, 4, m, dtype=np.uint8)]
+
+
+def hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples = []
+        self.reasons = set()
+        self.stop_flag = False
+        self.max_mhz = None
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        while not self.stop_flag:
+            try:
+                o = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                                   stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, timeout=5).stdout.decode().strip()
+                f = [x.strip() for x in o.split(",")]
+                self.samples.append(float(f[0]))
+                self.max_mhz = float(f[1])
+                for nm, v in zip(names, f[2:]):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def run_reference_sample(bases, sample_n):
+    """time the unmodified reference pfbwt-f on the first sample_n bases; returns (bases/s, seconds)"""
+    exe = os.path.join(ROOT, "oracle", "_ref", "pfbwt-f")
+    kind = "reference"
+    if not os.path.exists(exe):
+        exe = os.path.join(ROOT, "oracle", "_ref", "pfp_oracle")
+        kind = "port"
+        if not os.path.exists(exe):
+            subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "port"], check=True, stdout=subprocess.DEVNULL)
+    with tempfile.TemporaryDirectory() as td:
+        fa = os.path.join(td, "sample.fa")
+        with open(fa, "wb") as f:
+            f.write(b">sample\n")
+            f.write(bases[:sample_n].tobytes())
+            f.write(b"\n")
+        t0 = time.perf_counter()
+        subprocess.run([exe, "-w", str(W), "-p", str(PMOD), "-o", os.path.join(td, "out"), fa], check=True,
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        dt = time.perf_counter() - t0
+    return sample_n / dt, dt, kind
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--bases", type=int, default=1_000_000_000)
+    ap.add_argument("--ref-sample", type=int, default=12_000_000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    n = args.bases
+    workload = f"config2: synthetic {n / 1e9:g} Gbp uniform-random ACGT single sequence per GPU, -w {W} -p {PMOD}, 32-bit mode, .bwt only"
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        sample_n = min(args.ref_sample, n)
+        bases = np.empty(sample_n, dtype=np.uint8)
+        gen_bases(bases, 1)
+        for _ in range(min(args.warmup, 1)):
+            run_reference_sample(bases, min(sample_n, 2_000_000))
+        t_tot, kind = 0.0, "reference"
+        for _ in range(args.steps):
+            _, dt, kind = run_reference_sample(bases, sample_n)
+            t_tot += dt
+        v = sample_n * args.steps / t_tot
+        line = {"impl": "reference", "metric": "input bases/sec end-to-end fasta->.bwt", "value": v, "unit": "bases/s",
+                "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_tot / args.steps,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/u32/u64 integer",
+                "data": "synthetic", "config": {"workload": workload},
+                "cpu_baseline": {"value": v, "unit": "bases/s", "cores": 1, "kind": kind,
+                                 "sample": f"first {sample_n} bases of the workload text, whole pfbwt-f run incl. file I/O"},
+                "e2e": {"value": v, "unit": "bases/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    from pfbwt_b200_loader import binding
+    B = binding()
+
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    torch.cuda.set_device(local_rank)
+
+    # synthetic text of this rank in pinned host memory (rank r uses seed 1+r)
+    host = torch.empty(n, dtype=torch.uint8).pin_memory()
+    bases = host.numpy()
+    gen_bases(bases, 1 + rank)
+    out_host = torch.empty(n + W + 1, dtype=torch.uint8).pin_memory()
+    rec_len = np.array([n], dtype=np.uint64)
+
+    ctx = B.Context(device=local_rank, bits=32, w=W, p=PMOD)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---------------- value: text resident in HBM ---------------------------------------------
+    ctx.add_records(host.data_ptr(), rec_len)
+    ctx.upload_text()
+    for _ in range(args.warmup):
+        ctx.run_resident(False, False)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = ctx.stats()
+    barrier()
+    t0 = time.perf_counter()
+    stage_acc = {}
+    for _ in range(args.steps):
+        ctx.run_resident(False, False)
+        st = ctx.stats()
+        for k, v in st.items():
+            if k.endswith("_ms"):
+                stage_acc[k] = stage_acc.get(k, 0.0) + v
+    barrier()
+    t_res = time.perf_counter() - t0
+    st1 = ctx.stats()
+    sz = ctx.sizes()
+    D = sz.dict_bytes
+    launches = (st1["launches_own"] - launches0["launches_own"])
+    launches_lib = (st1["launches_lib"] - launches0["launches_lib"])
+
+    # ---------------- e2e: host buffers, H2D + D2H inside the timed region -----------------------
+    def e2e_step():
+        ctx.clear()
+        ctx.add_records(host.data_ptr(), rec_len)      # H2D from pinned memory
+        ctx.finalize()
+        ctx.bwt_of_parse()
+        ctx.generate_bwt(False, False)
+        ctx.bwt(out=out_host.numpy()[:n + W + 1])         # D2H of the .bwt image (n+w+1 bytes)
+
+    for _ in range(max(1, min(args.warmup, 2))):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    barrier()
+    t_e2e = time.perf_counter() - t0
+    sampler.stop_flag = True
+    sampler.join()
+
+    # max over ranks
+    if world > 1:
+        t = torch.tensor([t_res, t_e2e], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t_res, t_e2e = float(t[0]), float(t[1])
+
+    if rank == 0:
+        peak, peak_kind = hbm_peak()
+        stage_ms = {k: v / args.steps for k, v in stage_acc.items()}
+        dom = max(stage_ms, key=stage_ms.get)
+        U = 4
+        alg_bytes = {  # SURVEY.md 8(d) per-stage floors
+            "dict_sort_ms": D * (1 + U),
+            "emit_ms": D * (1 + U) + (sz.n_phrases + 1) * (2 * U + 1) + (sz.n + 1),
+            "groups_ms": D * (1 + U),
+            "trigger_ms": sz.n + sz.n_phrases * (5 + U),
+        }.get(dom, sz.n)
+        achieved = alg_bytes / (stage_ms[dom] * 1e-3) / 1e9
+        cpu = None
+        if not args.no_cpu_baseline:
+            sample_n = min(args.ref_sample, n)
+            v, dt, kind = run_reference_sample(bases, sample_n)
+            cpu = {"value": v, "unit": "bases/s", "cores": 1, "kind": kind,
+                   "sample": f"first {sample_n} bases of rank 0's text, whole pfbwt-f -w {W} -p {PMOD} run incl. file I/O ({dt:.1f} s)"}
+        line = {
+            "metric": "input bases/sec end-to-end fasta->.bwt",
+            "value": world * n * args.steps / t_res, "unit": "bases/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * t_res / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8/u32/u64 integer", "data": "synthetic",
+            "config": {"workload": workload, "n": int(sz.n), "phrases": int(sz.n_phrases), "dict_words": int(sz.n_words),
+                       "dict_bytes": int(D), "r": int(sz.r), "l2": "inputs larger than L2 (text 1 GB, dictionary 1.1 GB per step)",
+                       "multi_gpu": "independent text per rank, no data-path collective" if world > 1 else "single GPU"},
+            "e2e": {"value": world * n * args.steps / t_e2e, "unit": "bases/s", "h2d_bytes_per_step": int(n),
+                    "d2h_bytes_per_step": int(n + W + 1), "ms_per_step": 1e3 * t_e2e / args.steps},
+            "gpu_launches": int(launches), "gpu_launches_library_cub": int(launches_lib),
+            "roofline": {"bound": "hbm", "kernel": dom.replace("_ms", ""), "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_kind,
+                         "algorithmic_bytes": int(alg_bytes), "ms": stage_ms[dom]},
+            "stages_ms": stage_ms,
+            "clocks": sampler.summary(),
+            "dev_bytes_peak": int(st1["dev_bytes_peak"]),
+        }
+        if cpu:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

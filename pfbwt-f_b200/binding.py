@@ -1,0 +1,194 @@
+"""ctypes binding of libpfbwt_b200.so (include/pfbwt_b200.h) used by tests/, bench.py and
+__graft_entry__.py.  It is a thin view of the C ABI: no computation happens in Python and there
+is no fallback - loading fails loudly when the library has not been built, and pfb_create fails
+when no B200 is present."""
+import ctypes as C
+import os
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libpfbwt_b200.so")
+
+EXPORTS = [
+    "pfb_create", "pfb_destroy", "pfb_last_error", "pfb_create_error", "pfb_set_params", "pfb_add_fasta",
+    "pfb_add_records", "pfb_finalize", "pfb_parse_bwt", "pfb_append", "pfb_save_parse", "pfb_load_parse",
+    "pfb_build_bwt", "pfb_write_bwt", "pfb_get_sizes", "pfb_get_stats", "pfb_copy_dict", "pfb_copy_occ",
+    "pfb_copy_parse", "pfb_copy_last", "pfb_copy_sai", "pfb_copy_bwlast", "pfb_copy_ilist", "pfb_copy_bwsai",
+    "pfb_copy_bwt", "pfb_copy_sa", "pfb_copy_ssa", "pfb_copy_esa", "pfb_get_docs", "pfb_upload_text",
+    "pfb_run_resident", "pfb_release_text", "pfb_clear",
+]
+
+
+class ParseParams(C.Structure):
+    _fields_ = [("w", C.c_uint32), ("p", C.c_uint64), ("get_sai", C.c_int), ("store_docs", C.c_int),
+                ("verbose", C.c_int), ("trim_non_acgt", C.c_int), ("non_acgt_to_a", C.c_int)]
+
+
+class Sizes(C.Structure):
+    _fields_ = [("n", C.c_uint64), ("n_phrases", C.c_uint64), ("n_words", C.c_uint64), ("dict_bytes", C.c_uint64),
+                ("r", C.c_uint64), ("easy", C.c_uint64), ("hard", C.c_uint64), ("bits", C.c_int),
+                ("has_parse_bwt", C.c_int), ("has_bwt", C.c_int), ("has_sa", C.c_int), ("has_rssa", C.c_int)]
+
+
+class Stats(C.Structure):
+    _fields_ = [(k, C.c_float) for k in
+                ["normalise_ms", "trigger_ms", "compact_ms", "fingerprint_ms", "dedup_ms", "phrase_sort_ms",
+                 "dict_build_ms", "parse_sa_ms", "parse_bwt_ms", "dict_sort_ms", "groups_ms", "emit_ms", "runs_ms"]] + \
+               [(k, C.c_uint32) for k in ["dedup_attempts", "phrase_sort_rounds", "parse_sa_rounds", "dict_sort_rounds"]] + \
+               [("launches_own", C.c_uint64), ("launches_lib", C.c_uint64), ("dev_bytes_peak", C.c_uint64)]
+
+
+_lib = None
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} not built - run `make` (or __graft_entry__.build()); there is no CPU fallback")
+    lib = C.CDLL(LIB_PATH)
+    vp = C.c_void_p
+    lib.pfb_create.restype = vp
+    lib.pfb_create.argtypes = [C.c_int, C.c_int]
+    lib.pfb_destroy.restype = None
+    lib.pfb_destroy.argtypes = [vp]
+    lib.pfb_last_error.restype = C.c_char_p
+    lib.pfb_last_error.argtypes = [vp]
+    lib.pfb_create_error.restype = C.c_char_p
+    lib.pfb_set_params.argtypes = [vp, C.POINTER(ParseParams)]
+    lib.pfb_add_fasta.argtypes = [vp, C.c_char_p]
+    lib.pfb_add_records.argtypes = [vp, vp, vp, C.c_uint64]
+    for f in ["pfb_finalize", "pfb_parse_bwt", "pfb_upload_text", "pfb_release_text", "pfb_clear"]:
+        getattr(lib, f).argtypes = [vp]
+    lib.pfb_append.argtypes = [vp, vp]
+    lib.pfb_save_parse.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
+    lib.pfb_load_parse.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
+    lib.pfb_build_bwt.argtypes = [vp, C.c_int, C.c_int]
+    lib.pfb_run_resident.argtypes = [vp, C.c_int, C.c_int]
+    lib.pfb_write_bwt.argtypes = [vp, C.c_char_p, C.c_int, C.c_int, C.c_char_p]
+    lib.pfb_get_sizes.argtypes = [vp, C.POINTER(Sizes)]
+    lib.pfb_get_stats.argtypes = [vp, C.POINTER(Stats)]
+    for f in ["dict", "occ", "parse", "last", "sai", "bwlast", "ilist", "bwsai", "bwt", "sa", "ssa", "esa"]:
+        getattr(lib, "pfb_copy_" + f).argtypes = [vp, vp]
+    lib.pfb_get_docs.restype = C.c_int64
+    lib.pfb_get_docs.argtypes = [vp, vp]
+    _lib = lib
+    return lib
+
+
+class PfbError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"[{code}] {msg}")
+        self.code = code
+        self.msg = msg
+
+
+class Context:
+    """One pfb_ctx.  Method names follow the reference's classes (PfParser / PrefixFreeBWT)."""
+
+    def __init__(self, device=0, bits=32, w=10, p=100, get_sai=False, non_acgt_to_a=False, store_docs=False):
+        self.lib = load()
+        self.h = self.lib.pfb_create(device, bits)
+        if not self.h:
+            raise PfbError(-5, self.lib.pfb_create_error().decode())
+        self.bits = bits
+        self.utype = np.uint32 if bits == 32 else np.uint64
+        pp = ParseParams(w, p, int(get_sai), int(store_docs), 0, 0, int(non_acgt_to_a))
+        self._ck(self.lib.pfb_set_params(self.h, C.byref(pp)))
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise PfbError(rc, self.lib.pfb_last_error(self.h).decode(errors="replace"))
+
+    def close(self):
+        if self.h:
+            self.lib.pfb_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # parse step
+    def add_fasta(self, path):
+        self._ck(self.lib.pfb_add_fasta(self.h, path.encode()))
+
+    def add_records(self, seq, rec_len):
+        """seq: uint8 numpy array or an integer host address; rec_len: uint64 array"""
+        rec_len = np.ascontiguousarray(rec_len, dtype=np.uint64)
+        addr = seq if isinstance(seq, int) else seq.ctypes.data
+        self._ck(self.lib.pfb_add_records(self.h, addr, rec_len.ctypes.data, len(rec_len)))
+
+    def finalize(self):
+        self._ck(self.lib.pfb_finalize(self.h))
+
+    def bwt_of_parse(self):
+        self._ck(self.lib.pfb_parse_bwt(self.h))
+
+    def append(self, rhs):
+        self._ck(self.lib.pfb_append(self.h, rhs.h))
+
+    def save_parser(self, prefix, with_parse_bwt=False, with_sai=False):
+        self._ck(self.lib.pfb_save_parse(self.h, prefix.encode(), int(with_parse_bwt), int(with_sai)))
+
+    def load_parser(self, prefix, with_parse_bwt=False, with_sai=False):
+        self._ck(self.lib.pfb_load_parse(self.h, prefix.encode(), int(with_parse_bwt), int(with_sai)))
+
+    # BWT build
+    def generate_bwt(self, sa=False, rssa=False):
+        self._ck(self.lib.pfb_build_bwt(self.h, int(sa), int(rssa)))
+
+    def write_bwt(self, prefix, sa=False, rssa=False):
+        self._ck(self.lib.pfb_write_bwt(self.h, prefix.encode(), int(sa), int(rssa), None))
+
+    # measurement hooks
+    def upload_text(self):
+        self._ck(self.lib.pfb_upload_text(self.h))
+
+    def run_resident(self, sa=False, rssa=False):
+        self._ck(self.lib.pfb_run_resident(self.h, int(sa), int(rssa)))
+
+    def release_text(self):
+        self._ck(self.lib.pfb_release_text(self.h))
+
+    def clear(self):
+        self._ck(self.lib.pfb_clear(self.h))
+
+    # getters
+    def sizes(self):
+        s = Sizes()
+        self._ck(self.lib.pfb_get_sizes(self.h, C.byref(s)))
+        return s
+
+    def stats(self):
+        s = Stats()
+        self._ck(self.lib.pfb_get_stats(self.h, C.byref(s)))
+        return {k: getattr(s, k) for k, _ in Stats._fields_}
+
+    def _copy(self, what, count, dtype, out=None):
+        a = out if out is not None else np.empty(count, dtype=dtype)
+        self._ck(getattr(self.lib, "pfb_copy_" + what)(self.h, a.ctypes.data))
+        return a
+
+    def dict(self): return self._copy("dict", self.sizes().dict_bytes, np.uint8)
+    def occ(self): return self._copy("occ", self.sizes().n_words, self.utype)
+    def parse(self): return self._copy("parse", self.sizes().n_phrases, np.uint32)
+    def last(self): return self._copy("last", self.sizes().n_phrases, np.uint8)
+    def sai(self): return self._copy("sai", self.sizes().n_phrases, self.utype)
+    def bwlast(self): return self._copy("bwlast", self.sizes().n_phrases + 1, np.uint8)
+    def ilist(self): return self._copy("ilist", self.sizes().n_phrases + 1, self.utype)
+    def bwsai(self): return self._copy("bwsai", self.sizes().n_phrases + 1, self.utype)
+    def bwt(self, out=None): return self._copy("bwt", self.sizes().n + 1, np.uint8, out)
+    def sa(self, out=None): return self._copy("sa", self.sizes().n + 1, self.utype, out)
+    def ssa(self): return self._copy("ssa", 2 * self.sizes().r, self.utype)
+    def esa(self): return self._copy("esa", 2 * self.sizes().r, self.utype)
+
+    def docs(self):
+        n = self.lib.pfb_get_docs(self.h, None)
+        a = np.empty(max(n, 0), dtype=np.uint64)
+        if n > 0:
+            self.lib.pfb_get_docs(self.h, a.ctypes.data)
+        return a

@@ -810,23 +810,20 @@ inline int build_bwt(const DeviceParse &pp, const Params &prm, bool want_sa, boo
     }
     // classification per member: 0 = nothing to emit, 1 = easy (direct), 2 = hard (needs merge by ilist position)
     DevBuf<u64> hcnt(D), hoff(D);
-    DevBuf<u64> stats(2);
-    dev_memset(stats.get(), 0, 16, st);
     {
         const u8 *fl = flag.get(); const u32 *hd = head.get(); const u8 *gd = gdiff.get(); const u64 *cp = cnt.get();
-        u64 *hc = hcnt.get(); u64 *stp = stats.get();
+        u64 *hc = hcnt.get();
         launch_for(D, st, PFB_LAMBDA(u64 t) {
             u64 c = cp[t];
             bool single = fl[t] && (t + 1 == D || fl[t + 1]);
             bool hard = c && !single && (any_sa || gd[hd[t]]);   // include/pfbwt.hpp:146
             hc[t] = hard ? c : 0;
-            if (c) atomic_add(&stp[hard ? 1 : 0], c);
         });
     }
     exclusive_sum<u64, u64>(hcnt.get(), hoff.get(), D, ws.sc, st);
     u64 nhard = read_scalar(hoff.get() + (D - 1), st) + read_scalar(hcnt.get() + (D - 1), st);
-    out.easy = read_scalar(stats.get(), st);
-    out.hard = read_scalar(stats.get() + 1, st);
+    out.hard = nhard;                 // "# hard cases" of include/pfbwt.hpp:188
+    out.easy = n + 1 - nhard;
     tm.groups = timer.stop();
 
     // K8 emission ------------------------------------------------------------------------
