@@ -7,7 +7,9 @@
 namespace pfb {
 size_t &dev_bytes_live() { static size_t v = 0; return v; }
 size_t &dev_bytes_peak() { static size_t v = 0; return v; }
+SlabPool &slab_pool() { static SlabPool *p = new SlabPool(); return *p; }   // leaked on purpose: outlives every static DevBuf
 }
+static int g_live_ctx = 0;
 
 struct pfb_ctx {
     pfb::Engine eng;
@@ -75,6 +77,8 @@ pfb_ctx *pfb_create(int device, int bits) {
     if ((e = cudaStreamCreateWithFlags(&c->eng.ws.st, cudaStreamNonBlocking)) != cudaSuccess) {
         g_create_err = cudaGetErrorString(e); delete c; return nullptr;
     }
+    ++g_live_ctx;
+    pfb::alloc_stream() = c->eng.ws.st;
     c->eng.raw.alloc_fn = pinned_alloc;
     c->eng.raw.free_fn = pinned_free;
     c->eng.raw.pinned = true;
@@ -89,8 +93,10 @@ void pfb_destroy(pfb_ctx *c) {
     c->eng.clear();
     c->eng.ws.sc.buf.release();
     c->eng.raw.release();
+    cudaStreamSynchronize(st);
     cudaStreamDestroy(st);
     delete c;
+    if (--g_live_ctx == 0) pfb::slab_pool().trim();   // last context gone: hand the slabs back
 }
 
 const char *pfb_last_error(const pfb_ctx *c) { return c ? c->eng.err.c_str() : g_create_err.c_str(); }
@@ -98,7 +104,8 @@ const char *pfb_create_error(void) { return g_create_err.c_str(); }
 
 #define CTX_GUARD(c)                       \
     if (!(c)) return PFB_ERR_ARG;          \
-    cudaSetDevice((c)->eng.device);
+    cudaSetDevice((c)->eng.device);        \
+    pfb::alloc_stream() = (c)->eng.ws.st;
 
 int pfb_set_params(pfb_ctx *c, const pfb_parse_params *p) {
     CTX_GUARD(c);

@@ -66,16 +66,44 @@ struct DeviceBwt {
     DevBuf<u8> ssa, esa;    // r pairs of U-byte ints each
 };
 
+// PFB_TRACE=1: every lap() is timed (CUDA events) and printed to stderr at the end of a run;
+// without it lap() costs nothing (no event, no synchronisation).
+struct TraceLog {
+    bool on = getenv("PFB_TRACE") != nullptr;
+    std::vector<std::pair<std::string, float>> v;
+    void dump(const char *title) {
+        if (!on) return;
+        float tot = 0;
+        for (auto &e : v) tot += e.second;
+        fprintf(stderr, "[pfb trace] %s: %.3f ms in %zu laps\n", title, tot, v.size());
+        for (auto &e : v) fprintf(stderr, "[pfb trace]   %-28s %9.3f ms\n", e.first.c_str(), e.second);
+        v.clear();
+    }
+};
+inline TraceLog &trace_log() { static TraceLog t; return t; }
+
 struct Timer {
 #ifndef PFB_EMU
-    cudaEvent_t a, b;
+    cudaEvent_t a, b, c;
     pfbStream_t s;
-    Timer(pfbStream_t st) : s(st) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, s); }
+    Timer(pfbStream_t st) : s(st) {
+        cudaEventCreate(&a); cudaEventCreate(&b); cudaEventCreate(&c);
+        cudaEventRecord(a, s);
+        if (trace_log().on) cudaEventRecord(c, s);
+    }
     float stop() { cudaEventRecord(b, s); cudaEventSynchronize(b); float ms = 0; cudaEventElapsedTime(&ms, a, b); cudaEventRecord(a, s); return ms; }
-    ~Timer() { cudaEventDestroy(a); cudaEventDestroy(b); }
+    void lap(const char *name) {
+        if (!trace_log().on) return;
+        cudaEventRecord(b, s); cudaEventSynchronize(b);
+        float ms = 0; cudaEventElapsedTime(&ms, c, b);
+        trace_log().v.emplace_back(name, ms);
+        cudaEventRecord(c, s);
+    }
+    ~Timer() { cudaEventDestroy(a); cudaEventDestroy(b); cudaEventDestroy(c); }
 #else
     Timer(pfbStream_t) {}
     float stop() { return 0.f; }
+    void lap(const char *) {}
 #endif
 };
 
@@ -705,262 +733,6 @@ inline int parse_bwt(DeviceParse &pp, const Params &prm, Workspace &ws, StageTim
     return PFB_OK;
 }
 
-// ===========================================================================
-// build_bwt: dict suffix sort + emission (include/pfbwt.hpp:96-223,
-// src/pfbwt-f.cpp:298-328)
-// ===========================================================================
-inline int build_bwt(const DeviceParse &pp, const Params &prm, bool want_sa, bool want_rssa, DeviceBwt &out, Workspace &ws,
-                     StageTimes &tm, std::string &err) {
-    pfbStream_t st = ws.st;
-    const u64 D = pp.dsize, Dw = pp.Dw, n = pp.n, P = pp.P;
-    const u64 w = (u64)prm.w;
-    const bool any_sa = want_sa || want_rssa;
-    const int U = prm.bits / 8;
-    if (!pp.has_parse_bwt) { err = "parse BWT (bwlast/ilist) not available"; return PFB_ERR_ARG; }
-    if (any_sa && pp.bwsai.size() == 0) { err = "bwsai not available"; return PFB_ERR_ARG; }
-    Timer timer(st);
-    const u8 *dict = pp.dict.get();
-    const u32 *wstart = pp.wstart.get();
-
-    // K6 dictionary suffix sort -----------------------------------------------------
-    DevBuf<u32> sa(D), rank(D);
-    DevBuf<u8> flag(D);
-    {
-        DevBuf<u64> key_a(D), key_b(D);
-        DevBuf<u32> val_b(D);
-        u64 *ka = key_a.get(); u32 *sp = sa.get();
-        launch_for(D, st, PFB_LAMBDA(u64 i) {
-            // 21 symbols up to and including the word's EndOfWord, then zeros
-            u64 key = 0;
-            int j = 0;
-            for (; j < 21; ++j) {
-                u64 o = i + (u64)j;
-                u32 c = o < D ? sym3(dict[o]) : 0u;
-                key = (key << 3) | c;
-                if (c == 0) { ++j; break; }
-            }
-            key <<= 3 * (21 - j);
-            ka[i] = key;
-            sp[i] = (u32)i;
-        });
-        sort_pairs(key_a, key_b, sa, val_b, D, 0, 63, ws.sc, st);
-        const u64 *ks = key_a.get(); u8 *fl = flag.get();
-        launch_for(D, st, PFB_LAMBDA(u64 j) { fl[j] = (j == 0 || ks[j] != ks[j - 1]) ? 1 : 0; });
-    }
-    ranks_from_flags(sa, flag, rank, D, ws);
-    {
-        const u32 Dw32 = (u32)Dw;
-        // a tied suffix is complete once its EndOfWord lies inside the compared prefix
-        int rc = prefix_doubling(sa, rank, flag, D, 21, PFB_LAMBDA(u32 idx, u64 h) {
-            u32 d = word_of(wstart, Dw32 + 1, idx);   // wstart[Dw] = position of EndOfDict
-            u64 sl = d < Dw32 ? (u64)(wstart[d + 1] - 1 - idx) : 0;
-            return sl < h;
-        }, ws, &tm.dict_sort_rounds, err);
-        if (rc) return rc;
-    }
-    tm.dict_sort = timer.stop();
-
-    // K7 groups, counts, offsets ------------------------------------------------------
-    // per sorted position t: word, suffix length, validity (> w), occ(word)
-    DevBuf<u32> wordv(D);
-    DevBuf<u64> cnt(D), off(D);
-    DevBuf<u32> cum(Dw + 1);    // exclusive sums of occ: ilist slots of word d = ilist[1+cum[d] ..)
-    exclusive_sum<u32, u32>(pp.occ.get(), cum.get(), Dw, ws.sc, st);
-    {
-        const u32 *occ = pp.occ.get(); u32 *cm = cum.get();
-        launch_for(1, st, PFB_LAMBDA(u64) { cm[Dw] = Dw ? cm[Dw - 1] + occ[Dw - 1] : 0; });
-    }
-    {
-        const u32 *sp = sa.get(); const u32 *occ = pp.occ.get(); u32 *wv = wordv.get(); u64 *cp = cnt.get();
-        const u32 Dw32 = (u32)Dw;
-        launch_for(D, st, PFB_LAMBDA(u64 t) {
-            u32 idx = sp[t];
-            u32 d = word_of(wstart, Dw32 + 1, idx);
-            u64 sl = d < Dw32 ? (u64)(wstart[d + 1] - 1 - idx) : 0;
-            bool valid = sl > w;                 // include/pfbwt.hpp:114
-            wv[t] = d;
-            cp[t] = valid ? (u64)occ[d] : 0;
-        });
-    }
-    exclusive_sum<u64, u64>(cnt.get(), off.get(), D, ws.sc, st);
-    {
-        u64 total = read_scalar(off.get() + (D - 1), st) + read_scalar(cnt.get() + (D - 1), st);
-        if (total != n + 1) { err = "internal: emitted positions " + std::to_string(total) + " != n+1 = " + std::to_string(n + 1); return PFB_ERR_INTERNAL; }
-    }
-    // group structure: head position of each t, per-group "chars differ" flag
-    DevBuf<u32> head(D);
-    {
-        DevBuf<u32> hd(D);
-        const u8 *fl = flag.get(); u32 *hp = hd.get();
-        launch_for(D, st, PFB_LAMBDA(u64 j) { hp[j] = fl[j] ? (u32)j : 0; });
-        inclusive_max(hd.get(), head.get(), D, ws.sc, st);
-    }
-    DevBuf<u8> gdiff(D);
-    dev_memset(gdiff.get(), 0, D, st);
-    {
-        const u32 *sp = sa.get(); const u32 *hd = head.get(); u8 *gd = gdiff.get();
-        launch_for(D, st, PFB_LAMBDA(u64 t) {
-            u32 h = hd[t];
-            if (h == (u32)t) return;
-            u32 i0 = sp[h], i1 = sp[t];
-            u8 c0 = i0 > 1 ? dict[i0 - 1] : 0, c1 = i1 > 1 ? dict[i1 - 1] : 0;   // include/pfbwt.hpp:132,140
-            if (i0 == 0 || i1 == 0) return;   // full words never share a group
-            if (c0 != c1) gd[h] = 1;
-        });
-    }
-    // classification per member: 0 = nothing to emit, 1 = easy (direct), 2 = hard (needs merge by ilist position)
-    DevBuf<u64> hcnt(D), hoff(D);
-    {
-        const u8 *fl = flag.get(); const u32 *hd = head.get(); const u8 *gd = gdiff.get(); const u64 *cp = cnt.get();
-        u64 *hc = hcnt.get();
-        launch_for(D, st, PFB_LAMBDA(u64 t) {
-            u64 c = cp[t];
-            bool single = fl[t] && (t + 1 == D || fl[t + 1]);
-            bool hard = c && !single && (any_sa || gd[hd[t]]);   // include/pfbwt.hpp:146
-            hc[t] = hard ? c : 0;
-        });
-    }
-    exclusive_sum<u64, u64>(hcnt.get(), hoff.get(), D, ws.sc, st);
-    u64 nhard = read_scalar(hoff.get() + (D - 1), st) + read_scalar(hcnt.get() + (D - 1), st);
-    out.hard = nhard;                 // "# hard cases" of include/pfbwt.hpp:188
-    out.easy = n + 1 - nhard;
-    tm.groups = timer.stop();
-
-    // K8 emission ------------------------------------------------------------------------
-    out.n = n;
-    out.bwt.alloc(n + 1);
-    if (any_sa) out.sa.alloc((n + 1) * (u64)U);
-    u8 *bwt = out.bwt.get();
-    u8 *sa_out = out.sa.get();
-    const u32 *ilist = pp.ilist.get(); const u8 *bwlast = pp.bwlast.get(); const u64 *bwsai = pp.bwsai.get();
-    const u32 *cm = cum.get();
-    {   // easy members: occurrences already ordered by ilist position
-        const u32 *sp = sa.get(); const u32 *wv = wordv.get(); const u64 *cp = cnt.get(); const u64 *hc = hcnt.get();
-        const u64 *of = off.get();
-        launch_for(D, st, PFB_LAMBDA(u64 t) {
-            u64 c = cp[t];
-            if (!c || hc[t]) return;
-            u32 idx = sp[t], d = wv[t];
-            bool full = idx == wstart[d];
-            u64 sl = (u64)(wstart[d + 1] - 1 - idx);
-            u8 pc = idx > 1 ? dict[idx - 1] : 0;
-            u64 x = of[t];
-            u32 base = 1 + cm[d];
-            for (u64 j = 0; j < c; ++j) {
-                u32 ii = ilist[base + j];
-                bwt[x + j] = full ? bwlast[ii] : pc;          // include/pfbwt.hpp:119,151
-                if (any_sa) {
-                    u64 v = bwsai[ii] - sl;
-                    if (U == 4) reinterpret_cast<u32 *>(sa_out)[x + j] = (u32)v;
-                    else reinterpret_cast<u64 *>(sa_out)[x + j] = v;
-                }
-            }
-        });
-    }
-    if (nhard) {   // hard groups: gather (dense group, ilist position) keys, one global radix sort, scatter
-        DevBuf<u8> hh(D);
-        DevBuf<u32> hgid(D);
-        {
-            const u64 *hc = hcnt.get(); const u32 *hd = head.get(); u8 *hp = hh.get();
-            launch_for(D, st, PFB_LAMBDA(u64 t) { hp[t] = (hc[t] && (hd[t] == (u32)t || !hc[hd[t]])) ? 1 : 0; });
-        }
-        // (a hard group's head is always hard itself, so the second clause never fires;
-        //  kept as a guard)  dense id of the group = number of hard heads before it
-        u64 nhg = scan_flags(hh.get(), hgid.get(), D, ws);
-        const int ibits = bits_for(P);           // ilist values are in [0, P]
-        const int gbits = bits_for(nhg ? nhg - 1 : 0);
-        if (ibits + gbits > 64) { err = "internal: hard key overflow"; return PFB_ERR_INTERNAL; }
-        DevBuf<u64> hkey(nhard), hkey_b(nhard), hval(nhard), hval_b(nhard);
-        {
-            const u32 *sp = sa.get(); const u32 *wv = wordv.get(); const u64 *hc = hcnt.get(); const u64 *ho = hoff.get();
-            const u32 *hd = head.get(); const u32 *hg = hgid.get();
-            u64 *hk = hkey.get(); u64 *hv = hval.get();
-            launch_for(D, st, PFB_LAMBDA(u64 t) {
-                u64 c = hc[t];
-                if (!c) return;
-                u32 idx = sp[t], d = wv[t];
-                u8 pc = idx > 1 ? dict[idx - 1] : 0;
-                u32 h = hd[t];
-                u64 g = hg[h];
-                u64 e = ho[t];
-                u32 base = 1 + cm[d];
-                for (u64 j = 0; j < c; ++j) {
-                    u32 ii = ilist[base + j];
-                    hk[e + j] = (g << ibits) | (u64)ii;
-                    hv[e + j] = ((u64)h << 8) | pc;
-                }
-            });
-        }
-        sort_pairs(hkey, hkey_b, hval, hval_b, nhard, 0, ibits + gbits, ws.sc, st);
-        {
-            const u64 *hk = hkey.get(); const u64 *hv = hval.get(); const u64 *ho = hoff.get(); const u64 *of = off.get();
-            const u32 *sp = sa.get(); const u32 *wv = wordv.get();
-            const u64 imask = ibits >= 64 ? ~0ull : ((1ull << ibits) - 1);
-            launch_for(nhard, st, PFB_LAMBDA(u64 e) {
-                u64 v = hv[e];
-                u32 h = (u32)(v >> 8);
-                u8 pc = (u8)(v & 0xff);
-                u32 ii = (u32)(hk[e] & imask);
-                u64 x = of[h] + (e - ho[h]);
-                bwt[x] = pc;                                           // include/pfbwt.hpp:173-178
-                if (any_sa) {
-                    u32 idx = sp[h], d = wv[h];
-                    u64 sl = (u64)(wstart[d + 1] - 1 - idx);
-                    u64 s = bwsai[ii] - sl;
-                    if (U == 4) reinterpret_cast<u32 *>(sa_out)[x] = (u32)s;
-                    else reinterpret_cast<u64 *>(sa_out)[x] = s;
-                }
-            });
-        }
-    }
-    if (any_sa) {   // src/pfbwt-f.cpp:301
-        launch_for(1, st, PFB_LAMBDA(u64) {
-            if (U == 4) reinterpret_cast<u32 *>(sa_out)[0] = (u32)n;
-            else reinterpret_cast<u64 *>(sa_out)[0] = n;
-        });
-    }
-    tm.emit = timer.stop();
-
-    // K9 run boundaries + run-length SA samples (src/pfbwt-f.cpp:304-328) -------------------
-    {
-        DevBuf<u8> rf(n + 1);
-        u8 *rp = rf.get();
-        launch_for(n + 1, st, PFB_LAMBDA(u64 x) { rp[x] = bwt[x] != (x ? bwt[x - 1] : (u8)0) ? 1 : 0; });
-        if (!want_rssa) {
-            out.r = reduce_sum<u8, u64>(rf.get(), n + 1, ws.sc, st);
-        } else {
-            DevBuf<u64> ridx(n + 1);
-            exclusive_sum<u8, u64>(rf.get(), ridx.get(), n + 1, ws.sc, st);
-            u64 r = read_scalar(ridx.get() + n, st) + read_scalar(rf.get() + n, st);
-            out.r = r;
-            out.ssa.alloc(2 * r * (u64)U);
-            out.esa.alloc(2 * r * (u64)U);
-            u8 *ssa = out.ssa.get(); u8 *esa = out.esa.get(); const u64 *ri = ridx.get();
-            launch_for(n + 1, st, PFB_LAMBDA(u64 x) {
-                if (U == 4) {
-                    const u32 *S4 = reinterpret_cast<const u32 *>(sa_out);
-                    u32 *s4 = reinterpret_cast<u32 *>(ssa); u32 *e4 = reinterpret_cast<u32 *>(esa);
-                    if (rp[x]) {
-                        u64 k = ri[x];
-                        s4[2 * k] = (u32)x; s4[2 * k + 1] = S4[x];
-                        if (x) { e4[2 * (k - 1)] = (u32)(x - 1); e4[2 * (k - 1) + 1] = S4[x - 1]; }
-                    }
-                    if (x == n) { e4[2 * (r - 1)] = (u32)n; e4[2 * (r - 1) + 1] = S4[n]; }
-                } else {
-                    const u64 *S8 = reinterpret_cast<const u64 *>(sa_out);
-                    u64 *s8 = reinterpret_cast<u64 *>(ssa); u64 *e8 = reinterpret_cast<u64 *>(esa);
-                    if (rp[x]) {
-                        u64 k = ri[x];
-                        s8[2 * k] = x; s8[2 * k + 1] = S8[x];
-                        if (x) { e8[2 * (k - 1)] = x - 1; e8[2 * (k - 1) + 1] = S8[x - 1]; }
-                    }
-                    if (x == n) { e8[2 * (r - 1)] = n; e8[2 * (r - 1) + 1] = S8[n]; }
-                }
-            });
-        }
-    }
-    tm.runs = timer.stop();
-    return PFB_OK;
-}
-
 }  // namespace pfb
+
+#include "build.cuh"

@@ -36,6 +36,9 @@ typedef int pfbStream_t;
 // -------------------------------------------------------------------- CUDA --
 #include <cuda_runtime.h>
 #include <cub/cub.cuh>
+#include <map>
+#include <mutex>
+#include <unordered_map>
 #define PFB_DEV __device__
 #define PFB_HD __host__ __device__
 #define PFB_LAMBDA [=] __device__
@@ -71,20 +74,120 @@ inline LaunchStats &launch_stats() {
 }
 
 // ------------------------------------------------------------------ DevBuf --
+// Device memory is carved out of a few large slabs (cudaMalloc'ed on demand, kept until the
+// last context goes away) by a best-fit free list with coalescing, so the many short-lived
+// work arrays of a run cost no driver call and no device synchronisation.  Re-use of a
+// freed range is ordered by the stream: all work of a context runs on one stream, and a
+// call coming from a different stream first synchronises the device (merge_pfp, rare).
 size_t &dev_bytes_live();
 size_t &dev_bytes_peak();
+inline pfbStream_t &alloc_stream() {
+    static thread_local pfbStream_t s = 0;
+    return s;
+}
+#ifndef PFB_EMU
+struct SlabPool {
+    struct Slab { char *base; size_t size; };
+    std::mutex mu;
+    std::vector<Slab> slabs;
+    std::map<char *, size_t> free_;               // start -> bytes, coalesced, never spans slabs
+    std::unordered_map<void *, size_t> live;      // ptr -> bytes
+    pfbStream_t last_stream = 0;
+    bool have_stream = false;
+    static size_t round_up(size_t b) { return (b + 511) & ~(size_t)511; }
+
+    void order(pfbStream_t st) {
+        if (have_stream && st != last_stream) cudaDeviceSynchronize();
+        last_stream = st; have_stream = true;
+    }
+    void *take(size_t bytes) {   // best fit
+        auto best = free_.end();
+        for (auto it = free_.begin(); it != free_.end(); ++it)
+            if (it->second >= bytes && (best == free_.end() || it->second < best->second)) best = it;
+        if (best == free_.end()) return nullptr;
+        char *p = best->first;
+        size_t sz = best->second;
+        free_.erase(best);
+        if (sz > bytes) free_[p + bytes] = sz - bytes;
+        live[p] = bytes;
+        return p;
+    }
+    bool grow(size_t bytes) {
+        size_t fr = 0, tot = 0;
+        cudaMemGetInfo(&fr, &tot);
+        size_t want = (size_t)8 << 30;
+        if (want > fr / 2) want = fr / 2;
+        if (want < bytes) want = bytes;
+        want = (want + ((size_t)2 << 20) - 1) & ~(((size_t)2 << 20) - 1);
+        char *base = nullptr;
+        if (cudaMalloc((void **)&base, want) != cudaSuccess) {
+            cudaGetLastError();
+            want = (bytes + ((size_t)2 << 20) - 1) & ~(((size_t)2 << 20) - 1);
+            if (cudaMalloc((void **)&base, want) != cudaSuccess) { cudaGetLastError(); return false; }
+        }
+        slabs.push_back({base, want});
+        free_[base] = want;
+        return true;
+    }
+    void *alloc(size_t bytes, pfbStream_t st) {
+        std::lock_guard<std::mutex> lk(mu);
+        order(st);
+        bytes = round_up(bytes);
+        void *p = take(bytes);
+        if (p) return p;
+        if (!grow(bytes)) {
+            cudaDeviceSynchronize();
+            trim_locked();            // give empty slabs back and try once more
+            if (!grow(bytes)) return nullptr;
+        }
+        return take(bytes);
+    }
+    void release(void *p, pfbStream_t st) {
+        std::lock_guard<std::mutex> lk(mu);
+        order(st);
+        auto it = live.find(p);
+        if (it == live.end()) return;
+        char *b = (char *)p;
+        size_t sz = it->second;
+        live.erase(it);
+        const Slab *sl = nullptr;
+        for (auto &s : slabs) if (b >= s.base && b < s.base + s.size) sl = &s;
+        auto nx = free_.lower_bound(b);
+        if (nx != free_.end() && b + sz == nx->first && sl && nx->first < sl->base + sl->size) { sz += nx->second; nx = free_.erase(nx); }
+        if (nx != free_.begin()) {
+            auto pv = std::prev(nx);
+            if (pv->first + pv->second == b && sl && pv->first >= sl->base) { pv->second += sz; return; }
+        }
+        free_[b] = sz;
+    }
+    void trim_locked() {   // cudaFree every slab that is entirely free
+        for (size_t i = 0; i < slabs.size();) {
+            auto it = free_.find(slabs[i].base);
+            if (it != free_.end() && it->second == slabs[i].size) {
+                free_.erase(it);
+                cudaFree(slabs[i].base);
+                slabs.erase(slabs.begin() + (long)i);
+            } else ++i;
+        }
+    }
+    void trim() { std::lock_guard<std::mutex> lk(mu); cudaDeviceSynchronize(); trim_locked(); }
+    size_t reserved() { std::lock_guard<std::mutex> lk(mu); size_t t = 0; for (auto &s : slabs) t += s.size; return t; }
+};
+SlabPool &slab_pool();   // one per process (one device per process: one rank per GPU)
+#endif
 
 template <class T>
 struct DevBuf {
     T *p = nullptr;
     size_t n = 0;
+    pfbStream_t st_ = 0;
     DevBuf() {}
     explicit DevBuf(size_t count) { alloc(count); }
     DevBuf(const DevBuf &) = delete;
     DevBuf &operator=(const DevBuf &) = delete;
-    DevBuf(DevBuf &&o) noexcept : p(o.p), n(o.n) { o.p = nullptr; o.n = 0; }
+    DevBuf(DevBuf &&o) noexcept : p(o.p), n(o.n), st_(o.st_) { o.p = nullptr; o.n = 0; }
     DevBuf &operator=(DevBuf &&o) noexcept {
-        if (this != &o) { release(); p = o.p; n = o.n; o.p = nullptr; o.n = 0; }
+        if (this != &o) { release(); p = o.p; n = o.n; st_ = o.st_; o.p = nullptr; o.n = 0; }
         return *this;
     }
     ~DevBuf() { release(); }
@@ -96,11 +199,11 @@ struct DevBuf {
         p = (T *)malloc(bytes);
         if (!p) throw Error(-4, "emu: out of memory");
 #else
-        cudaError_t e = cudaMalloc((void **)&p, bytes);
-        if (e != cudaSuccess) {
-            p = nullptr; n = 0;
-            throw Error(-4, std::string("device out of memory allocating ") + std::to_string(bytes) + " bytes (" +
-                                cudaGetErrorString(e) + ")");
+        st_ = alloc_stream();
+        p = (T *)slab_pool().alloc(bytes, st_);
+        if (!p) {
+            n = 0;
+            throw Error(-4, std::string("device out of memory allocating ") + std::to_string(bytes) + " bytes");
         }
 #endif
         dev_bytes_live() += bytes;
@@ -112,14 +215,14 @@ struct DevBuf {
 #ifdef PFB_EMU
             free(p);
 #else
-            cudaFree(p);
+            slab_pool().release(p, st_);
 #endif
         }
         p = nullptr; n = 0;
     }
     T *get() const { return p; }
     size_t size() const { return n; }
-    void swap(DevBuf &o) { std::swap(p, o.p); std::swap(n, o.n); }
+    void swap(DevBuf &o) { std::swap(p, o.p); std::swap(n, o.n); std::swap(st_, o.st_); }
 };
 
 // ----------------------------------------------------------------- memory ops
@@ -175,6 +278,7 @@ template <class T> inline T atomic_or(T *a, T v) { T o = *a; *a = o | v; return 
 template <class T> inline T atomic_cas(T *a, T cmp, T v) { T o = *a; if (o == cmp) *a = v; return o; }
 inline int popc32(uint32_t x) { return __builtin_popcount(x); }
 inline int ffs32(uint32_t x) { return __builtin_ffs((int)x); }
+inline int clz64(uint64_t x) { return x ? __builtin_clzll(x) : 64; }
 #else
 __device__ __forceinline__ uint32_t atomic_add(uint32_t *a, uint32_t v) { return atomicAdd(a, v); }
 __device__ __forceinline__ uint64_t atomic_add(uint64_t *a, uint64_t v) {
@@ -191,6 +295,13 @@ __device__ __forceinline__ uint64_t atomic_cas(uint64_t *a, uint64_t cmp, uint64
 }
 __device__ __forceinline__ int popc32(uint32_t x) { return __popc(x); }
 __device__ __forceinline__ int ffs32(uint32_t x) { return __ffs((int)x); }
+__host__ __device__ __forceinline__ int clz64(uint64_t x) {
+#ifdef __CUDA_ARCH__
+    return __clzll((long long)x);
+#else
+    return x ? __builtin_clzll(x) : 64;
+#endif
+}
 #endif
 
 // -------------------------------------------------------------- launch_for --

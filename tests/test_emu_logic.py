@@ -23,6 +23,12 @@ CASES = [
     ("e_nrun", lambda: nrun_records(2, 50_000, 38), 64, ["-s", "--non-acgt-to-a"]),
     ("e_w3p5", lambda: [("a", random_bases(20_000, 3)), ("b", random_bases(0, 4)), ("c", random_bases(7, 5))], 32,
      ["-s", "-r", "-w", "3", "-p", "5"]),
+    # S[0..e1] is also a whole phrase elsewhere: the reference emits EndOfWord (0x01) bytes into the BWT
+    # for the full word grouped behind the first word's suffix (include/pfbwt.hpp:136-141)
+    ("e_w4p7", lambda: [("a", random_bases(50_000, 3)), ("b", random_bases(1, 4)), ("c", random_bases(30_000, 5))], 32,
+     ["-s", "-r", "-w", "4", "-p", "7"]),
+    ("e_w4p7_nosa", lambda: [("a", random_bases(50_000, 3)), ("b", random_bases(1, 4)), ("c", random_bases(30_000, 5))], 32,
+     ["-w", "4", "-p", "7"]),
 ]
 
 
@@ -51,3 +57,18 @@ def test_emu_merge(emu, ref_bins, datadir):
     merged = os.path.join(datadir, "emerged")
     run([emu, "--merge", "--bits", "64", "-s", "-o", merged] + parts)
     assert_same_files(mono, merged, ["dict", "occ", "parse", "n", "bwlast", "ilist", "bwsai"])
+
+
+@pytest.mark.parametrize("ext_rounds", ["0", "1", "100"])
+def test_emu_tie_refinement_paths(ext_rounds, emu, ref_bins, datadir):
+    """the dictionary suffix sort refines ties by symbol-extension rounds and/or prefix doubling;
+    the PFB_EXT_ROUNDS test knob forces doubling only (0), mixed (1) and extension only (100)."""
+    fa = os.path.join(datadir, "e_paths.fa")
+    recs = pangenome_records(40_000, 5, 40, 9) + nrun_records(1, 20_000, 11)
+    write_fasta(fa, recs, line_width=70)
+    a, b = os.path.join(datadir, "e_paths.port"), os.path.join(datadir, "e_paths.emu" + ext_rounds)
+    flags = ["-s", "-r", "--non-acgt-to-a"]
+    run([ref_bins["pfp_oracle"], "--bits", "64"] + flags + ["-o", a, fa])
+    env = dict(os.environ, PFB_EXT_ROUNDS=ext_rounds)
+    subprocess.run([emu, "--bits", "64"] + flags + ["-o", b, fa], check=True, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    assert_same_files(a, b, exts_for(True, True))
