@@ -5,8 +5,8 @@
 // (src/pfbwt-f.cpp:298-328).
 //
 // Data layout in HBM (D = dict bytes, Dw = words, P = phrases, n = |S|):
-//   key[D]   u64  bits 4..63: first 20 symbols of the suffix as 3-bit codes (cut
-//                 after the word's EndOfWord), bits 0..2: code of the preceding byte
+//   key[D]   u64  enumerative code of the first L symbols of the suffix, symbols consumed,
+//                 closed flag, code of the preceding byte (layout: dictkeys.cuh)
 //   sa[D]    u32  dictionary position of the j-th smallest suffix
 //   fl[D]    u8   1 at the first member of every group of identical suffix strings
 //   wc[Dw+2] u64  (word start | ilist base << 32): one 16-byte read gives both ends
@@ -14,81 +14,9 @@
 //   cnt[D]   u32  occurrences emitted by the j-th suffix (0 when suffix length <= w)
 //   off[D]   u64  exclusive sum of cnt = position in the BWT
 #pragma once
+#include "dictkeys.cuh"
 
 namespace pfb {
-
-// 3-bit order-preserving code of a dictionary byte without a branch:
-// perfect hash ((c*7)>>3)&15 into a nibble table (same mapping as sym3()).
-PFB_HD inline u32 sym3_fast(u32 c) { return (u32)(0x0500047320060010ull >> (4 * (((c * 7u) >> 3) & 15u))) & 7u; }
-// code -> byte (code 0 -> 0x00: the byte "before" S[0], include/pfbwt.hpp:132,140)
-PFB_HD inline u8 sym3_byte(u32 code) { return (u8)(0x544E4743412D0200ull >> (8 * code)); }
-
-// W holds 20 symbols in bits [0,60), first symbol in the top field.  Everything
-// after the first zero symbol (EndOfWord / EndOfDict) is cleared, so equal keys
-// with a terminator inside mean identical suffix strings.
-PFB_HD inline u64 cut_after_terminator(u64 W) {
-    const u64 L = 0x0249249249249249ull;   // bit 0 of each of the 20 fields
-    u64 nz = (W | (W >> 1) | (W >> 2)) & L;
-    u64 z = ~nz & L;
-    if (z) { int hb = 63 - clz64(z); W &= ~((1ull << hb) - 1); }
-    return W;
-}
-
-PFB_HD inline u64 load8(const u8 *p, u64 o, u64 lim) {   // 8 bytes at o (o % 8 == 0), zero past lim
-    if (o + 8 <= lim) return *reinterpret_cast<const u64 *>(p + o);
-    u64 x = 0;
-    for (u64 j = 0; j < 8 && o + j < lim; ++j) x |= (u64)p[o + j] << (8 * j);
-    return x;
-}
-
-// K6a: keys of 8 consecutive dictionary positions per logical thread (27 symbols loaded once)
-inline void k_suffix_keys(const u8 *dict, u64 D, u64 *key, u32 *sa, pfbStream_t st) {
-    launch_for((D + 7) / 8, st, PFB_LAMBDA(u64 t) {
-        const u64 i0 = t * 8;
-        u64 wd[4];
-        for (int q = 0; q < 4; ++q) wd[q] = load8(dict, i0 + 8 * (u64)q, D);
-        u32 prev = i0 ? (u32)dict[i0 - 1] : 0u;
-        u64 A = 0, B = 0;
-        for (int k = 0; k < 21; ++k) A = (A << 3) | sym3_fast((u32)(wd[k >> 3] >> (8 * (k & 7))) & 0xff);
-        for (int k = 21; k < 27; ++k) B = (B << 3) | sym3_fast((u32)(wd[k >> 3] >> (8 * (k & 7))) & 0xff);
-        B <<= 45;
-        const u64 M63 = 0x7FFFFFFFFFFFFFFFull;
-        for (int p = 0; p < 8; ++p) {
-            u64 i = i0 + (u64)p;
-            if (i >= D) break;
-            u64 W63 = p ? (((A << (3 * p)) & M63) | (B >> (63 - 3 * p))) : A;
-            u64 W = cut_after_terminator(W63 >> 3);
-            u32 pc = p ? (u32)(A >> (60 - 3 * (p - 1))) & 7u : sym3_fast(prev);
-            pc = i <= 1 ? 0u : (pc ? pc : 8u);   // include/pfbwt.hpp:132,140; 8 = EndOfWord precedes (word start)
-            key[i] = (W << 4) | pc;
-            sa[i] = (u32)i;
-        }
-    });
-}
-
-// symbols [depth, depth+nsym) of the suffix at idx (known to have no terminator
-// before depth), packed like the primary key
-PFB_HD inline u64 ext_syms(const u8 *dict, u64 D, u64 idx, u64 depth, int nsym) {
-    u64 key = 0;
-    int j = 0;
-    for (; j < nsym; ++j) {
-        u64 o = idx + depth + (u64)j;
-        u32 c = o < D ? sym3_fast(dict[o]) : 0u;
-        key = (key << 3) | c;
-        if (c == 0) { ++j; break; }
-    }
-    return key << (3 * (nsym - j));
-}
-
-// code of the byte preceding dictionary position idx (0 for idx <= 1, include/pfbwt.hpp:132,140)
-PFB_HD inline u64 prev_code(const u8 *dict, u32 idx) {
-    if (idx <= 1) return 0;
-    u64 c = sym3_fast(dict[idx - 1]);
-    return c ? c : 8;
-}
-// the byte a 4-bit preceding-byte code stands for.  A word start inside a group of equal suffixes
-// is emitted as EndOfWord (0x01), exactly like dict[gsa[j]-1] in include/pfbwt.hpp:140
-PFB_HD inline u8 prev_byte(u64 key) { return (key & 8) ? ENDOFWORD : sym3_byte((u32)key & 7); }
 
 // position -> (word, suffix length) through the sample table
 struct WordLookup {
@@ -119,12 +47,14 @@ inline u64 compact_indices(const u8 *flags, u64 n, DevBuf<u32> &scratch_idx, Dev
 }
 
 // ---------------------------------------------------------------------------
-// K6  dictionary suffix sort.  One radix sort on the 60-bit packed prefix, then
-//     only the tie groups that are still open (no terminator inside the compared
-//     prefix) are refined: a few rounds that append further symbols read from the
-//     dictionary, and - for long repeats - prefix doubling over rank[] (Larsson-
-//     Sadakane).  Replaces gsacak + the LCP array (include/pfbwt.hpp:206-223): a
-//     group of equal strings is exactly a run with glcp >= suff_len (:136-145).
+// K6  dictionary suffix sort.  One radix sort on the enumerative code of the first
+//     L symbols (dictkeys.cuh), then only the tie groups that are still open are
+//     refined: rounds that append the code of further symbols read from the
+//     dictionary (each open group continues at its own depth, because a stopper
+//     symbol ends a window early), and - for long repeats - prefix doubling over
+//     rank[] (Larsson-Sadakane) from the smallest depth still open.  Replaces
+//     gsacak + the LCP array (include/pfbwt.hpp:206-223): a group of equal strings
+//     is exactly a run with glcp >= suff_len (:136-145).
 // ---------------------------------------------------------------------------
 inline int sort_dict_suffixes(const DeviceParse &pp, DevBuf<u64> &key, DevBuf<u32> &sa, DevBuf<u8> &fl, const WordLookup &wl,
                               Workspace &ws, StageTimes &tm, Timer &timer, std::string &err) {
@@ -132,38 +62,50 @@ inline int sort_dict_suffixes(const DeviceParse &pp, DevBuf<u64> &key, DevBuf<u3
     const u64 D = pp.dsize;
     const u8 *dict = pp.dict.get();
     key.alloc(D); sa.alloc(D); fl.alloc(D);
+    int L = 1;
+    while (L < KEY_MAX_SYMS && (1ull << (2 * L)) < 128ull * D) ++L;     // ties become rare once 4^L >> D
+    if (const char *e = getenv("PFB_KEY_SYMS")) { L = atoi(e); if (L < 1) L = 1; if (L > KEY_MAX_SYMS) L = KEY_MAX_SYMS; }   // test knob
     {
         DevBuf<u64> key_b(D);
         DevBuf<u32> val_b(D);
-        k_suffix_keys(dict, D, key.get(), sa.get(), st);
+        k_suffix_keys(dict, D, L, key.get(), sa.get(), st);
         timer.lap("K6 keys");
-        sort_pairs(key, key_b, sa, val_b, D, 4, 64, ws.sc, st);
-        timer.lap("K6 radix sort 60 bits");
+        sort_pairs(key, key_b, sa, val_b, D, KEY_CODE_SHIFT, KEY_CODE_SHIFT + enum_bits(L), ws.sc, st);
+        timer.lap("K6 radix sort");
     }
     DevBuf<u8> act(D);
     {
         const u64 *ks = key.get(); u8 *f = fl.get(); u8 *ac = act.get();
         launch_for(D, st, PFB_LAMBDA(u64 j) {
-            u64 k = ks[j] >> 4;
-            bool head = j == 0 || k != (ks[j - 1] >> 4);
-            bool last = j + 1 == D || k != (ks[j + 1] >> 4);
+            u64 k = ks[j] >> KEY_CODE_SHIFT;
+            bool head = j == 0 || k != (ks[j - 1] >> KEY_CODE_SHIFT);
+            bool last = j + 1 == D || k != (ks[j + 1] >> KEY_CODE_SHIFT);
             f[j] = head ? 1 : 0;
-            ac[j] = (!(head && last) && (k & 7)) ? 1 : 0;     // tied and still open
+            ac[j] = (!(head && last) && !key_closed(ks[j])) ? 1 : 0;     // tied and still open
         });
     }
-    DevBuf<u32> apos;
+    DevBuf<u32> apos, adep;
     u64 m;
     {
         DevBuf<u32> scratch;
         m = compact_indices(act.get(), D, scratch, apos, ws);
     }
     act.release();
+    if (m) {
+        adep.alloc(m);
+        const u32 *ap = apos.get(); const u64 *ks = key.get(); u32 *dp = adep.get();
+        launch_for(m, st, PFB_LAMBDA(u64 a) { dp[a] = key_consumed(ks[ap[a]]); });
+    }
     timer.lap("K6 flags+open ties");
-    u64 depth = 20;
     u32 rounds = 0;
-    u32 max_ext_rounds = 3;
-    if (const char *e = getenv("PFB_EXT_ROUNDS")) max_ext_rounds = (u32)atoi(e);   // test knob: 0 = doubling only
-    while (m && rounds < max_ext_rounds) {
+    // Extension rounds go on while they make progress: a big open set after a few rounds means long
+    // repeats (prefix doubling, O(log) rounds); a handful of stragglers (e.g. the Dollar^w tail, one
+    // stopper per round) is cheaper to finish here than to hand all D suffixes to doubling.
+    u32 max_ext_rounds = 4, max_small_rounds = 256;
+    bool knob = false;
+    if (const char *e = getenv("PFB_EXT_ROUNDS")) { max_ext_rounds = (u32)atoi(e); knob = true; }   // test knob: 0 = doubling only
+    const u64 small_set = D / 2048 > 4096 ? D / 2048 : 4096;
+    while (m && (rounds < max_ext_rounds || (!knob && m <= small_set && rounds < max_small_rounds))) {
         // dense group ids inside the active list (whole groups are active, so the
         // first listed member of a group is its head)
         DevBuf<u8> ah(m);
@@ -174,59 +116,71 @@ inline int sort_dict_suffixes(const DeviceParse &pp, DevBuf<u64> &key, DevBuf<u3
         }
         u64 G = scan_flags(ah.get(), gidx.get(), m, ws);
         int gbits = bits_for(G ? G - 1 : 0);
-        int nsym = (64 - gbits) / 3;
-        if (nsym > 20) nsym = 20;
-        if (nsym < 1) break;   // cannot happen with D < 2^32; doubling below takes over
+        int L2 = KEY_MAX_SYMS;
+        while (L2 > 0 && 6 + enum_bits(L2) + gbits > 64) --L2;
+        if (L2 < 1) break;   // cannot happen with D < 2^32; doubling below takes over
+        const int ebits = enum_bits(L2);
         DevBuf<u64> k2(m), k2b(m);
         DevBuf<u32> v(m), vb(m);
         {
             const u32 *ap = apos.get(); const u8 *a_ = ah.get(); const u32 *gi = gidx.get(); const u32 *sp = sa.get();
+            const u32 *dp = adep.get();
             u64 *kp = k2.get(); u32 *vp = v.get();
             launch_for(m, st, PFB_LAMBDA(u64 a) {
                 u64 gid = (u64)gi[a] + a_[a] - 1;
                 u32 idx = sp[ap[a]];
                 vp[a] = idx;
-                kp[a] = (gid << (3 * nsym)) | ext_syms(dict, D, idx, depth, nsym);
+                EnumKey e = enum_scan(dict, D, (u64)idx + dp[a], L2);
+                kp[a] = (gid << (6 + ebits)) | (e.code << 6) | ((u64)e.consumed << 1) | (e.closed ? 1ull : 0ull);
             });
         }
-        sort_pairs(k2, k2b, v, vb, m, 0, gbits + 3 * nsym, ws.sc, st);
+        sort_pairs(k2, k2b, v, vb, m, 6, 6 + ebits + gbits, ws.sc, st);
         DevBuf<u8> act2(m);
         {
             const u32 *ap = apos.get(); const u64 *kp = k2.get(); const u32 *vp = v.get();
-            u32 *sp = sa.get(); u8 *f = fl.get(); u8 *ac = act2.get(); u64 *ks = key.get();
+            u32 *sp = sa.get(); u8 *f = fl.get(); u8 *ac = act2.get(); u64 *ks = key.get(); u32 *dp = adep.get();
             launch_for(m, st, PFB_LAMBDA(u64 a) {
-                u64 k = kp[a];
-                bool head = a == 0 || k != kp[a - 1];
-                bool last = a + 1 == m || k != kp[a + 1];
+                u64 k = kp[a] >> 6;
+                bool head = a == 0 || k != (kp[a - 1] >> 6);
+                bool last = a + 1 == m || k != (kp[a + 1] >> 6);
                 u32 j = ap[a];
                 sp[j] = vp[a];
                 ks[j] = (ks[j] & ~15ull) | prev_code(dict, vp[a]);   // the preceding-byte code travels with the suffix
                 f[j] = head ? 1 : 0;
-                ac[a] = (!(head && last) && (k & 7)) ? 1 : 0;
+                dp[a] += (u32)(kp[a] >> 1) & 31u;                      // slot a stays inside its old group: same depth so far
+                ac[a] = (!(head && last) && !(kp[a] & 1)) ? 1 : 0;
             });
         }
-        DevBuf<u32> scratch, sel, apos2;
+        DevBuf<u32> scratch, sel, apos2, adep2;
         u64 m2 = compact_indices(act2.get(), m, scratch, sel, ws);
-        apos2.alloc(m2);
+        apos2.alloc(m2); adep2.alloc(m2);
         if (m2) {
-            const u32 *sl = sel.get(); const u32 *ap = apos.get(); u32 *a2 = apos2.get();
-            launch_for(m2, st, PFB_LAMBDA(u64 a) { a2[a] = ap[sl[a]]; });
+            const u32 *sl = sel.get(); const u32 *ap = apos.get(); const u32 *dp = adep.get(); u32 *a2 = apos2.get(); u32 *d2 = adep2.get();
+            launch_for(m2, st, PFB_LAMBDA(u64 a) { a2[a] = ap[sl[a]]; d2[a] = dp[sl[a]]; });
         }
         apos = std::move(apos2);
+        adep = std::move(adep2);
         m = m2;
-        depth += (u64)nsym;
         ++rounds;
         timer.lap("K6 extension round");
     }
     if (m) {
-        // long repeats: hand the partially sorted array to prefix doubling
-        apos.release();
+        // long repeats: hand the partially sorted array to prefix doubling.  Every open group is
+        // sorted on at least h = min depth symbols, which is all the doubling step needs.
+        DevBuf<u32> hmin(1);
+        dev_memset(hmin.get(), 0xff, 4, st);
+        {
+            const u32 *dp = adep.get(); u32 *hm = hmin.get();
+            launch_for(m, st, PFB_LAMBDA(u64 a) { atomic_min(hm, dp[a]); });
+        }
+        u64 h = read_scalar(hmin.get(), st);
+        apos.release(); adep.release();
         DevBuf<u32> rank(D);
         ranks_from_flags(sa, fl, rank, D, ws);
         const WordLookup w2 = wl;
         u32 dr = 0;
-        int rc = prefix_doubling(sa, rank, fl, D, depth, PFB_LAMBDA(u32 idx, u64 h) {
-            return w2.suflen(w2.word(idx), idx) < h;   // EndOfWord already inside the compared prefix
+        int rc = prefix_doubling(sa, rank, fl, D, h, PFB_LAMBDA(u32 idx, u64 hh) {
+            return w2.suflen(w2.word(idx), idx) < hh;   // EndOfWord already inside the compared prefix
         }, ws, &dr, err);
         if (rc) return rc;
         rounds += dr;

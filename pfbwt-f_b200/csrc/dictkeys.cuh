@@ -1,0 +1,172 @@
+// dictkeys.cuh -- sort keys of the dictionary suffixes.
+//
+// A key holds an ORDER-PRESERVING ENUMERATIVE CODE of the first L symbols of a suffix.
+// The dictionary alphabet has 8 byte values (0x01<0x02<'-'<'A'<'C'<'G'<'N'<'T') but almost
+// every symbol is one of A,C,G,T, so instead of 3 bits per symbol the window is numbered
+// among the strings that can actually be told apart by one key:
+//   * EndOfWord / EndOfDict ends the string                      (closed: nothing follows)
+//   * 0x02, '-' and 'N' are "stoppers": the key stops after them (open: more symbols follow)
+//   * A,C,G,T continue
+// With N_0 = 1, N_L = 4 + 4 N_{L-1} = (7*4^L - 4)/3 such windows of length L, the code is
+//   V_L(x) = 0 | 1 | 2                       x0 = EndOfWord | 0x02 | '-'
+//          = 3 + a*N_{L-1} + [a==3] + V_{L-1}(x1..)   x0 = "ACGT"[a]
+//          = 3 + 3 N_{L-1}                   x0 = 'N'
+// which for a window of j leading ACGT symbols (2-bit digits a_i, B = sum a_i 4^(L-1-i),
+// S = sum a_i, nT = #{a_i == 3}) followed by a stopper has the closed form
+//   V = 3j + nT + (7B - 4S)/3 + stop,   stop = 0,1,2 or 7*4^(L-1-j) - 1 for 'N'.
+// 2.06 bits per symbol instead of 3: 19 symbols fit 40 bits (5 radix passes instead of 8), and
+// a 54-bit field holds 26 symbols.  Equal codes = identical windows (same stopper, same
+// position); two suffixes tied on a closed window are identical strings (a group of
+// include/pfbwt.hpp:136-145), tied on an open window they are refined further.
+//
+// key layout (u64):  [0,4) code of the preceding byte   [4] closed   [5,10) symbols consumed
+//                    [10, 10+bits) enumerative code
+#pragma once
+
+namespace pfb {
+
+// 3-bit order-preserving code of a dictionary byte without a branch:
+// perfect hash ((c*7)>>3)&15 into a nibble table (same mapping as sym3()).
+PFB_HD inline u32 sym3_fast(u32 c) { return (u32)(0x0500047320060010ull >> (4 * (((c * 7u) >> 3) & 15u))) & 7u; }
+// code -> byte (code 0 -> 0x00: the byte "before" S[0], include/pfbwt.hpp:132,140)
+PFB_HD inline u8 sym3_byte(u32 code) { return (u8)(0x544E4743412D0200ull >> (8 * code)); }
+// sym3 code -> 2-bit field (ACGT digit, or stopper kind 0 EndOfWord, 1 0x02, 2 '-', 3 'N') and "is a stopper"
+PFB_HD inline u32 sym_field(u32 s) { return (0x33210210u >> (4 * s)) & 3u; }
+PFB_HD inline u32 sym_stops(u32 s) { return (0x47u >> s) & 1u; }
+
+static const int KEY_CODE_SHIFT = 10;
+static const int KEY_MAX_SYMS = 26;     // N_26 < 2^54
+
+PFB_HD inline u64 enum_count(int L) { return (7ull * (1ull << (2 * L)) - 4ull) / 3ull; }   // N_L
+inline int enum_bits(int L) { return bits_for(enum_count(L) - 1); }
+
+// B: the j leading ACGT digits left-aligned in a field of L digits (zero below); kind: stopper when j < L
+PFB_HD inline u64 enum_code(u64 B, int j, int L, u32 kind) {
+    const u64 lo = 0x5555555555555555ull;
+    u64 S = (u64)popc64(B & lo) + 2ull * (u64)popc64(B & (lo << 1));
+    u64 nT = (u64)popc64(B & (B >> 1) & lo);
+    u64 v = 3ull * (u64)j + nT + (7ull * B - 4ull * S) * 0xAAAAAAAAAAAAAAABull;   // exact division by 3
+    if (j < L) v += kind < 3 ? (u64)kind : (7ull << (2 * (L - 1 - j))) - 1ull;
+    return v;
+}
+
+PFB_HD inline u64 pack_key(u64 code, u32 consumed, bool closed, u32 pc) {
+    return (code << KEY_CODE_SHIFT) | ((u64)consumed << 5) | (closed ? 16ull : 0ull) | (u64)pc;
+}
+PFB_HD inline bool key_closed(u64 k) { return (k >> 4) & 1; }
+PFB_HD inline u32 key_consumed(u64 k) { return (u32)(k >> 5) & 31u; }
+
+// byte-by-byte form (refinement rounds, emulator): window of L symbols starting at dict[pos]
+struct EnumKey { u64 code; u32 consumed; bool closed; };
+PFB_HD inline EnumKey enum_scan(const u8 *dict, u64 D, u64 pos, int L) {
+    u64 B = 0;
+    int j = 0;
+    u32 kind = 0;
+    for (; j < L; ++j) {
+        u64 o = pos + (u64)j;
+        u32 s = o < D ? sym3_fast(dict[o]) : 0u;
+        if (sym_stops(s)) { kind = sym_field(s); break; }
+        B = (B << 2) | sym_field(s);
+    }
+    EnumKey r;
+    if (j < L) { B <<= 2 * (L - j); r.consumed = (u32)j + 1; r.closed = kind == 0; }
+    else { r.consumed = (u32)L; r.closed = false; }
+    r.code = enum_code(B, j, L, kind);
+    return r;
+}
+
+// code of the byte preceding dictionary position idx (0 for idx <= 1, include/pfbwt.hpp:132,140;
+// 8 = EndOfWord precedes, i.e. idx is a word start)
+PFB_HD inline u64 prev_code(const u8 *dict, u64 idx) {
+    if (idx <= 1) return 0;
+    u64 c = sym3_fast(dict[idx - 1]);
+    return c ? c : 8;
+}
+// the byte a 4-bit preceding-byte code stands for.  A word start inside a group of equal suffixes
+// is emitted as EndOfWord (0x01), exactly like dict[gsa[j]-1] in include/pfbwt.hpp:140
+PFB_HD inline u8 prev_byte(u64 key) { return (key & 8) ? ENDOFWORD : sym3_byte((u32)key & 7); }
+
+#ifndef PFB_EMU
+// K6a: one CTA = 2048 consecutive dictionary positions, 8 per thread.  The tile (+40 bytes of
+// look-ahead) is staged in shared memory with 16-byte loads; each thread packs its 40 symbols
+// once into 2-bit fields + a stopper mask and derives its 8 windows with shifts; keys leave
+// through shared memory so that global stores are unit-stride.
+static const int KEYS_TILE = 2048;
+__global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict__ dict, u64 D, int L, u64 *__restrict__ key,
+                                                            u32 *__restrict__ sa) {
+    __shared__ __align__(16) u8 sb[KEYS_TILE + 48];
+    __shared__ u64 sk[KEYS_TILE];
+    const u64 base = (u64)blockIdx.x * KEYS_TILE;
+    for (int o = threadIdx.x * 16; o < KEYS_TILE + 48; o += 256 * 16) {
+        u64 g = base + (u64)o;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (g + 16 <= D) v = *reinterpret_cast<const uint4 *>(dict + g);
+        else if (g < D) {
+            u32 t[4] = {0, 0, 0, 0};
+            for (int b = 0; b < 16 && g + b < D; ++b) t[b >> 2] |= (u32)dict[g + b] << (8 * (b & 3));
+            v = make_uint4(t[0], t[1], t[2], t[3]);
+        }
+        *reinterpret_cast<uint4 *>(sb + o) = v;
+    }
+    __shared__ u32 sprev;
+    if (threadIdx.x == 0) sprev = base ? (u32)dict[base - 1] : 0u;
+    __syncthreads();
+    const int i0 = threadIdx.x * 8;
+    u64 xh = 0, xl = 0, rm = 0;
+    u32 pcs[8];
+    pcs[0] = sym3_fast(i0 ? (u32)sb[i0 - 1] : sprev);
+#pragma unroll
+    for (int q = 0; q < 5; ++q) {
+        u64 wd = *reinterpret_cast<const u64 *>(sb + i0 + 8 * q);
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+            const int k = 8 * q + b;
+            u32 s = sym3_fast((u32)(wd >> (8 * b)) & 0xffu);
+            u64 f = sym_field(s);
+            if (k < 32) xh |= f << (62 - 2 * k); else xl |= f << (62 - 2 * (k - 32));
+            rm |= (u64)sym_stops(s) << (63 - k);
+            if (k < 7) pcs[k + 1] = s;
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+        u64 W = p ? ((xh << (2 * p)) | (xl >> (64 - 2 * p))) : xh;
+        u64 Xw = W >> (64 - 2 * L);
+        u64 Rw = (rm << p) >> (64 - L);
+        int j = Rw ? L - 1 - (63 - __clzll((long long)Rw)) : L;
+        u32 kind = 0;
+        u64 B = Xw;
+        if (j < L) { kind = (u32)(Xw >> (2 * (L - 1 - j))) & 3u; B = (Xw >> (2 * (L - j))) << (2 * (L - j)); }
+        u64 code = enum_code(B, j, L, kind);
+        u64 i = base + (u64)(i0 + p);
+        u32 pc = i <= 1 ? 0u : (pcs[p] ? pcs[p] : 8u);
+        sk[i0 + p] = pack_key(code, j < L ? (u32)j + 1 : (u32)L, j < L && kind == 0, pc);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        int o = k * 256 + threadIdx.x;
+        u64 g = base + (u64)o;
+        if (g < D) { key[g] = sk[o]; sa[g] = (u32)g; }
+    }
+}
+#endif
+
+// keys + identity permutation for all D dictionary positions, L <= KEY_MAX_SYMS symbols per key
+inline void k_suffix_keys(const u8 *dict, u64 D, int L, u64 *key, u32 *sa, pfbStream_t st) {
+#ifdef PFB_EMU
+    (void)st;
+    for (u64 i = 0; i < D; ++i) {
+        EnumKey e = enum_scan(dict, D, i, L);
+        key[i] = pack_key(e.code, e.consumed, e.closed, (u32)prev_code(dict, i));
+        sa[i] = (u32)i;
+    }
+#else
+    if (D == 0) return;
+    k_suffix_keys_kernel<<<(unsigned)((D + KEYS_TILE - 1) / KEYS_TILE), 256, 0, st>>>(dict, D, L, key, sa);
+    PFB_CUDA_CHECK(cudaGetLastError());
+    launch_stats().own++;
+#endif
+}
+
+}  // namespace pfb

@@ -279,6 +279,7 @@ template <class T> inline T atomic_cas(T *a, T cmp, T v) { T o = *a; if (o == cm
 inline int popc32(uint32_t x) { return __builtin_popcount(x); }
 inline int ffs32(uint32_t x) { return __builtin_ffs((int)x); }
 inline int clz64(uint64_t x) { return x ? __builtin_clzll(x) : 64; }
+inline int popc64(uint64_t x) { return __builtin_popcountll(x); }
 #else
 __device__ __forceinline__ uint32_t atomic_add(uint32_t *a, uint32_t v) { return atomicAdd(a, v); }
 __device__ __forceinline__ uint64_t atomic_add(uint64_t *a, uint64_t v) {
@@ -295,6 +296,13 @@ __device__ __forceinline__ uint64_t atomic_cas(uint64_t *a, uint64_t cmp, uint64
 }
 __device__ __forceinline__ int popc32(uint32_t x) { return __popc(x); }
 __device__ __forceinline__ int ffs32(uint32_t x) { return __ffs((int)x); }
+__host__ __device__ __forceinline__ int popc64(uint64_t x) {
+#ifdef __CUDA_ARCH__
+    return __popcll((unsigned long long)x);
+#else
+    return __builtin_popcountll(x);
+#endif
+}
 __host__ __device__ __forceinline__ int clz64(uint64_t x) {
 #ifdef __CUDA_ARCH__
     return __clzll((long long)x);
