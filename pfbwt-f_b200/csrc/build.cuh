@@ -4,15 +4,18 @@
 // (include/pfbwt.hpp:96-223) and the writer lambda of run_pfbwt
 // (src/pfbwt-f.cpp:298-328).
 //
-// Data layout in HBM (D = dict bytes, Dw = words, P = phrases, n = |S|):
+// Data layout in HBM (D = dict bytes, Dw = words, P = phrases, n = |S|; per-suffix arrays are
+// padded to a multiple of the 2048-element tile):
 //   key[D]   u64  enumerative code of the first L symbols of the suffix, symbols consumed,
-//                 closed flag, code of the preceding byte (layout: dictkeys.cuh)
+//                 closed flag, code of the preceding byte (dictkeys.cuh); dropped after the sort
 //   sa[D]    u32  dictionary position of the j-th smallest suffix
-//   fl[D]    u8   1 at the first member of every group of identical suffix strings
+//   meta[D]  u8   preceding-byte code | head | full | valid | hard (emit.cuh)
 //   wc[Dw+2] u64  (word start | ilist base << 32): one 16-byte read gives both ends
 //   wsamp[D/128] u32  word id at every 128th dictionary byte (position -> word)
 //   cnt[D]   u32  occurrences emitted by the j-th suffix (0 when suffix length <= w)
-//   off[D]   u64  exclusive sum of cnt = position in the BWT
+//   tilebase[D/2048] u64  BWT position of the first output of a tile (offsets inside a tile are
+//                 recomputed by a block scan in the emission kernel)
+//   ibase[D], sl[D] u32  first ilist slot of the word / suffix length (only with SA output)
 #pragma once
 #include "dictkeys.cuh"
 
@@ -33,6 +36,12 @@ struct WordLookup {
     // length of the suffix starting at idx inside word d, EndOfWord excluded (0 for the EndOfDict slot)
     PFB_HD inline u64 suflen(u32 d, u32 idx) const { return d < Dw ? (u64)((u32)wc[d + 1] - 1 - idx) : 0; }
 };
+
+}  // namespace pfb
+
+#include "emit.cuh"
+
+namespace pfb {
 
 // ordered compaction of the indices j in [0,n) with flags[j] != 0
 inline u64 compact_indices(const u8 *flags, u64 n, DevBuf<u32> &scratch_idx, DevBuf<u32> &list, Workspace &ws) {
@@ -55,46 +64,33 @@ inline u64 compact_indices(const u8 *flags, u64 n, DevBuf<u32> &scratch_idx, Dev
 //     rank[] (Larsson-Sadakane) from the smallest depth still open.  Replaces
 //     gsacak + the LCP array (include/pfbwt.hpp:206-223): a group of equal strings
 //     is exactly a run with glcp >= suff_len (:136-145).
+//     Result: sa[] and meta[] (preceding-byte code + head bit), both padded(D) long.
 // ---------------------------------------------------------------------------
-inline int sort_dict_suffixes(const DeviceParse &pp, DevBuf<u64> &key, DevBuf<u32> &sa, DevBuf<u8> &fl, const WordLookup &wl,
+inline int sort_dict_suffixes(const DeviceParse &pp, DevBuf<u32> &sa, DevBuf<u8> &meta, const WordLookup &wl,
                               Workspace &ws, StageTimes &tm, Timer &timer, std::string &err) {
     pfbStream_t st = ws.st;
     const u64 D = pp.dsize;
     const u8 *dict = pp.dict.get();
-    key.alloc(D); sa.alloc(D); fl.alloc(D);
+    sa.alloc(padded(D)); meta.alloc(padded(D) + 64);
+    dev_memset(meta.get(), M_HEAD, padded(D) + 64, st);
     int L = 1;
     while (L < KEY_MAX_SYMS && (1ull << (2 * L)) < 128ull * D) ++L;     // ties become rare once 4^L >> D
     if (const char *e = getenv("PFB_KEY_SYMS")) { L = atoi(e); if (L < 1) L = 1; if (L > KEY_MAX_SYMS) L = KEY_MAX_SYMS; }   // test knob
+    DevBuf<u32> apos, adep;
+    u64 m;
     {
-        DevBuf<u64> key_b(D);
-        DevBuf<u32> val_b(D);
+        DevBuf<u64> key(D), key_b(D);
+        DevBuf<u32> val_b(padded(D));
         k_suffix_keys(dict, D, L, key.get(), sa.get(), st);
         timer.lap("K6 keys");
         sort_pairs(key, key_b, sa, val_b, D, KEY_CODE_SHIFT, KEY_CODE_SHIFT + enum_bits(L), ws.sc, st);
         timer.lap("K6 radix sort");
-    }
-    DevBuf<u8> act(D);
-    {
-        const u64 *ks = key.get(); u8 *f = fl.get(); u8 *ac = act.get();
-        launch_for(D, st, PFB_LAMBDA(u64 j) {
-            u64 k = ks[j] >> KEY_CODE_SHIFT;
-            bool head = j == 0 || k != (ks[j - 1] >> KEY_CODE_SHIFT);
-            bool last = j + 1 == D || k != (ks[j + 1] >> KEY_CODE_SHIFT);
-            f[j] = head ? 1 : 0;
-            ac[j] = (!(head && last) && !key_closed(ks[j])) ? 1 : 0;     // tied and still open
-        });
-    }
-    DevBuf<u32> apos, adep;
-    u64 m;
-    {
-        DevBuf<u32> scratch;
-        m = compact_indices(act.get(), D, scratch, apos, ws);
-    }
-    act.release();
-    if (m) {
-        adep.alloc(m);
-        const u32 *ap = apos.get(); const u64 *ks = key.get(); u32 *dp = adep.get();
-        launch_for(m, st, PFB_LAMBDA(u64 a) { dp[a] = key_consumed(ks[ap[a]]); });
+        m = sorted_flags_and_open_list(key.get(), D, meta.get(), apos, ws);
+        if (m) {
+            adep.alloc(m);
+            const u32 *ap = apos.get(); const u64 *ks = key.get(); u32 *dp = adep.get();
+            launch_for(m, st, PFB_LAMBDA(u64 a) { dp[a] = key_consumed(ks[ap[a]]); });
+        }
     }
     timer.lap("K6 flags+open ties");
     u32 rounds = 0;
@@ -105,14 +101,15 @@ inline int sort_dict_suffixes(const DeviceParse &pp, DevBuf<u64> &key, DevBuf<u3
     bool knob = false;
     if (const char *e = getenv("PFB_EXT_ROUNDS")) { max_ext_rounds = (u32)atoi(e); knob = true; }   // test knob: 0 = doubling only
     const u64 small_set = D / 2048 > 4096 ? D / 2048 : 4096;
+    u8 *mt = meta.get();
     while (m && (rounds < max_ext_rounds || (!knob && m <= small_set && rounds < max_small_rounds))) {
         // dense group ids inside the active list (whole groups are active, so the
         // first listed member of a group is its head)
         DevBuf<u8> ah(m);
         DevBuf<u32> gidx(m);
         {
-            const u32 *ap = apos.get(); const u8 *f = fl.get(); u8 *a_ = ah.get();
-            launch_for(m, st, PFB_LAMBDA(u64 a) { a_[a] = f[ap[a]]; });
+            const u32 *ap = apos.get(); u8 *a_ = ah.get();
+            launch_for(m, st, PFB_LAMBDA(u64 a) { a_[a] = (mt[ap[a]] & M_HEAD) ? 1 : 0; });
         }
         u64 G = scan_flags(ah.get(), gidx.get(), m, ws);
         int gbits = bits_for(G ? G - 1 : 0);
@@ -138,16 +135,15 @@ inline int sort_dict_suffixes(const DeviceParse &pp, DevBuf<u64> &key, DevBuf<u3
         DevBuf<u8> act2(m);
         {
             const u32 *ap = apos.get(); const u64 *kp = k2.get(); const u32 *vp = v.get();
-            u32 *sp = sa.get(); u8 *f = fl.get(); u8 *ac = act2.get(); u64 *ks = key.get(); u32 *dp = adep.get();
+            u32 *sp = sa.get(); u8 *ac = act2.get(); u32 *dp = adep.get();
             launch_for(m, st, PFB_LAMBDA(u64 a) {
                 u64 k = kp[a] >> 6;
                 bool head = a == 0 || k != (kp[a - 1] >> 6);
                 bool last = a + 1 == m || k != (kp[a + 1] >> 6);
                 u32 j = ap[a];
                 sp[j] = vp[a];
-                ks[j] = (ks[j] & ~15ull) | prev_code(dict, vp[a]);   // the preceding-byte code travels with the suffix
-                f[j] = head ? 1 : 0;
-                dp[a] += (u32)(kp[a] >> 1) & 31u;                      // slot a stays inside its old group: same depth so far
+                mt[j] = (u8)(prev_code(dict, vp[a]) | (head ? M_HEAD : 0));   // the preceding-byte code travels with the suffix
+                dp[a] += (u32)(kp[a] >> 1) & 31u;                             // slot a stays inside its old group: same depth so far
                 ac[a] = (!(head && last) && !(kp[a] & 1)) ? 1 : 0;
             });
         }
@@ -176,6 +172,11 @@ inline int sort_dict_suffixes(const DeviceParse &pp, DevBuf<u64> &key, DevBuf<u3
         u64 h = read_scalar(hmin.get(), st);
         apos.release(); adep.release();
         DevBuf<u32> rank(D);
+        DevBuf<u8> fl(D);
+        {
+            u8 *f = fl.get();
+            launch_for(D, st, PFB_LAMBDA(u64 j) { f[j] = (mt[j] & M_HEAD) ? 1 : 0; });
+        }
         ranks_from_flags(sa, fl, rank, D, ws);
         const WordLookup w2 = wl;
         u32 dr = 0;
@@ -184,8 +185,8 @@ inline int sort_dict_suffixes(const DeviceParse &pp, DevBuf<u64> &key, DevBuf<u3
         }, ws, &dr, err);
         if (rc) return rc;
         rounds += dr;
-        const u32 *sp = sa.get(); u64 *ks = key.get();
-        launch_for(D, st, PFB_LAMBDA(u64 j) { ks[j] = (ks[j] & ~15ull) | prev_code(dict, sp[j]); });
+        const u32 *sp = sa.get(); const u8 *f = fl.get();
+        launch_for(D, st, PFB_LAMBDA(u64 j) { mt[j] = (u8)(prev_code(dict, sp[j]) | (f[j] ? M_HEAD : 0)); });
         timer.lap("K6 prefix doubling");
     }
     tm.dict_sort_rounds = rounds;
@@ -212,7 +213,6 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
     if (any_sa && pp.bwsai.size() == 0) { err = "bwsai not available"; return PFB_ERR_ARG; }
     if (D > 0xFFFFFFF0ull) { err = "dictionary larger than 2^32 bytes is not supported yet"; return PFB_ERR_LIMIT; }
     Timer timer(st);
-    const u8 *dict = pp.dict.get();
 
     // word tables: wc[d] = (start, first ilist slot - 1), sample table for position -> word
     DevBuf<u64> wc(Dw + 2);
@@ -232,212 +232,98 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
     }
     WordLookup wl;
     wl.wc = wc.get(); wl.wsamp = wsamp.get(); wl.Dw = (u32)Dw;
+    timer.lap("K7 word tables");
 
     // K6 dictionary suffix sort -------------------------------------------------------
-    DevBuf<u64> key;
     DevBuf<u32> sa;
-    DevBuf<u8> fl;
-    timer.lap("K7 word tables");
-    int rc = sort_dict_suffixes(pp, key, sa, fl, wl, ws, tm, timer, err);
+    DevBuf<u8> meta;
+    int rc = sort_dict_suffixes(pp, sa, meta, wl, ws, tm, timer, err);
     if (rc) return rc;
     tm.dict_sort = timer.stop();
 
-    // K7 counts, offsets, groups ----------------------------------------------------
-    DevBuf<u32> wordv(D), cnt(D);
-    DevBuf<u64> off(D);
+    // K7 classify, tile offsets, hard groups ------------------------------------------------
+    const u64 nt = tiles_of(D);
+    DevBuf<u32> cnt(padded(D)), ibase, slen;
+    DevBuf<u64> tilesum(nt + 1), tilebase(nt + 1);
+    if (any_sa) { ibase.alloc(padded(D)); slen.alloc(padded(D)); }
     {
-        const u32 *sp = sa.get(); u32 *wv = wordv.get(); u32 *cp = cnt.get();
-        launch_for(D, st, PFB_LAMBDA(u64 t) {
-            u32 idx = sp[t];
-            u32 d = wl.word(idx);
-            bool valid = wl.suflen(d, idx) > w;                 // include/pfbwt.hpp:114
-            wv[t] = d;
-            cp[t] = valid ? wl.cum(d + 1) - wl.cum(d) : 0u;
-        });
+        ClassifyArgs ca;
+        ca.sa = sa.get(); ca.meta = meta.get(); ca.wl = wl; ca.D = D; ca.w = w;
+        ca.cnt = cnt.get(); ca.tilesum = tilesum.get(); ca.ibase = ibase.get(); ca.sl = slen.get();
+        k_classify(ca, any_sa, st);
     }
     timer.lap("K7 classify (word lookup)");
-    exclusive_sum<u32, u64>(cnt.get(), off.get(), D, ws.sc, st);
-    timer.lap("K7 offsets scan");
+    dev_memset(tilesum.get() + nt, 0, 8, st);
+    exclusive_sum<u64, u64>(tilesum.get(), tilebase.get(), nt + 1, ws.sc, st);
     {
-        u64 total = read_scalar(off.get() + (D - 1), st) + read_scalar(cnt.get() + (D - 1), st);
+        u64 total = read_scalar(tilebase.get() + nt, st);
         if (total != n + 1) { err = "internal: emitted positions " + std::to_string(total) + " != n+1 = " + std::to_string(n + 1); return PFB_ERR_INTERNAL; }
     }
-    // members of multi-word groups: head position, then "chars differ" per group (BWT-only mode)
-    // cls[t]: 0 nothing to emit, 1 easy (direct), 2 hard (merge by ilist position)
-    DevBuf<u8> cls(D);
-    DevBuf<u32> head(D);
+    k_group_classes(meta.get(), D, any_sa, ws);
+    timer.lap("K7 group classes");
+    // number of hard groups (sizes the work list of the emission kernel)
+    u64 nhg_cap;
     {
-        DevBuf<u32> hd(D);
-        const u8 *f = fl.get(); u32 *hp = hd.get();
-        launch_for(D, st, PFB_LAMBDA(u64 j) { hp[j] = f[j] ? (u32)j : 0; });
-        inclusive_max(hd.get(), head.get(), D, ws.sc, st);
+        DevBuf<u8> hh(D);
+        const u8 *mt = meta.get(); u8 *h = hh.get();
+        launch_for(D, st, PFB_LAMBDA(u64 t) { h[t] = (mt[t] & (M_HARD | M_HEAD)) == (M_HARD | M_HEAD) ? 1 : 0; });
+        nhg_cap = reduce_sum<u8, u64>(hh.get(), D, ws.sc, st);
     }
-    timer.lap("K7 group heads");
-    {
-        DevBuf<u8> gdiff;
-        if (!any_sa) {
-            gdiff.alloc(D);
-            dev_memset(gdiff.get(), 0, D, st);
-            const u8 *f = fl.get(); const u32 *hd = head.get(); const u64 *ks = key.get(); const u32 *cp = cnt.get(); u8 *gd = gdiff.get();
-            launch_for(D, st, PFB_LAMBDA(u64 t) {
-                if (f[t] || !cp[t]) return;
-                u32 h = hd[t];
-                if ((ks[t] & 15) != (ks[h] & 15)) gd[h] = 1;    // include/pfbwt.hpp:146
-            });
-        }
-        const u8 *f = fl.get(); const u32 *hd = head.get(); const u32 *cp = cnt.get(); const u8 *gd = gdiff.get(); u8 *cl = cls.get();
-        launch_for(D, st, PFB_LAMBDA(u64 t) {
-            u32 c = cp[t];
-            bool single = f[t] && (t + 1 == D || f[t + 1]);
-            bool hard = c && !single && (any_sa || gd[hd[t]]);
-            cl[t] = !c ? 0 : (hard ? 2 : 1);
-        });
-    }
-    timer.lap("K7 group class");
+    timer.lap("K7 hard count");
     tm.groups = timer.stop();
 
     // K8 emission ---------------------------------------------------------------------
     out.n = n;
-    out.bwt.alloc(n + 1);
-    if (any_sa) out.sa.alloc((n + 1) * (u64)U);
-    u8 *bwt = out.bwt.get();
-    u8 *sa_out = out.sa.get();
-    const u32 *ilist = pp.ilist.get(); const u8 *bwlast = pp.bwlast.get(); const u64 *bwsai = pp.bwsai.get();
-    const u32 SMALL = 8;
-    {   // easy members: their occurrences are already ordered by ilist position
-        const u64 bigcap = (n + 1) / (SMALL + 1) + 1 < D ? (n + 1) / (SMALL + 1) + 1 : D;
-        DevBuf<u32> biglist(bigcap), bigcount(1);
-        dev_memset(bigcount.get(), 0, 4, st);
-        const u32 *sp = sa.get(); const u32 *wv = wordv.get(); const u32 *cp = cnt.get(); const u8 *cl = cls.get();
-        const u64 *of = off.get(); const u64 *ks = key.get(); const u8 *f = fl.get();
-        u32 *bl = biglist.get(); u32 *bc = bigcount.get();
-        launch_for(D, st, PFB_LAMBDA(u64 t) {
-            if (cl[t] != 1) return;
-            u32 c = cp[t];
-            if (c > SMALL) { bl[atomic_add(bc, 1u)] = (u32)t; return; }
-            u32 idx = sp[t], d = wv[t];
-            bool full = idx == wl.start(d) && f[t] && (t + 1 == D || f[t + 1]);   // include/pfbwt.hpp:116 (EASY1 is never grouped)
-            u64 sl = wl.suflen(d, idx);
-            u8 pc = prev_byte(ks[t]);
-            u64 x = of[t];
-            u32 base = 1 + wl.cum(d);
-            for (u32 j = 0; j < c; ++j) {
-                if (full || any_sa) {
-                    u32 ii = ilist[base + j];
-                    bwt[x + j] = full ? bwlast[ii] : pc;          // include/pfbwt.hpp:119,151
-                    if (any_sa) store_sa<U>(sa_out, x + j, bwsai[ii] - sl);
-                } else bwt[x + j] = pc;
-            }
-        });
-        timer.lap("K8 easy small");
-        u64 nbig = read_scalar(bigcount.get(), st);
-        // frequent words: 32 logical lanes per member, unit-stride writes
-        launch_for(nbig * 32, st, PFB_LAMBDA(u64 i) {
-            u64 t = bl[i >> 5];
-            u32 lane = (u32)(i & 31);
-            u32 c = cp[t], idx = sp[t], d = wv[t];
-            bool full = idx == wl.start(d) && f[t] && (t + 1 == D || f[t + 1]);   // include/pfbwt.hpp:116 (EASY1 is never grouped)
-            u64 sl = wl.suflen(d, idx);
-            u8 pc = prev_byte(ks[t]);
-            u64 x = of[t];
-            u32 base = 1 + wl.cum(d);
-            for (u32 j = lane; j < c; j += 32) {
-                if (full || any_sa) {
-                    u32 ii = ilist[base + j];
-                    bwt[x + j] = full ? bwlast[ii] : pc;
-                    if (any_sa) store_sa<U>(sa_out, x + j, bwsai[ii] - sl);
-                } else bwt[x + j] = pc;
-            }
-        });
+    out.bwt.alloc(n + 1 + 16);
+    if (any_sa) out.sa.alloc((n + 1) * (u64)U + 16);
+    DevBuf<u32> hard_t(nhg_cap + 1), ctr32(2);
+    DevBuf<u64> hard_x(nhg_cap + 1), ctr64(1);
+    dev_memset(ctr32.get(), 0, 8, st);
+    dev_memset(ctr64.get(), 0, 8, st);
+    EmitArgs ea;
+    ea.meta = meta.get(); ea.cnt = cnt.get(); ea.sa = sa.get(); ea.ibase = ibase.get(); ea.sl = slen.get();
+    ea.wl = wl; ea.tilebase = tilebase.get(); ea.D = D;
+    ea.ilist = pp.ilist.get(); ea.bwlast = pp.bwlast.get(); ea.bwsai = pp.bwsai.get();
+    ea.bwt = out.bwt.get(); ea.sa_out = out.sa.get();
+    ea.hard_t = hard_t.get(); ea.hard_x = hard_x.get(); ea.n_hard_groups = ctr32.get(); ea.n_hard_occ = ctr64.get();
+#ifdef PFB_EMU
+    emu_emit<U>(ea, any_sa);
+#else
+    if (any_sa) k_emit_kernel<U, true><<<(unsigned)nt, 256, 0, st>>>(ea);
+    else k_emit_kernel<U, false><<<(unsigned)nt, 256, 0, st>>>(ea);
+    PFB_CUDA_CHECK(cudaGetLastError());
+    launch_stats().own++;
+#endif
+    timer.lap("K8 emit easy");
+    const u64 nhg = read_scalar(ctr32.get(), st);
+    const u64 nhard = read_scalar(ctr64.get(), st);
+    if (nhg != nhg_cap) { err = "internal: hard group count mismatch"; return PFB_ERR_INTERNAL; }
+    if (nhg) {
+        DevBuf<u32> biglist(nhg);
+        u32 *nbigp = ctr32.get() + 1;
+#ifdef PFB_EMU
+        emu_emit_hard<U>(ea, any_sa, (u32)nhg, biglist.get(), nbigp);
+#else
+        const unsigned blocks = (unsigned)((nhg + 31) / 32);
+        if (any_sa) k_emit_hard_kernel<U, true><<<blocks, 256, 0, st>>>(ea, (u32)nhg, biglist.get(), nbigp);
+        else k_emit_hard_kernel<U, false><<<blocks, 256, 0, st>>>(ea, (u32)nhg, biglist.get(), nbigp);
+        PFB_CUDA_CHECK(cudaGetLastError());
+        launch_stats().own++;
+#endif
+        timer.lap("K8 hard small groups");
+        const u64 nbig = read_scalar(nbigp, st);
+        if (nbig) {
+            rc = emit_big_groups<U>(ea, any_sa, biglist.get(), nbig, P, ws, err);
+            if (rc) return rc;
+        }
+        timer.lap("K8 hard big groups");
     }
-    timer.lap("K8 easy big");
-    u64 nhard = 0;
-    {   // hard groups: (dense group, ilist position) keys of every occurrence, one radix sort, scatter
-        DevBuf<u8> hf(D);
-        {
-            const u8 *cl = cls.get(); u8 *h = hf.get();
-            launch_for(D, st, PFB_LAMBDA(u64 t) { h[t] = cl[t] == 2 ? 1 : 0; });
-        }
-        DevBuf<u32> hl;
-        u64 mh;
-        {
-            DevBuf<u32> scratch;
-            mh = compact_indices(hf.get(), D, scratch, hl, ws);
-        }
-        hf.release();
-        timer.lap("K8 hard list");
-        if (mh) {
-            DevBuf<u32> hc(mh), ghead(mh), gid(mh);
-            DevBuf<u64> hoff(mh);
-            DevBuf<u8> gh(mh);
-            {
-                const u32 *hp = hl.get(); const u32 *cp = cnt.get(); const u8 *f = fl.get(); u32 *c_ = hc.get(); u8 *g = gh.get(); u32 *gd = ghead.get();
-                launch_for(mh, st, PFB_LAMBDA(u64 a) {
-                    u32 t = hp[a];
-                    c_[a] = cp[t];
-                    g[a] = f[t];                       // whole groups are listed: a group's head is its first listed member
-                    gd[a] = f[t] ? (u32)a : 0;
-                });
-            }
-            exclusive_sum<u32, u64>(hc.get(), hoff.get(), mh, ws.sc, st);
-            nhard = read_scalar(hoff.get() + (mh - 1), st) + read_scalar(hc.get() + (mh - 1), st);
-            u64 nhg = scan_flags(gh.get(), gid.get(), mh, ws);
-            {
-                DevBuf<u32> tmp(mh);
-                inclusive_max(ghead.get(), tmp.get(), mh, ws.sc, st);
-                ghead.swap(tmp);
-            }
-            const int ibits = bits_for(P);           // ilist values are in [0, P]
-            const int gbits = bits_for(nhg ? nhg - 1 : 0);
-            if (ibits + gbits > 64) { err = "internal: hard key overflow"; return PFB_ERR_INTERNAL; }
-            DevBuf<u64> hkey(nhard), hkey_b(nhard);
-            DevBuf<u32> hval(nhard), hval_b(nhard);
-            {
-                const u32 *hp = hl.get(); const u32 *wv = wordv.get(); const u32 *c_ = hc.get(); const u64 *ho = hoff.get();
-                const u32 *gi = gid.get(); const u8 *g = gh.get();
-                u64 *hk = hkey.get(); u32 *hv = hval.get();
-                launch_for(mh * 32, st, PFB_LAMBDA(u64 i) {
-                    u64 a = i >> 5;
-                    u32 lane = (u32)(i & 31);
-                    u32 t = hp[a];
-                    u32 c = c_[a];
-                    u64 gg = (u64)gi[a] + g[a] - 1;
-                    u64 e = ho[a];
-                    u32 base = 1 + wl.cum(wv[t]);
-                    for (u32 j = lane; j < c; j += 32) {
-                        hk[e + j] = (gg << ibits) | (u64)ilist[base + j];
-                        hv[e + j] = (u32)a;
-                    }
-                });
-            }
-            timer.lap("K8 hard keys");
-            sort_pairs(hkey, hkey_b, hval, hval_b, nhard, 0, ibits + gbits, ws.sc, st);
-            timer.lap("K8 hard sort");
-            {
-                const u64 *hk = hkey.get(); const u32 *hv = hval.get(); const u64 *ho = hoff.get(); const u64 *of = off.get();
-                const u32 *hp = hl.get(); const u32 *gd = ghead.get();
-                const u32 *sp = sa.get(); const u32 *wv = wordv.get(); const u64 *ks = key.get();
-                const u64 imask = ibits >= 64 ? ~0ull : ((1ull << ibits) - 1);
-                launch_for(nhard, st, PFB_LAMBDA(u64 e) {
-                    u32 a = hv[e];
-                    u32 t = hp[a];
-                    u32 ah = gd[a];
-                    u64 x = of[hp[ah]] + (e - ho[ah]);
-                    bwt[x] = prev_byte(ks[t]);                      // include/pfbwt.hpp:173-178
-                    if (any_sa) {
-                        u32 ii = (u32)(hk[e] & imask);
-                        u64 sl = wl.suflen(wv[t], sp[t]);
-                        store_sa<U>(sa_out, x, bwsai[ii] - sl);
-                    }
-                });
-            }
-        }
-    }
-    timer.lap("K8 hard scatter");
     out.hard = nhard;                 // "# hard cases" of include/pfbwt.hpp:188
     out.easy = n + 1 - nhard;
+    u8 *bwt = out.bwt.get();
+    u8 *sa_out = out.sa.get();
     if (any_sa) launch_for(1, st, PFB_LAMBDA(u64) { store_sa<U>(sa_out, 0, n); });   // src/pfbwt-f.cpp:301
-    key.release(); sa.release(); fl.release(); wordv.release(); cnt.release(); off.release(); cls.release(); head.release();
+    sa.release(); meta.release(); cnt.release(); ibase.release(); slen.release();
     tm.emit = timer.stop();
 
     // K9 run boundaries + run-length SA samples (src/pfbwt-f.cpp:304-328) -------------------
