@@ -10,7 +10,7 @@ BIN    := bin
 
 all: $(LIB) $(BIN)/pfbwt-f $(BIN)/pfbwt-f64 $(BIN)/merge_pfp emu
 
-$(LIB): $(CSRC)/capi.cu $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/build.cuh $(CSRC)/dictkeys.cuh $(CSRC)/emit.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp include/pfbwt_b200.h
+$(LIB): $(CSRC)/capi.cu $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/build.cuh $(CSRC)/dictkeys.cuh $(CSRC)/emit.cuh $(CSRC)/radix.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp include/pfbwt_b200.h
 	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/capi.cu -lz -lcudart
 
 $(BIN)/pfbwt-f: pfbwt-f_b200/src/pfbwt-f.cpp $(LIB)
@@ -25,7 +25,7 @@ $(BIN)/merge_pfp: pfbwt-f_b200/src/merge_pfp.cpp $(LIB)
 
 # developer logic check (tests only; see tests/emu/emu_main.cpp)
 emu: tests/emu/pfb_emu
-tests/emu/pfb_emu: tests/emu/emu_main.cpp $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/build.cuh $(CSRC)/dictkeys.cuh $(CSRC)/emit.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp
+tests/emu/pfb_emu: tests/emu/emu_main.cpp $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/build.cuh $(CSRC)/dictkeys.cuh $(CSRC)/emit.cuh $(CSRC)/radix.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp
 	$(CXX) -std=c++17 -O2 -Wall -Wno-unused -I $(CSRC) -o $@ $< -lz
 
 oracle:

@@ -121,6 +121,7 @@ def main():
     ap.add_argument("--bases", type=int, default=1_000_000_000)
     ap.add_argument("--ref-sample", type=int, default=12_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="profiling aid: skip the host-buffer leg")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -209,14 +210,16 @@ def main():
         ctx.generate_bwt(False, False)
         ctx.bwt(out=out_host.numpy()[:n + W + 1])         # D2H of the .bwt image (n+w+1 bytes)
 
-    for _ in range(max(1, min(args.warmup, 2))):
-        e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_step()
-    barrier()
-    t_e2e = time.perf_counter() - t0
+    t_e2e = float("nan")
+    if not args.no_e2e:
+        for _ in range(max(1, min(args.warmup, 2))):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        barrier()
+        t_e2e = time.perf_counter() - t0
     sampler.stop_flag = True
     sampler.join()
 

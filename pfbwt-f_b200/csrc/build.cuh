@@ -259,17 +259,8 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
         u64 total = read_scalar(tilebase.get() + nt, st);
         if (total != n + 1) { err = "internal: emitted positions " + std::to_string(total) + " != n+1 = " + std::to_string(n + 1); return PFB_ERR_INTERNAL; }
     }
-    k_group_classes(meta.get(), D, any_sa, ws);
+    const u64 nhg_cap = k_group_classes(meta.get(), D, any_sa, ws);   // number of hard groups (sizes the work list)
     timer.lap("K7 group classes");
-    // number of hard groups (sizes the work list of the emission kernel)
-    u64 nhg_cap;
-    {
-        DevBuf<u8> hh(D);
-        const u8 *mt = meta.get(); u8 *h = hh.get();
-        launch_for(D, st, PFB_LAMBDA(u64 t) { h[t] = (mt[t] & (M_HARD | M_HEAD)) == (M_HARD | M_HEAD) ? 1 : 0; });
-        nhg_cap = reduce_sum<u8, u64>(hh.get(), D, ws.sc, st);
-    }
-    timer.lap("K7 hard count");
     tm.groups = timer.stop();
 
     // K8 emission ---------------------------------------------------------------------
@@ -285,6 +276,11 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
     ea.wl = wl; ea.tilebase = tilebase.get(); ea.D = D;
     ea.ilist = pp.ilist.get(); ea.bwlast = pp.bwlast.get(); ea.bwsai = pp.bwsai.get();
     ea.bwt = out.bwt.get(); ea.sa_out = out.sa.get();
+    ea.small_lim = HARD_SMALL; ea.mid_lim = HARD_MID;
+    if (const char *e = getenv("PFB_HARD_LIMITS")) {   // test knob "small,mid": push groups down the larger-group paths
+        unsigned a_ = HARD_SMALL, b_ = HARD_MID;
+        if (sscanf(e, "%u,%u", &a_, &b_) == 2) { ea.small_lim = a_ < HARD_SMALL ? a_ : HARD_SMALL; ea.mid_lim = b_ < HARD_MID ? b_ : HARD_MID; }
+    }
     ea.hard_t = hard_t.get(); ea.hard_x = hard_x.get(); ea.n_hard_groups = ctr32.get(); ea.n_hard_occ = ctr64.get();
 #ifdef PFB_EMU
     emu_emit<U>(ea, any_sa);
@@ -311,10 +307,31 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
         launch_stats().own++;
 #endif
         timer.lap("K8 hard small groups");
-        const u64 nbig = read_scalar(nbigp, st);
-        if (nbig) {
-            rc = emit_big_groups<U>(ea, any_sa, biglist.get(), nbig, P, ws, err);
-            if (rc) return rc;
+        const u64 nmid = read_scalar(nbigp, st);
+        if (nmid) {
+            DevBuf<u32> biglist2(nmid), nbig2(1);
+            dev_memset(nbig2.get(), 0, 4, st);
+#ifdef PFB_EMU
+            emu_emit_hard_mid<U>(ea, any_sa, biglist.get(), (u32)nmid, biglist2.get(), nbig2.get());
+#else
+            static bool attr_set = false;
+            if (!attr_set) {
+                PFB_CUDA_CHECK(cudaFuncSetAttribute(k_emit_hard_mid_kernel<U, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MID_SMEM));
+                PFB_CUDA_CHECK(cudaFuncSetAttribute(k_emit_hard_mid_kernel<U, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MID_SMEM));
+                attr_set = true;
+            }
+            const unsigned mblocks = (unsigned)((nmid + 7) / 8);
+            if (any_sa) k_emit_hard_mid_kernel<U, true><<<mblocks, 256, MID_SMEM, st>>>(ea, biglist.get(), (u32)nmid, biglist2.get(), nbig2.get());
+            else k_emit_hard_mid_kernel<U, false><<<mblocks, 256, MID_SMEM, st>>>(ea, biglist.get(), (u32)nmid, biglist2.get(), nbig2.get());
+            PFB_CUDA_CHECK(cudaGetLastError());
+            launch_stats().own++;
+#endif
+            timer.lap("K8 hard mid groups");
+            const u64 nbig = read_scalar(nbig2.get(), st);
+            if (nbig) {
+                rc = emit_big_groups<U>(ea, any_sa, biglist2.get(), nbig, P, ws, err);
+                if (rc) return rc;
+            }
         }
         timer.lap("K8 hard big groups");
     }

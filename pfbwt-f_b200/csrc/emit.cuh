@@ -225,7 +225,7 @@ inline void k_classify(const ClassifyArgs &a, bool want_sa, pfbStream_t st) {
 static const u32 WALK_CAP = 1024;
 
 #ifndef PFB_EMU
-__global__ void __launch_bounds__(256) k_group_walk_kernel(u8 *meta, u64 D, u32 *longlist, u32 *nlong) {
+__global__ void __launch_bounds__(256) k_group_walk_kernel(u8 *meta, u64 D, u32 *longlist, u32 *nlong, u32 *nhard) {
     u64 t = (u64)blockIdx.x * 256 + threadIdx.x;
     const u64 stride = (u64)gridDim.x * 256;
     for (; t < D; t += stride) {
@@ -240,10 +240,10 @@ __global__ void __launch_bounds__(256) k_group_walk_kernel(u8 *meta, u64 D, u32 
             diff |= (x & 15) != (m & 15);
         }
         if (e < D && e - t > WALK_CAP) { longlist[atomicAdd(nlong, 1u)] = (u32)t; continue; }
-        if (diff) for (u64 i = t; i < e; ++i) meta[i] |= M_HARD;
+        if (diff) { for (u64 i = t; i < e; ++i) meta[i] |= M_HARD; atomicAdd(nhard, 1u); }
     }
 }
-__global__ void __launch_bounds__(256) k_group_long_kernel(u8 *meta, u64 D, const u32 *longlist) {
+__global__ void __launch_bounds__(256) k_group_long_kernel(u8 *meta, u64 D, const u32 *longlist, u32 *nhard) {
     const u64 t = longlist[blockIdx.x];
     const u32 pc = meta[t] & 15;
     __shared__ u64 s_end;
@@ -263,21 +263,26 @@ __global__ void __launch_bounds__(256) k_group_long_kernel(u8 *meta, u64 D, cons
     }
     any = __syncthreads_or(any);
     if (!any) return;
+    if (threadIdx.x == 0) atomicAdd(nhard, 1u);
     const u64 end = s_end;
     for (u64 i = t + threadIdx.x; i < end; i += 256) meta[i] |= M_HARD;
 }
 #endif
 
-inline void k_group_classes(u8 *meta, u64 D, bool any_sa, Workspace &ws) {
+// returns the number of hard groups
+inline u64 k_group_classes(u8 *meta, u64 D, bool any_sa, Workspace &ws) {
     pfbStream_t st = ws.st;
+    DevBuf<u32> nhard(1);
+    dev_memset(nhard.get(), 0, 4, st);
+    u32 *nh = nhard.get();
     if (any_sa) {
         launch_for(D, st, PFB_LAMBDA(u64 t) {
             u32 m = meta[t];
             if (!(m & M_VALID)) return;
             bool single = (m & M_HEAD) && (meta[t + 1] & M_HEAD);
-            if (!single) meta[t] = (u8)(m | M_HARD);
+            if (!single) { meta[t] = (u8)(m | M_HARD); if (m & M_HEAD) atomic_add(nh, 1u); }
         });
-        return;
+        return read_scalar(nh, st);
     }
 #ifdef PFB_EMU
     for (u64 t = 0; t < D; ++t) {
@@ -286,20 +291,22 @@ inline void k_group_classes(u8 *meta, u64 D, bool any_sa, Workspace &ws) {
         u64 e = t + 1;
         bool diff = false;
         for (; e < D && !(meta[e] & M_HEAD); ++e) diff |= (meta[e] & 15) != (m & 15);
-        if (diff) for (u64 i = t; i < e; ++i) meta[i] |= M_HARD;
+        if (diff) { for (u64 i = t; i < e; ++i) meta[i] |= M_HARD; ++*nh; }
     }
+    return *nh;
 #else
     DevBuf<u32> longlist(D / WALK_CAP + 2), nlong(1);
     dev_memset(nlong.get(), 0, 4, st);
-    k_group_walk_kernel<<<148 * 8, 256, 0, st>>>(meta, D, longlist.get(), nlong.get());
+    k_group_walk_kernel<<<148 * 8, 256, 0, st>>>(meta, D, longlist.get(), nlong.get(), nh);
     PFB_CUDA_CHECK(cudaGetLastError());
     launch_stats().own++;
     u32 nl = read_scalar(nlong.get(), st);
     if (nl) {
-        k_group_long_kernel<<<nl, 256, 0, st>>>(meta, D, longlist.get());
+        k_group_long_kernel<<<nl, 256, 0, st>>>(meta, D, longlist.get(), nh);
         PFB_CUDA_CHECK(cudaGetLastError());
         launch_stats().own++;
     }
+    return read_scalar(nh, st);
 #endif
 }
 
@@ -316,6 +323,7 @@ struct EmitArgs {
     u8 *bwt; u8 *sa_out;
     u32 *hard_t; u64 *hard_x;          // heads of hard groups and their first output position
     u32 *n_hard_groups; u64 *n_hard_occ;
+    u32 small_lim, mid_lim;            // <= HARD_SMALL / HARD_MID (test knob PFB_HARD_LIMITS lowers them)
 };
 
 // first ilist slot of the word that dictionary suffix t belongs to
@@ -473,7 +481,7 @@ __global__ void __launch_bounds__(256) k_emit_hard_kernel(EmitArgs a, u32 nh, u3
         u32 bal = (__ballot_sync(mask, stop) >> sh) & 0xffu;
         if (bal) { g = base + (u32)__ffs((int)bal) - 1; break; }
     }
-    if (g == 0 || g > HARD_SMALL) { if (l8 == 0) biglist[atomicAdd(nbig, 1u)] = (u32)gi; return; }
+    if (g == 0 || g > a.small_lim) { if (l8 == 0) biglist[atomicAdd(nbig, 1u)] = (u32)gi; return; }
     for (u32 k = l8; k < g; k += 8) { s_ib[sub][k] = ilist_base(a, t0 + k, SA); s_c[sub][k] = a.cnt[t0 + k]; }
     __syncwarp(mask);
     u64 T = 0;
@@ -492,6 +500,66 @@ __global__ void __launch_bounds__(256) k_emit_hard_kernel(EmitArgs a, u32 nh, u3
         if (SA) reinterpret_cast<UT *>(a.sa_out)[x] = (UT)(a.bwsai[v] - (u64)a.sl[t0 + k]);
     }
 }
+#endif
+
+// hard groups with more members but at most HARD_MID occurrences: one warp per group loads every
+// occurrence's ilist position into shared memory and ranks it by counting the smaller ones (the
+// positions are distinct); all lanes read the same shared word at a time (broadcast).
+static const u32 HARD_MID = 1024;
+
+#ifndef PFB_EMU
+template <int U, bool SA>
+__global__ void __launch_bounds__(256) k_emit_hard_mid_kernel(EmitArgs a, const u32 *midlist, u32 nmid, u32 *biglist, u32 *nbig) {
+    typedef typename UIntOf<U>::type UT;
+    extern __shared__ __align__(16) unsigned char mid_smem[];
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    u32 *s_val = reinterpret_cast<u32 *>(mid_smem) + wid * HARD_MID;
+    unsigned short *s_mem = reinterpret_cast<unsigned short *>(mid_smem + 8 * HARD_MID * 4) + wid * HARD_MID;
+    const u64 wg = (u64)blockIdx.x * 8 + wid;
+    if (wg >= nmid) return;
+    const u32 gi = midlist[wg];
+    const u64 t0 = a.hard_t[gi], X = a.hard_x[gi];
+    // members and occurrences (every member of a valid group has at least one occurrence)
+    u32 g = 0;
+    u64 T = 0;
+    for (u32 base = 0; base <= HARD_MID; base += 32) {
+        const u64 t = t0 + base + lane;
+        const bool stop = (base + lane) != 0 && (t >= a.D || (a.meta[t] & M_HEAD));
+        const u32 bal = __ballot_sync(0xffffffffu, stop);
+        const u32 nm = bal ? (u32)__ffs((int)bal) - 1 : 32u;      // members in this chunk
+        u32 c = lane < nm ? a.cnt[t] : 0u;
+#pragma unroll
+        for (int d = 16; d; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+        T += c; g += nm;
+        if (bal || T > HARD_MID) break;
+        if (base + 32 > HARD_MID) { T = HARD_MID + 1; break; }
+    }
+    if (T > a.mid_lim) { if (lane == 0) biglist[atomicAdd(nbig, 1u)] = gi; return; }
+    u32 run = 0;
+    for (u32 base = 0; base < g; base += 32) {
+        const u32 k = base + lane;
+        u32 c = 0, ib = 0;
+        if (k < g) { c = a.cnt[t0 + k]; ib = ilist_base(a, t0 + k, SA); }
+        u32 inc = c;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { u32 o = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += o; }
+        u32 off = run + inc - c;
+        for (u32 j = 0; j < c; ++j) { s_val[off + j] = a.ilist[(u64)ib + j]; s_mem[off + j] = (unsigned short)k; }
+        run += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    __syncwarp();
+    const u32 Tn = (u32)T;
+    for (u32 q = lane; q < Tn; q += 32) {
+        const u32 v = s_val[q];
+        u32 rank = 0;
+        for (u32 i = 0; i < Tn; ++i) rank += s_val[i] < v ? 1u : 0u;
+        const u32 k = s_mem[q];
+        const u64 x = X + rank;
+        a.bwt[x] = prev_byte(a.meta[t0 + k]);                     // include/pfbwt.hpp:173-178
+        if (SA) reinterpret_cast<UT *>(a.sa_out)[x] = (UT)(a.bwsai[v] - (u64)a.sl[t0 + k]);
+    }
+}
+static const size_t MID_SMEM = 8 * HARD_MID * 4 + 8 * HARD_MID * 2;
 #endif
 
 // serial twins (emulator) ------------------------------------------------------------------
@@ -531,7 +599,7 @@ inline void emu_emit_hard(const EmitArgs &a, bool SA, u32 nh, u32 *biglist, u32 
         u64 t0 = a.hard_t[gi], X = a.hard_x[gi];
         u32 g = 1;
         while (!(a.meta[t0 + g] & M_HEAD)) ++g;
-        if (g > HARD_SMALL) { biglist[(*nbig)++] = gi; continue; }
+        if (g > a.small_lim) { biglist[(*nbig)++] = gi; continue; }
         for (u32 k = 0; k < g; ++k) {
             u32 ib = ilist_base(a, t0 + k, SA), c = a.cnt[t0 + k];
             for (u32 j = 0; j < c; ++j) {
@@ -545,10 +613,32 @@ inline void emu_emit_hard(const EmitArgs &a, bool SA, u32 nh, u32 *biglist, u32 
         }
     }
 }
+template <int U>
+inline void emu_emit_hard_mid(const EmitArgs &a, bool SA, const u32 *midlist, u32 nmid, u32 *biglist, u32 *nbig) {
+    for (u32 w = 0; w < nmid; ++w) {
+        u32 gi = midlist[w];
+        u64 t0 = a.hard_t[gi], X = a.hard_x[gi];
+        u32 g = 1;
+        while (t0 + g < a.D && !(a.meta[t0 + g] & M_HEAD)) ++g;
+        u64 T = 0;
+        for (u32 k = 0; k < g; ++k) T += a.cnt[t0 + k];
+        if (T > a.mid_lim) { biglist[(*nbig)++] = gi; continue; }
+        std::vector<std::pair<u32, u32>> occ;
+        for (u32 k = 0; k < g; ++k) {
+            u32 ib = ilist_base(a, t0 + k, SA);
+            for (u32 j = 0; j < a.cnt[t0 + k]; ++j) occ.push_back({a.ilist[(u64)ib + j], k});
+        }
+        std::sort(occ.begin(), occ.end());
+        for (size_t r = 0; r < occ.size(); ++r) {
+            a.bwt[X + r] = prev_byte(a.meta[t0 + occ[r].second]);
+            if (SA) emu_store_sa<U>(a.sa_out, X + r, a.bwsai[occ[r].first] - (u64)a.sl[t0 + occ[r].second]);
+        }
+    }
+}
 #endif
 
 // ---------------------------------------------------------------------------
-// hard groups with more than HARD_SMALL members: all occurrences of a chunk of groups get a
+// hard groups with more than HARD_MID occurrences: all occurrences of a chunk of groups get a
 // (dense group id, ilist position) key, one radix sort orders them, a scatter writes them.  Chunks
 // bound the work memory (BIG_CHUNK occurrences at a time).
 // ---------------------------------------------------------------------------

@@ -21,9 +21,6 @@
 
 namespace pfb {
 
-typedef uint8_t u8;
-typedef uint32_t u32;
-typedef uint64_t u64;
 
 // error codes: PFB_OK / PFB_ERR_* from include/pfbwt_b200.h
 

@@ -340,9 +340,19 @@ inline void launch_for(uint64_t n, pfbStream_t s, F f) {
 #endif
 }
 
+typedef uint8_t u8;
+typedef uint32_t u32;
+typedef uint64_t u64;
+}  // namespace pfb
+#include "radix.cuh"
+namespace pfb {
+
 // ------------------------------------------------------------------- scans --
 struct Scratch {
     DevBuf<uint8_t> buf;
+#ifndef PFB_EMU
+    RadixWork rw;
+#endif
     void *ensure(size_t bytes) {
         if (buf.size() < bytes) buf.alloc(bytes + bytes / 4 + 256);
         return buf.get();
@@ -412,9 +422,19 @@ inline TOut reduce_sum(const TIn *in, uint64_t n, Scratch &sc, pfbStream_t s) {
 // ------------------------------------------------------------- radix sorts --
 // Stable LSD radix sort of (key,value) pairs on key bits [begin_bit,end_bit).
 // Result is left in keys_a/vals_a (buffers may be swapped internally).
+// (u64,u32) pairs go through the hand-written onesweep sort of radix.cuh; PFB_SORT=cub selects the
+// library sort for A/B timing.  iota_vals: input values are 0..n-1 (vals_a need not be initialised);
+// hist0: device histogram of the first 8-bit digit when the caller already has it.
 template <class K, class V>
 inline void sort_pairs(DevBuf<K> &keys_a, DevBuf<K> &keys_b, DevBuf<V> &vals_a, DevBuf<V> &vals_b, uint64_t n,
-                       int begin_bit, int end_bit, Scratch &sc, pfbStream_t s) {
+                       int begin_bit, int end_bit, Scratch &sc, pfbStream_t s, bool iota_vals = false, const uint64_t *hist0 = nullptr) {
+#ifndef PFB_EMU
+    if constexpr (sizeof(K) == 8 && sizeof(V) == 4) {
+        static const bool use_cub = getenv("PFB_SORT") && !strcmp(getenv("PFB_SORT"), "cub");
+        if (!use_cub) { radix_sort_pairs(keys_a, keys_b, vals_a, vals_b, n, begin_bit, end_bit, iota_vals, hist0, sc.rw, s); return; }
+    }
+#endif
+    if (iota_vals && n) { V *v = vals_a.get(); launch_for(n, s, PFB_LAMBDA(uint64_t i) { v[i] = (V)i; }); }
     if (n <= 1) return;
     if (end_bit <= begin_bit) return;
 #ifdef PFB_EMU
