@@ -19,26 +19,6 @@
 #pragma once
 #include "dictkeys.cuh"
 
-namespace pfb {
-
-// position -> (word, suffix length) through the sample table
-struct WordLookup {
-    const u64 *wc;      // Dw+2 entries, low 32 bits = word start; wc[Dw] = D-1, wc[Dw+1] = 2^32-1
-    const u32 *wsamp;
-    u32 Dw;
-    PFB_HD inline u32 word(u32 idx) const {
-        u32 d = wsamp[idx >> 7];
-        while ((u32)wc[d + 1] <= idx) ++d;
-        return d;
-    }
-    PFB_HD inline u32 start(u32 d) const { return (u32)wc[d]; }
-    PFB_HD inline u32 cum(u32 d) const { return (u32)(wc[d] >> 32); }
-    // length of the suffix starting at idx inside word d, EndOfWord excluded (0 for the EndOfDict slot)
-    PFB_HD inline u64 suflen(u32 d, u32 idx) const { return d < Dw ? (u64)((u32)wc[d + 1] - 1 - idx) : 0; }
-};
-
-}  // namespace pfb
-
 #include "emit.cuh"
 
 namespace pfb {
@@ -66,13 +46,16 @@ inline u64 compact_indices(const u8 *flags, u64 n, DevBuf<u32> &scratch_idx, Dev
 //     is exactly a run with glcp >= suff_len (:136-145).
 //     Result: sa[] and meta[] (preceding-byte code + head bit), both padded(D) long.
 // ---------------------------------------------------------------------------
-inline int sort_dict_suffixes(const DeviceParse &pp, DevBuf<u32> &sa, DevBuf<u8> &meta, const WordLookup &wl,
-                              Workspace &ws, StageTimes &tm, Timer &timer, std::string &err) {
+//     cnt[] (occurrences per suffix) and the valid/full bits of meta come out of the keys' upper
+//     bits; *reclassify is set when they have to be recomputed by lookup (prefix doubling ran).
+inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, DevBuf<u8> &meta, DevBuf<u32> &cnt, const WordLookup &wl,
+                              bool *reclassify, Workspace &ws, StageTimes &tm, Timer &timer, std::string &err) {
     pfbStream_t st = ws.st;
     const u64 D = pp.dsize;
     const u8 *dict = pp.dict.get();
-    sa.alloc(padded(D)); meta.alloc(padded(D) + 64);
+    sa.alloc(padded(D)); meta.alloc(padded(D) + 64); cnt.alloc(padded(D));
     dev_memset(meta.get(), M_HEAD, padded(D) + 64, st);
+    *reclassify = false;
     int L = 1;
     while (L < KEY_MAX_SYMS && (1ull << (2 * L)) < 128ull * D) ++L;     // ties become rare once 4^L >> D
     if (const char *e = getenv("PFB_KEY_SYMS")) { L = atoi(e); if (L < 1) L = 1; if (L > KEY_MAX_SYMS) L = KEY_MAX_SYMS; }   // test knob
@@ -81,11 +64,15 @@ inline int sort_dict_suffixes(const DeviceParse &pp, DevBuf<u32> &sa, DevBuf<u8>
     {
         DevBuf<u64> key(D), key_b(D);
         DevBuf<u32> val_b(padded(D));
-        k_suffix_keys(dict, D, L, key.get(), sa.get(), st);
+        const KeyExtra kx = key_extra_for(L);
+        k_suffix_keys(dict, D, L, key.get(), wl, pp.occ.get(), w, kx, st);
         timer.lap("K6 keys");
-        sort_pairs(key, key_b, sa, val_b, D, KEY_CODE_SHIFT, KEY_CODE_SHIFT + enum_bits(L), ws.sc, st);
+        sort_pairs(key, key_b, sa, val_b, D, KEY_CODE_SHIFT, KEY_CODE_SHIFT + enum_bits(L), ws.sc, st, /*iota_vals=*/true);
         timer.lap("K6 radix sort");
-        m = sorted_flags_and_open_list(key.get(), D, meta.get(), apos, ws);
+        FlagsArgs fa;
+        fa.key = key.get(); fa.sa = sa.get(); fa.D = D; fa.meta = meta.get(); fa.cnt = cnt.get(); fa.tilecnt = nullptr;
+        fa.kx = kx; fa.wl = wl; fa.w = (u64)w;
+        m = sorted_flags_and_open_list(fa, apos, ws);
         if (m) {
             adep.alloc(m);
             const u32 *ap = apos.get(); const u64 *ks = key.get(); u32 *dp = adep.get();
@@ -135,14 +122,18 @@ inline int sort_dict_suffixes(const DeviceParse &pp, DevBuf<u32> &sa, DevBuf<u8>
         DevBuf<u8> act2(m);
         {
             const u32 *ap = apos.get(); const u64 *kp = k2.get(); const u32 *vp = v.get();
-            u32 *sp = sa.get(); u8 *ac = act2.get(); u32 *dp = adep.get();
+            u32 *sp = sa.get(); u8 *ac = act2.get(); u32 *dp = adep.get(); u32 *cp = cnt.get();
+            const WordLookup w3 = wl; const u64 w64 = (u64)w;
             launch_for(m, st, PFB_LAMBDA(u64 a) {
                 u64 k = kp[a] >> 6;
                 bool head = a == 0 || k != (kp[a - 1] >> 6);
                 bool last = a + 1 == m || k != (kp[a + 1] >> 6);
                 u32 j = ap[a];
                 sp[j] = vp[a];
-                mt[j] = (u8)(prev_code(dict, vp[a]) | (head ? M_HEAD : 0));   // the preceding-byte code travels with the suffix
+                u32 c, ib, sl;
+                u32 vf = suffix_class(w3, vp[a], w64, c, ib, sl);         // what travels with the suffix: count, valid/full bits,
+                cp[j] = c;                                                 // and the preceding-byte code
+                mt[j] = (u8)(prev_code(dict, vp[a]) | (head ? M_HEAD : 0) | vf);
                 dp[a] += (u32)(kp[a] >> 1) & 31u;                             // slot a stays inside its old group: same depth so far
                 ac[a] = (!(head && last) && !(kp[a] & 1)) ? 1 : 0;
             });
@@ -187,6 +178,7 @@ inline int sort_dict_suffixes(const DeviceParse &pp, DevBuf<u32> &sa, DevBuf<u8>
         rounds += dr;
         const u32 *sp = sa.get(); const u8 *f = fl.get();
         launch_for(D, st, PFB_LAMBDA(u64 j) { mt[j] = (u8)(prev_code(dict, sp[j]) | (f[j] ? M_HEAD : 0)); });
+        *reclassify = true;
         timer.lap("K6 prefix doubling");
     }
     tm.dict_sort_rounds = rounds;
@@ -237,22 +229,28 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
     // K6 dictionary suffix sort -------------------------------------------------------
     DevBuf<u32> sa;
     DevBuf<u8> meta;
-    int rc = sort_dict_suffixes(pp, sa, meta, wl, ws, tm, timer, err);
+    DevBuf<u32> cnt, ibase, slen;
+    bool reclassify = false;
+    int rc = sort_dict_suffixes(pp, (int)w, sa, meta, cnt, wl, &reclassify, ws, tm, timer, err);
     if (rc) return rc;
     tm.dict_sort = timer.stop();
 
-    // K7 classify, tile offsets, hard groups ------------------------------------------------
+    // K7 tile offsets, hard groups ------------------------------------------------------
+    // Without SA output everything the emission needs per suffix came with the sort (meta, cnt);
+    // with SA output (or after prefix doubling) a lookup pass adds ilist base and suffix length.
     const u64 nt = tiles_of(D);
-    DevBuf<u32> cnt(padded(D)), ibase, slen;
     DevBuf<u64> tilesum(nt + 1), tilebase(nt + 1);
     if (any_sa) { ibase.alloc(padded(D)); slen.alloc(padded(D)); }
-    {
+    if (any_sa || reclassify) {
         ClassifyArgs ca;
         ca.sa = sa.get(); ca.meta = meta.get(); ca.wl = wl; ca.D = D; ca.w = w;
         ca.cnt = cnt.get(); ca.tilesum = tilesum.get(); ca.ibase = ibase.get(); ca.sl = slen.get();
         k_classify(ca, any_sa, st);
+        timer.lap("K7 classify (word lookup)");
+    } else {
+        k_tile_sums(cnt.get(), D, tilesum.get(), st);
+        timer.lap("K7 tile sums");
     }
-    timer.lap("K7 classify (word lookup)");
     dev_memset(tilesum.get() + nt, 0, 8, st);
     exclusive_sum<u64, u64>(tilesum.get(), tilebase.get(), nt + 1, ws.sc, st);
     {

@@ -40,6 +40,50 @@ static const int KEY_MAX_SYMS = 26;     // N_26 < 2^54
 PFB_HD inline u64 enum_count(int L) { return (7ull * (1ull << (2 * L)) - 4ull) / 3ull; }   // N_L
 inline int enum_bits(int L) { return bits_for(enum_count(L) - 1); }
 
+// position -> (word, suffix length) through the sample table
+struct WordLookup {
+    const u64 *wc;      // Dw+2 entries, low 32 bits = word start; wc[Dw] = D-1, wc[Dw+1] = 2^32-1
+    const u32 *wsamp;
+    u32 Dw;
+    PFB_HD inline u32 word(u32 idx) const {
+        u32 d = wsamp[idx >> 7];
+        while ((u32)wc[d + 1] <= idx) ++d;
+        return d;
+    }
+    PFB_HD inline u32 start(u32 d) const { return (u32)wc[d]; }
+    PFB_HD inline u32 cum(u32 d) const { return (u32)(wc[d] >> 32); }
+    // length of the suffix starting at idx inside word d, EndOfWord excluded (0 for the EndOfDict slot)
+    PFB_HD inline u64 suflen(u32 d, u32 idx) const { return d < Dw ? (u64)((u32)wc[d + 1] - 1 - idx) : 0; }
+};
+
+// The bits of a key above the code carry what the assembly needs to know about the suffix, so that
+// the sorted order can be classified without a random position -> word lookup per suffix:
+//   bit 63            full: the suffix is a whole dictionary word
+//   [cshift, 63)      occurrences it emits (occ of its word; 0 = suffix length <= w, all ones = look it up)
+struct KeyExtra {
+    int cshift = 63;      // first bit of the count field (10 + code bits)
+    u64 cmax = 0;         // all-ones value of the field (0: field absent)
+    PFB_HD inline u64 pack(u64 cnt, bool full) const {
+        if (!cmax) return 0;          // no room above the code: classification falls back to lookups
+        u64 c = cnt < cmax ? cnt : cmax;
+        return (c << cshift) | (full ? 1ull << 63 : 0ull);
+    }
+    PFB_HD inline u64 count(u64 key) const { return (key >> cshift) & cmax; }
+    u64 cmask = ~0ull;    // mask of the code after shifting the key right by KEY_CODE_SHIFT
+    PFB_HD inline u64 code(u64 key) const { return (key >> 10) & cmask; }
+    PFB_HD inline bool full(u64 key) const { return (key >> 63) != 0; }
+};
+inline KeyExtra key_extra_for(int L) {
+    KeyExtra x;
+    int top = 10 + enum_bits(L);
+    x.cmask = (1ull << enum_bits(L)) - 1;
+    int room = 63 - top;
+    if (const char *e = getenv("PFB_KEY_COUNT_BITS")) { int r = atoi(e); if (r < room) room = r; }   // test knob: force count overflow / absence
+    if (room >= 1) { if (room > 24) room = 24; x.cshift = top; x.cmax = (1ull << room) - 1; }
+    return x;
+}
+
+
 // B: the j leading ACGT digits left-aligned in a field of L digits (zero below); kind: stopper when j < L
 PFB_HD inline u64 enum_code(u64 B, int j, int L, u32 kind) {
     const u64 lo = 0x5555555555555555ull;
@@ -93,7 +137,7 @@ PFB_HD inline u8 prev_byte(u64 key) { return (key & 8) ? ENDOFWORD : sym3_byte((
 // through shared memory so that global stores are unit-stride.
 static const int KEYS_TILE = 2048;
 __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict__ dict, u64 D, int L, u64 *__restrict__ key,
-                                                            u32 *__restrict__ sa) {
+                                                            WordLookup wl, const u32 *__restrict__ occ, int w, KeyExtra kx) {
     __shared__ __align__(16) u8 sb[KEYS_TILE + 48];
     __shared__ u64 sk[KEYS_TILE];
     const u64 base = (u64)blockIdx.x * KEYS_TILE;
@@ -112,7 +156,7 @@ __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict
     if (threadIdx.x == 0) sprev = base ? (u32)dict[base - 1] : 0u;
     __syncthreads();
     const int i0 = threadIdx.x * 8;
-    u64 xh = 0, xl = 0, rm = 0;
+    u64 xh = 0, xl = 0, rm = 0, tmk = 0;    // tmk: EndOfWord / EndOfDict positions
     u32 pcs[8];
     pcs[0] = sym3_fast(i0 ? (u32)sb[i0 - 1] : sprev);
 #pragma unroll
@@ -125,9 +169,13 @@ __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict
             u64 f = sym_field(s);
             if (k < 32) xh |= f << (62 - 2 * k); else xl |= f << (62 - 2 * (k - 32));
             rm |= (u64)sym_stops(s) << (63 - k);
+            tmk |= (u64)(s == 0 ? 1u : 0u) << (63 - k);
             if (k < 7) pcs[k + 1] = s;
         }
     }
+    // word of the thread's first position (one sampled lookup per 8 positions); later positions add
+    // the EndOfWord bytes passed
+    u32 d = (base + (u64)i0 < D) ? wl.word((u32)(base + (u64)i0)) : wl.Dw;
 #pragma unroll
     for (int p = 0; p < 8; ++p) {
         u64 W = p ? ((xh << (2 * p)) | (xl >> (64 - 2 * p))) : xh;
@@ -140,30 +188,38 @@ __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict
         u64 code = enum_code(B, j, L, kind);
         u64 i = base + (u64)(i0 + p);
         u32 pc = i <= 1 ? 0u : (pcs[p] ? pcs[p] : 8u);
-        sk[i0 + p] = pack_key(code, j < L ? (u32)j + 1 : (u32)L, j < L && kind == 0, pc);
+        const bool valid = ((tmk << p) >> (63 - w)) == 0;          // no EndOfWord within the next w+1 bytes: suffix length > w
+        const bool full = i == 0 || (i > 1 && pcs[p] == 0) ;       // preceded by EndOfWord (or the very first byte)
+        u64 c = (valid && d < wl.Dw) ? (u64)occ[d] : 0ull;
+        sk[i0 + p] = pack_key(code, j < L ? (u32)j + 1 : (u32)L, j < L && kind == 0, pc) | kx.pack(c, valid && full);
+        d += (u32)((tmk >> (63 - p)) & 1);
     }
     __syncthreads();
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
         int o = k * 256 + threadIdx.x;
         u64 g = base + (u64)o;
-        if (g < D) { key[g] = sk[o]; sa[g] = (u32)g; }
+        if (g < D) key[g] = sk[o];
     }
 }
 #endif
 
-// keys + identity permutation for all D dictionary positions, L <= KEY_MAX_SYMS symbols per key
-inline void k_suffix_keys(const u8 *dict, u64 D, int L, u64 *key, u32 *sa, pfbStream_t st) {
+// keys of all D dictionary positions, L <= KEY_MAX_SYMS symbols per key (the identity permutation is
+// implied: the radix sort's first pass takes value = position)
+inline void k_suffix_keys(const u8 *dict, u64 D, int L, u64 *key, const WordLookup &wl, const u32 *occ, int w, const KeyExtra &kx,
+                          pfbStream_t st) {
 #ifdef PFB_EMU
     (void)st;
     for (u64 i = 0; i < D; ++i) {
         EnumKey e = enum_scan(dict, D, i, L);
-        key[i] = pack_key(e.code, e.consumed, e.closed, (u32)prev_code(dict, i));
-        sa[i] = (u32)i;
+        u32 d = wl.word((u32)i);
+        bool valid = wl.suflen(d, (u32)i) > (u64)w;
+        bool full = valid && (u32)i == wl.start(d);
+        key[i] = pack_key(e.code, e.consumed, e.closed, (u32)prev_code(dict, i)) | kx.pack(valid ? occ[d] : 0, full);
     }
 #else
     if (D == 0) return;
-    k_suffix_keys_kernel<<<(unsigned)((D + KEYS_TILE - 1) / KEYS_TILE), 256, 0, st>>>(dict, D, L, key, sa);
+    k_suffix_keys_kernel<<<(unsigned)((D + KEYS_TILE - 1) / KEYS_TILE), 256, 0, st>>>(dict, D, L, key, wl, occ, w, kx);
     PFB_CUDA_CHECK(cudaGetLastError());
     launch_stats().own++;
 #endif

@@ -24,6 +24,33 @@ static const u8 M_HEAD = 0x10, M_FULL = 0x20, M_VALID = 0x40, M_HARD = 0x80;
 inline u64 tiles_of(u64 n) { return (n + TILE - 1) / TILE; }
 inline u64 padded(u64 n) { return tiles_of(n) * TILE; }
 
+struct FlagsArgs {
+    const u64 *key; const u32 *sa; u64 D; u8 *meta; u32 *cnt; u32 *tilecnt; KeyExtra kx; WordLookup wl; u64 w;
+};
+// valid / full bits and occurrence count of dictionary suffix idx by position -> word lookup
+// (include/pfbwt.hpp:83-85,111-119)
+PFB_HD inline u32 suffix_class(const WordLookup &wl, u32 idx, u64 w, u32 &cnt, u32 &ibase, u32 &slen) {
+    u32 d = wl.word(idx);
+    u64 len = wl.suflen(d, idx);
+    cnt = 0; ibase = 0; slen = (u32)len;
+    if (len <= w) return 0;
+    u32 c0 = wl.cum(d);
+    cnt = wl.cum(d + 1) - c0;
+    ibase = 1 + c0;
+    return (u32)M_VALID | (idx == wl.start(d) ? (u32)M_FULL : 0u);
+}
+PFB_HD inline void flags_one(const FlagsArgs &a, u64 t, u64 kprev, u64 k, u64 knext, u32 &m, u32 &c, bool &act) {
+    u64 code = a.kx.code(k);
+    bool head = t == 0 || code != a.kx.code(kprev);
+    bool last = t + 1 == a.D || code != a.kx.code(knext);
+    act = !(head && last) && !key_closed(k);
+    u64 cf = a.kx.count(k);
+    m = (u32)(k & 15) | (head ? M_HEAD : 0) | (act ? M_HARD : 0);
+    if (a.kx.cmax && cf != a.kx.cmax) { c = (u32)cf; m |= (c ? M_VALID : 0) | (a.kx.full(k) ? M_FULL : 0); }
+    else { u32 ib, sl; m |= suffix_class(a.wl, a.sa[t], a.w, c, ib, sl); }      // no room in the key / count overflow
+}
+
+
 #ifndef PFB_EMU
 // exclusive prefix of one value per thread over a 256-thread block; returns the block total
 template <class T>
@@ -45,37 +72,43 @@ __device__ __forceinline__ T block_excl_scan(T v, T &total, T *warp_sums /* 8 */
     return base + inc - v;
 }
 
-// ---- after the main radix sort: head flags, "tied and open" flags, per-tile open counts ----
-__global__ void __launch_bounds__(256) k_sorted_flags_kernel(const u64 *__restrict__ key, u64 D, u8 *__restrict__ meta,
-                                                             u32 *__restrict__ tilecnt) {
+// ---- after the main radix sort: head flags, "tied and open" flags, per-tile open counts; the
+//      valid / full bits and the occurrence count come out of the key's upper bits (dictkeys.cuh) ----
+__global__ void __launch_bounds__(256) k_sorted_flags_kernel(FlagsArgs a) {
     __shared__ u32 ws[8];
     const u64 t0 = (u64)blockIdx.x * TILE + (u64)threadIdx.x * 8;
     u64 k[10];
 #pragma unroll
     for (int e = 0; e < 10; ++e) {
         u64 t = t0 + (u64)e - 1;
-        k[e] = (t0 + (u64)e >= 1 && t < D) ? key[t] : ~0ull;
+        k[e] = (t0 + (u64)e >= 1 && t < a.D) ? a.key[t] : ~0ull;
     }
     u64 m8 = 0;
-    u32 nact = 0;
+    u32 nact = 0, c[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
         u64 t = t0 + (u64)e;
-        u32 m = 0;
-        if (t < D) {
-            u64 c = k[e + 1] >> KEY_CODE_SHIFT;
-            bool head = t == 0 || c != (k[e] >> KEY_CODE_SHIFT);
-            bool last = t + 1 == D || c != (k[e + 2] >> KEY_CODE_SHIFT);
-            bool act = !(head && last) && !key_closed(k[e + 1]);
-            m = (u32)(k[e + 1] & 15) | (head ? M_HEAD : 0) | (act ? M_HARD : 0);
-            nact += act;
-        } else m = M_HEAD;
+        u32 m = M_HEAD;
+        c[e] = 0;
+        if (t < a.D) { bool act; flags_one(a, t, k[e], k[e + 1], k[e + 2], m, c[e], act); nact += act; }
         m8 |= (u64)m << (8 * e);
     }
-    *reinterpret_cast<u64 *>(meta + t0) = m8;
+    *reinterpret_cast<u64 *>(a.meta + t0) = m8;
+    reinterpret_cast<uint4 *>(a.cnt + t0)[0] = make_uint4(c[0], c[1], c[2], c[3]);
+    reinterpret_cast<uint4 *>(a.cnt + t0)[1] = make_uint4(c[4], c[5], c[6], c[7]);
     u32 tot;
     block_excl_scan<u32>(nact, tot, ws);
-    if (threadIdx.x == 0) tilecnt[blockIdx.x] = tot;
+    if (threadIdx.x == 0) a.tilecnt[blockIdx.x] = tot;
+}
+
+// per-tile sums of cnt[] (BWT positions emitted by a tile)
+__global__ void __launch_bounds__(256) k_tile_sums_kernel(const u32 *__restrict__ cnt, u64 *__restrict__ tilesum) {
+    __shared__ u64 ws[8];
+    const u64 t0 = (u64)blockIdx.x * TILE + (u64)threadIdx.x * 8;
+    uint4 x = reinterpret_cast<const uint4 *>(cnt + t0)[0], y = reinterpret_cast<const uint4 *>(cnt + t0)[1];
+    u64 sum = (u64)x.x + x.y + x.z + x.w + y.x + y.y + y.z + y.w, tot;
+    block_excl_scan<u64>(sum, tot, ws);
+    if (threadIdx.x == 0) tilesum[blockIdx.x] = tot;
 }
 
 // ---- ordered compaction of the positions whose meta byte has `bit` set ----
@@ -95,19 +128,18 @@ __global__ void __launch_bounds__(256) k_compact_bit_kernel(const u8 *__restrict
 }
 #endif
 
-// meta (head | pc | open bit) from sorted keys; returns the ordered list of open positions
-inline u64 sorted_flags_and_open_list(const u64 *key, u64 D, u8 *meta /* padded(D) */, DevBuf<u32> &list, Workspace &ws) {
+
+// meta (pc | head | full | valid | open bit) and cnt from sorted keys; returns the ordered list of open positions
+inline u64 sorted_flags_and_open_list(FlagsArgs fa, DevBuf<u32> &list, Workspace &ws) {
     pfbStream_t st = ws.st;
-    const u64 nt = tiles_of(D);
+    const u64 D = fa.D, nt = tiles_of(D);
 #ifdef PFB_EMU
     std::vector<u32> v;
     for (u64 t = 0; t < padded(D); ++t) {
-        if (t >= D) { meta[t] = M_HEAD; continue; }
-        u64 c = key[t] >> KEY_CODE_SHIFT;
-        bool head = t == 0 || c != (key[t - 1] >> KEY_CODE_SHIFT);
-        bool last = t + 1 == D || c != (key[t + 1] >> KEY_CODE_SHIFT);
-        bool act = !(head && last) && !key_closed(key[t]);
-        meta[t] = (u8)((key[t] & 15) | (head ? M_HEAD : 0) | (act ? M_HARD : 0));
+        if (t >= D) { fa.meta[t] = M_HEAD; fa.cnt[t] = 0; continue; }
+        u32 m, c; bool act;
+        flags_one(fa, t, t ? fa.key[t - 1] : 0, fa.key[t], t + 1 < D ? fa.key[t + 1] : 0, m, c, act);
+        fa.meta[t] = (u8)m; fa.cnt[t] = c;
         if (act) v.push_back((u32)t);
     }
     list.alloc(v.size());
@@ -116,7 +148,8 @@ inline u64 sorted_flags_and_open_list(const u64 *key, u64 D, u8 *meta /* padded(
     return v.size();
 #else
     DevBuf<u32> tcnt(nt + 1), tbase(nt + 1);
-    k_sorted_flags_kernel<<<(unsigned)nt, 256, 0, st>>>(key, D, meta, tcnt.get());
+    fa.tilecnt = tcnt.get();
+    k_sorted_flags_kernel<<<(unsigned)nt, 256, 0, st>>>(fa);
     PFB_CUDA_CHECK(cudaGetLastError());
     launch_stats().own++;
     dev_memset(tcnt.get() + nt, 0, 4, st);
@@ -124,11 +157,26 @@ inline u64 sorted_flags_and_open_list(const u64 *key, u64 D, u8 *meta /* padded(
     u64 m = read_scalar(tbase.get() + nt, st);
     list.alloc(m);
     if (m) {
-        k_compact_bit_kernel<<<(unsigned)nt, 256, 0, st>>>(meta, M_HARD, tbase.get(), list.get());
+        k_compact_bit_kernel<<<(unsigned)nt, 256, 0, st>>>(fa.meta, M_HARD, tbase.get(), list.get());
         PFB_CUDA_CHECK(cudaGetLastError());
         launch_stats().own++;
     }
     return m;
+#endif
+}
+
+inline void k_tile_sums(const u32 *cnt, u64 D, u64 *tilesum, pfbStream_t st) {
+#ifdef PFB_EMU
+    (void)st;
+    for (u64 tile = 0; tile < tiles_of(D); ++tile) {
+        u64 s = 0;
+        for (u64 t = tile * TILE; t < (tile + 1) * TILE; ++t) s += cnt[t];
+        tilesum[tile] = s;
+    }
+#else
+    k_tile_sums_kernel<<<(unsigned)tiles_of(D), 256, 0, st>>>(cnt, tilesum);
+    PFB_CUDA_CHECK(cudaGetLastError());
+    launch_stats().own++;
 #endif
 }
 
@@ -144,19 +192,7 @@ struct ClassifyArgs {
 };
 
 PFB_HD inline void classify_one(const ClassifyArgs &a, u64 t, u32 &m, u32 &c, u32 &ib, u32 &s) {
-    u32 idx = a.sa[t];
-    u32 d = a.wl.word(idx);
-    u64 len = a.wl.suflen(d, idx);
-    bool valid = len > a.w;
-    m &= (u32)(0x0f | M_HEAD);
-    c = 0; ib = 0; s = (u32)len;
-    if (valid) {
-        u32 c0 = a.wl.cum(d);
-        c = a.wl.cum(d + 1) - c0;
-        ib = 1 + c0;
-        m |= M_VALID;
-        if (idx == a.wl.start(d)) m |= M_FULL;
-    }
+    m = (m & (u32)(0x0f | M_HEAD)) | suffix_class(a.wl, a.sa[t], a.w, c, ib, s);
 }
 
 #ifndef PFB_EMU
