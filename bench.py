@@ -12,8 +12,9 @@ suffix sort -> BWT assembly) over one text.
   value      bases/s with the text already resident in HBM (pfb_run_resident), all ranks summed
   e2e        bases/s through the C ABI with HOST buffers: H2D of the record bytes from pinned
              memory and D2H of the .bwt image inside the timed region
-  roofline   dominant stage (dictionary suffix sort): algorithmic bytes D*(1+U)
-             divided by its CUDA-event time, against MEASURED_PEAKS.json hbm_gbs
+  roofline   dominant kernel k_radix_pass (one launch per 8-bit digit of the dictionary suffix sort):
+             algorithmic bytes D*(1+U) per launch divided by the average CUDA-event time
+             of a launch, against MEASURED_PEAKS.json hbm_gbs; moved_gbs = the 24 B/pair a pass really moves
   cpu_baseline  unmodified reference binary (oracle/_ref/pfbwt-f) on a bounded sample, 1 core
 
 --impl reference times the reference's own CPU implementation (oracle/_ref/pfbwt-f) on a bounded
@@ -119,7 +120,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--bases", type=int, default=1_000_000_000)
-    ap.add_argument("--ref-sample", type=int, default=12_000_000)
+    ap.add_argument("--ref-sample", type=int, default=40_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling aid: skip the host-buffer leg")
     args = ap.parse_args()
@@ -187,11 +188,13 @@ def main():
     barrier()
     t0 = time.perf_counter()
     stage_acc = {}
+    dev_ms = 0.0
     for _ in range(args.steps):
         ctx.run_resident(False, False)
         st = ctx.stats()
+        dev_ms += st["run_ms"]                      # CUDA events on the library's own stream
         for k, v in st.items():
-            if k.endswith("_ms"):
+            if k.endswith("_ms") and k not in ("run_ms", "radix_pass_ms"):
                 stage_acc[k] = stage_acc.get(k, 0.0) + v
     barrier()
     t_res = time.perf_counter() - t0
@@ -224,23 +227,31 @@ def main():
     sampler.join()
 
     # max over ranks
+    t_dev = dev_ms * 1e-3
     if world > 1:
-        t = torch.tensor([t_res, t_e2e], dtype=torch.float64, device="cuda")
+        t = torch.tensor([t_res, t_e2e, t_dev], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        t_res, t_e2e = float(t[0]), float(t[1])
+        t_res, t_e2e, t_dev = float(t[0]), float(t[1]), float(t[2])
 
     if rank == 0:
         peak, peak_kind = hbm_peak()
         stage_ms = {k: v / args.steps for k, v in stage_acc.items()}
-        dom = max(stage_ms, key=stage_ms.get)
+        # dominant kernel: k_radix_pass (5 launches of the dictionary suffix sort per step).  Algorithmic
+        # bytes per launch = SURVEY 8(d) per-unit figure of the dictionary suffix sort (1+U bytes per
+        # suffix) x the D suffixes one launch processes; duration = CUDA events around every launch.
         U = 4
-        alg_bytes = {  # SURVEY.md 8(d) per-stage floors
-            "dict_sort_ms": D * (1 + U),
-            "emit_ms": D * (1 + U) + (sz.n_phrases + 1) * (2 * U + 1) + (sz.n + 1),
-            "groups_ms": D * (1 + U),
-            "trigger_ms": sz.n + sz.n_phrases * (5 + U),
-        }.get(dom, sz.n)
-        achieved = alg_bytes / (stage_ms[dom] * 1e-3) / 1e9
+        npass = st1["radix_passes"] - launches0["radix_passes"]
+        pass_ms = (st1["radix_pass_ms"] - launches0["radix_pass_ms"]) / max(1, npass)
+        pairs = (st1["radix_pairs"] - launches0["radix_pairs"]) / max(1, npass)
+        alg_bytes = pairs * (1 + U)
+        achieved = alg_bytes / (pass_ms * 1e-3) / 1e9 if pass_ms else 0.0
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "radix_pass_traffic.json")   # dram bytes per launch from the committed ncu --set full capture
+        if os.path.exists(tp):
+            try:
+                traffic = json.load(open(tp))["dram_bytes_per_launch"]
+            except Exception:
+                traffic = None
         cpu = None
         if not args.no_cpu_baseline:
             sample_n = min(args.ref_sample, n)
@@ -249,8 +260,9 @@ def main():
                    "sample": f"first {sample_n} bases of rank 0's text, whole pfbwt-f -w {W} -p {PMOD} run incl. file I/O ({dt:.1f} s)"}
         line = {
             "metric": "input bases/sec end-to-end fasta->.bwt",
-            "value": world * n * args.steps / t_res, "unit": "bases/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 * t_res / args.steps, "higher_is_better": True,
+            "value": world * n * args.steps / t_dev, "unit": "bases/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * t_dev / args.steps, "wall_ms_per_step": 1e3 * t_res / args.steps,
+            "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8/u32/u64 integer", "data": "synthetic",
             "config": {"workload": workload, "n": int(sz.n), "phrases": int(sz.n_phrases), "dict_words": int(sz.n_words),
                        "dict_bytes": int(D), "r": int(sz.r), "l2": "inputs larger than L2 (text 1 GB, dictionary 1.1 GB per step)",
@@ -258,9 +270,12 @@ def main():
             "e2e": {"value": world * n * args.steps / t_e2e, "unit": "bases/s", "h2d_bytes_per_step": int(n),
                     "d2h_bytes_per_step": int(n + W + 1), "ms_per_step": 1e3 * t_e2e / args.steps},
             "gpu_launches": int(launches), "gpu_launches_library_cub": int(launches_lib),
-            "roofline": {"bound": "hbm", "kernel": dom.replace("_ms", ""), "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_kind,
-                         "algorithmic_bytes": int(alg_bytes), "ms": stage_ms[dom]},
+            "roofline": {"bound": "hbm", "kernel": "k_radix_pass (dictionary suffix sort, one 8-bit digit per launch)",
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                         "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs, burst copy)", "algorithmic_bytes": int(alg_bytes),
+                         "ms": pass_ms, "launches_timed": int(npass),
+                         "moved_bytes": int(pairs * 24), "moved_gbs": pairs * 24 / (pass_ms * 1e-3) / 1e9 if pass_ms else 0.0,
+                         "share_of_step": pass_ms * npass / args.steps / (1e3 * t_dev / args.steps) if t_dev else None},
             "stages_ms": stage_ms,
             "clocks": sampler.summary(),
             "dev_bytes_peak": int(st1["dev_bytes_peak"]),

@@ -66,6 +66,9 @@ typedef struct {
     uint64_t launches_own;  /* kernels written in this repository launched so far in this process */
     uint64_t launches_lib;  /* library (CUB) kernels launched so far                              */
     uint64_t dev_bytes_peak;
+    /* k_radix_pass launches over >= 2^24 pairs so far in this process: summed CUDA-event time, count, pairs moved */
+    double radix_pass_ms; uint64_t radix_passes, radix_pairs;
+    float run_ms;           /* device time of the last pfb_run_resident (CUDA events on the pipeline stream) */
 } pfb_stats;
 
 /* ---- lifetime ------------------------------------------------------------ */

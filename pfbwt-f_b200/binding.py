@@ -35,7 +35,8 @@ class Stats(C.Structure):
                 ["normalise_ms", "trigger_ms", "compact_ms", "fingerprint_ms", "dedup_ms", "phrase_sort_ms",
                  "dict_build_ms", "parse_sa_ms", "parse_bwt_ms", "dict_sort_ms", "groups_ms", "emit_ms", "runs_ms"]] + \
                [(k, C.c_uint32) for k in ["dedup_attempts", "phrase_sort_rounds", "parse_sa_rounds", "dict_sort_rounds"]] + \
-               [("launches_own", C.c_uint64), ("launches_lib", C.c_uint64), ("dev_bytes_peak", C.c_uint64)]
+               [("launches_own", C.c_uint64), ("launches_lib", C.c_uint64), ("dev_bytes_peak", C.c_uint64),
+                ("radix_pass_ms", C.c_double), ("radix_passes", C.c_uint64), ("radix_pairs", C.c_uint64), ("run_ms", C.c_float)]
 
 
 _lib = None

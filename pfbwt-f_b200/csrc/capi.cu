@@ -178,6 +178,9 @@ int pfb_get_stats(const pfb_ctx *c, pfb_stats *s) {
     s->parse_sa_rounds = t.parse_sa_rounds; s->dict_sort_rounds = t.dict_sort_rounds;
     s->launches_own = pfb::launch_stats().own; s->launches_lib = pfb::launch_stats().lib;
     s->dev_bytes_peak = pfb::dev_bytes_peak();
+    const_cast<pfb_ctx *>(c)->eng.ws.sc.rw.collect();
+    s->radix_pass_ms = pfb::launch_stats().radix_pass_ms; s->radix_passes = pfb::launch_stats().radix_passes;
+    s->radix_pairs = pfb::launch_stats().radix_pairs; s->run_ms = c->eng.run_ms;
     return PFB_OK;
 }
 
@@ -207,11 +210,17 @@ int pfb_upload_text(pfb_ctx *c) { CTX_GUARD(c); return c->eng.upload_text(); }
 int pfb_run_resident(pfb_ctx *c, int sa, int rssa) {
     CTX_GUARD(c);
     if (!c->eng.text_ready) return c->eng.fail(PFB_ERR_ARG, "no text resident on the device (call pfb_upload_text)");
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    cudaEventRecord(e0, c->eng.ws.st);
     int rc = c->eng.parse_device();
-    if (rc) return rc;
-    rc = c->eng.do_parse_bwt();
-    if (rc) return rc;
-    return c->eng.build(sa != 0, rssa != 0);
+    if (!rc) rc = c->eng.do_parse_bwt();
+    if (!rc) rc = c->eng.build(sa != 0, rssa != 0);
+    cudaEventRecord(e1, c->eng.ws.st);
+    cudaEventSynchronize(e1);
+    cudaEventElapsedTime(&c->eng.run_ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return rc;
 }
 int pfb_release_text(pfb_ctx *c) { CTX_GUARD(c); c->eng.release_text(); return PFB_OK; }
 int pfb_clear(pfb_ctx *c) { CTX_GUARD(c); c->eng.clear(); return PFB_OK; }

@@ -27,6 +27,7 @@ struct Engine {
     StageTimes tm;
     std::string err;
     int last_rc = 0;
+    float run_ms = 0;
 
     HostBytes raw;                   // record bytes + A^w padding, as read from FASTA / caller buffers
     std::vector<Segment> segs;

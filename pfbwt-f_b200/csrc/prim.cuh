@@ -67,6 +67,9 @@ struct Error : std::runtime_error {
 struct LaunchStats {
     uint64_t own = 0;   // kernels written in this repo
     uint64_t lib = 0;   // CUB kernels (library code)
+    // radix passes over >= 2^24 pairs, timed with CUDA events on the launching stream
+    double radix_pass_ms = 0; uint64_t radix_passes = 0, radix_pairs = 0;
+    float run_ms = 0;   // last pfb_run_resident, events on the pipeline stream
 };
 inline LaunchStats &launch_stats() {
     static LaunchStats s;

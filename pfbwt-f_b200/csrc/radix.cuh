@@ -216,6 +216,23 @@ __global__ void __launch_bounds__(C::NT, C::MINB) k_radix_pass(RadixPassArgs a) 
 struct RadixWork {                 // reusable scratch of the sort (look-back array, histograms, tile counters)
     DevBuf<unsigned long long> lookback, hist;
     DevBuf<unsigned> counters;
+    struct Timed { cudaEvent_t a, b; u64 n; };
+    std::vector<Timed> pending;        // big passes whose events have not been read yet
+    std::vector<cudaEvent_t> pool;
+    cudaEvent_t get_event() {
+        if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+        cudaEvent_t e; cudaEventCreate(&e); return e;
+    }
+    void collect() {                   // call when the stream is idle
+        for (auto &t : pending) {
+            float ms = 0;
+            if (cudaEventSynchronize(t.b) == cudaSuccess && cudaEventElapsedTime(&ms, t.a, t.b) == cudaSuccess) {
+                launch_stats().radix_pass_ms += ms; launch_stats().radix_passes++; launch_stats().radix_pairs += t.n;
+            }
+            pool.push_back(t.a); pool.push_back(t.b);
+        }
+        pending.clear();
+    }
 };
 
 // Stable sort of n pairs on key bits [begin_bit, end_bit).  Result is left in keys_a/vals_a (buffers
@@ -262,8 +279,12 @@ inline void radix_sort_pairs(DevBuf<u64> &keys_a, DevBuf<u64> &keys_b, DevBuf<u3
         a.lookback = (unsigned long long *)rw.lookback.get();
         a.tile_counter = rw.counters.get() + p;
         a.tag = (unsigned)(2 * p + 1);
+        const bool timed = n >= (1ull << 24);
+        RadixWork::Timed tv;
+        if (timed) { tv.a = rw.get_event(); tv.b = rw.get_event(); tv.n = n; cudaEventRecord(tv.a, st); }
         if (p == 0 && iota_vals) k_radix_pass<true, C><<<(unsigned)ntiles, C::NT, C::SMEM, st>>>(a);
         else k_radix_pass<false, C><<<(unsigned)ntiles, C::NT, C::SMEM, st>>>(a);
+        if (timed) { cudaEventRecord(tv.b, st); rw.pending.push_back(tv); }
         PFB_CUDA_CHECK(cudaGetLastError());
         launch_stats().own++;
         keys_a.swap(keys_b);
