@@ -10,8 +10,8 @@ BIN    := bin
 
 all: $(LIB) $(BIN)/pfbwt-f $(BIN)/pfbwt-f64 $(BIN)/merge_pfp emu
 
-$(LIB): $(CSRC)/capi.cu $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/build.cuh $(CSRC)/dictkeys.cuh $(CSRC)/emit.cuh $(CSRC)/radix.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp include/pfbwt_b200.h
-	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/capi.cu -lz -lcudart
+$(LIB): $(CSRC)/capi.cu $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/build.cuh $(CSRC)/dictkeys.cuh $(CSRC)/emit.cuh $(CSRC)/radix.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp $(CSRC)/comm.hpp $(CSRC)/shard.inl include/pfbwt_b200.h
+	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/capi.cu -lz -lcudart -ldl
 
 $(BIN)/pfbwt-f: pfbwt-f_b200/src/pfbwt-f.cpp $(LIB)
 	mkdir -p $(BIN)
@@ -24,14 +24,16 @@ $(BIN)/merge_pfp: pfbwt-f_b200/src/merge_pfp.cpp $(LIB)
 	$(CXX) -std=c++17 -O2 -I include -o $@ $< -Lpfbwt-f_b200 -lpfbwt_b200 -Wl,-rpath,'$$ORIGIN/../pfbwt-f_b200'
 
 # developer logic check (tests only; see tests/emu/emu_main.cpp)
-emu: tests/emu/pfb_emu
-tests/emu/pfb_emu: tests/emu/emu_main.cpp $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/build.cuh $(CSRC)/dictkeys.cuh $(CSRC)/emit.cuh $(CSRC)/radix.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp
+emu: tests/emu/pfb_emu tests/emu/libpfb_emu.so
+tests/emu/libpfb_emu.so: tests/emu/pfb_emu
+	$(CXX) -std=c++17 -O2 -Wall -Wno-unused -shared -fPIC -I $(CSRC) -o $@ tests/emu/emu_main.cpp -lz
+tests/emu/pfb_emu: tests/emu/emu_main.cpp $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/build.cuh $(CSRC)/dictkeys.cuh $(CSRC)/emit.cuh $(CSRC)/radix.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp $(CSRC)/comm.hpp $(CSRC)/shard.inl
 	$(CXX) -std=c++17 -O2 -Wall -Wno-unused -I $(CSRC) -o $@ $< -lz
 
 oracle:
 	$(MAKE) -C oracle all
 
 clean:
-	rm -rf $(LIB) $(BIN) tests/emu/pfb_emu
+	rm -rf $(LIB) $(BIN) tests/emu/pfb_emu tests/emu/libpfb_emu.so
 
 .PHONY: all emu oracle clean

@@ -69,7 +69,19 @@ typedef struct {
     /* k_radix_pass launches over >= 2^24 pairs so far in this process: summed CUDA-event time, count, pairs moved */
     double radix_pass_ms; uint64_t radix_passes, radix_pairs;
     float run_ms;           /* device time of the last pfb_run_resident (CUDA events on the pipeline stream) */
+    /* multi-GPU job: time spent in exchanges (incl. waiting for peers) / in the dictionary merge, bytes received */
+    float shard_exchange_ms, shard_merge_ms;
+    uint64_t shard_bytes_moved;
 } pfb_stats;
+
+/* which part of the job's outputs this context holds.  Without a communicator: everything. */
+typedef struct {
+    int rank, world;
+    uint64_t text_start;            /* offset of this rank's records in S                     */
+    uint64_t bwt_off, bwt_len;      /* BWT (and SA) positions [bwt_off, bwt_off + bwt_len)    */
+    uint64_t ssa_off, ssa_cnt;      /* .ssa pairs                                             */
+    uint64_t esa_off, esa_cnt;      /* .esa pairs                                             */
+} pfb_shard_info;
 
 /* ---- lifetime ------------------------------------------------------------ */
 /* bits = 32 replaces pfbwt-f, 64 replaces pfbwt-f64 / merge_pfp (gsa/gsacak.h:40-58). */
@@ -116,12 +128,28 @@ int pfb_copy_sai(pfb_ctx *, void *out /* n_phrases * bits/8 */);
 int pfb_copy_bwlast(pfb_ctx *, uint8_t *out /* n_phrases+1 */);
 int pfb_copy_ilist(pfb_ctx *, void *out /* (n_phrases+1) * bits/8 */);
 int pfb_copy_bwsai(pfb_ctx *, void *out /* (n_phrases+1) * bits/8 */);
-int pfb_copy_bwt(pfb_ctx *, uint8_t *out /* n+1 */);
+int pfb_copy_bwt(pfb_ctx *, uint8_t *out /* n+1; a rank of a multi-GPU job: bwt_len */);
 int pfb_copy_sa(pfb_ctx *, void *out /* (n+1) * bits/8 */);
 int pfb_copy_ssa(pfb_ctx *, void *out /* 2*r * bits/8 */);
 int pfb_copy_esa(pfb_ctx *, void *out /* 2*r * bits/8 */);
 /* doc table of --print-docs (include/pfbwt_io.hpp:224-231): number of docs; start offsets copied when out != NULL */
 int64_t pfb_get_docs(pfb_ctx *, uint64_t *starts_out);
+
+/* ---- one job over several GPUs: one process (context) per GPU --------------------------------
+ * Generalises merge_pfp (src/merge_pfp.cpp:97-170: per-file parsers merged with operator+=,
+ * include/pfparser.hpp:194-263) to a single job: rank r of `world` adds the records of the r-th
+ * contiguous piece of the record list (rank order = text order, cuts at record boundaries), then
+ * every rank calls pfb_finalize / pfb_parse_bwt / pfb_build_bwt / pfb_write_bwt at the same time
+ * (collective calls).  After pfb_finalize every rank holds the whole parse (getters as before);
+ * after pfb_build_bwt a rank holds one contiguous slice of .bwt/.sa/.ssa/.esa (pfb_get_shard_info,
+ * the pfb_copy_* getters copy the slice, pfb_write_bwt writes it at its offset of the common file).
+ * Transport: NCCL over NVLink/NVSwitch (the id comes from rank 0 via the launcher), or a
+ * caller-supplied host all-gather (tests: torch.distributed/gloo). */
+typedef int (*pfb_allgatherv_fn)(void *user, const void *send, void *recv, const uint64_t *counts, int world);
+int pfb_nccl_unique_id(void *out128);
+int pfb_shard_init_nccl(pfb_ctx *, int rank, int world, const void *unique_id128);
+int pfb_shard_init_host(pfb_ctx *, int rank, int world, pfb_allgatherv_fn fn, void *user);
+int pfb_get_shard_info(const pfb_ctx *, pfb_shard_info *);
 
 /* ---- measurement hooks (bench.py) -------------------------------------------------- */
 /* stage the pending records into HBM (H2D + normalise) without parsing */

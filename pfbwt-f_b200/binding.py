@@ -16,6 +16,7 @@ EXPORTS = [
     "pfb_copy_parse", "pfb_copy_last", "pfb_copy_sai", "pfb_copy_bwlast", "pfb_copy_ilist", "pfb_copy_bwsai",
     "pfb_copy_bwt", "pfb_copy_sa", "pfb_copy_ssa", "pfb_copy_esa", "pfb_get_docs", "pfb_upload_text",
     "pfb_run_resident", "pfb_release_text", "pfb_clear",
+    "pfb_nccl_unique_id", "pfb_shard_init_nccl", "pfb_shard_init_host", "pfb_get_shard_info",
 ]
 
 
@@ -36,7 +37,17 @@ class Stats(C.Structure):
                  "dict_build_ms", "parse_sa_ms", "parse_bwt_ms", "dict_sort_ms", "groups_ms", "emit_ms", "runs_ms"]] + \
                [(k, C.c_uint32) for k in ["dedup_attempts", "phrase_sort_rounds", "parse_sa_rounds", "dict_sort_rounds"]] + \
                [("launches_own", C.c_uint64), ("launches_lib", C.c_uint64), ("dev_bytes_peak", C.c_uint64),
-                ("radix_pass_ms", C.c_double), ("radix_passes", C.c_uint64), ("radix_pairs", C.c_uint64), ("run_ms", C.c_float)]
+                ("radix_pass_ms", C.c_double), ("radix_passes", C.c_uint64), ("radix_pairs", C.c_uint64), ("run_ms", C.c_float),
+                ("shard_exchange_ms", C.c_float), ("shard_merge_ms", C.c_float), ("shard_bytes_moved", C.c_uint64)]
+
+
+class ShardInfo(C.Structure):
+    _fields_ = [("rank", C.c_int), ("world", C.c_int)] + \
+               [(k, C.c_uint64) for k in ["text_start", "bwt_off", "bwt_len", "ssa_off", "ssa_cnt", "esa_off", "esa_cnt"]]
+
+
+# host all-gather-v callback of pfb_shard_init_host (include/pfbwt_b200.h)
+ALLGATHERV = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64), C.c_int)
 
 
 _lib = None
@@ -74,8 +85,21 @@ def load():
         getattr(lib, "pfb_copy_" + f).argtypes = [vp, vp]
     lib.pfb_get_docs.restype = C.c_int64
     lib.pfb_get_docs.argtypes = [vp, vp]
+    lib.pfb_nccl_unique_id.argtypes = [vp]
+    lib.pfb_shard_init_nccl.argtypes = [vp, C.c_int, C.c_int, vp]
+    lib.pfb_shard_init_host.argtypes = [vp, C.c_int, C.c_int, ALLGATHERV, vp]
+    lib.pfb_get_shard_info.argtypes = [vp, C.POINTER(ShardInfo)]
     _lib = lib
     return lib
+
+
+def nccl_unique_id():
+    """128-byte NCCL id (call on rank 0, hand to the other ranks)"""
+    lib = load()
+    buf = C.create_string_buffer(128)
+    if lib.pfb_nccl_unique_id(C.cast(buf, C.c_void_p)) != 0:
+        raise RuntimeError("ncclGetUniqueId failed: " + lib.pfb_create_error().decode())
+    return buf.raw
 
 
 class PfbError(RuntimeError):
@@ -112,6 +136,21 @@ class Context:
             self.close()
         except Exception:
             pass
+
+    # one job over several GPUs: attach this context to a communicator (collective calls afterwards)
+    def shard_init_nccl(self, rank, world, unique_id):
+        """unique_id: 128 bytes from nccl_unique_id() on rank 0, broadcast by the launcher"""
+        buf = C.create_string_buffer(bytes(unique_id), 128)
+        self._ck(self.lib.pfb_shard_init_nccl(self.h, rank, world, C.cast(buf, C.c_void_p)))
+
+    def shard_init_host(self, rank, world, callback):
+        self._cb = callback       # keep the ctypes thunk alive
+        self._ck(self.lib.pfb_shard_init_host(self.h, rank, world, callback, None))
+
+    def shard_info(self):
+        s = ShardInfo()
+        self._ck(self.lib.pfb_get_shard_info(self.h, C.byref(s)))
+        return s
 
     # parse step
     def add_fasta(self, path):
@@ -182,10 +221,11 @@ class Context:
     def bwlast(self): return self._copy("bwlast", self.sizes().n_phrases + 1, np.uint8)
     def ilist(self): return self._copy("ilist", self.sizes().n_phrases + 1, self.utype)
     def bwsai(self): return self._copy("bwsai", self.sizes().n_phrases + 1, self.utype)
-    def bwt(self, out=None): return self._copy("bwt", self.sizes().n + 1, np.uint8, out)
-    def sa(self, out=None): return self._copy("sa", self.sizes().n + 1, self.utype, out)
-    def ssa(self): return self._copy("ssa", 2 * self.sizes().r, self.utype)
-    def esa(self): return self._copy("esa", 2 * self.sizes().r, self.utype)
+    # a rank of a multi-GPU job gets its slice (shard_info()); otherwise the slice is everything
+    def bwt(self, out=None): return self._copy("bwt", self.shard_info().bwt_len, np.uint8, out)
+    def sa(self, out=None): return self._copy("sa", self.shard_info().bwt_len, self.utype, out)
+    def ssa(self): return self._copy("ssa", 2 * self.shard_info().ssa_cnt, self.utype)
+    def esa(self): return self._copy("esa", 2 * self.shard_info().esa_cnt, self.utype)
 
     def docs(self):
         n = self.lib.pfb_get_docs(self.h, None)

@@ -48,29 +48,69 @@ inline u64 compact_indices(const u8 *flags, u64 n, DevBuf<u32> &scratch_idx, Dev
 // ---------------------------------------------------------------------------
 //     cnt[] (occurrences per suffix) and the valid/full bits of meta come out of the keys' upper
 //     bits; *reclassify is set when they have to be recomputed by lookup (prefix doubling ran).
+//     Multi-GPU (sh != nullptr): the rank sorts only the valid suffixes whose code falls in its
+//     range of the key space (splitters from a weighted histogram of the leading code bits, computed
+//     identically on every rank from the replicated dictionary); *n_sorted = how many those are.
+struct ShardSpec { int rank = 0, world = 1; };
+
 inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, DevBuf<u8> &meta, DevBuf<u32> &cnt, const WordLookup &wl,
-                              bool *reclassify, Workspace &ws, StageTimes &tm, Timer &timer, std::string &err) {
+                              bool *reclassify, Workspace &ws, StageTimes &tm, Timer &timer, std::string &err,
+                              const ShardSpec *sh = nullptr, u64 *n_sorted = nullptr) {
     pfbStream_t st = ws.st;
     const u64 D = pp.dsize;
     const u8 *dict = pp.dict.get();
-    sa.alloc(padded(D)); meta.alloc(padded(D) + 64); cnt.alloc(padded(D));
-    dev_memset(meta.get(), M_HEAD, padded(D) + 64, st);
     *reclassify = false;
     int L = 1;
     while (L < KEY_MAX_SYMS && (1ull << (2 * L)) < 128ull * D) ++L;     // ties become rare once 4^L >> D
     if (const char *e = getenv("PFB_KEY_SYMS")) { L = atoi(e); if (L < 1) L = 1; if (L > KEY_MAX_SYMS) L = KEY_MAX_SYMS; }   // test knob
     DevBuf<u32> apos, adep;
     u64 m;
+    u64 N = D;                       // entries in the sorted array
     {
-        DevBuf<u64> key(D), key_b(D);
-        DevBuf<u32> val_b(padded(D));
+        DevBuf<u64> key, key_b;
+        DevBuf<u32> val_b;
         const KeyExtra kx = key_extra_for(L);
-        k_suffix_keys(dict, D, L, key.get(), wl, pp.occ.get(), w, kx, st);
-        timer.lap("K6 keys");
-        sort_pairs(key, key_b, sa, val_b, D, KEY_CODE_SHIFT, KEY_CODE_SHIFT + enum_bits(L), ws.sc, st, /*iota_vals=*/true);
+        if (!sh) {
+            key.alloc(D); key_b.alloc(D); val_b.alloc(padded(D)); sa.alloc(padded(D));
+            k_suffix_keys(dict, D, L, key.get(), wl, pp.occ.get(), w, kx, st);
+            timer.lap("K6 keys");
+            sort_pairs(key, key_b, sa, val_b, D, KEY_CODE_SHIFT, KEY_CODE_SHIFT + enum_bits(L), ws.sc, st, /*iota_vals=*/true);
+        } else {
+            const int cb = enum_bits(L), hb = cb < 14 ? cb : 14, hshift = cb - hb;
+            const u64 nbins = 1ull << hb;
+            std::vector<u64> h(nbins);
+            {
+                DevBuf<u64> hist(nbins);
+                dev_memset(hist.get(), 0, nbins * 8, st);
+                k_suffix_key_hist(dict, D, L, wl, pp.occ.get(), w, kx, hist.get(), hshift, st);
+                d2h(h.data(), hist.get(), nbins * 8, st);
+                stream_sync(st);
+            }
+            u64 total = 0;
+            for (u64 b = 0; b < nbins; ++b) total += h[b];
+            auto bound = [&](int r) -> u64 {      // first bin of rank r: smallest b with weight(bins < b) >= total*r/world
+                if (r <= 0) return 0;
+                if (r >= sh->world) return nbins;
+                const u64 want = (u64)(((unsigned __int128)total * (unsigned)r + (unsigned)sh->world - 1) / (unsigned)sh->world);
+                u64 cum = 0, b = 0;
+                while (b < nbins && cum < want) cum += h[b++];
+                return b;
+            };
+            const u64 lo = bound(sh->rank) << hshift;
+            const u64 hi = sh->rank + 1 >= sh->world ? ~0ull : bound(sh->rank + 1) << hshift;
+            timer.lap("K6 splitter histogram");
+            N = k_suffix_keys_select(dict, D, L, wl, pp.occ.get(), w, kx, lo, hi, key, sa, padded, ws);
+            timer.lap("K6 keys (selected)");
+            key_b.alloc(N); val_b.alloc(padded(N));
+            sort_pairs(key, key_b, sa, val_b, N, KEY_CODE_SHIFT, KEY_CODE_SHIFT + enum_bits(L), ws.sc, st, /*iota_vals=*/false);
+        }
+        if (n_sorted) *n_sorted = N;
+        meta.alloc(padded(N) + 64); cnt.alloc(padded(N));
+        dev_memset(meta.get(), M_HEAD, padded(N) + 64, st);
+        if (N == 0) { tm.dict_sort_rounds = 0; return PFB_OK; }
         timer.lap("K6 radix sort");
         FlagsArgs fa;
-        fa.key = key.get(); fa.sa = sa.get(); fa.D = D; fa.meta = meta.get(); fa.cnt = cnt.get(); fa.tilecnt = nullptr;
+        fa.key = key.get(); fa.sa = sa.get(); fa.D = N; fa.meta = meta.get(); fa.cnt = cnt.get(); fa.tilecnt = nullptr;
         fa.kx = kx; fa.wl = wl; fa.w = (u64)w;
         m = sorted_flags_and_open_list(fa, apos, ws);
         if (m) {
@@ -89,7 +129,10 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
     if (const char *e = getenv("PFB_EXT_ROUNDS")) { max_ext_rounds = (u32)atoi(e); knob = true; }   // test knob: 0 = doubling only
     const u64 small_set = D / 2048 > 4096 ? D / 2048 : 4096;
     u8 *mt = meta.get();
-    while (m && (rounds < max_ext_rounds || (!knob && m <= small_set && rounds < max_small_rounds))) {
+    // a rank that holds only its key range cannot switch to prefix doubling (rank[] of all suffixes):
+    // it keeps extending; phrases of ordinary length close within a few dozen rounds
+    const u32 shard_rounds = 1u << 16;
+    while (m && (rounds < max_ext_rounds || (!knob && m <= small_set && rounds < max_small_rounds) || (sh && rounds < shard_rounds))) {
         // dense group ids inside the active list (whole groups are active, so the
         // first listed member of a group is its head)
         DevBuf<u8> ah(m);
@@ -151,6 +194,7 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
         ++rounds;
         timer.lap("K6 extension round");
     }
+    if (m && sh) { err = "dictionary repeats too long for the range-partitioned suffix sort (use the single-GPU path)"; return PFB_ERR_LIMIT; }
     if (m) {
         // long repeats: hand the partially sorted array to prefix doubling.  Every open group is
         // sorted on at least h = min depth symbols, which is all the doubling step needs.
@@ -196,7 +240,7 @@ PFB_HD inline void store_sa(u8 *sa_out, u64 x, u64 v) {
 // ===========================================================================
 template <int U>
 inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, bool want_rssa, DeviceBwt &out, Workspace &ws,
-                       StageTimes &tm, std::string &err) {
+                       StageTimes &tm, std::string &err, Comm *comm) {
     pfbStream_t st = ws.st;
     const u64 D = pp.dsize, Dw = pp.Dw, n = pp.n, P = pp.P;
     const u64 w = (u64)prm.w;
@@ -231,47 +275,60 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
     DevBuf<u8> meta;
     DevBuf<u32> cnt, ibase, slen;
     bool reclassify = false;
-    int rc = sort_dict_suffixes(pp, (int)w, sa, meta, cnt, wl, &reclassify, ws, tm, timer, err);
+    ShardSpec spec;
+    if (comm) { spec.rank = comm->rank; spec.world = comm->world; }
+    u64 N = D;                          // sorted entries held by this rank (all D without a communicator)
+    int rc = sort_dict_suffixes(pp, (int)w, sa, meta, cnt, wl, &reclassify, ws, tm, timer, err, comm ? &spec : nullptr, &N);
     if (rc) return rc;
     tm.dict_sort = timer.stop();
 
     // K7 tile offsets, hard groups ------------------------------------------------------
     // Without SA output everything the emission needs per suffix came with the sort (meta, cnt);
     // with SA output (or after prefix doubling) a lookup pass adds ilist base and suffix length.
-    const u64 nt = tiles_of(D);
+    const u64 nt = tiles_of(N);
     DevBuf<u64> tilesum(nt + 1), tilebase(nt + 1);
-    if (any_sa) { ibase.alloc(padded(D)); slen.alloc(padded(D)); }
-    if (any_sa || reclassify) {
+    if (any_sa) { ibase.alloc(padded(N)); slen.alloc(padded(N)); }
+    if (N == 0) {
+    } else if (any_sa || reclassify) {
         ClassifyArgs ca;
-        ca.sa = sa.get(); ca.meta = meta.get(); ca.wl = wl; ca.D = D; ca.w = w;
+        ca.sa = sa.get(); ca.meta = meta.get(); ca.wl = wl; ca.D = N; ca.w = w;
         ca.cnt = cnt.get(); ca.tilesum = tilesum.get(); ca.ibase = ibase.get(); ca.sl = slen.get();
         k_classify(ca, any_sa, st);
         timer.lap("K7 classify (word lookup)");
     } else {
-        k_tile_sums(cnt.get(), D, tilesum.get(), st);
+        k_tile_sums(cnt.get(), N, tilesum.get(), st);
         timer.lap("K7 tile sums");
     }
     dev_memset(tilesum.get() + nt, 0, 8, st);
     exclusive_sum<u64, u64>(tilesum.get(), tilebase.get(), nt + 1, ws.sc, st);
-    {
-        u64 total = read_scalar(tilebase.get() + nt, st);
-        if (total != n + 1) { err = "internal: emitted positions " + std::to_string(total) + " != n+1 = " + std::to_string(n + 1); return PFB_ERR_INTERNAL; }
+    const u64 total = read_scalar(tilebase.get() + nt, st);     // BWT positions emitted by this rank
+    u64 slice_off = 0;
+    std::vector<u64> totals(1, total);
+    if (comm) {
+        // the ranks' key ranges are consecutive, so their outputs are consecutive slices of the BWT
+        totals = comm->gather_u64(&total, 1, st);
+        for (int r = 0; r < comm->rank; ++r) slice_off += totals[(size_t)r];
     }
-    const u64 nhg_cap = k_group_classes(meta.get(), D, any_sa, ws);   // number of hard groups (sizes the work list)
+    {
+        u64 sum = 0;
+        for (u64 t_ : totals) sum += t_;
+        if (sum != n + 1) { err = "internal: emitted positions " + std::to_string(sum) + " != n+1 = " + std::to_string(n + 1); return PFB_ERR_INTERNAL; }
+    }
+    const u64 nhg_cap = N ? k_group_classes(meta.get(), N, any_sa, ws) : 0;   // number of hard groups (sizes the work list)
     timer.lap("K7 group classes");
     tm.groups = timer.stop();
 
     // K8 emission ---------------------------------------------------------------------
-    out.n = n;
-    out.bwt.alloc(n + 1 + 16);
-    if (any_sa) out.sa.alloc((n + 1) * (u64)U + 16);
+    out.n = n; out.off = slice_off; out.len = total;
+    out.bwt.alloc(total + 16);
+    if (any_sa) out.sa.alloc(total * (u64)U + 16);
     DevBuf<u32> hard_t(nhg_cap + 1), ctr32(2);
     DevBuf<u64> hard_x(nhg_cap + 1), ctr64(1);
     dev_memset(ctr32.get(), 0, 8, st);
     dev_memset(ctr64.get(), 0, 8, st);
     EmitArgs ea;
     ea.meta = meta.get(); ea.cnt = cnt.get(); ea.sa = sa.get(); ea.ibase = ibase.get(); ea.sl = slen.get();
-    ea.wl = wl; ea.tilebase = tilebase.get(); ea.D = D;
+    ea.wl = wl; ea.tilebase = tilebase.get(); ea.D = N;
     ea.ilist = pp.ilist.get(); ea.bwlast = pp.bwlast.get(); ea.bwsai = pp.bwsai.get();
     ea.bwt = out.bwt.get(); ea.sa_out = out.sa.get();
     ea.small_lim = HARD_SMALL; ea.mid_lim = HARD_MID;
@@ -281,12 +338,14 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
     }
     ea.hard_t = hard_t.get(); ea.hard_x = hard_x.get(); ea.n_hard_groups = ctr32.get(); ea.n_hard_occ = ctr64.get();
 #ifdef PFB_EMU
-    emu_emit<U>(ea, any_sa);
+    if (N) emu_emit<U>(ea, any_sa);
 #else
-    if (any_sa) k_emit_kernel<U, true><<<(unsigned)nt, 256, 0, st>>>(ea);
-    else k_emit_kernel<U, false><<<(unsigned)nt, 256, 0, st>>>(ea);
-    PFB_CUDA_CHECK(cudaGetLastError());
-    launch_stats().own++;
+    if (N) {
+        if (any_sa) k_emit_kernel<U, true><<<(unsigned)nt, 256, 0, st>>>(ea);
+        else k_emit_kernel<U, false><<<(unsigned)nt, 256, 0, st>>>(ea);
+        PFB_CUDA_CHECK(cudaGetLastError());
+        launch_stats().own++;
+    }
 #endif
     timer.lap("K8 emit easy");
     const u64 nhg = read_scalar(ctr32.get(), st);
@@ -334,15 +393,60 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
         timer.lap("K8 hard big groups");
     }
     out.hard = nhard;                 // "# hard cases" of include/pfbwt.hpp:188
-    out.easy = n + 1 - nhard;
+    out.easy = total - nhard;
     u8 *bwt = out.bwt.get();
     u8 *sa_out = out.sa.get();
-    if (any_sa) launch_for(1, st, PFB_LAMBDA(u64) { store_sa<U>(sa_out, 0, n); });   // src/pfbwt-f.cpp:301
+    if (any_sa && slice_off == 0 && total) launch_for(1, st, PFB_LAMBDA(u64) { store_sa<U>(sa_out, 0, n); });   // src/pfbwt-f.cpp:301
     sa.release(); meta.release(); cnt.release(); ibase.release(); slen.release();
     tm.emit = timer.stop();
 
     // K9 run boundaries + run-length SA samples (src/pfbwt-f.cpp:304-328) -------------------
-    {
+    if (comm) {
+        // Slices meet at rank boundaries: a run start needs the byte before the slice, a run end the
+        // byte after it.  One small all-gather of (first byte, last byte) per rank supplies both.
+        u64 edge[2] = {0, 0};
+        if (total) { edge[0] = read_scalar(bwt, st); edge[1] = read_scalar(bwt + (total - 1), st); }
+        std::vector<u64> edges = comm->gather_u64(edge, 2, st);
+        u8 prevb = 0, nextb = 0;
+        bool has_next = false;
+        for (int r = comm->rank - 1; r >= 0; --r) if (totals[(size_t)r]) { prevb = (u8)edges[2 * (size_t)r + 1]; break; }
+        for (int r = comm->rank + 1; r < comm->world; ++r) if (totals[(size_t)r]) { nextb = (u8)edges[2 * (size_t)r]; has_next = true; break; }
+        DevBuf<u8> rf(total + 1), ef(total + 1);
+        u8 *rp = rf.get(); u8 *ep = ef.get();
+        launch_for(total, st, PFB_LAMBDA(u64 x) {
+            rp[x] = bwt[x] != (x ? bwt[x - 1] : prevb) ? 1 : 0;
+            ep[x] = (x + 1 < total) ? (bwt[x + 1] != bwt[x] ? 1 : 0) : ((!has_next || nextb != bwt[x]) ? 1 : 0);
+        });
+        DevBuf<u64> ridx, eidx;
+        u64 cnts[2] = {0, 0};
+        if (!want_rssa) {
+            cnts[0] = cnts[1] = total ? reduce_sum<u8, u64>(rf.get(), total, ws.sc, st) : 0;
+        } else if (total) {
+            ridx.alloc(total); eidx.alloc(total);
+            exclusive_sum<u8, u64>(rf.get(), ridx.get(), total, ws.sc, st);
+            exclusive_sum<u8, u64>(ef.get(), eidx.get(), total, ws.sc, st);
+            cnts[0] = read_scalar(ridx.get() + (total - 1), st) + read_scalar(rf.get() + (total - 1), st);
+            cnts[1] = read_scalar(eidx.get() + (total - 1), st) + read_scalar(ef.get() + (total - 1), st);
+        }
+        std::vector<u64> all = comm->gather_u64(cnts, 2, st);
+        u64 r = 0, so = 0, eo = 0;
+        for (int q = 0; q < comm->world; ++q) {
+            r += all[2 * (size_t)q];
+            if (q < comm->rank) { so += all[2 * (size_t)q]; eo += all[2 * (size_t)q + 1]; }
+        }
+        out.r = r;
+        if (want_rssa) {
+            out.ssa_off = so; out.ssa_cnt = cnts[0]; out.esa_off = eo; out.esa_cnt = cnts[1];
+            out.ssa.alloc(2 * cnts[0] * (u64)U + 16);
+            out.esa.alloc(2 * cnts[1] * (u64)U + 16);
+            u8 *ssa = out.ssa.get(); u8 *esa = out.esa.get(); const u64 *ri = ridx.get(); const u64 *ei = eidx.get();
+            launch_for(total, st, PFB_LAMBDA(u64 x) {
+                u64 v = U == 4 ? (u64)reinterpret_cast<const u32 *>(sa_out)[x] : reinterpret_cast<const u64 *>(sa_out)[x];
+                if (rp[x]) { store_sa<U>(ssa, 2 * ri[x], slice_off + x); store_sa<U>(ssa, 2 * ri[x] + 1, v); }
+                if (ep[x]) { store_sa<U>(esa, 2 * ei[x], slice_off + x); store_sa<U>(esa, 2 * ei[x] + 1, v); }
+            });
+        }
+    } else {
         DevBuf<u8> rf(n + 1);
         u8 *rp = rf.get();
         launch_for(n + 1, st, PFB_LAMBDA(u64 x) { rp[x] = bwt[x] != (x ? bwt[x - 1] : (u8)0) ? 1 : 0; });
@@ -379,6 +483,7 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
             });
         }
     }
+    if (!comm) { out.ssa_off = out.esa_off = 0; out.ssa_cnt = out.esa_cnt = want_rssa ? out.r : 0; }
     timer.lap("K9 runs");
     tm.runs = timer.stop();
     trace_log().dump("build_bwt");
@@ -386,9 +491,9 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
 }
 
 inline int build_bwt(const DeviceParse &pp, const Params &prm, bool want_sa, bool want_rssa, DeviceBwt &out, Workspace &ws,
-                     StageTimes &tm, std::string &err) {
-    return prm.bits == 64 ? build_bwt_t<8>(pp, prm, want_sa, want_rssa, out, ws, tm, err)
-                          : build_bwt_t<4>(pp, prm, want_sa, want_rssa, out, ws, tm, err);
+                     StageTimes &tm, std::string &err, Comm *comm = nullptr) {
+    return prm.bits == 64 ? build_bwt_t<8>(pp, prm, want_sa, want_rssa, out, ws, tm, err, comm)
+                          : build_bwt_t<4>(pp, prm, want_sa, want_rssa, out, ws, tm, err, comm);
 }
 
 }  // namespace pfb

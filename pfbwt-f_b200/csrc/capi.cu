@@ -91,6 +91,7 @@ void pfb_destroy(pfb_ctx *c) {
     cudaStream_t st = c->eng.ws.st;
     cudaStreamSynchronize(st);
     c->eng.clear();
+    c->eng.comm.reset();
     c->eng.ws.sc.buf.release();
     c->eng.raw.release();
     cudaStreamSynchronize(st);
@@ -181,6 +182,8 @@ int pfb_get_stats(const pfb_ctx *c, pfb_stats *s) {
     const_cast<pfb_ctx *>(c)->eng.ws.sc.rw.collect();
     s->radix_pass_ms = pfb::launch_stats().radix_pass_ms; s->radix_passes = pfb::launch_stats().radix_passes;
     s->radix_pairs = pfb::launch_stats().radix_pairs; s->run_ms = c->eng.run_ms;
+    s->shard_exchange_ms = c->eng.shard_exchange_ms; s->shard_merge_ms = c->eng.shard_merge_ms;
+    s->shard_bytes_moved = c->eng.comm ? c->eng.comm->bytes_moved : 0;
     return PFB_OK;
 }
 
@@ -192,13 +195,13 @@ int pfb_copy_sai(pfb_ctx *c, void *o) { CTX_GUARD(c); return copy_out_uint(c, c-
 int pfb_copy_bwlast(pfb_ctx *c, uint8_t *o) { CTX_GUARD(c); return copy_out(c, c->eng.parse.bwlast, c->eng.parse.P + 1, o, c->eng.parsed && c->eng.parse.has_parse_bwt, "bwlast"); }
 int pfb_copy_ilist(pfb_ctx *c, void *o) { CTX_GUARD(c); return copy_out_uint(c, c->eng.parse.ilist, c->eng.parse.P + 1, o, c->eng.parsed && c->eng.parse.has_parse_bwt, "ilist"); }
 int pfb_copy_bwsai(pfb_ctx *c, void *o) { CTX_GUARD(c); return copy_out_uint(c, c->eng.parse.bwsai, c->eng.parse.P + 1, o, c->eng.parsed && c->eng.parse.has_parse_bwt && c->eng.parse.bwsai.size(), "bwsai"); }
-int pfb_copy_bwt(pfb_ctx *c, uint8_t *o) { CTX_GUARD(c); return copy_out(c, c->eng.bwt.bwt, c->eng.bwt.n + 1, o, c->eng.built, "bwt"); }
+int pfb_copy_bwt(pfb_ctx *c, uint8_t *o) { CTX_GUARD(c); return copy_out(c, c->eng.bwt.bwt, c->eng.bwt.len, o, c->eng.built, "bwt"); }
 int pfb_copy_sa(pfb_ctx *c, void *o) {
     CTX_GUARD(c);
-    return copy_out(c, c->eng.bwt.sa, (c->eng.bwt.n + 1) * ((size_t)c->eng.prm.bits / 8), o, c->eng.built && (c->eng.built_sa || c->eng.built_rssa), "sa");
+    return copy_out(c, c->eng.bwt.sa, c->eng.bwt.len * ((size_t)c->eng.prm.bits / 8), o, c->eng.built && (c->eng.built_sa || c->eng.built_rssa), "sa");
 }
-int pfb_copy_ssa(pfb_ctx *c, void *o) { CTX_GUARD(c); return copy_out(c, c->eng.bwt.ssa, 2 * c->eng.bwt.r * ((size_t)c->eng.prm.bits / 8), o, c->eng.built && c->eng.built_rssa, "ssa"); }
-int pfb_copy_esa(pfb_ctx *c, void *o) { CTX_GUARD(c); return copy_out(c, c->eng.bwt.esa, 2 * c->eng.bwt.r * ((size_t)c->eng.prm.bits / 8), o, c->eng.built && c->eng.built_rssa, "esa"); }
+int pfb_copy_ssa(pfb_ctx *c, void *o) { CTX_GUARD(c); return copy_out(c, c->eng.bwt.ssa, 2 * c->eng.bwt.ssa_cnt * ((size_t)c->eng.prm.bits / 8), o, c->eng.built && c->eng.built_rssa, "ssa"); }
+int pfb_copy_esa(pfb_ctx *c, void *o) { CTX_GUARD(c); return copy_out(c, c->eng.bwt.esa, 2 * c->eng.bwt.esa_cnt * ((size_t)c->eng.prm.bits / 8), o, c->eng.built && c->eng.built_rssa, "esa"); }
 
 int64_t pfb_get_docs(pfb_ctx *c, uint64_t *starts_out) {
     if (!c) return PFB_ERR_ARG;
@@ -206,14 +209,60 @@ int64_t pfb_get_docs(pfb_ctx *c, uint64_t *starts_out) {
     return (int64_t)c->eng.docs.starts.size();
 }
 
-int pfb_upload_text(pfb_ctx *c) { CTX_GUARD(c); return c->eng.upload_text(); }
+int pfb_nccl_unique_id(void *out128) {
+    if (!out128) return PFB_ERR_ARG;
+    pfb::NcclApi &a = pfb::nccl_api();
+    if (!a.load()) { g_create_err = a.err; return PFB_ERR_CUDA; }
+    pfb::NcclApi::uid id;
+    if (a.GetUniqueId(&id) != 0) { g_create_err = "ncclGetUniqueId failed"; return PFB_ERR_CUDA; }
+    memcpy(out128, id.b, 128);
+    return PFB_OK;
+}
+int pfb_shard_init_nccl(pfb_ctx *c, int rank, int world, const void *uid) {
+    CTX_GUARD(c);
+    if (world < 1 || rank < 0 || rank >= world || !uid) return c->eng.fail(PFB_ERR_ARG, "bad rank / world / id");
+    try {
+        std::unique_ptr<pfb::NcclComm> nc(new pfb::NcclComm());
+        nc->init(rank, world, uid);
+        c->eng.comm = std::move(nc);
+        c->eng.invalidate();
+    } catch (const pfb::Error &e) { return c->eng.fail(e.code, e.what()); }
+    return PFB_OK;
+}
+int pfb_shard_init_host(pfb_ctx *c, int rank, int world, pfb_allgatherv_fn fn, void *user) {
+    CTX_GUARD(c);
+    if (world < 1 || rank < 0 || rank >= world || !fn) return c->eng.fail(PFB_ERR_ARG, "bad rank / world / callback");
+    std::unique_ptr<pfb::HostCallComm> hc(new pfb::HostCallComm());
+    hc->rank = rank; hc->world = world; hc->fn = fn; hc->user = user;
+    c->eng.comm = std::move(hc);
+    c->eng.invalidate();
+    return PFB_OK;
+}
+int pfb_get_shard_info(const pfb_ctx *c, pfb_shard_info *s) {
+    if (!c || !s) return PFB_ERR_ARG;
+    const pfb::Engine &e = c->eng;
+    memset(s, 0, sizeof(*s));
+    s->rank = e.comm ? e.comm->rank : 0; s->world = e.comm ? e.comm->world : 1;
+    s->text_start = e.shard_start;
+    if (e.built) {
+        s->bwt_off = e.bwt.off; s->bwt_len = e.bwt.len; s->ssa_off = e.bwt.ssa_off; s->ssa_cnt = e.bwt.ssa_cnt;
+        s->esa_off = e.bwt.esa_off; s->esa_cnt = e.bwt.esa_cnt;
+    }
+    return PFB_OK;
+}
+
+int pfb_upload_text(pfb_ctx *c) {
+    CTX_GUARD(c);
+    if (c->eng.comm) c->eng.text.tail_room = 4096;      // room for the bytes up to the next rank's first trigger
+    return c->eng.upload_text();
+}
 int pfb_run_resident(pfb_ctx *c, int sa, int rssa) {
     CTX_GUARD(c);
     if (!c->eng.text_ready) return c->eng.fail(PFB_ERR_ARG, "no text resident on the device (call pfb_upload_text)");
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     cudaEventRecord(e0, c->eng.ws.st);
-    int rc = c->eng.parse_device();
+    int rc = c->eng.finalize();
     if (!rc) rc = c->eng.do_parse_bwt();
     if (!rc) rc = c->eng.build(sa != 0, rssa != 0);
     cudaEventRecord(e1, c->eng.ws.st);

@@ -1,0 +1,131 @@
+// comm.hpp -- exchange layer of the single-job multi-GPU path.
+//
+// One process per GPU; a job of `world` ranks exchanges data only through all-gathers of
+// device buffers (fixed-size or variable-size).  Two transports:
+//   * NcclComm      NCCL over NVLink/NVSwitch.  libnccl.so.2 is dlopen'ed (the torch-bundled
+//                   copy is already resident in a torchrun process); the unique id is made on
+//                   rank 0 and handed to the other ranks by the launcher (torch.distributed).
+//   * HostCallComm  the caller supplies a host-level all-gather (e.g. torch.distributed/gloo);
+//                   device buffers are staged through host memory.  This is what the CPU tests
+//                   (world_size 2, gloo) and the single-GPU multi-process GPU tests use.
+// Replaces nothing in the reference one-to-one: the reference's only parallel step is the
+// thread pool of merge_pfp (src/merge_pfp.cpp:97-150).
+#pragma once
+#include "prim.cuh"
+#ifndef PFB_EMU
+#include <dlfcn.h>
+#endif
+
+extern "C" {
+// host-level all-gather-v: every rank passes `send` (counts[rank] bytes) and receives the
+// concatenation of all ranks' buffers, in rank order, in `recv` (sum(counts) bytes).  0 = ok.
+typedef int (*pfb_allgatherv_fn)(void *user, const void *send, void *recv, const uint64_t *counts, int world);
+}
+
+namespace pfb {
+
+struct Comm {
+    int rank = 0, world = 1;
+    uint64_t bytes_moved = 0;      // bytes received from other ranks so far
+    virtual ~Comm() {}
+    // device buffers; recv holds sum(counts) bytes, rank r's part at offset sum(counts[0..r))
+    virtual void all_gather_v(const void *d_send, void *d_recv, const u64 *counts, pfbStream_t st) = 0;
+
+    void all_gather(const void *d_send, void *d_recv, u64 bytes, pfbStream_t st) {
+        std::vector<u64> c((size_t)world, bytes);
+        all_gather_v(d_send, d_recv, c.data(), st);
+    }
+    // K 64-bit values per rank, host in / host out (out[r*K + i])
+    std::vector<u64> gather_u64(const u64 *vals, int K, pfbStream_t st) {
+        DevBuf<u64> s((size_t)K), r((size_t)K * world);
+        h2d(s.get(), vals, (size_t)K * 8, st);
+        all_gather(s.get(), r.get(), (u64)K * 8, st);
+        std::vector<u64> out((size_t)K * world);
+        d2h(out.data(), r.get(), out.size() * 8, st);
+        stream_sync(st);
+        return out;
+    }
+};
+
+struct HostCallComm : Comm {
+    pfb_allgatherv_fn fn = nullptr;
+    void *user = nullptr;
+    void all_gather_v(const void *d_send, void *d_recv, const u64 *counts, pfbStream_t st) override {
+        u64 tot = 0;
+        for (int r = 0; r < world; ++r) tot += counts[r];
+        std::vector<uint8_t> hs(counts[rank] ? counts[rank] : 1), hr(tot ? tot : 1);
+        if (counts[rank]) d2h(hs.data(), d_send, counts[rank], st);
+        stream_sync(st);
+        if (fn(user, hs.data(), hr.data(), counts, world)) throw Error(-8, "host all-gather callback failed");
+        if (tot) h2d(d_recv, hr.data(), tot, st);
+        stream_sync(st);
+        bytes_moved += tot - counts[rank];
+    }
+};
+
+#ifndef PFB_EMU
+// ---- NCCL through dlopen: only the handful of entry points the path needs ----------------
+struct NcclApi {
+    typedef struct ncclComm *comm_t;
+    struct uid { char b[128]; };
+    int (*GetUniqueId)(uid *) = nullptr;
+    int (*CommInitRank)(comm_t *, int, uid, int) = nullptr;
+    int (*CommDestroy)(comm_t) = nullptr;
+    int (*AllGather)(const void *, void *, size_t, int, comm_t, cudaStream_t) = nullptr;
+    int (*Broadcast)(const void *, void *, size_t, int, int, comm_t, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+    void *h = nullptr;
+    std::string err;
+    bool load() {
+        if (h) return true;
+        const char *names[] = {"libnccl.so.2", "libnccl.so"};
+        for (const char *n : names) { h = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (h) break; }
+        if (!h) { err = std::string("cannot load NCCL: ") + dlerror(); return false; }
+#define PFB_NCCL_SYM(f) *(void **)(&f) = dlsym(h, "nccl" #f); if (!f) { err = "NCCL symbol nccl" #f " missing"; return false; }
+        PFB_NCCL_SYM(GetUniqueId) PFB_NCCL_SYM(CommInitRank) PFB_NCCL_SYM(CommDestroy) PFB_NCCL_SYM(AllGather)
+        PFB_NCCL_SYM(Broadcast) PFB_NCCL_SYM(GroupStart) PFB_NCCL_SYM(GroupEnd) PFB_NCCL_SYM(GetErrorString)
+#undef PFB_NCCL_SYM
+        return true;
+    }
+};
+inline NcclApi &nccl_api() { static NcclApi a; return a; }
+
+struct NcclComm : Comm {
+    NcclApi::comm_t comm = nullptr;
+    void check(int rc, const char *what) {
+        if (rc != 0) throw Error(-5, std::string("NCCL ") + what + ": " + nccl_api().GetErrorString(rc));
+    }
+    void init(int rank_, int world_, const void *uid128) {
+        NcclApi &a = nccl_api();
+        if (!a.load()) throw Error(-5, a.err);
+        rank = rank_; world = world_;
+        NcclApi::uid id;
+        memcpy(id.b, uid128, 128);
+        check(a.CommInitRank(&comm, world, id, rank), "CommInitRank");
+    }
+    ~NcclComm() override { if (comm) nccl_api().CommDestroy(comm); }
+    void all_gather_v(const void *d_send, void *d_recv, const u64 *counts, pfbStream_t st) override {
+        NcclApi &a = nccl_api();
+        bool equal = true;
+        u64 tot = 0;
+        for (int r = 0; r < world; ++r) { equal &= counts[r] == counts[0]; tot += counts[r]; }
+        if (equal) {
+            if (counts[0]) check(a.AllGather(d_send, d_recv, counts[0], /*ncclChar*/ 0, comm, st), "AllGather");
+        } else {
+            // all-gather-v = one broadcast per root inside a group (fused by NCCL into one launch)
+            check(a.GroupStart(), "GroupStart");
+            u64 off = 0;
+            for (int r = 0; r < world; ++r) {
+                if (counts[r]) check(a.Broadcast(d_send, (char *)d_recv + off, counts[r], 0, r, comm, st), "Broadcast");
+                off += counts[r];
+            }
+            check(a.GroupEnd(), "GroupEnd");
+        }
+        bytes_moved += tot - counts[rank];
+    }
+};
+#endif
+
+}  // namespace pfb

@@ -136,11 +136,24 @@ PFB_HD inline u8 prev_byte(u64 key) { return (key & 8) ? ENDOFWORD : sym3_byte((
 // once into 2-bit fields + a stopper mask and derives its 8 windows with shifts; keys leave
 // through shared memory so that global stores are unit-stride.
 static const int KEYS_TILE = 2048;
+// MODE 0: keys of all positions -> key[].  The other modes serve the range-restricted sort of the
+// multi-GPU path (a rank sorts only the valid suffixes whose code lies in [lo, hi)):
+// MODE 1: weighted histogram of the top `hshift`-shifted code bits over sampled tiles (splitter choice)
+// MODE 2: number of selected suffixes per tile -> tilecnt[]
+// MODE 3: selected (key, position) pairs, in dictionary order, at tilebase[tile] + rank inside the tile
+struct KeySelect {
+    u64 lo = 0, hi = ~0ull;       // code range
+    u64 *hist = nullptr; int hshift = 0; u32 tile_stride = 1;
+    u32 *tilecnt = nullptr; const u64 *tilebase = nullptr;
+    u64 *key_out = nullptr; u32 *idx_out = nullptr;
+};
+template <int MODE>
 __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict__ dict, u64 D, int L, u64 *__restrict__ key,
-                                                            WordLookup wl, const u32 *__restrict__ occ, int w, KeyExtra kx) {
+                                                            WordLookup wl, const u32 *__restrict__ occ, int w, KeyExtra kx, KeySelect ks) {
     __shared__ __align__(16) u8 sb[KEYS_TILE + 48];
     __shared__ u64 sk[KEYS_TILE];
-    const u64 base = (u64)blockIdx.x * KEYS_TILE;
+    const u64 tile = MODE == 1 ? (u64)blockIdx.x * ks.tile_stride : (u64)blockIdx.x;
+    const u64 base = tile * KEYS_TILE;
     for (int o = threadIdx.x * 16; o < KEYS_TILE + 48; o += 256 * 16) {
         u64 g = base + (u64)o;
         uint4 v = make_uint4(0, 0, 0, 0);
@@ -176,6 +189,8 @@ __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict
     // word of the thread's first position (one sampled lookup per 8 positions); later positions add
     // the EndOfWord bytes passed
     u32 d = (base + (u64)i0 < D) ? wl.word((u32)(base + (u64)i0)) : wl.Dw;
+    u32 selmask = 0;
+    u64 mykeys[MODE == 3 ? 8 : 1];
 #pragma unroll
     for (int p = 0; p < 8; ++p) {
         u64 W = p ? ((xh << (2 * p)) | (xl >> (64 - 2 * p))) : xh;
@@ -191,15 +206,43 @@ __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict
         const bool valid = ((tmk << p) >> (63 - w)) == 0;          // no EndOfWord within the next w+1 bytes: suffix length > w
         const bool full = i == 0 || (i > 1 && pcs[p] == 0) ;       // preceded by EndOfWord (or the very first byte)
         u64 c = (valid && d < wl.Dw) ? (u64)occ[d] : 0ull;
-        sk[i0 + p] = pack_key(code, j < L ? (u32)j + 1 : (u32)L, j < L && kind == 0, pc) | kx.pack(c, valid && full);
+        const u64 kk = pack_key(code, j < L ? (u32)j + 1 : (u32)L, j < L && kind == 0, pc) | kx.pack(c, valid && full);
+        if (MODE == 0) sk[i0 + p] = kk;
+        else {
+            const bool sel = valid && d < wl.Dw && i < D && code >= ks.lo && code < ks.hi;
+            if (MODE == 1) { if (valid && d < wl.Dw && i < D) atomic_add(&ks.hist[code >> ks.hshift], 4ull + c); }
+            else { selmask |= sel ? 1u << p : 0u; if (MODE == 3) mykeys[MODE == 3 ? p : 0] = kk; }
+        }
         d += (u32)((tmk >> (63 - p)) & 1);
     }
-    __syncthreads();
+    if (MODE == 0) {
+        __syncthreads();
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        int o = k * 256 + threadIdx.x;
-        u64 g = base + (u64)o;
-        if (g < D) key[g] = sk[o];
+        for (int k = 0; k < 8; ++k) {
+            int o = k * 256 + threadIdx.x;
+            u64 g = base + (u64)o;
+            if (g < D) key[g] = sk[o];
+        }
+    } else if (MODE >= 2) {
+        // ordered compaction inside the tile: exclusive scan of the per-thread selected counts
+        __shared__ u32 wsum[8];
+        const u32 mine = (u32)__popc(selmask);
+        const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+        u32 inc = mine;
+#pragma unroll
+        for (int dd = 1; dd < 32; dd <<= 1) { u32 o = __shfl_up_sync(0xffffffffu, inc, dd); if (lane >= dd) inc += o; }
+        if (lane == 31) wsum[wid] = inc;
+        __syncthreads();
+        u32 before = 0, tot = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { u32 s_ = wsum[k]; if (k < wid) before += s_; tot += s_; }
+        if (MODE == 2) { if (threadIdx.x == 0) ks.tilecnt[blockIdx.x] = tot; }
+        else {
+            u64 o = ks.tilebase[blockIdx.x] + before + inc - mine;
+#pragma unroll
+            for (int p = 0; p < 8; ++p)
+                if (selmask & (1u << p)) { ks.key_out[o] = mykeys[MODE == 3 ? p : 0]; ks.idx_out[o] = (u32)(base + (u64)(i0 + p)); ++o; }
+        }
     }
 }
 #endif
@@ -219,9 +262,82 @@ inline void k_suffix_keys(const u8 *dict, u64 D, int L, u64 *key, const WordLook
     }
 #else
     if (D == 0) return;
-    k_suffix_keys_kernel<<<(unsigned)((D + KEYS_TILE - 1) / KEYS_TILE), 256, 0, st>>>(dict, D, L, key, wl, occ, w, kx);
+    k_suffix_keys_kernel<0><<<(unsigned)((D + KEYS_TILE - 1) / KEYS_TILE), 256, 0, st>>>(dict, D, L, key, wl, occ, w, kx, KeySelect());
     PFB_CUDA_CHECK(cudaGetLastError());
     launch_stats().own++;
+#endif
+}
+
+// ---- range-restricted keys (multi-GPU path): only VALID suffixes (length > w; the others emit
+// nothing and cannot tie with a valid one) whose code lies in [lo, hi) are handed to the sort ----
+PFB_HD inline bool key_is_valid(const WordLookup &wl, u32 i, int w, u32 &d) {
+    d = wl.word(i);
+    return d < wl.Dw && wl.suflen(d, i) > (u64)w;
+}
+// weighted histogram (4 + occurrences per valid suffix: sort work + emission work) of code >> hshift.
+// The CUDA build samples every `stride`-th tile: splitters only have to balance, not to be exact.
+inline void k_suffix_key_hist(const u8 *dict, u64 D, int L, const WordLookup &wl, const u32 *occ, int w, const KeyExtra &kx,
+                              u64 *hist, int hshift, pfbStream_t st) {
+#ifdef PFB_EMU
+    (void)st; (void)kx;
+    for (u64 i = 0; i < D; ++i) {
+        u32 d;
+        if (!key_is_valid(wl, (u32)i, w, d)) continue;
+        EnumKey e = enum_scan(dict, D, i, L);
+        hist[e.code >> hshift] += 4ull + occ[d];
+    }
+#else
+    if (D == 0) return;
+    const u64 nt = (D + KEYS_TILE - 1) / KEYS_TILE;
+    KeySelect ks;
+    ks.hist = hist; ks.hshift = hshift;
+    ks.tile_stride = nt > 16384 ? (u32)(nt / 16384) : 1u;
+    k_suffix_keys_kernel<1><<<(unsigned)((nt + ks.tile_stride - 1) / ks.tile_stride), 256, 0, st>>>(dict, D, L, nullptr, wl, occ, w, kx, ks);
+    PFB_CUDA_CHECK(cudaGetLastError());
+    launch_stats().own++;
+#endif
+}
+// selected (key, position) pairs in dictionary order; returns how many.  key_out / idx_out are (re)allocated.
+template <class WS>
+inline u64 k_suffix_keys_select(const u8 *dict, u64 D, int L, const WordLookup &wl, const u32 *occ, int w, const KeyExtra &kx,
+                                u64 lo, u64 hi, DevBuf<u64> &key_out, DevBuf<u32> &idx_out, u64 (*pad)(u64), WS &ws) {
+    pfbStream_t st = ws.st;
+#ifdef PFB_EMU
+    std::vector<u64> ks_; std::vector<u32> is_;
+    for (u64 i = 0; i < D; ++i) {
+        u32 d;
+        if (!key_is_valid(wl, (u32)i, w, d)) continue;
+        EnumKey e = enum_scan(dict, D, i, L);
+        if (e.code < lo || e.code >= hi) continue;
+        bool full = (u32)i == wl.start(d);
+        ks_.push_back(pack_key(e.code, e.consumed, e.closed, (u32)prev_code(dict, i)) | kx.pack(occ[d], full));
+        is_.push_back((u32)i);
+    }
+    const u64 m = ks_.size();
+    key_out.alloc(m); idx_out.alloc(pad(m));
+    if (m) { memcpy(key_out.get(), ks_.data(), m * 8); memcpy(idx_out.get(), is_.data(), m * 4); }
+    (void)st;
+    return m;
+#else
+    const u64 nt = (D + KEYS_TILE - 1) / KEYS_TILE;
+    if (nt == 0) { key_out.alloc(0); idx_out.alloc(pad(0)); return 0; }
+    DevBuf<u32> tcnt(nt + 1);
+    DevBuf<u64> tbase(nt + 1);
+    KeySelect ks;
+    ks.lo = lo; ks.hi = hi; ks.tilecnt = tcnt.get();
+    k_suffix_keys_kernel<2><<<(unsigned)nt, 256, 0, st>>>(dict, D, L, nullptr, wl, occ, w, kx, ks);
+    PFB_CUDA_CHECK(cudaGetLastError());
+    dev_memset(tcnt.get() + nt, 0, 4, st);
+    exclusive_sum<u32, u64>(tcnt.get(), tbase.get(), nt + 1, ws.sc, st);
+    const u64 m = read_scalar(tbase.get() + nt, st);
+    key_out.alloc(m); idx_out.alloc(pad(m));
+    if (m) {
+        ks.tilebase = tbase.get(); ks.key_out = key_out.get(); ks.idx_out = idx_out.get();
+        k_suffix_keys_kernel<3><<<(unsigned)nt, 256, 0, st>>>(dict, D, L, nullptr, wl, occ, w, kx, ks);
+        PFB_CUDA_CHECK(cudaGetLastError());
+    }
+    launch_stats().own += 2;
+    return m;
 #endif
 }
 

@@ -11,6 +11,7 @@
 #include "pipeline.cuh"
 #include <memory>
 
+
 namespace pfb {
 
 struct Segment {             // a piece of S waiting to be parsed
@@ -42,6 +43,11 @@ struct Engine {
     DeviceBwt bwt;
     bool built = false;
     bool built_sa = false, built_rssa = false;
+
+    // multi-GPU job: this context is rank comm->rank of comm->world; its records
+    // are one contiguous piece of the job's record list (rank order = text order)
+    std::unique_ptr<Comm> comm;
+    u64 shard_start = 0;             // offset of this rank's records in S
 
     int fail(int rc, const std::string &m) { err = m; last_rc = rc; return rc; }
 
@@ -124,7 +130,7 @@ struct Engine {
             const u64 n = pending_n;
             if (n == 0) return fail(PFB_ERR_ARG, "empty input");
             Timer timer(ws.st);
-            text.buf.alloc(16 + n + (u64)prm.w + 64);
+            text.buf.alloc(TextOnDevice::FRONT + n + (u64)prm.w + 64 + text.tail_room);
             text.n = n;
             u8 *S = text.S();
             u64 o = 0;
@@ -166,7 +172,7 @@ struct Engine {
             return PFB_OK;
         } catch (const Error &e) { return fail(e.code, e.what()); }
     }
-    int finalize() { return parse_device(); }
+    int finalize() { return comm ? shard_parse() : parse_device(); }      // collective when a communicator is attached
 
     int do_parse_bwt() {
         try {
@@ -182,7 +188,7 @@ struct Engine {
             if (!parsed) return fail(PFB_ERR_ARG, "no parse loaded");
             if (!parse.has_parse_bwt) { int rc = do_parse_bwt(); if (rc) return rc; }
             bwt = DeviceBwt();
-            int rc = build_bwt(parse, prm, sa, rssa, bwt, ws, tm, err);
+            int rc = build_bwt(parse, prm, sa, rssa, bwt, ws, tm, err, comm.get());
             if (rc) return fail(rc, err);
             built = true; built_sa = sa; built_rssa = rssa;
             return PFB_OK;
@@ -357,23 +363,31 @@ struct Engine {
         } catch (const Error &e) { return fail(e.code, e.what()); }
     }
 
+#include "shard.inl"
+
     // ---- output files: src/pfbwt-f.cpp:298-349 -------------------------------------------------
     int write_bwt_files(const std::string &prefix, bool sa, bool rssa, const std::string &stdout_ext) {
         try {
             if (!built) return fail(PFB_ERR_ARG, "BWT not built");
             std::string e;
             const int U = prm.bits / 8;
-            auto emit = [&](const std::string &ext, const DevBuf<u8> &b, size_t bytes) -> int {
+            // a rank of a multi-GPU job writes its slice at its offset of the common file
+            auto emit = [&](const std::string &ext, const DevBuf<u8> &b, size_t bytes, u64 off, u64 final_size) -> int {
                 auto v = to_host(b, bytes);
+                if (comm) {
+                    if (!stdout_ext.empty()) { e = "--stdout is not available in a multi-GPU job"; return -1; }
+                    return write_file_at(prefix + "." + ext, v.data(), v.size(), off, final_size, e);
+                }
                 if (stdout_ext == ext) { fwrite(v.data(), 1, v.size(), stdout); fflush(stdout); return 0; }
                 return write_file(prefix + "." + ext, v.data(), v.size(), e);
             };
-            if (emit("bwt", bwt.bwt, bwt.n + 1)) return fail(PFB_ERR_IO, e);
-            if (sa) { if (!built_sa && !built_rssa) return fail(PFB_ERR_ARG, "SA not built"); if (emit("sa", bwt.sa, (bwt.n + 1) * (size_t)U)) return fail(PFB_ERR_IO, e); }
+            if (emit("bwt", bwt.bwt, bwt.len, bwt.off, bwt.n + 1)) return fail(PFB_ERR_IO, e);
+            if (sa) { if (!built_sa && !built_rssa) return fail(PFB_ERR_ARG, "SA not built");
+                      if (emit("sa", bwt.sa, bwt.len * (size_t)U, bwt.off * (u64)U, (bwt.n + 1) * (u64)U)) return fail(PFB_ERR_IO, e); }
             if (rssa) {
                 if (!built_rssa) return fail(PFB_ERR_ARG, "run-length SA not built");
-                if (emit("ssa", bwt.ssa, 2 * bwt.r * (size_t)U)) return fail(PFB_ERR_IO, e);
-                if (emit("esa", bwt.esa, 2 * bwt.r * (size_t)U)) return fail(PFB_ERR_IO, e);
+                if (emit("ssa", bwt.ssa, 2 * bwt.ssa_cnt * (size_t)U, 2 * bwt.ssa_off * (u64)U, 2 * bwt.r * (u64)U)) return fail(PFB_ERR_IO, e);
+                if (emit("esa", bwt.esa, 2 * bwt.esa_cnt * (size_t)U, 2 * bwt.esa_off * (u64)U, 2 * bwt.r * (u64)U)) return fail(PFB_ERR_IO, e);
             }
             return PFB_OK;
         } catch (const Error &e) { return fail(e.code, e.what()); }

@@ -12,6 +12,7 @@
 #include <string>
 #include <vector>
 #include <unistd.h>
+#include <fcntl.h>
 
 namespace pfb {
 
@@ -183,6 +184,24 @@ inline std::vector<uint8_t> narrow_u64(const uint64_t *v, size_t n, int U) {
     if (U == 8) memcpy(o.data(), v, n * 8);
     else { uint32_t *q = (uint32_t *)o.data(); for (size_t i = 0; i < n; ++i) q[i] = (uint32_t)v[i]; }
     return o;
+}
+
+// one rank's slice of a file written by several processes: every writer sets the final size (idempotent)
+// and writes its bytes at its own offset
+inline int write_file_at(const std::string &path, const void *data, size_t bytes, uint64_t offset, uint64_t final_size, std::string &err) {
+    int fd = open(path.c_str(), O_CREAT | O_WRONLY, 0644);
+    if (fd < 0) { err = "could not open " + path; return -1; }
+    if (ftruncate(fd, (off_t)final_size) != 0) { close(fd); err = "could not size " + path; return -1; }
+    const char *p = (const char *)data;
+    size_t left = bytes;
+    uint64_t off = offset;
+    while (left) {
+        ssize_t k = pwrite(fd, p, left, (off_t)off);
+        if (k <= 0) { close(fd); err = "write failed: " + path; return -1; }
+        p += k; off += (uint64_t)k; left -= (size_t)k;
+    }
+    close(fd);
+    return 0;
 }
 
 }  // namespace pfb

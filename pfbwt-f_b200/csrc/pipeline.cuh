@@ -17,6 +17,7 @@
 // 64-bit text positions.
 #pragma once
 #include "prim.cuh"
+#include "comm.hpp"
 #include "../../include/pfbwt_b200.h"
 
 namespace pfb {
@@ -56,11 +57,15 @@ struct DeviceParse {
     bool has_parse_bwt = false;
 };
 
+// With a communicator (multi-GPU job) a rank holds one contiguous slice of every output: BWT
+// positions [off, off+len), .ssa pairs [ssa_off, ssa_off+ssa_cnt), .esa pairs [esa_off, ..); r, n
+// are the totals of the whole job.  Without one the slice is everything.
 struct DeviceBwt {
     u64 n = 0, r = 0, easy = 0, hard = 0;
-    DevBuf<u8> bwt;         // n+1
-    DevBuf<u8> sa;          // (n+1)*U bytes, U=bits/8 (empty unless any_sa)
-    DevBuf<u8> ssa, esa;    // r pairs of U-byte ints each
+    u64 off = 0, len = 0, ssa_off = 0, ssa_cnt = 0, esa_off = 0, esa_cnt = 0;
+    DevBuf<u8> bwt;         // len
+    DevBuf<u8> sa;          // len*U bytes, U=bits/8 (empty unless any_sa)
+    DevBuf<u8> ssa, esa;    // ssa_cnt / esa_cnt pairs of U-byte ints each
 };
 
 // PFB_TRACE=1: every lap() is timed (CUDA events) and printed to stderr at the end of a run;
@@ -193,12 +198,15 @@ inline void k_normalise(u8 *S, u64 n, bool non_acgt_to_a, u64 *d_errpos, pfbStre
 //     wang_hash(kmer ending at T'[q]) % p == 0          (include/pfparser.hpp:347)
 //     Tp points at T'[0]; valid q range is [w+1, n].
 // ---------------------------------------------------------------------------
-inline void k_trigger_words(const u8 *Tp, u64 n, int w, DivTest dt, u32 *trig, u32 *cnt, u64 nwords, pfbStream_t st) {
+//     A piece of T' handled by one rank of a multi-GPU job starts at a trigger window, so its first
+//     admissible position is qmin = w instead of w+1 (the global rule q > w holds for all of it).
+inline void k_trigger_words(const u8 *Tp, u64 n, int w, DivTest dt, u32 *trig, u32 *cnt, u64 nwords, pfbStream_t st, u64 qmin = 0) {
     const u64 mask = (w >= 32) ? ~0ull : ((1ull << (2 * w)) - 1);
+    if (qmin == 0) qmin = (u64)w + 1;
     launch_for(nwords, st, PFB_LAMBDA(u64 t) {
         u64 q0 = t * 32, q1 = q0 + 31;
         if (q1 > n) q1 = n;
-        u64 qs = q0 < (u64)w + 1 ? (u64)w + 1 : q0;
+        u64 qs = q0 < qmin ? qmin : q0;
         u32 bits = 0;
         if (qs <= q1) {
             u64 kmer = 0;
@@ -214,7 +222,8 @@ inline void k_trigger_words(const u8 *Tp, u64 n, int w, DivTest dt, u32 *trig, u
 }
 
 // K2  scatter trigger positions -> ends[] (sorted), ends[P-1] = n+w
-inline void k_scatter_ends(const u32 *trig, const u32 *wordoff, u64 nwords, u64 *ends, u64 P, u64 n, int w, pfbStream_t st) {
+inline void k_scatter_ends(const u32 *trig, const u32 *wordoff, u64 nwords, u64 *ends, u64 P, u64 n, int w, pfbStream_t st,
+                           bool dollar_end = true) {
     launch_for(nwords, st, PFB_LAMBDA(u64 t) {
         u32 bits = trig[t];
         u64 o = wordoff[t];
@@ -223,7 +232,7 @@ inline void k_scatter_ends(const u32 *trig, const u32 *wordoff, u64 nwords, u64 
             ends[o++] = t * 32 + (u64)b;
             bits &= bits - 1;
         }
-        if (t == 0) ends[P - 1] = n + (u64)w;
+        if (t == 0 && dollar_end) ends[P - 1] = n + (u64)w;
     });
 }
 
@@ -350,18 +359,33 @@ inline u64 scan_flags(const u8 *flags, u32 *idx, u64 n, Workspace &ws) {
 //      groups on (dense group id, next symbols).
 //      order[r] = text-order index k of the phrase of rank r.
 // ---------------------------------------------------------------------------
-inline int sort_phrases(const u8 *Tp, const u64 *ends, int w, DevBuf<u32> &order, u64 Dw, Workspace &ws, u32 *rounds_out,
-                        std::string &err) {
+//      The strings are given by an accessor str(k, &offset, &len) into the byte buffer Tp.  With
+//      flag_out != nullptr equal strings are allowed (union of the ranks' dictionaries in a multi-GPU
+//      job): a tie group whose members are exhausted is a set of identical strings and is left alone;
+//      flag_out[j] = 1 at the first member of every group of identical strings in the sorted order.
+struct PhraseStr {      // phrase k of the parse of Tp
+    const u64 *ends; int w;
+    PFB_HD inline void operator()(u64 k, u64 &s, u64 &len) const { s = phrase_start(ends, k, w); len = ends[k] - s + 1; }
+};
+struct WordStr {        // word k of a dictionary image (EndOfWord excluded)
+    const u64 *wstart;  // Dw+1 offsets
+    PFB_HD inline void operator()(u64 k, u64 &s, u64 &len) const { s = wstart[k]; len = wstart[k + 1] - 1 - s; }
+};
+
+template <class Str>
+inline int sort_strings(const u8 *Tp, Str str, DevBuf<u32> &order, u64 Dw, Workspace &ws, u32 *rounds_out, std::string &err,
+                        DevBuf<u8> *flag_out = nullptr) {
     pfbStream_t st = ws.st;
+    const bool dups = flag_out != nullptr;
     DevBuf<u64> key_a(Dw), key_b(Dw);
     DevBuf<u32> val_b(Dw);
     DevBuf<u8> flag(Dw);
     {
         u64 *ka = key_a.get(); const u32 *ord = order.get();
         launch_for(Dw, st, PFB_LAMBDA(u64 j) {
-            u64 k = ord[j];
-            u64 s = phrase_start(ends, k, w);
-            ka[j] = pack_syms(Tp + s, ends[k] - s + 1, 0, 21);
+            u64 s, len;
+            str(ord[j], s, len);
+            ka[j] = pack_syms(Tp + s, len, 0, 21);
         });
     }
     sort_pairs(key_a, key_b, order, val_b, Dw, 0, 63, ws.sc, st);
@@ -375,9 +399,14 @@ inline int sort_phrases(const u8 *Tp, const u64 *ends, int w, DevBuf<u32> &order
     DevBuf<u32> aidx(Dw), gidx(Dw);
     for (;;) {
         {
-            const u8 *fl = flag.get(); u8 *ac = act.get(); u8 *ah = acthead.get();
+            const u8 *fl = flag.get(); u8 *ac = act.get(); u8 *ah = acthead.get(); const u32 *ord = order.get();
             launch_for(Dw, st, PFB_LAMBDA(u64 j) {
                 bool single = fl[j] && (j + 1 == Dw || fl[j + 1]);
+                if (dups && !single) {      // tied on `depth` symbols and exhausted: identical strings (uniform over the group)
+                    u64 s, len;
+                    str(ord[j], s, len);
+                    single = len <= depth;
+                }
                 ac[j] = single ? 0 : 1;
                 ah[j] = (!single && fl[j]) ? 1 : 0;
             });
@@ -401,9 +430,10 @@ inline int sort_phrases(const u8 *Tp, const u64 *ends, int w, DevBuf<u32> &order
                 u32 a = ai[j];
                 u64 gid = (u64)gi[j] + (fl[j] ? 1 : 0) - 1;
                 u64 k = ord[j];
-                u64 s = phrase_start(ends, k, w);
+                u64 s, len;
+                str(k, s, len);
                 ap[a] = (u32)j; av[a] = (u32)k;
-                ak[a] = (gid << (3 * nsym)) | pack_syms(Tp + s, ends[k] - s + 1, depth, nsym);
+                ak[a] = (gid << (3 * nsym)) | pack_syms(Tp + s, len, depth, nsym);
             });
         }
         sort_pairs(akey, akey_b, aval, aval_b, m, 0, gbits + 3 * nsym, ws.sc, st);
@@ -420,7 +450,14 @@ inline int sort_phrases(const u8 *Tp, const u64 *ends, int w, DevBuf<u32> &order
         ++rounds;
     }
     if (rounds_out) *rounds_out = rounds;
+    if (flag_out) *flag_out = std::move(flag);
     return PFB_OK;
+}
+inline int sort_phrases(const u8 *Tp, const u64 *ends, int w, DevBuf<u32> &order, u64 Dw, Workspace &ws, u32 *rounds_out,
+                        std::string &err) {
+    PhraseStr ps;
+    ps.ends = ends; ps.w = w;
+    return sort_strings(Tp, ps, order, Dw, ws, rounds_out, err);
 }
 
 // ---------------------------------------------------------------------------
@@ -529,39 +566,45 @@ PFB_HD inline u32 word_of(const u32 *wstart, u32 Dw, u32 pos) {
 // parse_text: T' bytes already on the device and normalised
 // ===========================================================================
 struct TextOnDevice {
-    DevBuf<u8> buf;     // 16 pad | S (n) | Dollar^w | pad
-    u64 n = 0;
-    u8 *Tp() const { return buf.get() + 15; }   // T'[0] (the leading Dollar)
-    u8 *S() const { return buf.get() + 16; }
+    DevBuf<u8> buf;     // 64 front room | S (n) | Dollar^w | tail room   (a rank of a multi-GPU job puts the w+1 bytes
+    u64 n = 0;          //  before its records into the front room and the bytes up to the next trigger into the tail room)
+    u64 tail_room = 0;
+    static const u64 FRONT = 64;
+    u8 *Tp() const { return buf.get() + FRONT - 1; }   // T'[0] (the leading Dollar)
+    u8 *S() const { return buf.get() + FRONT; }
 };
 
-inline int parse_text(const TextOnDevice &T, const Params &prm, DeviceParse &out, Workspace &ws, StageTimes &tm, std::string &err) {
+// A piece of T' (multi-GPU parse): bytes Tp[0, tlen); positions qmin.. may trigger; the piece either
+// ends with Dollar^w (end of T') or exactly at a trigger position (the first trigger owned by a later rank).
+struct PieceSpec { u64 tlen = 0, qmin = 0; bool dollar_end = true; };
+
+inline int parse_piece(const u8 *Tp, const PieceSpec &ps, const Params &prm, DeviceParse &out, Workspace &ws, StageTimes &tm, std::string &err) {
     pfbStream_t st = ws.st;
     const int w = prm.w;
-    const u64 n = T.n;
-    const u8 *Tp = T.Tp();
-    const u64 tlen = n + (u64)w + 1;
+    const u64 tlen = ps.tlen;
+    const bool dollar_end = ps.dollar_end;
+    const u64 n = dollar_end ? tlen - (u64)w - 1 : tlen - 1;      // last position that may trigger
     if (w < 1 || w > 31) { err = "window size w must be < 32!"; return PFB_ERR_ARG; }
     if (prm.p < 1) { err = "modulus p must be >= 1"; return PFB_ERR_ARG; }
-    if (n == 0) { err = "empty input"; return PFB_ERR_ARG; }
     Timer timer(st);
 
     // K1 trigger bitmap ------------------------------------------------------
     const u64 nwords = n / 32 + 1;   // bits 0..n
     DevBuf<u32> trig(nwords), cnt(nwords), wordoff(nwords);
-    k_trigger_words(Tp, n, w, DivTest::make(prm.p), trig.get(), cnt.get(), nwords, st);
+    k_trigger_words(Tp, n, w, DivTest::make(prm.p), trig.get(), cnt.get(), nwords, st, ps.qmin);
     tm.trigger = timer.stop();
 
     // K2 compaction ------------------------------------------------------------
     exclusive_sum<u32, u32>(cnt.get(), wordoff.get(), nwords, ws.sc, st);
     u64 ntrig = (u64)read_scalar(wordoff.get() + (nwords - 1), st) + read_scalar(cnt.get() + (nwords - 1), st);
-    const u64 P = ntrig + 1;
+    const u64 P = dollar_end ? ntrig + 1 : ntrig;
+    if (P == 0) { err = "internal: piece without a phrase"; return PFB_ERR_INTERNAL; }
     if (prm.bits == 32 && P > 0x7FFFFFFEull) { err = "Input containing more than 2^31-2 phrases! Please use 64 bit version"; return PFB_ERR_LIMIT; }
     if (P > 0xFFFFFFFEull) { err = "Input containing more than 2^32-2 phrases! This is currently a hard limit"; return PFB_ERR_LIMIT; }
     cnt.release();
     out.sai.alloc(P);   // sai_[k] == end position of phrase k (include/pfparser.hpp:600)
     u64 *ends = out.sai.get();
-    k_scatter_ends(trig.get(), wordoff.get(), nwords, ends, P, n, w, st);
+    k_scatter_ends(trig.get(), wordoff.get(), nwords, ends, P, n, w, st, dollar_end);
     trig.release();
     out.last.alloc(P);
     {
@@ -670,6 +713,13 @@ inline int parse_text(const TextOnDevice &T, const Params &prm, DeviceParse &out
     }
     tm.dict_build = timer.stop();
     return PFB_OK;
+}
+
+inline int parse_text(const TextOnDevice &T, const Params &prm, DeviceParse &out, Workspace &ws, StageTimes &tm, std::string &err) {
+    if (T.n == 0) { err = "empty input"; return PFB_ERR_ARG; }
+    PieceSpec ps;
+    ps.tlen = T.n + (u64)prm.w + 1; ps.qmin = (u64)prm.w + 1; ps.dollar_end = true;
+    return parse_piece(T.Tp(), ps, prm, out, ws, tm, err);
 }
 
 // ===========================================================================

@@ -1,0 +1,256 @@
+// shard.inl -- methods of pfb::Engine (included inside the struct): the parse step of a single job
+// spread over the ranks of a communicator.
+//
+// Rank g holds the records S_g of a contiguous piece of the job's record list; S = S_0 S_1 ... S_{G-1}.
+//   1. trigger positions are position-local (a w-byte window), so a rank needs only the w+1 bytes
+//      before its piece: one tiny all-gather of every rank's tail bytes;
+//   2. a phrase belongs to the rank that holds its first byte.  The phrase that straddles the cut
+//      g | g+1 ends at the first trigger of a later rank: ranks all-gather their "heads"
+//      (bytes up to and including their first trigger), rank g appends what it needs to its text;
+//   3. every rank parses its piece (parse_piece: same kernels as the single-GPU path) into a local
+//      sorted dictionary + parse;
+//   4. merge_pfp-style merge (include/pfparser.hpp:194-263, src/merge_pfp.cpp:97-170): the local
+//      dictionaries are all-gathered over NVLink, the union is sorted and deduplicated on every rank
+//      (sort_strings with duplicate groups), local ranks are renamed to global ranks and the renamed
+//      parses / last / sai arrays are all-gathered.  After this every rank holds the whole parse
+//      (dictionary replicated, as the range-partitioned suffix sort of build.cuh needs it).
+// Error handling is collective: a rank that fails still takes part in the next exchange and all
+// ranks return an error together.
+
+    float shard_exchange_ms = 0, shard_merge_ms = 0;
+
+    int shard_fail_together(int rc, const char *what, pfbStream_t st) {
+        u64 v = rc ? 1 : 0;
+        std::vector<u64> all = comm->gather_u64(&v, 1, st);
+        for (int r = 0; r < comm->world; ++r)
+            if (all[(size_t)r]) {
+                if (rc) return rc;
+                return fail(PFB_ERR_ARG, std::string("rank ") + std::to_string(r) + " failed in " + what);
+            }
+        return PFB_OK;
+    }
+
+    // first trigger position inside S (index into S) given the w+1 bytes stored right before it; ~0 if none
+    u64 shard_first_trigger() {
+        pfbStream_t st = ws.st;
+        const u64 w = (u64)prm.w, len = text.n;
+        const u8 *X = text.S() - (w + 1);
+        const DivTest dt = DivTest::make(prm.p);
+        u64 done = 0, win = 1u << 16;
+        std::vector<u32> host;
+        while (done < len) {
+            const u64 cntp = win < len - done ? win : len - done;
+            const u64 qmax = w + cntp;                       // positions w+1 .. w+cntp of X+done are S[done .. done+cntp)
+            const u64 nwords = qmax / 32 + 1;
+            DevBuf<u32> trig(nwords), cnt(nwords);
+            k_trigger_words(X + done, qmax, (int)w, dt, trig.get(), cnt.get(), nwords, st, w + 1);
+            host.resize(nwords);
+            d2h(host.data(), trig.get(), nwords * 4, st);
+            stream_sync(st);
+            for (u64 t = 0; t < nwords; ++t)
+                if (host[t]) return done + (t * 32 + (u64)(__builtin_ffs((int)host[t]) - 1)) - (w + 1);
+            done += cntp;
+            win *= 8;
+        }
+        return ~0ull;
+    }
+
+    int shard_parse() {
+        try {
+            if (!comm) return fail(PFB_ERR_ARG, "no communicator attached to this context");
+            pfbStream_t st = ws.st;
+            const int G = comm->world, g = comm->rank;
+            const u64 w = (u64)prm.w;
+            Timer xt(st);
+            float t_x = 0, t_m = 0;
+
+            // ---- 0. text on the device, normalised; agree on sizes ---------------------------------
+            int rc = PFB_OK;
+            if (!text_ready) { text.tail_room = 4096; rc = upload_text(); }
+            u64 len = rc ? 0 : text.n;
+            if (!rc && len < w) rc = fail(PFB_ERR_ARG, "every rank needs at least one record");
+            u64 hdr[6] = {rc ? 1ull : 0ull, len, 0, 0, 0, 0};
+            const u64 tl = len < w + 1 ? len : w + 1;
+            if (!rc && tl) {
+                u8 tail[32];
+                memset(tail, 0, sizeof(tail));
+                d2h(tail + (32 - tl), text.S() + (len - tl), tl, st);
+                stream_sync(st);
+                memcpy(&hdr[2], tail, 32);
+            }
+            std::vector<u64> all = comm->gather_u64(hdr, 6, st);
+            for (int r = 0; r < G; ++r)
+                if (all[6 * (size_t)r]) return rc ? rc : fail(PFB_ERR_ARG, "rank " + std::to_string(r) + " could not load its records");
+            std::vector<u64> lens((size_t)G), starts((size_t)G + 1, 0);
+            for (int r = 0; r < G; ++r) { lens[(size_t)r] = all[6 * (size_t)r + 1]; starts[(size_t)r + 1] = starts[(size_t)r] + lens[(size_t)r]; }
+            const u64 n_total = starts[(size_t)G];
+            shard_start = starts[(size_t)g];
+            if (prm.bits == 32 && n_total > 0xFFFFFFFFull) return fail(PFB_ERR_TOO_LONG_32, "input too long, please use 64-bit version");
+
+            // ---- 1. the w+1 bytes of T' before this rank's records -----------------------------------
+            if (g > 0) {
+                std::vector<u8> pre(1, DOLLAR);
+                for (int r = 0; r < g; ++r) {
+                    const u64 tr = lens[(size_t)r] < w + 1 ? lens[(size_t)r] : w + 1;
+                    const u8 *tb = (const u8 *)&all[6 * (size_t)r + 2];
+                    pre.insert(pre.end(), tb + (32 - tr), tb + 32);
+                }
+                h2d(text.S() - (w + 1), pre.data() + (pre.size() - (w + 1)), w + 1, st);
+            }
+
+            // ---- 2. first trigger, heads ------------------------------------------------------------------
+            const u64 NONE = ~0ull;
+            u64 f = g > 0 ? shard_first_trigger() : NONE;
+            u64 fh[2] = {f, g == 0 ? 0ull : (f == NONE ? len : f + 1)};
+            std::vector<u64> fhs = comm->gather_u64(fh, 2, st);
+            std::vector<u64> hcnt((size_t)G), hoff((size_t)G + 1, 0);
+            for (int r = 0; r < G; ++r) { hcnt[(size_t)r] = fhs[2 * (size_t)r + 1]; hoff[(size_t)r + 1] = hoff[(size_t)r] + hcnt[(size_t)r]; }
+            DevBuf<u8> heads(hoff[(size_t)G] + 1);
+            comm->all_gather_v(text.S(), heads.get(), hcnt.data(), st);
+            const bool own = g == 0 || f != NONE;
+            u64 rlen = 0;
+            bool dollar_end = true;
+            int hlast = g;
+            for (int r = g + 1; r < G && own; ++r) {
+                rlen += hcnt[(size_t)r];
+                hlast = r;
+                if (fhs[2 * (size_t)r] != NONE) { dollar_end = false; break; }
+            }
+            if (own) {
+                if (rlen + w + 16 > w + 64 + text.tail_room) {          // rare: a very long straddling phrase
+                    DevBuf<u8> nb(TextOnDevice::FRONT + len + rlen + w + 64);
+                    d2d(nb.get(), text.buf.get(), TextOnDevice::FRONT + len, st);
+                    stream_sync(st);
+                    text.buf = std::move(nb);
+                    text.tail_room = rlen;
+                }
+                if (rlen) d2d(text.S() + len, heads.get() + hoff[(size_t)g + 1], hoff[(size_t)hlast + 1] - hoff[(size_t)g + 1], st);
+                if (dollar_end) { u8 *e = text.S() + len + rlen; launch_for(w, st, PFB_LAMBDA(u64 i) { e[i] = DOLLAR; }); }
+            }
+            heads.release();
+            t_x += xt.stop();
+
+            // ---- 3. local parse of the piece ---------------------------------------------------------------
+            DeviceParse lp;
+            u64 base = 0;                        // T' index of the first byte of the piece
+            if (own) {
+                PieceSpec ps;
+                const u8 *Tp;
+                if (g == 0) { Tp = text.Tp(); ps.qmin = w + 1; base = 0; }
+                else { Tp = text.S() + f - (w - 1); ps.qmin = w; base = 1 + shard_start + f - (w - 1); }
+                ps.dollar_end = dollar_end;
+                ps.tlen = (u64)((text.S() + len + rlen + (dollar_end ? w : 0)) - Tp);
+                rc = parse_piece(Tp, ps, prm, lp, ws, tm, err);
+                if (rc) fail(rc, err);
+                else if (base) {
+                    u64 *sp = lp.sai.get();
+                    launch_for(lp.P, st, PFB_LAMBDA(u64 k) { sp[k] += base; });
+                }
+            }
+            xt.stop();
+            rc = shard_fail_together(rc, "the local parse", st);
+            if (rc) return rc;
+            rc = shard_merge(lp, n_total, t_x, t_m);
+            shard_exchange_ms = t_x; shard_merge_ms = t_m;
+            return rc;
+        } catch (const Error &e) { return fail(e.code, e.what()); }
+    }
+
+    // ---- 4. merge of the ranks' parses -----------------------------------------------------------------
+    int shard_merge(DeviceParse &lp, u64 n_total, float &t_x, float &t_m) {
+        pfbStream_t st = ws.st;
+        const int G = comm->world, g = comm->rank;
+        Timer xt(st);
+        u64 sz[3] = {lp.P, lp.Dw, lp.dsize ? lp.dsize - 1 : 0};          // dictionary bytes without the EndOfDict byte
+        std::vector<u64> szs = comm->gather_u64(sz, 3, st);
+        std::vector<u64> cP((size_t)G), cW((size_t)G), cB((size_t)G), oP((size_t)G + 1, 0), oW((size_t)G + 1, 0), oB((size_t)G + 1, 0);
+        for (int r = 0; r < G; ++r) {
+            cP[(size_t)r] = szs[3 * (size_t)r]; cW[(size_t)r] = szs[3 * (size_t)r + 1]; cB[(size_t)r] = szs[3 * (size_t)r + 2];
+            oP[(size_t)r + 1] = oP[(size_t)r] + cP[(size_t)r]; oW[(size_t)r + 1] = oW[(size_t)r] + cW[(size_t)r]; oB[(size_t)r + 1] = oB[(size_t)r] + cB[(size_t)r];
+        }
+        const u64 P = oP[(size_t)G], M = oW[(size_t)G], UB = oB[(size_t)G];
+        if (prm.bits == 32 && P > 0x7FFFFFFEull) return fail(PFB_ERR_LIMIT, "Input containing more than 2^31-2 phrases! Please use 64 bit version");
+        if (P > 0xFFFFFFFEull) return fail(PFB_ERR_LIMIT, "Input containing more than 2^32-2 phrases! This is currently a hard limit");
+        if (M > 0xFFFFFFF0ull) return fail(PFB_ERR_LIMIT, "more than 2^32 dictionary words across the ranks");
+        // union of the local dictionaries: bytes, word starts, occurrence counts
+        DevBuf<u8> ub(UB + 1);
+        DevBuf<u32> uws(M + 1), uocc(M + 1);
+        DevBuf<u64> ustart(M + 1);
+        auto scaled = [&](const std::vector<u64> &c, u64 k) { std::vector<u64> v(c); for (auto &x : v) x *= k; return v; };
+        comm->all_gather_v(lp.dict.get(), ub.get(), cB.data(), st);
+        comm->all_gather_v(lp.wstart.get(), uws.get(), scaled(cW, 4).data(), st);
+        comm->all_gather_v(lp.occ.get(), uocc.get(), scaled(cW, 4).data(), st);
+        t_x += xt.stop();
+        for (int r = 0; r < G; ++r) {
+            const u64 c = cW[(size_t)r], o = oW[(size_t)r], b = oB[(size_t)r];
+            const u32 *src = uws.get() + o; u64 *dst = ustart.get() + o;
+            launch_for(c, st, PFB_LAMBDA(u64 j) { dst[j] = b + (u64)src[j]; });
+        }
+        { u64 *us = ustart.get(); launch_for(1, st, PFB_LAMBDA(u64) { us[M] = UB; }); }
+        // sort the union; groups of identical words collapse into one global word
+        DevBuf<u32> order(M + 1);
+        { u32 *op = order.get(); launch_for(M, st, PFB_LAMBDA(u64 j) { op[j] = (u32)j; }); }
+        DevBuf<u8> head;
+        WordStr wsr;
+        wsr.wstart = ustart.get();
+        int rc = sort_strings(ub.get(), wsr, order, M, ws, &tm.phrase_sort_rounds, err, &head);
+        if (rc) return fail(rc, err);
+        DevBuf<u32> gidx(M + 1);
+        const u64 Dw = scan_flags(head.get(), gidx.get(), M, ws);            // gidx[j] + head[j] = 1-based global rank of order[j]
+        DevBuf<u32> map(M + 1), headpos(Dw + 1);
+        parse = DeviceParse();
+        parse.occ.alloc(Dw);
+        dev_memset(parse.occ.get(), 0, Dw * 4, st);
+        {
+            const u32 *op = order.get(); const u32 *gi = gidx.get(); const u8 *hd = head.get(); const u32 *uo = uocc.get();
+            u32 *mp = map.get(); u32 *hp = headpos.get(); u32 *oc = parse.occ.get();
+            launch_for(M, st, PFB_LAMBDA(u64 j) {
+                u32 r = gi[j] + hd[j];               // 1-based
+                mp[op[j]] = r;
+                if (hd[j]) hp[r - 1] = op[j];
+                atomic_add(&oc[r - 1], uo[op[j]]);
+            });
+        }
+        // global dictionary image (include/pfbwt_io.hpp:71-82)
+        DevBuf<u64> wl(Dw + 1), ws64(Dw + 1);
+        {
+            u64 *wlp = wl.get(); const u32 *hp = headpos.get(); const u64 *us = ustart.get();
+            launch_for(Dw + 1, st, PFB_LAMBDA(u64 r) { wlp[r] = r == Dw ? 0 : us[hp[r] + 1] - us[hp[r]]; });   // word + EndOfWord
+        }
+        exclusive_sum<u64, u64>(wl.get(), ws64.get(), Dw + 1, ws.sc, st);
+        const u64 dsize = read_scalar(ws64.get() + Dw, st) + 1;
+        if (dsize > 0xFFFFFFF0ull) return fail(PFB_ERR_LIMIT, "dictionary larger than 2^32 bytes is not supported yet");
+        parse.n = n_total; parse.P = P; parse.Dw = Dw; parse.dsize = dsize;
+        parse.wstart.alloc(Dw + 1);
+        parse.dict.alloc(dsize);
+        {
+            const u64 *w64 = ws64.get(); u32 *wsp = parse.wstart.get(); const u32 *hp = headpos.get(); const u64 *us = ustart.get();
+            const u8 *src = ub.get(); u8 *dict = parse.dict.get();
+            launch_for(Dw + 1, st, PFB_LAMBDA(u64 r) { wsp[r] = (u32)w64[r]; });
+            launch_for(Dw * 32 + 1, st, PFB_LAMBDA(u64 i) {
+                if (i == Dw * 32) { dict[dsize - 1] = ENDOFDICT; return; }
+                u64 r = i / 32, lane = i % 32;
+                u64 s = us[hp[r]], len = us[hp[r] + 1] - s;          // includes the EndOfWord byte
+                u64 d0 = w64[r];
+                for (u64 j = lane; j < len; j += 32) dict[d0 + j] = src[s + j];
+            });
+        }
+        // local ranks -> global ranks, then the whole parse on every rank
+        DevBuf<u32> lp2(lp.P + 1);
+        {
+            const u32 *mp = map.get() + oW[(size_t)g]; const u32 *pr = lp.parse.get(); u32 *o = lp2.get();
+            launch_for(lp.P, st, PFB_LAMBDA(u64 k) { o[k] = mp[pr[k] - 1]; });
+        }
+        t_m += xt.stop();
+        parse.parse.alloc(P + 1);
+        parse.last.alloc(P + 1);
+        parse.sai.alloc(P + 1);
+        comm->all_gather_v(lp2.get(), parse.parse.get(), scaled(cP, 4).data(), st);
+        comm->all_gather_v(lp.last.get(), parse.last.get(), cP.data(), st);
+        comm->all_gather_v(lp.sai.get(), parse.sai.get(), scaled(cP, 8).data(), st);
+        dev_memset(parse.parse.get() + P, 0, 4, st);
+        stream_sync(st);
+        t_x += xt.stop();
+        parsed = true; built = false;
+        return PFB_OK;
+    }

@@ -58,3 +58,29 @@ int main(int argc, char **argv) {
             E.tm.phrase_sort_rounds, E.tm.parse_sa_rounds, E.tm.dict_sort_rounds);
     return 0;
 }
+
+// ---- multi-rank logic check (tests/test_shard_gloo.py): one call = one rank of a job whose exchanges go
+// through the caller's host all-gather (torch.distributed / gloo).  Writes this rank's slices of
+// <out>.bwt/.sa/.ssa/.esa at their offsets and, on rank 0, the merged parse files.
+extern "C" int pfb_emu_shard_run(int rank, int world, pfb_allgatherv_fn fn, void *user, const char *fasta, int w, int p, int bits,
+                                 int sa, int rssa, const char *out, unsigned long long *info /* 8 */) {
+    pfb::Engine E;
+    E.prm.w = w; E.prm.p = (uint64_t)p; E.prm.bits = bits; E.prm.get_sai = sa || rssa;
+    pfb::HostCallComm *hc = new pfb::HostCallComm();
+    hc->rank = rank; hc->world = world; hc->fn = fn; hc->user = user;
+    E.comm.reset(hc);
+    int rc = E.add_fasta(fasta);
+    if (rc) fprintf(stderr, "[emu rank %d] %s\n", rank, E.err.c_str());
+    // a failed load still has to take part in the collective finalize
+    rc = E.finalize();
+    if (!rc) rc = E.do_parse_bwt();
+    if (!rc && rank == 0) rc = E.save_parse(out, true, sa || rssa);
+    if (!rc) rc = E.build(sa, rssa);
+    if (!rc) rc = E.write_bwt_files(out, sa, rssa, "");
+    if (rc) { fprintf(stderr, "[emu rank %d] %s\n", rank, E.err.c_str()); return rc; }
+    if (info) {
+        info[0] = E.bwt.off; info[1] = E.bwt.len; info[2] = E.bwt.ssa_off; info[3] = E.bwt.ssa_cnt;
+        info[4] = E.bwt.esa_off; info[5] = E.bwt.esa_cnt; info[6] = E.bwt.r; info[7] = E.parse.P;
+    }
+    return 0;
+}

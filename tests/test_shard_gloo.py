@@ -1,0 +1,97 @@
+"""N>1 path of the single-job multi-GPU build on CPU: world_size-2/3 jobs whose
+exchanges run over torch.distributed/gloo.  The device pipeline is the serial logic emulator
+(tests/emu), so what is checked is the host logic of the sharded path -- piece boundaries and
+halos, the straddling phrase, the dictionary merge, rank renaming, key-range splitters, slice
+offsets, run boundaries across slices -- against the unmodified reference binary on the
+concatenated input (merge_pfp semantics: src/merge_pfp.cpp:153-155)."""
+import os
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from pfp_util import ROOT, ref_bin, run, write_fasta, pangenome_records, random_bases, nrun_records, exts_for, assert_same_files
+
+EMU_LIB = os.path.join(ROOT, "tests", "emu", "libpfb_emu.so")
+WORKER = os.path.join(ROOT, "tests", "shard_worker.py")
+
+pytestmark = pytest.mark.skipif(not os.path.exists(EMU_LIB) or ref_bin("pfbwt-f") is None,
+                                reason="emulator library or reference binaries not built")
+
+
+def free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def run_job(mode, tmp, pieces, w, p, bits, sa, rssa, non_acgt_to_a=False):
+    """pieces: list (one per rank) of record lists.  Returns (sharded prefix, reference prefix)."""
+    world = len(pieces)
+    allrecs = [r for pc in pieces for r in pc]
+    whole = os.path.join(tmp, "whole.fa")
+    write_fasta(whole, allrecs, line_width=70)
+    fas = []
+    for g, pc in enumerate(pieces):
+        fa = os.path.join(tmp, f"part{g}.fa")
+        write_fasta(fa, pc, line_width=70)
+        fas.append(fa)
+    refp = os.path.join(tmp, "ref")
+    cmd = [ref_bin("pfbwt-f64" if bits == 64 else "pfbwt-f"), "-w", str(w), "-p", str(p), "-o", refp]
+    if sa:
+        cmd.append("-s")
+    if rssa:
+        cmd.append("-r")
+    run(cmd + [whole])
+    out = os.path.join(tmp, "shard")
+    port = free_port()
+    procs = [subprocess.Popen([sys.executable, WORKER, mode, str(g), str(world), str(port), out, str(w), str(p), str(bits),
+                               str(int(sa)), str(int(rssa)), fas[g]], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+             for g in range(world)]
+    errs = []
+    for g, pr in enumerate(procs):
+        try:
+            _, e = pr.communicate(timeout=600)
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+        if pr.returncode != 0:
+            errs.append(f"rank {g} rc={pr.returncode}: {e.decode(errors='replace')[-1500:]}")
+    assert not errs, "\n".join(errs)
+    return out, refp
+
+
+def split_records(recs, world):
+    k = (len(recs) + world - 1) // world
+    return [recs[i * k:(i + 1) * k] for i in range(world)]
+
+
+@pytest.mark.parametrize("world,sa,rssa,bits", [(2, False, False, 32), (2, True, True, 32), (3, True, True, 64)])
+def test_pangenome_job(tmp_path, world, sa, rssa, bits):
+    recs = pangenome_records(6000, 6, 12, seed=11)
+    out, refp = run_job("emu", str(tmp_path), split_records(recs, world), 10, 100, bits, sa, rssa)
+    assert_same_files(out, refp, exts_for(sa, rssa))
+
+
+def test_random_job_small_modulus(tmp_path):
+    # p = 7: short phrases, many triggers next to the cuts, first trigger often inside the first w bytes
+    recs = [(f"r{i}", random_bases(3000 + 17 * i, 100 + i)) for i in range(4)]
+    out, refp = run_job("emu", str(tmp_path), split_records(recs, 2), 4, 7, 32, True, True)
+    assert_same_files(out, refp, exts_for(True, True))
+
+
+def test_rank_without_trigger(tmp_path):
+    # the middle rank's records hold no trigger at all (p large, tiny records): it owns no phrase and the
+    # phrase that starts on rank 0 runs across it into rank 2
+    big = [(f"b{i}", random_bases(20000, 7 + i)) for i in range(2)]
+    tiny = [("t0", np.frombuffer(b"ACGTTGCAAC", dtype=np.uint8))]
+    pieces = [[big[0]], tiny, [big[1]]]
+    whole_has_trigger = True
+    out, refp = run_job("emu", str(tmp_path), pieces, 10, 2000, 32, True, False)
+    assert whole_has_trigger
+    assert_same_files(out, refp, exts_for(True, False))
