@@ -113,6 +113,115 @@ def run_reference_sample(bases, sample_n):
     return sample_n / dt, dt, kind
 
 
+# ---- single job over all ranks (BASELINE.json configs[4] family) ----------------------
+JOB_HAPS, JOB_BASE, JOB_SNP_RATE = 10, 100_000_000, 0.001
+
+
+def gen_job_text(out, rank, haps, base_len):
+    """rank's records of the pangenome job: `haps` haplotypes of one base sequence (default_rng(2024)),
+    global haplotype H>0 carries 0.1 % substitutions at default_rng(5000+H) positions (drawn with replacement)."""
+    codes = np.random.default_rng(2024).integers(0, 4, base_len, dtype=np.uint8)
+    nsnp = int(base_len * JOB_SNP_RATE)
+    for h in range(haps):
+        H = rank * haps + h
+        c = codes
+        if H > 0:
+            rng = np.random.default_rng(5000 + H)
+            pos = rng.integers(0, base_len, nsnp)
+            c = codes.copy()
+            c[pos] = (c[pos] + rng.integers(1, 4, nsnp, dtype=np.uint8)) % 4
+        out[h * base_len:(h + 1) * base_len] = LUT[c]
+
+
+def single_job_leg(B, torch, dist, rank, local_rank, world, steps, warmup, haps, base_len, with_sa, do_e2e):
+    """One job over `world` GPUs: rank g holds haplotypes [g*haps, (g+1)*haps); pfbwt-f64 semantics
+    (-s when with_sa).  Returns the dict reported as "single_job" (rank 0) or None."""
+    n_rank = haps * base_len
+    host = torch.empty(n_rank, dtype=torch.uint8).pin_memory()
+    gen_job_text(host.numpy(), rank, haps, base_len)
+    rec_len = np.full(haps, base_len, dtype=np.uint64)
+    ctx = B.Context(device=local_rank, bits=64, w=W, p=PMOD, get_sai=with_sa)
+    if world > 1:
+        g = dist.new_group(backend="gloo")
+        ids = [B.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0, group=g)
+        ctx.shard_init_nccl(rank, world, ids[0])
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    ctx.add_records(host.data_ptr(), rec_len)
+    ctx.upload_text()
+    for _ in range(warmup):
+        ctx.run_resident(with_sa, False)
+    st0 = ctx.stats()
+    barrier()
+    dev_ms, acc = 0.0, {}
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        ctx.run_resident(with_sa, False)
+        st = ctx.stats()
+        dev_ms += st["run_ms"]
+        for k, v in st.items():
+            if k.endswith("_ms") and k not in ("run_ms", "radix_pass_ms"):
+                acc[k] = acc.get(k, 0.0) + v
+    barrier()
+    t_wall = time.perf_counter() - t0
+    st1 = ctx.stats()
+    sz, info = ctx.sizes(), ctx.shard_info()
+    t_e2e = float("nan")
+    h2d = d2h = 0
+    if do_e2e:
+        out_bwt = torch.empty(info.bwt_len + (info.bwt_len >> 2) + 4096, dtype=torch.uint8).pin_memory()
+        out_sa = torch.empty((info.bwt_len + (info.bwt_len >> 2) + 4096) if with_sa else 1, dtype=torch.int64).pin_memory()
+
+        def e2e_step():
+            ctx.clear()
+            ctx.add_records(host.data_ptr(), rec_len)
+            ctx.finalize()
+            ctx.bwt_of_parse()
+            ctx.generate_bwt(with_sa, False)
+            m = ctx.shard_info().bwt_len
+            ctx.bwt(out=out_bwt.numpy()[:m])
+            if with_sa:
+                ctx.sa(out=out_sa.numpy()[:m].view(np.uint64))
+            return m
+
+        e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            m = e2e_step()
+        barrier()
+        t_e2e = time.perf_counter() - t0
+        h2d, d2h = n_rank, m * (9 if with_sa else 1)
+    t = torch.tensor([dev_ms * 1e-3, t_wall, t_e2e], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    t_dev, t_wall, t_e2e = float(t[0]), float(t[1]), float(t[2])
+    ctx.close()
+    if rank != 0:
+        return None
+    n_tot = world * n_rank
+    return {
+        "workload": f"config5 family: ONE job, {world * haps} haplotypes x {base_len / 1e6:g} Mbp (0.1% substitutions), {haps} per GPU, "
+                    f"pfbwt-f64 -w {W} -p {PMOD}" + (" -s" if with_sa else ""),
+        "scaling": "weak", "value": n_tot * steps / t_dev, "unit": "bases/s", "ms_per_step": 1e3 * t_dev / steps,
+        "wall_ms_per_step": 1e3 * t_wall / steps,
+        "e2e": {"value": n_tot * steps / t_e2e if do_e2e else None, "unit": "bases/s", "ms_per_step": 1e3 * t_e2e / steps if do_e2e else None,
+                "h2d_bytes_per_step_rank0": int(h2d), "d2h_bytes_per_step_rank0": int(d2h)},
+        "n": int(sz.n), "phrases": int(sz.n_phrases), "dict_words": int(sz.n_words), "dict_bytes": int(sz.dict_bytes), "r": int(sz.r),
+        "rank0_slice": {"bwt_off": int(info.bwt_off), "bwt_len": int(info.bwt_len)},
+        "exchange": {"transport": "NCCL all-gather / grouped broadcast over NVLink" if world > 1 else "none",
+                     "bytes_received_rank0_per_step": int((st1["shard_bytes_moved"] - st0["shard_bytes_moved"]) / max(1, steps)),
+                     "exchange_ms_rank0": acc.get("shard_exchange_ms", 0.0) / steps, "merge_ms_rank0": acc.get("shard_merge_ms", 0.0) / steps},
+        "stages_ms_rank0": {k: v / steps for k, v in acc.items()},
+        "gpu_launches_rank0": int(st1["launches_own"] - st0["launches_own"]),
+    }
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -123,6 +232,10 @@ def main():
     ap.add_argument("--ref-sample", type=int, default=40_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling aid: skip the host-buffer leg")
+    ap.add_argument("--no-single-job", action="store_true", help="skip the one-job-over-all-GPUs leg")
+    ap.add_argument("--job-haps", type=int, default=JOB_HAPS)
+    ap.add_argument("--job-base", type=int, default=JOB_BASE)
+    ap.add_argument("--job-no-sa", action="store_true")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -233,6 +346,13 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         t_res, t_e2e, t_dev = float(t[0]), float(t[1]), float(t[2])
 
+    ctx.close()
+    del host, out_host
+    job = None
+    if not args.no_single_job:
+        job = single_job_leg(B, torch, dist, rank, local_rank, world, max(1, min(args.steps, 3)), max(1, min(args.warmup, 2)),
+                             args.job_haps, args.job_base, not args.job_no_sa, not args.no_e2e)
+
     if rank == 0:
         peak, peak_kind = hbm_peak()
         stage_ms = {k: v / args.steps for k, v in stage_acc.items()}
@@ -266,7 +386,8 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": "u8/u32/u64 integer", "data": "synthetic",
             "config": {"workload": workload, "n": int(sz.n), "phrases": int(sz.n_phrases), "dict_words": int(sz.n_words),
                        "dict_bytes": int(D), "r": int(sz.r), "l2": "inputs larger than L2 (text 1 GB, dictionary 1.1 GB per step)",
-                       "multi_gpu": "independent text per rank, no data-path collective" if world > 1 else "single GPU"},
+                       "multi_gpu": ("value/e2e: independent config-2 text per rank, no data-path collective; single_job: ONE job over all "
+                                     "ranks (piece-wise parse, NCCL all-gather merge, key-range partitioned suffix sort)") if world > 1 else "single GPU"},
             "e2e": {"value": world * n * args.steps / t_e2e, "unit": "bases/s", "h2d_bytes_per_step": int(n),
                     "d2h_bytes_per_step": int(n + W + 1), "ms_per_step": 1e3 * t_e2e / args.steps},
             "gpu_launches": int(launches), "gpu_launches_library_cub": int(launches_lib),
@@ -282,6 +403,8 @@ def main():
         }
         if cpu:
             line["cpu_baseline"] = cpu
+        if job:
+            line["single_job"] = job
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
