@@ -8,7 +8,7 @@ CSRC   := pfbwt-f_b200/csrc
 LIB    := pfbwt-f_b200/libpfbwt_b200.so
 BIN    := bin
 
-all: $(LIB) $(BIN)/pfbwt-f $(BIN)/pfbwt-f64 $(BIN)/merge_pfp emu
+all: $(LIB) $(BIN)/pfbwt-f $(BIN)/pfbwt-f64 $(BIN)/merge_pfp $(BIN)/shim_demo $(BIN)/shim_demo64 emu
 
 $(LIB): $(CSRC)/capi.cu $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/build.cuh $(CSRC)/dictkeys.cuh $(CSRC)/emit.cuh $(CSRC)/radix.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp $(CSRC)/comm.hpp $(CSRC)/shard.inl include/pfbwt_b200.h
 	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/capi.cu -lz -lcudart -ldl
@@ -22,6 +22,14 @@ $(BIN)/pfbwt-f64: pfbwt-f_b200/src/pfbwt-f.cpp $(LIB)
 $(BIN)/merge_pfp: pfbwt-f_b200/src/merge_pfp.cpp $(LIB)
 	mkdir -p $(BIN)
 	$(CXX) -std=c++17 -O2 -I include -o $@ $< -Lpfbwt-f_b200 -lpfbwt_b200 -Wl,-rpath,'$$ORIGIN/../pfbwt-f_b200'
+
+# a user-style driver compiled against the source-level shim of the reference's C++ API (tests/test_shim.py)
+$(BIN)/shim_demo: tests/shim/shim_main.cpp include/pfbwtf_shim.hpp $(LIB)
+	mkdir -p $(BIN)
+	$(CXX) -std=c++17 -O2 -Wall -I include -o $@ $< -Lpfbwt-f_b200 -lpfbwt_b200 -Wl,-rpath,'$$ORIGIN/../pfbwt-f_b200'
+$(BIN)/shim_demo64: tests/shim/shim_main.cpp include/pfbwtf_shim.hpp $(LIB)
+	mkdir -p $(BIN)
+	$(CXX) -std=c++17 -O2 -Wall -DM64=1 -I include -o $@ $< -Lpfbwt-f_b200 -lpfbwt_b200 -Wl,-rpath,'$$ORIGIN/../pfbwt-f_b200'
 
 # developer logic check (tests only; see tests/emu/emu_main.cpp)
 emu: tests/emu/pfb_emu tests/emu/libpfb_emu.so

@@ -119,6 +119,8 @@ int pfb_write_bwt(pfb_ctx *, const char *prefix, int sa, int rssa, const char *s
 
 /* ---- getters (PfParser getters include/pfparser.hpp:469-544; copies into caller buffers) ---- */
 int pfb_get_sizes(const pfb_ctx *, pfb_sizes *);
+/* bases (incl. the w-byte padding after each record) added since the last pfb_clear: PfParser::get_pos() - 1 before finalize */
+uint64_t pfb_get_pending_bases(const pfb_ctx *);
 int pfb_get_stats(const pfb_ctx *, pfb_stats *);
 int pfb_copy_dict(pfb_ctx *, uint8_t *out /* dict_bytes */);
 int pfb_copy_occ(pfb_ctx *, void *out /* n_words * bits/8 */);

@@ -16,7 +16,7 @@ EXPORTS = [
     "pfb_copy_parse", "pfb_copy_last", "pfb_copy_sai", "pfb_copy_bwlast", "pfb_copy_ilist", "pfb_copy_bwsai",
     "pfb_copy_bwt", "pfb_copy_sa", "pfb_copy_ssa", "pfb_copy_esa", "pfb_get_docs", "pfb_upload_text",
     "pfb_run_resident", "pfb_release_text", "pfb_clear",
-    "pfb_nccl_unique_id", "pfb_shard_init_nccl", "pfb_shard_init_host", "pfb_get_shard_info",
+    "pfb_nccl_unique_id", "pfb_shard_init_nccl", "pfb_shard_init_host", "pfb_get_shard_info", "pfb_get_pending_bases",
 ]
 
 

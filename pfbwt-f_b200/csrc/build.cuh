@@ -53,6 +53,39 @@ inline u64 compact_indices(const u8 *flags, u64 n, DevBuf<u32> &scratch_idx, Dev
 //     identically on every rank from the replicated dictionary); *n_sorted = how many those are.
 struct ShardSpec { int rank = 0, world = 1; };
 
+// ---- pivot rounds: refinement of LONG ties (repetitive dictionaries: variant phrases of a pangenome
+// share suffixes of hundreds of symbols, which rounds of <= 26 symbols close far too slowly) ----------
+// Every member of an open tie group is compared byte by byte with the group's first member (the
+// pivot), both read from the group's depth on.  With l = common length and c = the member's byte at
+// the mismatch, the group is ordered in ONE sort by
+//     less than pivot:  (0, l, c)         -- a shorter common prefix with the pivot sorts first
+//     identical:        (1, 0, 0) closed  -- equal up to and including EndOfWord
+//     greater:          (2, LMAX - l, c)  -- a longer common prefix sorts first
+// and members with equal keys are tied on l+1 more symbols (a new, smaller group).  Comparisons
+// stop after PIVOT_CAP symbols ("clamped": stays tied with the pivot, continues next round).
+static const int PIVOT_LBITS = 12;
+static const u32 PIVOT_CAP = (1u << PIVOT_LBITS) - 1;
+PFB_HD inline u64 pivot_key(const u8 *dict, u64 D, u64 a, u64 p) {
+    u32 l = 0;
+    for (; l < PIVOT_CAP; ++l) {
+        const u32 x = a + l < D ? dict[a + l] : 0u, y = p + l < D ? dict[p + l] : 0u;
+        if (x != y) {
+            const u64 side = x < y ? 0ull : 2ull;
+            const u64 lf = x < y ? (u64)l : (u64)(PIVOT_CAP - l);
+            return (side << (PIVOT_LBITS + 4)) | (lf << 4) | ((u64)sym3_fast(x) << 1);
+        }
+        if (x <= 1u) return (1ull << (PIVOT_LBITS + 4)) | 1ull;          // identical strings: closed
+    }
+    return (1ull << (PIVOT_LBITS + 4)) | (1ull << 1);                    // clamped: open, tied with the pivot
+}
+// symbols consumed by the occupant of a slot after a pivot round
+PFB_HD inline u32 pivot_consumed(u64 key) {
+    const u32 side = (u32)(key >> (PIVOT_LBITS + 4)) & 3u, lf = (u32)(key >> 4) & PIVOT_CAP;
+    if (side == 0) return lf + 1;
+    if (side == 2) return (PIVOT_CAP - lf) + 1;
+    return (key & 1) ? 0u : PIVOT_CAP;
+}
+
 inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, DevBuf<u8> &meta, DevBuf<u32> &cnt, const WordLookup &wl,
                               bool *reclassify, Workspace &ws, StageTimes &tm, Timer &timer, std::string &err,
                               const ShardSpec *sh = nullptr, u64 *n_sorted = nullptr) {
@@ -132,7 +165,16 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
     // a rank that holds only its key range cannot switch to prefix doubling (rank[] of all suffixes):
     // it keeps extending; phrases of ordinary length close within a few dozen rounds
     const u32 shard_rounds = 1u << 16;
-    while (m && (rounds < max_ext_rounds || (!knob && m <= small_set && rounds < max_small_rounds) || (sh && rounds < shard_rounds))) {
+    // pivot rounds take over when a large set is still open after two window rounds (long ties); they stop
+    // when many comparisons hit the cap (self-overlapping repeats such as poly-A: prefix doubling is the tool)
+    int pivot_knob = -1;
+    if (const char *e = getenv("PFB_PIVOT")) pivot_knob = atoi(e);         // test knob: 1 = pivot rounds from the start, 0 = never
+    bool pivot_ok = pivot_knob != 0;
+    u32 pivot_rounds = 0;
+    const u32 max_pivot_rounds = 64;
+    auto want_pivot = [&]() { return pivot_ok && pivot_rounds < max_pivot_rounds && (pivot_knob == 1 || (rounds >= 2 && m > small_set)); };
+    while (m && (want_pivot() || rounds < max_ext_rounds || (!knob && m <= small_set && rounds < max_small_rounds) || (sh && rounds < shard_rounds))) {
+        const bool pivot = want_pivot();
         // dense group ids inside the active list (whole groups are active, so the
         // first listed member of a group is its head)
         DevBuf<u8> ah(m);
@@ -149,7 +191,26 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
         const int ebits = enum_bits(L2);
         DevBuf<u64> k2(m), k2b(m);
         DevBuf<u32> v(m), vb(m);
-        {
+        const int kshift = pivot ? 1 : 6;                       // bits below the part of the key that orders / separates
+        const int kbits = pivot ? PIVOT_LBITS + 6 : 6 + ebits;    // bits below the group id
+        DevBuf<u32> clamped(1);
+        if (pivot) {
+            dev_memset(clamped.get(), 0, 4, st);
+            DevBuf<u32> hslot(G + 1);                           // list slot of every group's first member
+            const u32 *ap = apos.get(); const u8 *a_ = ah.get(); const u32 *gi = gidx.get(); const u32 *sp = sa.get();
+            const u32 *dp = adep.get();
+            u64 *kp = k2.get(); u32 *vp = v.get(); u32 *hs = hslot.get(); u32 *cl = clamped.get();
+            launch_for(m, st, PFB_LAMBDA(u64 a) { if (a_[a]) hs[gi[a]] = (u32)a; });
+            launch_for(m, st, PFB_LAMBDA(u64 a) {
+                u64 gid = (u64)gi[a] + a_[a] - 1;
+                u32 idx = sp[ap[a]];
+                vp[a] = idx;
+                u32 h = hs[gid];
+                u64 pk = pivot_key(dict, D, (u64)idx + dp[a], (u64)sp[ap[h]] + dp[h]);
+                if (!(pk & 1) && ((pk >> (PIVOT_LBITS + 4)) & 3) == 1) atomic_add(cl, 1u);
+                kp[a] = (gid << (PIVOT_LBITS + 6)) | pk;
+            });
+        } else {
             const u32 *ap = apos.get(); const u8 *a_ = ah.get(); const u32 *gi = gidx.get(); const u32 *sp = sa.get();
             const u32 *dp = adep.get();
             u64 *kp = k2.get(); u32 *vp = v.get();
@@ -161,23 +222,27 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
                 kp[a] = (gid << (6 + ebits)) | (e.code << 6) | ((u64)e.consumed << 1) | (e.closed ? 1ull : 0ull);
             });
         }
-        sort_pairs(k2, k2b, v, vb, m, 6, 6 + ebits + gbits, ws.sc, st);
+        sort_pairs(k2, k2b, v, vb, m, kshift, kbits + gbits, ws.sc, st);
+        if (pivot) {
+            ++pivot_rounds;
+            if ((u64)read_scalar(clamped.get(), st) * 8 > m) pivot_ok = false;      // mostly self-overlapping repeats
+        }
         DevBuf<u8> act2(m);
         {
             const u32 *ap = apos.get(); const u64 *kp = k2.get(); const u32 *vp = v.get();
             u32 *sp = sa.get(); u8 *ac = act2.get(); u32 *dp = adep.get(); u32 *cp = cnt.get();
             const WordLookup w3 = wl; const u64 w64 = (u64)w;
             launch_for(m, st, PFB_LAMBDA(u64 a) {
-                u64 k = kp[a] >> 6;
-                bool head = a == 0 || k != (kp[a - 1] >> 6);
-                bool last = a + 1 == m || k != (kp[a + 1] >> 6);
+                u64 k = kp[a] >> kshift;
+                bool head = a == 0 || k != (kp[a - 1] >> kshift);
+                bool last = a + 1 == m || k != (kp[a + 1] >> kshift);
                 u32 j = ap[a];
                 sp[j] = vp[a];
                 u32 c, ib, sl;
                 u32 vf = suffix_class(w3, vp[a], w64, c, ib, sl);         // what travels with the suffix: count, valid/full bits,
                 cp[j] = c;                                                 // and the preceding-byte code
                 mt[j] = (u8)(prev_code(dict, vp[a]) | (head ? M_HEAD : 0) | vf);
-                dp[a] += (u32)(kp[a] >> 1) & 31u;                             // slot a stays inside its old group: same depth so far
+                dp[a] += pivot ? pivot_consumed(kp[a]) : ((u32)(kp[a] >> 1) & 31u);   // slot a stays inside its old group: same depth so far
                 ac[a] = (!(head && last) && !(kp[a] & 1)) ? 1 : 0;
             });
         }
@@ -192,7 +257,7 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
         adep = std::move(adep2);
         m = m2;
         ++rounds;
-        timer.lap("K6 extension round");
+        timer.lap(pivot ? "K6 pivot round" : "K6 extension round");
     }
     if (m && sh) { err = "dictionary repeats too long for the range-partitioned suffix sort (use the single-GPU path)"; return PFB_ERR_LIMIT; }
     if (m) {

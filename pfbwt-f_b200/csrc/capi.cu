@@ -168,6 +168,7 @@ int pfb_get_sizes(const pfb_ctx *c, pfb_sizes *s) {
     }
     return PFB_OK;
 }
+uint64_t pfb_get_pending_bases(const pfb_ctx *c) { return c ? c->eng.pending_n : 0; }
 int pfb_get_stats(const pfb_ctx *c, pfb_stats *s) {
     if (!c || !s) return PFB_ERR_ARG;
     const pfb::StageTimes &t = c->eng.tm;

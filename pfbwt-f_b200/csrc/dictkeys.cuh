@@ -151,7 +151,7 @@ template <int MODE>
 __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict__ dict, u64 D, int L, u64 *__restrict__ key,
                                                             WordLookup wl, const u32 *__restrict__ occ, int w, KeyExtra kx, KeySelect ks) {
     __shared__ __align__(16) u8 sb[KEYS_TILE + 48];
-    __shared__ u64 sk[KEYS_TILE];
+    __shared__ u64 sk[KEYS_TILE + KEYS_TILE / 8];      // one pad slot per 8 keys: a thread's 8 consecutive keys spread over banks
     const u64 tile = MODE == 1 ? (u64)blockIdx.x * ks.tile_stride : (u64)blockIdx.x;
     const u64 base = tile * KEYS_TILE;
     for (int o = threadIdx.x * 16; o < KEYS_TILE + 48; o += 256 * 16) {
@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict
         const bool full = i == 0 || (i > 1 && pcs[p] == 0) ;       // preceded by EndOfWord (or the very first byte)
         u64 c = (valid && d < wl.Dw) ? (u64)occ[d] : 0ull;
         const u64 kk = pack_key(code, j < L ? (u32)j + 1 : (u32)L, j < L && kind == 0, pc) | kx.pack(c, valid && full);
-        if (MODE == 0) sk[i0 + p] = kk;
+        if (MODE == 0) sk[i0 + p + (i0 >> 3)] = kk;
         else {
             const bool sel = valid && d < wl.Dw && i < D && code >= ks.lo && code < ks.hi;
             if (MODE == 1) { if (valid && d < wl.Dw && i < D) atomic_add(&ks.hist[code >> ks.hshift], 4ull + c); }
@@ -221,7 +221,7 @@ __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict
         for (int k = 0; k < 8; ++k) {
             int o = k * 256 + threadIdx.x;
             u64 g = base + (u64)o;
-            if (g < D) key[g] = sk[o];
+            if (g < D) key[g] = sk[o + (o >> 3)];
         }
     } else if (MODE >= 2) {
         // ordered compaction inside the tile: exclusive scan of the per-thread selected counts

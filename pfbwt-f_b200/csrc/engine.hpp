@@ -319,6 +319,8 @@ struct Engine {
             if (!rhs.parsed) return fail(PFB_ERR_ARG, "rhs parse not finalized");
             if (rhs.prm.w != prm.w) return fail(PFB_ERR_ARG, "invalid w");
             if (rhs.prm.p != prm.p) return fail(PFB_ERR_ARG, "invalid p");
+            // a parser that was loaded from files holds no text: its own parse becomes the first segment
+            if (&rhs != this && parsed && segs.empty() && pending_n == 0) { int rc0 = append_parse_of(*this); if (rc0) return rc0; }
             const DeviceParse &rp = rhs.parse;
             const u64 P = rp.P; const int w = prm.w;
             DevBuf<u64> clen(P + 1), coff(P + 1);

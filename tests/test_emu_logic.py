@@ -72,3 +72,22 @@ def test_emu_tie_refinement_paths(ext_rounds, emu, ref_bins, datadir):
     env = dict(os.environ, PFB_EXT_ROUNDS=ext_rounds)
     subprocess.run([emu, "--bits", "64"] + flags + ["-o", b, fa], check=True, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
     assert_same_files(a, b, exts_for(True, True))
+
+
+@pytest.mark.parametrize("pivot,key_syms", [("1", "19"), ("1", "3"), ("0", "3")])
+def test_emu_pivot_rounds(pivot, key_syms, emu, ref_bins, datadir):
+    """long ties (variant phrases of a pangenome) are refined by pivot rounds: every member of a tie group is
+    compared with the group's first member and the group is ordered in one sort (build.cuh).  PFB_PIVOT=1
+    forces them from the first round, PFB_KEY_SYMS=3 makes nearly every suffix start out tied; the N-run
+    record exercises the comparison cap (poly-A) and the hand-over to prefix doubling."""
+    fa = os.path.join(datadir, "e_pivot.fa")
+    recs = pangenome_records(30_000, 8, 120, 19) + nrun_records(1, 30_000, 12, big_run=9000)
+    write_fasta(fa, recs, line_width=70)
+    a, b = os.path.join(datadir, "e_pivot.port"), os.path.join(datadir, f"e_pivot.emu{pivot}{key_syms}")
+    flags = ["-s", "-r", "--non-acgt-to-a"]
+    if not os.path.exists(a + ".bwt"):
+        run([ref_bins["pfp_oracle"], "--bits", "64"] + flags + ["-o", a, fa])
+    env = dict(os.environ, PFB_PIVOT=pivot, PFB_KEY_SYMS=key_syms)
+    r = subprocess.run([emu, "--bits", "64"] + flags + ["-o", b, fa], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    assert r.returncode == 0, r.stderr.decode()[-2000:]
+    assert_same_files(a, b, exts_for(True, True))

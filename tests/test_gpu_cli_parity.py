@@ -80,3 +80,21 @@ def test_cli_invalid_char_exits_1(datadir):
     r = run([os.path.join(BIN, "pfbwt-f"), fa], check=False)
     assert r.returncode == 1
     assert b"error, invalid character 82/R -> 5" in r.stderr
+
+
+@pytest.mark.parametrize("env", [{"PFB_PIVOT": "1"}, {"PFB_PIVOT": "1", "PFB_KEY_SYMS": "3"}, {"PFB_PIVOT": "0"}],
+                         ids=["pivot", "pivot_keysyms3", "nopivot"])
+def test_cli_pivot_rounds(env, ref_bins, datadir):
+    """tie refinement by pivot rounds (build.cuh): forced from the first round / on nearly all suffixes / off"""
+    fa = os.path.join(datadir, "pivot.fa")
+    recs = pangenome_records(200_000, 10, 600, 19) + nrun_records(1, 60_000, 12, big_run=15000)
+    write_fasta(fa, recs, line_width=70)
+    flags = ["-s", "-r", "--non-acgt-to-a"]
+    a, b = os.path.join(datadir, "pivot.ref"), os.path.join(datadir, "pivot.gpu" + "".join(env.values()))
+    if not os.path.exists(a + ".bwt"):
+        run(oracle_cmd(ref_bins, 64, flags, a, fa))
+    import subprocess
+    r = subprocess.run([os.path.join(BIN, "pfbwt-f64")] + flags + ["-o", b, fa], env=dict(os.environ, **env),
+                       stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    assert r.returncode == 0, r.stderr.decode()[-2000:]
+    assert_same_files(a, b, exts_for(True, True))
