@@ -65,16 +65,39 @@ struct ShardSpec { int rank = 0, world = 1; };
 // stop after PIVOT_CAP symbols ("clamped": stays tied with the pivot, continues next round).
 static const int PIVOT_LBITS = 12;
 static const u32 PIVOT_CAP = (1u << PIVOT_LBITS) - 1;
+// 8 dictionary bytes starting at any position (little endian), from two aligned words
+PFB_HD inline u64 load8_unaligned(const u8 *dict, u64 pos) {
+    const u64 *w = reinterpret_cast<const u64 *>(dict + (pos & ~7ull));
+    const u32 sh = (u32)(pos & 7) * 8;
+    const u64 lo = w[0];
+    return sh ? (lo >> sh) | (w[1] << (64 - sh)) : lo;
+}
+PFB_HD inline u64 pivot_key_result(u32 l, u32 x, u32 y) {
+    if (x == y) return (1ull << (PIVOT_LBITS + 4)) | 1ull;               // identical up to and including EndOfWord: closed
+    const u64 side = x < y ? 0ull : 2ull;
+    const u64 lf = x < y ? (u64)l : (u64)(PIVOT_CAP - l);
+    return (side << (PIVOT_LBITS + 4)) | (lf << 4) | ((u64)sym3_fast(x) << 1);
+}
 PFB_HD inline u64 pivot_key(const u8 *dict, u64 D, u64 a, u64 p) {
     u32 l = 0;
+    // 8 symbols per step while both windows (and the second aligned word behind them) lie inside the dictionary
+    const u64 hi = a > p ? a : p;
+    while (l + 8 <= PIVOT_CAP && hi + l + 16 <= D) {
+        const u64 x = load8_unaligned(dict, a + l), y = load8_unaligned(dict, p + l);
+        const u64 d = x ^ y;
+        const u64 e = (x - 0x0202020202020202ull) & ~x & 0x8080808080808080ull;      // lowest set bit: first byte < 2 (EndOfWord / EndOfDict)
+        if (d | e) {
+            const u64 ev = (d ? d & (0 - d) : ~0ull), ee = (e ? e & (0 - e) : ~0ull);   // lowest set bits
+            // the first event decides: a differing byte (also when that byte is EndOfWord on one side), else a common terminator
+            const u64 first = ev < ee ? ev : ee;
+            const u32 b = (u32)(63 - clz64(first)) >> 3;
+            return pivot_key_result(l + b, (u32)(x >> (8 * b)) & 0xffu, (u32)(y >> (8 * b)) & 0xffu);
+        }
+        l += 8;
+    }
     for (; l < PIVOT_CAP; ++l) {
         const u32 x = a + l < D ? dict[a + l] : 0u, y = p + l < D ? dict[p + l] : 0u;
-        if (x != y) {
-            const u64 side = x < y ? 0ull : 2ull;
-            const u64 lf = x < y ? (u64)l : (u64)(PIVOT_CAP - l);
-            return (side << (PIVOT_LBITS + 4)) | (lf << 4) | ((u64)sym3_fast(x) << 1);
-        }
-        if (x <= 1u) return (1ull << (PIVOT_LBITS + 4)) | 1ull;          // identical strings: closed
+        if (x != y || x <= 1u) return pivot_key_result(l, x, y);
     }
     return (1ull << (PIVOT_LBITS + 4)) | (1ull << 1);                    // clamped: open, tied with the pivot
 }
@@ -172,7 +195,9 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
     bool pivot_ok = pivot_knob != 0;
     u32 pivot_rounds = 0;
     const u32 max_pivot_rounds = 64;
-    auto want_pivot = [&]() { return pivot_ok && pivot_rounds < max_pivot_rounds && (pivot_knob == 1 || (rounds >= 2 && m > small_set)); };
+    // ... right away when a large part of the dictionary is tied after the main sort (repetitive dictionary), else
+    // after two window rounds (short random ties are cheaper to close with windows)
+    auto want_pivot = [&]() { return pivot_ok && pivot_rounds < max_pivot_rounds && (pivot_knob == 1 || rounds >= 2 || m > N / 16); };
     while (m && (want_pivot() || rounds < max_ext_rounds || (!knob && m <= small_set && rounds < max_small_rounds) || (sh && rounds < shard_rounds))) {
         const bool pivot = want_pivot();
         // dense group ids inside the active list (whole groups are active, so the
