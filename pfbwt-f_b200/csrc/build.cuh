@@ -63,20 +63,12 @@ struct ShardSpec { int rank = 0, world = 1; };
 //     greater:          (2, LMAX - l, c)  -- a longer common prefix sorts first
 // and members with equal keys are tied on l+1 more symbols (a new, smaller group).  Comparisons
 // stop after PIVOT_CAP symbols ("clamped": stays tied with the pivot, continues next round).
-static const int PIVOT_LBITS = 12;
-static const u32 PIVOT_CAP = (1u << PIVOT_LBITS) - 1;
 // 8 dictionary bytes starting at any position (little endian), from two aligned words
 PFB_HD inline u64 load8_unaligned(const u8 *dict, u64 pos) {
     const u64 *w = reinterpret_cast<const u64 *>(dict + (pos & ~7ull));
     const u32 sh = (u32)(pos & 7) * 8;
     const u64 lo = w[0];
     return sh ? (lo >> sh) | (w[1] << (64 - sh)) : lo;
-}
-PFB_HD inline u64 pivot_key_result(u32 l, u32 x, u32 y) {
-    if (x == y) return (1ull << (PIVOT_LBITS + 4)) | 1ull;               // identical up to and including EndOfWord: closed
-    const u64 side = x < y ? 0ull : 2ull;
-    const u64 lf = x < y ? (u64)l : (u64)(PIVOT_CAP - l);
-    return (side << (PIVOT_LBITS + 4)) | (lf << 4) | ((u64)sym3_fast(x) << 1);
 }
 PFB_HD inline u64 pivot_key(const u8 *dict, u64 D, u64 a, u64 p) {
     u32 l = 0;
@@ -101,14 +93,6 @@ PFB_HD inline u64 pivot_key(const u8 *dict, u64 D, u64 a, u64 p) {
     }
     return (1ull << (PIVOT_LBITS + 4)) | (1ull << 1);                    // clamped: open, tied with the pivot
 }
-// symbols consumed by the occupant of a slot after a pivot round
-PFB_HD inline u32 pivot_consumed(u64 key) {
-    const u32 side = (u32)(key >> (PIVOT_LBITS + 4)) & 3u, lf = (u32)(key >> 4) & PIVOT_CAP;
-    if (side == 0) return lf + 1;
-    if (side == 2) return (PIVOT_CAP - lf) + 1;
-    return (key & 1) ? 0u : PIVOT_CAP;
-}
-
 inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, DevBuf<u8> &meta, DevBuf<u32> &cnt, const WordLookup &wl,
                               bool *reclassify, Workspace &ws, StageTimes &tm, Timer &timer, std::string &err,
                               const ShardSpec *sh = nullptr, u64 *n_sorted = nullptr) {

@@ -338,6 +338,37 @@ PFB_HD inline u64 pack_syms(const u8 *p, u64 len, u64 off, int cnt) {
     return key;
 }
 
+// ---- pivot keys (shared by the phrase sort below and the dictionary suffix sort of build.cuh) ----------
+// A member of a tie group is compared with the group's first member (the pivot) from the group's depth on;
+// l = common length, x / y = the member's / pivot's byte at the first difference (0 = string ended).
+static const int PIVOT_LBITS = 12;
+static const u32 PIVOT_CAP = (1u << PIVOT_LBITS) - 1;
+PFB_HD inline u64 pivot_key_result(u32 l, u32 x, u32 y) {
+    if (x == y) return (1ull << (PIVOT_LBITS + 4)) | 1ull;               // identical up to and including EndOfWord: closed
+    const u64 side = x < y ? 0ull : 2ull;
+    const u64 lf = x < y ? (u64)l : (u64)(PIVOT_CAP - l);
+    return (side << (PIVOT_LBITS + 4)) | (lf << 4) | ((u64)sym3((u8)x) << 1);
+}
+// symbols consumed by the occupant of a slot after a pivot round
+PFB_HD inline u32 pivot_consumed(u64 key) {
+    const u32 side = (u32)(key >> (PIVOT_LBITS + 4)) & 3u, lf = (u32)(key >> 4) & PIVOT_CAP;
+    if (side == 0) return lf + 1;
+    if (side == 2) return (PIVOT_CAP - lf) + 1;
+    return (key & 1) ? 0u : PIVOT_CAP;
+}
+
+// strings buf[sa, sa+la) and buf[sp, sp+lp), compared from offset `depth` on
+PFB_HD inline u64 pivot_key_len(const u8 *buf, u64 sa, u64 la, u64 sp, u64 lp, u64 depth) {
+    const u64 ra = la > depth ? la - depth : 0, rp = lp > depth ? lp - depth : 0;
+    const u64 mn = ra < rp ? ra : rp;
+    const u8 *x = buf + sa + depth, *y = buf + sp + depth;
+    u32 l = 0;
+    for (; l < PIVOT_CAP && l < mn; ++l)
+        if (x[l] != y[l]) return pivot_key_result(l, x[l], y[l]);
+    if (l >= PIVOT_CAP) return (1ull << (PIVOT_LBITS + 4)) | (1ull << 1);       // clamped
+    return pivot_key_result(l, ra > l ? x[l] : 0u, rp > l ? y[l] : 0u);         // both ended: identical (closed)
+}
+
 struct Workspace {
     Scratch sc;
     pfbStream_t st = 0;
@@ -393,19 +424,26 @@ inline int sort_strings(const u8 *Tp, Str str, DevBuf<u32> &order, u64 Dw, Works
         const u64 *ka = key_a.get(); u8 *fl = flag.get();
         launch_for(Dw, st, PFB_LAMBDA(u64 j) { fl[j] = (j == 0 || ka[j] != ka[j - 1]) ? 1 : 0; });
     }
-    u64 depth = 21;
-    u32 rounds = 1;
+    // dep[j]: symbols on which the string at sorted position j is known to agree with its tie group
+    // (uniform over a group; ~0 = member of a closed group of identical strings)
+    const u32 CLOSED = 0xFFFFFFFFu;
+    DevBuf<u32> dep(Dw);
+    { u32 *dp = dep.get(); launch_for(Dw, st, PFB_LAMBDA(u64 j) { dp[j] = 21u; }); }
+    u32 rounds = 1, pivot_rounds = 0;
+    int pivot_knob = -1;
+    if (const char *e = getenv("PFB_PIVOT")) pivot_knob = atoi(e);          // test knob (see build.cuh)
     DevBuf<u8> act(Dw), acthead(Dw);
     DevBuf<u32> aidx(Dw), gidx(Dw);
     for (;;) {
         {
-            const u8 *fl = flag.get(); u8 *ac = act.get(); u8 *ah = acthead.get(); const u32 *ord = order.get();
+            const u8 *fl = flag.get(); u8 *ac = act.get(); u8 *ah = acthead.get(); const u32 *ord = order.get(); const u32 *dp = dep.get();
             launch_for(Dw, st, PFB_LAMBDA(u64 j) {
                 bool single = fl[j] && (j + 1 == Dw || fl[j + 1]);
-                if (dups && !single) {      // tied on `depth` symbols and exhausted: identical strings (uniform over the group)
+                if (!single && dp[j] == CLOSED) single = true;
+                if (dups && !single) {      // tied on dep symbols and exhausted: identical strings (uniform over the group)
                     u64 s, len;
                     str(ord[j], s, len);
-                    single = len <= depth;
+                    single = len <= (u64)dp[j];
                 }
                 ac[j] = single ? 0 : 1;
                 ah[j] = (!single && fl[j]) ? 1 : 0;
@@ -415,16 +453,22 @@ inline int sort_strings(const u8 *Tp, Str str, DevBuf<u32> &order, u64 Dw, Works
         if (m == 0) break;
         u64 G = scan_flags(acthead.get(), gidx.get(), Dw, ws);
         int gbits = bits_for(G ? G - 1 : 0);
+        // long ties (variant phrases of a pangenome differ hundreds of symbols in): pivot rounds, as in the
+        // dictionary suffix sort (build.cuh) - the whole group is ordered by one comparison with its first member
+        const bool pivot = pivot_knob != 0 && pivot_rounds < 4096 && (pivot_knob == 1 || rounds >= 2 || m > Dw / 8);
         int nsym = (63 - gbits) / 3;
         if (nsym > 21) nsym = 21;
-        if (nsym < 1) { err = "phrase sort: too many tie groups"; return PFB_ERR_INTERNAL; }
+        if (nsym < 1 || gbits + PIVOT_LBITS + 6 > 64) { err = "phrase sort: too many tie groups"; return PFB_ERR_INTERNAL; }
         if (rounds > 200000) { err = "phrase sort: distinct phrases share a prefix longer than supported"; return PFB_ERR_LIMIT; }
         DevBuf<u32> apos(m), aval(m), aval_b(m);
         DevBuf<u64> akey(m), akey_b(m);
         {
             const u8 *ac = act.get(); const u8 *fl = flag.get();
-            const u32 *ai = aidx.get(); const u32 *gi = gidx.get(); const u32 *ord = order.get();
+            const u32 *ai = aidx.get(); const u32 *gi = gidx.get(); const u32 *ord = order.get(); const u32 *dp = dep.get();
             u32 *ap = apos.get(); u32 *av = aval.get(); u64 *ak = akey.get();
+            DevBuf<u32> hpos(pivot ? G + 1 : 1);                 // sorted position of every group's first member
+            u32 *hp = hpos.get();
+            if (pivot) launch_for(Dw, st, PFB_LAMBDA(u64 j) { if (ac[j] && fl[j]) hp[gi[j]] = (u32)j; });
             launch_for(Dw, st, PFB_LAMBDA(u64 j) {
                 if (!ac[j]) return;
                 u32 a = ai[j];
@@ -433,20 +477,28 @@ inline int sort_strings(const u8 *Tp, Str str, DevBuf<u32> &order, u64 Dw, Works
                 u64 s, len;
                 str(k, s, len);
                 ap[a] = (u32)j; av[a] = (u32)k;
-                ak[a] = (gid << (3 * nsym)) | pack_syms(Tp + s, len, depth, nsym);
+                if (pivot) {
+                    u64 ps, pl;
+                    str(ord[hp[gid]], ps, pl);
+                    ak[a] = (gid << (PIVOT_LBITS + 6)) | pivot_key_len(Tp, s, len, ps, pl, dp[j]);
+                } else ak[a] = (gid << (3 * nsym)) | pack_syms(Tp + s, len, dp[j], nsym);
             });
         }
-        sort_pairs(akey, akey_b, aval, aval_b, m, 0, gbits + 3 * nsym, ws.sc, st);
+        sort_pairs(akey, akey_b, aval, aval_b, m, pivot ? 1 : 0, pivot ? gbits + PIVOT_LBITS + 6 : gbits + 3 * nsym, ws.sc, st);
         {
             const u32 *ap = apos.get(); const u32 *av = aval.get(); const u64 *ak = akey.get();
-            u32 *ord = order.get(); u8 *fl = flag.get();
+            u32 *ord = order.get(); u8 *fl = flag.get(); u32 *dp = dep.get();
+            const int ks = pivot ? 1 : 0;
             launch_for(m, st, PFB_LAMBDA(u64 a) {
                 u32 j = ap[a];
                 ord[j] = av[a];
-                fl[j] = (a == 0 || ak[a] != ak[a - 1]) ? 1 : 0;
+                fl[j] = (a == 0 || (ak[a] >> ks) != (ak[a - 1] >> ks)) ? 1 : 0;
+                // position j stays inside its old group, so dp[j] still holds that group's depth
+                if (!pivot) dp[j] += (u32)nsym;
+                else dp[j] = (ak[a] & 1) ? CLOSED : dp[j] + pivot_consumed(ak[a]);
             });
         }
-        depth += (u64)nsym;
+        if (pivot) ++pivot_rounds;
         ++rounds;
     }
     if (rounds_out) *rounds_out = rounds;

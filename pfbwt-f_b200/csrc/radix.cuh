@@ -15,7 +15,7 @@
 //   materialised.
 //
 // HBM traffic per pass: 12 B read + 12 B written per pair (first pass with iota values: 8 B read)
-// + 3 x 8 B x 256 look-back words per 3072-pair tile (8 %).
+// + 3 x 8 B x 256 look-back words per 5120-pair tile (5 %).
 #pragma once
 
 namespace pfb {
@@ -28,7 +28,7 @@ struct RxCfg {
     static const int NT = NT_, IPT = IPT_, MINB = MINB_, MATCH = MATCH_, NW = NT_ / 32, TILE = NT_ * IPT_;
     static const size_t SMEM = (size_t)NW * RX_R * 4 + (size_t)TILE * 8 + (size_t)TILE * 4 + (size_t)RX_R * 8 + (size_t)RX_R * 4 + 16 * 8;
 };
-typedef RxCfg<256, 12, 4, 0> RxDefault;   // best of the tools/bench_radix.cu sweep on B200 (no spills, 4 CTAs/SM)
+typedef RxCfg<256, 20, 3, 0> RxDefault;   // best of the tools/bench_radix.cu sweep on B200 with full-tile specialisation (5120-pair tiles, 3 CTAs/SM)
 static const int RX_MAX_PASSES = 8;
 
 __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long *p) {
@@ -89,8 +89,9 @@ __device__ __forceinline__ unsigned rx_peers(unsigned d) {
     return peers;
 }
 
-template <bool IOTA, class C>
-__global__ void __launch_bounds__(C::NT, C::MINB) k_radix_pass(RadixPassArgs a) {
+// FULL: the tile holds RX_TILE pairs (all but the last tile of a pass): no per-item bounds checks
+template <bool IOTA, class C, bool FULL>
+__device__ void rx_pass_body(const RadixPassArgs &a, const unsigned long long tile, const int tile_n_rt) {
     constexpr int RX_NT = C::NT, RX_IPT = C::IPT, RX_NW = C::NW, RX_TILE = C::TILE;
     extern __shared__ __align__(16) unsigned char rx_smem[];
     unsigned *whist = reinterpret_cast<unsigned *>(rx_smem);                                   // [RX_NW][RX_R]
@@ -99,22 +100,16 @@ __global__ void __launch_bounds__(C::NT, C::MINB) k_radix_pass(RadixPassArgs a) 
     unsigned long long *gbase = reinterpret_cast<unsigned long long *>(svals + RX_TILE);       // [RX_R]
     unsigned *dstart = reinterpret_cast<unsigned *>(gbase + RX_R);                             // [RX_R]
     unsigned long long *wsum = reinterpret_cast<unsigned long long *>(dstart + RX_R);          // [RX_NW]
-    __shared__ unsigned s_tile;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    if (tid == 0) s_tile = atomicAdd(a.tile_counter, 1u);
-    for (int i = tid; i < RX_NW * RX_R; i += RX_NT) whist[i] = 0;
-    __syncthreads();
-    const unsigned long long tile = s_tile;
     const unsigned long long base = tile * RX_TILE;
-    const unsigned long long left = a.n - base;
-    const int tile_n = left < (unsigned long long)RX_TILE ? (int)left : RX_TILE;
+    const int tile_n = FULL ? RX_TILE : tile_n_rt;
 
     unsigned long long key[RX_IPT];
     unsigned val[RX_IPT], rank[RX_IPT];
 #pragma unroll
     for (int j = 0; j < RX_IPT; ++j) {
         const int li = w * 32 * RX_IPT + j * 32 + lane;
-        if (li < tile_n) {
+        if (FULL || li < tile_n) {
             key[j] = a.kin[base + li];
             val[j] = IOTA ? (unsigned)(base + li) : a.vin[base + li];
         } else { key[j] = ~0ull; val[j] = 0; }
@@ -126,9 +121,9 @@ __global__ void __launch_bounds__(C::NT, C::MINB) k_radix_pass(RadixPassArgs a) 
 #pragma unroll
     for (int j = 0; j < RX_IPT; ++j) {
         const int li = w * 32 * RX_IPT + j * 32 + lane;
-        const bool valid = li < tile_n;
+        const bool valid = FULL || li < tile_n;
         const unsigned d = (unsigned)(key[j] >> a.shift) & a.mask;
-        unsigned peers = C::MATCH ? __match_any_sync(0xffffffffu, valid ? d : (unsigned)(RX_R + lane)) : (rx_peers(d) & __ballot_sync(0xffffffffu, valid));
+        unsigned peers = C::MATCH ? __match_any_sync(0xffffffffu, valid ? d : (unsigned)(RX_R + lane)) : (FULL ? rx_peers(d) : (rx_peers(d) & __ballot_sync(0xffffffffu, valid)));
         const int leader = __ffs((int)peers) - 1;
         unsigned old = 0;
         if (valid && lane == leader) { old = wh[d]; wh[d] = old + (unsigned)__popc(peers); }
@@ -176,7 +171,7 @@ __global__ void __launch_bounds__(C::NT, C::MINB) k_radix_pass(RadixPassArgs a) 
 #pragma unroll
     for (int j = 0; j < RX_IPT; ++j) {
         const int li = w * 32 * RX_IPT + j * 32 + lane;
-        if (li < tile_n) {
+        if (FULL || li < tile_n) {
             const unsigned d = (unsigned)(key[j] >> a.shift) & a.mask;
             const unsigned p = dstart[d] + wh[d] + rank[j];
             skeys[p] = key[j];
@@ -203,13 +198,33 @@ __global__ void __launch_bounds__(C::NT, C::MINB) k_radix_pass(RadixPassArgs a) 
 #pragma unroll
     for (int j = 0; j < RX_IPT; ++j) {
         const int i = j * RX_NT + tid;
-        if (i < tile_n) {
+        if (FULL || i < tile_n) {
             const unsigned long long k = skeys[i];
             const unsigned long long g = gbase[(unsigned)(k >> a.shift) & a.mask] + (unsigned long long)i;
             a.kout[g] = k;
             a.vout[g] = svals[i];
         }
     }
+}
+
+// the one partial tile of a pass goes through an out-of-line copy so that it does not cost the full tiles registers
+template <bool IOTA, class C>
+__device__ __noinline__ void rx_pass_tail(const RadixPassArgs a, const unsigned long long tile, const int tile_n) {
+    rx_pass_body<IOTA, C, false>(a, tile, tile_n);
+}
+
+template <bool IOTA, class C>
+__global__ void __launch_bounds__(C::NT, C::MINB) k_radix_pass(RadixPassArgs a) {
+    extern __shared__ __align__(16) unsigned char rx_smem0[];
+    unsigned *whist = reinterpret_cast<unsigned *>(rx_smem0);
+    __shared__ unsigned s_tile;
+    if (threadIdx.x == 0) s_tile = atomicAdd(a.tile_counter, 1u);
+    for (int i = threadIdx.x; i < C::NW * RX_R; i += C::NT) whist[i] = 0;
+    __syncthreads();
+    const unsigned long long tile = s_tile;
+    const unsigned long long left = a.n - tile * C::TILE;
+    if (left >= (unsigned long long)C::TILE) rx_pass_body<IOTA, C, true>(a, tile, C::TILE);
+    else rx_pass_tail<IOTA, C>(a, tile, (int)left);
 }
 
 // ---- host driver ------------------------------------------------------------------------------

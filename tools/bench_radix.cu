@@ -51,8 +51,8 @@ int main(int argc, char **argv) {
     DevBuf<u32> bad(2);
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     if (argc > 4) {
-        RUN(256, 16, 3, 0); RUN(256, 16, 3, 1); RUN(256, 16, 2, 0); RUN(512, 8, 2, 0); RUN(512, 8, 2, 1); RUN(256, 8, 5, 0);
-        RUN(256, 12, 4, 0); RUN(384, 12, 2, 0); RUN(512, 12, 1, 0); RUN(256, 20, 2, 0); RUN(1024, 4, 1, 0); RUN(512, 6, 3, 0);
+        RUN(256, 16, 3, 0); RUN(256, 20, 2, 0); RUN(256, 20, 3, 0); RUN(256, 24, 2, 0); RUN(256, 28, 2, 0); RUN(256, 32, 1, 0);
+        RUN(384, 16, 1, 0); RUN(384, 20, 1, 0); RUN(512, 16, 1, 0); RUN(256, 12, 4, 0);
     }
     for (int impl = 0; impl < 2; ++impl) {
         for (int r = 0; r < reps; ++r) {
