@@ -29,7 +29,7 @@ def free_port():
     return p
 
 
-def run_job(mode, tmp, pieces, w, p, bits, sa, rssa, non_acgt_to_a=False):
+def run_job(mode, tmp, pieces, w, p, bits, sa, rssa, non_acgt_to_a=False, expect_fail=False):
     """pieces: list (one per rank) of record lists.  Returns (sharded prefix, reference prefix)."""
     world = len(pieces)
     allrecs = [r for pc in pieces for r in pc]
@@ -46,7 +46,8 @@ def run_job(mode, tmp, pieces, w, p, bits, sa, rssa, non_acgt_to_a=False):
         cmd.append("-s")
     if rssa:
         cmd.append("-r")
-    run(cmd + [whole])
+    if not expect_fail:
+        run(cmd + [whole])
     out = os.path.join(tmp, "shard")
     port = free_port()
     procs = [subprocess.Popen([sys.executable, WORKER, mode, str(g), str(world), str(port), out, str(w), str(p), str(bits),
@@ -62,6 +63,9 @@ def run_job(mode, tmp, pieces, w, p, bits, sa, rssa, non_acgt_to_a=False):
             raise
         if pr.returncode != 0:
             errs.append(f"rank {g} rc={pr.returncode}: {e.decode(errors='replace')[-1500:]}")
+    if expect_fail:
+        assert len(errs) == world, f"every rank must fail together, got {len(errs)} of {world}: " + "\n".join(errs)
+        return out, "\n".join(errs)
     assert not errs, "\n".join(errs)
     return out, refp
 
@@ -95,3 +99,12 @@ def test_rank_without_trigger(tmp_path):
     out, refp = run_job("emu", str(tmp_path), pieces, 10, 2000, 32, True, False)
     assert whole_has_trigger
     assert_same_files(out, refp, exts_for(True, False))
+
+
+def test_failure_is_collective(tmp_path):
+    # rank 1's records hold a byte outside the hasher's alphabet (include/hash.hpp:31): the error is found on
+    # rank 1 only, every rank must return it together instead of waiting in an exchange
+    good = [(f"g{i}", random_bases(5000, 40 + i)) for i in range(2)]
+    bad = ("bad", np.frombuffer(b"ACGTACGTRRACGT" * 50, dtype=np.uint8))
+    out, msg = run_job("emu", str(tmp_path), [[good[0]], [bad], [good[1]]], 10, 100, 32, True, False, expect_fail=True)
+    assert "invalid character" in msg

@@ -42,3 +42,30 @@ def test_pangenome_job_nccl(tmp_path, world):
     recs = pangenome_records(400_000, 8, 400, seed=31)
     out, refp = run_job("nccl", str(tmp_path), split_records(recs, world), 10, 100, 64, True, True)
     assert_same_files(out, refp, exts_for(True, True))
+
+
+@pytest.mark.parametrize("world", [1, 2])
+def test_multi_launcher(tmp_path, world):
+    """pfbwt-f_b200/multi.py under torchrun: files dealt to the ranks, NCCL merge, slices written at their offsets"""
+    import os, subprocess, sys
+    from pfp_util import ROOT, write_fasta, run
+    from test_shard_gloo import free_port
+    if ngpu() < world:
+        pytest.skip(f"needs {world} GPUs")
+    recs = pangenome_records(250_000, 6, 250, seed=77)
+    fas = []
+    for g in range(3):
+        fa = os.path.join(str(tmp_path), f"in{g}.fa")
+        write_fasta(fa, recs[2 * g:2 * g + 2], line_width=80)
+        fas.append(fa)
+    whole = os.path.join(str(tmp_path), "whole.fa")
+    write_fasta(whole, recs, line_width=80)
+    refp, out = os.path.join(str(tmp_path), "ref"), os.path.join(str(tmp_path), "out")
+    run([ref_bin("pfbwt-f64"), "-s", "-r", "-o", refp, whole])
+    if world == 2:
+        fas = [fas[0], fas[1]] + [fas[2]]          # 3 files over 2 ranks: 2 + 1
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", str(free_port()), os.path.join(ROOT, "pfbwt-f_b200", "multi.py"), "-s", "-r", "--save-parse", "-o", out] + fas
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600)
+    assert r.returncode == 0, r.stderr.decode(errors="replace")[-3000:]
+    assert_same_files(out, refp, exts_for(True, True))
