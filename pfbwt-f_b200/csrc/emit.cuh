@@ -261,22 +261,33 @@ inline void k_classify(const ClassifyArgs &a, bool want_sa, pfbStream_t st) {
 static const u32 WALK_CAP = 1024;
 
 #ifndef PFB_EMU
+// 8 meta bytes per thread: nearly every suffix is a singleton group, found with a few word-wide bit operations;
+// only the heads of real multi-member groups walk their members
 __global__ void __launch_bounds__(256) k_group_walk_kernel(u8 *meta, u64 D, u32 *longlist, u32 *nlong, u32 *nhard) {
-    u64 t = (u64)blockIdx.x * 256 + threadIdx.x;
+    const u64 nwords = (D + 7) / 8;
     const u64 stride = (u64)gridDim.x * 256;
-    for (; t < D; t += stride) {
-        u32 m = meta[t];
-        if ((m & (M_HEAD | M_VALID)) != (M_HEAD | M_VALID)) continue;
-        if (meta[t + 1] & M_HEAD) continue;                    // singleton (meta is padded with head bytes)
-        bool diff = false;
-        u64 e = t + 1;
-        for (; e < D && e - t <= WALK_CAP; ++e) {
-            u32 x = meta[e];
-            if (x & M_HEAD) break;
-            diff |= (x & 15) != (m & 15);
+    const u64 ones = 0x0101010101010101ull;
+    for (u64 wd = (u64)blockIdx.x * 256 + threadIdx.x; wd < nwords; wd += stride) {
+        const u64 t0 = wd * 8;
+        const u64 m8 = *reinterpret_cast<const u64 *>(meta + t0);                 // meta is padded with head bytes past D
+        const u64 nx8 = (m8 >> 8) | ((u64)meta[t0 + 8] << 56);                     // the following element of each
+        u64 cand = (m8 >> 4) & (m8 >> 6) & ~(nx8 >> 4) & ones;                     // head & valid & next is not a head
+        while (cand) {
+            const int el = (__ffsll((long long)cand) - 1) >> 3;
+            cand &= cand - 1;
+            const u64 t = t0 + (u64)el;
+            if (t >= D) break;
+            const u32 m = (u32)(m8 >> (8 * el)) & 0xffu;
+            bool diff = false;
+            u64 e = t + 1;
+            for (; e < D && e - t <= WALK_CAP; ++e) {
+                u32 x = meta[e];
+                if (x & M_HEAD) break;
+                diff |= (x & 15) != (m & 15);
+            }
+            if (e < D && e - t > WALK_CAP) { longlist[atomicAdd(nlong, 1u)] = (u32)t; continue; }
+            if (diff) { for (u64 i = t; i < e; ++i) meta[i] |= M_HARD; atomicAdd(nhard, 1u); }
         }
-        if (e < D && e - t > WALK_CAP) { longlist[atomicAdd(nlong, 1u)] = (u32)t; continue; }
-        if (diff) { for (u64 i = t; i < e; ++i) meta[i] |= M_HARD; atomicAdd(nhard, 1u); }
     }
 }
 __global__ void __launch_bounds__(256) k_group_long_kernel(u8 *meta, u64 D, const u32 *longlist, u32 *nhard) {
