@@ -373,7 +373,7 @@ def main():
             except Exception:
                 traffic = None
         cpu = None
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:        # reported at N=1 only (rank 0's host cores)
             sample_n = min(args.ref_sample, n)
             v, dt, kind = run_reference_sample(bases, sample_n)
             cpu = {"value": v, "unit": "bases/s", "cores": 1, "kind": kind,
