@@ -94,6 +94,7 @@ inline NcclApi &nccl_api() { static NcclApi a; return a; }
 
 struct NcclComm : Comm {
     NcclApi::comm_t comm = nullptr;
+    DevBuf<u8> stage;              // padded slots of the variable-size all-gather
     void check(int rc, const char *what) {
         if (rc != 0) throw Error(-5, std::string("NCCL ") + what + ": " + nccl_api().GetErrorString(rc));
     }
@@ -109,10 +110,23 @@ struct NcclComm : Comm {
     void all_gather_v(const void *d_send, void *d_recv, const u64 *counts, pfbStream_t st) override {
         NcclApi &a = nccl_api();
         bool equal = true;
-        u64 tot = 0;
-        for (int r = 0; r < world; ++r) { equal &= counts[r] == counts[0]; tot += counts[r]; }
+        u64 tot = 0, mx = 0;
+        for (int r = 0; r < world; ++r) { equal &= counts[r] == counts[0]; tot += counts[r]; if (counts[r] > mx) mx = counts[r]; }
         if (equal) {
             if (counts[0]) check(a.AllGather(d_send, d_recv, counts[0], /*ncclChar*/ 0, comm, st), "AllGather");
+        } else if (tot >= (8u << 20) && mx * (u64)world <= tot + tot / 4) {
+            // large and nearly equal parts (the ranks' dictionaries / parses): one padded in-place all-gather at full
+            // NVLink rate, then the parts are packed.  Eight separate broadcasts reach about half of that.
+            const u64 slot = (mx + 15) & ~15ull;
+            if (stage.size() < slot * (u64)world) stage.alloc(slot * (u64)world);
+            u8 *sg = stage.get();
+            if (counts[rank]) PFB_CUDA_CHECK(cudaMemcpyAsync(sg + slot * (u64)rank, d_send, counts[rank], cudaMemcpyDeviceToDevice, st));
+            check(a.AllGather(sg + slot * (u64)rank, sg, slot, /*ncclChar*/ 0, comm, st), "AllGather");
+            u64 off = 0;
+            for (int r = 0; r < world; ++r) {
+                if (counts[r]) PFB_CUDA_CHECK(cudaMemcpyAsync((char *)d_recv + off, sg + slot * (u64)r, counts[r], cudaMemcpyDeviceToDevice, st));
+                off += counts[r];
+            }
         } else {
             // all-gather-v = one broadcast per root inside a group (fused by NCCL into one launch)
             check(a.GroupStart(), "GroupStart");

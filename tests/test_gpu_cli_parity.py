@@ -98,3 +98,41 @@ def test_cli_pivot_rounds(env, ref_bins, datadir):
                        stdout=subprocess.PIPE, stderr=subprocess.PIPE)
     assert r.returncode == 0, r.stderr.decode()[-2000:]
     assert_same_files(a, b, exts_for(True, True))
+
+
+def test_cli_surface_gzip_stdin_stdout_docs(ref_bins, datadir):
+    """the flags vcf_to_bwt.py drives the binaries with (vcf_to_bwt.py:118-129,174-181) - gzip input,
+    stdin `-` with -o, --stdout bwt|sa, --print-docs (<o>.docs), --parse-only then --pfbwt-only - against the reference."""
+    import gzip, subprocess
+    if not ref_bins["pfbwt-f"]:
+        pytest.skip("reference binaries not built")
+    recs = pangenome_records(90_000, 4, 90, 55) + [("last one", random_bases(12_345, 56))]
+    fa = os.path.join(datadir, "surf.fa")
+    write_fasta(fa, recs, line_width=60)
+    raw = open(fa, "rb").read()
+    gz = fa + ".gz"
+    with gzip.open(gz, "wb") as f:
+        f.write(raw)
+    ours, ref = os.path.join(BIN, "pfbwt-f"), ref_bins["pfbwt-f"]
+    # gzip input + --print-docs
+    a, b = os.path.join(datadir, "surf_gz.ref"), os.path.join(datadir, "surf_gz.gpu")
+    run([ref, "-s", "--print-docs", "-o", a, gz])
+    run([ours, "-s", "--print-docs", "-o", b, gz])
+    assert_same_files(a, b, exts_for(True, False) + ["docs"])
+    # stdin
+    a2, b2 = os.path.join(datadir, "surf_in.ref"), os.path.join(datadir, "surf_in.gpu")
+    run([ref, "-r", "-o", a2, "-"], stdin=raw)
+    run([ours, "-r", "-o", b2, "-"], stdin=raw)
+    assert_same_files(a2, b2, exts_for(False, True))
+    # --stdout bwt / sa
+    for what, flags in (("bwt", []), ("sa", ["-s"])):
+        ra = subprocess.run([ref] + flags + ["--stdout", what, "-o", os.path.join(datadir, "surf_so.ref"), fa], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        rb = subprocess.run([ours] + flags + ["--stdout", what, "-o", os.path.join(datadir, "surf_so.gpu"), fa], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        assert ra.returncode == 0 and rb.returncode == 0, rb.stderr.decode()[-1000:]
+        assert ra.stdout == rb.stdout and len(rb.stdout) > 0, f"--stdout {what} differs"
+    # two-step: --parse-only, then --pfbwt-only reading <o>.n
+    a3, b3 = os.path.join(datadir, "surf_2s.ref"), os.path.join(datadir, "surf_2s.gpu")
+    for exe, o in ((ref, a3), (ours, b3)):
+        run([exe, "--parse-only", "-s", "-o", o, fa])
+        run([exe, "--pfbwt-only", "-s", "-r", "-o", o])
+    assert_same_files(a3, b3, exts_for(True, True))
