@@ -465,8 +465,14 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
     if (N) emu_emit<U>(ea, any_sa);
 #else
     if (N) {
-        if (any_sa) k_emit_kernel<U, true><<<(unsigned)nt, 256, 0, st>>>(ea);
-        else k_emit_kernel<U, false><<<(unsigned)nt, 256, 0, st>>>(ea);
+        if (any_sa) {
+            static bool sa_attr_set = false;
+            if (!sa_attr_set) {
+                PFB_CUDA_CHECK(cudaFuncSetAttribute(k_emit_sa_kernel<U>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EmitSaSmem<U>::BYTES));
+                sa_attr_set = true;
+            }
+            k_emit_sa_kernel<U><<<(unsigned)nt, 256, EmitSaSmem<U>::BYTES, st>>>(ea);
+        } else k_emit_kernel<U, false><<<(unsigned)nt, 256, 0, st>>>(ea);
         PFB_CUDA_CHECK(cudaGetLastError());
         launch_stats().own++;
     }

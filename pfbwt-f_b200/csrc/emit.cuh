@@ -500,6 +500,128 @@ __global__ void __launch_bounds__(256) k_emit_kernel(EmitArgs a) {
 }
 #endif
 
+#ifndef PFB_EMU
+// ---- emission with SA output: load-balanced expansion ---------------------------------------------------
+// With SA output every BWT position costs two dependent gathers (ilist -> bwsai), and a suffix emits occ(word)
+// positions - tens to hundreds in a pangenome.  One thread walking "its" 8 suffixes leaves the CTA waiting at the
+// barrier for the thread with the longest walk (ncu on the first version: 18 barrier-stall cycles per issue, 15 % of
+// DRAM peak).  Here the tile's per-suffix output offsets go to shared memory and every OUTPUT SLOT of a window is
+// handled by its own thread (binary search slot -> suffix), four slots per thread in flight.
+static const int EMIT_SA_WIN = 4096;
+template <int U> struct EmitSaSmem {
+    static const size_t BYTES = (size_t)EMIT_SA_WIN * U + (size_t)(TILE + 2) * 8 + (size_t)TILE * 8 + EMIT_SA_WIN + TILE;
+};
+
+template <int U>
+__global__ void __launch_bounds__(256) k_emit_sa_kernel(EmitArgs a) {
+    typedef typename UIntOf<U>::type UT;
+    constexpr int WIN = EMIT_SA_WIN;
+    extern __shared__ __align__(16) u8 esm[];
+    UT *osa = reinterpret_cast<UT *>(esm);                              // [WIN]
+    u64 *eoff = reinterpret_cast<u64 *>(esm + (size_t)WIN * U);         // [TILE + 1] first output slot of every suffix of the tile
+    u32 *s_ib = reinterpret_cast<u32 *>(eoff + TILE + 2);               // [TILE]
+    u32 *s_sl = s_ib + TILE;                                            // [TILE]
+    u8 *obwt = reinterpret_cast<u8 *>(s_sl + TILE);                     // [WIN]
+    u8 *s_m = obwt + WIN;                                               // [TILE]
+    __shared__ u64 ws64[8];
+    __shared__ u32 ws32[8];
+    __shared__ u32 s_hbase;
+    const int tid = threadIdx.x;
+    const u64 t0 = (u64)blockIdx.x * TILE + (u64)tid * 8;
+    const u64 m8 = *reinterpret_cast<const u64 *>(a.meta + t0);
+    u32 c[8];
+    {
+        uint4 x = reinterpret_cast<const uint4 *>(a.cnt + t0)[0], y = reinterpret_cast<const uint4 *>(a.cnt + t0)[1];
+        c[0] = x.x; c[1] = x.y; c[2] = x.z; c[3] = x.w; c[4] = y.x; c[5] = y.y; c[6] = y.z; c[7] = y.w;
+    }
+    u64 sum = 0, hocc = 0;
+    u32 nh = 0;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        u32 m = (u32)(m8 >> (8 * e)) & 0xffu;
+        sum += c[e];
+        if (m & M_HARD) { hocc += c[e]; nh += (m & M_HEAD) ? 1u : 0u; }
+    }
+    u64 T, Hocc;
+    const u64 toff = block_excl_scan<u64>(sum, T, ws64);
+    block_excl_scan<u64>(hocc, Hocc, ws64);
+    u32 htot;
+    u32 hoff = block_excl_scan<u32>(nh, htot, ws32);
+    if (tid == 0) {
+        s_hbase = htot ? atomicAdd(a.n_hard_groups, htot) : 0u;
+        if (Hocc) atomicAdd((unsigned long long *)a.n_hard_occ, (unsigned long long)Hocc);
+    }
+    __syncthreads();
+    const u64 X0 = a.tilebase[blockIdx.x];
+    {
+        u64 o = toff;
+        u32 hi = s_hbase + hoff;
+        uint4 ib0 = reinterpret_cast<const uint4 *>(a.ibase + t0)[0], ib1 = reinterpret_cast<const uint4 *>(a.ibase + t0)[1];
+        uint4 sl0 = reinterpret_cast<const uint4 *>(a.sl + t0)[0], sl1 = reinterpret_cast<const uint4 *>(a.sl + t0)[1];
+        const u32 ibv[8] = {ib0.x, ib0.y, ib0.z, ib0.w, ib1.x, ib1.y, ib1.z, ib1.w};
+        const u32 slv[8] = {sl0.x, sl0.y, sl0.z, sl0.w, sl1.x, sl1.y, sl1.z, sl1.w};
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const u32 m = (u32)(m8 >> (8 * e)) & 0xffu;
+            const int le = tid * 8 + e;
+            eoff[le] = o; s_ib[le] = ibv[e]; s_sl[le] = slv[e]; s_m[le] = (u8)m;
+            if ((m & (M_HARD | M_HEAD)) == (M_HARD | M_HEAD)) { a.hard_t[hi] = (u32)(t0 + e); a.hard_x[hi] = X0 + o; ++hi; }
+            o += c[e];
+        }
+        if (tid == 255) eoff[TILE] = o;
+    }
+    __syncthreads();
+    const long long A = (long long)(X0 & 15);          // windows are 16-byte aligned in the output
+    for (long long wlo = -A; wlo < (long long)T; wlo += WIN) {
+        const long long whi = wlo + WIN;
+        const long long vlo = wlo > 0 ? wlo : 0, vhi = whi < (long long)T ? whi : (long long)T;
+        for (long long s0 = vlo + tid; s0 < vhi; s0 += 4 * 256) {
+            u32 ii[4], me[4], sle[4];
+            bool ok[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const long long sk = s0 + 256 * k;
+                ok[k] = sk < vhi;
+                ii[k] = 0; me[k] = 0; sle[k] = 0;
+                if (ok[k]) {
+                    int lo = 0, hi = TILE;                              // largest element with eoff <= sk
+                    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (eoff[mid] <= (u64)sk) lo = mid; else hi = mid; }
+                    me[k] = s_m[lo];
+                    ok[k] = !(me[k] & M_HARD);
+                    if (ok[k]) { sle[k] = s_sl[lo]; ii[k] = a.ilist[(u64)s_ib[lo] + ((u64)sk - eoff[lo])]; }
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (!ok[k]) continue;
+                const int pos = (int)(s0 + 256 * k - wlo);
+                osa[pos] = (UT)(a.bwsai[ii[k]] - (u64)sle[k]);
+                obwt[pos] = (me[k] & M_FULL) ? a.bwlast[ii[k]] : prev_byte(me[k]);      // include/pfbwt.hpp:119
+            }
+        }
+        __syncthreads();
+        for (int ch = tid; ch < WIN / 16; ch += 256) {
+            long long s0 = wlo + (long long)ch * 16;
+            if (s0 + 16 <= vlo || s0 >= vhi) continue;
+            u8 *g = a.bwt + (X0 + s0);
+            if (s0 >= vlo && s0 + 16 <= vhi) *reinterpret_cast<uint4 *>(g) = *reinterpret_cast<const uint4 *>(obwt + ch * 16);
+            else for (int b = 0; b < 16; ++b) if (s0 + b >= vlo && s0 + b < vhi) g[b] = obwt[ch * 16 + b];
+        }
+        {
+            constexpr int PER = 16 / U;
+            UT *gs = reinterpret_cast<UT *>(a.sa_out);
+            for (int ch = tid; ch < WIN / PER; ch += 256) {
+                long long s0 = wlo + (long long)ch * PER;
+                if (s0 + PER <= vlo || s0 >= vhi) continue;
+                if (s0 >= vlo && s0 + PER <= vhi) *reinterpret_cast<uint4 *>(gs + (X0 + s0)) = *reinterpret_cast<const uint4 *>(osa + ch * PER);
+                else for (int b = 0; b < PER; ++b) if (s0 + b >= vlo && s0 + b < vhi) gs[X0 + s0 + b] = osa[ch * PER + b];
+            }
+        }
+        __syncthreads();
+    }
+}
+#endif
+
 // hard groups of up to HARD_SMALL members: 8 lanes per group rank every occurrence among the
 // (ascending) ilist ranges of the other members by binary search; larger groups are listed for the
 // radix-sort path (emit_big_groups).
