@@ -5,7 +5,8 @@ and verifies, size-independently:
       SA[0] = n (so SA is a permutation and BWT is the BWT of S under that SA);
   (b) sortedness on sampled adjacent pairs: S[SA[i]:] < S[SA[i+1]:] (first 64 KiB compared, ties skipped);
   (c) r = number of runs of the returned BWT.
-  python tools/check_large.py [haps] [base] """
+  (d) with a third argument `r`: .ssa / .esa equal the run starts / ends of the returned BWT with their SA values.
+  python tools/check_large.py [haps] [base] [r]"""
 import os, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -25,12 +26,15 @@ print(f"generated {haps} x {base} in {time.time() - t0:.0f}s", flush=True)
 ctx = B.Context(device=0, bits=64, w=W, p=100, get_sai=True)
 ctx.add_records(host.data_ptr(), np.full(haps, base, dtype=np.uint64))
 t0 = time.time()
-ctx.finalize(); ctx.bwt_of_parse(); ctx.release_text(); ctx.generate_bwt(sa=True, rssa=False)
+RSSA = len(sys.argv) > 3 and sys.argv[3] == "r"          # also build and check the run-length SA samples (-r)
+ctx.finalize(); ctx.bwt_of_parse(); ctx.release_text(); ctx.generate_bwt(sa=True, rssa=RSSA)
 sz = ctx.sizes()
 n = int(sz.n)
 print(f"built in {time.time() - t0:.2f}s wall: n={n} (> 2^32: {n > 2**32}) P={sz.n_phrases} Dw={sz.n_words} D={sz.dict_bytes} r={sz.r} "
       f"stages={ {k: round(v, 1) for k, v in ctx.stats().items() if k.endswith('_ms')} }", flush=True)
 bwt = ctx.bwt(); sa = ctx.sa()
+if RSSA:
+    ssa = ctx.ssa().reshape(-1, 2); esa = ctx.esa().reshape(-1, 2)
 ctx.close()
 assert len(bwt) == n + 1 and len(sa) == n + 1
 assert int(sa[0]) == n, "SA[0] != n"
@@ -69,4 +73,12 @@ for i in rng.integers(1, n, 20000):
 print(f"sampled order ok ({ties} pairs tied beyond {K} bytes)", flush=True)
 r = int(np.count_nonzero(bwt[1:] != bwt[:-1])) + 1
 assert r == int(sz.r), (r, int(sz.r))
+if RSSA:
+    # src/pfbwt-f.cpp:304-328: .ssa = (i, SA[i]) at every run start, .esa = (i, SA[i]) at every run end
+    starts = np.flatnonzero(np.concatenate([[True], bwt[1:] != bwt[:-1]]))
+    ends = np.concatenate([starts[1:] - 1, [n]])
+    assert len(ssa) == r and len(esa) == r
+    assert np.array_equal(ssa[:, 0], starts.astype(np.uint64)) and np.array_equal(ssa[:, 1], sa[starts])
+    assert np.array_equal(esa[:, 0], ends.astype(np.uint64)) and np.array_equal(esa[:, 1], sa[ends])
+    print("ssa/esa ok", flush=True)
 print("runs ok; ALL OK", flush=True)
