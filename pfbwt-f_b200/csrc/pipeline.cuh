@@ -752,16 +752,31 @@ inline int parse_piece(const u8 *Tp, const PieceSpec &ps, const Params &prm, Dev
         const u64 *w64 = ws64.get(); u32 *wsp = out.wstart.get();
         launch_for(Dw + 1, st, PFB_LAMBDA(u64 r) { wsp[r] = (u32)w64[r]; });
         u8 *dict = out.dict.get(); const u32 *ord = order.get();
-        // 32 logical lanes per word copy it with unit stride (include/pfbwt_io.hpp:71-82)
+        // 32 logical lanes per word copy it with unit stride (include/pfbwt_io.hpp:71-82); the few words longer than
+        // LONGW (phrases spanning an N run: up to tens of Mbp) are listed and copied by the copy engine instead
+        const u64 LONGW = 1u << 13;
+        const u64 lcap = tlen / LONGW + 2;
+        DevBuf<u64> longw(3 * lcap);
+        DevBuf<u32> nlong(1);
+        dev_memset(nlong.get(), 0, 4, st);
+        u64 *lw = longw.get(); u32 *nl = nlong.get();
         launch_for(Dw * 32, st, PFB_LAMBDA(u64 i) {
             u64 r = i / 32, lane = i % 32;
             u64 k = ord[r];
             u64 s = phrase_start(ends, k, w), len = ends[k] - s + 1;
             u64 d0 = w64[r];
-            for (u64 j = lane; j < len; j += 32) dict[d0 + j] = Tp[s + j];
+            if (len <= LONGW) { for (u64 j = lane; j < len; j += 32) dict[d0 + j] = Tp[s + j]; }
+            else if (lane == 0) { u64 q = atomic_add(nl, 1u); lw[3 * q] = s; lw[3 * q + 1] = d0; lw[3 * q + 2] = len; }
             if (lane == 0) dict[d0 + len] = ENDOFWORD;
             if (i == 0) dict[dsize - 1] = ENDOFDICT;
         });
+        const u32 nlw = read_scalar(nl, st);
+        if (nlw) {
+            std::vector<u64> hl(3 * (size_t)nlw);
+            d2h(hl.data(), lw, hl.size() * 8, st);
+            stream_sync(st);
+            for (u32 q = 0; q < nlw; ++q) d2d(dict + hl[3 * q + 1], Tp + hl[3 * q], hl[3 * q + 2], st);
+        }
     }
     tm.dict_build = timer.stop();
     return PFB_OK;
