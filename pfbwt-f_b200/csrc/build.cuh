@@ -70,11 +70,27 @@ PFB_HD inline u64 load8_unaligned(const u8 *dict, u64 pos) {
     const u64 lo = w[0];
     return sh ? (lo >> sh) | (w[1] << (64 - sh)) : lo;
 }
-PFB_HD inline u64 pivot_key(const u8 *dict, u64 D, u64 a, u64 p) {
-    u32 l = 0;
+// Long single-symbol runs of the dictionary (poly-A phrases left by --non-acgt-to-a on Mbp N runs, poly-N without it):
+// two suffixes inside such runs share min(remaining run lengths) symbols, which the comparison skips in one step
+// instead of reading them - otherwise ties of millions of symbols would need prefix doubling over the whole dictionary.
+struct RunTable {
+    const u32 *start = nullptr, *end = nullptr;      // maximal runs [start, end) of one byte value, length >= RUN_MIN, ascending
+    u32 R = 0;
+    PFB_HD inline u64 remaining(u64 pos) const {     // symbols of the run containing pos from pos on (0 if none)
+        if (!R || pos < start[0]) return 0;
+        u32 lo = 0, hi = R;
+        while (hi - lo > 1) { u32 mid = (lo + hi) >> 1; if ((u64)start[mid] <= pos) lo = mid; else hi = mid; }
+        return pos < (u64)end[lo] ? (u64)end[lo] - pos : 0;
+    }
+};
+static const u64 RUN_BLOCK = 256, RUN_MIN = 3 * RUN_BLOCK;
+
+PFB_HD inline u64 pivot_key(const u8 *dict, u64 D, u64 a, u64 p, int lb, const RunTable &rt) {
+    const u64 cap = (1ull << lb) - 1;
+    u64 l = 0;
     // 8 symbols per step while both windows (and the second aligned word behind them) lie inside the dictionary
     const u64 hi = a > p ? a : p;
-    while (l + 8 <= PIVOT_CAP && hi + l + 16 <= D) {
+    while (l + 8 <= cap && hi + l + 16 <= D) {
         const u64 x = load8_unaligned(dict, a + l), y = load8_unaligned(dict, p + l);
         const u64 d = x ^ y;
         const u64 e = (x - 0x0202020202020202ull) & ~x & 0x8080808080808080ull;      // lowest set bit: first byte < 2 (EndOfWord / EndOfDict)
@@ -83,16 +99,89 @@ PFB_HD inline u64 pivot_key(const u8 *dict, u64 D, u64 a, u64 p) {
             // the first event decides: a differing byte (also when that byte is EndOfWord on one side), else a common terminator
             const u64 first = ev < ee ? ev : ee;
             const u32 b = (u32)(63 - clz64(first)) >> 3;
-            return pivot_key_result(l + b, (u32)(x >> (8 * b)) & 0xffu, (u32)(y >> (8 * b)) & 0xffu);
+            return pivot_key_result((u32)l + b, (u32)(x >> (8 * b)) & 0xffu, (u32)(y >> (8 * b)) & 0xffu, lb);
         }
-        l += 8;
+        u64 step = 8;
+        if (rt.R && x == (x & 0xffull) * 0x0101010101010101ull) {                    // 8 equal symbols on both sides: inside runs?
+            const u64 ra = rt.remaining(a + l), rp = rt.remaining(p + l);
+            const u64 both = ra < rp ? ra : rp;
+            if (both > 8) step = both;
+        }
+        l += step;
     }
-    for (; l < PIVOT_CAP; ++l) {
+    if (l > cap) l = cap;
+    for (; l < cap; ++l) {
         const u32 x = a + l < D ? dict[a + l] : 0u, y = p + l < D ? dict[p + l] : 0u;
-        if (x != y || x <= 1u) return pivot_key_result(l, x, y);
+        if (x != y || x <= 1u) return pivot_key_result((u32)l, x, y, lb);
     }
-    return (1ull << (PIVOT_LBITS + 4)) | (1ull << 1);                    // clamped: open, tied with the pivot
+    return pivot_key_clamped(lb);
 }
+
+// run table of the dictionary: 256-byte blocks of one byte value are found on the device, merged into candidate runs on
+// the host (a handful even for a human genome) and trimmed to their exact ends
+inline void build_run_table(const u8 *dict, u64 D, DevBuf<u32> &rs, DevBuf<u32> &re, u32 *R_out, u64 *longest, Workspace &ws) {
+    pfbStream_t st = ws.st;
+    *R_out = 0; *longest = 0;
+    const u64 nb = D / RUN_BLOCK;
+    if (nb == 0) return;
+    DevBuf<u8> uni(nb);
+    DevBuf<u32> uidx(nb);
+    {
+        u8 *up = uni.get();
+        launch_for(nb, st, PFB_LAMBDA(u64 b) {
+            const u64 *w = reinterpret_cast<const u64 *>(dict + b * RUN_BLOCK);
+            const u64 first = (w[0] & 0xffull) * 0x0101010101010101ull;
+            u64 acc = 0;
+            for (int k = 0; k < (int)(RUN_BLOCK / 8); ++k) acc |= w[k] ^ first;
+            up[b] = acc ? 0 : 1;
+        });
+    }
+    const u64 nu = scan_flags(uni.get(), uidx.get(), nb, ws);
+    if (nu < RUN_MIN / RUN_BLOCK) return;
+    DevBuf<u32> ub(nu);
+    DevBuf<u8> us(nu);
+    {
+        const u8 *up = uni.get(); const u32 *ui = uidx.get(); u32 *o = ub.get(); u8 *osym = us.get();
+        launch_for(nb, st, PFB_LAMBDA(u64 b) { if (up[b]) { o[ui[b]] = (u32)b; osym[ui[b]] = dict[b * RUN_BLOCK]; } });
+    }
+    std::vector<u32> hb(nu);
+    std::vector<u8> hs(nu);
+    d2h(hb.data(), ub.get(), nu * 4, st);
+    d2h(hs.data(), us.get(), nu, st);
+    stream_sync(st);
+    std::vector<u32> cs, ce;
+    std::vector<u8> csym;
+    for (u64 i = 0; i < nu;) {
+        u64 j = i + 1;
+        while (j < nu && hb[j] == hb[j - 1] + 1 && hs[j] == hs[i]) ++j;
+        if (j - i >= RUN_MIN / RUN_BLOCK) { cs.push_back((u32)(hb[i] * RUN_BLOCK)); ce.push_back((u32)((hb[j - 1] + 1) * RUN_BLOCK)); csym.push_back(hs[i]); }
+        i = j;
+    }
+    const u32 R = (u32)cs.size();
+    if (!R) return;
+    rs.alloc(R); re.alloc(R);
+    DevBuf<u8> rsym(R);
+    h2d(rs.get(), cs.data(), (size_t)R * 4, st);
+    h2d(re.get(), ce.data(), (size_t)R * 4, st);
+    h2d(rsym.get(), csym.data(), R, st);
+    DevBuf<u64> lmax(1);
+    dev_memset(lmax.get(), 0, 8, st);
+    {
+        u32 *sp = rs.get(); u32 *ep = re.get(); const u8 *sy = rsym.get(); u64 *lm = lmax.get();
+        launch_for(R, st, PFB_LAMBDA(u64 r) {          // exact ends: at most RUN_BLOCK - 1 steps each way
+            u64 s = sp[r], e = ep[r];
+            const u8 c = sy[r];
+            while (s > 0 && dict[s - 1] == c) --s;
+            while (e < D && dict[e] == c) ++e;
+            sp[r] = (u32)s; ep[r] = (u32)e;
+            atomic_max(lm, e - s);
+        });
+    }
+    *longest = read_scalar(lmax.get(), st);
+    stream_sync(st);            // the host vectors above fed asynchronous copies
+    *R_out = R;
+}
+
 inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, DevBuf<u8> &meta, DevBuf<u32> &cnt, const WordLookup &wl,
                               bool *reclassify, Workspace &ws, StageTimes &tm, Timer &timer, std::string &err,
                               const ShardSpec *sh = nullptr, u64 *n_sorted = nullptr) {
@@ -181,6 +270,10 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
     const u32 max_pivot_rounds = 64;
     // ... right away when a large part of the dictionary is tied after the main sort (repetitive dictionary), else
     // after two window rounds (short random ties are cheaper to close with windows)
+    RunTable rt;                       // built before the first pivot round
+    DevBuf<u32> run_s, run_e;
+    bool have_rt = false;
+    int lb = PIVOT_LBITS;
     auto want_pivot = [&]() { return pivot_ok && pivot_rounds < max_pivot_rounds && (pivot_knob == 1 || rounds >= 2 || m > N / 16); };
     while (m && (want_pivot() || rounds < max_ext_rounds || (!knob && m <= small_set && rounds < max_small_rounds) || (sh && rounds < shard_rounds))) {
         const bool pivot = want_pivot();
@@ -200,8 +293,16 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
         const int ebits = enum_bits(L2);
         DevBuf<u64> k2(m), k2b(m);
         DevBuf<u32> v(m), vb(m);
+        if (pivot && !have_rt) {
+            u32 R = 0; u64 longest = 0;
+            build_run_table(dict, D, run_s, run_e, &R, &longest, ws);
+            if (R) { rt.start = run_s.get(); rt.end = run_e.get(); rt.R = R; lb = bits_for(longest + 65536); if (lb < PIVOT_LBITS) lb = PIVOT_LBITS; }
+            have_rt = true;
+            timer.lap("K6 run table");
+        }
+        if (pivot && gbits + lb + 6 > 64) break;               // cannot happen with D < 2^32; doubling below takes over
         const int kshift = pivot ? 1 : 6;                       // bits below the part of the key that orders / separates
-        const int kbits = pivot ? PIVOT_LBITS + 6 : 6 + ebits;    // bits below the group id
+        const int kbits = pivot ? lb + 6 : 6 + ebits;    // bits below the group id
         DevBuf<u32> clamped(1);
         if (pivot) {
             dev_memset(clamped.get(), 0, 4, st);
@@ -209,15 +310,16 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
             const u32 *ap = apos.get(); const u8 *a_ = ah.get(); const u32 *gi = gidx.get(); const u32 *sp = sa.get();
             const u32 *dp = adep.get();
             u64 *kp = k2.get(); u32 *vp = v.get(); u32 *hs = hslot.get(); u32 *cl = clamped.get();
+            const int lbv = lb; const RunTable rtv = rt;
             launch_for(m, st, PFB_LAMBDA(u64 a) { if (a_[a]) hs[gi[a]] = (u32)a; });
             launch_for(m, st, PFB_LAMBDA(u64 a) {
                 u64 gid = (u64)gi[a] + a_[a] - 1;
                 u32 idx = sp[ap[a]];
                 vp[a] = idx;
                 u32 h = hs[gid];
-                u64 pk = pivot_key(dict, D, (u64)idx + dp[a], (u64)sp[ap[h]] + dp[h]);
-                if (!(pk & 1) && ((pk >> (PIVOT_LBITS + 4)) & 3) == 1) atomic_add(cl, 1u);
-                kp[a] = (gid << (PIVOT_LBITS + 6)) | pk;
+                u64 pk = pivot_key(dict, D, (u64)idx + dp[a], (u64)sp[ap[h]] + dp[h], lbv, rtv);
+                if (!(pk & 1) && ((pk >> (lbv + 4)) & 3) == 1) atomic_add(cl, 1u);
+                kp[a] = (gid << (lbv + 6)) | pk;
             });
         } else {
             const u32 *ap = apos.get(); const u8 *a_ = ah.get(); const u32 *gi = gidx.get(); const u32 *sp = sa.get();
@@ -240,7 +342,7 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
         {
             const u32 *ap = apos.get(); const u64 *kp = k2.get(); const u32 *vp = v.get();
             u32 *sp = sa.get(); u8 *ac = act2.get(); u32 *dp = adep.get(); u32 *cp = cnt.get();
-            const WordLookup w3 = wl; const u64 w64 = (u64)w;
+            const WordLookup w3 = wl; const u64 w64 = (u64)w; const int lbw = lb;
             launch_for(m, st, PFB_LAMBDA(u64 a) {
                 u64 k = kp[a] >> kshift;
                 bool head = a == 0 || k != (kp[a - 1] >> kshift);
@@ -251,7 +353,7 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
                 u32 vf = suffix_class(w3, vp[a], w64, c, ib, sl);         // what travels with the suffix: count, valid/full bits,
                 cp[j] = c;                                                 // and the preceding-byte code
                 mt[j] = (u8)(prev_code(dict, vp[a]) | (head ? M_HEAD : 0) | vf);
-                dp[a] += pivot ? pivot_consumed(kp[a]) : ((u32)(kp[a] >> 1) & 31u);   // slot a stays inside its old group: same depth so far
+                dp[a] += pivot ? pivot_consumed(kp[a], lbw) : ((u32)(kp[a] >> 1) & 31u);   // slot a stays inside its old group: same depth so far
                 ac[a] = (!(head && last) && !(kp[a] & 1)) ? 1 : 0;
             });
         }

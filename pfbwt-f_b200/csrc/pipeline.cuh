@@ -343,18 +343,23 @@ PFB_HD inline u64 pack_syms(const u8 *p, u64 len, u64 off, int cnt) {
 // l = common length, x / y = the member's / pivot's byte at the first difference (0 = string ended).
 static const int PIVOT_LBITS = 12;
 static const u32 PIVOT_CAP = (1u << PIVOT_LBITS) - 1;
-PFB_HD inline u64 pivot_key_result(u32 l, u32 x, u32 y) {
-    if (x == y) return (1ull << (PIVOT_LBITS + 4)) | 1ull;               // identical up to and including EndOfWord: closed
+// lb = bits of the common-length field (PIVOT_LBITS unless the dictionary holds long single-symbol runs, build.cuh)
+PFB_HD inline u64 pivot_key_result(u32 l, u32 x, u32 y, int lb = PIVOT_LBITS) {
+    if (x == y) return (1ull << (lb + 4)) | 1ull;               // identical up to and including EndOfWord: closed
+    const u64 cap = (1ull << lb) - 1;
     const u64 side = x < y ? 0ull : 2ull;
-    const u64 lf = x < y ? (u64)l : (u64)(PIVOT_CAP - l);
-    return (side << (PIVOT_LBITS + 4)) | (lf << 4) | ((u64)sym3((u8)x) << 1);
+    const u64 lf = x < y ? (u64)l : cap - (u64)l;
+    return (side << (lb + 4)) | (lf << 4) | ((u64)sym3((u8)x) << 1);
 }
+PFB_HD inline u64 pivot_key_clamped(int lb = PIVOT_LBITS) { return (1ull << (lb + 4)) | (1ull << 1); }   // open, tied with the pivot
+
 // symbols consumed by the occupant of a slot after a pivot round
-PFB_HD inline u32 pivot_consumed(u64 key) {
-    const u32 side = (u32)(key >> (PIVOT_LBITS + 4)) & 3u, lf = (u32)(key >> 4) & PIVOT_CAP;
+PFB_HD inline u32 pivot_consumed(u64 key, int lb = PIVOT_LBITS) {
+    const u32 cap = (u32)((1ull << lb) - 1);
+    const u32 side = (u32)(key >> (lb + 4)) & 3u, lf = (u32)(key >> 4) & cap;
     if (side == 0) return lf + 1;
-    if (side == 2) return (PIVOT_CAP - lf) + 1;
-    return (key & 1) ? 0u : PIVOT_CAP;
+    if (side == 2) return (cap - lf) + 1;
+    return (key & 1) ? 0u : cap;
 }
 
 // strings buf[sa, sa+la) and buf[sp, sp+lp), compared from offset `depth` on

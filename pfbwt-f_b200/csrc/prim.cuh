@@ -293,6 +293,9 @@ __device__ __forceinline__ uint64_t atomic_min(uint64_t *a, uint64_t v) {
     return (uint64_t)atomicMin((unsigned long long *)a, (unsigned long long)v);
 }
 __device__ __forceinline__ uint32_t atomic_max(uint32_t *a, uint32_t v) { return atomicMax(a, v); }
+__device__ __forceinline__ uint64_t atomic_max(uint64_t *a, uint64_t v) {
+    return (uint64_t)atomicMax((unsigned long long *)a, (unsigned long long)v);
+}
 __device__ __forceinline__ uint32_t atomic_or(uint32_t *a, uint32_t v) { return atomicOr(a, v); }
 __device__ __forceinline__ uint64_t atomic_cas(uint64_t *a, uint64_t cmp, uint64_t v) {
     return (uint64_t)atomicCAS((unsigned long long *)a, (unsigned long long)cmp, (unsigned long long)v);
