@@ -108,3 +108,11 @@ def test_failure_is_collective(tmp_path):
     bad = ("bad", np.frombuffer(b"ACGTACGTRRACGT" * 50, dtype=np.uint8))
     out, msg = run_job("emu", str(tmp_path), [[good[0]], [bad], [good[1]]], 10, 100, 32, True, False, expect_fail=True)
     assert "invalid character" in msg
+
+
+def test_nrun_job(tmp_path):
+    # N runs of 10^4 symbols (kept as N: a stopper symbol, one window round would consume one symbol each): the ranks hold
+    # only their key ranges, so these ties are closed by run-aware pivot rounds, not by prefix doubling
+    recs = nrun_records(4, 40_000, 5, big_run=12_000)
+    out, refp = run_job("emu", str(tmp_path), split_records(recs, 2), 10, 100, 64, True, True)
+    assert_same_files(out, refp, exts_for(True, True))

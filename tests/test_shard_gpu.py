@@ -35,6 +35,13 @@ def test_small_modulus_job_shared_gpu(tmp_path):
     assert_same_files(out, refp, exts_for(True, True))
 
 
+def test_nrun_job_shared_gpu(tmp_path):
+    # lower-case + N runs (kept as N) of 3*10^4 symbols: ties inside the runs are closed by run-aware pivot rounds
+    recs = nrun_records(4, 200_000, 5, big_run=30_000)
+    out, refp = run_job("cuda", str(tmp_path), split_records(recs, 2), 10, 100, 64, True, True)
+    assert_same_files(out, refp, exts_for(True, True))
+
+
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_pangenome_job_nccl(tmp_path, world):
     if ngpu() < world:
