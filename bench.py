@@ -17,6 +17,11 @@ suffix sort -> BWT assembly) over one text.
              of a launch, against MEASURED_PEAKS.json hbm_gbs; moved_gbs = the 24 B/pair a pass really moves
   cpu_baseline  unmodified reference binary (oracle/_ref/pfbwt-f) on a bounded sample, 1 core
 
+  single_job ONE job of the BASELINE.json configs[4] family over all ranks (N x 10 haplotypes of 100 Mbp, 0.1 %
+             substitutions, pfbwt-f64 -s): piece-wise parse, NCCL all-gather merge, key-range partitioned suffix sort,
+             every rank emits one slice of .bwt/.sa.  Weak scaling; at N=1 the same workload without a communicator.
+             `value` = text resident in HBM, `e2e` = from pinned host buffers incl. D2H of the BWT and SA slices.
+
 --impl reference times the reference's own CPU implementation (oracle/_ref/pfbwt-f) on a bounded
 sample of the same workload (rank 0 only).
 """
