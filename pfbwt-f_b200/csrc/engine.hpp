@@ -9,6 +9,8 @@
 #pragma once
 #include "host_io.hpp"
 #include "pipeline.cuh"
+#include "ingest.cuh"
+#include "devio.cuh"
 #include <memory>
 
 
@@ -35,6 +37,8 @@ struct Engine {
     FastaResult docs;
     bool store_docs = false;
     u64 pending_n = 0;               // bytes of S accumulated in segs
+    float ingest_ms = 0;             // device time of the FASTA record kernels so far
+    u64 ingest_files = 0;            // files that took the device reader
 
     TextOnDevice text;
     bool text_ready = false;
@@ -60,6 +64,29 @@ struct Engine {
     }
 
     int add_fasta(const std::string &path) {
+        // plain FASTA files are split into records on the device (ingest.cuh); everything else - gzip, stdin, FASTQ,
+        // CR LF line ends - goes through the host reader below
+        try {
+            IngestResult ir;
+            std::string e;
+            const int rc = ingest_fasta_device(path, prm.w, store_docs, device, ws, ir, e);
+            if (rc < 0) return fail(PFB_ERR_IO, e);
+            if (rc == 0) {
+                if (prm.bits == 32 && ir.total_len > 0xFFFFFFFFull)   // include/pfparser.hpp:326-332
+                    return fail(PFB_ERR_TOO_LONG_32, "input too long, please use 64-bit version");
+                for (u64 s : ir.starts) docs.starts.push_back(pending_n + s);
+                for (auto &nm : ir.names) docs.names.push_back(nm);
+                docs.nrec += ir.nrec; docs.total_len += ir.total_len;
+                Segment s;
+                s.on_device = true; s.len = ir.len;
+                s.dev = std::move(ir.seg);
+                pending_n += s.len;
+                segs.push_back(std::move(s));
+                ingest_ms += ir.device_ms; ingest_files++;
+                invalidate();
+                return PFB_OK;
+            }
+        } catch (const Error &ex) { return fail(ex.code, ex.what()); }
         size_t off0 = raw.n;
         FastaResult r;
         std::string e;
@@ -206,16 +233,34 @@ struct Engine {
         return v;
     }
 
+    // device array -> file (devio.cuh); integer arrays are brought to the file's width U on the device first
+    int dev_file(const std::string &path, const void *d, size_t bytes, std::string &e) {
+        return write_dev_file(path, d, bytes, 0, bytes, true, device, ws.st, e);
+    }
+    int dev_file_u32(const std::string &path, const DevBuf<u32> &b, size_t count, int U, std::string &e) {
+        if (U == 4) return dev_file(path, b.get(), count * 4, e);
+        DevBuf<u64> t(count ? count : 1);
+        const u32 *s = b.get(); u64 *d = t.get();
+        launch_for(count, ws.st, PFB_LAMBDA(u64 i) { d[i] = s[i]; });
+        return dev_file(path, t.get(), count * 8, e);
+    }
+    int dev_file_u64(const std::string &path, const DevBuf<u64> &b, size_t count, int U, std::string &e) {
+        if (U == 8) return dev_file(path, b.get(), count * 8, e);
+        DevBuf<u32> t(count ? count : 1);
+        const u64 *s = b.get(); u32 *d = t.get();
+        launch_for(count, ws.st, PFB_LAMBDA(u64 i) { d[i] = (u32)s[i]; });
+        return dev_file(path, t.get(), count * 4, e);
+    }
+
     // ---- files: save_parser (include/pfbwt_io.hpp:234-249) + parse-bwt (src/pfbwt-f.cpp:229-235)
     int save_parse(const std::string &prefix, bool with_parse_bwt, bool with_sai) {
         try {
             if (!parsed) return fail(PFB_ERR_ARG, "parse not finalized");
             const int U = prm.bits / 8;
             std::string e;
-            { auto v = to_host(parse.dict, parse.dsize); if (write_file(prefix + ".dict", v.data(), v.size(), e)) return fail(PFB_ERR_IO, e); }
-            { auto v = to_host(parse.occ, parse.Dw); auto o = widen_u32(v.data(), v.size(), U);
-              if (write_file(prefix + ".occ", o.data(), o.size(), e)) return fail(PFB_ERR_IO, e); }
-            { auto v = to_host(parse.parse, parse.P); if (write_file(prefix + ".parse", v.data(), v.size() * 4, e)) return fail(PFB_ERR_IO, e); }
+            if (dev_file(prefix + ".dict", parse.dict.get(), parse.dsize, e)) return fail(PFB_ERR_IO, e);
+            if (dev_file_u32(prefix + ".occ", parse.occ, parse.Dw, U, e)) return fail(PFB_ERR_IO, e);
+            if (dev_file(prefix + ".parse", parse.parse.get(), parse.P * 4, e)) return fail(PFB_ERR_IO, e);
             if (store_docs) {   // include/pfbwt_io.hpp:224-231
                 FILE *f = fopen((prefix + ".docs").c_str(), "w");
                 if (!f) return fail(PFB_ERR_IO, "could not open docs file");
@@ -227,11 +272,9 @@ struct Engine {
               fprintf(f, "%lu\n", (unsigned long)parse.n); fclose(f); }
             if (with_parse_bwt) {
                 if (!parse.has_parse_bwt) return fail(PFB_ERR_ARG, "parse BWT not computed");
-                { auto v = to_host(parse.bwlast, parse.P + 1); if (write_file(prefix + ".bwlast", v.data(), v.size(), e)) return fail(PFB_ERR_IO, e); }
-                { auto v = to_host(parse.ilist, parse.P + 1); auto o = widen_u32(v.data(), v.size(), U);
-                  if (write_file(prefix + ".ilist", o.data(), o.size(), e)) return fail(PFB_ERR_IO, e); }
-                if (with_sai) { auto v = to_host(parse.bwsai, parse.P + 1); auto o = narrow_u64(v.data(), v.size(), U);
-                  if (write_file(prefix + ".bwsai", o.data(), o.size(), e)) return fail(PFB_ERR_IO, e); }
+                if (dev_file(prefix + ".bwlast", parse.bwlast.get(), parse.P + 1, e)) return fail(PFB_ERR_IO, e);
+                if (dev_file_u32(prefix + ".ilist", parse.ilist, parse.P + 1, U, e)) return fail(PFB_ERR_IO, e);
+                if (with_sai && dev_file_u64(prefix + ".bwsai", parse.bwsai, parse.P + 1, U, e)) return fail(PFB_ERR_IO, e);
             }
             return PFB_OK;
         } catch (const Error &e) { return fail(e.code, e.what()); }
@@ -375,13 +418,12 @@ struct Engine {
             const int U = prm.bits / 8;
             // a rank of a multi-GPU job writes its slice at its offset of the common file
             auto emit = [&](const std::string &ext, const DevBuf<u8> &b, size_t bytes, u64 off, u64 final_size) -> int {
-                auto v = to_host(b, bytes);
                 if (comm) {
                     if (!stdout_ext.empty()) { e = "--stdout is not available in a multi-GPU job"; return -1; }
-                    return write_file_at(prefix + "." + ext, v.data(), v.size(), off, final_size, e);
+                    return write_dev_file(prefix + "." + ext, b.get(), bytes, off, final_size, false, device, ws.st, e);
                 }
-                if (stdout_ext == ext) { fwrite(v.data(), 1, v.size(), stdout); fflush(stdout); return 0; }
-                return write_file(prefix + "." + ext, v.data(), v.size(), e);
+                if (stdout_ext == ext) { auto v = to_host(b, bytes); fwrite(v.data(), 1, v.size(), stdout); fflush(stdout); return 0; }
+                return write_dev_file(prefix + "." + ext, b.get(), bytes, 0, bytes, true, device, ws.st, e);
             };
             if (emit("bwt", bwt.bwt, bwt.len, bwt.off, bwt.n + 1)) return fail(PFB_ERR_IO, e);
             if (sa) { if (!built_sa && !built_rssa) return fail(PFB_ERR_ARG, "SA not built");

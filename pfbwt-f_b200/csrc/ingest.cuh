@@ -1,0 +1,192 @@
+// ingest.cuh -- FASTA ingestion on the device.
+//
+// The reference reads records with kseq (include/kseq.h:178-216, driven by PfParser::add_fasta,
+// include/pfparser.hpp:299-337): header lines are skipped, line ends are dropped, every record is
+// followed by w filler 'A's.  host_io.hpp does that byte by byte on one core; here the raw bytes of a
+// plain FASTA file go to HBM as they are read (devio.cuh: several readers, each pread()ing into its own pinned buffer)
+// and three kernels over 64-byte tiles do the record work:
+//   A  kind of the last line that starts inside each tile (header / sequence) -> running maximum
+//      over the tiles = kind of the line every tile starts in
+//   B  per tile: bytes kept, headers started                                 -> two exclusive sums
+//   C  kept bytes to their place in S, w x 'A' after every record, header offsets and record starts
+// Everything kseq treats specially beyond plain FASTA - FASTQ ('@' records, '+' lines), '\r' before a
+// line end - is only DETECTED here; such files (and gzip, stdin) take the host reader, so behaviour
+// is the same for every input.  PFB_INGEST=host keeps the host reader for all files.
+#pragma once
+#include "pipeline.cuh"
+#include "devio.cuh"
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+namespace pfb {
+
+static const u64 ING_TILE = 64;
+
+struct IngestResult {
+    DevBuf<u8> seg;                 // records + padding, ready to be copied into S
+    u64 len = 0;                    // bytes in seg
+    u64 nrec = 0, total_len = 0;    // records, sum of record lengths (no padding)
+    std::vector<u64> starts;        // offset of every record in seg (store_docs)
+    std::vector<std::string> names; // header up to the first white space (store_docs)
+    float device_ms = 0;
+};
+
+// one tile: calls hdr(i) at every header start and keep(i, c) for every sequence byte, in order.
+// `kind` is the kind of the line the tile starts in (1 sequence, 2 header); returns the kind of the last line
+// that starts inside the tile, 0 when none does.  *bad is raised for what only the host reader handles.
+template <class FH, class FK>
+PFB_HD inline u32 ingest_walk_tile(const u8 *R, u64 m, u64 p0, u64 t, u32 kind, u32 *bad, FH hdr, FK keep) {
+    u64 lo = t * ING_TILE, hi = lo + ING_TILE;
+    if (hi > m) hi = m;
+    if (lo < p0) lo = p0;
+    u32 started = 0;
+    u8 prev = lo > p0 ? R[lo - 1] : (u8)'\n';
+    for (u64 i = lo; i < hi; ++i) {
+        const u8 c = R[i];
+        if (prev == '\n') {                      // kseq.h:194-198: first character of a line
+            if (c == '>') { kind = 2; hdr(i); }
+            else { kind = 1; if (c == '+' || c == '@') *bad = 1u; }
+            started = kind;
+        }
+        if (c == '\r') *bad = 1u;
+        if (kind == 1 && c != '\n') keep(i, c);
+        prev = c;
+    }
+    return started ? kind : 0;
+}
+
+// 0 = done, 1 = not a case for the device reader (caller uses read_fasta), -1 = error (err set)
+inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, int device, Workspace &ws, IngestResult &out, std::string &err) {
+    static const bool host_only = getenv("PFB_INGEST") && !strcmp(getenv("PFB_INGEST"), "host");
+    if (host_only || path == "-") return 1;
+    int fd = open(path.c_str(), O_RDONLY);
+    if (fd < 0) return 1;                                    // the host reader reports the error its way
+    struct stat sb;
+    if (fstat(fd, &sb) != 0 || !S_ISREG(sb.st_mode) || sb.st_size < 2) { close(fd); return 1; }
+    const u64 m = (u64)sb.st_size;
+    u8 magic[2] = {0, 0};
+    if (pread(fd, magic, 2, 0) != 2 || (magic[0] == 0x1f && magic[1] == 0x8b)) { close(fd); return 1; }   // gzip: zlib on the host
+
+    pfbStream_t st = ws.st;
+    DevBuf<u8> R(m + ING_TILE);
+    u64 p0 = ~0ull;                                          // kseq.h:183-187: first '>' or '@' anywhere
+    u8 first_marker = 0;
+    auto look_for_marker = [&](const u8 *b, u64 off, u64 len) {
+        if (p0 != ~0ull) return;
+        for (u64 i = 0; i < len; ++i) if (b[i] == '>' || b[i] == '@') { p0 = off + i; first_marker = b[i]; return; }
+    };
+#ifdef PFB_EMU
+    {
+        u64 off = 0;
+        while (off < m) {
+            ssize_t got = read(fd, R.get() + off, (size_t)(m - off < (1u << 26) ? m - off : (1u << 26)));
+            if (got < 0) { close(fd); err = "error reading input"; return -1; }
+            if (got == 0) break;
+            look_for_marker(R.get() + off, off, (u64)got);
+            off += (u64)got;
+        }
+        if (off != m) { close(fd); return 1; }
+    }
+#else
+    {
+        // the first header must show up in the first 16 MB chunk; otherwise the host reader takes the file
+        std::string e;
+        stream_sync(st);             // R may reuse a block that work queued on st still reads; the copies run on other streams
+        const int rc = read_file_to_dev(fd, m, R.get(), device, [&](const u8 *b, size_t len) { look_for_marker(b, 0, (u64)len); }, e);
+        if (rc) { close(fd); if (rc < 0) { err = e; return -1; } return 1; }
+    }
+#endif
+    if (p0 == ~0ull || first_marker != '>') { close(fd); stream_sync(st); return 1; }
+
+    Timer timer(st);
+    const u64 ntile = (m + ING_TILE - 1) / ING_TILE;
+    const u8 *Rp = R.get();
+    DevBuf<u32> bad(1);
+    dev_memset(bad.get(), 0, 4, st);
+    u32 *badp = bad.get();
+    // A: kind of the last line starting in each tile, tagged with the tile number for the running maximum
+    DevBuf<u64> tag(ntile), ent(ntile);
+    {
+        u64 *tg = tag.get();
+        launch_for(ntile, st, PFB_LAMBDA(u64 t) {
+            u32 k = ingest_walk_tile(Rp, m, p0, t, 2u, badp, [](u64) {}, [](u64, u8) {});
+            tg[t] = k ? ((t + 1) << 2) | k : 0ull;
+        });
+    }
+    inclusive_max<u64>(tag.get(), ent.get(), ntile, ws.sc, st);
+    // B: counts
+    DevBuf<u32> keptc(ntile), hdrc(ntile);
+    DevBuf<u64> koff(ntile), hoff(ntile);
+    {
+        const u64 *en = ent.get();
+        u32 *kc = keptc.get(), *hc = hdrc.get();
+        launch_for(ntile, st, PFB_LAMBDA(u64 t) {
+            u32 kind = t ? (u32)(en[t - 1] & 3) : 2u;
+            if (!kind) kind = 2u;                            // nothing started yet: still before the first header
+            u32 nk = 0, nh = 0;
+            u32 dummy = 0;
+            ingest_walk_tile(Rp, m, p0, t, kind, &dummy, [&](u64) { ++nh; }, [&](u64, u8) { ++nk; });
+            kc[t] = nk; hc[t] = nh;
+        });
+    }
+    exclusive_sum<u32, u64>(keptc.get(), koff.get(), ntile, ws.sc, st);
+    exclusive_sum<u32, u64>(hdrc.get(), hoff.get(), ntile, ws.sc, st);
+    const u64 K = read_scalar(koff.get() + (ntile - 1), st) + read_scalar(keptc.get() + (ntile - 1), st);
+    const u64 H = read_scalar(hoff.get() + (ntile - 1), st) + read_scalar(hdrc.get() + (ntile - 1), st);
+    if (read_scalar(bad.get(), st) || H == 0) { close(fd); return 1; }
+    // C: write
+    out.nrec = H; out.total_len = K; out.len = K + H * (u64)w;
+    out.seg.alloc(out.len);
+    DevBuf<u64> hpos(store_docs ? H : 1), dstart(store_docs ? H : 1);
+    {
+        const u64 *en = ent.get(), *ko = koff.get(), *ho = hoff.get();
+        u8 *o = out.seg.get();
+        u64 *hp = hpos.get(), *ds = dstart.get();
+        const u64 W = (u64)w;
+        const bool docs = store_docs;
+        launch_for(ntile, st, PFB_LAMBDA(u64 t) {
+            u32 kind = t ? (u32)(en[t - 1] & 3) : 2u;
+            if (!kind) kind = 2u;
+            u64 k = ko[t], h = ho[t];
+            u32 dummy = 0;
+            ingest_walk_tile(Rp, m, p0, t, kind, &dummy,
+                [&](u64 i) {
+                    ++h;                                     // record h starts; record h-1 (if any) is complete
+                    if (h >= 2) { u8 *pad = o + k + W * (h - 2); for (u64 j = 0; j < W; ++j) pad[j] = 'A'; }
+                    if (docs) { hp[h - 1] = i; ds[h - 1] = k + W * (h - 1); }
+                },
+                [&](u64, u8 c) { o[k + W * (h - 1)] = c; ++k; });
+        });
+        u8 *pad = o + K + W * (H - 1);
+        launch_for(W, st, PFB_LAMBDA(u64 j) { pad[j] = 'A'; });
+    }
+    if (store_docs) {
+        std::vector<u64> hp(H);
+        out.starts.resize(H);
+        d2h(hp.data(), hpos.get(), H * 8, st);
+        d2h(out.starts.data(), dstart.get(), H * 8, st);
+        stream_sync(st);
+        out.names.resize(H);
+        char buf[256];
+        for (u64 r = 0; r < H; ++r) {                        // name = header up to the first white space (kseq.h:188)
+            std::string &nm = out.names[r];
+            u64 pos = hp[r] + 1;
+            bool done = false;
+            while (!done && pos < m) {
+                ssize_t got = pread(fd, buf, sizeof(buf), (off_t)pos);
+                if (got <= 0) break;
+                for (ssize_t i = 0; i < got; ++i) {
+                    if (isspace((unsigned char)buf[i])) { done = true; break; }
+                    nm.push_back(buf[i]);
+                }
+                pos += (u64)got;
+            }
+        }
+    }
+    out.device_ms = timer.stop();
+    close(fd);
+    return 0;
+}
+
+}  // namespace pfb

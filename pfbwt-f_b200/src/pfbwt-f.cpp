@@ -3,6 +3,7 @@
 // :209-245 run_parser, :272-349 run_pfbwt, :351-367 main).  -DM64 builds pfbwt-f64.
 #include "pfbwt_b200.h"
 #include <chrono>
+#include <unistd.h>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -102,9 +103,23 @@ static Args parse_args(int argc, char **argv) {
     return args;
 }
 
+// PFB_CLI_TIMES=1: finer wall-clock lines than the reference's TASK lines (device start-up, compute vs file writing)
+struct SubTimer {
+    std::chrono::time_point<std::chrono::system_clock> start;
+    const char *what;
+    SubTimer(const char *w) : what(w) { start = std::chrono::system_clock::now(); }
+    ~SubTimer() {
+        static const bool on = getenv("PFB_CLI_TIMES") != NULL;
+        std::chrono::duration<double> d = std::chrono::system_clock::now() - start;
+        if (on) fprintf(stderr, "TIME\t%s\t%.3fs\n", what, d.count());
+    }
+};
+
 int main(int argc, char **argv) {
+    const auto t_main = std::chrono::system_clock::now();
     Args args = parse_args(argc, argv);
-    pfb_ctx *ctx = pfb_create(args.device, BITS);
+    pfb_ctx *ctx;
+    { SubTimer t("device start-up (pfb_create)"); ctx = pfb_create(args.device, BITS); }
     if (!ctx) { fprintf(stderr, "%s\n", pfb_create_error()); return 1; }
     pfb_parse_params pp;
     memset(&pp, 0, sizeof(pp));
@@ -125,10 +140,14 @@ int main(int argc, char **argv) {
         }
         {
             Timer t("TASK\tranking and bwt-ing parse and processing last-chars\t");
-            if (pfb_parse_bwt(ctx)) {
-                fprintf(stderr, "%s: Success\n", pfb_last_error(ctx));
-                exit(1);
+            {
+                SubTimer t2("parse BWT on device");
+                if (pfb_parse_bwt(ctx)) {
+                    fprintf(stderr, "%s: Success\n", pfb_last_error(ctx));
+                    exit(1);
+                }
             }
+            SubTimer t3("writing parse files");
             if (pfb_save_parse(ctx, args.output.c_str(), 1, any_sa)) die_ctx(ctx);
         }
         if (args.trim_non_acgt) { FILE *f = fopen((args.output + ".ntab").c_str(), "wb"); if (f) fclose(f); }
@@ -141,7 +160,8 @@ int main(int argc, char **argv) {
         fprintf(stderr, "workspace will be contained in HBM\n");
         {
             Timer t(any_sa ? "TASK\tgenerating final BWT w/ full and/or run-length SA\t" : "TASK\tgenerating final BWT w/o SA\t");
-            if (pfb_build_bwt(ctx, args.sa, args.rssa)) die_ctx(ctx);
+            { SubTimer t2("BWT on device"); if (pfb_build_bwt(ctx, args.sa, args.rssa)) die_ctx(ctx); }
+            SubTimer t3("writing BWT files");
             if (pfb_write_bwt(ctx, args.output.c_str(), args.sa, args.rssa, args.stdout_ext.empty() ? NULL : args.stdout_ext.c_str())) die_ctx(ctx);
         }
         pfb_sizes sz;
@@ -159,6 +179,13 @@ int main(int argc, char **argv) {
                 s.normalise_ms, s.trigger_ms, s.compact_ms, s.fingerprint_ms, s.dedup_ms, s.phrase_sort_ms, s.dict_build_ms,
                 s.parse_sa_ms, s.parse_bwt_ms, s.dict_sort_ms, s.groups_ms, s.emit_ms, s.runs_ms);
     }
-    pfb_destroy(ctx);
-    return 0;
+    // every output file is closed by now: leave without unmapping tens of GB of device slabs and pinned buffers
+    // (the driver reclaims them with the process; pfb_destroy costs 0.2-0.3 s at this point)
+    if (getenv("PFB_CLI_TIMES")) {
+        std::chrono::duration<double> d = std::chrono::system_clock::now() - t_main;
+        fprintf(stderr, "TIME\tmain() until all files are closed\t%.3fs\n", d.count());
+    }
+    fflush(stdout);
+    fflush(stderr);
+    _exit(0);
 }

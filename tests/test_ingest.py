@@ -1,0 +1,118 @@
+"""FASTA ingestion on the device (pfbwt-f_b200/csrc/ingest.cuh): record splitting, header
+skipping, line ends and the A^w padding must reproduce kseq as driven by PfParser::add_fasta
+(include/kseq.h:178-216, include/pfparser.hpp:299-337) on awkward files.
+
+CPU part (-m "not gpu"): the logic emulator runs the three ingestion kernels as serial loops; its files must equal
+the reference's and those of the host reader (PFB_INGEST=host).  GPU part: the real binaries, incl. --print-docs."""
+import os
+import subprocess
+import pytest
+from pfp_util import ROOT, random_bases, run, exts_for, assert_same_files
+
+EMU = os.path.join(ROOT, "tests", "emu", "pfb_emu")
+BIN = os.path.join(ROOT, "bin")
+
+
+def wrap(seq, width):
+    return b"\n".join(seq[i:i + width] for i in range(0, len(seq), width)) if len(seq) else b""
+
+
+def case_files():
+    a, b, c, d = (random_bases(n, s).tobytes() for n, s in ((40_000, 1), (25_000, 2), (7, 3), (30_001, 4)))
+    low = bytes(ch + 32 if i % 7 < 3 else ch for i, ch in enumerate(d))          # soft-masked stretches
+    withn = d[:9000] + b"N" * 700 + d[9700:20000] + b"n" * 3 + d[20003:]
+    cases = {}
+    # comments in headers, blank lines inside and between records, no newline at the end of the file
+    cases["blank_lines_no_eol"] = b">r1 some comment\tmore\n" + wrap(a, 60) + b"\n\n\n>r2\n\n" + wrap(b, 61) + b"\n>r3 x\n" + wrap(c, 3)
+    # text before the first header (no '>' or '@' in it), also with line ends
+    cases["garbage_first"] = b"this is not fasta\nACGT\n\n  >h1 c\n" + wrap(a, 80) + b"\n>h2\n" + wrap(d, 80) + b"\n"
+    # records without sequence: header directly followed by a header, and a header as the last line without newline
+    cases["empty_records"] = b">e0\n>r1\n" + wrap(a, 70) + b"\n>e1 c\n>e2\n\n>r2\n" + wrap(b, 70) + b"\n>last"
+    # line lengths around the 64-byte tile of the kernels, one very long line, one-character lines
+    cases["tile_edges"] = (b">t63\n" + wrap(a, 63) + b"\n>t64\n" + wrap(b, 64) + b"\n>t65\n" + wrap(d, 65) + b"\n>long\n" + a + b"\n>one\n" + wrap(a[:300], 1) + b"\n")
+    # 62 + newline + header start exactly at tile boundaries
+    cases["aligned"] = b">" + b"x" * 62 + b"\n" + wrap(a, 63) + b"\n" + b">" + b"y" * 30 + b"\n" + wrap(b, 127) + b"\n"
+    cases["lower_and_n"] = b">m1\n" + wrap(low, 60) + b"\n>m2 has N\n" + wrap(withn, 60) + b"\n"
+    # handled by the host reader (detected on the device): CR LF line ends, FASTQ
+    cases["crlf"] = b">c1 x\r\n" + wrap(a, 60).replace(b"\n", b"\r\n") + b"\r\n>c2\r\n" + wrap(b, 60).replace(b"\n", b"\r\n") + b"\r\n"
+    cases["fastq"] = b"@q1\n" + a[:20000] + b"\n+\n" + b"I" * 20000 + b"\n@q2 c\n" + b[:15000] + b"\n+q2\n" + b"#" * 15000 + b"\n"
+    return cases
+
+
+CASES = case_files()
+BAD = {"gt_inside_line": b">b1\n" + random_bases(5000, 9).tobytes() + b">notaheader\n" + b"ACGT" * 1000 + b"\n"}
+
+
+def write(datadir, name, data):
+    p = os.path.join(datadir, "ing_" + name + ".fa")
+    with open(p, "wb") as f:
+        f.write(data)
+    return p
+
+
+@pytest.fixture(scope="module")
+def emu():
+    subprocess.run(["make", "-C", ROOT, "emu"], check=True, stdout=subprocess.DEVNULL)
+    return EMU
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_ingest_logic_matches_reference_and_host_reader(name, emu, ref_bins, datadir):
+    fa = write(datadir, name, CASES[name])
+    flags = ["-s", "-r"]
+    dev, host = os.path.join(datadir, name + ".idev"), os.path.join(datadir, name + ".ihost")
+    r = subprocess.run([emu, "--bits", "32"] + flags + ["-o", dev, fa], check=True, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    took = b"ingest: host" if name in ("crlf", "fastq") else b"ingest: device"     # which reader the file must have taken
+    assert took in r.stderr, r.stderr.decode()[-500:]
+    env = dict(os.environ, PFB_INGEST="host")
+    subprocess.run([emu, "--bits", "32"] + flags + ["-o", host, fa], check=True, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    assert_same_files(host, dev, exts_for(True, True))
+    if ref_bins["pfbwt-f"]:
+        ref = os.path.join(datadir, name + ".iref")
+        run([ref_bins["pfbwt-f"]] + flags + ["-o", ref, fa])
+        assert_same_files(ref, dev, exts_for(True, True))
+
+
+def test_ingest_logic_invalid_character(emu, datadir):
+    """a '>' that is not the first character of a line is sequence: the reference dies in the hasher (include/hash.hpp:31)"""
+    fa = write(datadir, "gt_inside", BAD["gt_inside_line"])
+    r = subprocess.run([emu, "--bits", "32", "-o", os.path.join(datadir, "gt_inside.out"), fa], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    assert r.returncode != 0 and b"invalid character" in r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_ingest_gpu_cli(name, ref_bins, datadir):
+    if not ref_bins["pfbwt-f"]:
+        pytest.skip("reference binaries not built")
+    fa = write(datadir, name, CASES[name])
+    a, b = os.path.join(datadir, name + ".gref"), os.path.join(datadir, name + ".ggpu")
+    run([ref_bins["pfbwt-f"], "-s", "-r", "--print-docs", "-o", a, fa])
+    run([os.path.join(BIN, "pfbwt-f"), "-s", "-r", "--print-docs", "-o", b, fa])
+    assert_same_files(a, b, exts_for(True, True) + ["docs"])
+
+
+@pytest.mark.gpu
+def test_ingest_gpu_multi_file_and_host_reader_agree(ref_bins, datadir):
+    """64-bit build, larger file (several 32 MB read chunks are not needed for the logic, but many tiles are):
+    device reader == host reader == reference"""
+    recs = [(f"rec{i} len", random_bases(700_000 + 13 * i, 100 + i)) for i in range(4)]
+    data = b"".join(b">" + n.encode() + b"\n" + wrap(s.tobytes(), 60) + b"\n" for n, s in recs)
+    fa = write(datadir, "big", data)
+    ours = os.path.join(BIN, "pfbwt-f64")
+    b, c = os.path.join(datadir, "big.gdev"), os.path.join(datadir, "big.ghost")
+    run([ours, "-s", "--print-docs", "-o", b, fa])
+    subprocess.run([ours, "-s", "--print-docs", "-o", c, fa], check=True, env=dict(os.environ, PFB_INGEST="host"),
+                   stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    assert_same_files(c, b, exts_for(True, False) + ["docs"])
+    if ref_bins["pfbwt-f64"]:
+        a = os.path.join(datadir, "big.gref")
+        run([ref_bins["pfbwt-f64"], "-s", "--print-docs", "-o", a, fa])
+        assert_same_files(a, b, exts_for(True, False) + ["docs"])
+
+
+@pytest.mark.gpu
+def test_ingest_gpu_invalid_character(datadir):
+    fa = write(datadir, "gt_inside_gpu", BAD["gt_inside_line"])
+    r = subprocess.run([os.path.join(BIN, "pfbwt-f"), "-o", os.path.join(datadir, "gt_inside_gpu.out"), fa], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    assert r.returncode == 1 and b"invalid character" in r.stderr
