@@ -72,6 +72,8 @@ typedef struct {
     /* multi-GPU job: time spent in exchanges (incl. waiting for peers) / in the dictionary merge, bytes received */
     float shard_exchange_ms, shard_merge_ms;
     uint64_t shard_bytes_moved;
+    /* FASTA files whose records were split on the device (pfb_add_fasta on plain files) and the device time of that */
+    float ingest_ms; uint64_t ingest_files;
 } pfb_stats;
 
 /* which part of the job's outputs this context holds.  Without a communicator: everything. */

@@ -38,7 +38,8 @@ class Stats(C.Structure):
                [(k, C.c_uint32) for k in ["dedup_attempts", "phrase_sort_rounds", "parse_sa_rounds", "dict_sort_rounds"]] + \
                [("launches_own", C.c_uint64), ("launches_lib", C.c_uint64), ("dev_bytes_peak", C.c_uint64),
                 ("radix_pass_ms", C.c_double), ("radix_passes", C.c_uint64), ("radix_pairs", C.c_uint64), ("run_ms", C.c_float),
-                ("shard_exchange_ms", C.c_float), ("shard_merge_ms", C.c_float), ("shard_bytes_moved", C.c_uint64)]
+                ("shard_exchange_ms", C.c_float), ("shard_merge_ms", C.c_float), ("shard_bytes_moved", C.c_uint64),
+                ("ingest_ms", C.c_float), ("ingest_files", C.c_uint64)]
 
 
 class ShardInfo(C.Structure):

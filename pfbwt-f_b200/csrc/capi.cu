@@ -185,6 +185,7 @@ int pfb_get_stats(const pfb_ctx *c, pfb_stats *s) {
     s->radix_pairs = pfb::launch_stats().radix_pairs; s->run_ms = c->eng.run_ms;
     s->shard_exchange_ms = c->eng.shard_exchange_ms; s->shard_merge_ms = c->eng.shard_merge_ms;
     s->shard_bytes_moved = c->eng.comm ? c->eng.comm->bytes_moved : 0;
+    s->ingest_ms = c->eng.ingest_ms; s->ingest_files = c->eng.ingest_files;
     return PFB_OK;
 }
 

@@ -175,9 +175,9 @@ int main(int argc, char **argv) {
         pfb_stats s;
         pfb_get_stats(ctx, &s);
         fprintf(stderr, "GPU\tnormalise %.3f trigger %.3f compact %.3f fingerprint %.3f dedup %.3f phrase_sort %.3f dict_build %.3f "
-                        "parse_sa %.3f parse_bwt %.3f dict_sort %.3f groups %.3f emit %.3f runs %.3f ms\n",
+                        "parse_sa %.3f parse_bwt %.3f dict_sort %.3f groups %.3f emit %.3f runs %.3f fasta_records %.3f ms\n",
                 s.normalise_ms, s.trigger_ms, s.compact_ms, s.fingerprint_ms, s.dedup_ms, s.phrase_sort_ms, s.dict_build_ms,
-                s.parse_sa_ms, s.parse_bwt_ms, s.dict_sort_ms, s.groups_ms, s.emit_ms, s.runs_ms);
+                s.parse_sa_ms, s.parse_bwt_ms, s.dict_sort_ms, s.groups_ms, s.emit_ms, s.runs_ms, s.ingest_ms);
     }
     // every output file is closed by now: leave without unmapping tens of GB of device slabs and pinned buffers
     // (the driver reclaims them with the process; pfb_destroy costs 0.2-0.3 s at this point)
