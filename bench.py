@@ -22,6 +22,9 @@ suffix sort -> BWT assembly) over one text.
              every rank emits one slice of .bwt/.sa.  Weak scaling; at N=1 the same workload without a communicator.
              `value` = text resident in HBM, `e2e` = from pinned host buffers incl. D2H of the BWT and SA slices.
 
+  file_to_file (N=1) the same text as a 60-column FASTA file on tmpfs through bin/pfbwt-f until every output file is closed
+             (process wall clock; SURVEY.md 8(d)'s user-level metric).  --no-file-leg skips it.
+
 --impl reference times the reference's own CPU implementation (oracle/_ref/pfbwt-f) on a bounded
 sample of the same workload (rank 0 only).
 """
@@ -116,6 +119,57 @@ def run_reference_sample(bases, sample_n):
                        stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
         dt = time.perf_counter() - t0
     return sample_n / dt, dt, kind
+
+
+def file_to_file_leg(bases, runs=2, line_width=60):
+    """the metric as a user of the binaries sees it - config 2 as a FASTA file with 60-column lines on
+    tmpfs -> bin/pfbwt-f -> every output file closed; wall clock of the whole process (CUDA start-up and exit included).
+    One untimed run first (page cache, driver), then `runs` timed ones."""
+    exe = os.path.join(ROOT, "bin", "pfbwt-f")
+    if not os.path.exists(exe):
+        return {"unavailable": "bin/pfbwt-f not built"}
+    d = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else tempfile.gettempdir()
+    n = int(bases.shape[0])
+    with tempfile.TemporaryDirectory(dir=d) as td:
+        fa = os.path.join(td, "config2.fa")
+        with open(fa, "wb") as f:
+            f.write(b">rand1g\n")
+            step = 60_000_000 // line_width * line_width
+            for s0 in range(0, n, step):
+                x = bases[s0:s0 + step]
+                full = x.shape[0] // line_width * line_width
+                if full:
+                    a = np.empty((full // line_width, line_width + 1), dtype=np.uint8)
+                    a[:, :line_width] = x[:full].reshape(-1, line_width)
+                    a[:, line_width] = 10
+                    f.write(a.tobytes())
+                if x.shape[0] > full:
+                    f.write(x[full:].tobytes() + b"\n")
+        fbytes = os.path.getsize(fa)
+        walls, phases = [], {}
+        env = dict(os.environ, PFB_CLI_TIMES="1")
+        for it in range(runs + 1):
+            t0 = time.perf_counter()
+            r = subprocess.run([exe, "-w", str(W), "-p", str(PMOD), "-o", os.path.join(td, "out"), fa], env=env,
+                               stdout=subprocess.DEVNULL, stderr=subprocess.PIPE)
+            dt = time.perf_counter() - t0
+            if r.returncode != 0:
+                return {"unavailable": "bin/pfbwt-f failed: " + r.stderr.decode()[-200:]}
+            if it:
+                walls.append(dt)
+            phases = {}
+            for l in r.stderr.decode().splitlines():
+                f3 = l.split("\t")
+                if len(f3) >= 3 and f3[0] in ("TASK", "TIME"):
+                    try:
+                        phases[f3[1]] = float(f3[2].rstrip("s"))
+                    except ValueError:
+                        pass
+    wall = sum(walls) / len(walls)
+    return {"value": n / wall, "unit": "bases/s", "wall_s": wall, "runs": len(walls), "fasta_bytes": fbytes,
+            "what": f"bin/pfbwt-f -w {W} -p {PMOD} on the config-2 text as a {line_width}-column FASTA in {d}; process wall clock until exit, "
+                    ".dict .occ .parse .bwlast .ilist .bwt .n written",
+            "phases_s_last_run": phases}
 
 
 # ---- single job over all ranks (SURVEY.md 8(e), BASELINE.json configs[4] family) ----------------------
@@ -238,6 +292,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling aid: skip the host-buffer leg")
     ap.add_argument("--no-single-job", action="store_true", help="skip the one-job-over-all-GPUs leg")
+    ap.add_argument("--no-file-leg", action="store_true", help="skip the file-to-file run of bin/pfbwt-f (N=1 only)")
     ap.add_argument("--job-haps", type=int, default=JOB_HAPS)
     ap.add_argument("--job-base", type=int, default=JOB_BASE)
     ap.add_argument("--job-no-sa", action="store_true")
@@ -383,6 +438,9 @@ def main():
             v, dt, kind = run_reference_sample(bases, sample_n)
             cpu = {"value": v, "unit": "bases/s", "cores": 1, "kind": kind,
                    "sample": f"first {sample_n} bases of rank 0's text, whole pfbwt-f -w {W} -p {PMOD} run incl. file I/O ({dt:.1f} s)"}
+        f2f = None
+        if not args.no_file_leg and world == 1:
+            f2f = file_to_file_leg(bases)
         line = {
             "metric": "input bases/sec end-to-end fasta->.bwt",
             "value": world * n * args.steps / t_dev, "unit": "bases/s", "n_gpus": world, "steps": args.steps,
@@ -410,6 +468,8 @@ def main():
             line["cpu_baseline"] = cpu
         if job:
             line["single_job"] = job
+        if f2f:
+            line["file_to_file"] = f2f
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
