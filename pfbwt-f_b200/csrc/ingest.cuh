@@ -69,6 +69,13 @@ inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, 
     if (pread(fd, magic, 2, 0) != 2 || (magic[0] == 0x1f && magic[1] == 0x8b)) { close(fd); return 1; }   // gzip: zlib on the host
 
     pfbStream_t st = ws.st;
+#ifndef PFB_EMU
+    {
+        // raw bytes + records + 40 bytes of tile bookkeeping per 64 bytes: leave very large files to the host reader
+        size_t free_b = 0, total_b = 0;
+        if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess || (double)m * 2.8 + (256u << 20) > (double)free_b + (double)slab_pool().idle()) { close(fd); return 1; }
+    }
+#endif
     DevBuf<u8> R(m + ING_TILE);
     u64 p0 = ~0ull;                                          // kseq.h:183-187: first '>' or '@' anywhere
     u8 first_marker = 0;

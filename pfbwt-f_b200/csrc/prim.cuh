@@ -175,6 +175,7 @@ struct SlabPool {
     }
     void trim() { std::lock_guard<std::mutex> lk(mu); cudaDeviceSynchronize(); trim_locked(); }
     size_t reserved() { std::lock_guard<std::mutex> lk(mu); size_t t = 0; for (auto &s : slabs) t += s.size; return t; }
+    size_t idle() { std::lock_guard<std::mutex> lk(mu); size_t t = 0; for (auto &f : free_) t += f.second; return t; }   // bytes held but not handed out
 };
 SlabPool &slab_pool();   // one per process (one device per process: one rank per GPU)
 #endif

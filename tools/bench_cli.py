@@ -29,7 +29,7 @@ with open(fa, "wb") as f:
             f.write(x[full:].tobytes() + b"\n")
 print(f"# {fa}: {os.path.getsize(fa)} bytes, {n} bases, {lw}-column lines, written in {time.time() - t0:.1f} s", flush=True)
 exe = os.path.join(ROOT, "bin", "pfbwt-f64" if n > 4_000_000_000 else "pfbwt-f")
-for mode in ("device", "host", "device", "host"):
+for mode in ("device", "host", "device"):
     env = dict(os.environ, PFB_CLI_TIMES="1")
     if mode == "host":
         env["PFB_INGEST"] = "host"
@@ -40,6 +40,15 @@ for mode in ("device", "host", "device", "host"):
     tasks = [l.split("\t") for l in r.stderr.decode().splitlines() if l.startswith("TASK") or l.startswith("TIME")]
     print(f"ingest={mode:6s} rc={r.returncode} wall {wall:.3f} s ({n / wall / 1e9:.2f} Gbases/s file to file)  " +
           "  ".join(f"[{t[1]}: {t[2]}]" for t in tasks if len(t) > 2), flush=True)
+    import hashlib
+    def sha16(path):
+        h = hashlib.sha256()
+        with open(path, "rb") as f:
+            for blk in iter(lambda: f.read(1 << 24), b""):
+                h.update(blk)
+        return h.hexdigest()[:16]
+    if r.returncode == 0:
+        print("    sha256[:16]  " + "  ".join(f".{e} {sha16(out + '.' + e)}" for e in ("bwt", "dict", "parse") if os.path.exists(out + "." + e)), flush=True)
     for ext in ("bwt", "sa", "dict", "occ", "parse", "n", "bwlast", "ilist", "bwsai", "ssa", "esa"):
         try:
             os.remove(out + "." + ext)
