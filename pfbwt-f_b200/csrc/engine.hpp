@@ -64,8 +64,8 @@ struct Engine {
     }
 
     int add_fasta(const std::string &path) {
-        // plain FASTA files are split into records on the device (ingest.cuh); everything else - gzip, stdin, FASTQ,
-        // CR LF line ends - goes through the host reader below
+        // FASTA records are split on the device (ingest.cuh; gzip and stdin are inflated / drained on the host first);
+        // FASTQ, CR LF line ends and inputs too large for HBM go through the host reader below
         try {
             IngestResult ir;
             std::string e;
@@ -86,11 +86,20 @@ struct Engine {
                 invalidate();
                 return PFB_OK;
             }
+            if (rc == 2) {          // the stream has been taken in but needs the host reader (FASTQ, CR LF, no header, ...)
+                size_t off0 = raw.n;
+                FastaResult r;
+                read_fasta_mem(ir.hostraw.p, ir.hostraw.n, prm.w, raw, r, store_docs, 0);
+                return take_host_records(off0, r);
+            }
         } catch (const Error &ex) { return fail(ex.code, ex.what()); }
         size_t off0 = raw.n;
         FastaResult r;
         std::string e;
         if (read_fasta(path, prm.w, raw, r, store_docs, 0, e)) return fail(PFB_ERR_IO, e);
+        return take_host_records(off0, r);
+    }
+    int take_host_records(size_t off0, FastaResult &r) {
         if (prm.bits == 32 && r.total_len > 0xFFFFFFFFull)   // include/pfparser.hpp:326-332
             return fail(PFB_ERR_TOO_LONG_32, "input too long, please use 64-bit version");
         // doc starts are offsets in S of everything parsed so far

@@ -48,41 +48,35 @@ struct FastaResult {
     std::vector<uint64_t> starts;           // doc_starts_ (include/pfparser.hpp:321-325)
 };
 
-// Appends every record's bytes followed by w filler 'A's to `out` (the 'A's are
-// the inter-record padding of include/pfparser.hpp:333-337).  `base_n` is the
+// The reader is a state machine over the byte stream; it appends every record's bytes followed by w filler
+// 'A's to `out` (the 'A's are the inter-record padding of include/pfparser.hpp:333-337).  `base_n` is the
 // number of text bytes already held by the parser (for doc starts).
-// Returns 0, or -1 with err set.
-inline int read_fasta(const std::string &path, int w, HostBytes &out, FastaResult &res, bool store_docs, uint64_t base_n,
-                      std::string &err) {
-    gzFile fp = path == "-" ? gzdopen(fileno(stdin), "r") : gzopen(path.c_str(), "r");
-    if (fp == NULL) { err = "failed to open file!\n"; return -1; }
-    gzbuffer(fp, 1 << 20);
-    const size_t BUFSZ = 8u << 20;
-    std::vector<uint8_t> buf(BUFSZ);
-    // state machine over the byte stream
+struct FastaMachine {
+    int w;
+    HostBytes &out;
+    FastaResult &res;
+    bool store_docs;
+    uint64_t base_n;
     enum { SEEK_HDR, NAME, COMMENT, LINE_START, SEQ_LINE, PLUS_LINE, QUAL } state = SEEK_HDR;
     uint64_t seq_len = 0, qual_len = 0;
     std::string name;
     bool in_record = false;
-    auto finish_record = [&]() {
+    FastaMachine(int w_, HostBytes &o, FastaResult &r, bool docs, uint64_t base) : w(w_), out(o), res(r), store_docs(docs), base_n(base) {}
+    void finish_record() {
         out.append_fill('A', (size_t)w);
         res.total_len += seq_len;
         res.nrec++;
         in_record = false;
-    };
-    auto begin_record = [&]() {
+    }
+    void begin_record() {
         if (store_docs) {
             uint64_t nb = base_n + out.n;      // text bytes before this record (all already padded)
             res.starts.push_back(nb);
         }
         name.clear(); seq_len = 0; qual_len = 0; in_record = true;
-    };
-    for (;;) {
-        int got = gzread(fp, buf.data(), (unsigned)BUFSZ);
-        if (got < 0) { err = "error reading input"; gzclose(fp); return -1; }
-        if (got == 0) break;
-        const uint8_t *b = buf.data();
-        size_t i = 0, e = (size_t)got;
+    }
+    void feed(const uint8_t *b, size_t e) {
+        size_t i = 0;
         while (i < e) {
             switch (state) {
             case SEEK_HDR: {   // kseq.h:183-187: skip to the next '>' or '@' anywhere
@@ -138,13 +132,40 @@ inline int read_fasta(const std::string &path, int w, HostBytes &out, FastaResul
             }
         }
     }
-    if (state == NAME && store_docs && in_record) res.names.push_back(name);
-    if (in_record) {
-        if (seq_len > 1 && state == SEQ_LINE && out.p[out.n - 1] == '\r') { out.n--; seq_len--; }
-        finish_record();
+    void finish() {
+        if (state == NAME && store_docs && in_record) res.names.push_back(name);
+        if (in_record) {
+            if (seq_len > 1 && state == SEQ_LINE && out.p[out.n - 1] == '\r') { out.n--; seq_len--; }
+            finish_record();
+        }
     }
+};
+
+// plain or gzip, file or stdin ("-").  Returns 0, or -1 with err set.
+inline int read_fasta(const std::string &path, int w, HostBytes &out, FastaResult &res, bool store_docs, uint64_t base_n,
+                      std::string &err) {
+    gzFile fp = path == "-" ? gzdopen(fileno(stdin), "r") : gzopen(path.c_str(), "r");
+    if (fp == NULL) { err = "failed to open file!\n"; return -1; }
+    gzbuffer(fp, 1 << 20);
+    const size_t BUFSZ = 8u << 20;
+    std::vector<uint8_t> buf(BUFSZ);
+    FastaMachine M(w, out, res, store_docs, base_n);
+    for (;;) {
+        int got = gzread(fp, buf.data(), (unsigned)BUFSZ);
+        if (got < 0) { err = "error reading input"; gzclose(fp); return -1; }
+        if (got == 0) break;
+        M.feed(buf.data(), (size_t)got);
+    }
+    M.finish();
     gzclose(fp);
     return 0;
+}
+
+// the same over bytes already in memory (a stream the device reader took in and then handed back)
+inline void read_fasta_mem(const uint8_t *data, size_t len, int w, HostBytes &out, FastaResult &res, bool store_docs, uint64_t base_n) {
+    FastaMachine M(w, out, res, store_docs, base_n);
+    M.feed(data, len);
+    M.finish();
 }
 
 // ---------------------------------------------------------------- writers --

@@ -10,8 +10,9 @@
 //   B  per tile: bytes kept, headers started                                 -> two exclusive sums
 //   C  kept bytes to their place in S, w x 'A' after every record, header offsets and record starts
 // Everything kseq treats specially beyond plain FASTA - FASTQ ('@' records, '+' lines), '\r' before a
-// line end - is only DETECTED here; such files (and gzip, stdin) take the host reader, so behaviour
-// is the same for every input.  PFB_INGEST=host keeps the host reader for all files.
+// line end - is only DETECTED here; such inputs take the host reader (host_io.hpp), so behaviour is the
+// same for every input.  gzip files and stdin are inflated / drained by zlib on the host and then split here
+// as well.  PFB_INGEST=host keeps the host reader for all inputs.
 #pragma once
 #include "pipeline.cuh"
 #include "devio.cuh"
@@ -29,6 +30,7 @@ struct IngestResult {
     u64 nrec = 0, total_len = 0;    // records, sum of record lengths (no padding)
     std::vector<u64> starts;        // offset of every record in seg (store_docs)
     std::vector<std::string> names; // header up to the first white space (store_docs)
+    HostBytes hostraw;              // the whole inflated / drained stream when the input was not a plain regular file
     float device_ms = 0;
 };
 
@@ -56,35 +58,71 @@ PFB_HD inline u32 ingest_walk_tile(const u8 *R, u64 m, u64 p0, u64 t, u32 kind, 
     return started ? kind : 0;
 }
 
-// 0 = done, 1 = not a case for the device reader (caller uses read_fasta), -1 = error (err set)
+// 0 = done; 1 = not a case for the device reader, nothing consumed (caller uses read_fasta on the path);
+// 2 = not a case for the device reader, but the stream has been read: its bytes are in out.hostraw (caller uses
+// read_fasta_mem); -1 = error (err set)
 inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, int device, Workspace &ws, IngestResult &out, std::string &err) {
     static const bool host_only = getenv("PFB_INGEST") && !strcmp(getenv("PFB_INGEST"), "host");
-    if (host_only || path == "-") return 1;
-    int fd = open(path.c_str(), O_RDONLY);
-    if (fd < 0) return 1;                                    // the host reader reports the error its way
-    struct stat sb;
-    if (fstat(fd, &sb) != 0 || !S_ISREG(sb.st_mode) || sb.st_size < 2) { close(fd); return 1; }
-    const u64 m = (u64)sb.st_size;
-    u8 magic[2] = {0, 0};
-    if (pread(fd, magic, 2, 0) != 2 || (magic[0] == 0x1f && magic[1] == 0x8b)) { close(fd); return 1; }   // gzip: zlib on the host
-
-    pfbStream_t st = ws.st;
-#ifndef PFB_EMU
-    {
-        // raw bytes + records + 40 bytes of tile bookkeeping per 64 bytes: leave very large files to the host reader
-        size_t free_b = 0, total_b = 0;
-        if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess || (double)m * 2.8 + (256u << 20) > (double)free_b + (double)slab_pool().idle()) { close(fd); return 1; }
+    if (host_only) return 1;
+    // a regular uncompressed file is read straight into HBM by several readers; anything else (gzip, stdin, a pipe) is
+    // inflated / drained by zlib into host memory first and uploaded in one piece - the records are split on the device
+    // either way ("gzip-inflate stays on CPU, record splitting on device")
+    int fd = -1;
+    bool stream = path == "-";
+    u64 m = 0;
+    if (!stream) {
+        fd = open(path.c_str(), O_RDONLY);
+        if (fd < 0) return 1;                                // the host reader reports the error its way
+        struct stat sb;
+        if (fstat(fd, &sb) != 0) { close(fd); return 1; }
+        u8 magic[2] = {0, 0};
+        if (!S_ISREG(sb.st_mode) || sb.st_size < 2 || pread(fd, magic, 2, 0) != 2 || (magic[0] == 0x1f && magic[1] == 0x8b)) {
+            close(fd); fd = -1; stream = true;
+        } else m = (u64)sb.st_size;
     }
-#endif
-    DevBuf<u8> R(m + ING_TILE);
     u64 p0 = ~0ull;                                          // kseq.h:183-187: first '>' or '@' anywhere
     u8 first_marker = 0;
     auto look_for_marker = [&](const u8 *b, u64 off, u64 len) {
         if (p0 != ~0ull) return;
         for (u64 i = 0; i < len; ++i) if (b[i] == '>' || b[i] == '@') { p0 = off + i; first_marker = b[i]; return; }
     };
-#ifdef PFB_EMU
+    if (stream) {
+        gzFile fp = path == "-" ? gzdopen(fileno(stdin), "r") : gzopen(path.c_str(), "r");
+        if (fp == NULL) return 1;
+        gzbuffer(fp, 1 << 20);
+        HostBytes &hb = out.hostraw;
+        const size_t BUFSZ = 16u << 20;
+        for (;;) {
+            hb.reserve(hb.n + BUFSZ);
+            int got = gzread(fp, hb.p + hb.n, (unsigned)BUFSZ);
+            if (got < 0) { gzclose(fp); err = "error reading input"; return -1; }
+            if (got == 0) break;
+            hb.n += (size_t)got;
+        }
+        gzclose(fp);
+        m = hb.n;
+        if (m < 2) return 2;
+        look_for_marker(hb.p, 0, m);
+        if (p0 == ~0ull || first_marker != '>') return 2;
+    }
+    const int decline = stream ? 2 : 1;
+
+    pfbStream_t st = ws.st;
+#ifndef PFB_EMU
     {
+        // raw bytes + records + 40 bytes of tile bookkeeping per 64 bytes: leave very large inputs to the host reader
+        size_t free_b = 0, total_b = 0;
+        if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess || (double)m * 2.8 + (256u << 20) > (double)free_b + (double)slab_pool().idle()) {
+            if (fd >= 0) close(fd);
+            return decline;
+        }
+    }
+#endif
+    DevBuf<u8> R(m + ING_TILE);
+    if (stream) {
+        h2d(R.get(), out.hostraw.p, m, st);
+    } else {
+#ifdef PFB_EMU
         u64 off = 0;
         while (off < m) {
             ssize_t got = read(fd, R.get() + off, (size_t)(m - off < (1u << 26) ? m - off : (1u << 26)));
@@ -94,17 +132,15 @@ inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, 
             off += (u64)got;
         }
         if (off != m) { close(fd); return 1; }
-    }
 #else
-    {
         // the first header must show up in the first 16 MB chunk; otherwise the host reader takes the file
         std::string e;
         stream_sync(st);             // R may reuse a block that work queued on st still reads; the copies run on other streams
         const int rc = read_file_to_dev(fd, m, R.get(), device, [&](const u8 *b, size_t len) { look_for_marker(b, 0, (u64)len); }, e);
         if (rc) { close(fd); if (rc < 0) { err = e; return -1; } return 1; }
-    }
 #endif
-    if (p0 == ~0ull || first_marker != '>') { close(fd); stream_sync(st); return 1; }
+        if (p0 == ~0ull || first_marker != '>') { close(fd); stream_sync(st); return 1; }
+    }
 
     Timer timer(st);
     const u64 ntile = (m + ING_TILE - 1) / ING_TILE;
@@ -141,7 +177,7 @@ inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, 
     exclusive_sum<u32, u64>(hdrc.get(), hoff.get(), ntile, ws.sc, st);
     const u64 K = read_scalar(koff.get() + (ntile - 1), st) + read_scalar(keptc.get() + (ntile - 1), st);
     const u64 H = read_scalar(hoff.get() + (ntile - 1), st) + read_scalar(hdrc.get() + (ntile - 1), st);
-    if (read_scalar(bad.get(), st) || H == 0) { close(fd); return 1; }
+    if (read_scalar(bad.get(), st) || H == 0) { if (fd >= 0) close(fd); return decline; }
     // C: write
     out.nrec = H; out.total_len = K; out.len = K + H * (u64)w;
     out.seg.alloc(out.len);
@@ -180,6 +216,11 @@ inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, 
             std::string &nm = out.names[r];
             u64 pos = hp[r] + 1;
             bool done = false;
+            if (stream) {
+                const u8 *hp_ = out.hostraw.p;
+                while (pos < m && !isspace(hp_[pos])) nm.push_back((char)hp_[pos++]);
+                continue;
+            }
             while (!done && pos < m) {
                 ssize_t got = pread(fd, buf, sizeof(buf), (off_t)pos);
                 if (got <= 0) break;
@@ -192,7 +233,8 @@ inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, 
         }
     }
     out.device_ms = timer.stop();
-    close(fd);
+    if (fd >= 0) close(fd);
+    out.hostraw.release();
     return 0;
 }
 

@@ -136,3 +136,46 @@ def test_cli_surface_gzip_stdin_stdout_docs(ref_bins, datadir):
         run([exe, "--parse-only", "-s", "-o", o, fa])
         run([exe, "--pfbwt-only", "-s", "-r", "-o", o])
     assert_same_files(a3, b3, exts_for(True, True))
+
+
+def test_config2_full_size_bwt_hash(datadir):
+    """BASELINE.json configs[1] at FULL size: one record of 10^9 i.i.d. uniform bases (NumPy default_rng(1), SURVEY.md 8(d)
+    recipe), `pfbwt-f -w 10 -p 100`.  SURVEY.md 8(d) records what the unmodified reference wrote for this input when it was
+    run on it (n = 1 000 000 010, P = 10 153 944, D = 1 105 921 870, r = 749 996 069, sha256[:16] of .bwt = 4ab639c13f486fd2);
+    the drop-in binary must reproduce all of it.  The FASTA goes through the device record reader (60-column lines)."""
+    import hashlib, subprocess
+    import numpy as np
+    d = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else datadir
+    fa, out = os.path.join(d, "pfb_t_config2.fa"), os.path.join(d, "pfb_t_config2")
+    n, lw = 1_000_000_000, 60
+    rng = np.random.default_rng(1)
+    lut = np.frombuffer(b"ACGT", dtype=np.uint8)
+    try:
+        with open(fa, "wb") as f:
+            f.write(b">rand1g\n")
+            for s in range(0, n, 100_000_000):
+                x = lut[rng.integers(0, 4, 100_000_000, dtype=np.uint8)]
+                full = x.shape[0] // lw * lw
+                a = np.empty((full // lw, lw + 1), dtype=np.uint8)
+                a[:, :lw] = x[:full].reshape(-1, lw)
+                a[:, lw] = 10
+                f.write(a.tobytes())
+                f.write(x[full:].tobytes())       # 100 000 000 = 1 666 666 * 60 + 40: the line is continued by the next chunk
+            f.write(b"\n")
+        r = subprocess.run([os.path.join(BIN, "pfbwt-f"), "-w", "10", "-p", "100", "-o", out, fa], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        assert r.returncode == 0, r.stderr.decode()[-800:]
+        err = r.stderr.decode()
+        assert "n: 1000000010" in err and "r: 749996069" in err, err[-800:]
+        assert os.path.getsize(out + ".dict") == 1_105_921_870
+        assert os.path.getsize(out + ".parse") == 4 * 10_153_944
+        h = hashlib.sha256()
+        with open(out + ".bwt", "rb") as f:
+            for blk in iter(lambda: f.read(1 << 24), b""):
+                h.update(blk)
+        assert h.hexdigest()[:16] == "4ab639c13f486fd2"
+    finally:
+        for p in [fa] + [out + "." + e for e in ("bwt", "dict", "occ", "parse", "n", "bwlast", "ilist", "bwsai")]:
+            try:
+                os.remove(p)
+            except OSError:
+                pass

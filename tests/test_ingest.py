@@ -73,6 +73,34 @@ def test_ingest_logic_matches_reference_and_host_reader(name, emu, ref_bins, dat
         assert_same_files(ref, dev, exts_for(True, True))
 
 
+@pytest.mark.parametrize("name", ["blank_lines_no_eol", "tile_edges", "garbage_first", "crlf", "fastq"])
+@pytest.mark.parametrize("how", ["gz", "stdin", "gz_stdin"])
+def test_ingest_logic_streams(name, how, emu, ref_bins, datadir):
+    """gzip files and stdin: zlib inflates / drains the stream on the host, the records are split by the same kernels;
+    a stream that turns out to need the host reader (FASTQ, CR LF) is handed back to it from memory"""
+    import gzip
+    data = CASES[name]
+    if "gz" in how:
+        data = gzip.compress(data)
+    fa = write(datadir, name + "_" + how, data) + (".gz" if how == "gz" else "")
+    if how == "gz":
+        os.replace(fa[:-3], fa)
+    src, stdin = (fa, None) if how == "gz" else ("-", data)
+    dev = os.path.join(datadir, f"{name}_{how}.sdev")
+    r = subprocess.run([emu, "--bits", "32", "-s", "-r", "-o", dev, src], input=stdin, check=True, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    took = b"ingest: host" if name in ("crlf", "fastq") else b"ingest: device"
+    assert took in r.stderr, r.stderr.decode()[-500:]
+    if ref_bins["pfbwt-f"]:
+        ref = os.path.join(datadir, f"{name}_{how}.sref")
+        subprocess.run([ref_bins["pfbwt-f"], "-s", "-r", "-o", ref, src], input=stdin, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        assert_same_files(ref, dev, exts_for(True, True))
+    else:
+        host = os.path.join(datadir, f"{name}_{how}.shost")
+        subprocess.run([emu, "--bits", "32", "-s", "-r", "-o", host, src], input=stdin, check=True, env=dict(os.environ, PFB_INGEST="host"),
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        assert_same_files(host, dev, exts_for(True, True))
+
+
 def test_ingest_logic_invalid_character(emu, datadir):
     """a '>' that is not the first character of a line is sequence: the reference dies in the hasher (include/hash.hpp:31)"""
     fa = write(datadir, "gt_inside", BAD["gt_inside_line"])
@@ -90,6 +118,22 @@ def test_ingest_gpu_cli(name, ref_bins, datadir):
     run([ref_bins["pfbwt-f"], "-s", "-r", "--print-docs", "-o", a, fa])
     run([os.path.join(BIN, "pfbwt-f"), "-s", "-r", "--print-docs", "-o", b, fa])
     assert_same_files(a, b, exts_for(True, True) + ["docs"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("how", ["gz", "stdin"])
+def test_ingest_gpu_streams(how, ref_bins, datadir):
+    import gzip
+    if not ref_bins["pfbwt-f"]:
+        pytest.skip("reference binaries not built")
+    for name in ("empty_records", "tile_edges", "fastq"):
+        data = CASES[name]
+        fa = write(datadir, f"g_{name}_{how}", gzip.compress(data) if how == "gz" else data)
+        src, stdin = (fa, None) if how == "gz" else ("-", data)
+        a, b = os.path.join(datadir, f"{name}_{how}.gsref"), os.path.join(datadir, f"{name}_{how}.gsgpu")
+        subprocess.run([ref_bins["pfbwt-f"], "-s", "-r", "--print-docs", "-o", a, src], input=stdin, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        subprocess.run([os.path.join(BIN, "pfbwt-f"), "-s", "-r", "--print-docs", "-o", b, src], input=stdin, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        assert_same_files(a, b, exts_for(True, True) + ["docs"])
 
 
 @pytest.mark.gpu

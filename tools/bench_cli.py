@@ -1,6 +1,6 @@
 """File-to-file timing of the drop-in binary (FASTA on tmpfs -> all output files closed), with the
 FASTA records split on the device (default) and by the host reader (PFB_INGEST=host).
-usage: python tools/bench_cli.py [bases=1000000000] [line_width=60] [extra flags ...]"""
+usage: [BENCH_GZ=1] python tools/bench_cli.py [bases=1000000000] [line_width=60] [extra flags ...]"""
 import os, subprocess, sys, time
 import numpy as np
 
@@ -27,6 +27,14 @@ with open(fa, "wb") as f:
             f.write(a.tobytes())
         if m > full:
             f.write(x[full:].tobytes() + b"\n")
+if os.environ.get("BENCH_GZ"):           # gzip input: zlib inflate on the host, records split on the device
+    import gzip, shutil
+    t1 = time.time()
+    with open(fa, "rb") as fi, gzip.open(fa + ".gz", "wb", compresslevel=1) as fo:
+        shutil.copyfileobj(fi, fo, 1 << 24)
+    os.remove(fa)
+    fa = fa + ".gz"
+    print(f"# gzip -1 in {time.time() - t1:.1f} s", flush=True)
 print(f"# {fa}: {os.path.getsize(fa)} bytes, {n} bases, {lw}-column lines, written in {time.time() - t0:.1f} s", flush=True)
 exe = os.path.join(ROOT, "bin", "pfbwt-f64" if n > 4_000_000_000 else "pfbwt-f")
 for mode in ("device", "host", "device"):
