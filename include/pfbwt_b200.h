@@ -123,6 +123,11 @@ int pfb_write_bwt(pfb_ctx *, const char *prefix, int sa, int rssa, const char *s
 int pfb_get_sizes(const pfb_ctx *, pfb_sizes *);
 /* bases (incl. the w-byte padding after each record) added since the last pfb_clear: PfParser::get_pos() - 1 before finalize */
 uint64_t pfb_get_pending_bases(const pfb_ctx *);
+
+/* Known-answer hook for the trigger test of the parse (include/hash.hpp:12-21 wang_hash, include/pfparser.hpp:347
+ * `hash % p == 0`): the DEVICE functions the trigger kernel uses are run on n caller-supplied k-mer values;
+ * hash_out[i] = wang_hash(kmers[i]), divides_out[i] = 1 iff the kernel's division-free test says p divides it. */
+int pfb_kat_trigger(pfb_ctx *, const uint64_t *kmers, size_t n, uint64_t p, uint64_t *hash_out, uint8_t *divides_out);
 int pfb_get_stats(const pfb_ctx *, pfb_stats *);
 int pfb_copy_dict(pfb_ctx *, uint8_t *out /* dict_bytes */);
 int pfb_copy_occ(pfb_ctx *, void *out /* n_words * bits/8 */);

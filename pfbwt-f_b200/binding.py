@@ -17,6 +17,7 @@ EXPORTS = [
     "pfb_copy_bwt", "pfb_copy_sa", "pfb_copy_ssa", "pfb_copy_esa", "pfb_get_docs", "pfb_upload_text",
     "pfb_run_resident", "pfb_release_text", "pfb_clear",
     "pfb_nccl_unique_id", "pfb_shard_init_nccl", "pfb_shard_init_host", "pfb_get_shard_info", "pfb_get_pending_bases",
+    "pfb_kat_trigger",
 ]
 
 
@@ -75,6 +76,7 @@ def load():
     for f in ["pfb_finalize", "pfb_parse_bwt", "pfb_upload_text", "pfb_release_text", "pfb_clear"]:
         getattr(lib, f).argtypes = [vp]
     lib.pfb_append.argtypes = [vp, vp]
+    lib.pfb_kat_trigger.argtypes = [vp, vp, C.c_size_t, C.c_uint64, vp, vp]
     lib.pfb_save_parse.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
     lib.pfb_load_parse.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
     lib.pfb_build_bwt.argtypes = [vp, C.c_int, C.c_int]
@@ -147,6 +149,14 @@ class Context:
     def shard_init_host(self, rank, world, callback):
         self._cb = callback       # keep the ctypes thunk alive
         self._ck(self.lib.pfb_shard_init_host(self.h, rank, world, callback, None))
+
+    def kat_trigger(self, kmers, p):
+        """(wang_hash(kmers), p | hash) computed by the device functions of the trigger kernel"""
+        k = np.ascontiguousarray(kmers, dtype=np.uint64)
+        h = np.empty(k.shape[0], dtype=np.uint64)
+        d = np.empty(k.shape[0], dtype=np.uint8)
+        self._ck(self.lib.pfb_kat_trigger(self.h, k.ctypes.data, k.shape[0], int(p), h.ctypes.data, d.ctypes.data))
+        return h, d
 
     def shard_info(self):
         s = ShardInfo()

@@ -169,6 +169,23 @@ int pfb_get_sizes(const pfb_ctx *c, pfb_sizes *s) {
     return PFB_OK;
 }
 uint64_t pfb_get_pending_bases(const pfb_ctx *c) { return c ? c->eng.pending_n : 0; }
+
+int pfb_kat_trigger(pfb_ctx *c, const uint64_t *kmers, size_t n, uint64_t p, uint64_t *hash_out, uint8_t *divides_out) {
+    CTX_GUARD(c);
+    if (!kmers || !hash_out || !divides_out || p == 0) return c->eng.fail(PFB_ERR_ARG, "bad argument");
+    try {
+        cudaStream_t st = c->eng.ws.st;
+        pfb::DevBuf<pfb::u64> k(n ? n : 1), h(n ? n : 1);
+        pfb::DevBuf<pfb::u8> dv(n ? n : 1);
+        if (n) pfb::h2d(k.get(), kmers, n * 8, st);
+        const pfb::u64 *kp = k.get(); pfb::u64 *hp = h.get(); pfb::u8 *dp = dv.get();
+        const pfb::DivTest dt = pfb::DivTest::make(p);
+        pfb::launch_for(n, st, [=] __device__(pfb::u64 i) { pfb::u64 x = pfb::wang_hash(kp[i]); hp[i] = x; dp[i] = dt.divides(x) ? 1 : 0; });
+        if (n) { pfb::d2h(hash_out, h.get(), n * 8, st); pfb::d2h(divides_out, dv.get(), n, st); }
+        pfb::stream_sync(st);
+        return PFB_OK;
+    } catch (const pfb::Error &e) { return c->eng.fail(e.code, e.what()); }
+}
 int pfb_get_stats(const pfb_ctx *c, pfb_stats *s) {
     if (!c || !s) return PFB_ERR_ARG;
     const pfb::StageTimes &t = c->eng.tm;

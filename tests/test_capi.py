@@ -118,3 +118,31 @@ def test_capi_errors(datadir):
     ctx.close()
     with pytest.raises(B.PfbError):
         B.Context(device=0, bits=32, w=40)
+
+
+@pytest.mark.gpu
+def test_trigger_known_answers():
+    """a1/a2 of SURVEY 8: the device wang_hash equals the reference's (KAT wang_hash(0) = 0x77cfa1eef01bca90, probe of
+    include/hash.hpp:12-21; the C restatement for the rest) and the division-free divisibility test of the trigger
+    kernel equals `hash % p == 0` (include/pfparser.hpp:347) for odd, even and power-of-two moduli"""
+    import ctypes
+    B = binding()
+    ctx = B.Context(device=0, bits=32, w=10, p=100)
+    rng = np.random.default_rng(7)
+    kmers = np.concatenate([np.array([0, 1, 2, (1 << 20) - 1, (1 << 62) - 1, (1 << 64) - 1], dtype=np.uint64),
+                            rng.integers(0, 1 << 20, 50_000, dtype=np.uint64), rng.integers(0, 1 << 63, 50_000, dtype=np.uint64)])
+    lib = os.path.join(ROOT, "oracle", "_ref", "libpfp_oracle.so")
+    ora = ctypes.CDLL(lib) if os.path.exists(lib) else None
+    if ora:
+        ora.pfo_wang_hash.restype = ctypes.c_uint64
+        ora.pfo_wang_hash.argtypes = [ctypes.c_uint64]
+    for p in (100, 1, 2, 3, 5, 7, 64, 96, 97, 1000, 4096, 1_000_003, (1 << 31) - 1, 6_000_000_000):
+        h, d = ctx.kat_trigger(kmers, p)
+        assert int(h[0]) == 0x77cfa1eef01bca90
+        if ora:
+            exp = np.array([ora.pfo_wang_hash(int(k)) for k in kmers[:2000]], dtype=np.uint64)
+            assert np.array_equal(h[:2000], exp)
+        assert np.array_equal(d.astype(bool), (h % np.uint64(p)) == 0), f"p={p}"
+        if p <= 100:
+            assert d.sum() > 0
+    ctx.close()
