@@ -1,6 +1,6 @@
 """File-to-file timing of the drop-in binary (FASTA on tmpfs -> all output files closed), with the
 FASTA records split on the device (default) and by the host reader (PFB_INGEST=host).
-usage: [BENCH_GZ=1] python tools/bench_cli.py [bases=1000000000] [line_width=60] [extra flags ...]"""
+usage: [BENCH_GZ=1] [BENCH_HAPS=64] python tools/bench_cli.py [bases=1000000000] [line_width=60] [extra flags ...]"""
 import os, subprocess, sys, time
 import numpy as np
 
@@ -12,21 +12,49 @@ d = "/dev/shm" if os.path.isdir("/dev/shm") else "/tmp"
 fa = os.path.join(d, "pfb_cli_bench.fa")
 rng = np.random.default_rng(1)
 lut = np.frombuffer(b"ACGT", dtype=np.uint8)
+haps = int(os.environ.get("BENCH_HAPS", "0"))     # >0: that many haplotypes of ONE base sequence of `bases` bases, 0.1 % substitutions
 t0 = time.time()
+
+
+def write_record(f, name, x):
+    f.write(b">" + name + b"\n")
+    m = x.shape[0]
+    full = m // lw * lw
+    if full:
+        a = np.empty((full // lw, lw + 1), dtype=np.uint8)
+        a[:, :lw] = x[:full].reshape(-1, lw)
+        a[:, lw] = 10
+        f.write(a.tobytes())
+    if m > full:
+        f.write(x[full:].tobytes() + b"\n")
+
+
 with open(fa, "wb") as f:
-    f.write(b">rand\n")
-    step = 60_000_000 // lw * lw
-    for s in range(0, n, step):
-        m = min(step, n - s)
-        x = lut[rng.integers(0, 4, m, dtype=np.uint8)]
-        full = m // lw * lw
-        if full:
-            a = np.empty((full // lw, lw + 1), dtype=np.uint8)
-            a[:, :lw] = x[:full].reshape(-1, lw)
-            a[:, lw] = 10
-            f.write(a.tobytes())
-        if m > full:
-            f.write(x[full:].tobytes() + b"\n")
+    if haps:
+        codes = np.random.default_rng(2024).integers(0, 4, n, dtype=np.uint8)
+        for h in range(haps):
+            c = codes
+            if h:
+                r2 = np.random.default_rng(5000 + h)
+                pos = r2.integers(0, n, n // 1000)
+                c = codes.copy()
+                c[pos] = (c[pos] + r2.integers(1, 4, n // 1000, dtype=np.uint8)) % 4
+            write_record(f, b"hap%d some comment" % h, lut[c])
+        n = n * haps
+    else:
+        f.write(b">rand\n")
+        step = 60_000_000 // lw * lw
+        for s in range(0, n, step):
+            m = min(step, n - s)
+            x = lut[rng.integers(0, 4, m, dtype=np.uint8)]
+            full = m // lw * lw
+            if full:
+                a = np.empty((full // lw, lw + 1), dtype=np.uint8)
+                a[:, :lw] = x[:full].reshape(-1, lw)
+                a[:, lw] = 10
+                f.write(a.tobytes())
+            if m > full:
+                f.write(x[full:].tobytes() + b"\n")
 if os.environ.get("BENCH_GZ"):           # gzip input: zlib inflate on the host, records split on the device
     import gzip, shutil
     t1 = time.time()
@@ -37,7 +65,7 @@ if os.environ.get("BENCH_GZ"):           # gzip input: zlib inflate on the host,
     print(f"# gzip -1 in {time.time() - t1:.1f} s", flush=True)
 print(f"# {fa}: {os.path.getsize(fa)} bytes, {n} bases, {lw}-column lines, written in {time.time() - t0:.1f} s", flush=True)
 exe = os.path.join(ROOT, "bin", "pfbwt-f64" if n > 4_000_000_000 else "pfbwt-f")
-for mode in ("device", "host", "device"):
+for mode in (("device", "host") if haps else ("device", "host", "device")):
     env = dict(os.environ, PFB_CLI_TIMES="1")
     if mode == "host":
         env["PFB_INGEST"] = "host"
@@ -56,8 +84,8 @@ for mode in ("device", "host", "device"):
                 h.update(blk)
         return h.hexdigest()[:16]
     if r.returncode == 0:
-        print("    sha256[:16]  " + "  ".join(f".{e} {sha16(out + '.' + e)}" for e in ("bwt", "dict", "parse") if os.path.exists(out + "." + e)), flush=True)
-    for ext in ("bwt", "sa", "dict", "occ", "parse", "n", "bwlast", "ilist", "bwsai", "ssa", "esa"):
+        print("    sha256[:16]  " + "  ".join(f".{e} {sha16(out + '.' + e)}" for e in ("bwt", "dict", "parse", "docs") if os.path.exists(out + "." + e)), flush=True)
+    for ext in ("bwt", "sa", "dict", "occ", "parse", "n", "bwlast", "ilist", "bwsai", "ssa", "esa", "docs"):
         try:
             os.remove(out + "." + ext)
         except OSError:
