@@ -10,6 +10,7 @@
 #include "prim.cuh"
 #include <fcntl.h>
 #include <unistd.h>
+#include <sys/stat.h>
 #include <mutex>
 #include <thread>
 #include <atomic>
@@ -131,5 +132,32 @@ inline int read_file_to_dev(int fd, u64 m, void *dptr, int device, F first, std:
     return bad == 1 ? 1 : 0;
 }
 #endif
+
+// whole file -> device buffer (allocated here, `slack` spare bytes behind the data).  0 ok, -1 with err set.
+inline int read_whole_file_to_dev(const std::string &path, DevBuf<u8> &buf, u64 &size, size_t slack, int device, pfbStream_t st, std::string &err) {
+    int fd = open(path.c_str(), O_RDONLY);
+    if (fd < 0) { err = "error opening " + path; return -1; }
+    struct stat sb;
+    if (fstat(fd, &sb) != 0) { close(fd); err = "error opening " + path; return -1; }
+    size = (u64)sb.st_size;
+    buf.alloc(size + slack + 1);
+    int rc = 0;
+#ifdef PFB_EMU
+    (void)device; (void)st;
+    u64 off = 0;
+    while (off < size) {
+        ssize_t got = read(fd, buf.get() + off, (size_t)(size - off < (1u << 26) ? size - off : (1u << 26)));
+        if (got <= 0) { rc = -1; break; }
+        off += (u64)got;
+    }
+#else
+    stream_sync(st);
+    std::string e;
+    if (size) rc = read_file_to_dev(fd, size, buf.get(), device, [](const u8 *, size_t) {}, e) ? -1 : 0;
+#endif
+    close(fd);
+    if (rc) { err = "error reading " + path; return -1; }
+    return 0;
+}
 
 }  // namespace pfb

@@ -294,26 +294,47 @@ struct Engine {
         try {
             const int U = prm.bits / 8;
             std::string e;
-            std::vector<uint8_t> dict, occ, pr;
-            if (read_file(prefix + ".dict", dict, e)) return fail(PFB_ERR_IO, "bad dict file\n");
-            if (read_file(prefix + ".parse", pr, e)) return fail(PFB_ERR_IO, "bad parse file\n");
-            if (dict.empty() || dict.back() != ENDOFDICT) return fail(PFB_ERR_IO, "bad dict file\n");
-            if (dict.size() > 0xFFFFFFF0ull) return fail(PFB_ERR_LIMIT, "dictionary larger than 2^32 bytes is not supported yet");
-            for (size_t i = 0; i + 1 < dict.size(); ++i) {
-                uint8_t c = dict[i];
-                if (!(c == 1 || c == 2 || c == '-' || c == 'A' || c == 'C' || c == 'G' || c == 'N' || c == 'T'))
-                    return fail(PFB_ERR_IO, "dict file contains a byte outside the parser's alphabet");
-            }
+            std::vector<uint8_t> occ, pr;
+            // the dictionary (GBs) goes from the file straight to HBM; it is checked and cut into words there
             parse = DeviceParse();
-            parse.dsize = dict.size();
-            std::vector<u32> wstart;
-            wstart.push_back(0);
-            for (size_t i = 0; i + 1 < dict.size(); ++i) if (dict[i] == ENDOFWORD) wstart.push_back((u32)i + 1);
-            parse.Dw = wstart.size() - 1;
-            if (wstart.back() != dict.size() - 1) return fail(PFB_ERR_IO, "bad dict file\n");
+            u64 dsize = 0;
+            if (read_whole_file_to_dev(prefix + ".dict", parse.dict, dsize, 64, device, ws.st, e)) return fail(PFB_ERR_IO, "bad dict file\n");
+            if (read_file(prefix + ".parse", pr, e)) return fail(PFB_ERR_IO, "bad parse file\n");
+            if (dsize < 2) return fail(PFB_ERR_IO, "bad dict file\n");
+            if (dsize > 0xFFFFFFF0ull) return fail(PFB_ERR_LIMIT, "dictionary larger than 2^32 bytes is not supported yet");
+            parse.dsize = dsize;
+            std::vector<u32> wstart;       // host copy only where the .n file is missing
+            {
+                const u8 *dp = parse.dict.get();
+                DevBuf<u32> st3(3);        // [0] byte outside the alphabet, [1] bad tail
+                dev_memset(st3.get(), 0, 12, ws.st);
+                u32 *sp = st3.get();
+                DevBuf<u8> isend(dsize);
+                DevBuf<u32> rank(dsize);
+                u8 *ie = isend.get();
+                launch_for(dsize, ws.st, PFB_LAMBDA(u64 i) {
+                    const u8 c = dp[i];
+                    if (i + 1 == dsize) { ie[i] = 0; if (c != ENDOFDICT) sp[1] = 1u; return; }
+                    if (!(c == 1 || c == 2 || c == '-' || c == 'A' || c == 'C' || c == 'G' || c == 'N' || c == 'T')) sp[0] = 1u;
+                    if (i + 2 == dsize && c != ENDOFWORD) sp[1] = 1u;          // the last word must end right before EndOfDict
+                    ie[i] = c == ENDOFWORD ? 1 : 0;
+                });
+                const u64 Dw = scan_flags(isend.get(), rank.get(), dsize, ws);
+                u32 bad[3];
+                d2h(bad, st3.get(), 12, ws.st);
+                stream_sync(ws.st);
+                if (bad[1] || Dw == 0) return fail(PFB_ERR_IO, "bad dict file\n");
+                if (bad[0]) return fail(PFB_ERR_IO, "dict file contains a byte outside the parser's alphabet");
+                parse.Dw = Dw;
+                parse.wstart.alloc(Dw + 1);
+                u32 *wsp = parse.wstart.get();
+                const u32 *rk = rank.get();
+                launch_for(dsize, ws.st, PFB_LAMBDA(u64 i) {
+                    if (i == 0) wsp[0] = 0;
+                    if (ie[i]) wsp[rk[i] + 1] = (u32)i + 1;
+                });
+            }
             parse.P = pr.size() / 4;
-            parse.dict.alloc(parse.dsize); h2d(parse.dict.get(), dict.data(), dict.size(), ws.st);
-            parse.wstart.alloc(parse.Dw + 1); h2d(parse.wstart.get(), wstart.data(), wstart.size() * 4, ws.st);
             parse.parse.alloc(parse.P + 1);
             h2d(parse.parse.get(), pr.data(), parse.P * 4, ws.st);
             dev_memset(parse.parse.get() + parse.P, 0, 4, ws.st);
@@ -332,6 +353,9 @@ struct Engine {
                 unsigned long nn = 0;
                 if (f && fscanf(f, "%lu", &nn) == 1) parse.n = nn;
                 else {
+                    wstart.resize(parse.Dw + 1);
+                    d2h(wstart.data(), parse.wstart.get(), (parse.Dw + 1) * 4, ws.st);
+                    stream_sync(ws.st);
                     const u32 *p32 = (const u32 *)pr.data();
                     u64 tot = 0;
                     for (u64 k = 0; k < parse.P; ++k) { u64 d = p32[k] - 1; tot += (u64)(wstart[d + 1] - 1 - wstart[d]) - (k ? (u64)prm.w : 0); }

@@ -1,8 +1,8 @@
 // host_io.hpp -- host side of the drop-in boundary: FASTA/FASTQ (plain or gzip,
 // file or stdin) reader with kseq semantics (include/kseq.h:178-216 as driven by
-// PfParser::add_fasta, include/pfparser.hpp:299-337) and writers for the
-// reference's on-disk formats (include/pfbwt_io.hpp:44-82,
-// 224-249; src/pfbwt-f.cpp:229-243).
+// PfParser::add_fasta, include/pfparser.hpp:299-337); used for FASTQ / CR LF inputs and as the
+// checker of the device reader (ingest.cuh).  The writers of the reference's on-disk formats
+//  stream from HBM: devio.cuh.
 #pragma once
 #include <zlib.h>
 #include <cstdint>
@@ -168,20 +168,7 @@ inline void read_fasta_mem(const uint8_t *data, size_t len, int w, HostBytes &ou
     M.finish();
 }
 
-// ---------------------------------------------------------------- writers --
-inline int write_file(const std::string &path, const void *data, size_t bytes, std::string &err) {
-    FILE *f = fopen(path.c_str(), "wb");
-    if (!f) { err = "could not open " + path + " for writing"; return -1; }
-    const uint8_t *p = (const uint8_t *)data;
-    size_t done = 0;
-    while (done < bytes) {
-        size_t chunk = bytes - done < (1u << 30) ? bytes - done : (1u << 30);
-        if (fwrite(p + done, 1, chunk, f) != chunk) { fclose(f); err = "could not write file " + path; return -1; }
-        done += chunk;
-    }
-    if (fclose(f)) { err = "error closing " + path; return -1; }
-    return 0;
-}
+// ------------------------------------------------------------ small files --
 inline int read_file(const std::string &path, std::vector<uint8_t> &out, std::string &err) {
     FILE *f = fopen(path.c_str(), "rb");
     if (!f) { err = "error opening " + path; return -1; }
@@ -193,36 +180,4 @@ inline int read_file(const std::string &path, std::vector<uint8_t> &out, std::st
     fclose(f);
     return 0;
 }
-// widen u32 -> U-byte little-endian integers
-inline std::vector<uint8_t> widen_u32(const uint32_t *v, size_t n, int U) {
-    std::vector<uint8_t> o(n * (size_t)U);
-    if (U == 4) memcpy(o.data(), v, n * 4);
-    else { uint64_t *q = (uint64_t *)o.data(); for (size_t i = 0; i < n; ++i) q[i] = v[i]; }
-    return o;
-}
-inline std::vector<uint8_t> narrow_u64(const uint64_t *v, size_t n, int U) {
-    std::vector<uint8_t> o(n * (size_t)U);
-    if (U == 8) memcpy(o.data(), v, n * 8);
-    else { uint32_t *q = (uint32_t *)o.data(); for (size_t i = 0; i < n; ++i) q[i] = (uint32_t)v[i]; }
-    return o;
-}
-
-// one rank's slice of a file written by several processes: every writer sets the final size (idempotent)
-// and writes its bytes at its own offset
-inline int write_file_at(const std::string &path, const void *data, size_t bytes, uint64_t offset, uint64_t final_size, std::string &err) {
-    int fd = open(path.c_str(), O_CREAT | O_WRONLY, 0644);
-    if (fd < 0) { err = "could not open " + path; return -1; }
-    if (ftruncate(fd, (off_t)final_size) != 0) { close(fd); err = "could not size " + path; return -1; }
-    const char *p = (const char *)data;
-    size_t left = bytes;
-    uint64_t off = offset;
-    while (left) {
-        ssize_t k = pwrite(fd, p, left, (off_t)off);
-        if (k <= 0) { close(fd); err = "write failed: " + path; return -1; }
-        p += k; off += (uint64_t)k; left -= (size_t)k;
-    }
-    close(fd);
-    return 0;
-}
-
 }  // namespace pfb
