@@ -2,20 +2,19 @@
 // launch per digit ("onesweep": per-tile digit counts are chained through a decoupled
 // look-back array, so every pass reads and writes each pair exactly once).
 //
-//   k_radix_hist0   digit histogram of the first pass (the dictionary key kernel can
-//                   supply it for free instead)
+//   k_radix_hist_all  digit histograms of ALL passes in one read of the keys (shared-memory counters per CTA)
 //   k_radix_pass    one CTA per tile of RX_TILE pairs, tile ids handed out by an atomic
 //                   counter (a tile only ever waits for tiles that are already running):
 //                     warp-striped loads -> per-warp digit counters in shared memory with
 //                     match.any ranking (stable) -> column scan -> look-back per digit ->
 //                     pairs reordered through shared memory -> unit-stride runs to HBM.
-//                   While the keys are in registers the histogram of the NEXT digit is counted,
-//                   so no separate histogram pass ever re-reads the keys.
 //   values can be "iota" in the first pass (value = position): the identity permutation is never
 //   materialised.
 //
 // HBM traffic per pass: 12 B read + 12 B written per pair (first pass with iota values: 8 B read)
-// + 3 x 8 B x 256 look-back words per 5120-pair tile (5 %).
+// + 3 x 8 B x 256 look-back words per 5120-pair tile (5 %); the histogram kernel reads the keys once more (8 B per pair
+// for the whole sort).  Counting the next digit inside a pass and fusing the counts into the key kernel were both
+// measured slower on B200.
 #pragma once
 
 namespace pfb {
