@@ -13,8 +13,7 @@
 //
 // HBM traffic per pass: 12 B read + 12 B written per pair (first pass with iota values: 8 B read)
 // + 3 x 8 B x 256 look-back words per 5120-pair tile (5 %); the histogram kernel reads the keys once more (8 B per pair
-// for the whole sort).  Counting the next digit inside a pass and fusing the counts into the key kernel were both
-// measured slower on B200.
+// for the whole sort).  Fusing the counts into the key kernel was measured slower on B200.
 #pragma once
 
 namespace pfb {
