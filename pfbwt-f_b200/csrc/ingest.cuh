@@ -39,21 +39,40 @@ struct IngestResult {
 // that starts inside the tile, 0 when none does.  *bad is raised for what only the host reader handles.
 template <class FH, class FK>
 PFB_HD inline u32 ingest_walk_tile(const u8 *R, u64 m, u64 p0, u64 t, u32 kind, u32 *bad, FH hdr, FK keep) {
-    u64 lo = t * ING_TILE, hi = lo + ING_TILE;
+    const u64 base = t * ING_TILE;
+    u64 lo = base, hi = base + ING_TILE;
     if (hi > m) hi = m;
     if (lo < p0) lo = p0;
+    if (lo >= hi) return 0;
+    // eight 8-byte loads per tile (R is 512-byte aligned and has ING_TILE spare bytes behind m); the bytes of a word
+    // are walked with the loop unrolled, the words are not (keeps the three kernels small)
     u32 started = 0;
-    u8 prev = lo > p0 ? R[lo - 1] : (u8)'\n';
-    for (u64 i = lo; i < hi; ++i) {
-        const u8 c = R[i];
-        if (prev == '\n') {                      // kseq.h:194-198: first character of a line
-            if (c == '>') { kind = 2; hdr(i); }
-            else { kind = 1; if (c == '+' || c == '@') *bad = 1u; }
-            started = kind;
+    u8 prev = lo == p0 ? (u8)'\n' : R[lo - 1];
+#pragma unroll 1
+    for (int q = 0; q < (int)ING_TILE / 8; ++q) {
+        const u64 wbase = base + 8ull * (u64)q;
+        if (wbase + 8 <= lo || wbase >= hi) continue;
+        u64 wd;
+#ifdef __CUDA_ARCH__
+        wd = *reinterpret_cast<const u64 *>(R + wbase);
+#else
+        memcpy(&wd, R + wbase, 8);
+#endif
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+            const u64 i = wbase + (u64)b;
+            const u8 c = (u8)(wd >> (8 * b));
+            if (i >= lo && i < hi) {
+                if (prev == '\n') {                      // kseq.h:194-198: first character of a line
+                    if (c == '>') { kind = 2; hdr(i); }
+                    else { kind = 1; if (c == '+' || c == '@') *bad = 1u; }
+                    started = kind;
+                }
+                if (c == '\r') *bad = 1u;
+                if (kind == 1 && c != '\n') keep(i, c);
+                prev = c;
+            }
         }
-        if (c == '\r') *bad = 1u;
-        if (kind == 1 && c != '\n') keep(i, c);
-        prev = c;
     }
     return started ? kind : 0;
 }
@@ -193,13 +212,30 @@ inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, 
             if (!kind) kind = 2u;
             u64 k = ko[t], h = ho[t];
             u32 dummy = 0;
+            // kept bytes are gathered in a word and leave as aligned 8-byte stores (bytes at the ragged ends)
+            u64 acc = 0, dst = k + W * (h - 1);
+            u32 na = 0;
+            auto flush_bytes = [&]() {
+                for (u32 b = 0; b < na; ++b) o[dst + b] = (u8)(acc >> (8 * b));
+                dst += na; na = 0; acc = 0;
+            };
             ingest_walk_tile(Rp, m, p0, t, kind, &dummy,
                 [&](u64 i) {
+                    flush_bytes();
                     ++h;                                     // record h starts; record h-1 (if any) is complete
                     if (h >= 2) { u8 *pad = o + k + W * (h - 2); for (u64 j = 0; j < W; ++j) pad[j] = 'A'; }
                     if (docs) { hp[h - 1] = i; ds[h - 1] = k + W * (h - 1); }
+                    dst = k + W * (h - 1);
                 },
-                [&](u64, u8 c) { o[k + W * (h - 1)] = c; ++k; });
+                [&](u64, u8 c) {
+                    acc |= (u64)c << (8 * na);
+                    ++na; ++k;
+                    if (((dst + na) & 7) == 0) {
+                        if (na == 8) { *reinterpret_cast<u64 *>(o + dst) = acc; dst += 8; na = 0; acc = 0; }
+                        else flush_bytes();
+                    }
+                });
+            flush_bytes();
         });
         u8 *pad = o + K + W * (H - 1);
         launch_for(W, st, PFB_LAMBDA(u64 j) { pad[j] = 'A'; });
