@@ -1,3 +1,5 @@
+"""config 2 text (10^9-base recipe of SURVEY.md 8(d): NumPy default_rng(1), uniform ACGT) as a FASTA file with 60-column lines.
+usage: python tools/make_fasta.py <bases> <out.fa>"""
 import numpy as np, sys
 n=int(sys.argv[1]); lw=60
 rng=np.random.default_rng(1); lut=np.frombuffer(b"ACGT",dtype=np.uint8)
