@@ -171,25 +171,48 @@ struct DivTest {
 //     validate against the hasher's alphabet.   (include/pfparser.hpp:337-346,
 //     include/hash.hpp:30-31).  8 bytes per thread, S is 16-byte aligned.
 // ---------------------------------------------------------------------------
+PFB_DEV inline u64 normalise_word(u64 x, u64 lim, bool non_acgt_to_a, u64 base, u64 *d_errpos) {
+    u64 y = 0;
+    for (u64 j = 0; j < lim; ++j) {
+        u32 c = (u32)(x >> (8 * j)) & 0xff;
+        if (c >= 'a' && c <= 'z') c -= 32;
+        bool acgt = (c == 'A') | (c == 'C') | (c == 'G') | (c == 'T');
+        if (non_acgt_to_a && !acgt) { c = 'A'; acgt = true; }
+        if (!(acgt | (c == 'N') | (c == '-'))) atomic_min(d_errpos, base + j);
+        y |= (u64)c << (8 * j);
+    }
+    return y;
+}
 inline void k_normalise(u8 *S, u64 n, bool non_acgt_to_a, u64 *d_errpos, pfbStream_t st) {
-    u64 nwords = (n + 7) / 8;
-    launch_for(nwords, st, PFB_LAMBDA(u64 i) {
-        u64 base = i * 8;
-        u64 lim = n - base < 8 ? n - base : 8;
-        u64 x = 0;
-        if (lim == 8) x = *reinterpret_cast<const u64 *>(S + base);
-        else for (u64 j = 0; j < lim; ++j) x |= (u64)S[base + j] << (8 * j);
-        u64 y = 0;
-        for (u64 j = 0; j < lim; ++j) {
-            u32 c = (u32)(x >> (8 * j)) & 0xff;
-            if (c >= 'a' && c <= 'z') c -= 32;
-            bool acgt = (c == 'A') | (c == 'C') | (c == 'G') | (c == 'T');
-            if (non_acgt_to_a && !acgt) { c = 'A'; acgt = true; }
-            if (!(acgt | (c == 'N') | (c == '-'))) atomic_min(d_errpos, base + j);
-            y |= (u64)c << (8 * j);
+    u64 nchunks = (n + 15) / 16;
+    launch_for(nchunks, st, PFB_LAMBDA(u64 i) {
+        u64 base = i * 16;
+        if (base + 16 <= n) {
+#ifdef __CUDA_ARCH__
+            uint4 v = *reinterpret_cast<const uint4 *>(S + base);
+            u64 x0 = (u64)v.x | ((u64)v.y << 32), x1 = (u64)v.z | ((u64)v.w << 32);
+#else
+            u64 x0 = *reinterpret_cast<const u64 *>(S + base), x1 = *reinterpret_cast<const u64 *>(S + base + 8);
+#endif
+            // fast path: a word of upper-case ACGT needs no work (the common case); everything else goes byte by byte
+            u64 y0 = normalise_word(x0, 8, non_acgt_to_a, base, d_errpos);
+            u64 y1 = normalise_word(x1, 8, non_acgt_to_a, base + 8, d_errpos);
+            if (y0 != x0 || y1 != x1) {
+#ifdef __CUDA_ARCH__
+                *reinterpret_cast<uint4 *>(S + base) = make_uint4((u32)y0, (u32)(y0 >> 32), (u32)y1, (u32)(y1 >> 32));
+#else
+                *reinterpret_cast<u64 *>(S + base) = y0; *reinterpret_cast<u64 *>(S + base + 8) = y1;
+#endif
+            }
+            return;
         }
-        if (lim == 8) *reinterpret_cast<u64 *>(S + base) = y;
-        else for (u64 j = 0; j < lim; ++j) S[base + j] = (u8)(y >> (8 * j));
+        for (u64 b = base; b < n; b += 8) {
+            u64 lim = n - b < 8 ? n - b : 8;
+            u64 x = 0;
+            for (u64 j = 0; j < lim; ++j) x |= (u64)S[b + j] << (8 * j);
+            u64 y = normalise_word(x, lim, non_acgt_to_a, b, d_errpos);
+            for (u64 j = 0; j < lim; ++j) S[b + j] = (u8)(y >> (8 * j));
+        }
     });
 }
 
