@@ -147,7 +147,8 @@ inline int read_fasta(const std::string &path, int w, HostBytes &out, FastaResul
     gzFile fp = path == "-" ? gzdopen(fileno(stdin), "r") : gzopen(path.c_str(), "r");
     if (fp == NULL) { err = "failed to open file!\n"; return -1; }
     gzbuffer(fp, 1 << 20);
-    const size_t BUFSZ = 8u << 20;
+    size_t BUFSZ = 8u << 20;
+    if (const char *e = getenv("PFB_READ_CHUNK")) { long v = atol(e); if (v > 0) BUFSZ = (size_t)v; }   // test knob: states across chunk ends
     std::vector<uint8_t> buf(BUFSZ);
     FastaMachine M(w, out, res, store_docs, base_n);
     for (;;) {

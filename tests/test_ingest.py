@@ -101,6 +101,21 @@ def test_ingest_logic_streams(name, how, emu, ref_bins, datadir):
         assert_same_files(host, dev, exts_for(True, True))
 
 
+@pytest.mark.parametrize("chunk", ["1", "7", "64"])
+def test_host_reader_across_chunk_ends(chunk, emu, ref_bins, datadir):
+    """the host reader (FASTQ, CR LF, and the checker of the device reader) is a state machine fed in chunks: with chunks of
+    1, 7 and 64 bytes (PFB_READ_CHUNK) every state is cut at a chunk end somewhere in these files"""
+    if not ref_bins["pfbwt-f"]:
+        pytest.skip("reference binaries not built")
+    for name in ("blank_lines_no_eol", "empty_records", "crlf", "fastq", "garbage_first"):
+        fa = write(datadir, f"hc_{name}", CASES[name])
+        ref, host = os.path.join(datadir, f"{name}.hcref"), os.path.join(datadir, f"{name}.hc{chunk}")
+        run([ref_bins["pfbwt-f"], "-s", "-o", ref, fa])
+        subprocess.run([emu, "--bits", "32", "-s", "-o", host, fa], check=True, env=dict(os.environ, PFB_INGEST="host", PFB_READ_CHUNK=chunk),
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        assert_same_files(ref, host, exts_for(True, False))
+
+
 def test_ingest_logic_invalid_character(emu, datadir):
     """a '>' that is not the first character of a line is sequence: the reference dies in the hasher (include/hash.hpp:31)"""
     fa = write(datadir, "gt_inside", BAD["gt_inside_line"])
