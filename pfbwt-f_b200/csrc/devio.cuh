@@ -133,6 +133,39 @@ inline int read_file_to_dev(int fd, u64 m, void *dptr, int device, F first, std:
 }
 #endif
 
+// device array -> a stream that must be written in order (--stdout bwt|sa, src/pfbwt-f.cpp:113-127): two pinned buffers,
+// the D2H of the next chunk runs while the current one is written.  No host copy of the whole array (a 64 GB .sa
+// would not fit next to the page cache).  0 ok, -1 with err set.
+inline int write_dev_stream(FILE *f, const void *dptr, size_t bytes, int device, pfbStream_t st, std::string &err) {
+    stream_sync(st);
+#ifdef PFB_EMU
+    (void)device;
+    if (bytes && fwrite(dptr, 1, bytes, f) != bytes) { err = "could not write to the output stream"; return -1; }
+    fflush(f);
+    return 0;
+#else
+    DevIoPool &pool = devio_pool();
+    std::lock_guard<std::mutex> lock(pool.mu);
+    if (!pool.ensure(2)) { err = "could not allocate pinned staging memory"; return -1; }
+    if (cudaSetDevice(device) != cudaSuccess) { err = "cudaSetDevice failed"; return -1; }
+    const size_t CH = DevIoPool::CHUNK;
+    const u64 nchunk = (bytes + CH - 1) / CH;
+    auto start = [&](u64 c) {
+        const size_t o = (size_t)c * CH, len = bytes - o < CH ? bytes - o : CH;
+        return cudaMemcpyAsync(pool.buf[c & 1], (const u8 *)dptr + o, len, cudaMemcpyDeviceToHost, pool.st[c & 1]) == cudaSuccess;
+    };
+    if (nchunk && !start(0)) { err = "device to host copy failed"; return -1; }
+    for (u64 c = 0; c < nchunk; ++c) {
+        const size_t o = (size_t)c * CH, len = bytes - o < CH ? bytes - o : CH;
+        if (cudaStreamSynchronize(pool.st[c & 1]) != cudaSuccess) { err = "device to host copy failed"; return -1; }
+        if (c + 1 < nchunk && !start(c + 1)) { err = "device to host copy failed"; return -1; }
+        if (fwrite(pool.buf[c & 1], 1, len, f) != len) { err = "could not write to the output stream"; return -1; }
+    }
+    fflush(f);
+    return 0;
+#endif
+}
+
 // whole file -> device buffer (allocated here, `slack` spare bytes behind the data).  0 ok, -1 with err set.
 inline int read_whole_file_to_dev(const std::string &path, DevBuf<u8> &buf, u64 &size, size_t slack, int device, pfbStream_t st, std::string &err) {
     int fd = open(path.c_str(), O_RDONLY);

@@ -455,7 +455,7 @@ struct Engine {
                     if (!stdout_ext.empty()) { e = "--stdout is not available in a multi-GPU job"; return -1; }
                     return write_dev_file(prefix + "." + ext, b.get(), bytes, off, final_size, false, device, ws.st, e);
                 }
-                if (stdout_ext == ext) { auto v = to_host(b, bytes); fwrite(v.data(), 1, v.size(), stdout); fflush(stdout); return 0; }
+                if (stdout_ext == ext) return write_dev_stream(stdout, b.get(), bytes, device, ws.st, e);
                 return write_dev_file(prefix + "." + ext, b.get(), bytes, 0, bytes, true, device, ws.st, e);
             };
             if (emit("bwt", bwt.bwt, bwt.len, bwt.off, bwt.n + 1)) return fail(PFB_ERR_IO, e);
