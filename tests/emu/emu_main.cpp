@@ -49,8 +49,9 @@ int main(int argc, char **argv) {
         return 0;
     }
     if (out.empty()) out = in[0];
-    if (E.add_fasta(in[0])) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }
-    fprintf(stderr, "ingest: %s\n", E.ingest_files ? "device" : "host");
+    for (auto &f : in)                      // several inputs = one record list (PfParser::add_fasta called once per file)
+        if (E.add_fasta(f)) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }
+    fprintf(stderr, "ingest: %s\n", E.ingest_files == in.size() ? "device" : E.ingest_files ? "mixed" : "host");
     if (E.finalize() || E.do_parse_bwt() || E.save_parse(out, true, sa || rssa)) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }
     if (parse_only) return 0;
     if (E.build(sa, rssa) || E.write_bwt_files(out, sa, rssa, "")) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }

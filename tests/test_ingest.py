@@ -116,6 +116,24 @@ def test_host_reader_across_chunk_ends(chunk, emu, ref_bins, datadir):
         assert_same_files(ref, host, exts_for(True, False))
 
 
+def test_ingest_logic_several_files_mixed_readers(emu, ref_bins, datadir):
+    """add_fasta once per file: a plain file (device reader), a CR LF file (host reader) and a gzip file (device reader after
+    inflate) in one context give the parse of the concatenated record list"""
+    import gzip
+    if not ref_bins["pfbwt-f"]:
+        pytest.skip("reference binaries not built")
+    f1 = write(datadir, "mix1", CASES["tile_edges"])
+    f2 = write(datadir, "mix2", CASES["crlf"])
+    f3 = write(datadir, "mix3", gzip.compress(CASES["empty_records"] + b"\n")) + ".gz"
+    os.replace(f3[:-3], f3)
+    whole = write(datadir, "mix_all", CASES["tile_edges"] + CASES["crlf"] + CASES["empty_records"] + b"\n")
+    ref, dev = os.path.join(datadir, "mix.ref"), os.path.join(datadir, "mix.dev")
+    run([ref_bins["pfbwt-f"], "-s", "-r", "-o", ref, whole])
+    r = subprocess.run([emu, "--bits", "32", "-s", "-r", "-o", dev, f1, f2, f3], check=True, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    assert b"ingest: mixed" in r.stderr
+    assert_same_files(ref, dev, exts_for(True, True))
+
+
 def test_ingest_logic_invalid_character(emu, datadir):
     """a '>' that is not the first character of a line is sequence: the reference dies in the hasher (include/hash.hpp:31)"""
     fa = write(datadir, "gt_inside", BAD["gt_inside_line"])
