@@ -165,7 +165,8 @@ int pfb_get_shard_info(const pfb_ctx *, pfb_shard_info *);
 int pfb_upload_text(pfb_ctx *);
 /* whole hot path on text already resident in HBM: parse -> parse BWT -> BWT(+SA); no host copies */
 int pfb_run_resident(pfb_ctx *, int sa, int rssa);
-/* release device text / host staging once the parse exists */
+/* release the device text and the staged input (records in HBM, host staging) once the parse exists; parsing again
+ * needs pfb_clear and the input once more */
 int pfb_release_text(pfb_ctx *);
 /* forget all records, parses and outputs (keeps parameters and the CUDA stream) */
 int pfb_clear(pfb_ctx *);

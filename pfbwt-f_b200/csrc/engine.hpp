@@ -37,6 +37,7 @@ struct Engine {
     FastaResult docs;
     bool store_docs = false;
     u64 pending_n = 0;               // bytes of S accumulated in segs
+    bool input_released = false;     // pfb_release_text dropped the staged input (cleared by pfb_clear)
     float ingest_ms = 0;             // device time of the FASTA record kernels so far
     u64 ingest_files = 0;            // files that took the device reader
 
@@ -152,7 +153,7 @@ struct Engine {
     }
 
     void clear() {
-        segs.clear(); raw.n = 0; pending_n = 0; docs = FastaResult();
+        segs.clear(); raw.n = 0; pending_n = 0; docs = FastaResult(); input_released = false;
         text.buf.release(); text.n = 0;
         parse = DeviceParse(); bwt = DeviceBwt();
         invalidate();
@@ -165,6 +166,7 @@ struct Engine {
         try {
             const u64 n = pending_n;
             if (n == 0) return fail(PFB_ERR_ARG, "empty input");
+            if (input_released) return fail(PFB_ERR_ARG, "the input was released (pfb_release_text): pfb_clear and add it again");
             Timer timer(ws.st);
             text.buf.alloc(TextOnDevice::FRONT + n + (u64)prm.w + 64 + text.tail_room);
             text.n = n;
@@ -231,8 +233,16 @@ struct Engine {
         } catch (const Error &e) { return fail(e.code, e.what()); }
     }
 
-    // drop the text (and host staging) once the parse exists: only dict/parse are needed downstream
-    void release_text() { text.buf.release(); text_ready = false; }
+    // drop the text and the staged input (records in HBM from the device reader / add_records, host staging) once the
+    // parse exists: only dict/parse are needed downstream.  Parsing again needs pfb_clear + the input once more.
+    void release_text() {
+        text.buf.release(); text_ready = false;
+        if (parsed && !segs.empty()) {
+            for (auto &s : segs) s.dev.release();
+            raw.release();
+            input_released = true;
+        }
+    }
 
     // ---- copies to host -----------------------------------------------------------------
     template <class T>

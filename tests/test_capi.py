@@ -146,3 +146,27 @@ def test_trigger_known_answers():
         if p <= 100:
             assert d.sum() > 0
     ctx.close()
+
+
+@pytest.mark.gpu
+def test_release_text_drops_the_staged_input(datadir):
+    """pfb_release_text after the parse: the BWT build still works (it needs dict/parse only), parsing again is refused
+    with a message until pfb_clear"""
+    B = binding()
+    fa = os.path.join(datadir, "rel.fa")
+    seq = random_bases(200_000, 21)
+    write_fasta(fa, [("r", seq)], line_width=60)
+    ctx = B.Context(device=0, bits=32, w=10, p=100)
+    ctx.add_fasta(fa)
+    ctx.finalize(); ctx.bwt_of_parse()
+    ctx.release_text()
+    ctx.generate_bwt(True, False)
+    bwt1 = ctx.bwt().copy()
+    with pytest.raises(Exception) as ei:
+        ctx.finalize()
+    assert "released" in str(ei.value)
+    ctx.clear()
+    ctx.add_fasta(fa)
+    ctx.finalize(); ctx.bwt_of_parse(); ctx.generate_bwt(True, False)
+    assert np.array_equal(bwt1, ctx.bwt())
+    ctx.close()
