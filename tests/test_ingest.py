@@ -59,18 +59,18 @@ def emu():
 @pytest.mark.parametrize("name", sorted(CASES))
 def test_ingest_logic_matches_reference_and_host_reader(name, emu, ref_bins, datadir):
     fa = write(datadir, name, CASES[name])
-    flags = ["-s", "-r"]
+    flags = ["-s", "-r", "--print-docs"]
     dev, host = os.path.join(datadir, name + ".idev"), os.path.join(datadir, name + ".ihost")
     r = subprocess.run([emu, "--bits", "32"] + flags + ["-o", dev, fa], check=True, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
     took = b"ingest: host" if name in ("crlf", "fastq") else b"ingest: device"     # which reader the file must have taken
     assert took in r.stderr, r.stderr.decode()[-500:]
     env = dict(os.environ, PFB_INGEST="host")
     subprocess.run([emu, "--bits", "32"] + flags + ["-o", host, fa], check=True, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
-    assert_same_files(host, dev, exts_for(True, True))
+    assert_same_files(host, dev, exts_for(True, True) + ["docs"])
     if ref_bins["pfbwt-f"]:
         ref = os.path.join(datadir, name + ".iref")
         run([ref_bins["pfbwt-f"]] + flags + ["-o", ref, fa])
-        assert_same_files(ref, dev, exts_for(True, True))
+        assert_same_files(ref, dev, exts_for(True, True) + ["docs"])
 
 
 @pytest.mark.parametrize("name", ["blank_lines_no_eol", "tile_edges", "garbage_first", "crlf", "fastq"])
