@@ -116,6 +116,59 @@ def test_host_reader_across_chunk_ends(chunk, emu, ref_bins, datadir):
         assert_same_files(ref, host, exts_for(True, False))
 
 
+def random_fasta(seed):
+    """a structurally random FASTA: record count, header text, line widths (also per line), blank lines, missing last newline,
+    text before the first header, lower case / N"""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    out = bytearray()
+    if rng.random() < 0.3:
+        out += bytes(rng.choice(list(b"acgt xyz\n"), int(rng.integers(1, 200))).astype(np.uint8))
+    nrec = int(rng.integers(1, 6))
+    alphabet = np.frombuffer(b"ACGTACGTACGTACGTacgtN", dtype=np.uint8)
+    for r in range(nrec):
+        out += b">rec%d" % r
+        if rng.random() < 0.5:
+            out += b" " + bytes(rng.choice(list(b"abc \t>@+"), int(rng.integers(0, 90))).astype(np.uint8))
+        out += b"\n"
+        n = int(rng.integers(0, 30_000)) if rng.random() < 0.9 else 0
+        seq = alphabet[rng.integers(0, len(alphabet), n)].tobytes()
+        fixed = int(rng.integers(1, 200))
+        pos = 0
+        while pos < n:
+            wdt = fixed if rng.random() < 0.8 else int(rng.integers(1, 300))
+            out += seq[pos:pos + wdt] + b"\n"
+            pos += wdt
+            if rng.random() < 0.02:
+                out += b"\n" * int(rng.integers(1, 4))
+    if rng.random() < 0.3 and out.endswith(b"\n"):
+        out = out[:-1]
+    return bytes(out)
+
+
+@pytest.mark.parametrize("block", range(4))
+def test_ingest_logic_random_structures(block, emu, datadir):
+    """device reader logic == host reader on 40 structurally random files (-w 4 -p 11 so that short inputs still parse);
+    when the host route refuses an input (too few phrases) the device route must refuse it with the same message"""
+    for seed in range(block * 10, block * 10 + 10):
+        fa = write(datadir, f"rnd{seed}", random_fasta(1000 + seed))
+        res = {}
+        for mode in ("device", "host"):
+            env = dict(os.environ)
+            if mode == "host":
+                env["PFB_INGEST"] = "host"
+            o = os.path.join(datadir, f"rnd{seed}.{mode}")
+            r = subprocess.run([emu, "--bits", "64", "-s", "-r", "--print-docs", "--non-acgt-to-a", "-w", "4", "-p", "11", "-o", o, fa],
+                               env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+            res[mode] = (r.returncode, o, r.stderr)
+        assert res["device"][0] == res["host"][0], (seed, res["device"][2][-300:], res["host"][2][-300:])
+        if res["host"][0] == 0:
+            assert b"ingest: device" in res["device"][2], seed
+            assert_same_files(res["host"][1], res["device"][1], exts_for(True, True) + ["docs"])
+        else:
+            assert res["device"][2].splitlines()[-1:] == res["host"][2].splitlines()[-1:], seed
+
+
 def test_ingest_logic_several_files_mixed_readers(emu, ref_bins, datadir):
     """add_fasta once per file: a plain file (device reader), a CR LF file (host reader) and a gzip file (device reader after
     inflate) in one context give the parse of the concatenated record list"""
