@@ -5,6 +5,7 @@ files identical to the oracle.  The real parity tests are the `-m gpu` ones."""
 import os
 import subprocess
 import pytest
+import numpy as np
 from pfp_util import ROOT, write_fasta, random_bases, pangenome_records, nrun_records, run, exts_for, assert_same_files
 
 EMU = os.path.join(ROOT, "tests", "emu", "pfb_emu")
@@ -91,3 +92,62 @@ def test_emu_pivot_rounds(pivot, key_syms, emu, ref_bins, datadir):
     r = subprocess.run([emu, "--bits", "64"] + flags + ["-o", b, fa], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
     assert r.returncode == 0, r.stderr.decode()[-2000:]
     assert_same_files(a, b, exts_for(True, True))
+
+
+def fuzz_case(seed):
+    """random job: window / modulus, record mix (random, variants of one base, tandem repeats, poly-A, N runs, tiny records), flags"""
+    rng = np.random.default_rng(seed)
+    w = int(rng.integers(3, 13))
+    p = int(rng.choice([5, 7, 11, 20, 50, 100, 128]))
+    recs = []
+    base = random_bases(int(rng.integers(2_000, 25_000)), seed + 1)
+    for r in range(int(rng.integers(1, 7))):
+        kind = int(rng.integers(0, 6))
+        if kind == 0:
+            s = random_bases(int(rng.integers(1, 20_000)), seed * 31 + r)
+        elif kind == 1:                                     # variant of the shared base: long ties in the dictionary
+            s = base.copy()
+            k = int(rng.integers(0, 30))
+            pos = rng.integers(0, len(s), k)
+            s[pos] = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, k)]
+        elif kind == 2:                                     # tandem repeat
+            unit = random_bases(int(rng.integers(1, 40)), seed * 17 + r)
+            s = np.tile(unit, int(rng.integers(2, 400)))
+        elif kind == 3:                                     # one symbol
+            s = np.full(int(rng.integers(1, 5_000)), ord("ACGT"[int(rng.integers(0, 4))]), dtype=np.uint8)
+        elif kind == 4:                                     # N runs and lower case inside random text
+            s = random_bases(int(rng.integers(500, 15_000)), seed * 13 + r).copy()
+            a = int(rng.integers(0, len(s) // 2))
+            s[a:a + int(rng.integers(1, len(s) // 2))] = ord("N")
+            b = int(rng.integers(0, len(s) // 2))
+            s[b:b + 50] |= 0x20
+        else:
+            s = random_bases(int(rng.integers(0, 12)), seed * 7 + r)     # shorter than / around the window
+        recs.append((f"r{r}", s))
+    flags = ["-w", str(w), "-p", str(p)]
+    if rng.random() < 0.7:
+        flags.append("-s")
+    if rng.random() < 0.6:
+        flags.append("-r")
+    if rng.random() < 0.5:
+        flags.append("--non-acgt-to-a")
+    return recs, (32 if rng.random() < 0.5 else 64), flags
+
+
+@pytest.mark.parametrize("block", range(5))
+def test_emu_fuzz_against_restatement(block, emu, ref_bins, datadir):
+    """50 random jobs: the host logic of the device pipeline (emulator) writes what the C restatement of the reference writes;
+    a job the restatement refuses (e.g. a single dictionary word) must be refused too"""
+    for seed in range(block * 10, block * 10 + 10):
+        recs, bits, flags = fuzz_case(7000 + seed)
+        fa = os.path.join(datadir, f"fz{seed}.fa")
+        write_fasta(fa, recs, line_width=int(50 + seed))
+        a, b = os.path.join(datadir, f"fz{seed}.port"), os.path.join(datadir, f"fz{seed}.emu")
+        ra = subprocess.run([ref_bins["pfp_oracle"], "--bits", str(bits)] + flags + ["-o", a, fa], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        rb = subprocess.run([emu, "--bits", str(bits)] + flags + ["-o", b, fa], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        assert (ra.returncode == 0) == (rb.returncode == 0), (seed, flags, ra.stderr[-300:], rb.stderr[-300:])
+        if ra.returncode == 0:
+            try:
+                assert_same_files(a, b, exts_for("-s" in flags, "-r" in flags))
+            except AssertionError as e:
+                raise AssertionError(f"seed {seed} flags {flags} bits {bits}: {e}")
