@@ -170,3 +170,46 @@ def test_release_text_drops_the_staged_input(datadir):
     ctx.finalize(); ctx.bwt_of_parse(); ctx.generate_bwt(True, False)
     assert np.array_equal(bwt1, ctx.bwt())
     ctx.close()
+
+
+@pytest.mark.gpu
+def test_gpu_fuzz_against_restatement(ref_bins, datadir):
+    """the 50 random jobs of tests/test_emu_logic.py (window, modulus, record mix incl. tandem repeats, one-symbol records, N runs,
+    records shorter than the window; flags) through the C ABI on the device: every file equals the C restatement's, and a
+    job the restatement refuses is refused"""
+    import subprocess
+    from test_emu_logic import fuzz_case
+    from pfp_util import exts_for, assert_same_files
+    B = binding()
+    accepted = 0
+    njobs = int(os.environ.get("PFB_FUZZ_N", "50"))          # a longer hunt: PFB_FUZZ_N=500
+    for seed in range(njobs):
+        recs, bits, flags = fuzz_case(7000 + seed)
+        w, p = int(flags[flags.index("-w") + 1]), int(flags[flags.index("-p") + 1])
+        sa, rssa, ntoa = "-s" in flags, "-r" in flags, "--non-acgt-to-a" in flags
+        fa = os.path.join(datadir, f"gfz{seed}.fa")
+        write_fasta(fa, recs, line_width=50 + seed)
+        a, b = os.path.join(datadir, f"gfz{seed}.port"), os.path.join(datadir, f"gfz{seed}.gpu")
+        ra = subprocess.run([ref_bins["pfp_oracle"], "--bits", str(bits)] + flags + ["-o", a, fa], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        ctx = B.Context(device=0, bits=bits, w=w, p=p, get_sai=sa or rssa, non_acgt_to_a=ntoa)
+        try:
+            ctx.add_fasta(fa)
+            ctx.finalize()
+            ctx.bwt_of_parse()
+            ctx.save_parser(b, True, sa or rssa)
+            ctx.generate_bwt(sa, rssa)
+            ctx.write_bwt(b, sa, rssa)
+            ok = True
+        except Exception as e:
+            ok = False
+            msg = str(e)
+        finally:
+            ctx.close()
+        assert ok == (ra.returncode == 0), (seed, flags, ra.stderr[-300:], "" if ok else msg)
+        if ok:
+            accepted += 1
+            try:
+                assert_same_files(a, b, exts_for(sa, rssa))
+            except AssertionError as e:
+                raise AssertionError(f"seed {seed} flags {flags} bits {bits}: {e}")
+    assert accepted >= njobs * 4 // 5
