@@ -116,3 +116,25 @@ def test_nrun_job(tmp_path):
     recs = nrun_records(4, 40_000, 5, big_run=12_000)
     out, refp = run_job("emu", str(tmp_path), split_records(recs, 2), 10, 100, 64, True, True)
     assert_same_files(out, refp, exts_for(True, True))
+
+
+@pytest.mark.parametrize("seed", [9041, 9047, 9058, 9066])
+def test_random_jobs_over_ranks(tmp_path, seed):
+    """random jobs of tests/test_emu_logic.py::fuzz_case (window, modulus, record mix incl. tandem repeats, one-symbol and tiny
+    records) cut into 2-3 contiguous pieces: the ranks together write what the reference writes for the whole record list
+    (a one-off run over 90 seeds found no difference)"""
+    from test_emu_logic import fuzz_case
+    recs, bits, flags = fuzz_case(seed)
+    while len(recs) < 2:
+        seed += 1000
+        recs, bits, flags = fuzz_case(seed)
+    world = 2 if len(recs) < 3 else 3
+    cuts = [len(recs) * g // world for g in range(world + 1)]
+    pieces = [recs[cuts[g]:cuts[g + 1]] for g in range(world)]
+    w, p = int(flags[flags.index("-w") + 1]), int(flags[flags.index("-p") + 1])
+    sa, rssa = "-s" in flags, "-r" in flags
+    try:
+        out, refp = run_job("emu", str(tmp_path), pieces, w, p, bits, sa, rssa)
+    except RuntimeError:
+        pytest.skip("the reference refuses this job")
+    assert_same_files(out, refp, exts_for(sa, rssa))
