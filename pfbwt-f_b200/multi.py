@@ -48,8 +48,9 @@ def main():
         ids = [B.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
         ctx.shard_init_nccl(rank, world, ids[0])
-    per = (len(a.inputs) + world - 1) // world
-    mine = a.inputs[rank * per:(rank + 1) * per] if world > 1 else a.inputs
+    # contiguous, balanced, never empty (len(inputs) >= world): rank g takes files [n*g/world, n*(g+1)/world)
+    nin = len(a.inputs)
+    mine = a.inputs[nin * rank // world:nin * (rank + 1) // world]
     rc = 0
     try:
         for f in mine:

@@ -71,8 +71,9 @@ def run_job(mode, tmp, pieces, w, p, bits, sa, rssa, non_acgt_to_a=False, expect
 
 
 def split_records(recs, world):
-    k = (len(recs) + world - 1) // world
-    return [recs[i * k:(i + 1) * k] for i in range(world)]
+    """contiguous, balanced, never empty while len(recs) >= world (the rule of pfbwt-f_b200/multi.py)"""
+    n = len(recs)
+    return [recs[n * g // world:n * (g + 1) // world] for g in range(world)]
 
 
 @pytest.mark.parametrize("world,sa,rssa,bits", [(2, False, False, 32), (2, True, True, 32), (3, True, True, 64)])
