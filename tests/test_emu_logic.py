@@ -134,6 +134,11 @@ def fuzz_case(seed):
     return recs, (32 if rng.random() < 0.5 else 64), flags
 
 
+FUZZ_KNOBS = [{}, {"PFB_PIVOT": "1", "PFB_KEY_SYMS": "3"}, {"PFB_PIVOT": "0", "PFB_KEY_SYMS": "3"}, {"PFB_EXT_ROUNDS": "0"},
+              {"PFB_EXT_ROUNDS": "100", "PFB_PIVOT": "0"}, {"PFB_HARD_LIMITS": "2,4"}, {"PFB_KEY_COUNT_BITS": "0"},
+              {"PFB_KEY_COUNT_BITS": "2", "PFB_PIVOT": "1", "PFB_KEY_SYMS": "5"}]
+
+
 @pytest.mark.parametrize("block", range(5))
 def test_emu_fuzz_against_restatement(block, emu, ref_bins, datadir):
     """50 random jobs: the host logic of the device pipeline (emulator) writes what the C restatement of the reference writes;
@@ -144,10 +149,12 @@ def test_emu_fuzz_against_restatement(block, emu, ref_bins, datadir):
         write_fasta(fa, recs, line_width=int(50 + seed))
         a, b = os.path.join(datadir, f"fz{seed}.port"), os.path.join(datadir, f"fz{seed}.emu")
         ra = subprocess.run([ref_bins["pfp_oracle"], "--bits", str(bits)] + flags + ["-o", a, fa], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
-        rb = subprocess.run([emu, "--bits", str(bits)] + flags + ["-o", b, fa], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
-        assert (ra.returncode == 0) == (rb.returncode == 0), (seed, flags, ra.stderr[-300:], rb.stderr[-300:])
+        knobs = FUZZ_KNOBS[seed % len(FUZZ_KNOBS)]          # the tie-refinement / counting paths rotate with the seed
+        rb = subprocess.run([emu, "--bits", str(bits)] + flags + ["-o", b, fa], stdout=subprocess.PIPE, stderr=subprocess.PIPE,
+                            env=dict(os.environ, **knobs))
+        assert (ra.returncode == 0) == (rb.returncode == 0), (seed, flags, knobs, ra.stderr[-300:], rb.stderr[-300:])
         if ra.returncode == 0:
             try:
                 assert_same_files(a, b, exts_for("-s" in flags, "-r" in flags))
             except AssertionError as e:
-                raise AssertionError(f"seed {seed} flags {flags} bits {bits}: {e}")
+                raise AssertionError(f"seed {seed} flags {flags} bits {bits} knobs {knobs}: {e}")
