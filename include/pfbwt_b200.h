@@ -101,6 +101,15 @@ int pfb_set_params(pfb_ctx *, const pfb_parse_params *);
 int pfb_add_fasta(pfb_ctx *, const char *path_or_dash);
 /* same, from host buffers: nrec records, concatenated bytes in seq, lengths in rec_len */
 int pfb_add_records(pfb_ctx *, const uint8_t *seq, const uint64_t *rec_len, uint64_t nrec);
+/* a piece of ONE record (mid-record cut): `len` bytes continuing the record the previous chunk left open, or starting a new
+ * one; ends_record != 0 closes it (the w filler 'A's of include/pfparser.hpp:333-337 follow).  Chunks of a record added to
+ * one context concatenate; in a multi-GPU job rank g may end with an open record that rank g+1 continues - the
+ * w-overlapping chunk split that generalises the junction re-scan of PfParser::operator+= (include/pfparser.hpp:226-250). */
+int pfb_add_chunk(pfb_ctx *, const uint8_t *seq, uint64_t len, int ends_record);
+/* bytes [begin, end) of a plain FASTA file (one rank's share of a file split over the ranks of a multi-GPU job).  begin and
+ * end are moved forward to the next line start; sequence bytes before the range's first header continue the record of the
+ * previous range, and the last record stays open unless the next range starts with a header (or end reaches the file end). */
+int pfb_add_fasta_range(pfb_ctx *, const char *path, uint64_t begin, uint64_t end);
 /* PfParser::finalize, include/pfparser.hpp:484-492: runs the parse on the device */
 int pfb_finalize(pfb_ctx *);
 /* PfParser::bwt_of_parse, include/pfparser.hpp:379-467 */
@@ -147,7 +156,8 @@ int64_t pfb_get_docs(pfb_ctx *, uint64_t *starts_out);
 /* ---- one job over several GPUs: one process (context) per GPU --------------------------------
  * Generalises merge_pfp (src/merge_pfp.cpp:97-170: per-file parsers merged with operator+=,
  * include/pfparser.hpp:194-263) to a single job: rank r of `world` adds the records of the r-th
- * contiguous piece of the record list (rank order = text order, cuts at record boundaries), then
+ * contiguous piece of the text (rank order = text order; cuts at record boundaries with pfb_add_fasta /
+ * pfb_add_records, anywhere - also inside a record - with pfb_add_chunk / pfb_add_fasta_range), then
  * every rank calls pfb_finalize / pfb_parse_bwt / pfb_build_bwt / pfb_write_bwt at the same time
  * (collective calls).  After pfb_finalize every rank holds the whole parse (getters as before);
  * after pfb_build_bwt a rank holds one contiguous slice of .bwt/.sa/.ssa/.esa (pfb_get_shard_info,

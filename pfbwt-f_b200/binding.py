@@ -17,7 +17,7 @@ EXPORTS = [
     "pfb_copy_bwt", "pfb_copy_sa", "pfb_copy_ssa", "pfb_copy_esa", "pfb_get_docs", "pfb_upload_text",
     "pfb_run_resident", "pfb_release_text", "pfb_clear",
     "pfb_nccl_unique_id", "pfb_shard_init_nccl", "pfb_shard_init_host", "pfb_get_shard_info", "pfb_get_pending_bases",
-    "pfb_kat_trigger",
+    "pfb_kat_trigger", "pfb_add_chunk", "pfb_add_fasta_range",
 ]
 
 
@@ -73,6 +73,8 @@ def load():
     lib.pfb_set_params.argtypes = [vp, C.POINTER(ParseParams)]
     lib.pfb_add_fasta.argtypes = [vp, C.c_char_p]
     lib.pfb_add_records.argtypes = [vp, vp, vp, C.c_uint64]
+    lib.pfb_add_chunk.argtypes = [vp, vp, C.c_uint64, C.c_int]
+    lib.pfb_add_fasta_range.argtypes = [vp, C.c_char_p, C.c_uint64, C.c_uint64]
     for f in ["pfb_finalize", "pfb_parse_bwt", "pfb_upload_text", "pfb_release_text", "pfb_clear"]:
         getattr(lib, f).argtypes = [vp]
     lib.pfb_append.argtypes = [vp, vp]
@@ -172,6 +174,15 @@ class Context:
         rec_len = np.ascontiguousarray(rec_len, dtype=np.uint64)
         addr = seq if isinstance(seq, int) else seq.ctypes.data
         self._ck(self.lib.pfb_add_records(self.h, addr, rec_len.ctypes.data, len(rec_len)))
+
+    def add_chunk(self, seq, length=None, ends_record=True):
+        """a piece of one record (mid-record cut); seq: uint8 numpy array or an integer host address (+ length)"""
+        addr = seq if isinstance(seq, int) else seq.ctypes.data
+        n = int(length) if length is not None else int(seq.shape[0])
+        self._ck(self.lib.pfb_add_chunk(self.h, addr, n, int(ends_record)))
+
+    def add_fasta_range(self, path, begin, end):
+        self._ck(self.lib.pfb_add_fasta_range(self.h, path.encode(), int(begin), int(end)))
 
     def finalize(self):
         self._ck(self.lib.pfb_finalize(self.h))

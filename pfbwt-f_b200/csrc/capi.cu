@@ -130,6 +130,16 @@ int pfb_add_records(pfb_ctx *c, const uint8_t *seq, const uint64_t *rec_len, uin
     CTX_GUARD(c);
     return c->eng.add_records(seq, rec_len, nrec);
 }
+int pfb_add_chunk(pfb_ctx *c, const uint8_t *seq, uint64_t len, int ends_record) {
+    CTX_GUARD(c);
+    if (len && !seq) return c->eng.fail(PFB_ERR_ARG, "null chunk");
+    return c->eng.add_chunk(seq, len, ends_record != 0);
+}
+int pfb_add_fasta_range(pfb_ctx *c, const char *path, uint64_t begin, uint64_t end) {
+    CTX_GUARD(c);
+    if (!path) return c->eng.fail(PFB_ERR_ARG, "null path");
+    return c->eng.add_fasta_range(path, begin, end);
+}
 int pfb_finalize(pfb_ctx *c) { CTX_GUARD(c); return c->eng.finalize(); }
 int pfb_parse_bwt(pfb_ctx *c) { CTX_GUARD(c); return c->eng.do_parse_bwt(); }
 int pfb_append(pfb_ctx *l, pfb_ctx *r) {

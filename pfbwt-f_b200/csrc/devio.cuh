@@ -92,10 +92,10 @@ inline int write_dev_file(const std::string &path, const void *dptr, size_t byte
 }
 
 #ifndef PFB_EMU
-// Reads bytes [0, m) of fd into device memory.  first(buf, len) sees the first chunk on the host (the FASTA reader
+// Reads bytes [foff, foff + m) of fd into device memory.  first(buf, len) sees the first chunk on the host (the FASTA reader
 // looks for the first header there).  Returns 0, 1 when the file turned out shorter than m, -1 on errors.
 template <class F>
-inline int read_file_to_dev(int fd, u64 m, void *dptr, int device, F first, std::string &err) {
+inline int read_file_to_dev(int fd, u64 m, void *dptr, int device, F first, std::string &err, u64 foff = 0) {
     DevIoPool &pool = devio_pool();
     std::lock_guard<std::mutex> lock(pool.mu);
     const size_t CH = DevIoPool::CHUNK;
@@ -111,7 +111,7 @@ inline int read_file_to_dev(int fd, u64 m, void *dptr, int device, F first, std:
             const size_t len = (size_t)(m - o < CH ? m - o : CH);
             size_t have = 0;
             while (have < len) {
-                ssize_t got = pread(fd, pool.buf[k] + have, len - have, (off_t)(o + have));
+                ssize_t got = pread(fd, pool.buf[k] + have, len - have, (off_t)(foff + o + have));
                 if (got < 0) { bad = 2; return; }
                 if (got == 0) { bad = 1; return; }
                 have += (size_t)got;

@@ -65,6 +65,7 @@ struct Engine {
     }
 
     int add_fasta(const std::string &path) {
+        if (chunk_open) return fail(PFB_ERR_ARG, "a record is still open (pfb_add_chunk with ends_record = 0): close it first");
         // FASTA records are split on the device (ingest.cuh; gzip and stdin are inflated / drained on the host first);
         // FASTQ, CR LF line ends and inputs too large for HBM go through the host reader below
         try {
@@ -116,6 +117,7 @@ struct Engine {
     // Records handed over in caller memory go straight to HBM (one H2D per record, padding
     // written by a kernel); many small records are staged through `raw` instead.
     int add_records(const u8 *seq, const u64 *rec_len, u64 nrec) {
+        if (chunk_open) return fail(PFB_ERR_ARG, "a record is still open (pfb_add_chunk with ends_record = 0): close it first");
         try {
             u64 tot = 0;
             for (u64 r = 0; r < nrec; ++r) tot += rec_len[r];
@@ -152,8 +154,62 @@ struct Engine {
         } catch (const Error &e) { return fail(e.code, e.what()); }
     }
 
+    // A piece of ONE record: `len` bytes that continue the record the previous chunk left open (or start a new one);
+    // ends_record closes it (the w filler 'A's of include/pfparser.hpp:333-337 follow).  This is the mid-record cut of a
+    // multi-GPU job: rank g holds bytes [a_g, a_{g+1}) of the text whatever the record structure, and only the rank that
+    // holds a record's last byte pads it.  On one context, chunks of a record simply concatenate.
+    bool chunk_open = false;         // the last chunk added left its record open
+    int add_chunk(const u8 *seq, u64 len, bool ends_record) {
+        try {
+            if (prm.bits == 32 && docs.total_len + len > 0xFFFFFFFFull) return fail(PFB_ERR_TOO_LONG_32, "input too long, please use 64-bit version");
+            const u64 w = (u64)prm.w;
+            const u64 tot = len + (ends_record ? w : 0);
+            if (tot) {
+                Segment s;
+                s.on_device = true; s.len = tot;
+                s.dev.alloc(tot);
+                if (len) h2d(s.dev.get(), seq, len, ws.st);
+                if (ends_record) { u8 *pad = s.dev.get() + len; launch_for(w, ws.st, PFB_LAMBDA(u64 i) { pad[i] = 'A'; }); }
+                stream_sync(ws.st);   // caller memory may be reused after return
+                pending_n += tot;
+                segs.push_back(std::move(s));
+            }
+            if (ends_record) docs.nrec++;
+            docs.total_len += len;
+            chunk_open = !ends_record;
+            invalidate();
+            return PFB_OK;
+        } catch (const Error &e) { return fail(e.code, e.what()); }
+    }
+
+    // one rank's byte range of a plain FASTA file that is split over the ranks of a multi-GPU job (ingest.cuh, range mode)
+    int add_fasta_range(const std::string &path, u64 begin, u64 end) {
+        try {
+            IngestResult ir;
+            IngestRange rg;
+            rg.begin = begin; rg.end = end;
+            std::string e;
+            if (ingest_fasta_device(path, prm.w, store_docs, device, ws, ir, e, &rg) != 0) return fail(PFB_ERR_IO, e);
+            if (prm.bits == 32 && docs.total_len + ir.total_len > 0xFFFFFFFFull) return fail(PFB_ERR_TOO_LONG_32, "input too long, please use 64-bit version");
+            for (u64 s : ir.starts) docs.starts.push_back(pending_n + s);
+            for (auto &nm : ir.names) docs.names.push_back(nm);
+            docs.nrec += ir.nrec; docs.total_len += ir.total_len;
+            if (ir.len) {
+                Segment s;
+                s.on_device = true; s.len = ir.len;
+                s.dev = std::move(ir.seg);
+                pending_n += s.len;
+                segs.push_back(std::move(s));
+            }
+            if (rg.end > rg.begin) chunk_open = rg.open_end;
+            ingest_ms += ir.device_ms; ingest_files++;
+            invalidate();
+            return PFB_OK;
+        } catch (const Error &ex) { return fail(ex.code, ex.what()); }
+    }
+
     void clear() {
-        segs.clear(); raw.n = 0; pending_n = 0; docs = FastaResult(); input_released = false;
+        segs.clear(); raw.n = 0; pending_n = 0; docs = FastaResult(); input_released = false; chunk_open = false;
         text.buf.release(); text.n = 0;
         parse = DeviceParse(); bwt = DeviceBwt();
         invalidate();
@@ -165,7 +221,7 @@ struct Engine {
     int upload_text() {
         try {
             const u64 n = pending_n;
-            if (n == 0) return fail(PFB_ERR_ARG, "empty input");
+            if (n == 0 && !comm) return fail(PFB_ERR_ARG, "empty input");     // a rank of a multi-GPU job may hold nothing
             if (input_released) return fail(PFB_ERR_ARG, "the input was released (pfb_release_text): pfb_clear and add it again");
             Timer timer(ws.st);
             text.buf.alloc(TextOnDevice::FRONT + n + (u64)prm.w + 64 + text.tail_room);
@@ -202,6 +258,7 @@ struct Engine {
     // ---- finalize = parse on device ---------------------------------------------------
     int parse_device() {
         try {
+            if (chunk_open) return fail(PFB_ERR_ARG, "the last record is still open (pfb_add_chunk with ends_record = 0)");
             if (!text_ready) { int rc = upload_text(); if (rc) return rc; }
             parse = DeviceParse();
             int rc = parse_text(text, prm, parse, ws, tm, err);

@@ -80,16 +80,61 @@ PFB_HD inline u32 ingest_walk_tile(const u8 *R, u64 m, u64 p0, u64 t, u32 kind, 
 // 0 = done; 1 = not a case for the device reader, nothing consumed (caller uses read_fasta on the path);
 // 2 = not a case for the device reader, but the stream has been read: its bytes are in out.hostraw (caller uses
 // read_fasta_mem); -1 = error (err set)
-inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, int device, Workspace &ws, IngestResult &out, std::string &err) {
+// Range mode (rg != nullptr; pfb_add_fasta_range): only bytes [rg->begin, rg->end) of a plain file are taken, both ends
+// moved forward to a line start.  A range that does not start with a header continues the record of the range before it
+// (its bytes before the first header carry no new record; the w filler 'A's follow them when a header shows up in the
+// range); the range's last record is left open unless the next range starts with a header or the file ends.  FASTQ,
+// CR LF, gzip and streams are refused in this mode (-1).
+struct IngestRange { u64 begin = 0, end = 0; bool open_end = false; /* out */ };
+
+// first line start at or after x (x itself when the byte before it is a line end)
+inline int ingest_line_start(int fd, u64 size, u64 x, u64 &out) {
+    if (x == 0) { out = 0; return 0; }
+    if (x >= size) { out = size; return 0; }
+    char buf[4096];
+    u64 pos = x - 1;
+    while (pos < size) {
+        ssize_t got = pread(fd, buf, sizeof(buf), (off_t)pos);
+        if (got < 0) return -1;
+        if (got == 0) break;
+        const void *q = memchr(buf, '\n', (size_t)got);
+        if (q) { out = pos + (u64)((const char *)q - buf) + 1; return 0; }
+        pos += (u64)got;
+    }
+    out = size;
+    return 0;
+}
+
+inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, int device, Workspace &ws, IngestResult &out, std::string &err,
+                               IngestRange *rg = nullptr) {
     static const bool host_only = getenv("PFB_INGEST") && !strcmp(getenv("PFB_INGEST"), "host");
-    if (host_only) return 1;
+    if (host_only && !rg) return 1;
     // a regular uncompressed file is read straight into HBM by several readers; anything else (gzip, stdin, a pipe) is
     // inflated / drained by zlib into host memory first and uploaded in one piece - the records are split on the device
     // either way ("gzip-inflate stays on CPU, record splitting on device")
     int fd = -1;
     bool stream = path == "-";
-    u64 m = 0;
-    if (!stream) {
+    u64 m = 0, fbase = 0;                                    // bytes taken, file offset of the first one
+    u32 lead = 0;                                            // range mode: the range starts inside a record
+    bool closed = true;                                      // the last record ends with the bytes taken
+    if (rg) {
+        if (stream) { err = "a byte range needs a regular file"; return -1; }
+        fd = open(path.c_str(), O_RDONLY);
+        struct stat sb;
+        if (fd < 0 || fstat(fd, &sb) != 0 || !S_ISREG(sb.st_mode)) { if (fd >= 0) close(fd); err = "failed to open file!\n"; return -1; }
+        const u64 size = (u64)sb.st_size;
+        u64 a = 0, b = 0;
+        u8 c0[2] = {0, 0};
+        if (size < 2 || pread(fd, c0, 2, 0) != 2 || c0[0] != '>') { close(fd); err = "a byte range needs a plain FASTA file that starts with a header"; return -1; }
+        if (ingest_line_start(fd, size, rg->begin, a) || ingest_line_start(fd, size, rg->end, b)) { close(fd); err = "error reading input"; return -1; }
+        if (a >= b) { close(fd); out.len = 0; rg->open_end = b < size; rg->begin = a; rg->end = b; return 0; }     // nothing in this range
+        u8 ca = 0, cb = 0;
+        if (pread(fd, &ca, 1, (off_t)a) != 1 || (b < size && pread(fd, &cb, 1, (off_t)b) != 1)) { close(fd); err = "error reading input"; return -1; }
+        lead = (a > 0 && ca != '>') ? 1u : 0u;
+        closed = b >= size || cb == '>';
+        rg->begin = a; rg->end = b; rg->open_end = !closed;
+        m = b - a; fbase = a;
+    } else if (!stream) {
         fd = open(path.c_str(), O_RDONLY);
         if (fd < 0) return 1;                                // the host reader reports the error its way
         struct stat sb;
@@ -124,7 +169,8 @@ inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, 
         look_for_marker(hb.p, 0, m);
         if (p0 == ~0ull || first_marker != '>') return 2;
     }
-    const int decline = stream ? 2 : 1;
+    const int decline = rg ? -1 : stream ? 2 : 1;
+    if (rg) err = "a byte range needs a plain FASTA file (no FASTQ records, no CR LF line ends) that fits the device";
 
     pfbStream_t st = ws.st;
 #ifndef PFB_EMU
@@ -144,22 +190,24 @@ inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, 
 #ifdef PFB_EMU
         u64 off = 0;
         while (off < m) {
-            ssize_t got = read(fd, R.get() + off, (size_t)(m - off < (1u << 26) ? m - off : (1u << 26)));
+            ssize_t got = pread(fd, R.get() + off, (size_t)(m - off < (1u << 26) ? m - off : (1u << 26)), (off_t)(fbase + off));
             if (got < 0) { close(fd); err = "error reading input"; return -1; }
             if (got == 0) break;
             look_for_marker(R.get() + off, off, (u64)got);
             off += (u64)got;
         }
-        if (off != m) { close(fd); return 1; }
+        if (off != m) { close(fd); return rg ? -1 : 1; }
 #else
         // the first header must show up in the first 16 MB chunk; otherwise the host reader takes the file
         std::string e;
         stream_sync(st);             // R may reuse a block that work queued on st still reads; the copies run on other streams
-        const int rc = read_file_to_dev(fd, m, R.get(), device, [&](const u8 *b, size_t len) { look_for_marker(b, 0, (u64)len); }, e);
-        if (rc) { close(fd); if (rc < 0) { err = e; return -1; } return 1; }
+        const int rc = read_file_to_dev(fd, m, R.get(), device, [&](const u8 *b, size_t len) { look_for_marker(b, 0, (u64)len); }, e, fbase);
+        if (rc) { close(fd); if (rc < 0) { err = e; return -1; } return rg ? -1 : 1; }
 #endif
-        if (p0 == ~0ull || first_marker != '>') { close(fd); stream_sync(st); return 1; }
+        if (rg) p0 = 0;                                      // the range starts at a line start: a header, or sequence of the open record
+        else if (p0 == ~0ull || first_marker != '>') { close(fd); stream_sync(st); return 1; }
     }
+    const u32 kind0 = lead ? 1u : 2u;                        // kind of the line the first tile starts in
 
     Timer timer(st);
     const u64 ntile = (m + ING_TILE - 1) / ING_TILE;
@@ -172,7 +220,7 @@ inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, 
     {
         u64 *tg = tag.get();
         launch_for(ntile, st, PFB_LAMBDA(u64 t) {
-            u32 k = ingest_walk_tile(Rp, m, p0, t, 2u, badp, [](u64) {}, [](u64, u8) {});
+            u32 k = ingest_walk_tile(Rp, m, p0, t, kind0, badp, [](u64) {}, [](u64, u8) {});
             tg[t] = k ? ((t + 1) << 2) | k : 0ull;
         });
     }
@@ -184,8 +232,8 @@ inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, 
         const u64 *en = ent.get();
         u32 *kc = keptc.get(), *hc = hdrc.get();
         launch_for(ntile, st, PFB_LAMBDA(u64 t) {
-            u32 kind = t ? (u32)(en[t - 1] & 3) : 2u;
-            if (!kind) kind = 2u;                            // nothing started yet: still before the first header
+            u32 kind = t ? (u32)(en[t - 1] & 3) : kind0;
+            if (!kind) kind = kind0;                         // nothing started yet: still before the first header
             u32 nk = 0, nh = 0;
             u32 dummy = 0;
             ingest_walk_tile(Rp, m, p0, t, kind, &dummy, [&](u64) { ++nh; }, [&](u64, u8) { ++nk; });
@@ -195,12 +243,14 @@ inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, 
     exclusive_sum<u32, u64>(keptc.get(), koff.get(), ntile, ws.sc, st);
     exclusive_sum<u32, u64>(hdrc.get(), hoff.get(), ntile, ws.sc, st);
     const u64 K = read_scalar(koff.get() + (ntile - 1), st) + read_scalar(keptc.get() + (ntile - 1), st);
-    const u64 H = read_scalar(hoff.get() + (ntile - 1), st) + read_scalar(hdrc.get() + (ntile - 1), st);
+    const u64 Hh = read_scalar(hoff.get() + (ntile - 1), st) + read_scalar(hdrc.get() + (ntile - 1), st);
+    const u64 H = Hh + lead;                                 // records seen (the open one a range starts in included)
     if (read_scalar(bad.get(), st) || H == 0) { if (fd >= 0) close(fd); return decline; }
+    if (rg) err.clear();
     // C: write
-    out.nrec = H; out.total_len = K; out.len = K + H * (u64)w;
-    out.seg.alloc(out.len);
-    DevBuf<u64> hpos(store_docs ? H : 1), dstart(store_docs ? H : 1);
+    out.nrec = closed ? H : H - 1; out.total_len = K; out.len = K + out.nrec * (u64)w;
+    out.seg.alloc(out.len ? out.len : 1);
+    DevBuf<u64> hpos(store_docs ? H + 1 : 1), dstart(store_docs ? H + 1 : 1);
     {
         const u64 *en = ent.get(), *ko = koff.get(), *ho = hoff.get();
         u8 *o = out.seg.get();
@@ -208,9 +258,9 @@ inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, 
         const u64 W = (u64)w;
         const bool docs = store_docs;
         launch_for(ntile, st, PFB_LAMBDA(u64 t) {
-            u32 kind = t ? (u32)(en[t - 1] & 3) : 2u;
-            if (!kind) kind = 2u;
-            u64 k = ko[t], h = ho[t];
+            u32 kind = t ? (u32)(en[t - 1] & 3) : kind0;
+            if (!kind) kind = kind0;
+            u64 k = ko[t], h = ho[t] + lead;
             u32 dummy = 0;
             // kept bytes are gathered in a word and leave as aligned 8-byte stores (bytes at the ragged ends)
             u64 acc = 0, dst = k + W * (h - 1);
@@ -224,7 +274,7 @@ inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, 
                     flush_bytes();
                     ++h;                                     // record h starts; record h-1 (if any) is complete
                     if (h >= 2) { u8 *pad = o + k + W * (h - 2); for (u64 j = 0; j < W; ++j) pad[j] = 'A'; }
-                    if (docs) { hp[h - 1] = i; ds[h - 1] = k + W * (h - 1); }
+                    if (docs) { hp[h - 1 - lead] = i; ds[h - 1 - lead] = k + W * (h - 1); }
                     dst = k + W * (h - 1);
                 },
                 [&](u64, u8 c) {
@@ -238,26 +288,26 @@ inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, 
             flush_bytes();
         });
         u8 *pad = o + K + W * (H - 1);
-        launch_for(W, st, PFB_LAMBDA(u64 j) { pad[j] = 'A'; });
+        if (closed) launch_for(W, st, PFB_LAMBDA(u64 j) { pad[j] = 'A'; });
     }
-    if (store_docs) {
-        std::vector<u64> hp(H);
-        out.starts.resize(H);
-        d2h(hp.data(), hpos.get(), H * 8, st);
-        d2h(out.starts.data(), dstart.get(), H * 8, st);
+    if (store_docs && Hh) {
+        std::vector<u64> hp(Hh);
+        out.starts.resize(Hh);
+        d2h(hp.data(), hpos.get(), Hh * 8, st);
+        d2h(out.starts.data(), dstart.get(), Hh * 8, st);
         stream_sync(st);
-        out.names.resize(H);
+        out.names.resize(Hh);
         char buf[256];
-        for (u64 r = 0; r < H; ++r) {                        // name = header up to the first white space (kseq.h:188)
+        for (u64 r = 0; r < Hh; ++r) {                       // name = header up to the first white space (kseq.h:188)
             std::string &nm = out.names[r];
-            u64 pos = hp[r] + 1;
+            u64 pos = fbase + hp[r] + 1;
             bool done = false;
             if (stream) {
                 const u8 *hp_ = out.hostraw.p;
                 while (pos < m && !isspace(hp_[pos])) nm.push_back((char)hp_[pos++]);
                 continue;
             }
-            while (!done && pos < m) {
+            while (!done && pos < fbase + m) {
                 ssize_t got = pread(fd, buf, sizeof(buf), (off_t)pos);
                 if (got <= 0) break;
                 for (ssize_t i = 0; i < got; ++i) {

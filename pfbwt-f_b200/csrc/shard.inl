@@ -68,7 +68,9 @@
             int rc = PFB_OK;
             if (!text_ready) { text.tail_room = 4096; rc = upload_text(); }
             u64 len = rc ? 0 : text.n;
-            if (!rc && len < w) rc = fail(PFB_ERR_ARG, "every rank needs at least one record");
+            // a rank may hold fewer than w bytes, or none at all (a byte range that covers only a header line): it then owns
+            // no phrase of its own making, but its bytes still travel as tail / head of its neighbours
+            if (!rc && chunk_open && g == G - 1) rc = fail(PFB_ERR_ARG, "the last rank's last record is still open (pfb_add_chunk with ends_record = 0)");
             u64 hdr[6] = {rc ? 1ull : 0ull, len, 0, 0, 0, 0};
             const u64 tl = len < w + 1 ? len : w + 1;
             if (!rc && tl) {
@@ -85,6 +87,7 @@
             for (int r = 0; r < G; ++r) { lens[(size_t)r] = all[6 * (size_t)r + 1]; starts[(size_t)r + 1] = starts[(size_t)r] + lens[(size_t)r]; }
             const u64 n_total = starts[(size_t)G];
             shard_start = starts[(size_t)g];
+            if (n_total == 0) return fail(PFB_ERR_ARG, "empty input");
             if (prm.bits == 32 && n_total > 0xFFFFFFFFull) return fail(PFB_ERR_TOO_LONG_32, "input too long, please use 64-bit version");
 
             // ---- 1. the w+1 bytes of T' before this rank's records -----------------------------------

@@ -64,14 +64,16 @@ int main(int argc, char **argv) {
 // ---- multi-rank logic check (tests/test_shard_gloo.py): one call = one rank of a job whose exchanges go
 // through the caller's host all-gather (torch.distributed / gloo).  Writes this rank's slices of
 // <out>.bwt/.sa/.ssa/.esa at their offsets and, on rank 0, the merged parse files.
+// range_end > range_begin: the rank takes that byte range of the (common) FASTA file instead of a file of its own
 extern "C" int pfb_emu_shard_run(int rank, int world, pfb_allgatherv_fn fn, void *user, const char *fasta, int w, int p, int bits,
-                                 int sa, int rssa, const char *out, unsigned long long *info /* 8 */) {
+                                 int sa, int rssa, const char *out, unsigned long long *info /* 8 */,
+                                 unsigned long long range_begin, unsigned long long range_end) {
     pfb::Engine E;
     E.prm.w = w; E.prm.p = (uint64_t)p; E.prm.bits = bits; E.prm.get_sai = sa || rssa;
     pfb::HostCallComm *hc = new pfb::HostCallComm();
     hc->rank = rank; hc->world = world; hc->fn = fn; hc->user = user;
     E.comm.reset(hc);
-    int rc = E.add_fasta(fasta);
+    int rc = range_end > range_begin ? E.add_fasta_range(fasta, range_begin, range_end) : E.add_fasta(fasta);
     if (rc) fprintf(stderr, "[emu rank %d] %s\n", rank, E.err.c_str());
     // a failed load still has to take part in the collective finalize
     rc = E.finalize();

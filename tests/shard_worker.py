@@ -53,6 +53,10 @@ def make_allgatherv():
 def main():
     mode, rank, world, port, out, w, p, bits, sa, rssa, fasta = sys.argv[1:12]
     rank, world, w, p, bits, sa, rssa = int(rank), int(world), int(w), int(p), int(bits), int(sa), int(rssa)
+    rng = None                     # "<path>@<begin>:<end>": this rank takes a byte range of a common FASTA file (mid-record cuts)
+    if "@" in fasta:
+        fasta, r_ = fasta.rsplit("@", 1)
+        rng = tuple(int(x) for x in r_.split(":"))
     dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
     cb = make_allgatherv()
     if mode == "emu":
@@ -60,8 +64,9 @@ def main():
         info = (ctypes.c_ulonglong * 8)()
         lib.pfb_emu_shard_run.argtypes = [ctypes.c_int, ctypes.c_int, ALLGATHERV, ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int,
                                           ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_char_p,
-                                          ctypes.POINTER(ctypes.c_ulonglong)]
-        rc = lib.pfb_emu_shard_run(rank, world, cb, None, fasta.encode(), w, p, bits, sa, rssa, out.encode(), info)
+                                          ctypes.POINTER(ctypes.c_ulonglong), ctypes.c_ulonglong, ctypes.c_ulonglong]
+        rc = lib.pfb_emu_shard_run(rank, world, cb, None, fasta.encode(), w, p, bits, sa, rssa, out.encode(), info,
+                                   rng[0] if rng else 0, rng[1] if rng else 0)
     else:
         from pfbwt_b200_loader import binding
         b = binding()
@@ -74,7 +79,10 @@ def main():
             ctx.shard_init_host(rank, world, cb)
         rc = 0
         try:
-            ctx.add_fasta(fasta)
+            if rng:
+                ctx.add_fasta_range(fasta, rng[0], rng[1])
+            else:
+                ctx.add_fasta(fasta)
             ctx.finalize()
             ctx.bwt_of_parse()
             if rank == 0:

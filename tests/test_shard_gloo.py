@@ -29,17 +29,26 @@ def free_port():
     return p
 
 
-def run_job(mode, tmp, pieces, w, p, bits, sa, rssa, non_acgt_to_a=False, expect_fail=False):
-    """pieces: list (one per rank) of record lists.  Returns (sharded prefix, reference prefix)."""
+def run_job(mode, tmp, pieces, w, p, bits, sa, rssa, non_acgt_to_a=False, expect_fail=False, byte_cuts=None, line_width=70):
+    """pieces: list (one per rank) of record lists.  Returns (sharded prefix, reference prefix).
+    byte_cuts = (world, [fractions]) instead splits ONE file holding all records by byte ranges (cuts fall anywhere,
+    also inside records and header lines: pfb_add_fasta_range)."""
     world = len(pieces)
     allrecs = [r for pc in pieces for r in pc]
     whole = os.path.join(tmp, "whole.fa")
-    write_fasta(whole, allrecs, line_width=70)
+    write_fasta(whole, allrecs, line_width=line_width)
     fas = []
-    for g, pc in enumerate(pieces):
-        fa = os.path.join(tmp, f"part{g}.fa")
-        write_fasta(fa, pc, line_width=70)
-        fas.append(fa)
+    if byte_cuts is not None:
+        world, fr = byte_cuts
+        size = os.path.getsize(whole)
+        cuts = [0] + [int(size * f) for f in fr] + [size]
+        assert len(cuts) == world + 1
+        fas = [f"{whole}@{cuts[g]}:{cuts[g + 1]}" for g in range(world)]
+    else:
+        for g, pc in enumerate(pieces):
+            fa = os.path.join(tmp, f"part{g}.fa")
+            write_fasta(fa, pc, line_width=line_width)
+            fas.append(fa)
     refp = os.path.join(tmp, "ref")
     cmd = [ref_bin("pfbwt-f64" if bits == 64 else "pfbwt-f"), "-w", str(w), "-p", str(p), "-o", refp]
     if sa:
@@ -139,3 +148,44 @@ def test_random_jobs_over_ranks(tmp_path, seed):
     except RuntimeError:
         pytest.skip("the reference refuses this job")
     assert_same_files(out, refp, exts_for(sa, rssa))
+
+
+# ---- mid-record cuts: ONE FASTA file split by byte ranges over the ranks (pfb_add_fasta_range) -----------------------
+@pytest.mark.parametrize("world,fracs,sa,rssa,bits", [
+    (2, [0.5], True, True, 32),                  # one record cut in the middle
+    (3, [0.31, 0.64], True, True, 64),
+    (4, [0.2, 0.5, 0.77], False, False, 32),
+])
+def test_single_record_split_by_bytes(tmp_path, world, fracs, sa, rssa, bits):
+    recs = [("one", random_bases(60_000, 321))]
+    out, refp = run_job("emu", str(tmp_path), [recs], 10, 100, bits, sa, rssa, byte_cuts=(world, fracs))
+    assert_same_files(out, refp, exts_for(sa, rssa))
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3, 4, 5, 6])
+def test_multi_record_split_by_bytes(tmp_path, seed):
+    """several records of uneven length, cuts at pseudo-random byte offsets: inside records, inside header lines, right at
+    a header, at a line end; small modulus so that triggers sit next to the cuts"""
+    rng = np.random.default_rng(seed)
+    recs = [(f"rec{i}_{'x' * int(rng.integers(0, 40))}", random_bases(int(rng.integers(30, 9000)), 1000 * seed + i)) for i in range(int(rng.integers(2, 7)))]
+    world = int(rng.integers(2, 4))
+    fracs = sorted(float(x) for x in rng.uniform(0.05, 0.95, world - 1))
+    w, p = (4, 7) if seed % 2 else (10, 50)
+    out, refp = run_job("emu", str(tmp_path), [recs], w, p, 32, True, True, byte_cuts=(world, fracs), line_width=int(rng.integers(20, 90)))
+    assert_same_files(out, refp, exts_for(True, True))
+
+
+def test_split_cut_exactly_at_header_and_in_header(tmp_path):
+    recs = [("alpha", random_bases(5000, 77)), ("beta_with_a_long_name_to_cut_inside", random_bases(7000, 78)), ("gamma", random_bases(6000, 79))]
+    whole = os.path.join(str(tmp_path), "probe.fa")
+    write_fasta(whole, recs, line_width=60)
+    data = open(whole, "rb").read()
+    size = len(data)
+    h2 = data.index(b">beta")
+    h3 = data.index(b">gamma")
+    for cuts in ([h2, h3], [h2 + 7, h3 - 1], [h2 - 1, h2 + 1]):
+        sub = tmp_path / f"c{cuts[0]}_{cuts[1]}"
+        sub.mkdir()
+        fr = [(c + 0.25) / size for c in cuts]
+        out, refp = run_job("emu", str(sub), [recs], 10, 100, 32, True, False, byte_cuts=(3, fr), line_width=60)
+        assert_same_files(out, refp, exts_for(True, False))
