@@ -76,3 +76,52 @@ def test_multi_launcher(tmp_path, world):
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600)
     assert r.returncode == 0, r.stderr.decode(errors="replace")[-3000:]
     assert_same_files(out, refp, exts_for(True, True))
+
+
+# ---- mid-record cuts (pfb_add_chunk / pfb_add_fasta_range) --------------------------------------------------------------
+@pytest.mark.parametrize("world,fracs,bits", [(2, [0.47], 32), (3, [0.3, 0.71], 64)])
+def test_one_record_split_by_bytes_shared_gpu(tmp_path, world, fracs, bits):
+    """ONE record (the shape of BASELINE.json configs[1]) cut inside the record: each rank takes a byte range of the file"""
+    recs = [("one", random_bases(3_000_000, 901))]
+    out, refp = run_job("cuda", str(tmp_path), [recs], 10, 100, bits, True, True, byte_cuts=(world, fracs))
+    assert_same_files(out, refp, exts_for(True, True))
+
+
+def test_records_split_by_bytes_shared_gpu(tmp_path):
+    recs = pangenome_records(200_000, 5, 200, seed=41) + [("tiny", random_bases(7, 1)), ("last", random_bases(90_000, 2))]
+    out, refp = run_job("cuda", str(tmp_path), [recs], 10, 100, 64, True, True, byte_cuts=(3, [0.21, 0.66]), line_width=61)
+    assert_same_files(out, refp, exts_for(True, True))
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_one_record_split_by_bytes_nccl(tmp_path, world):
+    if ngpu() < world:
+        pytest.skip(f"needs {world} GPUs")
+    recs = [("one", random_bases(4_000_000, 902))]
+    fr = [(g + 1) / world for g in range(world - 1)]
+    out, refp = run_job("nccl", str(tmp_path), [recs], 10, 100, 32, True, True, byte_cuts=(world, fr))
+    assert_same_files(out, refp, exts_for(True, True))
+
+
+def test_chunks_on_one_context_equal_records(tmp_path):
+    """chunks of a record added to ONE context concatenate: same parse and BWT as pfb_add_records"""
+    import numpy as np
+    from pfbwt_b200_loader import binding
+    B = binding()
+    a, b = random_bases(500_000, 5), random_bases(300_000, 6)
+    one = B.Context(device=0, bits=32, w=10, p=100, get_sai=True)
+    one.add_records(np.concatenate([a, b]), np.array([len(a), len(b)], dtype=np.uint64))
+    one.finalize(); one.bwt_of_parse(); one.generate_bwt(True, True)
+    two = B.Context(device=0, bits=32, w=10, p=100, get_sai=True)
+    two.add_chunk(np.ascontiguousarray(a[:123_457]), ends_record=False)
+    with pytest.raises(B.PfbError):
+        two.add_records(b, np.array([len(b)], dtype=np.uint64))            # a record is still open
+    two.add_chunk(np.ascontiguousarray(a[123_457:]), ends_record=True)
+    two.add_chunk(np.ascontiguousarray(b[:10]), ends_record=False)
+    with pytest.raises(B.PfbError):
+        two.finalize()                                                     # the last record must be closed
+    two.add_chunk(np.ascontiguousarray(b[10:]), ends_record=True)
+    two.finalize(); two.bwt_of_parse(); two.generate_bwt(True, True)
+    for f in ("dict", "parse", "occ", "bwt", "sa", "ssa", "esa"):
+        assert np.array_equal(getattr(one, f)(), getattr(two, f)()), f
+    one.close(); two.close()
