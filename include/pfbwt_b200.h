@@ -116,8 +116,14 @@ int pfb_finalize(pfb_ctx *);
 int pfb_parse_bwt(pfb_ctx *);
 /* PfParser::operator+=, include/pfparser.hpp:194-263 (call pfb_finalize(lhs) afterwards) */
 int pfb_append(pfb_ctx *lhs, pfb_ctx *rhs);
-/* save_parser + the bwt_of_parse writer: include/pfbwt_io.hpp:234-249, src/pfbwt-f.cpp:229-243 */
+/* save_parser + the bwt_of_parse writer: include/pfbwt_io.hpp:234-249, src/pfbwt-f.cpp:229-243.
+ * with_parse_bwt: 0 = .dict .occ .parse .n (.docs); 1 = those + .bwlast .ilist (.bwsai with with_sai);
+ * 2 = only .bwlast .ilist (.bwsai) - run_parser's third task, after the parse files were saved in its second */
 int pfb_save_parse(pfb_ctx *, const char *prefix, int with_parse_bwt, int with_sai);
+/* <prefix>.last (n_phrases bytes, PfParser::last_) and <prefix>.sai (n_phrases x bits/8, PfParser::sai_): the extensions
+ * include/utils.h:22,24 defines; the reference never writes them (only tests/test_parser.cpp:126,139 reads them), so they
+ * are written on request only */
+int pfb_save_last_sai(pfb_ctx *, const char *prefix, int with_last, int with_sai);
 /* load_parser (include/pfbwt_io.hpp:211-222) / PrefixFreeBWT ctor (include/pfbwt.hpp:64-81) */
 int pfb_load_parse(pfb_ctx *, const char *prefix, int with_parse_bwt, int with_sai);
 

@@ -12,7 +12,7 @@
 #include <string.h>
 
 int main(int argc, char **argv) {
-    int w = 10, p = 100, sa = 0, rssa = 0, bits = 32, ntoa = 0, parse_only = 0, merge = 0;
+    int w = 10, p = 100, sa = 0, rssa = 0, bits = 32, ntoa = 0, parse_only = 0, merge = 0, write_last = 0;
     const char *out = NULL; const char *in[1024]; int nin = 0;
     for (int i = 1; i < argc; ++i) {
         if (!strcmp(argv[i], "-w")) w = atoi(argv[++i]);
@@ -23,6 +23,7 @@ int main(int argc, char **argv) {
         else if (!strcmp(argv[i], "--non-acgt-to-a")) ntoa = 1;
         else if (!strcmp(argv[i], "--parse-only")) parse_only = 1;
         else if (!strcmp(argv[i], "--merge")) merge = 1;
+        else if (!strcmp(argv[i], "--write-last")) write_last = 1;   /* <prefix>.last / .sai = last_ / sai_ (include/pfparser.hpp:599-600) */
         else if (!strcmp(argv[i], "-o")) out = argv[++i];
         else if (nin < 1024) in[nin++] = argv[i];
     }
@@ -44,6 +45,17 @@ int main(int argc, char **argv) {
     if (!out) out = in[0];
     if (pfo_read_fasta(&o, in[0])) { fprintf(stderr, "%s\n", o.err); return 1; }
     if (pfo_parse(&o)) { fprintf(stderr, "%s\n", o.err); return 1; }
+    if (write_last) {
+        char fn[4096];
+        FILE *f;
+        snprintf(fn, sizeof(fn), "%s.last", out);
+        if (!(f = fopen(fn, "wb"))) return 1;
+        fwrite(o.last, 1, o.P, f); fclose(f);
+        snprintf(fn, sizeof(fn), "%s.sai", out);
+        if (!(f = fopen(fn, "wb"))) return 1;
+        for (uint64_t k = 0; k < o.P; ++k) { if (U == 4) { uint32_t v = (uint32_t)o.sai[k]; fwrite(&v, 4, 1, f); } else fwrite(&o.sai[k], 8, 1, f); }
+        fclose(f);
+    }
     if (pfo_parse_bwt(&o)) { fprintf(stderr, "%s\n", o.err); return 1; }
     if (pfo_write_parse_files(&o, out, U, sa || rssa)) return 1;
     if (parse_only) return 0;

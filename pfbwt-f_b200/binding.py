@@ -17,7 +17,7 @@ EXPORTS = [
     "pfb_copy_bwt", "pfb_copy_sa", "pfb_copy_ssa", "pfb_copy_esa", "pfb_get_docs", "pfb_upload_text",
     "pfb_run_resident", "pfb_release_text", "pfb_clear",
     "pfb_nccl_unique_id", "pfb_shard_init_nccl", "pfb_shard_init_host", "pfb_get_shard_info", "pfb_get_pending_bases",
-    "pfb_kat_trigger", "pfb_add_chunk", "pfb_add_fasta_range",
+    "pfb_kat_trigger", "pfb_add_chunk", "pfb_add_fasta_range", "pfb_save_last_sai",
 ]
 
 
@@ -81,6 +81,7 @@ def load():
     lib.pfb_kat_trigger.argtypes = [vp, vp, C.c_size_t, C.c_uint64, vp, vp]
     lib.pfb_save_parse.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
     lib.pfb_load_parse.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
+    lib.pfb_save_last_sai.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
     lib.pfb_build_bwt.argtypes = [vp, C.c_int, C.c_int]
     lib.pfb_run_resident.argtypes = [vp, C.c_int, C.c_int]
     lib.pfb_write_bwt.argtypes = [vp, C.c_char_p, C.c_int, C.c_int, C.c_char_p]
@@ -195,6 +196,9 @@ class Context:
 
     def save_parser(self, prefix, with_parse_bwt=False, with_sai=False):
         self._ck(self.lib.pfb_save_parse(self.h, prefix.encode(), int(with_parse_bwt), int(with_sai)))
+
+    def save_last_sai(self, prefix, with_last=True, with_sai=True):
+        self._ck(self.lib.pfb_save_last_sai(self.h, prefix.encode(), int(with_last), int(with_sai)))
 
     def load_parser(self, prefix, with_parse_bwt=False, with_sai=False):
         self._ck(self.lib.pfb_load_parse(self.h, prefix.encode(), int(with_parse_bwt), int(with_sai)))

@@ -151,7 +151,13 @@ int pfb_append(pfb_ctx *l, pfb_ctx *r) {
 }
 int pfb_save_parse(pfb_ctx *c, const char *prefix, int with_parse_bwt, int with_sai) {
     CTX_GUARD(c);
-    return c->eng.save_parse(prefix, with_parse_bwt != 0, with_sai != 0);
+    if (!prefix) return c->eng.fail(PFB_ERR_ARG, "null prefix");
+    return c->eng.save_parse(prefix, with_parse_bwt != 0, with_sai != 0, with_parse_bwt == 2);
+}
+int pfb_save_last_sai(pfb_ctx *c, const char *prefix, int with_last, int with_sai) {
+    CTX_GUARD(c);
+    if (!prefix) return c->eng.fail(PFB_ERR_ARG, "null prefix");
+    return c->eng.save_last_sai(prefix, with_last != 0, with_sai != 0);
 }
 int pfb_load_parse(pfb_ctx *c, const char *prefix, int with_parse_bwt, int with_sai) {
     CTX_GUARD(c);

@@ -329,11 +329,20 @@ struct Engine {
     }
 
     // ---- files: save_parser (include/pfbwt_io.hpp:234-249) + parse-bwt (src/pfbwt-f.cpp:229-235)
-    int save_parse(const std::string &prefix, bool with_parse_bwt, bool with_sai) {
+    // only_parse_bwt: just .bwlast/.ilist(/.bwsai) - run_parser writes the four parse files in its second task and the
+    // parse-BWT files in its third (src/pfbwt-f.cpp:221-236), so a failing bwt_of_parse leaves the former behind
+    int save_parse(const std::string &prefix, bool with_parse_bwt, bool with_sai, bool only_parse_bwt = false) {
         try {
             if (!parsed) return fail(PFB_ERR_ARG, "parse not finalized");
             const int U = prm.bits / 8;
             std::string e;
+            if (only_parse_bwt) {
+                if (!parse.has_parse_bwt) return fail(PFB_ERR_ARG, "parse BWT not computed");
+                if (dev_file(prefix + ".bwlast", parse.bwlast.get(), parse.P + 1, e)) return fail(PFB_ERR_IO, e);
+                if (dev_file_u32(prefix + ".ilist", parse.ilist, parse.P + 1, U, e)) return fail(PFB_ERR_IO, e);
+                if (with_sai && dev_file_u64(prefix + ".bwsai", parse.bwsai, parse.P + 1, U, e)) return fail(PFB_ERR_IO, e);
+                return PFB_OK;
+            }
             if (dev_file(prefix + ".dict", parse.dict.get(), parse.dsize, e)) return fail(PFB_ERR_IO, e);
             if (dev_file_u32(prefix + ".occ", parse.occ, parse.Dw, U, e)) return fail(PFB_ERR_IO, e);
             if (dev_file(prefix + ".parse", parse.parse.get(), parse.P * 4, e)) return fail(PFB_ERR_IO, e);
@@ -449,12 +458,45 @@ struct Engine {
                 stream_sync(ws.st);
                 parse.has_parse_bwt = true;
             }
+            docs = FastaResult();
+            if (store_docs) {          // load_doc_info, include/pfbwt_io.hpp:177-205 ("<name> <start>" per line)
+                FILE *f = fopen((prefix + ".docs").c_str(), "r");
+                if (!f) return fail(PFB_ERR_IO, "error opening doc file " + prefix + ".docs");
+                char *line = NULL;
+                size_t cap = 0;
+                while (getline(&line, &cap, f) >= 0) {
+                    char *save = NULL;
+                    char *tok = strtok_r(line, " ", &save);
+                    if (!tok) { free(line); fclose(f); return fail(PFB_ERR_IO, "error parsing name in doc file line"); }
+                    std::string nm(tok);
+                    tok = strtok_r(NULL, " ", &save);
+                    if (!tok) { free(line); fclose(f); return fail(PFB_ERR_IO, "error parsing size in doc file line: " + nm); }
+                    docs.names.push_back(nm);
+                    docs.starts.push_back(strtoull(tok, NULL, 10));
+                }
+                free(line);
+                fclose(f);
+                docs.nrec = docs.starts.size();
+            }
             parsed = true; built = false;
             return PFB_OK;
         } catch (const Error &e) { return fail(e.code, e.what()); }
     }
 
-    // ---- operator+= (include/pfparser.hpp:194-263): the result is defined as the parse of
+    // .last (P bytes = last_) and .sai (P x U = sai_): extensions include/utils.h:22,24 defines and only
+    // tests/test_parser.cpp:126,139 of the reference reads; written on request only
+    int save_last_sai(const std::string &prefix, bool with_last, bool with_sai) {
+        try {
+            if (!parsed) return fail(PFB_ERR_ARG, "parse not finalized");
+            if (parse.last.size() < parse.P || parse.sai.size() < parse.P) return fail(PFB_ERR_ARG, "last / sai are not held by a parse loaded from files");
+            std::string e;
+            if (with_last && dev_file(prefix + ".last", parse.last.get(), parse.P, e)) return fail(PFB_ERR_IO, e);
+            if (with_sai && dev_file_u64(prefix + ".sai", parse.sai, parse.P, prm.bits / 8, e)) return fail(PFB_ERR_IO, e);
+            return PFB_OK;
+        } catch (const Error &e) { return fail(e.code, e.what()); }
+    }
+
+    // ---- operator+=(include/pfparser.hpp:194-263): the result is defined as the parse of
     // the concatenated record list, so the rhs parse is expanded back to its text on the
     // device (phrases minus their w-byte overlaps) and queued as a device segment.
     int append_parse_of(Engine &rhs) {

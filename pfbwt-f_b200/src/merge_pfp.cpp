@@ -51,23 +51,33 @@ int main(int argc, char **argv) {
     pfb_ctx *acc = pfb_create(device, 64);
     if (!acc) { fprintf(stderr, "%s\n", pfb_create_error()); return 1; }
     if (pfb_set_params(acc, &pp)) { fprintf(stderr, "%s\n", pfb_last_error(acc)); return 1; }
+    // src/merge_pfp.cpp:122,156-160: with few files per thread the reference runs serially and logs to <out>.pfbwt.log;
+    // the threaded mode logs to stderr.  The merge itself is device work either way.
+    FILE *logf = stderr;
+    if (!(nthreads && prefixes.size() / nthreads > 2)) {
+        logf = fopen((output + ".pfbwt.log").c_str(), "w");
+        if (logf == NULL) { fprintf(stderr, "error opening log\n"); exit(1); }
+        fprintf(logf, "not using threads (%lu files, %lu threads specified)\n", prefixes.size(), nthreads);
+        fprintf(stderr, "not using threads (%lu files, %lu threads specified)\n", prefixes.size(), nthreads);
+    }
     for (auto &prefix : prefixes) {   // load_or_generate_parser_w_log, include/pfbwt_io.hpp:270-285
         if (exists(prefix + ".dict") && exists(prefix + ".parse")) {
-            fprintf(stderr, "loading %s, %s, and maybe %s from file\n", (prefix + ".dict").c_str(), (prefix + ".parse").c_str(), (prefix + ".docs").c_str());
+            fprintf(logf, "loading %s, %s, and maybe %s from file\n", (prefix + ".dict").c_str(), (prefix + ".parse").c_str(), (prefix + ".docs").c_str());
             pfb_ctx *rhs = pfb_create(device, 64);
             if (!rhs) { fprintf(stderr, "%s\n", pfb_create_error()); return 1; }
             if (pfb_set_params(rhs, &pp) || pfb_load_parse(rhs, prefix.c_str(), 0, 0)) { fprintf(stderr, "%s\n", pfb_last_error(rhs)); return 1; }
             if (pfb_append(acc, rhs)) { fprintf(stderr, "%s\n", pfb_last_error(acc)); return 1; }
             pfb_destroy(rhs);
         } else {
-            fprintf(stderr, "generating parse for %s\n", prefix.c_str());
+            fprintf(logf, "generating parse for %s\n", prefix.c_str());
             if (exists(prefix)) {
                 if (pfb_add_fasta(acc, prefix.c_str())) { fprintf(stderr, "%s\n", pfb_last_error(acc)); return 1; }
             } else {
-                fprintf(stderr, "ERROR: %s not found, cannot add it to parse!\n", prefix.c_str());
+                fprintf(logf, "ERROR: %s not found, cannot add it to parse!\n", prefix.c_str());
             }
         }
     }
+    if (logf != stderr) fflush(logf);
     if (pfb_finalize(acc)) { fprintf(stderr, "%s\n", pfb_last_error(acc)); return 1; }
     if (parse_bwt && pfb_parse_bwt(acc)) { fprintf(stderr, "%s: Success\n", pfb_last_error(acc)); return 1; }
     if (pfb_save_parse(acc, output.c_str(), parse_bwt, sai)) { fprintf(stderr, "%s\n", pfb_last_error(acc)); return 1; }

@@ -20,6 +20,7 @@ struct Args {
     std::string in_fname, output, stdout_ext;
     size_t w = 10, p = 100;
     int sa = 0, rssa = 0, mmap = 0, parse_only = 0, trim_non_acgt = 0, non_acgt_to_a = 0, pfbwt_only = 0, verbose = 0, print_docs = 0;
+    int write_last = 0, write_sai = 0;
     int device = 0;
 };
 
@@ -52,6 +53,8 @@ static void print_help() {
 "    --pfbwt-only        build pfbwt from parse + parse-bwt. Requires -o to match parse files' prefix.\n"
 "    --non-acgt-to-a     convert non-ACGT characters to A\n"
 "    --print-docs        write <prefix>.docs\n"
+"    --write-last        also write <prefix>.last (last char of every phrase, include/utils.h EXTLST)\n"
+"    --write-sai         also write <prefix>.sai (end position of every phrase, include/utils.h EXTSAI)\n"
 "    --stdout <ext>      output file ending <ext> will be stdout instead (bwt, sa)\n"
 "    --device <int>      CUDA device ordinal [default: 0]\n"
 "    -h                  print this help message\n");
@@ -68,6 +71,8 @@ static Args parse_args(int argc, char **argv) {
         {"trim-non-acgt", no_argument, &args.trim_non_acgt, 1},
         {"non-acgt-to-a", no_argument, &args.non_acgt_to_a, 1},
         {"print-docs", no_argument, &args.print_docs, 1},
+        {"write-last", no_argument, &args.write_last, 1},
+        {"write-sai", no_argument, &args.write_sai, 1},
         {"stdout", required_argument, NULL, 'c'},
         {"verbose", no_argument, &args.verbose, 1},
         {"sa", no_argument, NULL, 's'},
@@ -135,8 +140,12 @@ int main(int argc, char **argv) {
             if (pfb_add_fasta(ctx, args.in_fname.c_str())) die_ctx(ctx);
         }
         {
+            // src/pfbwt-f.cpp:221-228: the parse files are written in this task, before bwt_of_parse can fail
             Timer t("TASK\tfinalizing parse, writing dict, occs, and ranks\t");
-            if (pfb_finalize(ctx)) die_ctx(ctx);
+            { SubTimer t2("parse on device"); if (pfb_finalize(ctx)) die_ctx(ctx); }
+            SubTimer t3("writing parse files");
+            if (pfb_save_parse(ctx, args.output.c_str(), 0, 0)) die_ctx(ctx);
+            if ((args.write_last || args.write_sai) && pfb_save_last_sai(ctx, args.output.c_str(), args.write_last, args.write_sai)) die_ctx(ctx);
         }
         {
             Timer t("TASK\tranking and bwt-ing parse and processing last-chars\t");
@@ -147,8 +156,8 @@ int main(int argc, char **argv) {
                     exit(1);
                 }
             }
-            SubTimer t3("writing parse files");
-            if (pfb_save_parse(ctx, args.output.c_str(), 1, any_sa)) die_ctx(ctx);
+            SubTimer t3("writing parse BWT files");
+            if (pfb_save_parse(ctx, args.output.c_str(), 2, any_sa)) die_ctx(ctx);
         }
         if (args.trim_non_acgt) { FILE *f = fopen((args.output + ".ntab").c_str(), "wb"); if (f) fclose(f); }
         pfb_release_text(ctx);

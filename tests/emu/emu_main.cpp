@@ -16,7 +16,7 @@ size_t &dev_bytes_peak() { static size_t v = 0; return v; }
 }
 
 int main(int argc, char **argv) {
-    int w = 10, p = 100, sa = 0, rssa = 0, bits = 32, ntoa = 0, parse_only = 0, merge = 0, docs = 0;
+    int w = 10, p = 100, sa = 0, rssa = 0, bits = 32, ntoa = 0, parse_only = 0, merge = 0, docs = 0, write_last = 0;
     std::string out;
     std::vector<std::string> in;
     for (int i = 1; i < argc; ++i) {
@@ -30,6 +30,7 @@ int main(int argc, char **argv) {
         else if (a == "--parse-only") parse_only = 1;
         else if (a == "--print-docs") docs = 1;
         else if (a == "--merge") merge = 1;
+        else if (a == "--write-last") write_last = 1;
         else if (a == "-o") out = argv[++i];
         else in.push_back(a);
     }
@@ -41,7 +42,7 @@ int main(int argc, char **argv) {
         if (out.empty()) out = "out";
         for (auto &pfx : in) {
             pfb::Engine R;
-            R.prm = E.prm;
+            R.prm = E.prm; R.store_docs = docs;
             if (R.load_parse(pfx, false, false)) { fprintf(stderr, "%s\n", R.err.c_str()); return 1; }
             if (E.append_parse_of(R)) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }
         }
@@ -52,7 +53,9 @@ int main(int argc, char **argv) {
     for (auto &f : in)                      // several inputs = one record list (PfParser::add_fasta called once per file)
         if (E.add_fasta(f)) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }
     fprintf(stderr, "ingest: %s\n", E.ingest_files == in.size() ? "device" : E.ingest_files ? "mixed" : "host");
-    if (E.finalize() || E.do_parse_bwt() || E.save_parse(out, true, sa || rssa)) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }
+    // the order of run_parser (src/pfbwt-f.cpp:221-236): parse files first, parse-BWT files after bwt_of_parse
+    if (E.finalize() || E.save_parse(out, false, false) || (write_last && E.save_last_sai(out, true, true)) || E.do_parse_bwt() ||
+        E.save_parse(out, true, sa || rssa, true)) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }
     if (parse_only) return 0;
     if (E.build(sa, rssa) || E.write_bwt_files(out, sa, rssa, "")) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }
     fprintf(stderr, "# easy cases: %lu, # hard cases: %lu\nn: %lu\nr: %lu\nrounds: phrase %u parse_sa %u dict %u\n",

@@ -158,3 +158,31 @@ def test_emu_fuzz_against_restatement(block, emu, ref_bins, datadir):
                 assert_same_files(a, b, exts_for("-s" in flags, "-r" in flags))
             except AssertionError as e:
                 raise AssertionError(f"seed {seed} flags {flags} bits {bits} knobs {knobs}: {e}")
+
+
+def test_emu_write_last_sai_and_merge_docs(emu, ref_bins, datadir):
+    """host logic of two small rows: <o>.last / <o>.sai (= last_ / sai_ of the restatement) and --docs through a merge of
+    pre-parsed prefixes (load_parse reads <prefix>.docs, operator+= offsets the starts; include/pfbwt_io.hpp:216-218)"""
+    recs = pangenome_records(30_000, 4, 30, 5)
+    fa = os.path.join(datadir, "wl.fa")
+    write_fasta(fa, recs, line_width=50)
+    a, b = os.path.join(datadir, "wl.port"), os.path.join(datadir, "wl.emu")
+    run([ref_bins["pfp_oracle"], "--bits", "64", "--write-last", "--parse-only", "-o", a, fa])
+    run([emu, "--bits", "64", "--write-last", "--parse-only", "-o", b, fa])
+    assert_same_files(a, b, ["last", "sai", "parse"])
+    # docs: monolithic --print-docs == merge of two pre-parsed halves with their .docs
+    mono = os.path.join(datadir, "wl_mono")
+    run([emu, "--bits", "64", "--print-docs", "--parse-only", "-o", mono, fa])
+    parts = []
+    for g in range(2):
+        p = os.path.join(datadir, f"wl_part{g}.fa")
+        write_fasta(p, recs[2 * g:2 * g + 2], line_width=50)
+        run([emu, "--bits", "64", "--print-docs", "--parse-only", p])
+        parts.append(p)
+    merged = os.path.join(datadir, "wl_merged")
+    run([emu, "--merge", "--print-docs", "--bits", "64", "-o", merged] + parts)
+    assert_same_files(mono, merged, ["dict", "parse", "docs"])
+    if ref_bins["pfbwt-f64"]:
+        refd = os.path.join(datadir, "wl_refdocs")
+        run([ref_bins["pfbwt-f64"], "--print-docs", "--parse-only", "-o", refd, fa])
+        assert_same_files(refd, merged, ["docs"])

@@ -189,3 +189,58 @@ def test_config2_full_size_bwt_hash(datadir):
                 os.remove(p)
             except OSError:
                 pass
+
+
+@pytest.mark.parametrize("bits", [32, 64])
+def test_cli_write_last_sai(bits, ref_bins, datadir):
+    """--write-last / --write-sai: <o>.last = PfParser::last_ (P bytes), <o>.sai = sai_ (P x U); the reference defines the
+    extensions (include/utils.h:22,24) but never writes them, so the checker is the CPU restatement's arrays"""
+    fa = os.path.join(datadir, f"wl{bits}.fa")
+    write_fasta(fa, pangenome_records(120_000, 3, 100, 91) + [("x", random_bases(5, 3))], line_width=70)
+    a, b = os.path.join(datadir, f"wl{bits}.ref"), os.path.join(datadir, f"wl{bits}.gpu")
+    run([ref_bins["pfp_oracle"], "--bits", str(bits), "--write-last", "--parse-only", "-o", a, fa])
+    run([os.path.join(BIN, "pfbwt-f64" if bits == 64 else "pfbwt-f"), "--write-last", "--write-sai", "--parse-only", "-o", b, fa])
+    assert_same_files(a, b, ["last", "sai", "parse", "dict"])
+    P = os.path.getsize(a + ".parse") // 4
+    assert os.path.getsize(b + ".last") == P and os.path.getsize(b + ".sai") == P * bits // 8
+
+
+def test_cli_merge_docs_and_log(ref_bins, datadir):
+    """merge_pfp --docs over pre-parsed prefixes: the loaded .docs are offset and merged (include/pfbwt_io.hpp:216-218,
+    include/pfparser.hpp:194-263), and the serial mode writes <out>.pfbwt.log (src/merge_pfp.cpp:157-160)"""
+    if not ref_bins["merge_pfp"]:
+        pytest.skip("reference binaries not built")
+    recs = pangenome_records(60_000, 4, 60, 33)
+    outs = {}
+    for who, parse_exe, merge_exe in (("ref", ref_bins["pfbwt-f64"], ref_bins["merge_pfp"]),
+                                      ("gpu", os.path.join(BIN, "pfbwt-f64"), os.path.join(BIN, "merge_pfp"))):
+        parts = []
+        for g in range(2):
+            p = os.path.join(datadir, f"md_{who}{g}.fa")
+            write_fasta(p, [(f"{n}_{g}", s) for n, s in recs[2 * g:2 * g + 2]], line_width=60)
+            run([parse_exe, "--parse-only", "--print-docs", p])
+            parts.append(p)
+        out = os.path.join(datadir, f"md_{who}_merged")
+        run([merge_exe, "--docs", "-o", out, "-t", "1"] + parts)
+        outs[who] = out
+    assert_same_files(outs["ref"], outs["gpu"], ["dict", "occ", "parse", "n", "docs"])
+    rl = open(outs["ref"] + ".pfbwt.log").read().replace("md_ref", "md_X")
+    gl = open(outs["gpu"] + ".pfbwt.log").read().replace("md_gpu", "md_X")
+    assert rl == gl and "not using threads (2 files, 1 threads specified)" in gl
+
+
+def test_cli_one_word_leaves_parse_files(ref_bins, datadir):
+    """the reference saves .dict/.occ/.parse/.n before bwt_of_parse (src/pfbwt-f.cpp:221-228): on the 'only one dict word'
+    exit those files exist, the parse-BWT files do not"""
+    fa = os.path.join(datadir, "oneword.fa")
+    write_fasta(fa, [("r", random_bases(3000, 5))])
+    a, b = os.path.join(datadir, "oneword.ref"), os.path.join(datadir, "oneword.gpu")
+    rb = run([os.path.join(BIN, "pfbwt-f"), "-p", "1000000", "-o", b, fa], check=False)
+    assert rb.returncode == 1 and b"only one dict word" in rb.stderr
+    for e in ("dict", "occ", "parse", "n"):
+        assert os.path.exists(b + "." + e), e
+    assert not os.path.exists(b + ".bwlast") and not os.path.exists(b + ".ilist")
+    if ref_bins["pfbwt-f"]:
+        ra = run([ref_bins["pfbwt-f"], "-p", "1000000", "-o", a, fa], check=False)
+        assert ra.returncode == 1
+        assert_same_files(a, b, ["dict", "occ", "parse", "n"])
