@@ -51,7 +51,7 @@ inline u64 compact_indices(const u8 *flags, u64 n, DevBuf<u32> &scratch_idx, Dev
 //     Multi-GPU (sh != nullptr): the rank sorts only the valid suffixes whose code falls in its
 //     range of the key space (splitters from a weighted histogram of the leading code bits, computed
 //     identically on every rank from the replicated dictionary); *n_sorted = how many those are.
-struct ShardSpec { int rank = 0, world = 1; };
+struct ShardSpec { int rank = 0, world = 1; Comm *comm = nullptr; };   // comm == nullptr: key range `rank` of `world` on ONE GPU
 
 // ---- pivot rounds: refinement of LONG ties (repetitive dictionaries: variant phrases of a pangenome
 // share suffixes of hundreds of symbols, which rounds of <= 26 symbols close far too slowly) ----------
@@ -225,11 +225,39 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
                 while (b < nbins && cum < want) cum += h[b++];
                 return b;
             };
-            const u64 lo = bound(sh->rank) << hshift;
-            const u64 hi = sh->rank + 1 >= sh->world ? ~0ull : bound(sh->rank + 1) << hshift;
             timer.lap("K6 splitter histogram");
-            N = k_suffix_keys_select(dict, D, L, wl, pp.occ.get(), w, kx, lo, hi, key, sa, padded, ws);
-            timer.lap("K6 keys (selected)");
+            if (!sh->comm) {
+                // time-multiplexed form (one GPU sorting one key range after the other): select from all positions
+                const u64 lo = bound(sh->rank) << hshift;
+                const u64 hi = sh->rank + 1 >= sh->world ? ~0ull : bound(sh->rank + 1) << hshift;
+                N = k_suffix_keys_select(dict, D, L, wl, pp.occ.get(), w, kx, lo, hi, key, sa, padded, ws);
+                timer.lap("K6 keys (selected)");
+            } else {
+                // position-sliced: this rank computes the keys of ITS 1/world of the dictionary positions and routes every
+                // (key, position) pair to the owner of the key's range - one all-to-all over NVLink instead of every rank
+                // scanning all D positions.  Pairs arrive ordered by source rank = by dictionary position.
+                const int G = sh->world, g = sh->rank;
+                if (G > KEY_MAX_DEST) { err = "more ranks than the key router supports"; return PFB_ERR_LIMIT; }
+                std::vector<u64> bnd((size_t)G + 1);
+                for (int r = 0; r <= G; ++r) bnd[(size_t)r] = r >= G ? ~0ull : bound(r) << hshift;
+                const u64 ntiles = (D + KEYS_TILE - 1) / KEYS_TILE;
+                const u64 t0 = ntiles * (u64)g / (u64)G, t1 = ntiles * (u64)(g + 1) / (u64)G;
+                DevBuf<u64> skey;
+                DevBuf<u32> sidx;
+                std::vector<u64> cnts;
+                k_suffix_keys_route(dict, D, L, wl, pp.occ.get(), w, kx, bnd, t0, t1 - t0, skey, sidx, cnts, ws);
+                timer.lap("K6 keys (routed)");
+                std::vector<u64> mat = sh->comm->gather_u64(cnts.data(), G, st);          // mat[s * G + d] = pairs s -> d
+                N = 0;
+                for (int s = 0; s < G; ++s) N += mat[(size_t)s * G + g];
+                key.alloc(N); sa.alloc(padded(N));
+                std::vector<u64> m8(mat), m4(mat);
+                for (auto &x : m8) x *= 8;
+                for (auto &x : m4) x *= 4;
+                sh->comm->all_to_all_v(skey.get(), key.get(), m8.data(), st);
+                sh->comm->all_to_all_v(sidx.get(), sa.get(), m4.data(), st);
+                timer.lap("K6 key exchange (all-to-all)");
+            }
             key_b.alloc(N); val_b.alloc(padded(N));
             sort_pairs(key, key_b, sa, val_b, N, KEY_CODE_SHIFT, KEY_CODE_SHIFT + enum_bits(L), ws.sc, st, /*iota_vals=*/false);
         }
@@ -502,9 +530,23 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
     DevBuf<u32> cnt, ibase, slen;
     bool reclassify = false;
     ShardSpec spec;
-    if (comm) { spec.rank = comm->rank; spec.world = comm->world; }
+    if (comm) { spec.rank = comm->rank; spec.world = comm->world; spec.comm = comm; }
     u64 N = D;                          // sorted entries held by this rank (all D without a communicator)
-    int rc = sort_dict_suffixes(pp, (int)w, sa, meta, cnt, wl, &reclassify, ws, tm, timer, err, comm ? &spec : nullptr, &N);
+    int rc;
+    try {
+        rc = sort_dict_suffixes(pp, (int)w, sa, meta, cnt, wl, &reclassify, ws, tm, timer, err, comm ? &spec : nullptr, &N);
+    } catch (const Error &e) {
+        if (!comm) throw;
+        rc = e.code; err = e.what();
+    }
+    if (comm) {
+        // a failure on one rank (a tie its key range cannot close, out of memory) must not leave the others waiting in the
+        // next exchange: agree on it here
+        u64 f = rc ? 1 : 0;
+        std::vector<u64> all = comm->gather_u64(&f, 1, st);
+        for (int r = 0; r < comm->world && !rc; ++r)
+            if (all[(size_t)r]) { err = "rank " + std::to_string(r) + " failed in the dictionary suffix sort"; rc = PFB_ERR_ARG; }
+    }
     if (rc) return rc;
     tm.dict_sort = timer.stop();
 
@@ -545,91 +587,105 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
     tm.groups = timer.stop();
 
     // K8 emission ---------------------------------------------------------------------
-    out.n = n; out.off = slice_off; out.len = total;
-    out.bwt.alloc(total + 16);
-    if (any_sa) out.sa.alloc(total * (u64)U + 16);
-    DevBuf<u32> hard_t(nhg_cap + 1), ctr32(2);
-    DevBuf<u64> hard_x(nhg_cap + 1), ctr64(1);
-    dev_memset(ctr32.get(), 0, 8, st);
-    dev_memset(ctr64.get(), 0, 8, st);
-    EmitArgs ea;
-    ea.meta = meta.get(); ea.cnt = cnt.get(); ea.sa = sa.get(); ea.ibase = ibase.get(); ea.sl = slen.get();
-    ea.wl = wl; ea.tilebase = tilebase.get(); ea.D = N;
-    ea.ilist = pp.ilist.get(); ea.bwlast = pp.bwlast.get(); ea.bwsai = pp.bwsai.get();
-    ea.bwt = out.bwt.get(); ea.sa_out = out.sa.get();
-    ea.small_lim = HARD_SMALL; ea.mid_lim = HARD_MID;
-    if (const char *e = getenv("PFB_HARD_LIMITS")) {   // test knob "small,mid": push groups down the larger-group paths
-        unsigned a_ = HARD_SMALL, b_ = HARD_MID;
-        if (sscanf(e, "%u,%u", &a_, &b_) == 2) { ea.small_lim = a_ < HARD_SMALL ? a_ : HARD_SMALL; ea.mid_lim = b_ < HARD_MID ? b_ : HARD_MID; }
-    }
-    ea.hard_t = hard_t.get(); ea.hard_x = hard_x.get(); ea.n_hard_groups = ctr32.get(); ea.n_hard_occ = ctr64.get();
-#ifdef PFB_EMU
-    if (N) emu_emit<U>(ea, any_sa);
-#else
-    if (N) {
-        if (any_sa) {
-            static bool sa_attr_set = false;
-            if (!sa_attr_set) {
-                PFB_CUDA_CHECK(cudaFuncSetAttribute(k_emit_sa_kernel<U>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EmitSaSmem<U>::BYTES));
-                sa_attr_set = true;
-            }
-            k_emit_sa_kernel<U><<<(unsigned)nt, 256, EmitSaSmem<U>::BYTES, st>>>(ea);
-        } else k_emit_kernel<U, false><<<(unsigned)nt, 256, 0, st>>>(ea);
-        PFB_CUDA_CHECK(cudaGetLastError());
-        launch_stats().own++;
-    }
-#endif
-    timer.lap("K8 emit easy");
-    const u64 nhg = read_scalar(ctr32.get(), st);
-    const u64 nhard = read_scalar(ctr64.get(), st);
-    if (nhg != nhg_cap) { err = "internal: hard group count mismatch"; return PFB_ERR_INTERNAL; }
-    if (nhg) {
-        DevBuf<u32> biglist(nhg);
-        u32 *nbigp = ctr32.get() + 1;
-#ifdef PFB_EMU
-        emu_emit_hard<U>(ea, any_sa, (u32)nhg, biglist.get(), nbigp);
-#else
-        const unsigned blocks = (unsigned)((nhg + 31) / 32);
-        if (any_sa) k_emit_hard_kernel<U, true><<<blocks, 256, 0, st>>>(ea, (u32)nhg, biglist.get(), nbigp);
-        else k_emit_hard_kernel<U, false><<<blocks, 256, 0, st>>>(ea, (u32)nhg, biglist.get(), nbigp);
-        PFB_CUDA_CHECK(cudaGetLastError());
-        launch_stats().own++;
-#endif
-        timer.lap("K8 hard small groups");
-        const u64 nmid = read_scalar(nbigp, st);
-        if (nmid) {
-            DevBuf<u32> biglist2(nmid), nbig2(1);
-            dev_memset(nbig2.get(), 0, 4, st);
-#ifdef PFB_EMU
-            emu_emit_hard_mid<U>(ea, any_sa, biglist.get(), (u32)nmid, biglist2.get(), nbig2.get());
-#else
-            static bool attr_set = false;
-            if (!attr_set) {
-                PFB_CUDA_CHECK(cudaFuncSetAttribute(k_emit_hard_mid_kernel<U, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MID_SMEM));
-                PFB_CUDA_CHECK(cudaFuncSetAttribute(k_emit_hard_mid_kernel<U, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MID_SMEM));
-                attr_set = true;
-            }
-            const unsigned mblocks = (unsigned)((nmid + 7) / 8);
-            if (any_sa) k_emit_hard_mid_kernel<U, true><<<mblocks, 256, MID_SMEM, st>>>(ea, biglist.get(), (u32)nmid, biglist2.get(), nbig2.get());
-            else k_emit_hard_mid_kernel<U, false><<<mblocks, 256, MID_SMEM, st>>>(ea, biglist.get(), (u32)nmid, biglist2.get(), nbig2.get());
+    // (one pass through a do-while so that a failure on one rank - an exception included - is agreed on by all ranks before
+    // the next exchange instead of leaving them waiting in it)
+    rc = PFB_OK;
+    try { do {
+        out.n = n; out.off = slice_off; out.len = total;
+        out.bwt.alloc(total + 16);
+        if (any_sa) out.sa.alloc(total * (u64)U + 16);
+        DevBuf<u32> hard_t(nhg_cap + 1), ctr32(2);
+        DevBuf<u64> hard_x(nhg_cap + 1), ctr64(1);
+        dev_memset(ctr32.get(), 0, 8, st);
+        dev_memset(ctr64.get(), 0, 8, st);
+        EmitArgs ea;
+        ea.meta = meta.get(); ea.cnt = cnt.get(); ea.sa = sa.get(); ea.ibase = ibase.get(); ea.sl = slen.get();
+        ea.wl = wl; ea.tilebase = tilebase.get(); ea.D = N;
+        ea.ilist = pp.ilist.get(); ea.bwlast = pp.bwlast.get(); ea.bwsai = pp.bwsai.get();
+        ea.bwt = out.bwt.get(); ea.sa_out = out.sa.get();
+        ea.small_lim = HARD_SMALL; ea.mid_lim = HARD_MID;
+        if (const char *e = getenv("PFB_HARD_LIMITS")) {   // test knob "small,mid": push groups down the larger-group paths
+            unsigned a_ = HARD_SMALL, b_ = HARD_MID;
+            if (sscanf(e, "%u,%u", &a_, &b_) == 2) { ea.small_lim = a_ < HARD_SMALL ? a_ : HARD_SMALL; ea.mid_lim = b_ < HARD_MID ? b_ : HARD_MID; }
+        }
+        ea.hard_t = hard_t.get(); ea.hard_x = hard_x.get(); ea.n_hard_groups = ctr32.get(); ea.n_hard_occ = ctr64.get();
+    #ifdef PFB_EMU
+        if (N) emu_emit<U>(ea, any_sa);
+    #else
+        if (N) {
+            if (any_sa) {
+                static bool sa_attr_set = false;
+                if (!sa_attr_set) {
+                    PFB_CUDA_CHECK(cudaFuncSetAttribute(k_emit_sa_kernel<U>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EmitSaSmem<U>::BYTES));
+                    sa_attr_set = true;
+                }
+                k_emit_sa_kernel<U><<<(unsigned)nt, 256, EmitSaSmem<U>::BYTES, st>>>(ea);
+            } else k_emit_kernel<U, false><<<(unsigned)nt, 256, 0, st>>>(ea);
             PFB_CUDA_CHECK(cudaGetLastError());
             launch_stats().own++;
-#endif
-            timer.lap("K8 hard mid groups");
-            const u64 nbig = read_scalar(nbig2.get(), st);
-            if (nbig) {
-                rc = emit_big_groups<U>(ea, any_sa, biglist2.get(), nbig, P, ws, err);
-                if (rc) return rc;
-            }
         }
-        timer.lap("K8 hard big groups");
+    #endif
+        timer.lap("K8 emit easy");
+        const u64 nhg = read_scalar(ctr32.get(), st);
+        const u64 nhard = read_scalar(ctr64.get(), st);
+        if (nhg != nhg_cap) { err = "internal: hard group count mismatch"; rc = PFB_ERR_INTERNAL; break; }
+        if (nhg) {
+            DevBuf<u32> biglist(nhg);
+            u32 *nbigp = ctr32.get() + 1;
+    #ifdef PFB_EMU
+            emu_emit_hard<U>(ea, any_sa, (u32)nhg, biglist.get(), nbigp);
+    #else
+            const unsigned blocks = (unsigned)((nhg + 31) / 32);
+            if (any_sa) k_emit_hard_kernel<U, true><<<blocks, 256, 0, st>>>(ea, (u32)nhg, biglist.get(), nbigp);
+            else k_emit_hard_kernel<U, false><<<blocks, 256, 0, st>>>(ea, (u32)nhg, biglist.get(), nbigp);
+            PFB_CUDA_CHECK(cudaGetLastError());
+            launch_stats().own++;
+    #endif
+            timer.lap("K8 hard small groups");
+            const u64 nmid = read_scalar(nbigp, st);
+            if (nmid) {
+                DevBuf<u32> biglist2(nmid), nbig2(1);
+                dev_memset(nbig2.get(), 0, 4, st);
+    #ifdef PFB_EMU
+                emu_emit_hard_mid<U>(ea, any_sa, biglist.get(), (u32)nmid, biglist2.get(), nbig2.get());
+    #else
+                static bool attr_set = false;
+                if (!attr_set) {
+                    PFB_CUDA_CHECK(cudaFuncSetAttribute(k_emit_hard_mid_kernel<U, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MID_SMEM));
+                    PFB_CUDA_CHECK(cudaFuncSetAttribute(k_emit_hard_mid_kernel<U, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MID_SMEM));
+                    attr_set = true;
+                }
+                const unsigned mblocks = (unsigned)((nmid + 7) / 8);
+                if (any_sa) k_emit_hard_mid_kernel<U, true><<<mblocks, 256, MID_SMEM, st>>>(ea, biglist.get(), (u32)nmid, biglist2.get(), nbig2.get());
+                else k_emit_hard_mid_kernel<U, false><<<mblocks, 256, MID_SMEM, st>>>(ea, biglist.get(), (u32)nmid, biglist2.get(), nbig2.get());
+                PFB_CUDA_CHECK(cudaGetLastError());
+                launch_stats().own++;
+    #endif
+                timer.lap("K8 hard mid groups");
+                const u64 nbig = read_scalar(nbig2.get(), st);
+                if (nbig) {
+                    rc = emit_big_groups<U>(ea, any_sa, biglist2.get(), nbig, P, ws, err);
+                    if (rc) break;
+                }
+            }
+            timer.lap("K8 hard big groups");
+        }
+        out.hard = nhard;                 // "# hard cases" of include/pfbwt.hpp:188
+        out.easy = total - nhard;
+        u8 *sa_out0 = out.sa.get();
+        if (any_sa && slice_off == 0 && total) launch_for(1, st, PFB_LAMBDA(u64) { store_sa<U>(sa_out0, 0, n); });   // src/pfbwt-f.cpp:301
+        sa.release(); meta.release(); cnt.release(); ibase.release(); slen.release();
+    } while (0); }
+    catch (const Error &e) { if (!comm) throw; rc = e.code; err = e.what(); }
+    if (comm) {
+        u64 f = rc ? 1 : 0;
+        std::vector<u64> all = comm->gather_u64(&f, 1, st);
+        for (int r = 0; r < comm->world && !rc; ++r)
+            if (all[(size_t)r]) { err = "rank " + std::to_string(r) + " failed in the BWT assembly"; rc = PFB_ERR_ARG; }
     }
-    out.hard = nhard;                 // "# hard cases" of include/pfbwt.hpp:188
-    out.easy = total - nhard;
+    if (rc) return rc;
     u8 *bwt = out.bwt.get();
     u8 *sa_out = out.sa.get();
-    if (any_sa && slice_off == 0 && total) launch_for(1, st, PFB_LAMBDA(u64) { store_sa<U>(sa_out, 0, n); });   // src/pfbwt-f.cpp:301
-    sa.release(); meta.release(); cnt.release(); ibase.release(); slen.release();
     tm.emit = timer.stop();
 
     // K9 run boundaries + run-length SA samples (src/pfbwt-f.cpp:304-328) -------------------

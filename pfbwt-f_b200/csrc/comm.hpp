@@ -31,6 +31,11 @@ struct Comm {
     // device buffers; recv holds sum(counts) bytes, rank r's part at offset sum(counts[0..r))
     virtual void all_gather_v(const void *d_send, void *d_recv, const u64 *counts, pfbStream_t st) = 0;
 
+    // all-to-all-v of device buffers.  cnt[s * world + d] = bytes rank s sends to rank d (the whole matrix, known on every
+    // rank); d_send holds this rank's row back to back (part for rank 0 first), d_recv receives column `rank` back to back
+    // (part from rank 0 first).
+    virtual void all_to_all_v(const void *d_send, void *d_recv, const u64 *cnt, pfbStream_t st) = 0;
+
     void all_gather(const void *d_send, void *d_recv, u64 bytes, pfbStream_t st) {
         std::vector<u64> c((size_t)world, bytes);
         all_gather_v(d_send, d_recv, c.data(), st);
@@ -61,6 +66,29 @@ struct HostCallComm : Comm {
         stream_sync(st);
         bytes_moved += tot - counts[rank];
     }
+    // test transport: every rank's whole row travels through the host all-gather, the receiver picks its column
+    void all_to_all_v(const void *d_send, void *d_recv, const u64 *cnt, pfbStream_t st) override {
+        std::vector<u64> row((size_t)world, 0);
+        u64 tot = 0, mine = 0;
+        for (int s = 0; s < world; ++s) { for (int d = 0; d < world; ++d) row[(size_t)s] += cnt[(size_t)s * world + d]; tot += row[(size_t)s]; }
+        for (int s = 0; s < world; ++s) mine += cnt[(size_t)s * world + rank];
+        std::vector<uint8_t> hs(row[(size_t)rank] ? row[(size_t)rank] : 1), hr(tot ? tot : 1), out(mine ? mine : 1);
+        if (row[(size_t)rank]) d2h(hs.data(), d_send, row[(size_t)rank], st);
+        stream_sync(st);
+        if (fn(user, hs.data(), hr.data(), row.data(), world)) throw Error(-8, "host all-gather callback failed");
+        u64 base = 0, o = 0;
+        for (int s = 0; s < world; ++s) {
+            u64 off = base;
+            for (int d = 0; d < rank; ++d) off += cnt[(size_t)s * world + d];
+            const u64 c = cnt[(size_t)s * world + rank];
+            if (c) memcpy(out.data() + o, hr.data() + off, c);
+            o += c;
+            base += row[(size_t)s];
+        }
+        if (mine) h2d(d_recv, out.data(), mine, st);
+        stream_sync(st);
+        bytes_moved += mine - cnt[(size_t)rank * world + rank];
+    }
 };
 
 #ifndef PFB_EMU
@@ -73,6 +101,8 @@ struct NcclApi {
     int (*CommDestroy)(comm_t) = nullptr;
     int (*AllGather)(const void *, void *, size_t, int, comm_t, cudaStream_t) = nullptr;
     int (*Broadcast)(const void *, void *, size_t, int, int, comm_t, cudaStream_t) = nullptr;
+    int (*Send)(const void *, size_t, int, int, comm_t, cudaStream_t) = nullptr;
+    int (*Recv)(void *, size_t, int, int, comm_t, cudaStream_t) = nullptr;
     int (*GroupStart)() = nullptr;
     int (*GroupEnd)() = nullptr;
     const char *(*GetErrorString)(int) = nullptr;
@@ -85,7 +115,7 @@ struct NcclApi {
         if (!h) { err = std::string("cannot load NCCL: ") + dlerror(); return false; }
 #define PFB_NCCL_SYM(f) *(void **)(&f) = dlsym(h, "nccl" #f); if (!f) { err = "NCCL symbol nccl" #f " missing"; return false; }
         PFB_NCCL_SYM(GetUniqueId) PFB_NCCL_SYM(CommInitRank) PFB_NCCL_SYM(CommDestroy) PFB_NCCL_SYM(AllGather)
-        PFB_NCCL_SYM(Broadcast) PFB_NCCL_SYM(GroupStart) PFB_NCCL_SYM(GroupEnd) PFB_NCCL_SYM(GetErrorString)
+        PFB_NCCL_SYM(Broadcast) PFB_NCCL_SYM(Send) PFB_NCCL_SYM(Recv) PFB_NCCL_SYM(GroupStart) PFB_NCCL_SYM(GroupEnd) PFB_NCCL_SYM(GetErrorString)
 #undef PFB_NCCL_SYM
         return true;
     }
@@ -131,13 +161,39 @@ struct NcclComm : Comm {
             // all-gather-v = one broadcast per root inside a group (fused by NCCL into one launch)
             check(a.GroupStart(), "GroupStart");
             u64 off = 0;
-            for (int r = 0; r < world; ++r) {
-                if (counts[r]) check(a.Broadcast(d_send, (char *)d_recv + off, counts[r], 0, r, comm, st), "Broadcast");
+            int rcb = 0;
+            for (int r = 0; r < world && !rcb; ++r) {
+                if (counts[r]) rcb = a.Broadcast(d_send, (char *)d_recv + off, counts[r], 0, r, comm, st);
                 off += counts[r];
             }
-            check(a.GroupEnd(), "GroupEnd");
+            const int rce = a.GroupEnd();        // the group is closed on the error path too
+            check(rcb, "Broadcast");
+            check(rce, "GroupEnd");
         }
         bytes_moved += tot - counts[rank];
+    }
+    // grouped point-to-point sends / receives over NVLink (one fused launch); the part a rank keeps is a device copy
+    void all_to_all_v(const void *d_send, void *d_recv, const u64 *cnt, pfbStream_t st) override {
+        NcclApi &a = nccl_api();
+        std::vector<u64> soff((size_t)world + 1, 0), roff((size_t)world + 1, 0);
+        for (int r = 0; r < world; ++r) {
+            soff[(size_t)r + 1] = soff[(size_t)r] + cnt[(size_t)rank * world + r];
+            roff[(size_t)r + 1] = roff[(size_t)r] + cnt[(size_t)r * world + rank];
+        }
+        const u64 self = cnt[(size_t)rank * world + rank];
+        if (self) PFB_CUDA_CHECK(cudaMemcpyAsync((char *)d_recv + roff[(size_t)rank], (const char *)d_send + soff[(size_t)rank], self, cudaMemcpyDeviceToDevice, st));
+        const u64 CH = 1ull << 30;               // a send / receive pair moves at most 1 GiB per call
+        int rc = a.GroupStart(), rc2 = 0;
+        for (int r = 0; r < world && !rc; ++r) {
+            if (r == rank) continue;
+            const u64 sc = cnt[(size_t)rank * world + r], rcv = cnt[(size_t)r * world + rank];
+            for (u64 o = 0; o < sc && !rc; o += CH) rc = a.Send((const char *)d_send + soff[(size_t)r] + o, (size_t)(sc - o < CH ? sc - o : CH), /*ncclChar*/ 0, r, comm, st);
+            for (u64 o = 0; o < rcv && !rc; o += CH) rc = a.Recv((char *)d_recv + roff[(size_t)r] + o, (size_t)(rcv - o < CH ? rcv - o : CH), /*ncclChar*/ 0, r, comm, st);
+        }
+        rc2 = a.GroupEnd();                      // always closed, also on the error path
+        check(rc, "Send/Recv");
+        check(rc2, "GroupEnd");
+        bytes_moved += roff[(size_t)world] - self;
     }
 };
 #endif

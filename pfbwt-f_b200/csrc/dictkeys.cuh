@@ -130,29 +130,41 @@ PFB_HD inline u64 prev_code(const u8 *dict, u64 idx) {
 // is emitted as EndOfWord (0x01), exactly like dict[gsa[j]-1] in include/pfbwt.hpp:140
 PFB_HD inline u8 prev_byte(u64 key) { return (key & 8) ? ENDOFWORD : sym3_byte((u32)key & 7); }
 
-#ifndef PFB_EMU
+static const int KEYS_TILE = 2048;
 // K6a: one CTA = 2048 consecutive dictionary positions, 8 per thread.  The tile (+40 bytes of
 // look-ahead) is staged in shared memory with 16-byte loads; each thread packs its 40 symbols
 // once into 2-bit fields + a stopper mask and derives its 8 windows with shifts; keys leave
 // through shared memory so that global stores are unit-stride.
-static const int KEYS_TILE = 2048;
 // MODE 0: keys of all positions -> key[].  The other modes serve the range-restricted sort of the
 // multi-GPU path (a rank sorts only the valid suffixes whose code lies in [lo, hi)):
 // MODE 1: weighted histogram of the top `hshift`-shifted code bits over sampled tiles (splitter choice)
 // MODE 2: number of selected suffixes per tile -> tilecnt[]
 // MODE 3: selected (key, position) pairs, in dictionary order, at tilebase[tile] + rank inside the tile
+// MODE 4 / 5: the position-sliced form of the multi-GPU path - a rank scans only ITS slice of the dictionary positions
+//   (tiles [tile0, tile0 + ntl)) and routes every valid suffix to the rank that owns its code range (bound[d] <= code <
+//   bound[d+1]); 4 counts per (destination, tile), 5 writes the pairs grouped by destination, dictionary order inside
+static const int KEY_MAX_DEST = 64;
 struct KeySelect {
     u64 lo = 0, hi = ~0ull;       // code range
     u64 *hist = nullptr; int hshift = 0; u32 tile_stride = 1;
     u32 *tilecnt = nullptr; const u64 *tilebase = nullptr;
     u64 *key_out = nullptr; u32 *idx_out = nullptr;
+    u64 tile0 = 0, ntl = 0;       // modes 4 / 5: first tile and number of tiles of this rank's position slice
+    int nd = 0;                   // destinations
+    u64 bound[KEY_MAX_DEST + 1];  // bound[0] = 0 <= ... <= bound[nd] = ~0
 };
+PFB_HD inline int key_dest(const u64 *bound, int nd, u64 code) {      // largest d with bound[d] <= code
+    int lo = 0, hi = nd;
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (bound[mid] <= code) lo = mid; else hi = mid; }
+    return lo;
+}
+#ifndef PFB_EMU
 template <int MODE>
 __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict__ dict, u64 D, int L, u64 *__restrict__ key,
                                                             WordLookup wl, const u32 *__restrict__ occ, int w, KeyExtra kx, KeySelect ks) {
     __shared__ __align__(16) u8 sb[KEYS_TILE + 48];
     __shared__ u64 sk[KEYS_TILE + KEYS_TILE / 8];      // one pad slot per 8 keys: a thread's 8 consecutive keys spread over banks
-    const u64 tile = MODE == 1 ? (u64)blockIdx.x * ks.tile_stride : (u64)blockIdx.x;
+    const u64 tile = MODE == 1 ? (u64)blockIdx.x * ks.tile_stride : MODE >= 4 ? ks.tile0 + (u64)blockIdx.x : (u64)blockIdx.x;
     const u64 base = tile * KEYS_TILE;
     for (int o = threadIdx.x * 16; o < KEYS_TILE + 48; o += 256 * 16) {
         u64 g = base + (u64)o;
@@ -190,7 +202,8 @@ __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict
     // the EndOfWord bytes passed
     u32 d = (base + (u64)i0 < D) ? wl.word((u32)(base + (u64)i0)) : wl.Dw;
     u32 selmask = 0;
-    u64 mykeys[MODE == 3 ? 8 : 1];
+    u64 dstv = ~0ull;                       // modes 4 / 5: destination of each of the 8 positions, one byte each (0xff = none)
+    u64 mykeys[(MODE == 3 || MODE == 5) ? 8 : 1];
 #pragma unroll
     for (int p = 0; p < 8; ++p) {
         u64 W = p ? ((xh << (2 * p)) | (xl >> (64 - 2 * p))) : xh;
@@ -211,6 +224,10 @@ __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict
         else {
             const bool sel = valid && d < wl.Dw && i < D && code >= ks.lo && code < ks.hi;
             if (MODE == 1) { if (valid && d < wl.Dw && i < D) atomic_add(&ks.hist[code >> ks.hshift], 4ull + c); }
+            else if (MODE >= 4) {
+                if (valid && d < wl.Dw && i < D) dstv = (dstv & ~(0xffull << (8 * p))) | ((u64)key_dest(ks.bound, ks.nd, code) << (8 * p));
+                if (MODE == 5) mykeys[MODE == 5 ? p : 0] = kk;
+            }
             else { selmask |= sel ? 1u << p : 0u; if (MODE == 3) mykeys[MODE == 3 ? p : 0] = kk; }
         }
         d += (u32)((tmk >> (63 - p)) & 1);
@@ -222,6 +239,48 @@ __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict
             int o = k * 256 + threadIdx.x;
             u64 g = base + (u64)o;
             if (g < D) key[g] = sk[o + (o >> 3)];
+        }
+    } else if (MODE >= 4) {
+        // per destination: exclusive scan of the per-thread counts over the CTA -> rank of every routed position inside
+        // the (tile, destination) run, in dictionary order
+        __shared__ u32 rsum[8][KEY_MAX_DEST];
+        const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+        u32 offp[8];
+#pragma unroll
+        for (int p = 0; p < 8; ++p) offp[p] = 0;
+        for (int dd = 0; dd < ks.nd; ++dd) {
+            const u64 x = dstv ^ ((u64)dd * 0x0101010101010101ull);                          // zero byte <=> destination dd
+            const u64 z = ~((((x & 0x7f7f7f7f7f7f7f7full) + 0x7f7f7f7f7f7f7f7full) | x) | 0x7f7f7f7f7f7f7f7full);
+            const u32 c = (u32)__popcll((unsigned long long)z);
+            u32 inc = c;
+#pragma unroll
+            for (int q = 1; q < 32; q <<= 1) { u32 o = __shfl_up_sync(0xffffffffu, inc, q); if (lane >= q) inc += o; }
+            if (lane == 31) rsum[wid][dd] = inc;
+            if (MODE == 5 && c) {
+                u32 e = inc - c;
+#pragma unroll
+                for (int p = 0; p < 8; ++p) if ((z >> (8 * p + 7)) & 1) offp[p] = e++;
+            }
+        }
+        __syncthreads();
+        if (MODE == 4) {
+            if ((int)threadIdx.x < ks.nd) {
+                u32 t = 0;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) t += rsum[k][threadIdx.x];
+                ks.tilecnt[(u64)threadIdx.x * ks.ntl + blockIdx.x] = t;
+            }
+        } else {
+#pragma unroll
+            for (int p = 0; p < 8; ++p) {
+                const u32 dd = (u32)(dstv >> (8 * p)) & 0xffu;
+                if (dd == 0xffu) continue;
+                u32 wb = 0;
+                for (int k = 0; k < wid; ++k) wb += rsum[k][dd];
+                const u64 o = ks.tilebase[(u64)dd * ks.ntl + blockIdx.x] + wb + offp[p];
+                ks.key_out[o] = mykeys[MODE == 5 ? p : 0];
+                ks.idx_out[o] = (u32)(base + (u64)(i0 + p));
+            }
         }
     } else if (MODE >= 2) {
         // ordered compaction inside the tile: exclusive scan of the per-thread selected counts
@@ -338,6 +397,70 @@ inline u64 k_suffix_keys_select(const u8 *dict, u64 D, int L, const WordLookup &
     }
     launch_stats().own += 2;
     return m;
+#endif
+}
+
+// ---- position-sliced routing (multi-GPU path): this rank scans the tiles [tile0, tile0 + ntl) of the dictionary and
+// groups the (key, position) pairs of the valid suffixes by the rank that owns their code range.  key_out / idx_out
+// (allocated here) hold destination 0's pairs first, each part in dictionary order; counts[d] = pairs for rank d.
+template <class WS>
+inline void k_suffix_keys_route(const u8 *dict, u64 D, int L, const WordLookup &wl, const u32 *occ, int w, const KeyExtra &kx,
+                                const std::vector<u64> &bound, u64 tile0, u64 ntl, DevBuf<u64> &key_out, DevBuf<u32> &idx_out,
+                                std::vector<u64> &counts, WS &ws) {
+    pfbStream_t st = ws.st;
+    const int nd = (int)bound.size() - 1;
+    counts.assign((size_t)nd, 0);
+#ifdef PFB_EMU
+    (void)st;
+    std::vector<std::vector<u64>> ks_((size_t)nd);
+    std::vector<std::vector<u32>> is_((size_t)nd);
+    const u64 p0 = tile0 * KEYS_TILE, p1 = (tile0 + ntl) * KEYS_TILE < D ? (tile0 + ntl) * KEYS_TILE : D;
+    for (u64 i = p0; i < p1; ++i) {
+        u32 d;
+        if (!key_is_valid(wl, (u32)i, w, d)) continue;
+        EnumKey e = enum_scan(dict, D, i, L);
+        const int dst = key_dest(bound.data(), nd, e.code);
+        bool full = (u32)i == wl.start(d);
+        ks_[(size_t)dst].push_back(pack_key(e.code, e.consumed, e.closed, (u32)prev_code(dict, i)) | kx.pack(occ[d], full));
+        is_[(size_t)dst].push_back((u32)i);
+    }
+    u64 m = 0;
+    for (int d = 0; d < nd; ++d) { counts[(size_t)d] = ks_[(size_t)d].size(); m += counts[(size_t)d]; }
+    key_out.alloc(m); idx_out.alloc(m);
+    u64 o = 0;
+    for (int d = 0; d < nd; ++d) {
+        if (counts[(size_t)d]) { memcpy(key_out.get() + o, ks_[(size_t)d].data(), counts[(size_t)d] * 8); memcpy(idx_out.get() + o, is_[(size_t)d].data(), counts[(size_t)d] * 4); }
+        o += counts[(size_t)d];
+    }
+#else
+    if (ntl == 0) { key_out.alloc(0); idx_out.alloc(0); return; }
+    const u64 cells = (u64)nd * ntl;
+    DevBuf<u32> tcnt(cells + 1);
+    DevBuf<u64> tbase(cells + 1), ends((size_t)nd + 1);
+    KeySelect ks;
+    ks.tile0 = tile0; ks.ntl = ntl; ks.nd = nd;
+    for (int d = 0; d <= nd; ++d) ks.bound[d] = bound[(size_t)d];
+    ks.tilecnt = tcnt.get();
+    k_suffix_keys_kernel<4><<<(unsigned)ntl, 256, 0, st>>>(dict, D, L, nullptr, wl, occ, w, kx, ks);
+    PFB_CUDA_CHECK(cudaGetLastError());
+    dev_memset(tcnt.get() + cells, 0, 4, st);
+    exclusive_sum<u32, u64>(tcnt.get(), tbase.get(), cells + 1, ws.sc, st);
+    {
+        const u64 *tb = tbase.get(); u64 *ep = ends.get(); const u64 ntl_ = ntl;
+        launch_for((u64)nd + 1, st, PFB_LAMBDA(u64 d) { ep[d] = tb[d * ntl_]; });
+    }
+    std::vector<u64> he((size_t)nd + 1);
+    d2h(he.data(), ends.get(), ((size_t)nd + 1) * 8, st);
+    stream_sync(st);
+    for (int d = 0; d < nd; ++d) counts[(size_t)d] = he[(size_t)d + 1] - he[(size_t)d];
+    const u64 m = he[(size_t)nd];
+    key_out.alloc(m); idx_out.alloc(m);
+    if (m) {
+        ks.tilebase = tbase.get(); ks.key_out = key_out.get(); ks.idx_out = idx_out.get();
+        k_suffix_keys_kernel<5><<<(unsigned)ntl, 256, 0, st>>>(dict, D, L, nullptr, wl, occ, w, kx, ks);
+        PFB_CUDA_CHECK(cudaGetLastError());
+    }
+    launch_stats().own += 2;
 #endif
 }
 
