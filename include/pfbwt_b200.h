@@ -74,6 +74,8 @@ typedef struct {
     uint64_t shard_bytes_moved;
     /* FASTA files whose records were split on the device (pfb_add_fasta on plain files) and the device time of that */
     float ingest_ms; uint64_t ingest_files;
+    /* last pfb_build_bwt_to_files: key-range buckets the build was cut into, peak device bytes while it ran */
+    uint64_t stream_buckets, stream_peak_bytes;
 } pfb_stats;
 
 /* which part of the job's outputs this context holds.  Without a communicator: everything. */
@@ -131,6 +133,16 @@ int pfb_load_parse(pfb_ctx *, const char *prefix, int with_parse_bwt, int with_s
 /* PrefixFreeBWT::generate_bwt_lcp driven by run_pfbwt, include/pfbwt.hpp:96-194,
  * src/pfbwt-f.cpp:272-349.  sa / rssa = -s / -r. */
 int pfb_build_bwt(pfb_ctx *, int sa, int rssa);
+/* The -m mode (workspace larger than memory: include/file_wrappers.hpp:35-124 mmap sinks, include/pfbwt.hpp:208-209,
+ * selected at src/pfbwt-f.cpp:359-365).  Build and write in one call: when the work arrays of a full build would not fit in
+ * hbm_limit_bytes (0 = what the device has free; the environment variable PFB_HBM_LIMIT=48G overrides), the dictionary
+ * suffixes are sorted and emitted one key range after the other and every finished slice of <prefix>.bwt/.sa/.ssa/.esa is
+ * streamed to its offset of the file.  Afterwards pfb_get_sizes reports n, r, easy, hard; the arrays are not kept. */
+int pfb_build_bwt_to_files(pfb_ctx *, const char *prefix, int sa, int rssa, uint64_t hbm_limit_bytes);
+/* device bytes a full in-memory pfb_build_bwt needs at its peak (estimate), incl. what the context already holds */
+uint64_t pfb_build_workspace_bytes(const pfb_ctx *, int sa, int rssa);
+/* device bytes available to this context right now (free on the device + held idle by the library's allocator) */
+int pfb_device_free_bytes(const pfb_ctx *, size_t *out);
 /* the .bwt/.sa/.ssa/.esa writer of src/pfbwt-f.cpp:298-328; stdout_ext = "bwt" | "sa" | NULL (--stdout) */
 int pfb_write_bwt(pfb_ctx *, const char *prefix, int sa, int rssa, const char *stdout_ext);
 

@@ -17,7 +17,7 @@ EXPORTS = [
     "pfb_copy_bwt", "pfb_copy_sa", "pfb_copy_ssa", "pfb_copy_esa", "pfb_get_docs", "pfb_upload_text",
     "pfb_run_resident", "pfb_release_text", "pfb_clear",
     "pfb_nccl_unique_id", "pfb_shard_init_nccl", "pfb_shard_init_host", "pfb_get_shard_info", "pfb_get_pending_bases",
-    "pfb_kat_trigger", "pfb_add_chunk", "pfb_add_fasta_range", "pfb_save_last_sai",
+    "pfb_kat_trigger", "pfb_add_chunk", "pfb_add_fasta_range", "pfb_save_last_sai", "pfb_build_bwt_to_files", "pfb_build_workspace_bytes",
 ]
 
 
@@ -40,7 +40,8 @@ class Stats(C.Structure):
                [("launches_own", C.c_uint64), ("launches_lib", C.c_uint64), ("dev_bytes_peak", C.c_uint64),
                 ("radix_pass_ms", C.c_double), ("radix_passes", C.c_uint64), ("radix_pairs", C.c_uint64), ("run_ms", C.c_float),
                 ("shard_exchange_ms", C.c_float), ("shard_merge_ms", C.c_float), ("shard_bytes_moved", C.c_uint64),
-                ("ingest_ms", C.c_float), ("ingest_files", C.c_uint64)]
+                ("ingest_ms", C.c_float), ("ingest_files", C.c_uint64),
+                ("stream_buckets", C.c_uint64), ("stream_peak_bytes", C.c_uint64)]
 
 
 class ShardInfo(C.Structure):
@@ -84,6 +85,9 @@ def load():
     lib.pfb_save_last_sai.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
     lib.pfb_build_bwt.argtypes = [vp, C.c_int, C.c_int]
     lib.pfb_run_resident.argtypes = [vp, C.c_int, C.c_int]
+    lib.pfb_build_bwt_to_files.argtypes = [vp, C.c_char_p, C.c_int, C.c_int, C.c_uint64]
+    lib.pfb_build_workspace_bytes.restype = C.c_uint64
+    lib.pfb_build_workspace_bytes.argtypes = [vp, C.c_int, C.c_int]
     lib.pfb_write_bwt.argtypes = [vp, C.c_char_p, C.c_int, C.c_int, C.c_char_p]
     lib.pfb_get_sizes.argtypes = [vp, C.POINTER(Sizes)]
     lib.pfb_get_stats.argtypes = [vp, C.POINTER(Stats)]
@@ -206,6 +210,13 @@ class Context:
     # BWT build
     def generate_bwt(self, sa=False, rssa=False):
         self._ck(self.lib.pfb_build_bwt(self.h, int(sa), int(rssa)))
+
+    def generate_bwt_to_files(self, prefix, sa=False, rssa=False, hbm_limit=0):
+        """-m mode: build key range by key range, streaming every slice to <prefix>.bwt/.sa/.ssa/.esa"""
+        self._ck(self.lib.pfb_build_bwt_to_files(self.h, prefix.encode(), int(sa), int(rssa), int(hbm_limit)))
+
+    def build_workspace_bytes(self, sa=False, rssa=False):
+        return int(self.lib.pfb_build_workspace_bytes(self.h, int(sa), int(rssa)))
 
     def write_bwt(self, prefix, sa=False, rssa=False):
         self._ck(self.lib.pfb_write_bwt(self.h, prefix.encode(), int(sa), int(rssa), None))

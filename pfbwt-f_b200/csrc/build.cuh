@@ -242,21 +242,49 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
                 for (int r = 0; r <= G; ++r) bnd[(size_t)r] = r >= G ? ~0ull : bound(r) << hshift;
                 const u64 ntiles = (D + KEYS_TILE - 1) / KEYS_TILE;
                 const u64 t0 = ntiles * (u64)g / (u64)G, t1 = ntiles * (u64)(g + 1) / (u64)G;
-                DevBuf<u64> skey;
-                DevBuf<u32> sidx;
-                std::vector<u64> cnts;
-                k_suffix_keys_route(dict, D, L, wl, pp.occ.get(), w, kx, bnd, t0, t1 - t0, skey, sidx, cnts, ws);
-                timer.lap("K6 keys (routed)");
-                std::vector<u64> mat = sh->comm->gather_u64(cnts.data(), G, st);          // mat[s * G + d] = pairs s -> d
+                KeyRouter kr;
+                kr.dict = dict; kr.D = D; kr.L = L; kr.wl = wl; kr.occ = pp.occ.get(); kr.w = w; kr.kx = kx;
+                kr.bound = bnd; kr.tile0 = t0; kr.ntl = t1 - t0;
+                kr.count(ws);
+                timer.lap("K6 keys (count per owner)");
+                std::vector<u64> mat = sh->comm->gather_u64(kr.counts.data(), G, st);     // mat[s * G + d] = pairs s -> d
                 N = 0;
                 for (int s = 0; s < G; ++s) N += mat[(size_t)s * G + g];
                 key.alloc(N); sa.alloc(padded(N));
-                std::vector<u64> m8(mat), m4(mat);
-                for (auto &x : m8) x *= 8;
-                for (auto &x : m4) x *= 4;
-                sh->comm->all_to_all_v(skey.get(), key.get(), m8.data(), st);
-                sh->comm->all_to_all_v(sidx.get(), sa.get(), m4.data(), st);
-                timer.lap("K6 key exchange (all-to-all)");
+                std::vector<u64 *> kouts((size_t)G);
+                std::vector<u32 *> iouts((size_t)G);
+                void *mine[2] = {key.get(), sa.get()};
+                std::vector<void *> peers;
+                if (sh->comm->peer_pointers(mine, 2, peers, st)) {
+                    // FUSED: the key kernel stores every pair straight into its owner's receive buffer over NVLink (peer
+                    // memory): the all-to-all is the kernel's own unit-stride stores, overlapped with the key arithmetic
+                    for (int d = 0; d < G; ++d) {
+                        u64 before = 0;                                   // pairs the ranks before this one send to d
+                        for (int s = 0; s < g; ++s) before += mat[(size_t)s * G + d];
+                        kouts[(size_t)d] = (u64 *)peers[(size_t)d * 2] + before;
+                        iouts[(size_t)d] = (u32 *)peers[(size_t)d * 2 + 1] + before;
+                    }
+                    kr.scatter(kouts.data(), iouts.data(), ws);
+                    stream_sync(st);
+                    sh->comm->barrier(st);                                // every rank's stores into this rank's buffers have landed
+                    u64 got = 0;
+                    for (int s = 0; s < G; ++s) if (s != g) got += mat[(size_t)s * G + g];
+                    sh->comm->bytes_moved += got * 12;
+                    timer.lap("K6 keys -> owners (peer stores over NVLink)");
+                } else {
+                    const u64 m = kr.destbase[(size_t)G];
+                    DevBuf<u64> skey(m);
+                    DevBuf<u32> sidx(m);
+                    for (int d = 0; d < G; ++d) { kouts[(size_t)d] = skey.get() + kr.destbase[(size_t)d]; iouts[(size_t)d] = sidx.get() + kr.destbase[(size_t)d]; }
+                    kr.scatter(kouts.data(), iouts.data(), ws);
+                    timer.lap("K6 keys (grouped by owner)");
+                    std::vector<u64> m8(mat), m4(mat);
+                    for (auto &x : m8) x *= 8;
+                    for (auto &x : m4) x *= 4;
+                    sh->comm->all_to_all_v(skey.get(), key.get(), m8.data(), st);
+                    sh->comm->all_to_all_v(sidx.get(), sa.get(), m4.data(), st);
+                    timer.lap("K6 key exchange (all-to-all)");
+                }
             }
             key_b.alloc(N); val_b.alloc(padded(N));
             sort_pairs(key, key_b, sa, val_b, N, KEY_CODE_SHIFT, KEY_CODE_SHIFT + enum_bits(L), ws.sc, st, /*iota_vals=*/false);
@@ -492,9 +520,18 @@ PFB_HD inline void store_sa(u8 *sa_out, u64 x, u64 v) {
 // ===========================================================================
 // build_bwt (include/pfbwt.hpp:96-223, src/pfbwt-f.cpp:298-328)
 // ===========================================================================
+// bucket / carry: ONE GPU builds the BWT one key range after the other (rank `bucket->rank` of `bucket->world` ranges, no
+// communicator) so that the per-suffix work arrays are 1/world of the full ones: the -m mode.  *carry
+// hands what a later bucket needs from the earlier ones.
+struct BucketCarry {
+    u64 off = 0;                               // BWT positions emitted so far
+    u64 r = 0, ssa = 0, esa = 0;               // runs, .ssa pairs, .esa pairs so far
+    u64 easy = 0, hard = 0;
+    bool have_last = false; u8 last_byte = 0; u64 last_sa = 0;     // the last position emitted: the next bucket decides whether it ends a run
+};
 template <int U>
 inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, bool want_rssa, DeviceBwt &out, Workspace &ws,
-                       StageTimes &tm, std::string &err, Comm *comm) {
+                       StageTimes &tm, std::string &err, Comm *comm, const ShardSpec *bucket = nullptr, BucketCarry *carry = nullptr) {
     pfbStream_t st = ws.st;
     const u64 D = pp.dsize, Dw = pp.Dw, n = pp.n, P = pp.P;
     const u64 w = (u64)prm.w;
@@ -531,10 +568,13 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
     bool reclassify = false;
     ShardSpec spec;
     if (comm) { spec.rank = comm->rank; spec.world = comm->world; spec.comm = comm; }
+    else if (bucket && carry) { spec = *bucket; spec.comm = nullptr; }
+    else carry = nullptr;
+    const bool ranged = comm || carry;
     u64 N = D;                          // sorted entries held by this rank (all D without a communicator)
     int rc;
     try {
-        rc = sort_dict_suffixes(pp, (int)w, sa, meta, cnt, wl, &reclassify, ws, tm, timer, err, comm ? &spec : nullptr, &N);
+        rc = sort_dict_suffixes(pp, (int)w, sa, meta, cnt, wl, &reclassify, ws, tm, timer, err, ranged ? &spec : nullptr, &N);
     } catch (const Error &e) {
         if (!comm) throw;
         rc = e.code; err = e.what();
@@ -577,8 +617,9 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
         totals = comm->gather_u64(&total, 1, st);
         for (int r = 0; r < comm->rank; ++r) slice_off += totals[(size_t)r];
     }
-    {
-        u64 sum = 0;
+    if (carry) slice_off = carry->off;
+    if (!carry || spec.rank + 1 == spec.world) {
+        u64 sum = carry ? carry->off : 0;
         for (u64 t_ : totals) sum += t_;
         if (sum != n + 1) { err = "internal: emitted positions " + std::to_string(sum) + " != n+1 = " + std::to_string(n + 1); return PFB_ERR_INTERNAL; }
     }
@@ -689,21 +730,31 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
     tm.emit = timer.stop();
 
     // K9 run boundaries + run-length SA samples (src/pfbwt-f.cpp:304-328) -------------------
-    if (comm) {
-        // Slices meet at rank boundaries: a run start needs the byte before the slice, a run end the
-        // byte after it.  One small all-gather of (first byte, last byte) per rank supplies both.
-        u64 edge[2] = {0, 0};
-        if (total) { edge[0] = read_scalar(bwt, st); edge[1] = read_scalar(bwt + (total - 1), st); }
-        std::vector<u64> edges = comm->gather_u64(edge, 2, st);
+    if (comm || carry) {
+        // Slices meet at rank (or bucket) boundaries: a run start needs the byte before the slice, a run end the
+        // byte after it.  Ranks: one small all-gather of (first byte, last byte) per rank supplies both.  Buckets come
+        // one after the other: the byte before is carried over, and whether a bucket's last position ends a run is decided
+        // by the next bucket, which then writes that .esa pair first (`pend`).
         u8 prevb = 0, nextb = 0;
-        bool has_next = false;
-        for (int r = comm->rank - 1; r >= 0; --r) if (totals[(size_t)r]) { prevb = (u8)edges[2 * (size_t)r + 1]; break; }
-        for (int r = comm->rank + 1; r < comm->world; ++r) if (totals[(size_t)r]) { nextb = (u8)edges[2 * (size_t)r]; has_next = true; break; }
+        bool has_next = false, defer_last = false;
+        u64 pend = 0, pend_pos = 0, pend_sa = 0;
+        if (comm) {
+            u64 edge[2] = {0, 0};
+            if (total) { edge[0] = read_scalar(bwt, st); edge[1] = read_scalar(bwt + (total - 1), st); }
+            std::vector<u64> edges = comm->gather_u64(edge, 2, st);
+            for (int r = comm->rank - 1; r >= 0; --r) if (totals[(size_t)r]) { prevb = (u8)edges[2 * (size_t)r + 1]; break; }
+            for (int r = comm->rank + 1; r < comm->world; ++r) if (totals[(size_t)r]) { nextb = (u8)edges[2 * (size_t)r]; has_next = true; break; }
+        } else {
+            prevb = carry->have_last ? carry->last_byte : (u8)0;
+            defer_last = spec.rank + 1 < spec.world;
+            const u8 first = total ? read_scalar(bwt, st) : (u8)0;
+            if (carry->have_last && ((total && first != carry->last_byte) || (!total && !defer_last))) { pend = 1; pend_pos = carry->off - 1; pend_sa = carry->last_sa; }
+        }
         DevBuf<u8> rf(total + 1), ef(total + 1);
         u8 *rp = rf.get(); u8 *ep = ef.get();
         launch_for(total, st, PFB_LAMBDA(u64 x) {
             rp[x] = bwt[x] != (x ? bwt[x - 1] : prevb) ? 1 : 0;
-            ep[x] = (x + 1 < total) ? (bwt[x + 1] != bwt[x] ? 1 : 0) : ((!has_next || nextb != bwt[x]) ? 1 : 0);
+            ep[x] = (x + 1 < total) ? (bwt[x + 1] != bwt[x] ? 1 : 0) : (defer_last ? 0 : ((!has_next || nextb != bwt[x]) ? 1 : 0));
         });
         DevBuf<u64> ridx, eidx;
         u64 cnts[2] = {0, 0};
@@ -716,23 +767,38 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
             cnts[0] = read_scalar(ridx.get() + (total - 1), st) + read_scalar(rf.get() + (total - 1), st);
             cnts[1] = read_scalar(eidx.get() + (total - 1), st) + read_scalar(ef.get() + (total - 1), st);
         }
-        std::vector<u64> all = comm->gather_u64(cnts, 2, st);
         u64 r = 0, so = 0, eo = 0;
-        for (int q = 0; q < comm->world; ++q) {
-            r += all[2 * (size_t)q];
-            if (q < comm->rank) { so += all[2 * (size_t)q]; eo += all[2 * (size_t)q + 1]; }
-        }
+        if (comm) {
+            std::vector<u64> all = comm->gather_u64(cnts, 2, st);
+            for (int q = 0; q < comm->world; ++q) {
+                r += all[2 * (size_t)q];
+                if (q < comm->rank) { so += all[2 * (size_t)q]; eo += all[2 * (size_t)q + 1]; }
+            }
+        } else { r = carry->r + cnts[0]; so = carry->ssa; eo = carry->esa; }
         out.r = r;
         if (want_rssa) {
-            out.ssa_off = so; out.ssa_cnt = cnts[0]; out.esa_off = eo; out.esa_cnt = cnts[1];
+            out.ssa_off = so; out.ssa_cnt = cnts[0]; out.esa_off = eo; out.esa_cnt = pend + cnts[1];
             out.ssa.alloc(2 * cnts[0] * (u64)U + 16);
-            out.esa.alloc(2 * cnts[1] * (u64)U + 16);
+            out.esa.alloc(2 * (pend + cnts[1]) * (u64)U + 16);
             u8 *ssa = out.ssa.get(); u8 *esa = out.esa.get(); const u64 *ri = ridx.get(); const u64 *ei = eidx.get();
             launch_for(total, st, PFB_LAMBDA(u64 x) {
                 u64 v = U == 4 ? (u64)reinterpret_cast<const u32 *>(sa_out)[x] : reinterpret_cast<const u64 *>(sa_out)[x];
                 if (rp[x]) { store_sa<U>(ssa, 2 * ri[x], slice_off + x); store_sa<U>(ssa, 2 * ri[x] + 1, v); }
-                if (ep[x]) { store_sa<U>(esa, 2 * ei[x], slice_off + x); store_sa<U>(esa, 2 * ei[x] + 1, v); }
+                if (ep[x]) { store_sa<U>(esa, 2 * (ei[x] + pend), slice_off + x); store_sa<U>(esa, 2 * (ei[x] + pend) + 1, v); }
             });
+            if (pend) launch_for(1, st, PFB_LAMBDA(u64) { store_sa<U>(esa, 0, pend_pos); store_sa<U>(esa, 1, pend_sa); });
+        }
+        if (carry) {
+            carry->r = r; carry->ssa += cnts[0]; carry->esa += pend + cnts[1];
+            carry->easy += out.easy; carry->hard += out.hard;
+            if (total) {
+                carry->have_last = true;
+                carry->last_byte = read_scalar(bwt + (total - 1), st);
+                if (any_sa) carry->last_sa = U == 4 ? (u64)read_scalar(reinterpret_cast<const u32 *>(sa_out) + (total - 1), st)
+                                                    : read_scalar(reinterpret_cast<const u64 *>(sa_out) + (total - 1), st);
+            }
+            carry->off += total;
+            out.easy = carry->easy; out.hard = carry->hard;
         }
     } else if (!want_rssa) {
         out.r = count_runs(bwt, n + 1, ws);
@@ -771,7 +837,7 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
             });
         }
     }
-    if (!comm) { out.ssa_off = out.esa_off = 0; out.ssa_cnt = out.esa_cnt = want_rssa ? out.r : 0; }
+    if (!comm && !carry) { out.ssa_off = out.esa_off = 0; out.ssa_cnt = out.esa_cnt = want_rssa ? out.r : 0; }
     timer.lap("K9 runs");
     tm.runs = timer.stop();
     trace_log().dump("build_bwt");
@@ -779,9 +845,9 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
 }
 
 inline int build_bwt(const DeviceParse &pp, const Params &prm, bool want_sa, bool want_rssa, DeviceBwt &out, Workspace &ws,
-                     StageTimes &tm, std::string &err, Comm *comm = nullptr) {
-    return prm.bits == 64 ? build_bwt_t<8>(pp, prm, want_sa, want_rssa, out, ws, tm, err, comm)
-                          : build_bwt_t<4>(pp, prm, want_sa, want_rssa, out, ws, tm, err, comm);
+                     StageTimes &tm, std::string &err, Comm *comm = nullptr, const ShardSpec *bucket = nullptr, BucketCarry *carry = nullptr) {
+    return prm.bits == 64 ? build_bwt_t<8>(pp, prm, want_sa, want_rssa, out, ws, tm, err, comm, bucket, carry)
+                          : build_bwt_t<4>(pp, prm, want_sa, want_rssa, out, ws, tm, err, comm, bucket, carry);
 }
 
 }  // namespace pfb

@@ -164,6 +164,23 @@ int pfb_load_parse(pfb_ctx *c, const char *prefix, int with_parse_bwt, int with_
     return c->eng.load_parse(prefix, with_parse_bwt != 0, with_sai != 0);
 }
 int pfb_build_bwt(pfb_ctx *c, int sa, int rssa) { CTX_GUARD(c); return c->eng.build(sa != 0, rssa != 0); }
+int pfb_build_bwt_to_files(pfb_ctx *c, const char *prefix, int sa, int rssa, uint64_t hbm_limit_bytes) {
+    CTX_GUARD(c);
+    if (!prefix) return c->eng.fail(PFB_ERR_ARG, "null prefix");
+    return c->eng.build_to_files(prefix, sa != 0, rssa != 0, hbm_limit_bytes);
+}
+uint64_t pfb_build_workspace_bytes(const pfb_ctx *c, int sa, int rssa) {
+    if (!c || !c->eng.parsed) return 0;
+    return c->eng.build_workspace_estimate(sa || rssa, rssa != 0) + pfb::dev_bytes_live();
+}
+int pfb_device_free_bytes(const pfb_ctx *c, size_t *out) {
+    if (!c || !out) return PFB_ERR_ARG;
+    cudaSetDevice(c->eng.device);
+    size_t fr = 0, tot = 0;
+    if (cudaMemGetInfo(&fr, &tot) != cudaSuccess) return PFB_ERR_CUDA;
+    *out = fr + pfb::slab_pool().idle();
+    return PFB_OK;
+}
 int pfb_write_bwt(pfb_ctx *c, const char *prefix, int sa, int rssa, const char *stdout_ext) {
     CTX_GUARD(c);
     return c->eng.write_bwt_files(prefix, sa != 0, rssa != 0, stdout_ext ? stdout_ext : "");
@@ -181,6 +198,8 @@ int pfb_get_sizes(const pfb_ctx *c, pfb_sizes *s) {
     if (e.built) {
         s->r = e.bwt.r; s->easy = e.bwt.easy; s->hard = e.bwt.hard;
         s->has_bwt = 1; s->has_sa = (e.built_sa || e.built_rssa); s->has_rssa = e.built_rssa;
+    } else if (e.streamed) {        // pfb_build_bwt_to_files: the counts are known, the arrays went to the files
+        s->r = e.bwt.r; s->easy = e.bwt.easy; s->hard = e.bwt.hard;
     }
     return PFB_OK;
 }
@@ -219,6 +238,7 @@ int pfb_get_stats(const pfb_ctx *c, pfb_stats *s) {
     s->shard_exchange_ms = c->eng.shard_exchange_ms; s->shard_merge_ms = c->eng.shard_merge_ms;
     s->shard_bytes_moved = c->eng.comm ? c->eng.comm->bytes_moved : 0;
     s->ingest_ms = c->eng.ingest_ms; s->ingest_files = c->eng.ingest_files;
+    s->stream_buckets = c->eng.stream_buckets; s->stream_peak_bytes = c->eng.stream_peak;
     return PFB_OK;
 }
 

@@ -36,6 +36,15 @@ struct Comm {
     // (part from rank 0 first).
     virtual void all_to_all_v(const void *d_send, void *d_recv, const u64 *cnt, pfbStream_t st) = 0;
 
+    // Peer windows: every rank passes k device pointers into its own memory; out[r * k + i] = rank r's i-th buffer mapped
+    // into this process, so that a kernel of this rank can store straight into it over NVLink.  Collective; false (on every
+    // rank alike) when the transport has no peer windows - the caller then stages and uses all_to_all_v.
+    virtual bool peer_pointers(void *const *mine, int k, std::vector<void *> &out, pfbStream_t st) {
+        (void)mine; (void)k; (void)out; (void)st;
+        return false;
+    }
+    void barrier(pfbStream_t st) { u64 z = 0; gather_u64(&z, 1, st); }
+
     void all_gather(const void *d_send, void *d_recv, u64 bytes, pfbStream_t st) {
         std::vector<u64> c((size_t)world, bytes);
         all_gather_v(d_send, d_recv, c.data(), st);
@@ -136,7 +145,53 @@ struct NcclComm : Comm {
         memcpy(id.b, uid128, 128);
         check(a.CommInitRank(&comm, world, id, rank), "CommInitRank");
     }
-    ~NcclComm() override { if (comm) nccl_api().CommDestroy(comm); }
+    ~NcclComm() override {
+        for (auto &o : opened) cudaIpcCloseMemHandle(o.second);
+        if (comm) nccl_api().CommDestroy(comm);
+    }
+    // CUDA IPC: the slab a buffer lives in is exported once, opened once per peer and kept open (slabs live as long as
+    // the process); what travels per call is (handle, offset) per buffer.  PFB_PEER=0 keeps everything on NCCL.
+    std::map<std::string, void *> opened;          // 64-byte handle -> where the peer's slab is mapped here
+    bool peer_ok = !(getenv("PFB_PEER") && !strcmp(getenv("PFB_PEER"), "0"));
+    bool peer_pointers(void *const *mine, int k, std::vector<void *> &out, pfbStream_t st) override {
+        const int W = 10;                          // u64 words per buffer: 8 handle, offset, ok
+        std::vector<u64> msg((size_t)k * W, 0);
+        bool ok = peer_ok;
+        for (int i = 0; i < k && ok; ++i) {
+            char *base = nullptr; size_t off = 0;
+            cudaIpcMemHandle_t h;
+            if (!slab_pool().locate(mine[i], base, off) || cudaIpcGetMemHandle(&h, base) != cudaSuccess) { cudaGetLastError(); ok = false; break; }
+            static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+            memcpy(&msg[(size_t)i * W], &h, 64);
+            msg[(size_t)i * W + 8] = off;
+        }
+        for (int i = 0; i < k; ++i) msg[(size_t)i * W + 9] = ok ? 1 : 0;
+        std::vector<u64> all = gather_u64(msg.data(), k * W, st);
+        for (int r = 0; r < world; ++r) for (int i = 0; i < k; ++i) ok = ok && all[((size_t)r * k + i) * W + 9] != 0;
+        out.assign((size_t)world * k, nullptr);
+        for (int r = 0; r < world && ok; ++r)
+            for (int i = 0; i < k && ok; ++i) {
+                if (r == rank) { out[(size_t)r * k + i] = mine[i]; continue; }
+                const u64 *m = &all[((size_t)r * k + i) * W];
+                std::string key((const char *)m, 64);
+                auto it = opened.find(key);
+                void *base = nullptr;
+                if (it != opened.end()) base = it->second;
+                else {
+                    cudaIpcMemHandle_t h;
+                    memcpy(&h, m, 64);
+                    if (cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = false; break; }
+                    opened[key] = base;
+                }
+                out[(size_t)r * k + i] = (char *)base + m[8];
+            }
+        // a rank that could not map a peer makes every rank fall back
+        u64 f = ok ? 1 : 0;
+        std::vector<u64> fl = gather_u64(&f, 1, st);
+        for (int r = 0; r < world; ++r) ok = ok && fl[(size_t)r] != 0;
+        if (!ok) peer_ok = false;
+        return ok;
+    }
     void all_gather_v(const void *d_send, void *d_recv, const u64 *counts, pfbStream_t st) override {
         NcclApi &a = nccl_api();
         bool equal = true;

@@ -152,6 +152,9 @@ struct KeySelect {
     u64 tile0 = 0, ntl = 0;       // modes 4 / 5: first tile and number of tiles of this rank's position slice
     int nd = 0;                   // destinations
     u64 bound[KEY_MAX_DEST + 1];  // bound[0] = 0 <= ... <= bound[nd] = ~0
+    // mode 5: where destination d's pairs go - a staging buffer of this rank, or the receive buffer of rank d itself mapped
+    // over NVLink (the part this rank contributes) - and tilebase[d * ntl] (pairs for destinations before d)
+    u64 *key_outs[KEY_MAX_DEST]; u32 *idx_outs[KEY_MAX_DEST]; u64 destbase[KEY_MAX_DEST];
 };
 PFB_HD inline int key_dest(const u64 *bound, int nd, u64 code) {      // largest d with bound[d] <= code
     int lo = 0, hi = nd;
@@ -271,15 +274,42 @@ __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict
                 ks.tilecnt[(u64)threadIdx.x * ks.ntl + blockIdx.x] = t;
             }
         } else {
+            // the tile's pairs are grouped by destination in shared memory, then every destination's run leaves as
+            // unit-stride stores: towards a peer GPU these are full 128-byte NVLink writes instead of scattered 8-byte ones
+            __shared__ u32 dstart[KEY_MAX_DEST + 1];
+            __shared__ u64 dglob[KEY_MAX_DEST];
+            __shared__ u32 sidx[MODE == 5 ? KEYS_TILE : 1];
+            __shared__ u8 sdst[MODE == 5 ? KEYS_TILE : 1];
+            if (threadIdx.x == 0) {
+                u32 run = 0;
+                for (int dd = 0; dd < ks.nd; ++dd) {
+                    u32 t = 0;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) t += rsum[k][dd];
+                    dstart[dd] = run; run += t;
+                    dglob[dd] = ks.tilebase[(u64)dd * ks.ntl + blockIdx.x] - ks.destbase[dd];
+                }
+                dstart[ks.nd] = run;
+            }
+            __syncthreads();
 #pragma unroll
             for (int p = 0; p < 8; ++p) {
                 const u32 dd = (u32)(dstv >> (8 * p)) & 0xffu;
                 if (dd == 0xffu) continue;
                 u32 wb = 0;
                 for (int k = 0; k < wid; ++k) wb += rsum[k][dd];
-                const u64 o = ks.tilebase[(u64)dd * ks.ntl + blockIdx.x] + wb + offp[p];
-                ks.key_out[o] = mykeys[MODE == 5 ? p : 0];
-                ks.idx_out[o] = (u32)(base + (u64)(i0 + p));
+                const u32 q = dstart[dd] + wb + offp[p];
+                sk[q] = mykeys[MODE == 5 ? p : 0];
+                sidx[MODE == 5 ? q : 0] = (u32)(base + (u64)(i0 + p));
+                sdst[MODE == 5 ? q : 0] = (u8)dd;
+            }
+            __syncthreads();
+            const u32 T = dstart[ks.nd];
+            for (u32 i = threadIdx.x; i < T; i += 256) {
+                const u32 dd = sdst[MODE == 5 ? i : 0];
+                const u64 o = dglob[dd] + (u64)(i - dstart[dd]);
+                ks.key_outs[dd][o] = sk[i];
+                ks.idx_outs[dd][o] = sidx[MODE == 5 ? i : 0];
             }
         }
     } else if (MODE >= 2) {
@@ -401,67 +431,84 @@ inline u64 k_suffix_keys_select(const u8 *dict, u64 D, int L, const WordLookup &
 }
 
 // ---- position-sliced routing (multi-GPU path): this rank scans the tiles [tile0, tile0 + ntl) of the dictionary and
-// groups the (key, position) pairs of the valid suffixes by the rank that owns their code range.  key_out / idx_out
-// (allocated here) hold destination 0's pairs first, each part in dictionary order; counts[d] = pairs for rank d.
-template <class WS>
-inline void k_suffix_keys_route(const u8 *dict, u64 D, int L, const WordLookup &wl, const u32 *occ, int w, const KeyExtra &kx,
-                                const std::vector<u64> &bound, u64 tile0, u64 ntl, DevBuf<u64> &key_out, DevBuf<u32> &idx_out,
-                                std::vector<u64> &counts, WS &ws) {
-    pfbStream_t st = ws.st;
-    const int nd = (int)bound.size() - 1;
-    counts.assign((size_t)nd, 0);
+// sends the (key, position) pair of every valid suffix to the rank that owns its code range.  Two steps, because the
+// receivers' buffers can only be sized (and their addresses exchanged) once every rank knows what it will get:
+//   count()    keys of the slice, pairs per destination
+//   scatter()  keys again, every pair written to its place: key_outs[d] / idx_outs[d] point at the start of THIS rank's
+//              part of destination d's pairs - inside a local staging buffer, or inside rank d's receive buffer mapped over
+//              NVLink (the stores of the key kernel are then the exchange).  A destination's part is in dictionary order.
+struct KeyRouter {
+    const u8 *dict; u64 D; int L; WordLookup wl; const u32 *occ; int w; KeyExtra kx;
+    std::vector<u64> bound; u64 tile0 = 0, ntl = 0;
+    std::vector<u64> counts, destbase;        // pairs for destination d / pairs for the destinations before d
 #ifdef PFB_EMU
-    (void)st;
-    std::vector<std::vector<u64>> ks_((size_t)nd);
-    std::vector<std::vector<u32>> is_((size_t)nd);
-    const u64 p0 = tile0 * KEYS_TILE, p1 = (tile0 + ntl) * KEYS_TILE < D ? (tile0 + ntl) * KEYS_TILE : D;
-    for (u64 i = p0; i < p1; ++i) {
-        u32 d;
-        if (!key_is_valid(wl, (u32)i, w, d)) continue;
-        EnumKey e = enum_scan(dict, D, i, L);
-        const int dst = key_dest(bound.data(), nd, e.code);
-        bool full = (u32)i == wl.start(d);
-        ks_[(size_t)dst].push_back(pack_key(e.code, e.consumed, e.closed, (u32)prev_code(dict, i)) | kx.pack(occ[d], full));
-        is_[(size_t)dst].push_back((u32)i);
-    }
-    u64 m = 0;
-    for (int d = 0; d < nd; ++d) { counts[(size_t)d] = ks_[(size_t)d].size(); m += counts[(size_t)d]; }
-    key_out.alloc(m); idx_out.alloc(m);
-    u64 o = 0;
-    for (int d = 0; d < nd; ++d) {
-        if (counts[(size_t)d]) { memcpy(key_out.get() + o, ks_[(size_t)d].data(), counts[(size_t)d] * 8); memcpy(idx_out.get() + o, is_[(size_t)d].data(), counts[(size_t)d] * 4); }
-        o += counts[(size_t)d];
-    }
+    std::vector<std::vector<u64>> ks_;
+    std::vector<std::vector<u32>> is_;
 #else
-    if (ntl == 0) { key_out.alloc(0); idx_out.alloc(0); return; }
-    const u64 cells = (u64)nd * ntl;
-    DevBuf<u32> tcnt(cells + 1);
-    DevBuf<u64> tbase(cells + 1), ends((size_t)nd + 1);
+    DevBuf<u32> tcnt;
+    DevBuf<u64> tbase;
     KeySelect ks;
-    ks.tile0 = tile0; ks.ntl = ntl; ks.nd = nd;
-    for (int d = 0; d <= nd; ++d) ks.bound[d] = bound[(size_t)d];
-    ks.tilecnt = tcnt.get();
-    k_suffix_keys_kernel<4><<<(unsigned)ntl, 256, 0, st>>>(dict, D, L, nullptr, wl, occ, w, kx, ks);
-    PFB_CUDA_CHECK(cudaGetLastError());
-    dev_memset(tcnt.get() + cells, 0, 4, st);
-    exclusive_sum<u32, u64>(tcnt.get(), tbase.get(), cells + 1, ws.sc, st);
-    {
-        const u64 *tb = tbase.get(); u64 *ep = ends.get(); const u64 ntl_ = ntl;
-        launch_for((u64)nd + 1, st, PFB_LAMBDA(u64 d) { ep[d] = tb[d * ntl_]; });
+#endif
+    template <class WS>
+    void count(WS &ws) {
+        pfbStream_t st = ws.st;
+        const int nd = (int)bound.size() - 1;
+        counts.assign((size_t)nd, 0); destbase.assign((size_t)nd + 1, 0);
+#ifdef PFB_EMU
+        (void)st;
+        ks_.assign((size_t)nd, std::vector<u64>()); is_.assign((size_t)nd, std::vector<u32>());
+        const u64 p0 = tile0 * KEYS_TILE, p1 = (tile0 + ntl) * KEYS_TILE < D ? (tile0 + ntl) * KEYS_TILE : D;
+        for (u64 i = p0; i < p1; ++i) {
+            u32 d;
+            if (!key_is_valid(wl, (u32)i, w, d)) continue;
+            EnumKey e = enum_scan(dict, D, i, L);
+            const int dst = key_dest(bound.data(), nd, e.code);
+            bool full = (u32)i == wl.start(d);
+            ks_[(size_t)dst].push_back(pack_key(e.code, e.consumed, e.closed, (u32)prev_code(dict, i)) | kx.pack(occ[d], full));
+            is_[(size_t)dst].push_back((u32)i);
+        }
+        for (int d = 0; d < nd; ++d) { counts[(size_t)d] = ks_[(size_t)d].size(); destbase[(size_t)d + 1] = destbase[(size_t)d] + counts[(size_t)d]; }
+#else
+        if (ntl == 0) return;
+        const u64 cells = (u64)nd * ntl;
+        tcnt.alloc(cells + 1); tbase.alloc(cells + 1);
+        DevBuf<u64> ends((size_t)nd + 1);
+        ks = KeySelect();
+        ks.tile0 = tile0; ks.ntl = ntl; ks.nd = nd;
+        for (int d = 0; d <= nd; ++d) ks.bound[d] = bound[(size_t)d];
+        ks.tilecnt = tcnt.get();
+        k_suffix_keys_kernel<4><<<(unsigned)ntl, 256, 0, st>>>(dict, D, L, nullptr, wl, occ, w, kx, ks);
+        PFB_CUDA_CHECK(cudaGetLastError());
+        launch_stats().own++;
+        dev_memset(tcnt.get() + cells, 0, 4, st);
+        exclusive_sum<u32, u64>(tcnt.get(), tbase.get(), cells + 1, ws.sc, st);
+        {
+            const u64 *tb = tbase.get(); u64 *ep = ends.get(); const u64 ntl_ = ntl;
+            launch_for((u64)nd + 1, st, PFB_LAMBDA(u64 d) { ep[d] = tb[d * ntl_]; });
+        }
+        d2h(destbase.data(), ends.get(), ((size_t)nd + 1) * 8, st);
+        stream_sync(st);
+        for (int d = 0; d < nd; ++d) counts[(size_t)d] = destbase[(size_t)d + 1] - destbase[(size_t)d];
+#endif
     }
-    std::vector<u64> he((size_t)nd + 1);
-    d2h(he.data(), ends.get(), ((size_t)nd + 1) * 8, st);
-    stream_sync(st);
-    for (int d = 0; d < nd; ++d) counts[(size_t)d] = he[(size_t)d + 1] - he[(size_t)d];
-    const u64 m = he[(size_t)nd];
-    key_out.alloc(m); idx_out.alloc(m);
-    if (m) {
-        ks.tilebase = tbase.get(); ks.key_out = key_out.get(); ks.idx_out = idx_out.get();
+    template <class WS>
+    void scatter(u64 *const *key_outs, u32 *const *idx_outs, WS &ws) {
+        pfbStream_t st = ws.st;
+        const int nd = (int)bound.size() - 1;
+#ifdef PFB_EMU
+        (void)st;
+        for (int d = 0; d < nd; ++d)
+            if (counts[(size_t)d]) { memcpy(key_outs[d], ks_[(size_t)d].data(), counts[(size_t)d] * 8); memcpy(idx_outs[d], is_[(size_t)d].data(), counts[(size_t)d] * 4); }
+        ks_.clear(); is_.clear();
+#else
+        if (ntl == 0 || destbase[(size_t)nd] == 0) return;
+        ks.tilebase = tbase.get();
+        for (int d = 0; d < nd; ++d) { ks.key_outs[d] = key_outs[d]; ks.idx_outs[d] = idx_outs[d]; ks.destbase[d] = destbase[(size_t)d]; }
         k_suffix_keys_kernel<5><<<(unsigned)ntl, 256, 0, st>>>(dict, D, L, nullptr, wl, occ, w, kx, ks);
         PFB_CUDA_CHECK(cudaGetLastError());
-    }
-    launch_stats().own += 2;
+        launch_stats().own++;
 #endif
-}
+    }
+};
 
 }  // namespace pfb

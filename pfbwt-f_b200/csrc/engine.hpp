@@ -215,7 +215,7 @@ struct Engine {
         invalidate();
     }
 
-    void invalidate() { text_ready = false; parsed = false; built = false; }
+    void invalidate() { text_ready = false; parsed = false; built = false; streamed = false; }
 
     // ---- text upload: T' = Dollar . S . Dollar^w, S 16-byte aligned ---------------
     int upload_text() {
@@ -289,6 +289,84 @@ struct Engine {
             return PFB_OK;
         } catch (const Error &e) { return fail(e.code, e.what()); }
     }
+
+    // ---- -m: workspace larger than the device memory (include/file_wrappers.hpp:35-124, include/pfbwt.hpp:208-209; the
+    // reference keeps gsa/glcp/ilist in mmap'ed files).  Here the per-suffix work arrays are what does not fit, so the
+    // dictionary suffixes are sorted and emitted one key range ("bucket") after the other on the same GPU - the
+    // range-partitioned sort of the multi-GPU path run as a loop - and every finished slice of .bwt/.sa/.ssa/.esa is
+    // streamed to its place in the output files before the next bucket starts.
+    u64 stream_buckets = 0, stream_peak = 0;      // of the last build_to_files
+    static u64 parse_size_bytes(const std::string &s) {        // "48G", "512M", plain bytes
+        char *end = nullptr;
+        double v = strtod(s.c_str(), &end);
+        if (end && (*end == 'G' || *end == 'g')) v *= (double)(1ull << 30);
+        else if (end && (*end == 'M' || *end == 'm')) v *= (double)(1ull << 20);
+        else if (end && (*end == 'K' || *end == 'k')) v *= 1024.0;
+        return v > 0 ? (u64)v : 0;
+    }
+    // bytes of per-suffix / per-position work and output one full build holds at its peak (measured: 111 GB at D = 3.38e9,
+    // n = 3.1e9, U = 8 with SA - keys 2 x 8, positions 2 x 4, meta, counts, lookups with SA; output 1 + U per position)
+    u64 build_workspace_estimate(bool any_sa, bool rssa) const {
+        const u64 U = (u64)prm.bits / 8;
+        return parse.dsize * (any_sa ? 38ull : 30ull) + (parse.n + 1) * (1 + (any_sa ? U : 0) + (rssa ? 18ull : 0));
+    }
+    int build_to_files(const std::string &prefix, bool sa, bool rssa, u64 limit_bytes) {
+        try {
+            if (!parsed) return fail(PFB_ERR_ARG, "no parse loaded");
+            if (comm) return fail(PFB_ERR_ARG, "the bucketed build is a single-GPU mode");
+            if (!parse.has_parse_bwt) { int rc = do_parse_bwt(); if (rc) return rc; }
+            const bool any_sa = sa || rssa;
+            const int U = prm.bits / 8;
+            if (const char *e = getenv("PFB_HBM_LIMIT")) { const u64 v = parse_size_bytes(e); if (v) limit_bytes = v; }
+#ifndef PFB_EMU
+            if (!limit_bytes) {
+                size_t fr = 0, tot = 0;
+                cudaMemGetInfo(&fr, &tot);
+                limit_bytes = (u64)fr + slab_pool().idle();
+            }
+#endif
+            const u64 est = build_workspace_estimate(any_sa, rssa);
+            const u64 resident = dev_bytes_live();
+            u64 B = 1;
+            if (limit_bytes && est + resident > limit_bytes) {
+                if (resident + (est >> 6) >= limit_bytes) return fail(PFB_ERR_NOMEM, "the memory limit does not even hold the dictionary and the parse");
+                B = (est + (limit_bytes - resident) - 1) / (limit_bytes - resident);
+            }
+            if (const char *e = getenv("PFB_BUCKETS")) { const long v = atol(e); if (v > 0) B = (u64)v; }       // test knob
+            if (B > (u64)KEY_MAX_DEST) B = KEY_MAX_DEST;
+            bwt = DeviceBwt();
+            built = false;
+            const size_t peak0 = dev_bytes_peak();
+            dev_bytes_peak() = dev_bytes_live();
+            BucketCarry carry;
+            std::string e;
+            for (const char *ext : {"bwt", "sa", "ssa", "esa"}) {
+                const bool want = !strcmp(ext, "bwt") || (!strcmp(ext, "sa") && sa) || ((!strcmp(ext, "ssa") || !strcmp(ext, "esa")) && rssa);
+                if (want) unlink((prefix + "." + ext).c_str());
+            }
+            DeviceBwt last;
+            for (u64 b = 0; b < B; ++b) {
+                ShardSpec spec;
+                spec.rank = (int)b; spec.world = (int)B;
+                DeviceBwt out;
+                int rc = build_bwt(parse, prm, sa, rssa, out, ws, tm, err, nullptr, &spec, &carry);
+                if (rc) return fail(rc, err);
+                if (write_dev_file(prefix + ".bwt", out.bwt.get(), out.len, out.off, out.n + 1, false, device, ws.st, e)) return fail(PFB_ERR_IO, e);
+                if (sa && write_dev_file(prefix + ".sa", out.sa.get(), out.len * (size_t)U, out.off * (u64)U, (out.n + 1) * (u64)U, false, device, ws.st, e)) return fail(PFB_ERR_IO, e);
+                if (rssa) {
+                    if (write_dev_file(prefix + ".ssa", out.ssa.get(), 2 * out.ssa_cnt * (size_t)U, 2 * out.ssa_off * (u64)U, 2 * (out.ssa_off + out.ssa_cnt) * (u64)U, false, device, ws.st, e)) return fail(PFB_ERR_IO, e);
+                    if (write_dev_file(prefix + ".esa", out.esa.get(), 2 * out.esa_cnt * (size_t)U, 2 * out.esa_off * (u64)U, 2 * (out.esa_off + out.esa_cnt) * (u64)U, false, device, ws.st, e)) return fail(PFB_ERR_IO, e);
+                }
+                last.n = out.n; last.r = out.r; last.easy = out.easy; last.hard = out.hard;
+            }
+            bwt.n = last.n; bwt.r = last.r; bwt.easy = last.easy; bwt.hard = last.hard;      // sizes only: the slices went to the files
+            streamed = true;
+            stream_buckets = B; stream_peak = dev_bytes_peak();
+            if (dev_bytes_peak() < peak0) dev_bytes_peak() = peak0;
+            return PFB_OK;
+        } catch (const Error &e) { return fail(e.code, e.what()); }
+    }
+    bool streamed = false;            // the last build went straight to files (sizes available, arrays not)
 
     // drop the text and the staged input (records in HBM from the device reader / add_records, host staging) once the
     // parse exists: only dict/parse are needed downstream.  Parsing again needs pfb_clear + the input once more.

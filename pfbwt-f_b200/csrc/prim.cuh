@@ -174,6 +174,13 @@ struct SlabPool {
         }
     }
     void trim() { std::lock_guard<std::mutex> lk(mu); cudaDeviceSynchronize(); trim_locked(); }
+    // the slab (one cudaMalloc allocation) a pointer lies in: what CUDA IPC exports to the peers of a multi-GPU job
+    bool locate(const void *p, char *&base, size_t &off) {
+        std::lock_guard<std::mutex> lk(mu);
+        const char *c = (const char *)p;
+        for (auto &s : slabs) if (c >= s.base && c < s.base + s.size) { base = s.base; off = (size_t)(c - s.base); return true; }
+        return false;
+    }
     size_t reserved() { std::lock_guard<std::mutex> lk(mu); size_t t = 0; for (auto &s : slabs) t += s.size; return t; }
     size_t idle() { std::lock_guard<std::mutex> lk(mu); size_t t = 0; for (auto &f : free_) t += f.second; return t; }   // bytes held but not handed out
 };

@@ -48,7 +48,9 @@ static void print_help() {
 "    -r                  Output run-length sampled suffix arrray to <fasta file>.ssa (run-starts) and <fasta file>.esa (run-ends)\n"
 "    -w <int>            window-size for parsing [default: 10]\n"
 "    -p <int>            modulo for parsing [default: 100]\n"
-"    -m                  accepted for compatibility (workspace lives in HBM)\n"
+"    -m                  workspace larger than the device memory: build and write the BWT one key range after the other\n"
+"                        (PFB_HBM_LIMIT=<bytes|48G> caps the device memory used; chosen automatically when the work arrays\n"
+"                        of a full build would not fit)\n"
 "    --parse-only        only produce parse (dict, occ, ilist, last, bwlast)\n"
 "    --pfbwt-only        build pfbwt from parse + parse-bwt. Requires -o to match parse files' prefix.\n"
 "    --non-acgt-to-a     convert non-ACGT characters to A\n"
@@ -166,12 +168,28 @@ int main(int argc, char **argv) {
     }
     if (!args.parse_only) {   // run_pfbwt, src/pfbwt-f.cpp:272-349
         fprintf(stderr, "generating BWT using pfbwt algorithm...\n");
-        fprintf(stderr, "workspace will be contained in HBM\n");
+        // src/pfbwt-f.cpp:359-365: -m selects the file-backed workspace.  Here: key-range buckets streamed to the files; also
+        // taken when a full build would not fit the device memory (the reference would swap or die)
+        bool bucketed = args.mmap || getenv("PFB_HBM_LIMIT") != NULL;
+        if (!bucketed && args.stdout_ext.empty()) {
+            size_t fr = 0;
+            const uint64_t need = pfb_build_workspace_bytes(ctx, args.sa, args.rssa);
+            if (pfb_device_free_bytes(ctx, &fr) == 0 && need > fr) bucketed = true;
+        }
+        if (bucketed && !args.stdout_ext.empty()) { fprintf(stderr, "--stdout is not available with -m\n"); exit(1); }
+        fprintf(stderr, bucketed ? "workspace will be cut into key-range buckets streamed to the output files\n" : "workspace will be contained in HBM\n");
         {
             Timer t(any_sa ? "TASK\tgenerating final BWT w/ full and/or run-length SA\t" : "TASK\tgenerating final BWT w/o SA\t");
-            { SubTimer t2("BWT on device"); if (pfb_build_bwt(ctx, args.sa, args.rssa)) die_ctx(ctx); }
-            SubTimer t3("writing BWT files");
-            if (pfb_write_bwt(ctx, args.output.c_str(), args.sa, args.rssa, args.stdout_ext.empty() ? NULL : args.stdout_ext.c_str())) die_ctx(ctx);
+            if (bucketed) {
+                if (pfb_build_bwt_to_files(ctx, args.output.c_str(), args.sa, args.rssa, 0)) die_ctx(ctx);
+                pfb_stats s;
+                pfb_get_stats(ctx, &s);
+                fprintf(stderr, "buckets: %lu, peak device bytes: %lu\n", (unsigned long)s.stream_buckets, (unsigned long)s.stream_peak_bytes);
+            } else {
+                { SubTimer t2("BWT on device"); if (pfb_build_bwt(ctx, args.sa, args.rssa)) die_ctx(ctx); }
+                SubTimer t3("writing BWT files");
+                if (pfb_write_bwt(ctx, args.output.c_str(), args.sa, args.rssa, args.stdout_ext.empty() ? NULL : args.stdout_ext.c_str())) die_ctx(ctx);
+            }
         }
         pfb_sizes sz;
         pfb_get_sizes(ctx, &sz);

@@ -16,7 +16,7 @@ size_t &dev_bytes_peak() { static size_t v = 0; return v; }
 }
 
 int main(int argc, char **argv) {
-    int w = 10, p = 100, sa = 0, rssa = 0, bits = 32, ntoa = 0, parse_only = 0, merge = 0, docs = 0, write_last = 0;
+    int w = 10, p = 100, sa = 0, rssa = 0, bits = 32, ntoa = 0, parse_only = 0, merge = 0, docs = 0, write_last = 0, bucketed = 0;
     std::string out;
     std::vector<std::string> in;
     for (int i = 1; i < argc; ++i) {
@@ -31,6 +31,7 @@ int main(int argc, char **argv) {
         else if (a == "--print-docs") docs = 1;
         else if (a == "--merge") merge = 1;
         else if (a == "--write-last") write_last = 1;
+        else if (a == "-m") bucketed = 1;                 // key-range buckets streamed to the files (PFB_BUCKETS / PFB_HBM_LIMIT)
         else if (a == "-o") out = argv[++i];
         else in.push_back(a);
     }
@@ -57,7 +58,8 @@ int main(int argc, char **argv) {
     if (E.finalize() || E.save_parse(out, false, false) || (write_last && E.save_last_sai(out, true, true)) || E.do_parse_bwt() ||
         E.save_parse(out, true, sa || rssa, true)) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }
     if (parse_only) return 0;
-    if (E.build(sa, rssa) || E.write_bwt_files(out, sa, rssa, "")) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }
+    if (bucketed ? E.build_to_files(out, sa, rssa, 0) : (E.build(sa, rssa) || E.write_bwt_files(out, sa, rssa, ""))) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }
+    if (bucketed) fprintf(stderr, "buckets: %lu\n", (unsigned long)E.stream_buckets);
     fprintf(stderr, "# easy cases: %lu, # hard cases: %lu\nn: %lu\nr: %lu\nrounds: phrase %u parse_sa %u dict %u\n",
             (unsigned long)E.bwt.easy, (unsigned long)E.bwt.hard, (unsigned long)E.bwt.n, (unsigned long)E.bwt.r,
             E.tm.phrase_sort_rounds, E.tm.parse_sa_rounds, E.tm.dict_sort_rounds);

@@ -186,3 +186,20 @@ def test_emu_write_last_sai_and_merge_docs(emu, ref_bins, datadir):
         refd = os.path.join(datadir, "wl_refdocs")
         run([ref_bins["pfbwt-f64"], "--print-docs", "--parse-only", "-o", refd, fa])
         assert_same_files(refd, merged, ["docs"])
+
+
+@pytest.mark.parametrize("buckets,flags,bits", [(1, ["-s", "-r"], 32), (3, ["-s", "-r"], 64), (7, ["-r"], 32), (5, [], 32), (64, ["-s", "-r"], 32)])
+def test_emu_bucketed_build(buckets, flags, bits, emu, ref_bins, datadir):
+    """-m: the BWT is built one key range after the other and every slice streamed to its offset of .bwt/.sa/.ssa/.esa
+    (run boundaries and the deferred run end across bucket borders, empty buckets) - same bytes as the one-piece build"""
+    fa = os.path.join(datadir, "bucket.fa")
+    if not os.path.exists(fa):
+        write_fasta(fa, pangenome_records(40_000, 5, 40, 3) + nrun_records(1, 20_000, 9, big_run=3000), line_width=60)
+    a = os.path.join(datadir, f"bucket{bits}{''.join(flags)}.port")
+    b = os.path.join(datadir, f"bucket{bits}{''.join(flags)}_{buckets}.emu")
+    run([ref_bins["pfp_oracle"], "--bits", str(bits)] + flags + ["-o", a, fa])
+    r = subprocess.run([emu, "--bits", str(bits), "-m"] + flags + ["-o", b, fa], env=dict(os.environ, PFB_BUCKETS=str(buckets)),
+                       stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    assert r.returncode == 0, r.stderr.decode()[-1500:]
+    assert f"buckets: {buckets}" in r.stderr.decode()
+    assert_same_files(a, b, exts_for("-s" in flags, "-r" in flags))

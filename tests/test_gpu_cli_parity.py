@@ -244,3 +244,34 @@ def test_cli_one_word_leaves_parse_files(ref_bins, datadir):
         ra = run([ref_bins["pfbwt-f"], "-p", "1000000", "-o", a, fa], check=False)
         assert ra.returncode == 1
         assert_same_files(a, b, ["dict", "occ", "parse", "n"])
+
+
+@pytest.mark.parametrize("env", [{"PFB_BUCKETS": "4"}, {"PFB_HBM_LIMIT": "40M"}, {"PFB_BUCKETS": "1"}], ids=["buckets4", "limit40M", "one"])
+def test_cli_bucketed_build(env, ref_bins, datadir):
+    """-m: workspace cut into key-range buckets, every slice of .bwt/.sa/.ssa/.esa streamed to its offset -
+    byte-identical to the reference whatever the number of buckets"""
+    import re, subprocess
+    fa = os.path.join(datadir, "bucketed.fa")
+    flags = ["-s", "-r", "--non-acgt-to-a"]
+    a = os.path.join(datadir, "bucketed.ref")
+    if not os.path.exists(a + ".bwt"):
+        write_fasta(fa, pangenome_records(400_000, 6, 400, 5) + nrun_records(2, 150_000, 9, big_run=20_000), line_width=70)
+        run(oracle_cmd(ref_bins, 64, flags, a, fa))
+    b = os.path.join(datadir, "bucketed.gpu" + "".join(env.values()))
+    r = subprocess.run([os.path.join(BIN, "pfbwt-f64"), "-m"] + flags + ["-o", b, fa], env=dict(os.environ, **env),
+                       stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    assert r.returncode == 0, r.stderr.decode()[-2000:]
+    m = re.search(r"buckets: (\d+), peak device bytes: (\d+)", r.stderr.decode())
+    assert m, r.stderr.decode()[-800:]
+    if "PFB_HBM_LIMIT" in env:
+        assert int(m.group(1)) > 1 and int(m.group(2)) <= 40 << 20, m.group(0)
+    if "PFB_BUCKETS" in env:
+        assert int(m.group(1)) == int(env["PFB_BUCKETS"])
+    assert_same_files(a, b, exts_for(True, True))
+    # the counts the driver prints come from the carried totals
+    ra = run(oracle_cmd(ref_bins, 64, flags, a + "2", fa))
+    for key in (b"n: ", b"r: ", b"# easy cases"):
+        la = [l for l in ra.stderr.splitlines() if l.startswith(key)]
+        lb = [l for l in r.stderr.splitlines() if l.startswith(key)]
+        if la:
+            assert la == lb, (la, lb)
