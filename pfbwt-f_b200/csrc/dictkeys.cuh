@@ -161,6 +161,29 @@ PFB_HD inline int key_dest(const u64 *bound, int nd, u64 code) {      // largest
     while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (bound[mid] <= code) lo = mid; else hi = mid; }
     return lo;
 }
+// 8 dictionary bytes (little endian: symbol 0 in the low byte) -> [0,16) their 2-bit fields, [16,24) "is a stopper",
+// [24,32) "is EndOfWord / EndOfDict", symbol 0 in the most significant position of each part.  Word-wide arithmetic on the
+// 8 byte values of the alphabet: field = ((c >> 1) & 3) ^ bit1-of-that ^ bit 3 of c (ACGT -> 0..3; 0x00/0x01 -> 0, 0x02 -> 1,
+// '-' -> 2, 'N' -> 3 = sym_field(sym3(c))), stopper = bit 6 clear or bit 3 set, end = c < 2; bits gathered by multiplication.
+PFB_HD inline u32 key_pack8(u64 x) {
+    // byte swap: symbol 0 to the most significant byte, so that the gathers below keep the order
+    u64 z = ((x & 0x00ff00ff00ff00ffull) << 8) | ((x >> 8) & 0x00ff00ff00ff00ffull);
+    z = ((z & 0x0000ffff0000ffffull) << 16) | ((z >> 16) & 0x0000ffff0000ffffull);
+    z = (z << 32) | (z >> 32);
+    const u64 ONE = 0x0101010101010101ull;
+    u64 y = (z >> 1) & (3 * ONE);
+    y ^= (y >> 1) & ONE;
+    y ^= (z >> 3) & ONE;
+    u64 a = (y | (y >> 6)) & 0x000F000F000F000Full;          // stride 8 -> 4 -> 2 bits
+    a = (a | (a >> 12)) & 0x000000FF000000FFull;
+    a = (a | (a >> 24)) & 0xFFFFull;
+    const u64 st = ((~z >> 6) | (z >> 3)) & ONE;
+    const u32 stops = (u32)((st * 0x0102040810204080ull) >> 56);
+    const u64 v = z & (0xFEull * ONE);
+    const u64 e = ~((((v & (0x7Full * ONE)) + 0x7Full * ONE) | v) | (0x7Full * ONE));     // 0x80 in every byte that is < 2
+    const u32 ends = (u32)(((e >> 7) * 0x0102040810204080ull) >> 56);
+    return (u32)a | (stops << 16) | (ends << 24);
+}
 #ifndef PFB_EMU
 template <int MODE>
 __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict__ dict, u64 D, int L, u64 *__restrict__ key,
@@ -181,25 +204,29 @@ __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict
         *reinterpret_cast<uint4 *>(sb + o) = v;
     }
     __shared__ u32 sprev;
+    __shared__ u32 spk[KEYS_TILE / 8 + 8];
     if (threadIdx.x == 0) sprev = base ? (u32)dict[base - 1] : 0u;
     __syncthreads();
+    // every 8 bytes of the tile are packed ONCE (word-wide arithmetic, key_pack8) and shared; a thread then assembles
+    // the 40-symbol window of its 8 positions from five packed words instead of packing 40 symbols itself
+    for (int q = threadIdx.x; q < KEYS_TILE / 8 + 6; q += 256) spk[q] = key_pack8(*reinterpret_cast<const u64 *>(sb + 8 * q));
+    __syncthreads();
     const int i0 = threadIdx.x * 8;
-    u64 xh = 0, xl = 0, rm = 0, tmk = 0;    // tmk: EndOfWord / EndOfDict positions
+    u64 xh, xl, rm, tmk;                    // 2-bit fields of symbols 0..31 / 32..39, stopper mask, EndOfWord / EndOfDict mask (MSB first)
+    {
+        const u32 w0 = spk[threadIdx.x], w1 = spk[threadIdx.x + 1], w2 = spk[threadIdx.x + 2], w3 = spk[threadIdx.x + 3], w4 = spk[threadIdx.x + 4];
+        xh = ((u64)(w0 & 0xffffu) << 48) | ((u64)(w1 & 0xffffu) << 32) | ((u64)(w2 & 0xffffu) << 16) | (u64)(w3 & 0xffffu);
+        xl = (u64)(w4 & 0xffffu) << 48;
+        rm = ((u64)((w0 >> 16) & 0xffu) << 56) | ((u64)((w1 >> 16) & 0xffu) << 48) | ((u64)((w2 >> 16) & 0xffu) << 40) |
+             ((u64)((w3 >> 16) & 0xffu) << 32) | ((u64)((w4 >> 16) & 0xffu) << 24);
+        tmk = ((u64)(w0 >> 24) << 56) | ((u64)(w1 >> 24) << 48) | ((u64)(w2 >> 24) << 40) | ((u64)(w3 >> 24) << 32) | ((u64)(w4 >> 24) << 24);
+    }
     u32 pcs[8];
     pcs[0] = sym3_fast(i0 ? (u32)sb[i0 - 1] : sprev);
+    {
+        const u64 wd = *reinterpret_cast<const u64 *>(sb + i0);
 #pragma unroll
-    for (int q = 0; q < 5; ++q) {
-        u64 wd = *reinterpret_cast<const u64 *>(sb + i0 + 8 * q);
-#pragma unroll
-        for (int b = 0; b < 8; ++b) {
-            const int k = 8 * q + b;
-            u32 s = sym3_fast((u32)(wd >> (8 * b)) & 0xffu);
-            u64 f = sym_field(s);
-            if (k < 32) xh |= f << (62 - 2 * k); else xl |= f << (62 - 2 * (k - 32));
-            rm |= (u64)sym_stops(s) << (63 - k);
-            tmk |= (u64)(s == 0 ? 1u : 0u) << (63 - k);
-            if (k < 7) pcs[k + 1] = s;
-        }
+        for (int k = 0; k < 7; ++k) pcs[k + 1] = sym3_fast((u32)(wd >> (8 * k)) & 0xffu);
     }
     // word of the thread's first position (one sampled lookup per 8 positions); later positions add
     // the EndOfWord bytes passed
