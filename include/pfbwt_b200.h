@@ -139,6 +139,10 @@ int pfb_build_bwt(pfb_ctx *, int sa, int rssa);
  * suffixes are sorted and emitted one key range after the other and every finished slice of <prefix>.bwt/.sa/.ssa/.esa is
  * streamed to its offset of the file.  Afterwards pfb_get_sizes reports n, r, easy, hard; the arrays are not kept. */
 int pfb_build_bwt_to_files(pfb_ctx *, const char *prefix, int sa, int rssa, uint64_t hbm_limit_bytes);
+/* Document array (README.md:29-33 "Document Array and other SA-related data structures" - announced, not present in the
+ * reference, so the format is ours): <prefix>.da = one uint32 per BWT position i, the index of the record (line of
+ * <prefix>.docs, include/pfbwt_io.hpp:224-231) holding text position SA[i].  Needs store_docs and pfb_build_bwt with sa/rssa. */
+int pfb_write_doc_array(pfb_ctx *, const char *prefix);
 /* device bytes a full in-memory pfb_build_bwt needs at its peak (estimate), incl. what the context already holds */
 uint64_t pfb_build_workspace_bytes(const pfb_ctx *, int sa, int rssa);
 /* device bytes available to this context right now (free on the device + held idle by the library's allocator) */

@@ -17,7 +17,7 @@ EXPORTS = [
     "pfb_copy_bwt", "pfb_copy_sa", "pfb_copy_ssa", "pfb_copy_esa", "pfb_get_docs", "pfb_upload_text",
     "pfb_run_resident", "pfb_release_text", "pfb_clear",
     "pfb_nccl_unique_id", "pfb_shard_init_nccl", "pfb_shard_init_host", "pfb_get_shard_info", "pfb_get_pending_bases",
-    "pfb_kat_trigger", "pfb_add_chunk", "pfb_add_fasta_range", "pfb_save_last_sai", "pfb_build_bwt_to_files", "pfb_build_workspace_bytes",
+    "pfb_kat_trigger", "pfb_add_chunk", "pfb_add_fasta_range", "pfb_save_last_sai", "pfb_build_bwt_to_files", "pfb_build_workspace_bytes", "pfb_write_doc_array", "pfb_device_free_bytes",
 ]
 
 
@@ -86,6 +86,8 @@ def load():
     lib.pfb_build_bwt.argtypes = [vp, C.c_int, C.c_int]
     lib.pfb_run_resident.argtypes = [vp, C.c_int, C.c_int]
     lib.pfb_build_bwt_to_files.argtypes = [vp, C.c_char_p, C.c_int, C.c_int, C.c_uint64]
+    lib.pfb_write_doc_array.argtypes = [vp, C.c_char_p]
+    lib.pfb_device_free_bytes.argtypes = [vp, vp]
     lib.pfb_build_workspace_bytes.restype = C.c_uint64
     lib.pfb_build_workspace_bytes.argtypes = [vp, C.c_int, C.c_int]
     lib.pfb_write_bwt.argtypes = [vp, C.c_char_p, C.c_int, C.c_int, C.c_char_p]
@@ -217,6 +219,9 @@ class Context:
 
     def build_workspace_bytes(self, sa=False, rssa=False):
         return int(self.lib.pfb_build_workspace_bytes(self.h, int(sa), int(rssa)))
+
+    def write_doc_array(self, prefix):
+        self._ck(self.lib.pfb_write_doc_array(self.h, prefix.encode()))
 
     def write_bwt(self, prefix, sa=False, rssa=False):
         self._ck(self.lib.pfb_write_bwt(self.h, prefix.encode(), int(sa), int(rssa), None))

@@ -173,6 +173,11 @@ uint64_t pfb_build_workspace_bytes(const pfb_ctx *c, int sa, int rssa) {
     if (!c || !c->eng.parsed) return 0;
     return c->eng.build_workspace_estimate(sa || rssa, rssa != 0) + pfb::dev_bytes_live();
 }
+int pfb_write_doc_array(pfb_ctx *c, const char *prefix) {
+    CTX_GUARD(c);
+    if (!prefix) return c->eng.fail(PFB_ERR_ARG, "null prefix");
+    return c->eng.write_doc_array(prefix);
+}
 int pfb_device_free_bytes(const pfb_ctx *c, size_t *out) {
     if (!c || !out) return PFB_ERR_ARG;
     cudaSetDevice(c->eng.device);

@@ -290,6 +290,32 @@ struct Engine {
         } catch (const Error &e) { return fail(e.code, e.what()); }
     }
 
+    // ---- document array (README.md:29-33 lists it as a feature to come, so there is no reference format):
+    // <prefix>.da = one uint32 per BWT position, the index of the record (line of <prefix>.docs) that holds text position
+    // SA[i]; the terminator's entry SA[0] = n counts to the last record.  Needs --print-docs and an SA on the device.
+    int write_doc_array(const std::string &prefix) {
+        try {
+            if (!built || !(built_sa || built_rssa)) return fail(PFB_ERR_ARG, "the document array needs a BWT built with the suffix array (-s / -r)");
+            if (docs.starts.empty()) return fail(PFB_ERR_ARG, "the document array needs the record starts (store_docs / --print-docs)");
+            if (comm) return fail(PFB_ERR_ARG, "the document array is a single-GPU output");
+            const u64 nd = docs.starts.size(), len = bwt.len;
+            DevBuf<u64> ds(nd);
+            h2d(ds.get(), docs.starts.data(), nd * 8, ws.st);
+            DevBuf<u32> da(len ? len : 1);
+            const u64 *sp = ds.get(); u32 *dp = da.get(); const u8 *sa_out = bwt.sa.get();
+            const int U = prm.bits / 8;
+            launch_for(len, ws.st, PFB_LAMBDA(u64 x) {
+                const u64 v = U == 4 ? (u64)reinterpret_cast<const u32 *>(sa_out)[x] : reinterpret_cast<const u64 *>(sa_out)[x];
+                u64 lo = 0, hi = nd;                    // largest d with starts[d] <= v
+                while (hi - lo > 1) { const u64 mid = (lo + hi) >> 1; if (sp[mid] <= v) lo = mid; else hi = mid; }
+                dp[x] = (u32)lo;
+            });
+            std::string e;
+            if (dev_file(prefix + ".da", da.get(), len * 4, e)) return fail(PFB_ERR_IO, e);
+            return PFB_OK;
+        } catch (const Error &e) { return fail(e.code, e.what()); }
+    }
+
     // ---- -m: workspace larger than the device memory (include/file_wrappers.hpp:35-124, include/pfbwt.hpp:208-209; the
     // reference keeps gsa/glcp/ilist in mmap'ed files).  Here the per-suffix work arrays are what does not fit, so the
     // dictionary suffixes are sorted and emitted one key range ("bucket") after the other on the same GPU - the

@@ -397,9 +397,14 @@ PFB_HD inline u64 pivot_key_len(const u8 *buf, u64 sa, u64 la, u64 sp, u64 lp, u
     return pivot_key_result(l, ra > l ? x[l] : 0u, rp > l ? y[l] : 0u);         // both ended: identical (closed)
 }
 
+}  // namespace pfb
+#include "parsekernels.cuh"
+namespace pfb {
+
 struct Workspace {
     Scratch sc;
     pfbStream_t st = 0;
+    TriggerLut lut;          // trigger table of the last (w, p): parsekernels.cuh
 };
 
 // compaction helper: out positions for flagged items; returns number selected
@@ -656,7 +661,10 @@ struct TextOnDevice {
 
 // A piece of T' (multi-GPU parse): bytes Tp[0, tlen); positions qmin.. may trigger; the piece either
 // ends with Dollar^w (end of T') or exactly at a trigger position (the first trigger owned by a later rank).
-struct PieceSpec { u64 tlen = 0, qmin = 0; bool dollar_end = true; };
+struct PieceSpec {
+    u64 tlen = 0, qmin = 0; bool dollar_end = true;
+    const u8 *mem_lo = nullptr, *mem_hi = nullptr;      // the allocation Tp lies in (the tiled trigger scan loads whole aligned tiles)
+};
 
 inline int parse_piece(const u8 *Tp, const PieceSpec &ps, const Params &prm, DeviceParse &out, Workspace &ws, StageTimes &tm, std::string &err) {
     pfbStream_t st = ws.st;
@@ -671,7 +679,11 @@ inline int parse_piece(const u8 *Tp, const PieceSpec &ps, const Params &prm, Dev
     // K1 trigger bitmap ------------------------------------------------------
     const u64 nwords = n / 32 + 1;   // bits 0..n
     DevBuf<u32> trig(nwords), cnt(nwords), wordoff(nwords);
-    k_trigger_words(Tp, n, w, DivTest::make(prm.p), trig.get(), cnt.get(), nwords, st, ps.qmin);
+    bool tiled = false;
+#ifndef PFB_EMU
+    if (ps.mem_lo) tiled = k_trigger_tiled(Tp, n, w, prm.p, trig.get(), cnt.get(), nwords, ps.qmin, ps.mem_lo, ps.mem_hi, ws.lut, st);
+#endif
+    if (!tiled) k_trigger_words(Tp, n, w, DivTest::make(prm.p), trig.get(), cnt.get(), nwords, st, ps.qmin);
     tm.trigger = timer.stop();
 
     // K2 compaction ------------------------------------------------------------
@@ -814,6 +826,7 @@ inline int parse_text(const TextOnDevice &T, const Params &prm, DeviceParse &out
     if (T.n == 0) { err = "empty input"; return PFB_ERR_ARG; }
     PieceSpec ps;
     ps.tlen = T.n + (u64)prm.w + 1; ps.qmin = (u64)prm.w + 1; ps.dollar_end = true;
+    ps.mem_lo = T.buf.get(); ps.mem_hi = T.buf.get() + T.buf.size();
     return parse_piece(T.Tp(), ps, prm, out, ws, tm, err);
 }
 

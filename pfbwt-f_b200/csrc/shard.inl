@@ -142,6 +142,7 @@
                 if (g == 0) { Tp = text.Tp(); ps.qmin = w + 1; base = 0; }
                 else { Tp = text.S() + f - (w - 1); ps.qmin = w; base = 1 + shard_start + f - (w - 1); }
                 ps.dollar_end = dollar_end;
+                ps.mem_lo = text.buf.get(); ps.mem_hi = text.buf.get() + text.buf.size();
                 ps.tlen = (u64)((text.S() + len + rlen + (dollar_end ? w : 0)) - Tp);
                 rc = parse_piece(Tp, ps, prm, lp, ws, tm, err);
                 if (rc) fail(rc, err);

@@ -20,7 +20,7 @@ struct Args {
     std::string in_fname, output, stdout_ext;
     size_t w = 10, p = 100;
     int sa = 0, rssa = 0, mmap = 0, parse_only = 0, trim_non_acgt = 0, non_acgt_to_a = 0, pfbwt_only = 0, verbose = 0, print_docs = 0;
-    int write_last = 0, write_sai = 0;
+    int write_last = 0, write_sai = 0, doc_array = 0;
     int device = 0;
 };
 
@@ -56,6 +56,7 @@ static void print_help() {
 "    --non-acgt-to-a     convert non-ACGT characters to A\n"
 "    --print-docs        write <prefix>.docs\n"
 "    --write-last        also write <prefix>.last (last char of every phrase, include/utils.h EXTLST)\n"
+"    --doc-array         also write <prefix>.da: uint32 record index of SA[i] for every BWT position (implies --print-docs, needs -s or -r)\n"
 "    --write-sai         also write <prefix>.sai (end position of every phrase, include/utils.h EXTSAI)\n"
 "    --stdout <ext>      output file ending <ext> will be stdout instead (bwt, sa)\n"
 "    --device <int>      CUDA device ordinal [default: 0]\n"
@@ -75,6 +76,7 @@ static Args parse_args(int argc, char **argv) {
         {"print-docs", no_argument, &args.print_docs, 1},
         {"write-last", no_argument, &args.write_last, 1},
         {"write-sai", no_argument, &args.write_sai, 1},
+        {"doc-array", no_argument, &args.doc_array, 1},
         {"stdout", required_argument, NULL, 'c'},
         {"verbose", no_argument, &args.verbose, 1},
         {"sa", no_argument, NULL, 's'},
@@ -107,6 +109,10 @@ static Args parse_args(int argc, char **argv) {
     if (args.in_fname == "-" && args.output == "") die("if reading from stdin, need a prefix for output files (-o, --output)");
     if (args.in_fname != "-" && args.output == "") args.output = args.in_fname;
     if (args.parse_only && args.pfbwt_only) die("cannot simulatneously do parse_only and pfbwt_only");
+    if (args.doc_array) {
+        args.print_docs = 1;
+        if (!args.sa && !args.rssa) { fprintf(stderr, "--doc-array needs the suffix array (-s or -r)\n"); exit(1); }
+    }
     return args;
 }
 
@@ -189,6 +195,7 @@ int main(int argc, char **argv) {
                 { SubTimer t2("BWT on device"); if (pfb_build_bwt(ctx, args.sa, args.rssa)) die_ctx(ctx); }
                 SubTimer t3("writing BWT files");
                 if (pfb_write_bwt(ctx, args.output.c_str(), args.sa, args.rssa, args.stdout_ext.empty() ? NULL : args.stdout_ext.c_str())) die_ctx(ctx);
+                if (args.doc_array && pfb_write_doc_array(ctx, args.output.c_str())) die_ctx(ctx);
             }
         }
         pfb_sizes sz;

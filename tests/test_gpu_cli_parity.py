@@ -275,3 +275,23 @@ def test_cli_bucketed_build(env, ref_bins, datadir):
         lb = [l for l in r.stderr.splitlines() if l.startswith(key)]
         if la:
             assert la == lb, (la, lb)
+
+
+def test_cli_doc_array(ref_bins, datadir):
+    """--doc-array: <o>.da[i] = index of the record holding SA[i]; checked against the reference's own .sa and
+    .docs of the same input (numpy searchsorted), through --pfbwt-only too (docs loaded from <o>.docs)"""
+    if not ref_bins["pfbwt-f"]:
+        pytest.skip("reference binaries not built")
+    recs = pangenome_records(50_000, 5, 50, 61) + [("tiny", random_bases(3, 9)), ("tail", random_bases(20_000, 10))]
+    fa = os.path.join(datadir, "da.fa")
+    write_fasta(fa, recs, line_width=60)
+    a, b = os.path.join(datadir, "da.ref"), os.path.join(datadir, "da.gpu")
+    run([ref_bins["pfbwt-f"], "-s", "--print-docs", "-o", a, fa])
+    run([os.path.join(BIN, "pfbwt-f"), "-s", "--doc-array", "-o", b, fa])
+    assert_same_files(a, b, ["sa", "docs", "bwt"])
+    sa = np.fromfile(a + ".sa", dtype=np.uint32).astype(np.int64)
+    starts = np.array([int(l.split()[-1]) for l in open(a + ".docs")], dtype=np.int64)
+    want = (np.searchsorted(starts, sa, side="right") - 1).astype(np.uint32)
+    got = np.fromfile(b + ".da", dtype=np.uint32)
+    assert np.array_equal(want, got)
+    assert got.max() == len(recs) - 1 and got[0] == len(recs) - 1
