@@ -389,20 +389,75 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
                 kp[a] = (gid << (6 + ebits)) | (e.code << 6) | ((u64)e.consumed << 1) | (e.closed ? 1ull : 0ull);
             });
         }
-        sort_pairs(k2, k2b, v, vb, m, kshift, kbits + gbits, ws.sc, st);
+        // Order every group by its members' keys.  Tie groups are SMALL where this loop matters (a pangenome dictionary: the
+        // variants of one phrase, a handful of members, but 10^8 of them), so a radix sort of the whole list - six passes
+        // over (key, value) pairs - is the wrong tool: every member of a group of at most SMALL_GROUP members ranks itself by
+        // counting the smaller keys of its group (one pass, the group's keys come from L1/L2).  Larger groups (poly-A runs,
+        // tandem repeats) are compacted and take the radix sort as before.
+        DevBuf<u8> hl(m);                                       // 1 = first, 2 = last member with its key inside the group
+        {
+            static const u32 SMALL_GROUP = getenv("PFB_SMALL_GROUP") ? (u32)atoi(getenv("PFB_SMALL_GROUP")) : 48u;   // test knob: 0 = radix sort only
+            DevBuf<u32> hslot2(G + 1);
+            DevBuf<u8> bigf(m);
+            {
+                const u8 *a_ = ah.get(); const u32 *gi = gidx.get(); u32 *hs = hslot2.get();
+                const u32 m32 = (u32)m; const u64 G_ = G;
+                launch_for(m + 1, st, PFB_LAMBDA(u64 a) { if (a == m32) hs[G_] = m32; else if (a_[a]) hs[gi[a]] = (u32)a; });
+                const u64 *kp = k2.get(); const u32 *vp = v.get(); u64 *ko = k2b.get(); u32 *vo = vb.get(); u8 *hp = hl.get(); u8 *bf = bigf.get();
+                const u32 cap = SMALL_GROUP;
+                launch_for(m, st, PFB_LAMBDA(u64 a) {
+                    const u64 gid = (u64)gi[a] + a_[a] - 1;
+                    const u32 s = hs[gid], e = hs[gid + 1];
+                    if (e - s > cap) { bf[a] = 1; return; }
+                    bf[a] = 0;
+                    const u64 mine = kp[a] >> kshift;
+                    u32 less = 0, eqb = 0, eqa = 0;
+                    for (u32 j = s; j < e; ++j) {
+                        const u64 o = kp[j] >> kshift;
+                        less += o < mine ? 1u : 0u;
+                        if (o == mine) { if (j < (u32)a) ++eqb; else if (j > (u32)a) ++eqa; }
+                    }
+                    const u32 dest = s + less + eqb;               // stable: equal keys keep their order
+                    ko[dest] = kp[a]; vo[dest] = vp[a];
+                    hp[dest] = (u8)((eqb == 0 ? 1 : 0) | (eqa == 0 ? 2 : 0));
+                });
+            }
+            DevBuf<u32> bscratch, bslots;
+            const u64 mb = compact_indices(bigf.get(), m, bscratch, bslots, ws);
+            if (mb) {
+                DevBuf<u64> bk(mb), bkb(mb);
+                DevBuf<u32> bv(mb), bvb(mb);
+                {
+                    const u32 *bs = bslots.get(); const u64 *kp = k2.get(); const u32 *vp = v.get(); u64 *bkp = bk.get(); u32 *bvp = bv.get();
+                    launch_for(mb, st, PFB_LAMBDA(u64 i) { bkp[i] = kp[bs[i]]; bvp[i] = vp[bs[i]]; });
+                }
+                sort_pairs(bk, bkb, bv, bvb, mb, kshift, kbits + gbits, ws.sc, st);
+                {
+                    // whole groups were taken and the group id leads the key: the i-th sorted pair belongs into the i-th slot
+                    const u32 *bs = bslots.get(); const u64 *bkp = bk.get(); const u32 *bvp = bv.get(); u64 *ko = k2b.get(); u32 *vo = vb.get(); u8 *hp = hl.get();
+                    launch_for(mb, st, PFB_LAMBDA(u64 i) {
+                        const u64 k = bkp[i] >> kshift;
+                        const bool head = i == 0 || k != (bkp[i - 1] >> kshift);
+                        const bool last = i + 1 == mb || k != (bkp[i + 1] >> kshift);
+                        const u32 dest = bs[i];
+                        ko[dest] = bkp[i]; vo[dest] = bvp[i];
+                        hp[dest] = (u8)((head ? 1 : 0) | (last ? 2 : 0));
+                    });
+                }
+            }
+            k2.swap(k2b); v.swap(vb);
+        }
         if (pivot) {
             ++pivot_rounds;
             if ((u64)read_scalar(clamped.get(), st) * 8 > m) pivot_ok = false;      // mostly self-overlapping repeats
         }
         DevBuf<u8> act2(m);
         {
-            const u32 *ap = apos.get(); const u64 *kp = k2.get(); const u32 *vp = v.get();
+            const u32 *ap = apos.get(); const u64 *kp = k2.get(); const u32 *vp = v.get(); const u8 *hp = hl.get();
             u32 *sp = sa.get(); u8 *ac = act2.get(); u32 *dp = adep.get(); u32 *cp = cnt.get();
             const WordLookup w3 = wl; const u64 w64 = (u64)w; const int lbw = lb;
             launch_for(m, st, PFB_LAMBDA(u64 a) {
-                u64 k = kp[a] >> kshift;
-                bool head = a == 0 || k != (kp[a - 1] >> kshift);
-                bool last = a + 1 == m || k != (kp[a + 1] >> kshift);
+                const bool head = hp[a] & 1, last = (hp[a] & 2) != 0;
                 u32 j = ap[a];
                 sp[j] = vp[a];
                 u32 c, ib, sl;

@@ -136,7 +136,9 @@ def fuzz_case(seed):
 
 FUZZ_KNOBS = [{}, {"PFB_PIVOT": "1", "PFB_KEY_SYMS": "3"}, {"PFB_PIVOT": "0", "PFB_KEY_SYMS": "3"}, {"PFB_EXT_ROUNDS": "0"},
               {"PFB_EXT_ROUNDS": "100", "PFB_PIVOT": "0"}, {"PFB_HARD_LIMITS": "2,4"}, {"PFB_KEY_COUNT_BITS": "0"},
-              {"PFB_KEY_COUNT_BITS": "2", "PFB_PIVOT": "1", "PFB_KEY_SYMS": "5"}]
+              {"PFB_KEY_COUNT_BITS": "2", "PFB_PIVOT": "1", "PFB_KEY_SYMS": "5"},
+              {"PFB_SMALL_GROUP": "0", "PFB_PIVOT": "1", "PFB_KEY_SYMS": "4"}, {"PFB_SMALL_GROUP": "3", "PFB_KEY_SYMS": "3"},
+              {"PFB_SMALL_GROUP": "2", "PFB_PIVOT": "1", "PFB_KEY_SYMS": "2"}]
 
 
 @pytest.mark.parametrize("block", range(5))
