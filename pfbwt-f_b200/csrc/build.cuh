@@ -90,6 +90,21 @@ PFB_HD inline u64 pivot_key(const u8 *dict, u64 D, u64 a, u64 p, int lb, const R
     u64 l = 0;
     // 8 symbols per step while both windows (and the second aligned word behind them) lie inside the dictionary
     const u64 hi = a > p ? a : p;
+    // four 8-symbol steps at a time while nothing happens in them (all loads of a step are independent: the comparison is
+    // bound by memory latency, variants of a phrase agree for tens of symbols); the exact step loop below takes over at the
+    // first difference, terminator or candidate run
+    while (l + 32 <= cap && hi + l + 40 <= D) {
+        u64 acc = 0;
+        u64 x0 = 0;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const u64 x = load8_unaligned(dict, a + l + 8 * c), y = load8_unaligned(dict, p + l + 8 * c);
+            if (c == 0) x0 = x;
+            acc |= (x ^ y) | ((x - 0x0202020202020202ull) & ~x & 0x8080808080808080ull);
+        }
+        if (acc || (rt.R && x0 == (x0 & 0xffull) * 0x0101010101010101ull)) break;
+        l += 32;
+    }
     while (l + 8 <= cap && hi + l + 16 <= D) {
         const u64 x = load8_unaligned(dict, a + l), y = load8_unaligned(dict, p + l);
         const u64 d = x ^ y;
@@ -342,6 +357,7 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
             launch_for(m, st, PFB_LAMBDA(u64 a) { a_[a] = (mt[ap[a]] & M_HEAD) ? 1 : 0; });
         }
         u64 G = scan_flags(ah.get(), gidx.get(), m, ws);
+        timer.lap("K6 round: group ids");
         int gbits = bits_for(G ? G - 1 : 0);
         int L2 = KEY_MAX_SYMS;
         while (L2 > 0 && 6 + enum_bits(L2) + gbits > 64) --L2;
@@ -349,6 +365,14 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
         const int ebits = enum_bits(L2);
         DevBuf<u64> k2(m), k2b(m);
         DevBuf<u32> v(m), vb(m);
+        // what travels with a suffix (occurrence count, preceding-byte code, valid / full bits) is gathered once and follows
+        // the permutation of the small groups instead of being looked up again (position -> word) after every round
+        DevBuf<u32> tcnt(m), srcslot(m);
+        DevBuf<u8> tmeta(m);
+        {
+            const u32 *ap = apos.get(); const u32 *cp = cnt.get(); u32 *tc = tcnt.get(); u8 *tm_ = tmeta.get();
+            launch_for(m, st, PFB_LAMBDA(u64 a) { const u32 j = ap[a]; tc[a] = cp[j]; tm_[a] = mt[j]; });
+        }
         if (pivot && !have_rt) {
             u32 R = 0; u64 longest = 0;
             build_run_table(dict, D, run_s, run_e, &R, &longest, ws);
@@ -389,6 +413,7 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
                 kp[a] = (gid << (6 + ebits)) | (e.code << 6) | ((u64)e.consumed << 1) | (e.closed ? 1ull : 0ull);
             });
         }
+        timer.lap(pivot ? "K6 round: pivot keys" : "K6 round: window keys");
         // Order every group by its members' keys.  Tie groups are SMALL where this loop matters (a pangenome dictionary: the
         // variants of one phrase, a handful of members, but 10^8 of them), so a radix sort of the whole list - six passes
         // over (key, value) pairs - is the wrong tool: every member of a group of at most SMALL_GROUP members ranks itself by
@@ -404,6 +429,7 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
                 const u32 m32 = (u32)m; const u64 G_ = G;
                 launch_for(m + 1, st, PFB_LAMBDA(u64 a) { if (a == m32) hs[G_] = m32; else if (a_[a]) hs[gi[a]] = (u32)a; });
                 const u64 *kp = k2.get(); const u32 *vp = v.get(); u64 *ko = k2b.get(); u32 *vo = vb.get(); u8 *hp = hl.get(); u8 *bf = bigf.get();
+                u32 *srcp = srcslot.get();
                 const u32 cap = SMALL_GROUP;
                 launch_for(m, st, PFB_LAMBDA(u64 a) {
                     const u64 gid = (u64)gi[a] + a_[a] - 1;
@@ -418,10 +444,11 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
                         if (o == mine) { if (j < (u32)a) ++eqb; else if (j > (u32)a) ++eqa; }
                     }
                     const u32 dest = s + less + eqb;               // stable: equal keys keep their order
-                    ko[dest] = kp[a]; vo[dest] = vp[a];
+                    ko[dest] = kp[a]; vo[dest] = vp[a]; srcp[dest] = (u32)a;
                     hp[dest] = (u8)((eqb == 0 ? 1 : 0) | (eqa == 0 ? 2 : 0));
                 });
             }
+            timer.lap("K6 round: rank inside small groups");
             DevBuf<u32> bscratch, bslots;
             const u64 mb = compact_indices(bigf.get(), m, bscratch, bslots, ws);
             if (mb) {
@@ -435,17 +462,19 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
                 {
                     // whole groups were taken and the group id leads the key: the i-th sorted pair belongs into the i-th slot
                     const u32 *bs = bslots.get(); const u64 *bkp = bk.get(); const u32 *bvp = bv.get(); u64 *ko = k2b.get(); u32 *vo = vb.get(); u8 *hp = hl.get();
+                    u32 *srcp = srcslot.get();
                     launch_for(mb, st, PFB_LAMBDA(u64 i) {
                         const u64 k = bkp[i] >> kshift;
                         const bool head = i == 0 || k != (bkp[i - 1] >> kshift);
                         const bool last = i + 1 == mb || k != (bkp[i + 1] >> kshift);
                         const u32 dest = bs[i];
-                        ko[dest] = bkp[i]; vo[dest] = bvp[i];
+                        ko[dest] = bkp[i]; vo[dest] = bvp[i]; srcp[dest] = 0xFFFFFFFFu;      // the sort does not say where a pair came from: looked up again
                         hp[dest] = (u8)((head ? 1 : 0) | (last ? 2 : 0));
                     });
                 }
             }
             k2.swap(k2b); v.swap(vb);
+            timer.lap("K6 round: large groups (radix sort)");
         }
         if (pivot) {
             ++pivot_rounds;
@@ -456,18 +485,22 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
             const u32 *ap = apos.get(); const u64 *kp = k2.get(); const u32 *vp = v.get(); const u8 *hp = hl.get();
             u32 *sp = sa.get(); u8 *ac = act2.get(); u32 *dp = adep.get(); u32 *cp = cnt.get();
             const WordLookup w3 = wl; const u64 w64 = (u64)w; const int lbw = lb;
+            const u32 *srcp = srcslot.get(); const u32 *tc = tcnt.get(); const u8 *tm_ = tmeta.get();
             launch_for(m, st, PFB_LAMBDA(u64 a) {
                 const bool head = hp[a] & 1, last = (hp[a] & 2) != 0;
                 u32 j = ap[a];
                 sp[j] = vp[a];
-                u32 c, ib, sl;
-                u32 vf = suffix_class(w3, vp[a], w64, c, ib, sl);         // what travels with the suffix: count, valid/full bits,
-                cp[j] = c;                                                 // and the preceding-byte code
-                mt[j] = (u8)(prev_code(dict, vp[a]) | (head ? M_HEAD : 0) | vf);
+                const u32 from = srcp[a];
+                u32 c, mb_;                                                // what travels with the suffix: count, valid/full bits,
+                if (from != 0xFFFFFFFFu) { c = tc[from]; mb_ = tm_[from] & (u32)(0x0f | M_VALID | M_FULL); }      // and the preceding-byte code
+                else { u32 ib, sl; const u32 vf = suffix_class(w3, vp[a], w64, c, ib, sl); mb_ = (u32)prev_code(dict, vp[a]) | vf; }
+                cp[j] = c;
+                mt[j] = (u8)(mb_ | (head ? M_HEAD : 0));
                 dp[a] += pivot ? pivot_consumed(kp[a], lbw) : ((u32)(kp[a] >> 1) & 31u);   // slot a stays inside its old group: same depth so far
                 ac[a] = (!(head && last) && !(kp[a] & 1)) ? 1 : 0;
             });
         }
+        timer.lap("K6 round: write back + classify");
         DevBuf<u32> scratch, sel, apos2, adep2;
         u64 m2 = compact_indices(act2.get(), m, scratch, sel, ws);
         apos2.alloc(m2); adep2.alloc(m2);
@@ -479,7 +512,7 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
         adep = std::move(adep2);
         m = m2;
         ++rounds;
-        timer.lap(pivot ? "K6 pivot round" : "K6 extension round");
+        timer.lap(pivot ? "K6 round: compact open list (pivot round ends)" : "K6 round: compact open list (extension round ends)");
     }
     if (m && sh) { err = "dictionary repeats too long for the range-partitioned suffix sort (use the single-GPU path)"; return PFB_ERR_LIMIT; }
     if (m) {
