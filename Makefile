@@ -10,7 +10,7 @@ BIN    := bin
 
 all: $(LIB) $(BIN)/pfbwt-f $(BIN)/pfbwt-f64 $(BIN)/merge_pfp $(BIN)/shim_demo $(BIN)/shim_demo64 emu
 
-$(LIB): $(CSRC)/capi.cu $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/build.cuh $(CSRC)/dictkeys.cuh $(CSRC)/emit.cuh $(CSRC)/radix.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp $(CSRC)/comm.hpp $(CSRC)/shard.inl $(CSRC)/ingest.cuh $(CSRC)/devio.cuh $(CSRC)/parsekernels.cuh include/pfbwt_b200.h
+$(LIB): $(CSRC)/capi.cu $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/build.cuh $(CSRC)/dictkeys.cuh $(CSRC)/emit.cuh $(CSRC)/radix.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp $(CSRC)/comm.hpp $(CSRC)/shard.inl $(CSRC)/ingest.cuh $(CSRC)/devio.cuh $(CSRC)/parsekernels.cuh $(CSRC)/scan.cuh include/pfbwt_b200.h
 	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/capi.cu -lz -lcudart -ldl -lpthread
 
 $(BIN)/pfbwt-f: pfbwt-f_b200/src/pfbwt-f.cpp $(LIB)
@@ -35,7 +35,7 @@ $(BIN)/shim_demo64: tests/shim/shim_main.cpp include/pfbwtf_shim.hpp $(LIB)
 emu: tests/emu/pfb_emu tests/emu/libpfb_emu.so
 tests/emu/libpfb_emu.so: tests/emu/pfb_emu
 	$(CXX) -std=c++17 -O2 -Wall -Wno-unused -shared -fPIC -I $(CSRC) -o $@ tests/emu/emu_main.cpp -lz
-tests/emu/pfb_emu: tests/emu/emu_main.cpp $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/build.cuh $(CSRC)/dictkeys.cuh $(CSRC)/emit.cuh $(CSRC)/radix.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp $(CSRC)/comm.hpp $(CSRC)/shard.inl $(CSRC)/ingest.cuh $(CSRC)/devio.cuh $(CSRC)/parsekernels.cuh
+tests/emu/pfb_emu: tests/emu/emu_main.cpp $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/build.cuh $(CSRC)/dictkeys.cuh $(CSRC)/emit.cuh $(CSRC)/radix.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp $(CSRC)/comm.hpp $(CSRC)/shard.inl $(CSRC)/ingest.cuh $(CSRC)/devio.cuh $(CSRC)/parsekernels.cuh $(CSRC)/scan.cuh
 	$(CXX) -std=c++17 -O2 -Wall -Wno-unused -I $(CSRC) -o $@ $< -lz
 
 oracle:

@@ -866,9 +866,10 @@ inline int parse_bwt(DeviceParse &pp, const Params &prm, Workspace &ws, StageTim
     pp.bwsai.alloc(m);
     pp.ilist.alloc(m);
     {
-        DevBuf<u32> bwtp(m), bwtp_b(m), il_b(m);
+        DevBuf<u64> bwtp(m), bwtp_b(m);          // 64-bit keys: the onesweep sort of radix.cuh takes (u64, u32) pairs
+        DevBuf<u32> il_b(m);
         const u32 *sp = sa.get(); const u32 *R = pp.parse.get(); const u8 *last = pp.last.get(); const u64 *sai = pp.sai.get();
-        u8 *bl = pp.bwlast.get(); u64 *bs = pp.bwsai.get(); u32 *bp = bwtp.get(); u32 *il = pp.ilist.get();
+        u8 *bl = pp.bwlast.get(); u64 *bs = pp.bwsai.get(); u64 *bp = bwtp.get(); u32 *il = pp.ilist.get();
         launch_for(m, st, PFB_LAMBDA(u64 i) {     // include/pfparser.hpp:429-451
             u64 s = sp[i];
             il[i] = (u32)i;

@@ -35,7 +35,6 @@ typedef int pfbStream_t;
 #else
 // -------------------------------------------------------------------- CUDA --
 #include <cuda_runtime.h>
-#include <cub/cub.cuh>
 #include <map>
 #include <mutex>
 #include <unordered_map>
@@ -359,11 +358,15 @@ typedef uint32_t u32;
 typedef uint64_t u64;
 }  // namespace pfb
 #include "radix.cuh"
+#ifndef PFB_EMU
+#include "scan.cuh"
+#endif
 namespace pfb {
 
 // ------------------------------------------------------------------- scans --
 struct Scratch {
     DevBuf<uint8_t> buf;
+    DevBuf<uint8_t> scanbuf;     // status words of the look-back scans
 #ifndef PFB_EMU
     RadixWork rw;
 #endif
@@ -389,12 +392,7 @@ inline void exclusive_sum(const TIn *in, TOut *out, uint64_t n, Scratch &sc, pfb
     TOut acc = 0;
     for (uint64_t i = 0; i < n; ++i) { TOut v = (TOut)in[i]; out[i] = acc; acc += v; }
 #else
-    auto it = cub::TransformInputIterator<TOut, CastOp<TIn, TOut>, const TIn *>(in, CastOp<TIn, TOut>());
-    size_t bytes = 0;
-    PFB_CUDA_CHECK(cub::DeviceScan::ExclusiveSum(nullptr, bytes, it, out, (int64_t)n, s));
-    void *tmp = sc.ensure(bytes);
-    PFB_CUDA_CHECK(cub::DeviceScan::ExclusiveSum(tmp, bytes, it, out, (int64_t)n, s));
-    launch_stats().lib += 2;
+    device_scan<TIn, TOut, false, false>(in, out, n, sc.scanbuf, s);          // scan.cuh: single pass, decoupled look-back
 #endif
 }
 template <class T>
@@ -405,11 +403,7 @@ inline void inclusive_max(const T *in, T *out, uint64_t n, Scratch &sc, pfbStrea
     T acc = in[0];
     for (uint64_t i = 0; i < n; ++i) { acc = in[i] > acc ? in[i] : acc; out[i] = acc; }
 #else
-    size_t bytes = 0;
-    PFB_CUDA_CHECK(cub::DeviceScan::InclusiveScan(nullptr, bytes, in, out, MaxOp(), (int64_t)n, s));
-    void *tmp = sc.ensure(bytes);
-    PFB_CUDA_CHECK(cub::DeviceScan::InclusiveScan(tmp, bytes, in, out, MaxOp(), (int64_t)n, s));
-    launch_stats().lib += 2;
+    device_scan<T, T, true, true>(in, out, n, sc.scanbuf, s);
 #endif
 }
 
@@ -422,36 +416,35 @@ inline TOut reduce_sum(const TIn *in, uint64_t n, Scratch &sc, pfbStream_t s) {
     for (uint64_t i = 0; i < n; ++i) acc += (TOut)in[i];
     return acc;
 #else
-    auto it = cub::TransformInputIterator<TOut, CastOp<TIn, TOut>, const TIn *>(in, CastOp<TIn, TOut>());
-    DevBuf<TOut> out(1);
-    size_t bytes = 0;
-    PFB_CUDA_CHECK(cub::DeviceReduce::Sum(nullptr, bytes, it, out.get(), (int64_t)n, s));
-    void *tmp = sc.ensure(bytes);
-    PFB_CUDA_CHECK(cub::DeviceReduce::Sum(tmp, bytes, it, out.get(), (int64_t)n, s));
-    launch_stats().lib += 2;
-    return read_scalar(out.get(), s);
+    (void)sc;
+    DevBuf<unsigned long long> out(1);
+    PFB_CUDA_CHECK(cudaMemsetAsync(out.get(), 0, 8, s));
+    uint64_t blocks = (n + 256 * 16 - 1) / (256 * 16);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    k_reduce_sum<TIn><<<(unsigned)blocks, 256, 0, s>>>(in, n, out.get());
+    PFB_CUDA_CHECK(cudaGetLastError());
+    launch_stats().own++;
+    return (TOut)read_scalar(out.get(), s);
 #endif
 }
 
 // ------------------------------------------------------------- radix sorts --
 // Stable LSD radix sort of (key,value) pairs on key bits [begin_bit,end_bit).
 // Result is left in keys_a/vals_a (buffers may be swapped internally).
-// (u64,u32) pairs go through the hand-written onesweep sort of radix.cuh; PFB_SORT=cub selects the
-// library sort for A/B timing.  iota_vals: input values are 0..n-1 (vals_a need not be initialised);
+// Pairs go through the hand-written onesweep sort of radix.cuh (the emulator uses std::stable_sort).  iota_vals: input values are 0..n-1 (vals_a need not be initialised);
 // hist0: device histogram of the first 8-bit digit when the caller already has it.
 template <class K, class V>
 inline void sort_pairs(DevBuf<K> &keys_a, DevBuf<K> &keys_b, DevBuf<V> &vals_a, DevBuf<V> &vals_b, uint64_t n,
                        int begin_bit, int end_bit, Scratch &sc, pfbStream_t s, bool iota_vals = false, const uint64_t *hist0 = nullptr) {
 #ifndef PFB_EMU
-    if constexpr (sizeof(K) == 8 && sizeof(V) == 4) {
-        static const bool use_cub = getenv("PFB_SORT") && !strcmp(getenv("PFB_SORT"), "cub");
-        if (!use_cub) { radix_sort_pairs(keys_a, keys_b, vals_a, vals_b, n, begin_bit, end_bit, iota_vals, hist0, sc.rw, s); return; }
-    }
-#endif
+    // the product build sorts (u64 key, u32 value) pairs only, with the hand-written onesweep sort of radix.cuh
+    static_assert(sizeof(K) == 8 && sizeof(V) == 4, "sort_pairs: (u64, u32) pairs only");
+    radix_sort_pairs(keys_a, keys_b, vals_a, vals_b, n, begin_bit, end_bit, iota_vals, hist0, sc.rw, s);
+    return;
+#else
     if (iota_vals && n) { V *v = vals_a.get(); launch_for(n, s, PFB_LAMBDA(uint64_t i) { v[i] = (V)i; }); }
     if (n <= 1) return;
     if (end_bit <= begin_bit) return;
-#ifdef PFB_EMU
     (void)sc; (void)s; (void)keys_b; (void)vals_b;
     std::vector<uint64_t> perm(n);
     std::iota(perm.begin(), perm.end(), 0);
@@ -463,16 +456,6 @@ inline void sort_pairs(DevBuf<K> &keys_a, DevBuf<K> &keys_b, DevBuf<V> &vals_a, 
     std::vector<K> k2(n); std::vector<V> v2(n);
     for (uint64_t i = 0; i < n; ++i) { k2[i] = kp[perm[i]]; v2[i] = vp[perm[i]]; }
     memcpy(kp, k2.data(), n * sizeof(K)); memcpy(vp, v2.data(), n * sizeof(V));
-#else
-    cub::DoubleBuffer<K> dk(keys_a.get(), keys_b.get());
-    cub::DoubleBuffer<V> dv(vals_a.get(), vals_b.get());
-    size_t bytes = 0;
-    PFB_CUDA_CHECK(cub::DeviceRadixSort::SortPairs(nullptr, bytes, dk, dv, (int64_t)n, begin_bit, end_bit, s));
-    void *tmp = sc.ensure(bytes);
-    PFB_CUDA_CHECK(cub::DeviceRadixSort::SortPairs(tmp, bytes, dk, dv, (int64_t)n, begin_bit, end_bit, s));
-    launch_stats().lib += 1 + (uint64_t)((end_bit - begin_bit + 7) / 8);
-    if (dk.Current() != keys_a.get()) keys_a.swap(keys_b);
-    if (dv.Current() != vals_a.get()) vals_a.swap(vals_b);
 #endif
 }
 
