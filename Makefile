@@ -34,9 +34,9 @@ $(BIN)/shim_demo64: tests/shim/shim_main.cpp include/pfbwtf_shim.hpp $(LIB)
 # developer logic check (tests only; see tests/emu/emu_main.cpp)
 emu: tests/emu/pfb_emu tests/emu/libpfb_emu.so
 tests/emu/libpfb_emu.so: tests/emu/pfb_emu
-	$(CXX) -std=c++17 -O2 -Wall -Wno-unused -shared -fPIC -I $(CSRC) -o $@ tests/emu/emu_main.cpp -lz
+	$(CXX) -std=c++17 -O2 -Wall -Wno-unused -shared -fPIC -I $(CSRC) -o $@ tests/emu/emu_main.cpp -lz -pthread
 tests/emu/pfb_emu: tests/emu/emu_main.cpp $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/build.cuh $(CSRC)/dictkeys.cuh $(CSRC)/emit.cuh $(CSRC)/radix.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp $(CSRC)/comm.hpp $(CSRC)/shard.inl $(CSRC)/ingest.cuh $(CSRC)/devio.cuh $(CSRC)/parsekernels.cuh $(CSRC)/scan.cuh
-	$(CXX) -std=c++17 -O2 -Wall -Wno-unused -I $(CSRC) -o $@ $< -lz
+	$(CXX) -std=c++17 -O2 -Wall -Wno-unused -I $(CSRC) -o $@ $< -lz -pthread
 
 oracle:
 	$(MAKE) -C oracle all

@@ -122,6 +122,11 @@ int pfb_append(pfb_ctx *lhs, pfb_ctx *rhs);
  * with_parse_bwt: 0 = .dict .occ .parse .n (.docs); 1 = those + .bwlast .ilist (.bwsai with with_sai);
  * 2 = only .bwlast .ilist (.bwsai) - run_parser's third task, after the parse files were saved in its second */
 int pfb_save_parse(pfb_ctx *, const char *prefix, int with_parse_bwt, int with_sai);
+/* pfb_save_parse in the background: the files are written by a writer thread (own pinned staging, own copy streams) while
+ * the caller goes on with pfb_parse_bwt / pfb_build_bwt / pfb_write_bwt on the same context.  pfb_wait_saves joins the
+ * writers and returns their first error; everything that replaces the parse waits by itself. */
+int pfb_save_parse_async(pfb_ctx *, const char *prefix, int with_parse_bwt, int with_sai);
+int pfb_wait_saves(pfb_ctx *);
 /* <prefix>.last (n_phrases bytes, PfParser::last_) and <prefix>.sai (n_phrases x bits/8, PfParser::sai_): the extensions
  * include/utils.h:22,24 defines; the reference never writes them (only tests/test_parser.cpp:126,139 reads them), so they
  * are written on request only */

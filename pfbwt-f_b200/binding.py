@@ -17,7 +17,7 @@ EXPORTS = [
     "pfb_copy_bwt", "pfb_copy_sa", "pfb_copy_ssa", "pfb_copy_esa", "pfb_get_docs", "pfb_upload_text",
     "pfb_run_resident", "pfb_release_text", "pfb_clear",
     "pfb_nccl_unique_id", "pfb_shard_init_nccl", "pfb_shard_init_host", "pfb_get_shard_info", "pfb_get_pending_bases",
-    "pfb_kat_trigger", "pfb_add_chunk", "pfb_add_fasta_range", "pfb_save_last_sai", "pfb_build_bwt_to_files", "pfb_build_workspace_bytes", "pfb_write_doc_array", "pfb_device_free_bytes",
+    "pfb_kat_trigger", "pfb_add_chunk", "pfb_add_fasta_range", "pfb_save_last_sai", "pfb_build_bwt_to_files", "pfb_build_workspace_bytes", "pfb_write_doc_array", "pfb_device_free_bytes", "pfb_save_parse_async", "pfb_wait_saves",
 ]
 
 
@@ -83,6 +83,8 @@ def load():
     lib.pfb_save_parse.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
     lib.pfb_load_parse.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
     lib.pfb_save_last_sai.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
+    lib.pfb_save_parse_async.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
+    lib.pfb_wait_saves.argtypes = [vp]
     lib.pfb_build_bwt.argtypes = [vp, C.c_int, C.c_int]
     lib.pfb_run_resident.argtypes = [vp, C.c_int, C.c_int]
     lib.pfb_build_bwt_to_files.argtypes = [vp, C.c_char_p, C.c_int, C.c_int, C.c_uint64]
@@ -202,6 +204,12 @@ class Context:
 
     def save_parser(self, prefix, with_parse_bwt=False, with_sai=False):
         self._ck(self.lib.pfb_save_parse(self.h, prefix.encode(), int(with_parse_bwt), int(with_sai)))
+
+    def save_parser_async(self, prefix, with_parse_bwt=0, with_sai=False):
+        self._ck(self.lib.pfb_save_parse_async(self.h, prefix.encode(), int(with_parse_bwt), int(with_sai)))
+
+    def wait_saves(self):
+        self._ck(self.lib.pfb_wait_saves(self.h))
 
     def save_last_sai(self, prefix, with_last=True, with_sai=True):
         self._ck(self.lib.pfb_save_last_sai(self.h, prefix.encode(), int(with_last), int(with_sai)))

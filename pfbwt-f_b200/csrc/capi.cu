@@ -154,6 +154,12 @@ int pfb_save_parse(pfb_ctx *c, const char *prefix, int with_parse_bwt, int with_
     if (!prefix) return c->eng.fail(PFB_ERR_ARG, "null prefix");
     return c->eng.save_parse(prefix, with_parse_bwt != 0, with_sai != 0, with_parse_bwt == 2);
 }
+int pfb_save_parse_async(pfb_ctx *c, const char *prefix, int with_parse_bwt, int with_sai) {
+    CTX_GUARD(c);
+    if (!prefix) return c->eng.fail(PFB_ERR_ARG, "null prefix");
+    return c->eng.save_parse_async(prefix, with_parse_bwt, with_sai != 0);
+}
+int pfb_wait_saves(pfb_ctx *c) { CTX_GUARD(c); return c->eng.wait_saves(); }
 int pfb_save_last_sai(pfb_ctx *c, const char *prefix, int with_last, int with_sai) {
     CTX_GUARD(c);
     if (!prefix) return c->eng.fail(PFB_ERR_ARG, "null prefix");

@@ -34,15 +34,16 @@ struct DevIoPool {
         return true;
     }
 };
-inline DevIoPool &devio_pool() { static DevIoPool p; return p; }
+// one pool per thread: the background writer of the parse files (engine.hpp) and the pipeline thread copy at the same time
+inline DevIoPool &devio_pool() { static thread_local DevIoPool p; return p; }
 #endif
 
 // Writes `bytes` bytes of device memory at `off` of the file.  whole = true: the file is created/truncated and
 // holds exactly these bytes; false: the file is sized to final_size and other writers (ranks of a multi-GPU job)
 // fill the rest.  The producing stream `st` is synchronised first.
 inline int write_dev_file(const std::string &path, const void *dptr, size_t bytes, u64 off, u64 final_size, bool whole, int device,
-                          pfbStream_t st, std::string &err) {
-    stream_sync(st);
+                          pfbStream_t st, std::string &err, bool sync_producer = true) {
+    if (sync_producer) stream_sync(st);
     int fd = open(path.c_str(), whole ? (O_CREAT | O_WRONLY | O_TRUNC) : (O_CREAT | O_WRONLY), 0644);
     if (fd < 0) { err = "could not open " + path + " for writing"; return -1; }
     if (!whole && ftruncate(fd, (off_t)final_size) != 0) { close(fd); err = "could not size " + path; return -1; }

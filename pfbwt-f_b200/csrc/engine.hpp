@@ -12,6 +12,7 @@
 #include "ingest.cuh"
 #include "devio.cuh"
 #include <memory>
+#include <thread>
 
 
 namespace pfb {
@@ -55,6 +56,7 @@ struct Engine {
     u64 shard_start = 0;             // offset of this rank's records in S
 
     int fail(int rc, const std::string &m) { err = m; last_rc = rc; return rc; }
+    ~Engine() { wait_saves(); }
 
     // ---- ingestion -----------------------------------------------------------
     void push_host_segment(size_t off, u64 len) {
@@ -209,6 +211,7 @@ struct Engine {
     }
 
     void clear() {
+        wait_saves();
         segs.clear(); raw.n = 0; pending_n = 0; docs = FastaResult(); input_released = false; chunk_open = false;
         text.buf.release(); text.n = 0;
         parse = DeviceParse(); bwt = DeviceBwt();
@@ -267,7 +270,7 @@ struct Engine {
             return PFB_OK;
         } catch (const Error &e) { return fail(e.code, e.what()); }
     }
-    int finalize() { return comm ? shard_parse() : parse_device(); }      // collective when a communicator is attached
+    int finalize() { wait_saves(); return comm ? shard_parse() : parse_device(); }      // collective when a communicator is attached
 
     int do_parse_bwt() {
         try {
@@ -469,9 +472,84 @@ struct Engine {
         } catch (const Error &e) { return fail(e.code, e.what()); }
     }
 
+    // ---- the same files written in the background: the GB-sized parse files leave through a writer thread (own pinned
+    // staging buffers and copy streams, devio.cuh) while the device goes on with the parse BWT and the BWT build - file
+    // writing, not the device, is what a file-to-file run waits for.  The arrays written are those of `parse`, which stay
+    // untouched until wait_saves() (called by everything that replaces the parse).
+    struct SaveJob {
+        struct Item { std::string path; const void *d = nullptr; size_t bytes = 0; };
+        std::vector<Item> items;
+        std::vector<DevBuf<u8>> held;        // width-converted images
+        std::thread th;
+        std::string err;
+        int rc = 0;
+    };
+    std::vector<std::unique_ptr<SaveJob>> save_jobs;
+    int wait_saves() {
+        int rc = PFB_OK;
+        for (auto &j : save_jobs) {
+            if (j->th.joinable()) j->th.join();
+            if (j->rc && !rc) rc = fail(PFB_ERR_IO, j->err);
+        }
+        save_jobs.clear();
+        return rc;
+    }
+    template <class T, class O>
+    const void *widen_into(SaveJob &job, const DevBuf<T> &b, size_t count) {          // device array as O-wide integers
+        if (sizeof(T) == sizeof(O)) return b.get();
+        DevBuf<u8> t((count ? count : 1) * sizeof(O));
+        const T *s = b.get(); O *d = reinterpret_cast<O *>(t.get());
+        launch_for(count, ws.st, PFB_LAMBDA(u64 i) { d[i] = (O)s[i]; });
+        job.held.push_back(std::move(t));
+        return job.held.back().get();
+    }
+    int save_parse_async(const std::string &prefix, int mode, bool with_sai) {          // mode as pfb_save_parse's with_parse_bwt
+        try {
+            if (!parsed) return fail(PFB_ERR_ARG, "parse not finalized");
+            if (mode && !parse.has_parse_bwt) return fail(PFB_ERR_ARG, "parse BWT not computed");
+            const int U = prm.bits / 8;
+            std::unique_ptr<SaveJob> job(new SaveJob());
+            job->held.reserve(4);
+            auto add = [&](const char *ext, const void *d, size_t bytes) { SaveJob::Item it; it.path = prefix + "." + ext; it.d = d; it.bytes = bytes; job->items.push_back(it); };
+            if (mode != 2) {
+                add("dict", parse.dict.get(), parse.dsize);
+                add("occ", U == 4 ? widen_into<u32, u32>(*job, parse.occ, parse.Dw) : widen_into<u32, u64>(*job, parse.occ, parse.Dw), parse.Dw * (size_t)U);
+                add("parse", parse.parse.get(), parse.P * 4);
+                if (store_docs) {   // include/pfbwt_io.hpp:224-231
+                    FILE *f = fopen((prefix + ".docs").c_str(), "w");
+                    if (!f) return fail(PFB_ERR_IO, "could not open docs file");
+                    for (size_t i = 0; i < docs.starts.size(); ++i)
+                        fprintf(f, "%s %lu\n", i < docs.names.size() ? docs.names[i].c_str() : "", (unsigned long)docs.starts[i]);
+                    fclose(f);
+                }
+                FILE *f = fopen((prefix + ".n").c_str(), "w");
+                if (!f) return fail(PFB_ERR_IO, "could not open .n file");
+                fprintf(f, "%lu\n", (unsigned long)parse.n);
+                fclose(f);
+            }
+            if (mode) {
+                add("bwlast", parse.bwlast.get(), parse.P + 1);
+                add("ilist", U == 4 ? widen_into<u32, u32>(*job, parse.ilist, parse.P + 1) : widen_into<u32, u64>(*job, parse.ilist, parse.P + 1), (parse.P + 1) * (size_t)U);
+                if (with_sai) add("bwsai", U == 8 ? widen_into<u64, u64>(*job, parse.bwsai, parse.P + 1) : widen_into<u64, u32>(*job, parse.bwsai, parse.P + 1), (parse.P + 1) * (size_t)U);
+            }
+            stream_sync(ws.st);                 // the images are complete; the writer does not touch the pipeline's stream
+            SaveJob *jp = job.get();
+            const int dev = device;
+            jp->th = std::thread([jp, dev]() {
+                for (auto &it : jp->items) {
+                    std::string e;
+                    if (write_dev_file(it.path, it.d, it.bytes, 0, it.bytes, true, dev, 0, e, /*sync_producer=*/false)) { jp->rc = -1; jp->err = e; return; }
+                }
+            });
+            save_jobs.push_back(std::move(job));
+            return PFB_OK;
+        } catch (const Error &e) { return fail(e.code, e.what()); }
+    }
+
     // ---- load: PrefixFreeBWT ctor (include/pfbwt.hpp:64-81) / load_parser (include/pfbwt_io.hpp:211-222)
     int load_parse(const std::string &prefix, bool with_parse_bwt, bool with_sai) {
         try {
+            wait_saves();
             const int U = prm.bits / 8;
             std::string e;
             std::vector<uint8_t> occ, pr;

@@ -151,8 +151,9 @@ int main(int argc, char **argv) {
             // src/pfbwt-f.cpp:221-228: the parse files are written in this task, before bwt_of_parse can fail
             Timer t("TASK\tfinalizing parse, writing dict, occs, and ranks\t");
             { SubTimer t2("parse on device"); if (pfb_finalize(ctx)) die_ctx(ctx); }
-            SubTimer t3("writing parse files");
-            if (pfb_save_parse(ctx, args.output.c_str(), 0, 0)) die_ctx(ctx);
+            SubTimer t3("handing the parse files to the writer thread");
+            // the GB-sized files are written in the background while the device goes on; PFB_SYNC_WRITES=1 writes in place
+            if (getenv("PFB_SYNC_WRITES") ? pfb_save_parse(ctx, args.output.c_str(), 0, 0) : pfb_save_parse_async(ctx, args.output.c_str(), 0, 0)) die_ctx(ctx);
             if ((args.write_last || args.write_sai) && pfb_save_last_sai(ctx, args.output.c_str(), args.write_last, args.write_sai)) die_ctx(ctx);
         }
         {
@@ -164,11 +165,12 @@ int main(int argc, char **argv) {
                     exit(1);
                 }
             }
-            SubTimer t3("writing parse BWT files");
-            if (pfb_save_parse(ctx, args.output.c_str(), 2, any_sa)) die_ctx(ctx);
+            SubTimer t3("handing the parse BWT files to the writer thread");
+            if (getenv("PFB_SYNC_WRITES") ? pfb_save_parse(ctx, args.output.c_str(), 2, any_sa) : pfb_save_parse_async(ctx, args.output.c_str(), 2, any_sa)) die_ctx(ctx);
         }
         if (args.trim_non_acgt) { FILE *f = fopen((args.output + ".ntab").c_str(), "wb"); if (f) fclose(f); }
         pfb_release_text(ctx);
+        if (args.parse_only && pfb_wait_saves(ctx)) die_ctx(ctx);
     } else {
         if (pfb_load_parse(ctx, args.output.c_str(), 1, any_sa)) die_ctx(ctx);
     }
@@ -205,6 +207,7 @@ int main(int argc, char **argv) {
         fprintf(stderr, "r: %lu\n", (unsigned long)sz.r);
         fprintf(stderr, "n/r: %.3f\n", (double)sz.n / (double)sz.r);
     }
+    { SubTimer t("waiting for the writer thread"); if (pfb_wait_saves(ctx)) die_ctx(ctx); }
     if (args.verbose) {
         pfb_stats s;
         pfb_get_stats(ctx, &s);
