@@ -416,6 +416,68 @@ inline u64 scan_flags(const u8 *flags, u32 *idx, u64 n, Workspace &ws) {
     return (u64)last_idx + last_flag;
 }
 
+// Orders the members of every group of an active list by key.  Groups are contiguous in the list; the group id leads the
+// key (bits >= gshift) and hs[g] = list slot of group g's first member, hs[G] = m.  Members of a group of at most `cap`
+// members rank themselves by counting the smaller keys of their group - one pass, the group's keys come out of L1/L2 -;
+// larger groups are compacted and take the radix sort (whole groups, group id in the key: the i-th sorted pair belongs
+// into the i-th of their slots).  Tie groups are small where refinement rounds cost the most (repetitive inputs: the
+// variants of one phrase, the copies of one phrase sequence), so rounds become linear passes instead of 6-7 radix passes.
+// Result in k / v (buffers swapped); hl[a]: 1 = first, 2 = last member with its key (bits >= kshift) inside its group.
+static const u32 SMALL_GROUP_DEFAULT = 48;
+inline u32 small_group_cap() {
+    static const u32 c = getenv("PFB_SMALL_GROUP") ? (u32)atoi(getenv("PFB_SMALL_GROUP")) : SMALL_GROUP_DEFAULT;   // test knob: 0 = radix sort only
+    return c;
+}
+inline void order_groups(DevBuf<u64> &k, DevBuf<u64> &kb, DevBuf<u32> &v, DevBuf<u32> &vb, DevBuf<u8> &hl, u64 m, const u32 *hs,
+                         int gshift, int kshift, int sortbits, Workspace &ws) {
+    pfbStream_t st = ws.st;
+    DevBuf<u8> bigf(m);
+    {
+        const u64 *kp = k.get(); const u32 *vp = v.get(); u64 *ko = kb.get(); u32 *vo = vb.get(); u8 *hp = hl.get(); u8 *bf = bigf.get();
+        const u32 cap = small_group_cap();
+        launch_for(m, st, PFB_LAMBDA(u64 a) {
+            const u64 gid = kp[a] >> gshift;
+            const u32 s = hs[gid], e = hs[gid + 1];
+            if (e - s > cap) { bf[a] = 1; return; }
+            bf[a] = 0;
+            const u64 mine = kp[a] >> kshift;
+            u32 less = 0, eqb = 0, eqa = 0;
+            for (u32 j = s; j < e; ++j) {
+                const u64 o = kp[j] >> kshift;
+                less += o < mine ? 1u : 0u;
+                if (o == mine) { if (j < (u32)a) ++eqb; else if (j > (u32)a) ++eqa; }
+            }
+            const u32 dest = s + less + eqb;               // stable
+            ko[dest] = kp[a]; vo[dest] = vp[a];
+            hp[dest] = (u8)((eqb == 0 ? 1 : 0) | (eqa == 0 ? 2 : 0));
+        });
+    }
+    DevBuf<u32> bidx(m);
+    const u64 mb = scan_flags(bigf.get(), bidx.get(), m, ws);
+    if (mb) {
+        DevBuf<u64> bk(mb), bkb(mb);
+        DevBuf<u32> bv(mb), bvb(mb), bs(mb);
+        {
+            const u8 *bf = bigf.get(); const u32 *bi = bidx.get(); const u64 *kp = k.get(); const u32 *vp = v.get();
+            u64 *bkp = bk.get(); u32 *bvp = bv.get(); u32 *bsp = bs.get();
+            launch_for(m, st, PFB_LAMBDA(u64 a) { if (bf[a]) { const u32 i = bi[a]; bkp[i] = kp[a]; bvp[i] = vp[a]; bsp[i] = (u32)a; } });
+        }
+        sort_pairs(bk, bkb, bv, bvb, mb, kshift, sortbits, ws.sc, st);
+        {
+            const u32 *bsp = bs.get(); const u64 *bkp = bk.get(); const u32 *bvp = bv.get(); u64 *ko = kb.get(); u32 *vo = vb.get(); u8 *hp = hl.get();
+            launch_for(mb, st, PFB_LAMBDA(u64 i) {
+                const u64 x = bkp[i] >> kshift;
+                const bool head = i == 0 || x != (bkp[i - 1] >> kshift);
+                const bool last = i + 1 == mb || x != (bkp[i + 1] >> kshift);
+                const u32 dest = bsp[i];
+                ko[dest] = bkp[i]; vo[dest] = bvp[i];
+                hp[dest] = (u8)((head ? 1 : 0) | (last ? 2 : 0));
+            });
+        }
+    }
+    k.swap(kb); v.swap(vb);
+}
+
 // ---------------------------------------------------------------------------
 // K5a  lexicographic sort of the distinct phrases (strcmp order,
 //      include/pfparser.hpp:494-502) by MSD rounds of packed 3-bit symbols:
@@ -517,15 +579,22 @@ inline int sort_strings(const u8 *Tp, Str str, DevBuf<u32> &order, u64 Dw, Works
                 } else ak[a] = (gid << (3 * nsym)) | pack_syms(Tp + s, len, dp[j], nsym);
             });
         }
-        sort_pairs(akey, akey_b, aval, aval_b, m, pivot ? 1 : 0, pivot ? gbits + PIVOT_LBITS + 6 : gbits + 3 * nsym, ws.sc, st);
+        DevBuf<u8> hl(m);
         {
-            const u32 *ap = apos.get(); const u32 *av = aval.get(); const u64 *ak = akey.get();
+            DevBuf<u32> hslot(G + 1);
+            const u8 *ah = acthead.get(); const u32 *ai = aidx.get(); const u32 *gi = gidx.get(); u32 *hs = hslot.get();
+            const u32 m32 = (u32)m; const u64 G_ = G, Dw_ = Dw;
+            launch_for(Dw + 1, st, PFB_LAMBDA(u64 j) { if (j == Dw_) hs[G_] = m32; else if (ah[j]) hs[gi[j]] = ai[j]; });
+            order_groups(akey, akey_b, aval, aval_b, hl, m, hslot.get(), pivot ? PIVOT_LBITS + 6 : 3 * nsym, pivot ? 1 : 0,
+                         pivot ? gbits + PIVOT_LBITS + 6 : gbits + 3 * nsym, ws);
+        }
+        {
+            const u32 *ap = apos.get(); const u32 *av = aval.get(); const u64 *ak = akey.get(); const u8 *hlp = hl.get();
             u32 *ord = order.get(); u8 *fl = flag.get(); u32 *dp = dep.get();
-            const int ks = pivot ? 1 : 0;
             launch_for(m, st, PFB_LAMBDA(u64 a) {
                 u32 j = ap[a];
                 ord[j] = av[a];
-                fl[j] = (a == 0 || (ak[a] >> ks) != (ak[a - 1] >> ks)) ? 1 : 0;
+                fl[j] = (hlp[a] & 1) ? 1 : 0;
                 // position j stays inside its old group, so dp[j] still holds that group's depth
                 if (!pivot) dp[j] += (u32)nsym;
                 else dp[j] = (ak[a] & 1) ? CLOSED : dp[j] + pivot_consumed(ak[a]);
@@ -596,15 +665,22 @@ inline int prefix_doubling(DevBuf<u32> &sa, DevBuf<u32> &rank, DevBuf<u8> &flag,
                 ak[a] = (gid << rbits) | r2;
             });
         }
-        sort_pairs(akey, akey_b, aval, aval_b, ma, 0, gbits + rbits, ws.sc, st);
+        DevBuf<u8> hl(ma);
+        {
+            DevBuf<u32> hslot(G + 1);
+            const u8 *ah = acthead.get(); const u32 *ai = aidx.get(); const u32 *gi = gidx.get(); u32 *hs = hslot.get();
+            const u32 ma32 = (u32)ma; const u64 G_ = G;
+            launch_for(m + 1, st, PFB_LAMBDA(u64 j) { if (j == m) hs[G_] = ma32; else if (ah[j]) hs[gi[j]] = ai[j]; });
+            order_groups(akey, akey_b, aval, aval_b, hl, ma, hslot.get(), rbits, 0, gbits + rbits, ws);
+        }
         DevBuf<u32> hd(ma), hd2(ma);
         {
-            const u32 *ap = apos.get(); const u32 *av = aval.get(); const u64 *ak = akey.get();
+            const u32 *ap = apos.get(); const u32 *av = aval.get(); const u8 *hlp = hl.get();
             u32 *sp = sa.get(); u8 *fl = flag.get(); u32 *hp = hd.get();
             launch_for(ma, st, PFB_LAMBDA(u64 a) {
                 u32 j = ap[a];
                 sp[j] = av[a];
-                bool head = (a == 0 || ak[a] != ak[a - 1]);
+                bool head = (hlp[a] & 1) != 0;
                 fl[j] = head ? 1 : 0;
                 hp[a] = head ? j : 0;
             });
