@@ -35,7 +35,12 @@ struct Timer {   // src/pfbwt-f.cpp:35-50
 };
 
 static void die(const char *s) { perror(s); exit(1); }   // src/utils.c:13-17
-static void die_ctx(pfb_ctx *c) { fprintf(stderr, "%s\n", pfb_last_error(c)); exit(1); }
+static void die_ctx(pfb_ctx *c) {
+    const std::string msg = pfb_last_error(c);
+    pfb_wait_saves(c);                  // let the background writer finish what it was handed
+    fprintf(stderr, "%s\n", msg.c_str());
+    exit(1);
+}
 
 static void print_help() {
     fprintf(stderr, "%s. use the prefix-free parsing algorithm to build a BWT for %sgenomic data (B200 build).\n\n"
@@ -162,6 +167,7 @@ int main(int argc, char **argv) {
                 SubTimer t2("parse BWT on device");
                 if (pfb_parse_bwt(ctx)) {
                     fprintf(stderr, "%s: Success\n", pfb_last_error(ctx));
+                    pfb_wait_saves(ctx);          // the parse files of the previous task are complete before the exit, as in the reference
                     exit(1);
                 }
             }
