@@ -6,8 +6,9 @@ src/pfbwt-f.cpp:351-367), without the per-part files in between.
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \\
       pfbwt-f_b200/multi.py [-w W] [-p P] [-s] [-r] [--bits 32|64] [--non-acgt-to-a] [--save-parse] -o OUT in0.fa [in1.fa ...]
 
-The input files are dealt to the ranks in order, as contiguous groups (rank order = text order); every rank needs at
-least one file.  Rank g parses its files on GPU g; the parses are merged over NCCL; every rank builds and writes its
+The input files are dealt to the ranks in order, as contiguous groups (rank order = text order).  With fewer files than
+ranks (typically ONE multi-record or single-record FASTA) every file is instead cut into byte ranges, one per rank of its
+share of the ranks (pfb_add_fasta_range: the cuts fall anywhere, also inside a record - the w-overlapping chunk split).  Rank g parses its files on GPU g; the parses are merged over NCCL; every rank builds and writes its
 slice of OUT.bwt (/.sa/.ssa/.esa) at its offset.  Host code only plumbs: all work is in libpfbwt_b200.so
 (include/pfbwt_b200.h, "one job over several GPUs")."""
 import argparse
@@ -37,9 +38,10 @@ def main():
     B = binding()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if len(a.inputs) < world:
+    split = len(a.inputs) < world
+    if split and world % len(a.inputs) != 0:
         if rank == 0:
-            sys.stderr.write(f"need at least one input file per rank ({len(a.inputs)} files, {world} ranks)\n")
+            sys.stderr.write(f"{len(a.inputs)} input files cannot be split evenly over {world} ranks (use 1 file, or a divisor of the ranks)\n")
         return 1
     torch.cuda.set_device(local_rank)
     ctx = B.Context(device=local_rank, bits=a.bits, w=a.w, p=a.p, get_sai=a.s or a.r, non_acgt_to_a=a.non_acgt_to_a)
@@ -53,8 +55,14 @@ def main():
     mine = a.inputs[nin * rank // world:nin * (rank + 1) // world]
     rc = 0
     try:
-        for f in mine:
-            ctx.add_fasta(f)
+        if split:
+            per = world // nin                         # ranks per file
+            f, k = a.inputs[rank // per], rank % per
+            size = os.path.getsize(f)
+            ctx.add_fasta_range(f, size * k // per, size * (k + 1) // per)
+        else:
+            for f in mine:
+                ctx.add_fasta(f)
     except B.PfbError as e:                        # keep going: the failure is agreed on inside finalize()
         sys.stderr.write(f"[rank {rank}] {e.msg}\n")
     try:

@@ -125,3 +125,22 @@ def test_chunks_on_one_context_equal_records(tmp_path):
     for f in ("dict", "parse", "occ", "bwt", "sa", "ssa", "esa"):
         assert np.array_equal(getattr(one, f)(), getattr(two, f)()), f
     one.close(); two.close()
+
+
+def test_multi_launcher_splits_one_file(tmp_path):
+    """pfbwt-f_b200/multi.py with ONE input file and two ranks: the file is cut into byte ranges (mid-record), NCCL job"""
+    import os, subprocess, sys
+    from pfp_util import ROOT, write_fasta, run
+    from test_shard_gloo import free_port
+    if ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    recs = [("only", random_bases(2_500_000, 55))]
+    whole = os.path.join(str(tmp_path), "whole.fa")
+    write_fasta(whole, recs, line_width=80)
+    refp, out = os.path.join(str(tmp_path), "ref"), os.path.join(str(tmp_path), "out")
+    run([ref_bin("pfbwt-f64"), "-s", "-r", "-o", refp, whole])
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", str(free_port()), os.path.join(ROOT, "pfbwt-f_b200", "multi.py"), "-s", "-r", "--save-parse", "-o", out, whole]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600)
+    assert r.returncode == 0, r.stderr.decode(errors="replace")[-3000:]
+    assert_same_files(out, refp, exts_for(True, True))
