@@ -268,6 +268,16 @@ PFB_HD inline u64 phrase_start(const u64 *ends, u64 k, int w) { return k ? ends[
 //     are spread over many threads.
 // ---------------------------------------------------------------------------
 static const u64 FP_B1 = 0x9E3779B97F4A7C15ull, FP_B2 = 0xC2B2AE3D27D4EB4Full;
+// 8 bytes at any address (little endian) from the two aligned words around it (the text buffers carry >= 16 spare bytes)
+PFB_HD inline u64 load8_any(const u8 *p) {
+    const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+    const u64 *w = reinterpret_cast<const u64 *>(a & ~(uintptr_t)7);
+    const u32 sh = (u32)(a & 7) * 8;
+    const u64 lo = w[0];
+    return sh ? (lo >> sh) | (w[1] << (64 - sh)) : lo;
+}
+// bytes from .. to (inclusive, 0..7) of a little-endian word
+PFB_HD inline u64 bytes_mask(int from, int to) { return (~0ull << (8 * from)) & (~0ull >> (8 * (7 - to))); }
 PFB_HD inline u64 pow_u64(u64 b, u64 e) {
     u64 r = 1;
     while (e) { if (e & 1) r *= b; b *= b; e >>= 1; }
@@ -284,9 +294,16 @@ inline void k_fingerprint(const u8 *Tp, u64 tlen, const u64 *ends, u64 P, int w,
             u64 s = phrase_start(ends, k, w), e = ends[k];
             if (s > hi) break;
             u64 a = s > lo ? s : lo, b = e < hi ? e : hi;
+            // the phrase as 8-byte words counted from ITS first byte (the last one zero padded): the slice adds the words it
+            // overlaps, bytes outside [a, b] masked off - a word split between two slices adds up (the sum is linear)
+            const u64 q0 = (a - s) >> 3, q1 = (b - s) >> 3, nw = ((e - s) >> 3) + 1;
             u64 h1 = 0, h2 = 0;
-            for (u64 j = a; j <= b; ++j) { u64 ch = Tp[j]; h1 = h1 * FP_B1 + ch; h2 = h2 * FP_B2 + ch; }
-            u64 rem = e - b;
+            for (u64 q = q0; q <= q1; ++q) {
+                const u64 pq = s + 8 * q;
+                const u64 x = load8_any(Tp + pq) & bytes_mask(a > pq ? (int)(a - pq) : 0, b < pq + 7 ? (int)(b - pq) : 7);
+                h1 = h1 * FP_B1 + x; h2 = h2 * FP_B2 + x;
+            }
+            u64 rem = nw - 1 - q1;
             if (rem) { h1 *= pow_u64(FP_B1, rem); h2 *= pow_u64(FP_B2, rem); }
             atomic_add(&fp1[k], h1);
             atomic_add(&fp2[k], h2);
@@ -343,7 +360,10 @@ inline void k_verify(const u8 *Tp, u64 tlen, const u64 *ends, u64 P, int w, cons
             bool bad = (re - rs) != (e - s);
             if (!bad) {
                 u64 a = s > lo ? s : lo, b = e < hi ? e : hi;
-                for (u64 j = a; j <= b; ++j) bad |= Tp[j] != Tp[rs + (j - s)];
+                for (u64 pq = a; pq <= b; pq += 8) {                 // 8 bytes per step, the tail masked
+                    const u64 mk = bytes_mask(0, b < pq + 7 ? (int)(b - pq) : 7);
+                    bad |= ((load8_any(Tp + pq) ^ load8_any(Tp + rs + (pq - s))) & mk) != 0;
+                }
             }
             if (bad) atomic_or(d_flag, 1u);
         }
@@ -626,53 +646,59 @@ template <class DoneFn>
 inline int prefix_doubling(DevBuf<u32> &sa, DevBuf<u32> &rank, DevBuf<u8> &flag, u64 m, u64 h, DoneFn done, Workspace &ws,
                            u32 *rounds_out, std::string &err) {
     pfbStream_t st = ws.st;
-    DevBuf<u8> act(m), acthead(m);
-    DevBuf<u32> aidx(m), gidx(m);
     const int rbits = bits_for(m ? m - 1 : 0);
     u32 rounds = 0;
-    for (;;) {
-        {
-            const u8 *fl = flag.get(); const u32 *sp = sa.get(); u8 *ac = act.get();
-            launch_for(m, st, PFB_LAMBDA(u64 j) {
-                bool single = fl[j] && (j + 1 == m || fl[j + 1]);
-                ac[j] = (single || done(sp[j], h)) ? 0 : 1;
-            });
-            // a group is active as a whole (done() is uniform over a tie group), so the
-            // first active member of a group is its head
-            u8 *ah = acthead.get();
-            launch_for(m, st, PFB_LAMBDA(u64 j) { ah[j] = (ac[j] && fl[j]) ? 1 : 0; });
+    // the open list: sorted positions j of the members of tie groups that still have to be refined, ascending.  Built
+    // once from the flags; after that a round only touches the list (it shrinks geometrically on typical inputs), never
+    // all m positions again.
+    DevBuf<u32> apos;
+    u64 ma;
+    {
+        DevBuf<u8> act(m);
+        const u8 *fl = flag.get(); const u32 *sp = sa.get(); u8 *ac = act.get();
+        launch_for(m, st, PFB_LAMBDA(u64 j) {
+            bool single = fl[j] && (j + 1 == m || fl[j + 1]);
+            ac[j] = (single || done(sp[j], h)) ? 0 : 1;
+        });
+        DevBuf<u32> scratch(m);
+        ma = scan_flags(act.get(), scratch.get(), m, ws);
+        apos.alloc(ma);
+        if (ma) {
+            const u32 *ix = scratch.get(); u32 *ap = apos.get();
+            launch_for(m, st, PFB_LAMBDA(u64 j) { if (ac[j]) ap[ix[j]] = (u32)j; });
         }
-        u64 ma = scan_flags(act.get(), aidx.get(), m, ws);
-        if (ma == 0) break;
-        u64 G = scan_flags(acthead.get(), gidx.get(), m, ws);
-        int gbits = bits_for(G ? G - 1 : 0);
-        if (gbits + rbits > 64) { err = "prefix doubling: key overflow"; return PFB_ERR_INTERNAL; }
+    }
+    while (ma) {
         if (rounds > 64) { err = "prefix doubling did not converge"; return PFB_ERR_INTERNAL; }
-        DevBuf<u32> apos(ma), aval(ma), aval_b(ma);
+        // a group is active as a whole (done() is uniform over a tie group): the first listed member of a group is its head
+        DevBuf<u8> ah(ma);
+        DevBuf<u32> gidx(ma);
+        {
+            const u32 *ap = apos.get(); const u8 *fl = flag.get(); u8 *a_ = ah.get();
+            launch_for(ma, st, PFB_LAMBDA(u64 a) { a_[a] = fl[ap[a]] ? 1 : 0; });
+        }
+        const u64 G = scan_flags(ah.get(), gidx.get(), ma, ws);
+        const int gbits = bits_for(G ? G - 1 : 0);
+        if (gbits + rbits > 64) { err = "prefix doubling: key overflow"; return PFB_ERR_INTERNAL; }
+        DevBuf<u32> aval(ma), aval_b(ma), hslot(G + 1);
         DevBuf<u64> akey(ma), akey_b(ma);
         {
-            const u8 *ac = act.get(); const u8 *fl = flag.get();
-            const u32 *ai = aidx.get(); const u32 *gi = gidx.get(); const u32 *sp = sa.get(); const u32 *rk = rank.get();
-            u32 *ap = apos.get(); u32 *av = aval.get(); u64 *ak = akey.get();
-            launch_for(m, st, PFB_LAMBDA(u64 j) {
-                if (!ac[j]) return;
-                u32 a = ai[j];
-                u64 gid = (u64)gi[j] + (fl[j] ? 1 : 0) - 1;
-                u64 i = sp[j];
-                u64 nx = i + h;
-                u64 r2 = nx < m ? (u64)rk[nx] : 0;
-                ap[a] = (u32)j; av[a] = (u32)i;
+            const u32 *ap = apos.get(); const u8 *a_ = ah.get(); const u32 *gi = gidx.get(); const u32 *sp = sa.get(); const u32 *rk = rank.get();
+            u32 *av = aval.get(); u64 *ak = akey.get(); u32 *hs = hslot.get();
+            const u32 ma32 = (u32)ma; const u64 G_ = G;
+            launch_for(ma + 1, st, PFB_LAMBDA(u64 a) {
+                if (a == ma32) { hs[G_] = ma32; return; }
+                const u64 gid = (u64)gi[a] + a_[a] - 1;
+                if (a_[a]) hs[gid] = (u32)a;
+                const u64 i = sp[ap[a]];
+                const u64 nx = i + h;
+                const u64 r2 = nx < m ? (u64)rk[nx] : 0;
+                av[a] = (u32)i;
                 ak[a] = (gid << rbits) | r2;
             });
         }
         DevBuf<u8> hl(ma);
-        {
-            DevBuf<u32> hslot(G + 1);
-            const u8 *ah = acthead.get(); const u32 *ai = aidx.get(); const u32 *gi = gidx.get(); u32 *hs = hslot.get();
-            const u32 ma32 = (u32)ma; const u64 G_ = G;
-            launch_for(m + 1, st, PFB_LAMBDA(u64 j) { if (j == m) hs[G_] = ma32; else if (ah[j]) hs[gi[j]] = ai[j]; });
-            order_groups(akey, akey_b, aval, aval_b, hl, ma, hslot.get(), rbits, 0, gbits + rbits, ws);
-        }
+        order_groups(akey, akey_b, aval, aval_b, hl, ma, hslot.get(), rbits, 0, gbits + rbits, ws);
         DevBuf<u32> hd(ma), hd2(ma);
         {
             const u32 *ap = apos.get(); const u32 *av = aval.get(); const u8 *hlp = hl.get();
@@ -686,16 +712,32 @@ inline int prefix_doubling(DevBuf<u32> &sa, DevBuf<u32> &rank, DevBuf<u8> &flag,
             });
         }
         inclusive_max(hd.get(), hd2.get(), ma, ws.sc, st);
-        {
-            const u32 *av = aval.get(); const u32 *hp = hd2.get(); u32 *rk = rank.get();
-            launch_for(ma, st, PFB_LAMBDA(u64 a) { rk[av[a]] = hp[a]; });
-        }
         h *= 2;
         ++rounds;
+        // new ranks; what stays open: members of groups that are still tied and not complete within the doubled depth
+        DevBuf<u8> keep(ma);
+        {
+            const u32 *av = aval.get(); const u32 *hp = hd2.get(); const u8 *hlp = hl.get(); u32 *rk = rank.get(); u8 *kp = keep.get();
+            const u64 hn = h;
+            launch_for(ma, st, PFB_LAMBDA(u64 a) {
+                rk[av[a]] = hp[a];
+                kp[a] = ((hlp[a] & 3) == 3 || done(av[a], hn)) ? 0 : 1;
+            });
+        }
+        DevBuf<u32> kidx(ma);
+        const u64 m2 = scan_flags(keep.get(), kidx.get(), ma, ws);
+        DevBuf<u32> apos2(m2);
+        if (m2) {
+            const u32 *ap = apos.get(); const u8 *kp = keep.get(); const u32 *ki = kidx.get(); u32 *a2 = apos2.get();
+            launch_for(ma, st, PFB_LAMBDA(u64 a) { if (kp[a]) a2[ki[a]] = ap[a]; });
+        }
+        apos = std::move(apos2);
+        ma = m2;
     }
     if (rounds_out) *rounds_out = rounds;
     return PFB_OK;
 }
+
 
 // heads/ranks from sorted keys: flag[j] = key differs from predecessor,
 // rank[sa[j]] = position of the group head
