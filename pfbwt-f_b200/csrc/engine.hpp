@@ -640,6 +640,25 @@ struct Engine {
                 stream_sync(ws.st);
                 parse.has_parse_bwt = true;
             }
+            {
+                // a stale or mismatched file set must end in "bad parse file", not in out-of-range device reads later: every
+                // rank of .parse in 1..Dw, .occ = the histogram of .parse, every .ilist entry a position of the parse BWT
+                DevBuf<u32> bad(1), hist(parse.Dw);
+                dev_memset(bad.get(), 0, 4, ws.st);
+                dev_memset(hist.get(), 0, parse.Dw * 4, ws.st);
+                const u32 *pr_ = parse.parse.get(); const u32 *oc = parse.occ.get(); u32 *hp = hist.get(); u32 *bp = bad.get();
+                const u64 P_ = parse.P, Dw_ = parse.Dw;
+                launch_for(P_, ws.st, PFB_LAMBDA(u64 k) {
+                    const u32 r = pr_[k];
+                    if (r < 1 || (u64)r > Dw_) bp[0] = 1u; else atomic_add(&hp[r - 1], 1u);
+                });
+                launch_for(Dw_, ws.st, PFB_LAMBDA(u64 d) { if (hp[d] != oc[d]) bp[0] = 1u; });
+                if (with_parse_bwt) {
+                    const u32 *il = parse.ilist.get();
+                    launch_for(P_ + 1, ws.st, PFB_LAMBDA(u64 i) { if ((u64)il[i] > P_) bp[0] = 1u; });
+                }
+                if (P_ == 0 || read_scalar(bad.get(), ws.st)) { parse = DeviceParse(); return fail(PFB_ERR_IO, "bad parse file\n"); }
+            }
             docs = FastaResult();
             if (store_docs) {          // load_doc_info, include/pfbwt_io.hpp:177-205 ("<name> <start>" per line)
                 FILE *f = fopen((prefix + ".docs").c_str(), "r");

@@ -61,6 +61,7 @@ struct FastaMachine {
     uint64_t seq_len = 0, qual_len = 0;
     std::string name;
     bool in_record = false;
+    bool hdr_fresh = false;          // a header marker was the last byte seen so far
     FastaMachine(int w_, HostBytes &o, FastaResult &r, bool docs, uint64_t base) : w(w_), out(o), res(r), store_docs(docs), base_n(base) {}
     void finish_record() {
         out.append_fill('A', (size_t)w);
@@ -73,7 +74,7 @@ struct FastaMachine {
             uint64_t nb = base_n + out.n;      // text bytes before this record (all already padded)
             res.starts.push_back(nb);
         }
-        name.clear(); seq_len = 0; qual_len = 0; in_record = true;
+        name.clear(); seq_len = 0; qual_len = 0; in_record = true; hdr_fresh = true;
     }
     void feed(const uint8_t *b, size_t e) {
         size_t i = 0;
@@ -85,6 +86,7 @@ struct FastaMachine {
                 break;
             }
             case NAME: {       // name = up to first whitespace
+                hdr_fresh = false;
                 while (i < e && !isspace(b[i])) { if (store_docs) name.push_back((char)b[i]); ++i; }
                 if (i < e) {
                     if (store_docs) res.names.push_back(name);
@@ -133,6 +135,11 @@ struct FastaMachine {
         }
     }
     void finish() {
+        if (in_record && hdr_fresh) {          // kseq.h:188: a header marker as the very last byte gives no record (the name read hits EOF)
+            if (store_docs && !res.starts.empty()) res.starts.pop_back();
+            in_record = false;
+            return;
+        }
         if (state == NAME && store_docs && in_record) res.names.push_back(name);
         if (in_record) {
             if (seq_len > 1 && state == SEQ_LINE && out.p[out.n - 1] == '\r') { out.n--; seq_len--; }

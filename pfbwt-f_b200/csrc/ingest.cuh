@@ -169,6 +169,14 @@ inline int ingest_fasta_device(const std::string &path, int w, bool store_docs, 
         look_for_marker(hb.p, 0, m);
         if (p0 == ~0ull || first_marker != '>') return 2;
     }
+    if (!rg && m >= 2) {
+        // kseq.h:188: a header marker as the very last byte of the input starts no record (its name read hits EOF)
+        u8 tail2[2] = {0, 0};
+        bool have = false;
+        if (stream) { tail2[0] = out.hostraw.p[m - 2]; tail2[1] = out.hostraw.p[m - 1]; have = true; }
+        else have = pread(fd, tail2, 2, (off_t)(m - 2)) == 2;
+        if (have && tail2[1] == '>' && tail2[0] == '\n') --m;
+    }
     const int decline = rg ? -1 : stream ? 2 : 1;
     if (rg) err = "a byte range needs a plain FASTA file (no FASTQ records, no CR LF line ends) that fits the device";
 

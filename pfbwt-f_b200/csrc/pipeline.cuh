@@ -294,14 +294,18 @@ inline void k_fingerprint(const u8 *Tp, u64 tlen, const u64 *ends, u64 P, int w,
             u64 s = phrase_start(ends, k, w), e = ends[k];
             if (s > hi) break;
             u64 a = s > lo ? s : lo, b = e < hi ? e : hi;
-            // the phrase as 8-byte words counted from ITS first byte (the last one zero padded): the slice adds the words it
-            // overlaps, bytes outside [a, b] masked off - a word split between two slices adds up (the sum is linear)
-            const u64 q0 = (a - s) >> 3, q1 = (b - s) >> 3, nw = ((e - s) >> 3) + 1;
+            // the phrase as 8-byte words counted from ITS first byte (the last one zero padded past e): a word belongs to the
+            // slice that holds its first byte.  Every word is mixed before it enters the polynomial: two phrases that differ
+            // in the top byte of a word (one substituted base) would otherwise differ in the top bits of both sums only
+            const u64 q0 = (a - s + 7) >> 3, q1 = (b - s) >> 3, nw = ((e - s) >> 3) + 1;
+            if (q0 > q1) continue;
             u64 h1 = 0, h2 = 0;
             for (u64 q = q0; q <= q1; ++q) {
                 const u64 pq = s + 8 * q;
-                const u64 x = load8_any(Tp + pq) & bytes_mask(a > pq ? (int)(a - pq) : 0, b < pq + 7 ? (int)(b - pq) : 7);
-                h1 = h1 * FP_B1 + x; h2 = h2 * FP_B2 + x;
+                const u64 x = load8_any(Tp + pq) & bytes_mask(0, e < pq + 7 ? (int)(e - pq) : 7);
+                u64 f = (x ^ (x >> 32)) * 0x9FB21C651E98DF25ull;
+                u64 g = (x ^ (x >> 27)) * 0xD6E8FEB86659FD93ull;
+                h1 = h1 * FP_B1 + (f ^ (f >> 29)); h2 = h2 * FP_B2 + (g ^ (g >> 31));
             }
             u64 rem = nw - 1 - q1;
             if (rem) { h1 *= pow_u64(FP_B1, rem); h2 *= pow_u64(FP_B2, rem); }

@@ -205,3 +205,24 @@ def test_emu_bucketed_build(buckets, flags, bits, emu, ref_bins, datadir):
     assert r.returncode == 0, r.stderr.decode()[-1500:]
     assert f"buckets: {buckets}" in r.stderr.decode()
     assert_same_files(a, b, exts_for("-s" in flags, "-r" in flags))
+
+
+def test_emu_load_rejects_mismatched_files(emu, datadir):
+    """load_parser with a stale file set: a rank outside 1..Dw or an .occ that is not the histogram of .parse must end in
+    'bad parse file', not in out-of-range reads"""
+    fa = os.path.join(datadir, "stale.fa")
+    write_fasta(fa, pangenome_records(20_000, 3, 20, 4), line_width=50)
+    run([emu, "--bits", "64", "--parse-only", fa])
+    import shutil
+    for what in ("occ", "parse"):
+        pfx = os.path.join(datadir, "stale_" + what)
+        for e in ("dict", "occ", "parse", "n"):
+            shutil.copy(fa + "." + e, pfx + "." + e)
+        raw = bytearray(open(pfx + "." + what, "rb").read())
+        if what == "occ":
+            raw[0] ^= 1                       # a count that no longer matches the parse
+        else:
+            raw[4:8] = (0xFFFFFF).to_bytes(4, "little")       # a rank far past the dictionary
+        open(pfx + "." + what, "wb").write(bytes(raw))
+        r = run([emu, "--merge", "--bits", "64", "-o", os.path.join(datadir, "stale_out"), pfx], check=False)
+        assert r.returncode != 0 and b"bad parse file" in r.stderr, (what, r.stderr[-300:])

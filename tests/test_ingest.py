@@ -32,6 +32,8 @@ def case_files():
     cases["tile_edges"] = (b">t63\n" + wrap(a, 63) + b"\n>t64\n" + wrap(b, 64) + b"\n>t65\n" + wrap(d, 65) + b"\n>long\n" + a + b"\n>one\n" + wrap(a[:300], 1) + b"\n")
     # 62 + newline + header start exactly at tile boundaries
     cases["aligned"] = b">" + b"x" * 62 + b"\n" + wrap(a, 63) + b"\n" + b">" + b"y" * 30 + b"\n" + wrap(b, 127) + b"\n"
+    # a header marker as the very last byte of the file: kseq's name read hits EOF, no record (kseq.h:188)
+    cases["lone_marker_at_eof"] = b">r1 c\n" + wrap(a, 60) + b"\n>r2\n" + wrap(b, 60) + b"\n>"
     cases["lower_and_n"] = b">m1\n" + wrap(low, 60) + b"\n>m2 has N\n" + wrap(withn, 60) + b"\n"
     # handled by the host reader (detected on the device): CR LF line ends, FASTQ
     cases["crlf"] = b">c1 x\r\n" + wrap(a, 60).replace(b"\n", b"\r\n") + b"\r\n>c2\r\n" + wrap(b, 60).replace(b"\n", b"\r\n") + b"\r\n"
