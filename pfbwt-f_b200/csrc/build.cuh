@@ -70,6 +70,28 @@ PFB_HD inline u64 load8_unaligned(const u8 *dict, u64 pos) {
     const u64 lo = w[0];
     return sh ? (lo >> sh) | (w[1] << (64 - sh)) : lo;
 }
+// 32 dictionary bytes starting at any position as four little-endian words, from three aligned 16-byte loads: a divergent
+// warp pays per load instruction (one L1 wavefront per distinct line), so the comparison loop wants few, wide loads
+PFB_HD inline void load32_unaligned(const u8 *dict, u64 pos, u64 *o) {
+    const u64 A = pos & ~15ull;
+    u64 t[6];
+#ifdef __CUDA_ARCH__
+    const uint4 *q = reinterpret_cast<const uint4 *>(dict + A);
+    const uint4 v0 = q[0], v1 = q[1], v2 = q[2];
+    t[0] = (u64)v0.x | ((u64)v0.y << 32); t[1] = (u64)v0.z | ((u64)v0.w << 32);
+    t[2] = (u64)v1.x | ((u64)v1.y << 32); t[3] = (u64)v1.z | ((u64)v1.w << 32);
+    t[4] = (u64)v2.x | ((u64)v2.y << 32); t[5] = (u64)v2.z | ((u64)v2.w << 32);
+#else
+    const u64 *q = reinterpret_cast<const u64 *>(dict + A);
+    for (int i = 0; i < 6; ++i) t[i] = q[i];
+#endif
+    const u32 wi = (u32)(pos & 15) >> 3, bs = (u32)(pos & 7) * 8;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const u64 lo = wi ? t[k + 1] : t[k], hi2 = wi ? t[k + 2] : t[k + 1];
+        o[k] = bs ? (lo >> bs) | (hi2 << (64 - bs)) : lo;
+    }
+}
 // Long single-symbol runs of the dictionary (poly-A phrases left by --non-acgt-to-a on Mbp N runs, poly-N without it):
 // two suffixes inside such runs share min(remaining run lengths) symbols, which the comparison skips in one step
 // instead of reading them - otherwise ties of millions of symbols would need prefix doubling over the whole dictionary.
@@ -93,16 +115,14 @@ PFB_HD inline u64 pivot_key(const u8 *dict, u64 D, u64 a, u64 p, int lb, const R
     // four 8-symbol steps at a time while nothing happens in them (all loads of a step are independent: the comparison is
     // bound by memory latency, variants of a phrase agree for tens of symbols); the exact step loop below takes over at the
     // first difference, terminator or candidate run
-    while (l + 32 <= cap && hi + l + 40 <= D) {
+    while (l + 32 <= cap && hi + l + 48 <= D) {
+        u64 x[4], y[4];
+        load32_unaligned(dict, a + l, x);
+        load32_unaligned(dict, p + l, y);
         u64 acc = 0;
-        u64 x0 = 0;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const u64 x = load8_unaligned(dict, a + l + 8 * c), y = load8_unaligned(dict, p + l + 8 * c);
-            if (c == 0) x0 = x;
-            acc |= (x ^ y) | ((x - 0x0202020202020202ull) & ~x & 0x8080808080808080ull);
-        }
-        if (acc || (rt.R && x0 == (x0 & 0xffull) * 0x0101010101010101ull)) break;
+        for (int c = 0; c < 4; ++c) acc |= (x[c] ^ y[c]) | ((x[c] - 0x0202020202020202ull) & ~x[c] & 0x8080808080808080ull);
+        if (acc || (rt.R && x[0] == (x[0] & 0xffull) * 0x0101010101010101ull)) break;
         l += 32;
     }
     while (l + 8 <= cap && hi + l + 16 <= D) {

@@ -914,7 +914,7 @@ inline int parse_piece(const u8 *Tp, const PieceSpec &ps, const Params &prm, Dev
         const u64 *w64 = ws64.get(); u32 *wsp = out.wstart.get();
         launch_for(Dw + 1, st, PFB_LAMBDA(u64 r) { wsp[r] = (u32)w64[r]; });
         u8 *dict = out.dict.get(); const u32 *ord = order.get();
-        // 32 logical lanes per word copy it with unit stride (include/pfbwt_io.hpp:71-82); the few words longer than
+        // the words are copied into the image (include/pfbwt_io.hpp:71-82); the few words longer than
         // LONGW (phrases spanning an N run: up to tens of Mbp) are listed and copied by the copy engine instead
         const u64 LONGW = 1u << 13;
         const u64 lcap = tlen / LONGW + 2;
@@ -922,13 +922,21 @@ inline int parse_piece(const u8 *Tp, const PieceSpec &ps, const Params &prm, Dev
         DevBuf<u32> nlong(1);
         dev_memset(nlong.get(), 0, 4, st);
         u64 *lw = longw.get(); u32 *nl = nlong.get();
-        launch_for(Dw * 32, st, PFB_LAMBDA(u64 i) {
-            u64 r = i / 32, lane = i % 32;
+        // 8 lanes per word, 8 bytes per lane and step: aligned 8-byte stores into the image, the source read with load8_any
+        // (phrases start anywhere); the ragged head / tail of a word byte by byte
+        launch_for(Dw * 8, st, PFB_LAMBDA(u64 i) {
+            u64 r = i / 8, lane = i % 8;
             u64 k = ord[r];
             u64 s = phrase_start(ends, k, w), len = ends[k] - s + 1;
             u64 d0 = w64[r];
-            if (len <= LONGW) { for (u64 j = lane; j < len; j += 32) dict[d0 + j] = Tp[s + j]; }
-            else if (lane == 0) { u64 q = atomic_add(nl, 1u); lw[3 * q] = s; lw[3 * q + 1] = d0; lw[3 * q + 2] = len; }
+            if (len <= LONGW) {
+                u64 head = (8 - (d0 & 7)) & 7;
+                if (head > len) head = len;
+                const u64 nfull = (len - head) >> 3;
+                if (lane == 0) for (u64 j = 0; j < head; ++j) dict[d0 + j] = Tp[s + j];
+                for (u64 j = lane; j < nfull; j += 8) *reinterpret_cast<u64 *>(dict + d0 + head + 8 * j) = load8_any(Tp + s + head + 8 * j);
+                if (lane == 7) for (u64 j = head + 8 * nfull; j < len; ++j) dict[d0 + j] = Tp[s + j];
+            } else if (lane == 0) { u64 q = atomic_add(nl, 1u); lw[3 * q] = s; lw[3 * q + 1] = d0; lw[3 * q + 2] = len; }
             if (lane == 0) dict[d0 + len] = ENDOFWORD;
             if (i == 0) dict[dsize - 1] = ENDOFDICT;
         });
