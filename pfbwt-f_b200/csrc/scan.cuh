@@ -21,17 +21,24 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan(const TIn *__restrict__ i
     __shared__ unsigned s_tile;
     __shared__ TOut s_warp[SCAN_THREADS / 32];
     __shared__ TOut s_base;
+    __shared__ TOut s_item[SCAN_TILE + SCAN_TILE / SCAN_ITEMS];      // the tile, one pad slot per thread: global accesses are striped (unit stride across the warp), a thread's 16 consecutive items come from here
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     if (tid == 0) s_tile = atomicAdd(counter, 1u);
     __syncthreads();
     const unsigned long long tile = s_tile;
-    const unsigned long long base = tile * SCAN_TILE + (unsigned long long)tid * SCAN_ITEMS;
     auto op = [](TOut a, TOut b) -> TOut { return MAX ? (a > b ? a : b) : (TOut)(a + b); };
+    const unsigned long long tbase = tile * SCAN_TILE;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+        const int e = k * SCAN_THREADS + tid;
+        s_item[e + e / SCAN_ITEMS] = tbase + e < n ? (TOut)in[tbase + e] : (TOut)0;
+    }
+    __syncthreads();
     TOut v[SCAN_ITEMS];
     TOut acc = 0;                                          // identity of both operations on unsigned values
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; ++k) {
-        v[k] = base + k < n ? (TOut)in[base + k] : (TOut)0;
+        v[k] = s_item[tid * (SCAN_ITEMS + 1) + k];
         acc = op(acc, v[k]);
     }
     // inclusive scan of the thread partials over the CTA
@@ -74,8 +81,14 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan(const TIn *__restrict__ i
     }
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; ++k) {
-        if (INCL) { run = op(run, v[k]); if (base + k < n) out[base + k] = run; }
-        else { if (base + k < n) out[base + k] = run; run = op(run, v[k]); }
+        if (INCL) { run = op(run, v[k]); s_item[tid * (SCAN_ITEMS + 1) + k] = run; }
+        else { s_item[tid * (SCAN_ITEMS + 1) + k] = run; run = op(run, v[k]); }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+        const int e = k * SCAN_THREADS + tid;
+        if (tbase + e < n) out[tbase + e] = s_item[e + e / SCAN_ITEMS];
     }
 }
 

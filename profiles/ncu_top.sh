@@ -4,7 +4,7 @@
 # capture of the longest launch of every kernel regex given.  Outputs under gpurun_out/.
 set -u
 TAG=$1; shift
-CMD="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e --no-single-job --no-file-leg --no-parity"
+CMD=${NCU_CMD:-"python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e --no-single-job --no-file-leg --no-parity"}
 mkdir -p gpurun_out
 $CMD > gpurun_out/${TAG}_plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/${TAG}_plain.log; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu_list.log 2>&1
