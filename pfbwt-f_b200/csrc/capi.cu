@@ -41,10 +41,22 @@ static int copy_out_uint(pfb_ctx *c, const pfb::DevBuf<T> &b, size_t count, void
     const size_t U = (size_t)c->eng.prm.bits / 8;
     try {
         if (U == sizeof(T)) { if (count) { pfb::d2h(out, b.get(), count * sizeof(T), c->eng.ws.st); pfb::stream_sync(c->eng.ws.st); } }
-        else {
-            std::vector<T> v = c->eng.to_host(b, count);
-            if (U == 4) { uint32_t *o = (uint32_t *)out; for (size_t i = 0; i < count; ++i) o[i] = (uint32_t)v[i]; }
-            else { uint64_t *o = (uint64_t *)out; for (size_t i = 0; i < count; ++i) o[i] = (uint64_t)v[i]; }
+        else if (count) {       // widened / narrowed on the device, then one copy
+            cudaStream_t st = c->eng.ws.st;
+            const T *s = b.get();
+            if (U == 4) {
+                pfb::DevBuf<uint32_t> t(count);
+                uint32_t *d = t.get();
+                pfb::launch_for(count, st, [=] __device__(pfb::u64 i) { d[i] = (uint32_t)s[i]; });
+                pfb::d2h(out, t.get(), count * 4, st);
+                pfb::stream_sync(st);
+            } else {
+                pfb::DevBuf<uint64_t> t(count);
+                uint64_t *d = t.get();
+                pfb::launch_for(count, st, [=] __device__(pfb::u64 i) { d[i] = (uint64_t)s[i]; });
+                pfb::d2h(out, t.get(), count * 8, st);
+                pfb::stream_sync(st);
+            }
         }
     } catch (const pfb::Error &e) { return c->eng.fail(e.code, e.what()); }
     return PFB_OK;

@@ -546,22 +546,38 @@ struct Engine {
         } catch (const Error &e) { return fail(e.code, e.what()); }
     }
 
+    // a file of `count` integers of the binary's width U -> device array of the pipeline's width, converted on the device
+    // (0 ok - present says whether the file exists -, -1 wrong size)
+    template <class TD>
+    int load_uint_file(const std::string &path, u64 count, DevBuf<TD> &dst, bool &present) {
+        const int U = prm.bits / 8;
+        DevBuf<u8> rawb;
+        u64 sz = 0;
+        std::string e2;
+        present = read_whole_file_to_dev(path, rawb, sz, 64, device, ws.st, e2) == 0;
+        if (!present) return 0;
+        if (sz != count * (u64)U) return -1;
+        dst.alloc(count ? count : 1);
+        TD *d = dst.get();
+        if (U == 4) { const u32 *s4 = reinterpret_cast<const u32 *>(rawb.get()); launch_for(count, ws.st, PFB_LAMBDA(u64 i) { d[i] = (TD)s4[i]; }); }
+        else { const u64 *s8 = reinterpret_cast<const u64 *>(rawb.get()); launch_for(count, ws.st, PFB_LAMBDA(u64 i) { d[i] = (TD)s8[i]; }); }
+        stream_sync(ws.st);
+        return 0;
+    }
+
     // ---- load: PrefixFreeBWT ctor (include/pfbwt.hpp:64-81) / load_parser (include/pfbwt_io.hpp:211-222)
     int load_parse(const std::string &prefix, bool with_parse_bwt, bool with_sai) {
         try {
             wait_saves();
             const int U = prm.bits / 8;
             std::string e;
-            std::vector<uint8_t> occ, pr;
             // the dictionary (GBs) goes from the file straight to HBM; it is checked and cut into words there
             parse = DeviceParse();
             u64 dsize = 0;
             if (read_whole_file_to_dev(prefix + ".dict", parse.dict, dsize, 64, device, ws.st, e)) return fail(PFB_ERR_IO, "bad dict file\n");
-            if (read_file(prefix + ".parse", pr, e)) return fail(PFB_ERR_IO, "bad parse file\n");
             if (dsize < 2) return fail(PFB_ERR_IO, "bad dict file\n");
             if (dsize > 0xFFFFFFF0ull) return fail(PFB_ERR_LIMIT, "dictionary larger than 2^32 bytes is not supported yet");
             parse.dsize = dsize;
-            std::vector<u32> wstart;       // host copy only where the .n file is missing
             {
                 const u8 *dp = parse.dict.get();
                 DevBuf<u32> st3(3);        // [0] byte outside the alphabet, [1] bad tail
@@ -592,52 +608,49 @@ struct Engine {
                     if (ie[i]) wsp[rk[i] + 1] = (u32)i + 1;
                 });
             }
-            parse.P = pr.size() / 4;
-            parse.parse.alloc(parse.P + 1);
-            h2d(parse.parse.get(), pr.data(), parse.P * 4, ws.st);
-            dev_memset(parse.parse.get() + parse.P, 0, 4, ws.st);
-            // occ: from file if present, else recount
-            std::vector<u32> occ32(parse.Dw, 0);
-            if (!read_file(prefix + ".occ", occ, e) && occ.size() == parse.Dw * (size_t)U) {
-                for (u64 d = 0; d < parse.Dw; ++d) occ32[d] = U == 4 ? ((u32 *)occ.data())[d] : (u32)((u64 *)occ.data())[d];
-            } else {
-                const u32 *p32 = (const u32 *)pr.data();
-                for (u64 k = 0; k < parse.P; ++k) { if (p32[k] < 1 || p32[k] > parse.Dw) return fail(PFB_ERR_IO, "bad parse file\n"); occ32[p32[k] - 1]++; }
+            // .parse / .occ / .ilist / .bwsai go from their files straight to HBM (devio.cuh) and are brought to the device
+            // widths there: no element-wise loops on a host core
+            {
+                DevBuf<u8> rawp;
+                u64 psz = 0;
+                if (read_whole_file_to_dev(prefix + ".parse", rawp, psz, 64, device, ws.st, e)) return fail(PFB_ERR_IO, "bad parse file\n");
+                parse.P = psz / 4;
+                parse.parse.alloc(parse.P + 1);
+                d2d(parse.parse.get(), rawp.get(), parse.P * 4, ws.st);
+                dev_memset(parse.parse.get() + parse.P, 0, 4, ws.st);
+                stream_sync(ws.st);
             }
-            parse.occ.alloc(parse.Dw); h2d(parse.occ.get(), occ32.data(), parse.Dw * 4, ws.st);
+            bool have_occ = false;
+            if (load_uint_file(prefix + ".occ", parse.Dw, parse.occ, have_occ)) have_occ = false;      // wrong size: recount below
+            if (!have_occ) { parse.occ.alloc(parse.Dw); dev_memset(parse.occ.get(), 0, parse.Dw * 4, ws.st); }
             // n from <prefix>.n (src/pfbwt-f.cpp:255-270) or from the phrase lengths
             {
                 FILE *f = fopen((prefix + ".n").c_str(), "r");
                 unsigned long nn = 0;
                 if (f && fscanf(f, "%lu", &nn) == 1) parse.n = nn;
                 else {
-                    wstart.resize(parse.Dw + 1);
-                    d2h(wstart.data(), parse.wstart.get(), (parse.Dw + 1) * 4, ws.st);
-                    stream_sync(ws.st);
-                    const u32 *p32 = (const u32 *)pr.data();
-                    u64 tot = 0;
-                    for (u64 k = 0; k < parse.P; ++k) { u64 d = p32[k] - 1; tot += (u64)(wstart[d + 1] - 1 - wstart[d]) - (k ? (u64)prm.w : 0); }
-                    parse.n = tot - 1 - (u64)prm.w;
+                    DevBuf<u64> tot(1);
+                    dev_memset(tot.get(), 0, 8, ws.st);
+                    const u32 *pr_ = parse.parse.get(); const u32 *wsr = parse.wstart.get(); u64 *tp = tot.get();
+                    const u64 Dw_ = parse.Dw, w_ = (u64)prm.w;
+                    launch_for(parse.P, ws.st, PFB_LAMBDA(u64 k) {
+                        const u64 d = (u64)pr_[k] - 1;
+                        if (d < Dw_) atomic_add(tp, (u64)(wsr[d + 1] - 1 - wsr[d]) - (k ? w_ : 0));
+                    });
+                    parse.n = read_scalar(tot.get(), ws.st) - 1 - (u64)prm.w;
                 }
                 if (f) fclose(f);
             }
             stream_sync(ws.st);
             if (with_parse_bwt) {
-                std::vector<uint8_t> bl, il, bs;
-                if (read_file(prefix + ".bwlast", bl, e) || read_file(prefix + ".ilist", il, e)) return fail(PFB_ERR_IO, e);
-                if (bl.size() != parse.P + 1 || il.size() != (parse.P + 1) * (size_t)U) return fail(PFB_ERR_IO, "bwlast/ilist size mismatch");
-                parse.bwlast.alloc(parse.P + 1); h2d(parse.bwlast.get(), bl.data(), bl.size(), ws.st);
-                std::vector<u32> il32(parse.P + 1);
-                for (u64 i = 0; i <= parse.P; ++i) il32[i] = U == 4 ? ((u32 *)il.data())[i] : (u32)((u64 *)il.data())[i];
-                parse.ilist.alloc(parse.P + 1); h2d(parse.ilist.get(), il32.data(), il32.size() * 4, ws.st);
+                u64 bsz = 0;
+                if (read_whole_file_to_dev(prefix + ".bwlast", parse.bwlast, bsz, 64, device, ws.st, e)) return fail(PFB_ERR_IO, e);
+                bool have = false;
+                if (bsz != parse.P + 1 || load_uint_file(prefix + ".ilist", parse.P + 1, parse.ilist, have) || !have) return fail(PFB_ERR_IO, "bwlast/ilist size mismatch");
                 if (with_sai) {
-                    if (read_file(prefix + ".bwsai", bs, e)) return fail(PFB_ERR_IO, e);
-                    if (bs.size() != (parse.P + 1) * (size_t)U) return fail(PFB_ERR_IO, "bwsai size mismatch");
-                    std::vector<u64> b64(parse.P + 1);
-                    for (u64 i = 0; i <= parse.P; ++i) b64[i] = U == 4 ? ((u32 *)bs.data())[i] : ((u64 *)bs.data())[i];
-                    parse.bwsai.alloc(parse.P + 1); h2d(parse.bwsai.get(), b64.data(), b64.size() * 8, ws.st);
+                    if (load_uint_file(prefix + ".bwsai", parse.P + 1, parse.bwsai, have)) return fail(PFB_ERR_IO, "bwsai size mismatch");
+                    if (!have) return fail(PFB_ERR_IO, "error opening " + prefix + ".bwsai");
                 }
-                stream_sync(ws.st);
                 parse.has_parse_bwt = true;
             }
             {
@@ -652,7 +665,8 @@ struct Engine {
                     const u32 r = pr_[k];
                     if (r < 1 || (u64)r > Dw_) bp[0] = 1u; else atomic_add(&hp[r - 1], 1u);
                 });
-                launch_for(Dw_, ws.st, PFB_LAMBDA(u64 d) { if (hp[d] != oc[d]) bp[0] = 1u; });
+                if (have_occ) launch_for(Dw_, ws.st, PFB_LAMBDA(u64 d) { if (hp[d] != oc[d]) bp[0] = 1u; });
+                else d2d(parse.occ.get(), hist.get(), Dw_ * 4, ws.st);           // no .occ file: the counts of the parse
                 if (with_parse_bwt) {
                     const u32 *il = parse.ilist.get();
                     launch_for(P_ + 1, ws.st, PFB_LAMBDA(u64 i) { if ((u64)il[i] > P_) bp[0] = 1u; });

@@ -44,11 +44,15 @@
             const u64 nwords = qmax / 32 + 1;
             DevBuf<u32> trig(nwords), cnt(nwords);
             k_trigger_words(X + done, qmax, (int)w, dt, trig.get(), cnt.get(), nwords, st, w + 1);
-            host.resize(nwords);
-            d2h(host.data(), trig.get(), nwords * 4, st);
-            stream_sync(st);
-            for (u64 t = 0; t < nwords; ++t)
-                if (host[t]) return done + (t * 32 + (u64)(__builtin_ffs((int)host[t]) - 1)) - (w + 1);
+            // the smallest set position is reduced on the device: one scalar comes back, not the bitmap
+            DevBuf<u64> first(1);
+            dev_memset(first.get(), 0xff, 8, st);
+            {
+                const u32 *tg = trig.get(); u64 *fp = first.get();
+                launch_for(nwords, st, PFB_LAMBDA(u64 t) { const u32 b = tg[t]; if (b) atomic_min(fp, t * 32 + (u64)(ffs32(b) - 1)); });
+            }
+            const u64 q = read_scalar(first.get(), st);
+            if (q != ~0ull) return done + q - (w + 1);
             done += cntp;
             win *= 8;
         }
