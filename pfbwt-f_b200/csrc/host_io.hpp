@@ -62,6 +62,10 @@ struct FastaMachine {
     std::string name;
     bool in_record = false;
     bool hdr_fresh = false;          // a header marker was the last byte seen so far
+    bool stopped = false;            // kseq_read returned an error (-2): add_fasta's loop ends, the record and everything behind it are dropped
+    size_t rec_out_start = 0;        // out.n when the current record began
+    size_t names_before = 0;
+    uint8_t qlast = 0;               // last quality character taken (a trailing CR is trimmed line by line, kseq.h:141)
     FastaMachine(int w_, HostBytes &o, FastaResult &r, bool docs, uint64_t base) : w(w_), out(o), res(r), store_docs(docs), base_n(base) {}
     void finish_record() {
         out.append_fill('A', (size_t)w);
@@ -75,10 +79,20 @@ struct FastaMachine {
             res.starts.push_back(nb);
         }
         name.clear(); seq_len = 0; qual_len = 0; in_record = true; hdr_fresh = true;
+        rec_out_start = out.n; names_before = res.names.size(); qlast = 0;
+    }
+    void drop_record() {             // kseq.h:209-213: no / short / long quality string -> -2
+        out.n = rec_out_start;
+        if (store_docs) { if (!res.starts.empty()) res.starts.pop_back(); if (res.names.size() > names_before) res.names.resize(names_before); }
+        in_record = false;
+        stopped = true;
+    }
+    void qual_line_done() {
+        if (qual_len > 1 && qlast == '\r') { --qual_len; qlast = 0; }
     }
     void feed(const uint8_t *b, size_t e) {
         size_t i = 0;
-        while (i < e) {
+        while (i < e && !stopped) {
             switch (state) {
             case SEEK_HDR: {   // kseq.h:183-187: skip to the next '>' or '@' anywhere
                 while (i < e && b[i] != '>' && b[i] != '@') ++i;
@@ -126,9 +140,19 @@ struct FastaMachine {
                 if (q) { i = (size_t)(q - b) + 1; state = seq_len ? QUAL : SEEK_HDR; if (!seq_len) finish_record(); } else i = e;
                 break;
             }
-            case QUAL: {       // kseq.h:209: read quality lines until as long as the sequence
-                while (i < e && qual_len < seq_len) { if (b[i] != '\n') ++qual_len; ++i; }
-                if (qual_len >= seq_len) { finish_record(); state = SEEK_HDR; }
+            case QUAL: {       // kseq.h:209-213: whole quality lines until at least as long as the sequence, then the lengths must agree
+                const uint8_t *q = (const uint8_t *)memchr(b + i, '\n', e - i);
+                const size_t le = q ? (size_t)(q - b) : e;
+                if (le > i) { qual_len += le - i; qlast = b[le - 1]; }
+                i = le;
+                if (q) {
+                    ++i;
+                    qual_line_done();
+                    if (qual_len >= seq_len) {
+                        if (qual_len == seq_len) { finish_record(); state = SEEK_HDR; }
+                        else drop_record();
+                    }
+                }
                 break;
             }
             }
@@ -138,6 +162,13 @@ struct FastaMachine {
         if (in_record && hdr_fresh) {          // kseq.h:188: a header marker as the very last byte gives no record (the name read hits EOF)
             if (store_docs && !res.starts.empty()) res.starts.pop_back();
             in_record = false;
+            return;
+        }
+        if (stopped) return;
+        if (in_record && state == PLUS_LINE) { drop_record(); return; }            // EOF inside the '+' line: no quality string
+        if (in_record && state == QUAL) {
+            qual_line_done();
+            if (qual_len == seq_len) finish_record(); else drop_record();
             return;
         }
         if (state == NAME && store_docs && in_record) res.names.push_back(name);

@@ -38,6 +38,12 @@ def case_files():
     # handled by the host reader (detected on the device): CR LF line ends, FASTQ
     cases["crlf"] = b">c1 x\r\n" + wrap(a, 60).replace(b"\n", b"\r\n") + b"\r\n>c2\r\n" + wrap(b, 60).replace(b"\n", b"\r\n") + b"\r\n"
     cases["fastq"] = b"@q1\n" + a[:20000] + b"\n+\n" + b"I" * 20000 + b"\n@q2 c\n" + b[:15000] + b"\n+q2\n" + b"#" * 15000 + b"\n"
+    # FASTQ corners (kseq.h:205-213): CR LF line ends with multi-line quality, quality characters that look like markers,
+    # a truncated quality string (the record and everything behind it are dropped), EOF inside the '+' line
+    cases["fastq_crlf_multiline"] = (b"@q1\r\n" + wrap(a[:3000], 70).replace(b"\n", b"\r\n") + b"\r\n+\r\n" +
+                                     wrap(b"@>I#" * 750, 70).replace(b"\n", b"\r\n") + b"\r\n@q2\r\n" + b[:500] + b"\r\n+\r\n" + b"I" * 500 + b"\r\n")
+    cases["fastq_truncated_qual"] = b"@q1\n" + a[:2000] + b"\n+\n" + b"I" * 2000 + b"\n@q2\n" + b[:900] + b"\n+\n" + b"I" * 400 + b"\n"
+    cases["fastq_eof_in_plus"] = b"@q1\n" + a[:2000] + b"\n+\n" + b"I" * 2000 + b"\n@q2\n" + b[:900] + b"\n+"
     return cases
 
 
@@ -64,7 +70,7 @@ def test_ingest_logic_matches_reference_and_host_reader(name, emu, ref_bins, dat
     flags = ["-s", "-r", "--print-docs"]
     dev, host = os.path.join(datadir, name + ".idev"), os.path.join(datadir, name + ".ihost")
     r = subprocess.run([emu, "--bits", "32"] + flags + ["-o", dev, fa], check=True, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
-    took = b"ingest: host" if name in ("crlf", "fastq") else b"ingest: device"     # which reader the file must have taken
+    took = b"ingest: host" if name == "crlf" or name.startswith("fastq") else b"ingest: device"     # which reader the file must have taken
     assert took in r.stderr, r.stderr.decode()[-500:]
     env = dict(os.environ, PFB_INGEST="host")
     subprocess.run([emu, "--bits", "32"] + flags + ["-o", host, fa], check=True, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
@@ -90,7 +96,7 @@ def test_ingest_logic_streams(name, how, emu, ref_bins, datadir):
     src, stdin = (fa, None) if how == "gz" else ("-", data)
     dev = os.path.join(datadir, f"{name}_{how}.sdev")
     r = subprocess.run([emu, "--bits", "32", "-s", "-r", "-o", dev, src], input=stdin, check=True, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
-    took = b"ingest: host" if name in ("crlf", "fastq") else b"ingest: device"
+    took = b"ingest: host" if name == "crlf" or name.startswith("fastq") else b"ingest: device"
     assert took in r.stderr, r.stderr.decode()[-500:]
     if ref_bins["pfbwt-f"]:
         ref = os.path.join(datadir, f"{name}_{how}.sref")
