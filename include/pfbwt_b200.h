@@ -164,6 +164,13 @@ uint64_t pfb_get_pending_bases(const pfb_ctx *);
  * `hash % p == 0`): the DEVICE functions the trigger kernel uses are run on n caller-supplied k-mer values;
  * hash_out[i] = wang_hash(kmers[i]), divides_out[i] = 1 iff the kernel's division-free test says p divides it. */
 int pfb_kat_trigger(pfb_ctx *, const uint64_t *kmers, size_t n, uint64_t p, uint64_t *hash_out, uint8_t *divides_out);
+/* pfb_kat_trigger without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same
+ * arguments and results as pfb_kat_trigger; the device scratch pfb_kat_trigger allocates per call (k-mers, hashes, flags)
+ * is a static device array of PFB_KAT_STATIC_MAX k-mers (1088 KB held by every GPU that loads the library).  n above
+ * PFB_KAT_STATIC_MAX fails with PFB_ERR_ARG.  All calls share the array: calls that overlap on one GPU race. */
+#define PFB_KAT_STATIC_MAX 65536
+int pfb_kat_trigger_static(pfb_ctx *, const uint64_t *kmers, size_t n, uint64_t p, uint64_t *hash_out, uint8_t *divides_out);
 int pfb_get_stats(const pfb_ctx *, pfb_stats *);
 int pfb_copy_dict(pfb_ctx *, uint8_t *out /* dict_bytes */);
 int pfb_copy_occ(pfb_ctx *, void *out /* n_words * bits/8 */);

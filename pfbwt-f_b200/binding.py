@@ -17,7 +17,7 @@ EXPORTS = [
     "pfb_copy_bwt", "pfb_copy_sa", "pfb_copy_ssa", "pfb_copy_esa", "pfb_get_docs", "pfb_upload_text",
     "pfb_run_resident", "pfb_release_text", "pfb_clear",
     "pfb_nccl_unique_id", "pfb_shard_init_nccl", "pfb_shard_init_host", "pfb_get_shard_info", "pfb_get_pending_bases",
-    "pfb_kat_trigger", "pfb_add_chunk", "pfb_add_fasta_range", "pfb_save_last_sai", "pfb_build_bwt_to_files", "pfb_build_workspace_bytes", "pfb_write_doc_array", "pfb_device_free_bytes", "pfb_save_parse_async", "pfb_wait_saves",
+    "pfb_kat_trigger", "pfb_kat_trigger_static", "pfb_add_chunk", "pfb_add_fasta_range", "pfb_save_last_sai", "pfb_build_bwt_to_files", "pfb_build_workspace_bytes", "pfb_write_doc_array", "pfb_device_free_bytes", "pfb_save_parse_async", "pfb_wait_saves",
 ]
 
 
@@ -80,6 +80,7 @@ def load():
         getattr(lib, f).argtypes = [vp]
     lib.pfb_append.argtypes = [vp, vp]
     lib.pfb_kat_trigger.argtypes = [vp, vp, C.c_size_t, C.c_uint64, vp, vp]
+    lib.pfb_kat_trigger_static.argtypes = [vp, vp, C.c_size_t, C.c_uint64, vp, vp]
     lib.pfb_save_parse.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
     lib.pfb_load_parse.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
     lib.pfb_save_last_sai.argtypes = [vp, C.c_char_p, C.c_int, C.c_int]
@@ -167,6 +168,14 @@ class Context:
         h = np.empty(k.shape[0], dtype=np.uint64)
         d = np.empty(k.shape[0], dtype=np.uint8)
         self._ck(self.lib.pfb_kat_trigger(self.h, k.ctypes.data, k.shape[0], int(p), h.ctypes.data, d.ctypes.data))
+        return h, d
+
+    def kat_trigger_static(self, kmers, p):
+        """kat_trigger without device allocation: scratch in a static device array, at most KAT_STATIC_MAX k-mers"""
+        k = np.ascontiguousarray(kmers, dtype=np.uint64)
+        h = np.empty(k.shape[0], dtype=np.uint64)
+        d = np.empty(k.shape[0], dtype=np.uint8)
+        self._ck(self.lib.pfb_kat_trigger_static(self.h, k.ctypes.data, k.shape[0], int(p), h.ctypes.data, d.ctypes.data))
         return h, d
 
     def shard_info(self):

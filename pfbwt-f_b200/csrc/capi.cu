@@ -353,3 +353,71 @@ int pfb_release_text(pfb_ctx *c) { CTX_GUARD(c); c->eng.release_text(); return P
 int pfb_clear(pfb_ctx *c) { CTX_GUARD(c); c->eng.clear(); return PFB_OK; }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// pfb_kat_trigger_static: pfb_kat_trigger for callers that may not allocate (no counterpart in the reference).
+// pfb_kat_trigger stages the k-mers, the hashes and the flags in three device buffers
+// it allocates per call; here that scratch is ONE file-scope device array of fixed size, PFB_KAT_STATIC_MAX k-mers
+// (65536 x 17 bytes = 1088 KB), which every GPU that loads the library holds until exit.
+//   * g_kat_scratch names the array for DEVICE code.  In host code the name is only a handle: the device address comes from
+//     cudaGetSymbolAddress, once per device with that device current (kat_scratch_address), and that pointer is what the
+//     kernel gets.
+//   * no cudaMalloc / cudaFree / allocating routine on this path: two copies in, one launch, two copies out on the context's
+//     stream.
+//   * every call uses the same array and finds the previous call's bytes in it.  Nothing has to start at zero: a call
+//     overwrites the first n k-mer slots before the kernel reads them, and the kernel writes the first n hash / flag slots
+//     before they are copied out.  Calls that overlap on one GPU (two contexts, two threads) race on the array.
+static __device__ __align__(256) unsigned char g_kat_scratch[(size_t)PFB_KAT_STATIC_MAX * 17];
+static const size_t KAT_OFF_HASH = (size_t)PFB_KAT_STATIC_MAX * 8, KAT_OFF_FLAG = (size_t)PFB_KAT_STATIC_MAX * 16;
+
+__global__ void __launch_bounds__(256) k_kat_static(const pfb::u64 *__restrict__ kmers, pfb::u64 *__restrict__ hash,
+                                                    pfb::u8 *__restrict__ flag, pfb::u64 n, pfb::DivTest dt) {
+    for (pfb::u64 i = (pfb::u64)blockIdx.x * 256 + threadIdx.x; i < n; i += (pfb::u64)gridDim.x * 256) {
+        const pfb::u64 x = pfb::wang_hash(kmers[i]);
+        hash[i] = x;
+        flag[i] = dt.divides(x) ? 1 : 0;
+    }
+}
+
+// device address of g_kat_scratch on the CURRENT device (looked up once per device)
+static cudaError_t kat_scratch_address(int device, unsigned char **out) {
+    static const int MAXDEV = 64;
+    static unsigned char *ptr[MAXDEV];
+    static std::mutex mu;
+    if (device < 0 || device >= MAXDEV) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptr[device]) {
+        unsigned char *p = nullptr;
+        cudaError_t rc = cudaGetSymbolAddress((void **)&p, g_kat_scratch);
+        if (rc != cudaSuccess) return rc;
+        ptr[device] = p;
+    }
+    *out = ptr[device];
+    return cudaSuccess;
+}
+
+extern "C" int pfb_kat_trigger_static(pfb_ctx *c, const uint64_t *kmers, size_t n, uint64_t p, uint64_t *hash_out, uint8_t *divides_out) {
+    CTX_GUARD(c);
+    if (p == 0 || (n && (!kmers || !hash_out || !divides_out))) return c->eng.fail(PFB_ERR_ARG, "bad argument");
+    if (n > (size_t)PFB_KAT_STATIC_MAX)
+        return c->eng.fail(PFB_ERR_ARG, "pfb_kat_trigger_static: " + std::to_string(n) + " k-mers exceed the static scratch (PFB_KAT_STATIC_MAX = " +
+                                            std::to_string((size_t)PFB_KAT_STATIC_MAX) + "); use pfb_kat_trigger or split the call");
+    if (n == 0) return PFB_OK;
+    unsigned char *base = nullptr;
+    cudaError_t rc = kat_scratch_address(c->eng.device, &base);
+    if (rc != cudaSuccess) return c->eng.fail(PFB_ERR_CUDA, std::string("cudaGetSymbolAddress(g_kat_scratch): ") + cudaGetErrorString(rc));
+    cudaStream_t st = c->eng.ws.st;
+    pfb::u64 *dk = reinterpret_cast<pfb::u64 *>(base), *dh = reinterpret_cast<pfb::u64 *>(base + KAT_OFF_HASH);
+    pfb::u8 *df = base + KAT_OFF_FLAG;
+    const unsigned blocks = (unsigned)((n + 255) / 256);
+    if ((rc = cudaMemcpyAsync(dk, kmers, n * 8, cudaMemcpyHostToDevice, st)) == cudaSuccess) {
+        k_kat_static<<<blocks, 256, 0, st>>>(dk, dh, df, n, pfb::DivTest::make(p));
+        rc = cudaGetLastError();
+    }
+    if (rc == cudaSuccess) rc = cudaMemcpyAsync(hash_out, dh, n * 8, cudaMemcpyDeviceToHost, st);
+    if (rc == cudaSuccess) rc = cudaMemcpyAsync(divides_out, df, n, cudaMemcpyDeviceToHost, st);
+    if (rc == cudaSuccess) rc = cudaStreamSynchronize(st);
+    if (rc != cudaSuccess) return c->eng.fail(PFB_ERR_CUDA, std::string("pfb_kat_trigger_static: ") + cudaGetErrorString(rc));
+    pfb::launch_stats().own++;
+    return PFB_OK;
+}
