@@ -8,7 +8,8 @@
 // padded to a multiple of the 2048-element tile):
 //   key[D]   u64  enumerative code of the first L symbols of the suffix, symbols consumed,
 //                 closed flag, code of the preceding byte (dictkeys.cuh); dropped after the sort
-//   sa[D]    u32  dictionary position of the j-th smallest suffix
+//   sa[D]    DP   dictionary position of the j-th smallest suffix (DP = u32; u64 for a dictionary of 2^32 bytes or more, which
+//                 is always sorted in key ranges of fewer than 2^32 suffixes: indices INTO the sorted arrays stay u32)
 //   meta[D]  u8   preceding-byte code | head | full | valid | hard (emit.cuh)
 //   wc[Dw+2] u64  (word start | ilist base << 32): one 16-byte read gives both ends
 //   wsamp[D/128] u32  word id at every 128th dictionary byte (position -> word)
@@ -95,8 +96,9 @@ PFB_HD inline void load32_unaligned(const u8 *dict, u64 pos, u64 *o) {
 // Long single-symbol runs of the dictionary (poly-A phrases left by --non-acgt-to-a on Mbp N runs, poly-N without it):
 // two suffixes inside such runs share min(remaining run lengths) symbols, which the comparison skips in one step
 // instead of reading them - otherwise ties of millions of symbols would need prefix doubling over the whole dictionary.
-struct RunTable {
-    const u32 *start = nullptr, *end = nullptr;      // maximal runs [start, end) of one byte value, length >= RUN_MIN, ascending
+template <class DP>
+struct RunTableT {
+    const DP *start = nullptr, *end = nullptr;       // maximal runs [start, end) of one byte value, length >= RUN_MIN, ascending
     u32 R = 0;
     PFB_HD inline u64 remaining(u64 pos) const {     // symbols of the run containing pos from pos on (0 if none)
         if (!R || pos < start[0]) return 0;
@@ -107,7 +109,8 @@ struct RunTable {
 };
 static const u64 RUN_BLOCK = 256, RUN_MIN = 3 * RUN_BLOCK;
 
-PFB_HD inline u64 pivot_key(const u8 *dict, u64 D, u64 a, u64 p, int lb, const RunTable &rt) {
+template <class RT>
+PFB_HD inline u64 pivot_key(const u8 *dict, u64 D, u64 a, u64 p, int lb, const RT &rt) {
     const u64 cap = (1ull << lb) - 1;
     u64 l = 0;
     // 8 symbols per step while both windows (and the second aligned word behind them) lie inside the dictionary
@@ -154,7 +157,8 @@ PFB_HD inline u64 pivot_key(const u8 *dict, u64 D, u64 a, u64 p, int lb, const R
 
 // run table of the dictionary: 256-byte blocks of one byte value are found on the device, merged into candidate runs on
 // the host (a handful even for a human genome) and trimmed to their exact ends
-inline void build_run_table(const u8 *dict, u64 D, DevBuf<u32> &rs, DevBuf<u32> &re, u32 *R_out, u64 *longest, Workspace &ws) {
+template <class DP>
+inline void build_run_table(const u8 *dict, u64 D, DevBuf<DP> &rs, DevBuf<DP> &re, u32 *R_out, u64 *longest, Workspace &ws) {
     pfbStream_t st = ws.st;
     *R_out = 0; *longest = 0;
     const u64 nb = D / RUN_BLOCK;
@@ -184,31 +188,31 @@ inline void build_run_table(const u8 *dict, u64 D, DevBuf<u32> &rs, DevBuf<u32> 
     d2h(hb.data(), ub.get(), nu * 4, st);
     d2h(hs.data(), us.get(), nu, st);
     stream_sync(st);
-    std::vector<u32> cs, ce;
+    std::vector<DP> cs, ce;
     std::vector<u8> csym;
     for (u64 i = 0; i < nu;) {
         u64 j = i + 1;
         while (j < nu && hb[j] == hb[j - 1] + 1 && hs[j] == hs[i]) ++j;
-        if (j - i >= RUN_MIN / RUN_BLOCK) { cs.push_back((u32)(hb[i] * RUN_BLOCK)); ce.push_back((u32)((hb[j - 1] + 1) * RUN_BLOCK)); csym.push_back(hs[i]); }
+        if (j - i >= RUN_MIN / RUN_BLOCK) { cs.push_back((DP)((u64)hb[i] * RUN_BLOCK)); ce.push_back((DP)(((u64)hb[j - 1] + 1) * RUN_BLOCK)); csym.push_back(hs[i]); }
         i = j;
     }
     const u32 R = (u32)cs.size();
     if (!R) return;
     rs.alloc(R); re.alloc(R);
     DevBuf<u8> rsym(R);
-    h2d(rs.get(), cs.data(), (size_t)R * 4, st);
-    h2d(re.get(), ce.data(), (size_t)R * 4, st);
+    h2d(rs.get(), cs.data(), (size_t)R * sizeof(DP), st);
+    h2d(re.get(), ce.data(), (size_t)R * sizeof(DP), st);
     h2d(rsym.get(), csym.data(), R, st);
     DevBuf<u64> lmax(1);
     dev_memset(lmax.get(), 0, 8, st);
     {
-        u32 *sp = rs.get(); u32 *ep = re.get(); const u8 *sy = rsym.get(); u64 *lm = lmax.get();
+        DP *sp = rs.get(); DP *ep = re.get(); const u8 *sy = rsym.get(); u64 *lm = lmax.get();
         launch_for(R, st, PFB_LAMBDA(u64 r) {          // exact ends: at most RUN_BLOCK - 1 steps each way
             u64 s = sp[r], e = ep[r];
             const u8 c = sy[r];
             while (s > 0 && dict[s - 1] == c) --s;
             while (e < D && dict[e] == c) ++e;
-            sp[r] = (u32)s; ep[r] = (u32)e;
+            sp[r] = (DP)s; ep[r] = (DP)e;
             atomic_max(lm, e - s);
         });
     }
@@ -217,7 +221,22 @@ inline void build_run_table(const u8 *dict, u64 D, DevBuf<u32> &rs, DevBuf<u32> 
     *R_out = R;
 }
 
-inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, DevBuf<u8> &meta, DevBuf<u32> &cnt, const WordLookup &wl,
+// positions as u32 for prefix doubling (identity for DP = u32)
+inline DevBuf<u32> &sa_as_u32(DevBuf<u32> &sa, DevBuf<u32> &, u64, pfbStream_t) { return sa; }
+inline DevBuf<u32> &sa_as_u32(DevBuf<u64> &sa, DevBuf<u32> &tmp, u64 n, pfbStream_t st) {
+    tmp.alloc(n);
+    const u64 *s = sa.get(); u32 *d = tmp.get();
+    launch_for(n, st, PFB_LAMBDA(u64 j) { d[j] = (u32)s[j]; });
+    return tmp;
+}
+inline void sa_from_u32(DevBuf<u32> &, DevBuf<u32> &, u64, pfbStream_t) {}
+inline void sa_from_u32(DevBuf<u64> &sa, DevBuf<u32> &tmp, u64 n, pfbStream_t st) {
+    const u32 *s = tmp.get(); u64 *d = sa.get();
+    launch_for(n, st, PFB_LAMBDA(u64 j) { d[j] = s[j]; });
+}
+
+template <class DP>
+inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<DP> &sa, DevBuf<u8> &meta, DevBuf<u32> &cnt, const WordLookupT<DP> &wl,
                               bool *reclassify, Workspace &ws, StageTimes &tm, Timer &timer, std::string &err,
                               const ShardSpec *sh = nullptr, u64 *n_sorted = nullptr) {
     pfbStream_t st = ws.st;
@@ -232,8 +251,9 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
     u64 N = D;                       // entries in the sorted array
     {
         DevBuf<u64> key, key_b;
-        DevBuf<u32> val_b;
+        DevBuf<DP> val_b;
         const KeyExtra kx = key_extra_for(L);
+        if (!sh && D > 0xFFFFFFF0ull) { err = "internal: a dictionary of 2^32 bytes or more is sorted in key ranges"; return PFB_ERR_INTERNAL; }
         if (!sh) {
             key.alloc(D); key_b.alloc(D); val_b.alloc(padded(D)); sa.alloc(padded(D));
             k_suffix_keys(dict, D, L, key.get(), wl, pp.occ.get(), w, kx, st);
@@ -265,7 +285,8 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
                 // time-multiplexed form (one GPU sorting one key range after the other): select from all positions
                 const u64 lo = bound(sh->rank) << hshift;
                 const u64 hi = sh->rank + 1 >= sh->world ? ~0ull : bound(sh->rank + 1) << hshift;
-                N = k_suffix_keys_select(dict, D, L, wl, pp.occ.get(), w, kx, lo, hi, key, sa, padded, ws);
+                N = k_suffix_keys_select<DP>(dict, D, L, wl, pp.occ.get(), w, kx, lo, hi, key, sa, padded, ws);
+                if (N > 0xFFFFFFF0ull) { err = "more than 2^32 dictionary suffixes in one key range (more buckets needed)"; return PFB_ERR_LIMIT; }
                 timer.lap("K6 keys (selected)");
             } else {
                 // position-sliced: this rank computes the keys of ITS 1/world of the dictionary positions and routes every
@@ -277,7 +298,7 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
                 for (int r = 0; r <= G; ++r) bnd[(size_t)r] = r >= G ? ~0ull : bound(r) << hshift;
                 const u64 ntiles = (D + KEYS_TILE - 1) / KEYS_TILE;
                 const u64 t0 = ntiles * (u64)g / (u64)G, t1 = ntiles * (u64)(g + 1) / (u64)G;
-                KeyRouter kr;
+                KeyRouterT<DP> kr;
                 kr.dict = dict; kr.D = D; kr.L = L; kr.wl = wl; kr.occ = pp.occ.get(); kr.w = w; kr.kx = kx;
                 kr.bound = bnd; kr.tile0 = t0; kr.ntl = t1 - t0;
                 kr.count(ws);
@@ -285,9 +306,10 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
                 std::vector<u64> mat = sh->comm->gather_u64(kr.counts.data(), G, st);     // mat[s * G + d] = pairs s -> d
                 N = 0;
                 for (int s = 0; s < G; ++s) N += mat[(size_t)s * G + g];
+                if (N > 0xFFFFFFF0ull) { err = "more than 2^32 dictionary suffixes in one rank's key range (use more GPUs)"; return PFB_ERR_LIMIT; }
                 key.alloc(N); sa.alloc(padded(N));
                 std::vector<u64 *> kouts((size_t)G);
-                std::vector<u32 *> iouts((size_t)G);
+                std::vector<DP *> iouts((size_t)G);
                 void *mine[2] = {key.get(), sa.get()};
                 std::vector<void *> peers;
                 if (sh->comm->peer_pointers(mine, 2, peers, st)) {
@@ -297,25 +319,25 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
                         u64 before = 0;                                   // pairs the ranks before this one send to d
                         for (int s = 0; s < g; ++s) before += mat[(size_t)s * G + d];
                         kouts[(size_t)d] = (u64 *)peers[(size_t)d * 2] + before;
-                        iouts[(size_t)d] = (u32 *)peers[(size_t)d * 2 + 1] + before;
+                        iouts[(size_t)d] = (DP *)peers[(size_t)d * 2 + 1] + before;
                     }
                     kr.scatter(kouts.data(), iouts.data(), ws);
                     stream_sync(st);
                     sh->comm->barrier(st);                                // every rank's stores into this rank's buffers have landed
                     u64 got = 0;
                     for (int s = 0; s < G; ++s) if (s != g) got += mat[(size_t)s * G + g];
-                    sh->comm->bytes_moved += got * 12;
+                    sh->comm->bytes_moved += got * (8 + sizeof(DP));
                     timer.lap("K6 keys -> owners (peer stores over NVLink)");
                 } else {
                     const u64 m = kr.destbase[(size_t)G];
                     DevBuf<u64> skey(m);
-                    DevBuf<u32> sidx(m);
+                    DevBuf<DP> sidx(m);
                     for (int d = 0; d < G; ++d) { kouts[(size_t)d] = skey.get() + kr.destbase[(size_t)d]; iouts[(size_t)d] = sidx.get() + kr.destbase[(size_t)d]; }
                     kr.scatter(kouts.data(), iouts.data(), ws);
                     timer.lap("K6 keys (grouped by owner)");
                     std::vector<u64> m8(mat), m4(mat);
                     for (auto &x : m8) x *= 8;
-                    for (auto &x : m4) x *= 4;
+                    for (auto &x : m4) x *= sizeof(DP);
                     sh->comm->all_to_all_v(skey.get(), key.get(), m8.data(), st);
                     sh->comm->all_to_all_v(sidx.get(), sa.get(), m4.data(), st);
                     timer.lap("K6 key exchange (all-to-all)");
@@ -329,7 +351,7 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
         dev_memset(meta.get(), M_HEAD, padded(N) + 64, st);
         if (N == 0) { tm.dict_sort_rounds = 0; return PFB_OK; }
         timer.lap("K6 radix sort");
-        FlagsArgs fa;
+        FlagsArgsT<DP> fa;
         fa.key = key.get(); fa.sa = sa.get(); fa.D = N; fa.meta = meta.get(); fa.cnt = cnt.get(); fa.tilecnt = nullptr;
         fa.kx = kx; fa.wl = wl; fa.w = (u64)w;
         m = sorted_flags_and_open_list(fa, apos, ws);
@@ -361,8 +383,8 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
     const u32 max_pivot_rounds = 64;
     // ... right away when a large part of the dictionary is tied after the main sort (repetitive dictionary), else
     // after two window rounds (short random ties are cheaper to close with windows)
-    RunTable rt;                       // built before the first pivot round
-    DevBuf<u32> run_s, run_e;
+    RunTableT<DP> rt;                  // built before the first pivot round
+    DevBuf<DP> run_s, run_e;
     bool have_rt = false;
     int lb = PIVOT_LBITS;
     auto want_pivot = [&]() { return pivot_ok && pivot_rounds < max_pivot_rounds && (pivot_knob == 1 || rounds >= 2 || m > N / 16); };
@@ -384,7 +406,7 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
         if (L2 < 1) break;   // cannot happen with D < 2^32; doubling below takes over
         const int ebits = enum_bits(L2);
         DevBuf<u64> k2(m), k2b(m);
-        DevBuf<u32> v(m), vb(m);
+        DevBuf<DP> v(m), vb(m);
         // what travels with a suffix (occurrence count, preceding-byte code, valid / full bits) is gathered once and follows
         // the permutation of the small groups instead of being looked up again (position -> word) after every round
         DevBuf<u32> tcnt(m), srcslot(m);
@@ -395,7 +417,7 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
         }
         if (pivot && !have_rt) {
             u32 R = 0; u64 longest = 0;
-            build_run_table(dict, D, run_s, run_e, &R, &longest, ws);
+            build_run_table<DP>(dict, D, run_s, run_e, &R, &longest, ws);
             if (R) { rt.start = run_s.get(); rt.end = run_e.get(); rt.R = R; lb = bits_for(longest + 65536); if (lb < PIVOT_LBITS) lb = PIVOT_LBITS; }
             have_rt = true;
             timer.lap("K6 run table");
@@ -407,14 +429,14 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
         if (pivot) {
             dev_memset(clamped.get(), 0, 4, st);
             DevBuf<u32> hslot(G + 1);                           // list slot of every group's first member
-            const u32 *ap = apos.get(); const u8 *a_ = ah.get(); const u32 *gi = gidx.get(); const u32 *sp = sa.get();
+            const u32 *ap = apos.get(); const u8 *a_ = ah.get(); const u32 *gi = gidx.get(); const DP *sp = sa.get();
             const u32 *dp = adep.get();
-            u64 *kp = k2.get(); u32 *vp = v.get(); u32 *hs = hslot.get(); u32 *cl = clamped.get();
-            const int lbv = lb; const RunTable rtv = rt;
+            u64 *kp = k2.get(); DP *vp = v.get(); u32 *hs = hslot.get(); u32 *cl = clamped.get();
+            const int lbv = lb; const RunTableT<DP> rtv = rt;
             launch_for(m, st, PFB_LAMBDA(u64 a) { if (a_[a]) hs[gi[a]] = (u32)a; });
             launch_for(m, st, PFB_LAMBDA(u64 a) {
                 u64 gid = (u64)gi[a] + a_[a] - 1;
-                u32 idx = sp[ap[a]];
+                DP idx = sp[ap[a]];
                 vp[a] = idx;
                 u32 h = hs[gid];
                 u64 pk = pivot_key(dict, D, (u64)idx + dp[a], (u64)sp[ap[h]] + dp[h], lbv, rtv);
@@ -422,12 +444,12 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
                 kp[a] = (gid << (lbv + 6)) | pk;
             });
         } else {
-            const u32 *ap = apos.get(); const u8 *a_ = ah.get(); const u32 *gi = gidx.get(); const u32 *sp = sa.get();
+            const u32 *ap = apos.get(); const u8 *a_ = ah.get(); const u32 *gi = gidx.get(); const DP *sp = sa.get();
             const u32 *dp = adep.get();
-            u64 *kp = k2.get(); u32 *vp = v.get();
+            u64 *kp = k2.get(); DP *vp = v.get();
             launch_for(m, st, PFB_LAMBDA(u64 a) {
                 u64 gid = (u64)gi[a] + a_[a] - 1;
-                u32 idx = sp[ap[a]];
+                DP idx = sp[ap[a]];
                 vp[a] = idx;
                 EnumKey e = enum_scan(dict, D, (u64)idx + dp[a], L2);
                 kp[a] = (gid << (6 + ebits)) | (e.code << 6) | ((u64)e.consumed << 1) | (e.closed ? 1ull : 0ull);
@@ -448,7 +470,7 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
                 const u8 *a_ = ah.get(); const u32 *gi = gidx.get(); u32 *hs = hslot2.get();
                 const u32 m32 = (u32)m; const u64 G_ = G;
                 launch_for(m + 1, st, PFB_LAMBDA(u64 a) { if (a == m32) hs[G_] = m32; else if (a_[a]) hs[gi[a]] = (u32)a; });
-                const u64 *kp = k2.get(); const u32 *vp = v.get(); u64 *ko = k2b.get(); u32 *vo = vb.get(); u8 *hp = hl.get(); u8 *bf = bigf.get();
+                const u64 *kp = k2.get(); const DP *vp = v.get(); u64 *ko = k2b.get(); DP *vo = vb.get(); u8 *hp = hl.get(); u8 *bf = bigf.get();
                 u32 *srcp = srcslot.get();
                 const u32 cap = SMALL_GROUP;
                 launch_for(m, st, PFB_LAMBDA(u64 a) {
@@ -473,15 +495,15 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
             const u64 mb = compact_indices(bigf.get(), m, bscratch, bslots, ws);
             if (mb) {
                 DevBuf<u64> bk(mb), bkb(mb);
-                DevBuf<u32> bv(mb), bvb(mb);
+                DevBuf<DP> bv(mb), bvb(mb);
                 {
-                    const u32 *bs = bslots.get(); const u64 *kp = k2.get(); const u32 *vp = v.get(); u64 *bkp = bk.get(); u32 *bvp = bv.get();
+                    const u32 *bs = bslots.get(); const u64 *kp = k2.get(); const DP *vp = v.get(); u64 *bkp = bk.get(); DP *bvp = bv.get();
                     launch_for(mb, st, PFB_LAMBDA(u64 i) { bkp[i] = kp[bs[i]]; bvp[i] = vp[bs[i]]; });
                 }
                 sort_pairs(bk, bkb, bv, bvb, mb, kshift, kbits + gbits, ws.sc, st);
                 {
                     // whole groups were taken and the group id leads the key: the i-th sorted pair belongs into the i-th slot
-                    const u32 *bs = bslots.get(); const u64 *bkp = bk.get(); const u32 *bvp = bv.get(); u64 *ko = k2b.get(); u32 *vo = vb.get(); u8 *hp = hl.get();
+                    const u32 *bs = bslots.get(); const u64 *bkp = bk.get(); const DP *bvp = bv.get(); u64 *ko = k2b.get(); DP *vo = vb.get(); u8 *hp = hl.get();
                     u32 *srcp = srcslot.get();
                     launch_for(mb, st, PFB_LAMBDA(u64 i) {
                         const u64 k = bkp[i] >> kshift;
@@ -502,9 +524,9 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
         }
         DevBuf<u8> act2(m);
         {
-            const u32 *ap = apos.get(); const u64 *kp = k2.get(); const u32 *vp = v.get(); const u8 *hp = hl.get();
-            u32 *sp = sa.get(); u8 *ac = act2.get(); u32 *dp = adep.get(); u32 *cp = cnt.get();
-            const WordLookup w3 = wl; const u64 w64 = (u64)w; const int lbw = lb;
+            const u32 *ap = apos.get(); const u64 *kp = k2.get(); const DP *vp = v.get(); const u8 *hp = hl.get();
+            DP *sp = sa.get(); u8 *ac = act2.get(); u32 *dp = adep.get(); u32 *cp = cnt.get();
+            const WordLookupT<DP> w3 = wl; const u64 w64 = (u64)w; const int lbw = lb;
             const u32 *srcp = srcslot.get(); const u32 *tc = tcnt.get(); const u8 *tm_ = tmeta.get();
             launch_for(m, st, PFB_LAMBDA(u64 a) {
                 const bool head = hp[a] & 1, last = (hp[a] & 2) != 0;
@@ -513,7 +535,7 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
                 const u32 from = srcp[a];
                 u32 c, mb_;                                                // what travels with the suffix: count, valid/full bits,
                 if (from != 0xFFFFFFFFu) { c = tc[from]; mb_ = tm_[from] & (u32)(0x0f | M_VALID | M_FULL); }      // and the preceding-byte code
-                else { u32 ib, sl; const u32 vf = suffix_class(w3, vp[a], w64, c, ib, sl); mb_ = (u32)prev_code(dict, vp[a]) | vf; }
+                else { u32 ib, sl; const u32 vf = suffix_class<DP>(w3, vp[a], w64, c, ib, sl); mb_ = (u32)prev_code(dict, vp[a]) | vf; }
                 cp[j] = c;
                 mt[j] = (u8)(mb_ | (head ? M_HEAD : 0));
                 dp[a] += pivot ? pivot_consumed(kp[a], lbw) : ((u32)(kp[a] >> 1) & 31u);   // slot a stays inside its old group: same depth so far
@@ -552,15 +574,19 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<u32> &sa, Dev
             u8 *f = fl.get();
             launch_for(D, st, PFB_LAMBDA(u64 j) { f[j] = (mt[j] & M_HEAD) ? 1 : 0; });
         }
-        ranks_from_flags(sa, fl, rank, D, ws);
-        const WordLookup w2 = wl;
+        // prefix doubling runs over ALL D < 2^32 suffixes (never inside a key range): 32-bit positions, whatever DP is
+        DevBuf<u32> sa_tmp;
+        DevBuf<u32> &sa32 = sa_as_u32(sa, sa_tmp, D, st);
+        ranks_from_flags(sa32, fl, rank, D, ws);
+        const WordLookupT<DP> w2 = wl;
         u32 dr = 0;
-        int rc = prefix_doubling(sa, rank, fl, D, h, PFB_LAMBDA(u32 idx, u64 hh) {
-            return w2.suflen(w2.word(idx), idx) < hh;   // EndOfWord already inside the compared prefix
+        int rc = prefix_doubling(sa32, rank, fl, D, h, PFB_LAMBDA(u32 idx, u64 hh) {
+            return w2.suflen(w2.word((DP)idx), (DP)idx) < hh;   // EndOfWord already inside the compared prefix
         }, ws, &dr, err);
         if (rc) return rc;
+        sa_from_u32(sa, sa_tmp, D, st);
         rounds += dr;
-        const u32 *sp = sa.get(); const u8 *f = fl.get();
+        const DP *sp = sa.get(); const u8 *f = fl.get();
         launch_for(D, st, PFB_LAMBDA(u64 j) { mt[j] = (u8)(prev_code(dict, sp[j]) | (f[j] ? M_HEAD : 0)); });
         *reclassify = true;
         timer.lap("K6 prefix doubling");
@@ -619,6 +645,10 @@ inline u64 count_runs(const u8 *b, u64 len, Workspace &ws) {
 #endif
 }
 
+// what the emission kernels look positions up with: 32-bit positions and their tables, or nothing (ibase[] is filled)
+inline void set_emit_lookup(EmitArgs &ea, const u32 *sa, const WordLookupT<u32> &wl) { ea.sa = sa; ea.wl = wl; }
+inline void set_emit_lookup(EmitArgs &ea, const u64 *, const WordLookupT<u64> &) { ea.sa = nullptr; ea.wl = WordLookupT<u32>(); }
+
 template <int U>
 PFB_HD inline void store_sa(u8 *sa_out, u64 x, u64 v) {
     if (U == 4) reinterpret_cast<u32 *>(sa_out)[x] = (u32)v;
@@ -637,7 +667,49 @@ struct BucketCarry {
     u64 easy = 0, hard = 0;
     bool have_last = false; u8 last_byte = 0; u64 last_sa = 0;     // the last position emitted: the next bucket decides whether it ends a run
 };
-template <int U>
+// word tables of the position -> word lookup: (start | first ilist slot - 1 << 32) packed for 32-bit positions, two arrays for 64-bit
+struct WordTables { DevBuf<u64> wc; DevBuf<u32> cm; DevBuf<u32> wsamp; };
+inline WordLookupT<u32> make_word_lookup(WordTables &t, const DeviceParse &pp, u32 tag, Workspace &ws) {
+    (void)tag;
+    pfbStream_t st = ws.st;
+    const u64 D = pp.dsize, Dw = pp.Dw;
+    t.wc.alloc(Dw + 2); t.wsamp.alloc((D + 127) / 128);
+    DevBuf<u32> cum(Dw + 1);
+    exclusive_sum<u32, u32>(pp.occ.get(), cum.get(), Dw, ws.sc, st);
+    const u32 *occ = pp.occ.get(); const u64 *wstart = pp.wstart.get(); u32 *cm = cum.get(); u64 *wp = t.wc.get();
+    launch_for(Dw + 2, st, PFB_LAMBDA(u64 d) {
+        u64 c = d < Dw ? cm[d] : (Dw ? (u64)cm[Dw - 1] + occ[Dw - 1] : 0);
+        u64 s = d <= Dw ? wstart[d] : 0xFFFFFFFFull;
+        wp[d] = s | (c << 32);
+    });
+    u32 *wsm = t.wsamp.get();
+    const u32 Dw32 = (u32)Dw;
+    launch_for((D + 127) / 128, st, PFB_LAMBDA(u64 b) { wsm[b] = word_of(wstart, Dw32 + 1, b * 128); });
+    WordLookupT<u32> wl;
+    wl.wc = t.wc.get(); wl.wsamp = t.wsamp.get(); wl.Dw = (u32)Dw;
+    return wl;
+}
+inline WordLookupT<u64> make_word_lookup(WordTables &t, const DeviceParse &pp, u64 tag, Workspace &ws) {
+    (void)tag;
+    pfbStream_t st = ws.st;
+    const u64 D = pp.dsize, Dw = pp.Dw;
+    t.wc.alloc(Dw + 2); t.cm.alloc(Dw + 2); t.wsamp.alloc((D + 127) / 128);
+    DevBuf<u32> cum(Dw + 1);
+    exclusive_sum<u32, u32>(pp.occ.get(), cum.get(), Dw, ws.sc, st);
+    const u32 *occ = pp.occ.get(); const u64 *wstart = pp.wstart.get(); const u32 *cs = cum.get(); u64 *wp = t.wc.get(); u32 *cp = t.cm.get();
+    launch_for(Dw + 2, st, PFB_LAMBDA(u64 d) {
+        cp[d] = d < Dw ? cs[d] : (Dw ? cs[Dw - 1] + occ[Dw - 1] : 0u);
+        wp[d] = d <= Dw ? wstart[d] : ~0ull;
+    });
+    u32 *wsm = t.wsamp.get();
+    const u32 Dw32 = (u32)Dw;
+    launch_for((D + 127) / 128, st, PFB_LAMBDA(u64 b) { wsm[b] = word_of(wstart, Dw32 + 1, b * 128); });
+    WordLookupT<u64> wl;
+    wl.ws = t.wc.get(); wl.cm = t.cm.get(); wl.wsamp = t.wsamp.get(); wl.Dw = (u32)Dw;
+    return wl;
+}
+
+template <int U, class DP>
 inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, bool want_rssa, DeviceBwt &out, Workspace &ws,
                        StageTimes &tm, std::string &err, Comm *comm, const ShardSpec *bucket = nullptr, BucketCarry *carry = nullptr) {
     pfbStream_t st = ws.st;
@@ -646,33 +718,20 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
     const bool any_sa = want_sa || want_rssa;
     if (!pp.has_parse_bwt) { err = "parse BWT (bwlast/ilist) not available"; return PFB_ERR_ARG; }
     if (any_sa && pp.bwsai.size() == 0) { err = "bwsai not available"; return PFB_ERR_ARG; }
-    if (D > 0xFFFFFFF0ull) { err = "dictionary larger than 2^32 bytes is not supported yet"; return PFB_ERR_LIMIT; }
+    if (sizeof(DP) == 4 && D > 0xFFFFFFF0ull) { err = "internal: 32-bit positions for a dictionary of 2^32 bytes or more"; return PFB_ERR_INTERNAL; }
+    if (D > 0xFFFFFFF0ull && !comm && !(bucket && carry)) { err = "a dictionary of 2^32 bytes or more is built in key ranges (bucketed build)"; return PFB_ERR_LIMIT; }
     Timer timer(st);
 
     // word tables: wc[d] = (start, first ilist slot - 1), sample table for position -> word
-    DevBuf<u64> wc(Dw + 2);
-    DevBuf<u32> wsamp((D + 127) / 128);
-    {
-        DevBuf<u32> cum(Dw + 1);
-        exclusive_sum<u32, u32>(pp.occ.get(), cum.get(), Dw, ws.sc, st);
-        const u32 *occ = pp.occ.get(); const u32 *wstart = pp.wstart.get(); u32 *cm = cum.get(); u64 *wp = wc.get();
-        launch_for(Dw + 2, st, PFB_LAMBDA(u64 d) {
-            u64 c = d < Dw ? cm[d] : (Dw ? (u64)cm[Dw - 1] + occ[Dw - 1] : 0);
-            u64 s = d <= Dw ? (u64)wstart[d] : 0xFFFFFFFFull;
-            wp[d] = s | (c << 32);
-        });
-        u32 *wsm = wsamp.get();
-        const u32 Dw32 = (u32)Dw;
-        launch_for((D + 127) / 128, st, PFB_LAMBDA(u64 b) { wsm[b] = word_of(wstart, Dw32 + 1, (u32)(b * 128)); });
-    }
-    WordLookup wl;
-    wl.wc = wc.get(); wl.wsamp = wsamp.get(); wl.Dw = (u32)Dw;
-    timer.lap("K7 word tables");
+    WordTables wtab;
+    const WordLookupT<DP> wl = make_word_lookup(wtab, pp, DP(0), ws);
+    timer.lap(sizeof(DP) == 8 ? "K7 word tables (64-bit dictionary positions)" : "K7 word tables");
 
     // K6 dictionary suffix sort -------------------------------------------------------
-    DevBuf<u32> sa;
+    DevBuf<DP> sa;
     DevBuf<u8> meta;
     DevBuf<u32> cnt, ibase, slen;
+    const bool wide = sizeof(DP) == 8;     // the emission kernels never see 64-bit positions: ibase[] replaces their lookup
     bool reclassify = false;
     ShardSpec spec;
     if (comm) { spec.rank = comm->rank; spec.world = comm->world; spec.comm = comm; }
@@ -682,7 +741,7 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
     u64 N = D;                          // sorted entries held by this rank (all D without a communicator)
     int rc;
     try {
-        rc = sort_dict_suffixes(pp, (int)w, sa, meta, cnt, wl, &reclassify, ws, tm, timer, err, ranged ? &spec : nullptr, &N);
+        rc = sort_dict_suffixes<DP>(pp, (int)w, sa, meta, cnt, wl, &reclassify, ws, tm, timer, err, ranged ? &spec : nullptr, &N);
     } catch (const Error &e) {
         if (!comm) throw;
         rc = e.code; err = e.what();
@@ -703,13 +762,13 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
     // with SA output (or after prefix doubling) a lookup pass adds ilist base and suffix length.
     const u64 nt = tiles_of(N);
     DevBuf<u64> tilesum(nt + 1), tilebase(nt + 1);
-    if (any_sa) { ibase.alloc(padded(N)); slen.alloc(padded(N)); }
+    if (any_sa || wide) { ibase.alloc(padded(N)); slen.alloc(padded(N)); }
     if (N == 0) {
-    } else if (any_sa || reclassify) {
-        ClassifyArgs ca;
+    } else if (any_sa || reclassify || wide) {
+        ClassifyArgsT<DP> ca;
         ca.sa = sa.get(); ca.meta = meta.get(); ca.wl = wl; ca.D = N; ca.w = w;
         ca.cnt = cnt.get(); ca.tilesum = tilesum.get(); ca.ibase = ibase.get(); ca.sl = slen.get();
-        k_classify(ca, any_sa, st);
+        k_classify<DP>(ca, any_sa || wide, st);
         timer.lap("K7 classify (word lookup)");
     } else {
         k_tile_sums(cnt.get(), N, tilesum.get(), st);
@@ -748,8 +807,9 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
         dev_memset(ctr32.get(), 0, 8, st);
         dev_memset(ctr64.get(), 0, 8, st);
         EmitArgs ea;
-        ea.meta = meta.get(); ea.cnt = cnt.get(); ea.sa = sa.get(); ea.ibase = ibase.get(); ea.sl = slen.get();
-        ea.wl = wl; ea.tilebase = tilebase.get(); ea.D = N;
+        ea.meta = meta.get(); ea.cnt = cnt.get(); ea.ibase = ibase.get(); ea.sl = slen.get();
+        set_emit_lookup(ea, sa.get(), wl);
+        ea.tilebase = tilebase.get(); ea.D = N;
         ea.ilist = pp.ilist.get(); ea.bwlast = pp.bwlast.get(); ea.bwsai = pp.bwsai.get();
         ea.bwt = out.bwt.get(); ea.sa_out = out.sa.get();
         ea.small_lim = HARD_SMALL; ea.mid_lim = HARD_MID;
@@ -954,8 +1014,13 @@ inline int build_bwt_t(const DeviceParse &pp, const Params &prm, bool want_sa, b
 
 inline int build_bwt(const DeviceParse &pp, const Params &prm, bool want_sa, bool want_rssa, DeviceBwt &out, Workspace &ws,
                      StageTimes &tm, std::string &err, Comm *comm = nullptr, const ShardSpec *bucket = nullptr, BucketCarry *carry = nullptr) {
-    return prm.bits == 64 ? build_bwt_t<8>(pp, prm, want_sa, want_rssa, out, ws, tm, err, comm, bucket, carry)
-                          : build_bwt_t<4>(pp, prm, want_sa, want_rssa, out, ws, tm, err, comm, bucket, carry);
+    // positions inside the dictionary: 32-bit below 2^32 bytes, 64-bit above (PFB_DICT64=1: test knob, 64-bit at any size)
+    static const bool force64 = getenv("PFB_DICT64") && atoi(getenv("PFB_DICT64")) != 0;
+    if (pp.dsize > 0xFFFFFFF0ull || force64)
+        return prm.bits == 64 ? build_bwt_t<8, u64>(pp, prm, want_sa, want_rssa, out, ws, tm, err, comm, bucket, carry)
+                              : build_bwt_t<4, u64>(pp, prm, want_sa, want_rssa, out, ws, tm, err, comm, bucket, carry);
+    return prm.bits == 64 ? build_bwt_t<8, u32>(pp, prm, want_sa, want_rssa, out, ws, tm, err, comm, bucket, carry)
+                          : build_bwt_t<4, u32>(pp, prm, want_sa, want_rssa, out, ws, tm, err, comm, bucket, carry);
 }
 
 }  // namespace pfb

@@ -40,8 +40,10 @@ static const int KEY_MAX_SYMS = 26;     // N_26 < 2^54
 PFB_HD inline u64 enum_count(int L) { return (7ull * (1ull << (2 * L)) - 4ull) / 3ull; }   // N_L
 inline int enum_bits(int L) { return bits_for(enum_count(L) - 1); }
 
-// position -> (word, suffix length) through the sample table
-struct WordLookup {
+// position -> (word, suffix length) through the sample table.  DP = type of a dictionary position: u32 while the
+// dictionary has fewer than 2^32 bytes, u64 beyond (pfbwt-f64 indexes the dictionary with 64-bit uint_t, gsa/gsacak.h:44-58)
+template <class DP> struct WordLookupT;
+template <> struct WordLookupT<u32> {
     const u64 *wc;      // Dw+2 entries, low 32 bits = word start; wc[Dw] = D-1, wc[Dw+1] = 2^32-1
     const u32 *wsamp;
     u32 Dw;
@@ -55,6 +57,21 @@ struct WordLookup {
     // length of the suffix starting at idx inside word d, EndOfWord excluded (0 for the EndOfDict slot)
     PFB_HD inline u64 suflen(u32 d, u32 idx) const { return d < Dw ? (u64)((u32)wc[d + 1] - 1 - idx) : 0; }
 };
+template <> struct WordLookupT<u64> {
+    const u64 *ws;      // Dw+2 word starts; ws[Dw] = D-1, ws[Dw+1] = 2^64-1
+    const u32 *cm;      // Dw+2 first ilist slots - 1
+    const u32 *wsamp;
+    u32 Dw;
+    PFB_HD inline u32 word(u64 idx) const {
+        u32 d = wsamp[idx >> 7];
+        while (ws[d + 1] <= idx) ++d;
+        return d;
+    }
+    PFB_HD inline u64 start(u32 d) const { return ws[d]; }
+    PFB_HD inline u32 cum(u32 d) const { return cm[d]; }
+    PFB_HD inline u64 suflen(u32 d, u64 idx) const { return d < Dw ? ws[d + 1] - 1 - idx : 0; }
+};
+typedef WordLookupT<u32> WordLookup;
 
 // The bits of a key above the code carry what the assembly needs to know about the suffix, so that
 // the sorted order can be classified without a random position -> word lookup per suffix:
@@ -144,18 +161,20 @@ static const int KEYS_TILE = 2048;
 //   (tiles [tile0, tile0 + ntl)) and routes every valid suffix to the rank that owns its code range (bound[d] <= code <
 //   bound[d+1]); 4 counts per (destination, tile), 5 writes the pairs grouped by destination, dictionary order inside
 static const int KEY_MAX_DEST = 64;
-struct KeySelect {
+template <class DP>
+struct KeySelectT {
     u64 lo = 0, hi = ~0ull;       // code range
     u64 *hist = nullptr; int hshift = 0; u32 tile_stride = 1;
     u32 *tilecnt = nullptr; const u64 *tilebase = nullptr;
-    u64 *key_out = nullptr; u32 *idx_out = nullptr;
+    u64 *key_out = nullptr; DP *idx_out = nullptr;
     u64 tile0 = 0, ntl = 0;       // modes 4 / 5: first tile and number of tiles of this rank's position slice
     int nd = 0;                   // destinations
     u64 bound[KEY_MAX_DEST + 1];  // bound[0] = 0 <= ... <= bound[nd] = ~0
     // mode 5: where destination d's pairs go - a staging buffer of this rank, or the receive buffer of rank d itself mapped
     // over NVLink (the part this rank contributes) - and tilebase[d * ntl] (pairs for destinations before d)
-    u64 *key_outs[KEY_MAX_DEST]; u32 *idx_outs[KEY_MAX_DEST]; u64 destbase[KEY_MAX_DEST];
+    u64 *key_outs[KEY_MAX_DEST]; DP *idx_outs[KEY_MAX_DEST]; u64 destbase[KEY_MAX_DEST];
 };
+typedef KeySelectT<u32> KeySelect;
 PFB_HD inline int key_dest(const u64 *bound, int nd, u64 code) {      // largest d with bound[d] <= code
     int lo = 0, hi = nd;
     while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (bound[mid] <= code) lo = mid; else hi = mid; }
@@ -185,9 +204,9 @@ PFB_HD inline u32 key_pack8(u64 x) {
     return (u32)a | (stops << 16) | (ends << 24);
 }
 #ifndef PFB_EMU
-template <int MODE>
+template <int MODE, class DP>
 __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict__ dict, u64 D, int L, u64 *__restrict__ key,
-                                                            WordLookup wl, const u32 *__restrict__ occ, int w, KeyExtra kx, KeySelect ks) {
+                                                            WordLookupT<DP> wl, const u32 *__restrict__ occ, int w, KeyExtra kx, KeySelectT<DP> ks) {
     __shared__ __align__(16) u8 sb[KEYS_TILE + 48];
     __shared__ u64 sk[KEYS_TILE + KEYS_TILE / 8];      // one pad slot per 8 keys: a thread's 8 consecutive keys spread over banks
     const u64 tile = MODE == 1 ? (u64)blockIdx.x * ks.tile_stride : MODE >= 4 ? ks.tile0 + (u64)blockIdx.x : (u64)blockIdx.x;
@@ -230,7 +249,7 @@ __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict
     }
     // word of the thread's first position (one sampled lookup per 8 positions); later positions add
     // the EndOfWord bytes passed
-    u32 d = (base + (u64)i0 < D) ? wl.word((u32)(base + (u64)i0)) : wl.Dw;
+    u32 d = (base + (u64)i0 < D) ? wl.word((DP)(base + (u64)i0)) : wl.Dw;
     u32 selmask = 0;
     u64 dstv = ~0ull;                       // modes 4 / 5: destination of each of the 8 positions, one byte each (0xff = none)
     u64 mykeys[(MODE == 3 || MODE == 5) ? 8 : 1];
@@ -305,7 +324,7 @@ __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict
             // unit-stride stores: towards a peer GPU these are full 128-byte NVLink writes instead of scattered 8-byte ones
             __shared__ u32 dstart[KEY_MAX_DEST + 1];
             __shared__ u64 dglob[KEY_MAX_DEST];
-            __shared__ u32 sidx[MODE == 5 ? KEYS_TILE : 1];
+            __shared__ DP sidx[MODE == 5 ? KEYS_TILE : 1];
             __shared__ u8 sdst[MODE == 5 ? KEYS_TILE : 1];
             if (threadIdx.x == 0) {
                 u32 run = 0;
@@ -327,7 +346,7 @@ __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict
                 for (int k = 0; k < wid; ++k) wb += rsum[k][dd];
                 const u32 q = dstart[dd] + wb + offp[p];
                 sk[q] = mykeys[MODE == 5 ? p : 0];
-                sidx[MODE == 5 ? q : 0] = (u32)(base + (u64)(i0 + p));
+                sidx[MODE == 5 ? q : 0] = (DP)(base + (u64)(i0 + p));
                 sdst[MODE == 5 ? q : 0] = (u8)dd;
             }
             __syncthreads();
@@ -357,7 +376,7 @@ __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict
             u64 o = ks.tilebase[blockIdx.x] + before + inc - mine;
 #pragma unroll
             for (int p = 0; p < 8; ++p)
-                if (selmask & (1u << p)) { ks.key_out[o] = mykeys[MODE == 3 ? p : 0]; ks.idx_out[o] = (u32)(base + (u64)(i0 + p)); ++o; }
+                if (selmask & (1u << p)) { ks.key_out[o] = mykeys[MODE == 3 ? p : 0]; ks.idx_out[o] = (DP)(base + (u64)(i0 + p)); ++o; }
         }
     }
 }
@@ -365,20 +384,21 @@ __global__ void __launch_bounds__(256) k_suffix_keys_kernel(const u8 *__restrict
 
 // keys of all D dictionary positions, L <= KEY_MAX_SYMS symbols per key (the identity permutation is
 // implied: the radix sort's first pass takes value = position)
-inline void k_suffix_keys(const u8 *dict, u64 D, int L, u64 *key, const WordLookup &wl, const u32 *occ, int w, const KeyExtra &kx,
+template <class DP>
+inline void k_suffix_keys(const u8 *dict, u64 D, int L, u64 *key, const WordLookupT<DP> &wl, const u32 *occ, int w, const KeyExtra &kx,
                           pfbStream_t st) {
 #ifdef PFB_EMU
     (void)st;
     for (u64 i = 0; i < D; ++i) {
         EnumKey e = enum_scan(dict, D, i, L);
-        u32 d = wl.word((u32)i);
-        bool valid = wl.suflen(d, (u32)i) > (u64)w;
-        bool full = valid && (u32)i == wl.start(d);
+        u32 d = wl.word((DP)i);
+        bool valid = wl.suflen(d, (DP)i) > (u64)w;
+        bool full = valid && (DP)i == wl.start(d);
         key[i] = pack_key(e.code, e.consumed, e.closed, (u32)prev_code(dict, i)) | kx.pack(valid ? occ[d] : 0, full);
     }
 #else
     if (D == 0) return;
-    k_suffix_keys_kernel<0><<<(unsigned)((D + KEYS_TILE - 1) / KEYS_TILE), 256, 0, st>>>(dict, D, L, key, wl, occ, w, kx, KeySelect());
+    k_suffix_keys_kernel<0, DP><<<(unsigned)((D + KEYS_TILE - 1) / KEYS_TILE), 256, 0, st>>>(dict, D, L, key, wl, occ, w, kx, KeySelectT<DP>());
     PFB_CUDA_CHECK(cudaGetLastError());
     launch_stats().own++;
 #endif
@@ -386,52 +406,54 @@ inline void k_suffix_keys(const u8 *dict, u64 D, int L, u64 *key, const WordLook
 
 // ---- range-restricted keys (multi-GPU path): only VALID suffixes (length > w; the others emit
 // nothing and cannot tie with a valid one) whose code lies in [lo, hi) are handed to the sort ----
-PFB_HD inline bool key_is_valid(const WordLookup &wl, u32 i, int w, u32 &d) {
+template <class DP>
+PFB_HD inline bool key_is_valid(const WordLookupT<DP> &wl, DP i, int w, u32 &d) {
     d = wl.word(i);
     return d < wl.Dw && wl.suflen(d, i) > (u64)w;
 }
 // weighted histogram (4 + occurrences per valid suffix: sort work + emission work) of code >> hshift.
 // The CUDA build samples every `stride`-th tile: splitters only have to balance, not to be exact.
-inline void k_suffix_key_hist(const u8 *dict, u64 D, int L, const WordLookup &wl, const u32 *occ, int w, const KeyExtra &kx,
+template <class DP>
+inline void k_suffix_key_hist(const u8 *dict, u64 D, int L, const WordLookupT<DP> &wl, const u32 *occ, int w, const KeyExtra &kx,
                               u64 *hist, int hshift, pfbStream_t st) {
 #ifdef PFB_EMU
     (void)st; (void)kx;
     for (u64 i = 0; i < D; ++i) {
         u32 d;
-        if (!key_is_valid(wl, (u32)i, w, d)) continue;
+        if (!key_is_valid<DP>(wl, (DP)i, w, d)) continue;
         EnumKey e = enum_scan(dict, D, i, L);
         hist[e.code >> hshift] += 4ull + occ[d];
     }
 #else
     if (D == 0) return;
     const u64 nt = (D + KEYS_TILE - 1) / KEYS_TILE;
-    KeySelect ks;
+    KeySelectT<DP> ks;
     ks.hist = hist; ks.hshift = hshift;
     ks.tile_stride = nt > 16384 ? (u32)(nt / 16384) : 1u;
-    k_suffix_keys_kernel<1><<<(unsigned)((nt + ks.tile_stride - 1) / ks.tile_stride), 256, 0, st>>>(dict, D, L, nullptr, wl, occ, w, kx, ks);
+    k_suffix_keys_kernel<1, DP><<<(unsigned)((nt + ks.tile_stride - 1) / ks.tile_stride), 256, 0, st>>>(dict, D, L, nullptr, wl, occ, w, kx, ks);
     PFB_CUDA_CHECK(cudaGetLastError());
     launch_stats().own++;
 #endif
 }
 // selected (key, position) pairs in dictionary order; returns how many.  key_out / idx_out are (re)allocated.
-template <class WS>
-inline u64 k_suffix_keys_select(const u8 *dict, u64 D, int L, const WordLookup &wl, const u32 *occ, int w, const KeyExtra &kx,
-                                u64 lo, u64 hi, DevBuf<u64> &key_out, DevBuf<u32> &idx_out, u64 (*pad)(u64), WS &ws) {
+template <class DP, class WS>
+inline u64 k_suffix_keys_select(const u8 *dict, u64 D, int L, const WordLookupT<DP> &wl, const u32 *occ, int w, const KeyExtra &kx,
+                                u64 lo, u64 hi, DevBuf<u64> &key_out, DevBuf<DP> &idx_out, u64 (*pad)(u64), WS &ws) {
     pfbStream_t st = ws.st;
 #ifdef PFB_EMU
-    std::vector<u64> ks_; std::vector<u32> is_;
+    std::vector<u64> ks_; std::vector<DP> is_;
     for (u64 i = 0; i < D; ++i) {
         u32 d;
-        if (!key_is_valid(wl, (u32)i, w, d)) continue;
+        if (!key_is_valid<DP>(wl, (DP)i, w, d)) continue;
         EnumKey e = enum_scan(dict, D, i, L);
         if (e.code < lo || e.code >= hi) continue;
-        bool full = (u32)i == wl.start(d);
+        bool full = (DP)i == wl.start(d);
         ks_.push_back(pack_key(e.code, e.consumed, e.closed, (u32)prev_code(dict, i)) | kx.pack(occ[d], full));
-        is_.push_back((u32)i);
+        is_.push_back((DP)i);
     }
     const u64 m = ks_.size();
     key_out.alloc(m); idx_out.alloc(pad(m));
-    if (m) { memcpy(key_out.get(), ks_.data(), m * 8); memcpy(idx_out.get(), is_.data(), m * 4); }
+    if (m) { memcpy(key_out.get(), ks_.data(), m * 8); memcpy(idx_out.get(), is_.data(), m * sizeof(DP)); }
     (void)st;
     return m;
 #else
@@ -439,9 +461,9 @@ inline u64 k_suffix_keys_select(const u8 *dict, u64 D, int L, const WordLookup &
     if (nt == 0) { key_out.alloc(0); idx_out.alloc(pad(0)); return 0; }
     DevBuf<u32> tcnt(nt + 1);
     DevBuf<u64> tbase(nt + 1);
-    KeySelect ks;
+    KeySelectT<DP> ks;
     ks.lo = lo; ks.hi = hi; ks.tilecnt = tcnt.get();
-    k_suffix_keys_kernel<2><<<(unsigned)nt, 256, 0, st>>>(dict, D, L, nullptr, wl, occ, w, kx, ks);
+    k_suffix_keys_kernel<2, DP><<<(unsigned)nt, 256, 0, st>>>(dict, D, L, nullptr, wl, occ, w, kx, ks);
     PFB_CUDA_CHECK(cudaGetLastError());
     dev_memset(tcnt.get() + nt, 0, 4, st);
     exclusive_sum<u32, u64>(tcnt.get(), tbase.get(), nt + 1, ws.sc, st);
@@ -449,7 +471,7 @@ inline u64 k_suffix_keys_select(const u8 *dict, u64 D, int L, const WordLookup &
     key_out.alloc(m); idx_out.alloc(pad(m));
     if (m) {
         ks.tilebase = tbase.get(); ks.key_out = key_out.get(); ks.idx_out = idx_out.get();
-        k_suffix_keys_kernel<3><<<(unsigned)nt, 256, 0, st>>>(dict, D, L, nullptr, wl, occ, w, kx, ks);
+        k_suffix_keys_kernel<3, DP><<<(unsigned)nt, 256, 0, st>>>(dict, D, L, nullptr, wl, occ, w, kx, ks);
         PFB_CUDA_CHECK(cudaGetLastError());
     }
     launch_stats().own += 2;
@@ -464,17 +486,18 @@ inline u64 k_suffix_keys_select(const u8 *dict, u64 D, int L, const WordLookup &
 //   scatter()  keys again, every pair written to its place: key_outs[d] / idx_outs[d] point at the start of THIS rank's
 //              part of destination d's pairs - inside a local staging buffer, or inside rank d's receive buffer mapped over
 //              NVLink (the stores of the key kernel are then the exchange).  A destination's part is in dictionary order.
-struct KeyRouter {
-    const u8 *dict; u64 D; int L; WordLookup wl; const u32 *occ; int w; KeyExtra kx;
+template <class DP>
+struct KeyRouterT {
+    const u8 *dict; u64 D; int L; WordLookupT<DP> wl; const u32 *occ; int w; KeyExtra kx;
     std::vector<u64> bound; u64 tile0 = 0, ntl = 0;
     std::vector<u64> counts, destbase;        // pairs for destination d / pairs for the destinations before d
 #ifdef PFB_EMU
     std::vector<std::vector<u64>> ks_;
-    std::vector<std::vector<u32>> is_;
+    std::vector<std::vector<DP>> is_;
 #else
     DevBuf<u32> tcnt;
     DevBuf<u64> tbase;
-    KeySelect ks;
+    KeySelectT<DP> ks;
 #endif
     template <class WS>
     void count(WS &ws) {
@@ -483,16 +506,16 @@ struct KeyRouter {
         counts.assign((size_t)nd, 0); destbase.assign((size_t)nd + 1, 0);
 #ifdef PFB_EMU
         (void)st;
-        ks_.assign((size_t)nd, std::vector<u64>()); is_.assign((size_t)nd, std::vector<u32>());
+        ks_.assign((size_t)nd, std::vector<u64>()); is_.assign((size_t)nd, std::vector<DP>());
         const u64 p0 = tile0 * KEYS_TILE, p1 = (tile0 + ntl) * KEYS_TILE < D ? (tile0 + ntl) * KEYS_TILE : D;
         for (u64 i = p0; i < p1; ++i) {
             u32 d;
-            if (!key_is_valid(wl, (u32)i, w, d)) continue;
+            if (!key_is_valid<DP>(wl, (DP)i, w, d)) continue;
             EnumKey e = enum_scan(dict, D, i, L);
             const int dst = key_dest(bound.data(), nd, e.code);
-            bool full = (u32)i == wl.start(d);
+            bool full = (DP)i == wl.start(d);
             ks_[(size_t)dst].push_back(pack_key(e.code, e.consumed, e.closed, (u32)prev_code(dict, i)) | kx.pack(occ[d], full));
-            is_[(size_t)dst].push_back((u32)i);
+            is_[(size_t)dst].push_back((DP)i);
         }
         for (int d = 0; d < nd; ++d) { counts[(size_t)d] = ks_[(size_t)d].size(); destbase[(size_t)d + 1] = destbase[(size_t)d] + counts[(size_t)d]; }
 #else
@@ -500,11 +523,11 @@ struct KeyRouter {
         const u64 cells = (u64)nd * ntl;
         tcnt.alloc(cells + 1); tbase.alloc(cells + 1);
         DevBuf<u64> ends((size_t)nd + 1);
-        ks = KeySelect();
+        ks = KeySelectT<DP>();
         ks.tile0 = tile0; ks.ntl = ntl; ks.nd = nd;
         for (int d = 0; d <= nd; ++d) ks.bound[d] = bound[(size_t)d];
         ks.tilecnt = tcnt.get();
-        k_suffix_keys_kernel<4><<<(unsigned)ntl, 256, 0, st>>>(dict, D, L, nullptr, wl, occ, w, kx, ks);
+        k_suffix_keys_kernel<4, DP><<<(unsigned)ntl, 256, 0, st>>>(dict, D, L, nullptr, wl, occ, w, kx, ks);
         PFB_CUDA_CHECK(cudaGetLastError());
         launch_stats().own++;
         dev_memset(tcnt.get() + cells, 0, 4, st);
@@ -519,19 +542,19 @@ struct KeyRouter {
 #endif
     }
     template <class WS>
-    void scatter(u64 *const *key_outs, u32 *const *idx_outs, WS &ws) {
+    void scatter(u64 *const *key_outs, DP *const *idx_outs, WS &ws) {
         pfbStream_t st = ws.st;
         const int nd = (int)bound.size() - 1;
 #ifdef PFB_EMU
         (void)st;
         for (int d = 0; d < nd; ++d)
-            if (counts[(size_t)d]) { memcpy(key_outs[d], ks_[(size_t)d].data(), counts[(size_t)d] * 8); memcpy(idx_outs[d], is_[(size_t)d].data(), counts[(size_t)d] * 4); }
+            if (counts[(size_t)d]) { memcpy(key_outs[d], ks_[(size_t)d].data(), counts[(size_t)d] * 8); memcpy(idx_outs[d], is_[(size_t)d].data(), counts[(size_t)d] * sizeof(DP)); }
         ks_.clear(); is_.clear();
 #else
         if (ntl == 0 || destbase[(size_t)nd] == 0) return;
         ks.tilebase = tbase.get();
         for (int d = 0; d < nd; ++d) { ks.key_outs[d] = key_outs[d]; ks.idx_outs[d] = idx_outs[d]; ks.destbase[d] = destbase[(size_t)d]; }
-        k_suffix_keys_kernel<5><<<(unsigned)ntl, 256, 0, st>>>(dict, D, L, nullptr, wl, occ, w, kx, ks);
+        k_suffix_keys_kernel<5, DP><<<(unsigned)ntl, 256, 0, st>>>(dict, D, L, nullptr, wl, occ, w, kx, ks);
         PFB_CUDA_CHECK(cudaGetLastError());
         launch_stats().own++;
 #endif

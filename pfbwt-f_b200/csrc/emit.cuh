@@ -24,12 +24,14 @@ static const u8 M_HEAD = 0x10, M_FULL = 0x20, M_VALID = 0x40, M_HARD = 0x80;
 inline u64 tiles_of(u64 n) { return (n + TILE - 1) / TILE; }
 inline u64 padded(u64 n) { return tiles_of(n) * TILE; }
 
-struct FlagsArgs {
-    const u64 *key; const u32 *sa; u64 D; u8 *meta; u32 *cnt; u32 *tilecnt; KeyExtra kx; WordLookup wl; u64 w;
+template <class DP>
+struct FlagsArgsT {
+    const u64 *key; const DP *sa; u64 D; u8 *meta; u32 *cnt; u32 *tilecnt; KeyExtra kx; WordLookupT<DP> wl; u64 w;
 };
 // valid / full bits and occurrence count of dictionary suffix idx by position -> word lookup
 // (include/pfbwt.hpp:83-85,111-119)
-PFB_HD inline u32 suffix_class(const WordLookup &wl, u32 idx, u64 w, u32 &cnt, u32 &ibase, u32 &slen) {
+template <class DP>
+PFB_HD inline u32 suffix_class(const WordLookupT<DP> &wl, DP idx, u64 w, u32 &cnt, u32 &ibase, u32 &slen) {
     u32 d = wl.word(idx);
     u64 len = wl.suflen(d, idx);
     cnt = 0; ibase = 0; slen = (u32)len;
@@ -39,7 +41,8 @@ PFB_HD inline u32 suffix_class(const WordLookup &wl, u32 idx, u64 w, u32 &cnt, u
     ibase = 1 + c0;
     return (u32)M_VALID | (idx == wl.start(d) ? (u32)M_FULL : 0u);
 }
-PFB_HD inline void flags_one(const FlagsArgs &a, u64 t, u64 kprev, u64 k, u64 knext, u32 &m, u32 &c, bool &act) {
+template <class DP>
+PFB_HD inline void flags_one(const FlagsArgsT<DP> &a, u64 t, u64 kprev, u64 k, u64 knext, u32 &m, u32 &c, bool &act) {
     u64 code = a.kx.code(k);
     bool head = t == 0 || code != a.kx.code(kprev);
     bool last = t + 1 == a.D || code != a.kx.code(knext);
@@ -47,7 +50,7 @@ PFB_HD inline void flags_one(const FlagsArgs &a, u64 t, u64 kprev, u64 k, u64 kn
     u64 cf = a.kx.count(k);
     m = (u32)(k & 15) | (head ? M_HEAD : 0) | (act ? M_HARD : 0);
     if (a.kx.cmax && cf != a.kx.cmax) { c = (u32)cf; m |= (c ? M_VALID : 0) | (a.kx.full(k) ? M_FULL : 0); }
-    else { u32 ib, sl; m |= suffix_class(a.wl, a.sa[t], a.w, c, ib, sl); }      // no room in the key / count overflow
+    else { u32 ib, sl; m |= suffix_class<DP>(a.wl, a.sa[t], a.w, c, ib, sl); }      // no room in the key / count overflow
 }
 
 
@@ -74,7 +77,8 @@ __device__ __forceinline__ T block_excl_scan(T v, T &total, T *warp_sums /* 8 */
 
 // ---- after the main radix sort: head flags, "tied and open" flags, per-tile open counts; the
 //      valid / full bits and the occurrence count come out of the key's upper bits (dictkeys.cuh) ----
-__global__ void __launch_bounds__(256) k_sorted_flags_kernel(FlagsArgs a) {
+template <class DP>
+__global__ void __launch_bounds__(256) k_sorted_flags_kernel(FlagsArgsT<DP> a) {
     __shared__ u32 ws[8];
     const u64 t0 = (u64)blockIdx.x * TILE + (u64)threadIdx.x * 8;
     u64 k[10];
@@ -130,7 +134,8 @@ __global__ void __launch_bounds__(256) k_compact_bit_kernel(const u8 *__restrict
 
 
 // meta (pc | head | full | valid | open bit) and cnt from sorted keys; returns the ordered list of open positions
-inline u64 sorted_flags_and_open_list(FlagsArgs fa, DevBuf<u32> &list, Workspace &ws) {
+template <class DP>
+inline u64 sorted_flags_and_open_list(FlagsArgsT<DP> fa, DevBuf<u32> &list, Workspace &ws) {
     pfbStream_t st = ws.st;
     const u64 D = fa.D, nt = tiles_of(D);
 #ifdef PFB_EMU
@@ -149,7 +154,7 @@ inline u64 sorted_flags_and_open_list(FlagsArgs fa, DevBuf<u32> &list, Workspace
 #else
     DevBuf<u32> tcnt(nt + 1), tbase(nt + 1);
     fa.tilecnt = tcnt.get();
-    k_sorted_flags_kernel<<<(unsigned)nt, 256, 0, st>>>(fa);
+    k_sorted_flags_kernel<DP><<<(unsigned)nt, 256, 0, st>>>(fa);
     PFB_CUDA_CHECK(cudaGetLastError());
     launch_stats().own++;
     dev_memset(tcnt.get() + nt, 0, 4, st);
@@ -186,18 +191,20 @@ inline void k_tile_sums(const u32 *cnt, u64 D, u64 *tilesum, pfbStream_t st) {
 // With SA output also the first ilist slot of the word and the suffix length, so that the
 // emission kernels need no second lookup.        (include/pfbwt.hpp:83-85,111-119)
 // ---------------------------------------------------------------------------
-struct ClassifyArgs {
-    const u32 *sa; u8 *meta; WordLookup wl; u64 D; u64 w;
+template <class DP>
+struct ClassifyArgsT {
+    const DP *sa; u8 *meta; WordLookupT<DP> wl; u64 D; u64 w;
     u32 *cnt; u64 *tilesum; u32 *ibase; u32 *sl;   // ibase/sl only when want_sa
 };
 
-PFB_HD inline void classify_one(const ClassifyArgs &a, u64 t, u32 &m, u32 &c, u32 &ib, u32 &s) {
-    m = (m & (u32)(0x0f | M_HEAD)) | suffix_class(a.wl, a.sa[t], a.w, c, ib, s);
+template <class DP>
+PFB_HD inline void classify_one(const ClassifyArgsT<DP> &a, u64 t, u32 &m, u32 &c, u32 &ib, u32 &s) {
+    m = (m & (u32)(0x0f | M_HEAD)) | suffix_class<DP>(a.wl, a.sa[t], a.w, c, ib, s);
 }
 
 #ifndef PFB_EMU
-template <bool SA>
-__global__ void __launch_bounds__(256) k_classify_kernel(ClassifyArgs a) {
+template <bool SA, class DP>
+__global__ void __launch_bounds__(256) k_classify_kernel(ClassifyArgsT<DP> a) {
     __shared__ u64 ws[8];
     const u64 t0 = (u64)blockIdx.x * TILE + (u64)threadIdx.x * 8;
     u64 m8 = *reinterpret_cast<const u64 *>(a.meta + t0);
@@ -228,7 +235,8 @@ __global__ void __launch_bounds__(256) k_classify_kernel(ClassifyArgs a) {
 }
 #endif
 
-inline void k_classify(const ClassifyArgs &a, bool want_sa, pfbStream_t st) {
+template <class DP>
+inline void k_classify(const ClassifyArgsT<DP> &a, bool want_sa, pfbStream_t st) {
     const u64 nt = tiles_of(a.D);
 #ifdef PFB_EMU
     (void)st;
@@ -244,8 +252,8 @@ inline void k_classify(const ClassifyArgs &a, bool want_sa, pfbStream_t st) {
         a.tilesum[tile] = sum;
     }
 #else
-    if (want_sa) k_classify_kernel<true><<<(unsigned)nt, 256, 0, st>>>(a);
-    else k_classify_kernel<false><<<(unsigned)nt, 256, 0, st>>>(a);
+    if (want_sa) k_classify_kernel<true, DP><<<(unsigned)nt, 256, 0, st>>>(a);
+    else k_classify_kernel<false, DP><<<(unsigned)nt, 256, 0, st>>>(a);
     PFB_CUDA_CHECK(cudaGetLastError());
     launch_stats().own++;
 #endif
@@ -373,9 +381,10 @@ struct EmitArgs {
     u32 small_lim, mid_lim;            // <= HARD_SMALL / HARD_MID (test knob PFB_HARD_LIMITS lowers them)
 };
 
-// first ilist slot of the word that dictionary suffix t belongs to
+// first ilist slot of the word that dictionary suffix t belongs to.  a.sa == nullptr: the positions are 64-bit (dictionary of
+// 2^32 bytes or more); the classify pass has then filled ibase[] also without SA output and no lookup happens here
 PFB_HD inline u32 ilist_base(const EmitArgs &a, u64 t, bool sa_mode) {
-    return sa_mode ? a.ibase[t] : 1u + a.wl.cum(a.wl.word(a.sa[t]));
+    return (sa_mode || !a.sa) ? a.ibase[t] : 1u + a.wl.cum(a.wl.word(a.sa[t]));
 }
 
 #ifndef PFB_EMU

@@ -286,11 +286,73 @@ struct Engine {
             if (!parsed) return fail(PFB_ERR_ARG, "no parse loaded");
             if (!parse.has_parse_bwt) { int rc = do_parse_bwt(); if (rc) return rc; }
             bwt = DeviceBwt();
+            u64 mem_buckets = 0;
+            if (const char *e = getenv("PFB_MEM_BUCKETS")) mem_buckets = (u64)atol(e);          // test knob
+            if (!comm && (parse.dsize > 0xFFFFFFF0ull || mem_buckets > 1)) return build_in_key_ranges(sa, rssa, mem_buckets);
             int rc = build_bwt(parse, prm, sa, rssa, bwt, ws, tm, err, comm.get());
             if (rc) return fail(rc, err);
             built = true; built_sa = sa; built_rssa = rssa;
             return PFB_OK;
         } catch (const Error &e) { return fail(e.code, e.what()); }
+    }
+
+    // ---- dictionaries of 2^32 bytes or more (pfbwt-f64: gsa/gsacak.h:44-58 indexes the dictionary with 64-bit uint_t).
+    // Indices INTO the sorted suffix array stay 32-bit here, so such a dictionary is sorted and emitted one key range
+    // after the other (each fewer than 2^32 suffixes, the loop of build_to_files) and the slices are put together in HBM:
+    // the result is the same DeviceBwt a one-piece build leaves.
+    int build_in_key_ranges(bool sa, bool rssa, u64 B) {
+        const bool any_sa = sa || rssa;
+        const u64 U = (u64)prm.bits / 8, n = parse.n;
+        if (B < 2) {
+            B = parse.dsize / (1ull << 30) + 1;                  // <= 2^30 suffixes per range on average: splitters balance work, not counts
+#ifndef PFB_EMU
+            size_t fr = 0, tot = 0;
+            cudaMemGetInfo(&fr, &tot);
+            const u64 avail = (u64)fr + slab_pool().idle();
+            const u64 keep = (n + 1) * (1 + (any_sa ? U : 0)), est = build_workspace_estimate(any_sa, rssa);
+            if (avail > keep + (est >> 6)) { const u64 byMem = est / (avail - keep) + 1; if (byMem > B) B = byMem; }
+#endif
+        }
+        if (B > (u64)KEY_MAX_DEST) B = KEY_MAX_DEST;
+        bwt.n = n; bwt.off = 0; bwt.len = n + 1;
+        bwt.bwt.alloc(n + 1 + 16);
+        if (any_sa) bwt.sa.alloc((n + 1) * U + 16);
+        struct Piece { DevBuf<u8> ssa, esa; u64 so, sc, eo, ec; };
+        std::vector<Piece> pieces;
+        BucketCarry carry;
+        for (u64 b = 0; b < B; ++b) {
+            ShardSpec spec;
+            spec.rank = (int)b; spec.world = (int)B;
+            DeviceBwt out;
+            int rc = build_bwt(parse, prm, sa, rssa, out, ws, tm, err, nullptr, &spec, &carry);
+            if (rc) return fail(rc, err);
+            if (out.len) {
+                d2d(bwt.bwt.get() + out.off, out.bwt.get(), out.len, ws.st);
+                if (any_sa) d2d(bwt.sa.get() + out.off * U, out.sa.get(), out.len * U, ws.st);
+            }
+            if (rssa) {
+                Piece pc;
+                pc.so = out.ssa_off; pc.sc = out.ssa_cnt; pc.eo = out.esa_off; pc.ec = out.esa_cnt;
+                pc.ssa = std::move(out.ssa); pc.esa = std::move(out.esa);
+                pieces.push_back(std::move(pc));
+            }
+            bwt.r = out.r; bwt.easy = out.easy; bwt.hard = out.hard;
+            stream_sync(ws.st);
+        }
+        if (carry.off != n + 1) return fail(PFB_ERR_INTERNAL, "internal: key ranges emitted " + std::to_string(carry.off) + " positions, n+1 = " + std::to_string(n + 1));
+        if (rssa) {
+            // the last range cannot know that its last position ends the last run only if another range followed: it did not
+            if (carry.ssa != bwt.r || carry.esa != bwt.r) return fail(PFB_ERR_INTERNAL, "internal: run samples of the key ranges do not add up");
+            bwt.ssa.alloc(2 * bwt.r * U + 16); bwt.esa.alloc(2 * bwt.r * U + 16);
+            for (auto &pc : pieces) {
+                if (pc.sc) d2d(bwt.ssa.get() + 2 * pc.so * U, pc.ssa.get(), 2 * pc.sc * U, ws.st);
+                if (pc.ec) d2d(bwt.esa.get() + 2 * pc.eo * U, pc.esa.get(), 2 * pc.ec * U, ws.st);
+            }
+            stream_sync(ws.st);
+        }
+        bwt.ssa_off = bwt.esa_off = 0; bwt.ssa_cnt = bwt.esa_cnt = rssa ? bwt.r : 0;
+        built = true; built_sa = sa; built_rssa = rssa;
+        return PFB_OK;
     }
 
     // ---- document array (README.md:29-33 lists it as a feature to come, so there is no reference format):
@@ -337,7 +399,8 @@ struct Engine {
     // n = 3.1e9, U = 8 with SA - keys 2 x 8, positions 2 x 4, meta, counts, lookups with SA; output 1 + U per position)
     u64 build_workspace_estimate(bool any_sa, bool rssa) const {
         const u64 U = (u64)prm.bits / 8;
-        return parse.dsize * (any_sa ? 38ull : 30ull) + (parse.n + 1) * (1 + (any_sa ? U : 0) + (rssa ? 18ull : 0));
+        const u64 wide = parse.dsize > 0xFFFFFFF0ull ? 16ull : 0ull;      // 64-bit positions: 2 x 4 more per suffix, lookups always
+        return parse.dsize * ((any_sa ? 38ull : 30ull) + wide) + (parse.n + 1) * (1 + (any_sa ? U : 0) + (rssa ? 18ull : 0));
     }
     int build_to_files(const std::string &prefix, bool sa, bool rssa, u64 limit_bytes) {
         try {
@@ -361,6 +424,7 @@ struct Engine {
                 if (resident + (est >> 6) >= limit_bytes) return fail(PFB_ERR_NOMEM, "the memory limit does not even hold the dictionary and the parse");
                 B = (est + (limit_bytes - resident) - 1) / (limit_bytes - resident);
             }
+            if (parse.dsize > 0xFFFFFFF0ull && B < parse.dsize / (1ull << 30) + 1) B = parse.dsize / (1ull << 30) + 1;   // a key range holds fewer than 2^32 suffixes
             if (const char *e = getenv("PFB_BUCKETS")) { const long v = atol(e); if (v > 0) B = (u64)v; }       // test knob
             if (B > (u64)KEY_MAX_DEST) B = KEY_MAX_DEST;
             bwt = DeviceBwt();
@@ -576,7 +640,7 @@ struct Engine {
             u64 dsize = 0;
             if (read_whole_file_to_dev(prefix + ".dict", parse.dict, dsize, 64, device, ws.st, e)) return fail(PFB_ERR_IO, "bad dict file\n");
             if (dsize < 2) return fail(PFB_ERR_IO, "bad dict file\n");
-            if (dsize > 0xFFFFFFF0ull) return fail(PFB_ERR_LIMIT, "dictionary larger than 2^32 bytes is not supported yet");
+            if (dsize >= DICT_MAX_BYTES) return fail(PFB_ERR_LIMIT, "dictionary larger than 2^40 bytes is not supported");
             parse.dsize = dsize;
             {
                 const u8 *dp = parse.dict.get();
@@ -601,11 +665,11 @@ struct Engine {
                 if (bad[0]) return fail(PFB_ERR_IO, "dict file contains a byte outside the parser's alphabet");
                 parse.Dw = Dw;
                 parse.wstart.alloc(Dw + 1);
-                u32 *wsp = parse.wstart.get();
+                u64 *wsp = parse.wstart.get();
                 const u32 *rk = rank.get();
                 launch_for(dsize, ws.st, PFB_LAMBDA(u64 i) {
                     if (i == 0) wsp[0] = 0;
-                    if (ie[i]) wsp[rk[i] + 1] = (u32)i + 1;
+                    if (ie[i]) wsp[rk[i] + 1] = i + 1;
                 });
             }
             // .parse / .occ / .ilist / .bwsai go from their files straight to HBM (devio.cuh) and are brought to the device
@@ -631,7 +695,7 @@ struct Engine {
                 else {
                     DevBuf<u64> tot(1);
                     dev_memset(tot.get(), 0, 8, ws.st);
-                    const u32 *pr_ = parse.parse.get(); const u32 *wsr = parse.wstart.get(); u64 *tp = tot.get();
+                    const u32 *pr_ = parse.parse.get(); const u64 *wsr = parse.wstart.get(); u64 *tp = tot.get();
                     const u64 Dw_ = parse.Dw, w_ = (u64)prm.w;
                     launch_for(parse.P, ws.st, PFB_LAMBDA(u64 k) {
                         const u64 d = (u64)pr_[k] - 1;
@@ -725,7 +789,7 @@ struct Engine {
             const u64 P = rp.P; const int w = prm.w;
             DevBuf<u64> clen(P + 1), coff(P + 1);
             {
-                const u32 *pr = rp.parse.get(); const u32 *wsr = rp.wstart.get(); u64 *cl = clen.get();
+                const u32 *pr = rp.parse.get(); const u64 *wsr = rp.wstart.get(); u64 *cl = clen.get();
                 launch_for(P + 1, ws.st, PFB_LAMBDA(u64 k) {
                     if (k == P) { cl[k] = 0; return; }
                     u32 d = pr[k] - 1;
@@ -739,7 +803,7 @@ struct Engine {
             u64 n = tlen - (u64)w - 1;
             DevBuf<u8> tp(tlen);
             {
-                const u32 *pr = rp.parse.get(); const u32 *wsr = rp.wstart.get(); const u8 *dict = rp.dict.get();
+                const u32 *pr = rp.parse.get(); const u64 *wsr = rp.wstart.get(); const u8 *dict = rp.dict.get();
                 const u64 *co = coff.get(); u8 *out = tp.get();
                 launch_for(P * 32, ws.st, PFB_LAMBDA(u64 i) {
                     u64 k = i / 32, lane = i % 32;

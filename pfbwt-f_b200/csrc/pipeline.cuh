@@ -46,7 +46,7 @@ struct StageTimes {   // milliseconds, CUDA events on the pipeline stream
 struct DeviceParse {
     u64 n = 0, P = 0, Dw = 0, dsize = 0;
     DevBuf<u8> dict;        // dsize           .dict image
-    DevBuf<u32> wstart;     // Dw+1            word start offsets in dict
+    DevBuf<u64> wstart;     // Dw+1            word start offsets in dict (64-bit: a dictionary may pass 2^32 bytes)
     DevBuf<u32> occ;        // Dw              .occ
     DevBuf<u32> parse;      // P+1             .parse (+ EOS slot)
     DevBuf<u8> last;        // P               last_
@@ -105,7 +105,7 @@ struct Timer {
 #else
     Timer(pfbStream_t) {}
     float stop() { return 0.f; }
-    void lap(const char *) {}
+    void lap(const char *name) { if (trace_log().on) trace_log().v.emplace_back(name, 0.f); }      // the steps taken, untimed
 #endif
 };
 
@@ -760,7 +760,7 @@ inline void ranks_from_flags(const DevBuf<u32> &sa, DevBuf<u8> &flag, DevBuf<u32
 }
 
 // largest d with wstart[d] <= pos   (wstart has Dw+1 entries, wstart[Dw] = dsize-1)
-PFB_HD inline u32 word_of(const u32 *wstart, u32 Dw, u32 pos) {
+PFB_HD inline u32 word_of(const u64 *wstart, u32 Dw, u64 pos) {
     u32 lo = 0, hi = Dw;   // answer in [lo, hi)
     while (hi - lo > 1) {
         u32 mid = lo + (hi - lo) / 2;
@@ -783,6 +783,7 @@ struct TextOnDevice {
 
 // A piece of T' (multi-GPU parse): bytes Tp[0, tlen); positions qmin.. may trigger; the piece either
 // ends with Dollar^w (end of T') or exactly at a trigger position (the first trigger owned by a later rank).
+static const u64 DICT_MAX_BYTES = 1ull << 40;      // dictionary positions are u32 below 2^32 bytes and u64 above (build.cuh)
 struct PieceSpec {
     u64 tlen = 0, qmin = 0; bool dollar_end = true;
     const u8 *mem_lo = nullptr, *mem_hi = nullptr;      // the allocation Tp lies in (the tiled trigger scan loads whole aligned tiles)
@@ -906,13 +907,12 @@ inline int parse_piece(const u8 *Tp, const PieceSpec &ps, const Params &prm, Dev
     }
     exclusive_sum<u64, u64>(wl.get(), ws64.get(), Dw + 1, ws.sc, st);
     u64 dsize = read_scalar(ws64.get() + Dw, st) + 1;
-    if (dsize > 0xFFFFFFF0ull) { err = "dictionary larger than 2^32 bytes is not supported yet"; return PFB_ERR_LIMIT; }
+    if (dsize >= DICT_MAX_BYTES) { err = "dictionary larger than 2^40 bytes is not supported"; return PFB_ERR_LIMIT; }
     out.dsize = dsize;
-    out.wstart.alloc(Dw + 1);
+    out.wstart = std::move(ws64);
     out.dict.alloc(dsize);
     {
-        const u64 *w64 = ws64.get(); u32 *wsp = out.wstart.get();
-        launch_for(Dw + 1, st, PFB_LAMBDA(u64 r) { wsp[r] = (u32)w64[r]; });
+        const u64 *w64 = out.wstart.get();
         u8 *dict = out.dict.get(); const u32 *ord = order.get();
         // the words are copied into the image (include/pfbwt_io.hpp:71-82); the few words longer than
         // LONGW (phrases spanning an N run: up to tens of Mbp) are listed and copied by the copy engine instead

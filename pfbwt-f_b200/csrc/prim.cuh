@@ -21,6 +21,7 @@
 #include <cstring>
 #include <stdexcept>
 #include <string>
+#include <type_traits>
 #include <utility>
 #include <vector>
 
@@ -437,9 +438,9 @@ template <class K, class V>
 inline void sort_pairs(DevBuf<K> &keys_a, DevBuf<K> &keys_b, DevBuf<V> &vals_a, DevBuf<V> &vals_b, uint64_t n,
                        int begin_bit, int end_bit, Scratch &sc, pfbStream_t s, bool iota_vals = false, const uint64_t *hist0 = nullptr) {
 #ifndef PFB_EMU
-    // the product build sorts (u64 key, u32 value) pairs only, with the hand-written onesweep sort of radix.cuh
-    static_assert(sizeof(K) == 8 && sizeof(V) == 4, "sort_pairs: (u64, u32) pairs only");
-    radix_sort_pairs(keys_a, keys_b, vals_a, vals_b, n, begin_bit, end_bit, iota_vals, hist0, sc.rw, s);
+    // the product build sorts (u64 key, u32 / u64 value) pairs with the hand-written onesweep sort of radix.cuh
+    static_assert(sizeof(K) == 8 && (sizeof(V) == 4 || sizeof(V) == 8), "sort_pairs: (u64, u32) and (u64, u64) pairs only");
+    radix_sort_pairs<typename std::conditional<sizeof(V) == 4, RxDefault, RxWide>::type>(keys_a, keys_b, vals_a, vals_b, n, begin_bit, end_bit, iota_vals, hist0, sc.rw, s);
     return;
 #else
     if (iota_vals && n) { V *v = vals_a.get(); launch_for(n, s, PFB_LAMBDA(uint64_t i) { v[i] = (V)i; }); }

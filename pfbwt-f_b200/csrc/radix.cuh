@@ -1,4 +1,4 @@
-// radix.cuh -- hand-written stable LSD radix sort of (u64 key, u32 value) pairs, one kernel
+// radix.cuh -- hand-written stable LSD radix sort of (u64 key, u32 or u64 value) pairs, one kernel
 // launch per digit ("onesweep": per-tile digit counts are chained through a decoupled
 // look-back array, so every pass reads and writes each pair exactly once).
 //
@@ -21,12 +21,14 @@ namespace pfb {
 #ifndef PFB_EMU
 static const int RX_BITS = 8, RX_R = 1 << RX_BITS;
 // tile shape: NT threads x IPT pairs, MINB resident CTAs per SM asked of ptxas, MATCH 0 = ballots, 1 = match.any
-template <int NT_, int IPT_, int MINB_, int MATCH_>
+template <int NT_, int IPT_, int MINB_, int MATCH_, class V_ = unsigned>
 struct RxCfg {
+    typedef V_ V;                           // value type: u32, or u64 (positions in a dictionary of 2^32 bytes or more)
     static const int NT = NT_, IPT = IPT_, MINB = MINB_, MATCH = MATCH_, NW = NT_ / 32, TILE = NT_ * IPT_;
-    static const size_t SMEM = (size_t)NW * RX_R * 4 + (size_t)TILE * 8 + (size_t)TILE * 4 + (size_t)RX_R * 8 + (size_t)RX_R * 4 + 16 * 8;
+    static const size_t SMEM = (size_t)NW * RX_R * 4 + (size_t)TILE * 8 + (size_t)TILE * sizeof(V_) + (size_t)RX_R * 8 + (size_t)RX_R * 4 + 16 * 8;
 };
 typedef RxCfg<256, 20, 3, 0> RxDefault;   // best of the tools/bench_radix.cu sweep on B200 with full-tile specialisation (5120-pair tiles, 3 CTAs/SM)
+typedef RxCfg<256, 15, 3, 0, u64> RxWide;   // 64-bit values: 3840-pair tiles keep 3 CTAs/SM within shared memory
 static const int RX_MAX_PASSES = 8;
 
 __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long *p) {
@@ -64,8 +66,9 @@ __global__ void __launch_bounds__(256) k_radix_hist_all(const unsigned long long
         if (sh[i2]) atomicAdd(&hist[i2], (unsigned long long)sh[i2]);
 }
 
+template <class V>
 struct RadixPassArgs {
-    const unsigned long long *kin; const unsigned *vin; unsigned long long *kout; unsigned *vout;
+    const unsigned long long *kin; const V *vin; unsigned long long *kout; V *vout;
     unsigned long long n;
     int shift; unsigned mask;               // digit of this pass
     const unsigned long long *hist;         // RX_R counts of this digit over all keys
@@ -89,12 +92,13 @@ __device__ __forceinline__ unsigned rx_peers(unsigned d) {
 
 // FULL: the tile holds RX_TILE pairs (all but the last tile of a pass): no per-item bounds checks
 template <bool IOTA, class C, bool FULL>
-__device__ void rx_pass_body(const RadixPassArgs &a, const unsigned long long tile, const int tile_n_rt) {
+__device__ void rx_pass_body(const RadixPassArgs<typename C::V> &a, const unsigned long long tile, const int tile_n_rt) {
     constexpr int RX_NT = C::NT, RX_IPT = C::IPT, RX_NW = C::NW, RX_TILE = C::TILE;
+    typedef typename C::V V;
     extern __shared__ __align__(16) unsigned char rx_smem[];
     unsigned *whist = reinterpret_cast<unsigned *>(rx_smem);                                   // [RX_NW][RX_R]
     unsigned long long *skeys = reinterpret_cast<unsigned long long *>(whist + RX_NW * RX_R);  // [RX_TILE]
-    unsigned *svals = reinterpret_cast<unsigned *>(skeys + RX_TILE);                           // [RX_TILE]
+    V *svals = reinterpret_cast<V *>(skeys + RX_TILE);                                         // [RX_TILE]
     unsigned long long *gbase = reinterpret_cast<unsigned long long *>(svals + RX_TILE);       // [RX_R]
     unsigned *dstart = reinterpret_cast<unsigned *>(gbase + RX_R);                             // [RX_R]
     unsigned long long *wsum = reinterpret_cast<unsigned long long *>(dstart + RX_R);          // [RX_NW]
@@ -103,13 +107,14 @@ __device__ void rx_pass_body(const RadixPassArgs &a, const unsigned long long ti
     const int tile_n = FULL ? RX_TILE : tile_n_rt;
 
     unsigned long long key[RX_IPT];
-    unsigned val[RX_IPT], rank[RX_IPT];
+    V val[RX_IPT];
+    unsigned rank[RX_IPT];
 #pragma unroll
     for (int j = 0; j < RX_IPT; ++j) {
         const int li = w * 32 * RX_IPT + j * 32 + lane;
         if (FULL || li < tile_n) {
             key[j] = a.kin[base + li];
-            val[j] = IOTA ? (unsigned)(base + li) : a.vin[base + li];
+            val[j] = IOTA ? (V)(base + li) : a.vin[base + li];
         } else { key[j] = ~0ull; val[j] = 0; }
     }
     // stable ranks inside the warp: items are ordered (j, lane); invalid items of the last tile carry
@@ -207,12 +212,12 @@ __device__ void rx_pass_body(const RadixPassArgs &a, const unsigned long long ti
 
 // the one partial tile of a pass goes through an out-of-line copy so that it does not cost the full tiles registers
 template <bool IOTA, class C>
-__device__ __noinline__ void rx_pass_tail(const RadixPassArgs a, const unsigned long long tile, const int tile_n) {
+__device__ __noinline__ void rx_pass_tail(const RadixPassArgs<typename C::V> a, const unsigned long long tile, const int tile_n) {
     rx_pass_body<IOTA, C, false>(a, tile, tile_n);
 }
 
 template <bool IOTA, class C>
-__global__ void __launch_bounds__(C::NT, C::MINB) k_radix_pass(RadixPassArgs a) {
+__global__ void __launch_bounds__(C::NT, C::MINB) k_radix_pass(RadixPassArgs<typename C::V> a) {
     extern __shared__ __align__(16) unsigned char rx_smem0[];
     unsigned *whist = reinterpret_cast<unsigned *>(rx_smem0);
     __shared__ unsigned s_tile;
@@ -252,10 +257,11 @@ struct RadixWork {                 // reusable scratch of the sort (look-back ar
 // may be swapped).  iota_vals: the input values are 0..n-1 and vals_a need not be initialised.
 // hist0: optional device histogram (RX_R u64) of the first digit, already computed by the caller.
 template <class C = RxDefault>
-inline void radix_sort_pairs(DevBuf<u64> &keys_a, DevBuf<u64> &keys_b, DevBuf<u32> &vals_a, DevBuf<u32> &vals_b, u64 n, int begin_bit,
+inline void radix_sort_pairs(DevBuf<u64> &keys_a, DevBuf<u64> &keys_b, DevBuf<typename C::V> &vals_a, DevBuf<typename C::V> &vals_b, u64 n, int begin_bit,
                              int end_bit, bool iota_vals, const u64 *hist0, RadixWork &rw, pfbStream_t st) {
+    typedef typename C::V V;
     if (n == 0 || end_bit <= begin_bit) {
-        if (iota_vals && n) { u32 *v = vals_a.get(); launch_for(n, st, PFB_LAMBDA(u64 i) { v[i] = (u32)i; }); }
+        if (iota_vals && n) { V *v = vals_a.get(); launch_for(n, st, PFB_LAMBDA(u64 i) { v[i] = (V)i; }); }
         return;
     }
     const int npass = (end_bit - begin_bit + RX_BITS - 1) / RX_BITS;
@@ -284,7 +290,7 @@ inline void radix_sort_pairs(DevBuf<u64> &keys_a, DevBuf<u64> &keys_b, DevBuf<u3
         launch_stats().own++;
     }
     for (int p = 0; p < npass; ++p) {
-        RadixPassArgs a;
+        RadixPassArgs<V> a;
         a.kin = (const unsigned long long *)keys_a.get(); a.vin = vals_a.get();
         a.kout = (unsigned long long *)keys_b.get(); a.vout = vals_b.get();
         a.n = n; a.shift = begin_bit + p * RX_BITS; a.mask = dmask(p);

@@ -182,17 +182,17 @@
         if (M > 0xFFFFFFF0ull) return fail(PFB_ERR_LIMIT, "more than 2^32 dictionary words across the ranks");
         // union of the local dictionaries: bytes, word starts, occurrence counts
         DevBuf<u8> ub(UB + 1);
-        DevBuf<u32> uws(M + 1), uocc(M + 1);
-        DevBuf<u64> ustart(M + 1);
+        DevBuf<u32> uocc(M + 1);
+        DevBuf<u64> uws(M + 1), ustart(M + 1);
         auto scaled = [&](const std::vector<u64> &c, u64 k) { std::vector<u64> v(c); for (auto &x : v) x *= k; return v; };
         comm->all_gather_v(lp.dict.get(), ub.get(), cB.data(), st);
-        comm->all_gather_v(lp.wstart.get(), uws.get(), scaled(cW, 4).data(), st);
+        comm->all_gather_v(lp.wstart.get(), uws.get(), scaled(cW, 8).data(), st);
         comm->all_gather_v(lp.occ.get(), uocc.get(), scaled(cW, 4).data(), st);
         t_x += xt.stop();
         for (int r = 0; r < G; ++r) {
             const u64 c = cW[(size_t)r], o = oW[(size_t)r], b = oB[(size_t)r];
-            const u32 *src = uws.get() + o; u64 *dst = ustart.get() + o;
-            launch_for(c, st, PFB_LAMBDA(u64 j) { dst[j] = b + (u64)src[j]; });
+            const u64 *src = uws.get() + o; u64 *dst = ustart.get() + o;
+            launch_for(c, st, PFB_LAMBDA(u64 j) { dst[j] = b + src[j]; });
         }
         { u64 *us = ustart.get(); launch_for(1, st, PFB_LAMBDA(u64) { us[M] = UB; }); }
         // sort the union; groups of identical words collapse into one global word
@@ -227,14 +227,13 @@
         }
         exclusive_sum<u64, u64>(wl.get(), ws64.get(), Dw + 1, ws.sc, st);
         const u64 dsize = read_scalar(ws64.get() + Dw, st) + 1;
-        if (dsize > 0xFFFFFFF0ull) return fail(PFB_ERR_LIMIT, "dictionary larger than 2^32 bytes is not supported yet");
+        if (dsize >= DICT_MAX_BYTES) return fail(PFB_ERR_LIMIT, "dictionary larger than 2^40 bytes is not supported");
         parse.n = n_total; parse.P = P; parse.Dw = Dw; parse.dsize = dsize;
-        parse.wstart.alloc(Dw + 1);
+        parse.wstart = std::move(ws64);
         parse.dict.alloc(dsize);
         {
-            const u64 *w64 = ws64.get(); u32 *wsp = parse.wstart.get(); const u32 *hp = headpos.get(); const u64 *us = ustart.get();
+            const u64 *w64 = parse.wstart.get(); const u32 *hp = headpos.get(); const u64 *us = ustart.get();
             const u8 *src = ub.get(); u8 *dict = parse.dict.get();
-            launch_for(Dw + 1, st, PFB_LAMBDA(u64 r) { wsp[r] = (u32)w64[r]; });
             launch_for(Dw * 32 + 1, st, PFB_LAMBDA(u64 i) {
                 if (i == Dw * 32) { dict[dsize - 1] = ENDOFDICT; return; }
                 u64 r = i / 32, lane = i % 32;

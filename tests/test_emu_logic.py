@@ -138,7 +138,11 @@ FUZZ_KNOBS = [{}, {"PFB_PIVOT": "1", "PFB_KEY_SYMS": "3"}, {"PFB_PIVOT": "0", "P
               {"PFB_EXT_ROUNDS": "100", "PFB_PIVOT": "0"}, {"PFB_HARD_LIMITS": "2,4"}, {"PFB_KEY_COUNT_BITS": "0"},
               {"PFB_KEY_COUNT_BITS": "2", "PFB_PIVOT": "1", "PFB_KEY_SYMS": "5"},
               {"PFB_SMALL_GROUP": "0", "PFB_PIVOT": "1", "PFB_KEY_SYMS": "4"}, {"PFB_SMALL_GROUP": "3", "PFB_KEY_SYMS": "3"},
-              {"PFB_SMALL_GROUP": "2", "PFB_PIVOT": "1", "PFB_KEY_SYMS": "2"}]
+              {"PFB_SMALL_GROUP": "2", "PFB_PIVOT": "1", "PFB_KEY_SYMS": "2"},
+              # 64-bit dictionary positions (the build of a dictionary of 2^32 bytes or more) forced at small sizes, alone,
+              # through the in-memory key ranges such a dictionary is built in, and through the prefix-doubling hand-over
+              {"PFB_DICT64": "1"}, {"PFB_DICT64": "1", "PFB_MEM_BUCKETS": "3", "PFB_PIVOT": "1", "PFB_KEY_SYMS": "3"},
+              {"PFB_DICT64": "1", "PFB_EXT_ROUNDS": "0"}, {"PFB_MEM_BUCKETS": "4", "PFB_KEY_COUNT_BITS": "0"}]
 
 
 @pytest.mark.parametrize("block", range(5))
@@ -226,3 +230,31 @@ def test_emu_load_rejects_mismatched_files(emu, datadir):
         open(pfx + "." + what, "wb").write(bytes(raw))
         r = run([emu, "--merge", "--bits", "64", "-o", os.path.join(datadir, "stale_out"), pfx], check=False)
         assert r.returncode != 0 and b"bad parse file" in r.stderr, (what, r.stderr[-300:])
+
+
+WIDE_KNOBS = [{"PFB_DICT64": "1"}, {"PFB_DICT64": "1", "PFB_MEM_BUCKETS": "5"}, {"PFB_DICT64": "1", "PFB_MEM_BUCKETS": "64"},
+              {"PFB_DICT64": "1", "PFB_KEY_COUNT_BITS": "0", "PFB_MEM_BUCKETS": "2"}, {"PFB_DICT64": "1", "PFB_BUCKETS": "3", "-m": "1"},
+              {"PFB_DICT64": "1", "PFB_PIVOT": "1", "PFB_KEY_SYMS": "3", "PFB_SMALL_GROUP": "2"}, {"PFB_DICT64": "1", "PFB_EXT_ROUNDS": "0"}]
+
+
+@pytest.mark.parametrize("knobs", WIDE_KNOBS, ids=["-".join(f"{k[4:] if k.startswith('PFB_') else k}{v}" for k, v in kn.items()) for kn in WIDE_KNOBS])
+@pytest.mark.parametrize("flags,bits", [(["-s", "-r"], 64), ([], 32)])
+def test_emu_wide_dictionary_positions(knobs, flags, bits, emu, ref_bins, datadir):
+    """dictionaries of 2^32 bytes or more (pfbwt-f64 indexes the dictionary with 64-bit uint_t, gsa/gsacak.h:44-58): the
+    build then runs on 64-bit dictionary positions - (u64, u64) sort pairs, two-array word lookup, ilist bases from the
+    classify pass also without SA output - and one key range after the other, the slices put together in memory
+    (Engine::build_in_key_ranges) or streamed (-m).  PFB_DICT64=1 / PFB_MEM_BUCKETS force all of it at a size the oracle runs."""
+    fa = os.path.join(datadir, "wide.fa")
+    if not os.path.exists(fa):
+        write_fasta(fa, pangenome_records(40_000, 5, 40, 23) + nrun_records(1, 20_000, 29, big_run=3000) + [("r", random_bases(30_000, 31))], line_width=60)
+    fl = flags + ["--non-acgt-to-a"]
+    a = os.path.join(datadir, f"wide{bits}{''.join(flags)}.port")
+    b = os.path.join(datadir, f"wide{bits}{''.join(flags)}_{'_'.join(knobs.values())}.emu")
+    if not os.path.exists(a + ".bwt"):
+        run([ref_bins["pfp_oracle"], "--bits", str(bits)] + fl + ["-o", a, fa])
+    env = dict(os.environ, PFB_TRACE="1", **{k: v for k, v in knobs.items() if k.startswith("PFB_")})
+    r = subprocess.run([emu, "--bits", str(bits)] + (["-m"] if "-m" in knobs else []) + fl + ["-o", b, fa], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    assert r.returncode == 0, r.stderr.decode()[-1500:]
+    ranges = int(knobs.get("PFB_MEM_BUCKETS", knobs.get("PFB_BUCKETS", "1")))
+    assert r.stderr.decode().count("K7 word tables (64-bit dictionary positions)") == ranges      # the path under test ran, once per key range
+    assert_same_files(a, b, exts_for("-s" in flags, "-r" in flags))
