@@ -8,9 +8,9 @@ CSRC   := pfbwt-f_b200/csrc
 LIB    := pfbwt-f_b200/libpfbwt_b200.so
 BIN    := bin
 
-all: $(LIB) $(BIN)/pfbwt-f $(BIN)/pfbwt-f64 $(BIN)/merge_pfp $(BIN)/shim_demo $(BIN)/shim_demo64 emu
+all: $(LIB) $(BIN)/pfbwt-f $(BIN)/pfbwt-f64 $(BIN)/merge_pfp $(BIN)/mps_to_ma $(BIN)/shim_demo $(BIN)/shim_demo64 emu
 
-$(LIB): $(CSRC)/capi.cu $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/build.cuh $(CSRC)/dictkeys.cuh $(CSRC)/emit.cuh $(CSRC)/radix.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp $(CSRC)/comm.hpp $(CSRC)/shard.inl $(CSRC)/ingest.cuh $(CSRC)/devio.cuh $(CSRC)/parsekernels.cuh $(CSRC)/scan.cuh include/pfbwt_b200.h
+$(LIB): $(CSRC)/capi.cu $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/build.cuh $(CSRC)/dictkeys.cuh $(CSRC)/emit.cuh $(CSRC)/radix.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp $(CSRC)/comm.hpp $(CSRC)/shard.inl $(CSRC)/ingest.cuh $(CSRC)/devio.cuh $(CSRC)/parsekernels.cuh $(CSRC)/scan.cuh $(CSRC)/markers.cuh include/pfbwt_b200.h
 	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/capi.cu -lz -lcudart -ldl -lpthread
 
 $(BIN)/pfbwt-f: pfbwt-f_b200/src/pfbwt-f.cpp $(LIB)
@@ -20,6 +20,10 @@ $(BIN)/pfbwt-f64: pfbwt-f_b200/src/pfbwt-f.cpp $(LIB)
 	mkdir -p $(BIN)
 	$(CXX) -std=c++17 -O2 -DM64 -I include -o $@ $< -Lpfbwt-f_b200 -lpfbwt_b200 -Wl,-rpath,'$$ORIGIN/../pfbwt-f_b200'
 $(BIN)/merge_pfp: pfbwt-f_b200/src/merge_pfp.cpp $(LIB)
+	mkdir -p $(BIN)
+	$(CXX) -std=c++17 -O2 -I include -o $@ $< -Lpfbwt-f_b200 -lpfbwt_b200 -Wl,-rpath,'$$ORIGIN/../pfbwt-f_b200'
+
+$(BIN)/mps_to_ma: pfbwt-f_b200/src/mps_to_ma.cpp $(LIB)
 	mkdir -p $(BIN)
 	$(CXX) -std=c++17 -O2 -I include -o $@ $< -Lpfbwt-f_b200 -lpfbwt_b200 -Wl,-rpath,'$$ORIGIN/../pfbwt-f_b200'
 
@@ -35,7 +39,7 @@ $(BIN)/shim_demo64: tests/shim/shim_main.cpp include/pfbwtf_shim.hpp $(LIB)
 emu: tests/emu/pfb_emu tests/emu/libpfb_emu.so
 tests/emu/libpfb_emu.so: tests/emu/pfb_emu
 	$(CXX) -std=c++17 -O2 -Wall -Wno-unused -shared -fPIC -I $(CSRC) -o $@ tests/emu/emu_main.cpp -lz -pthread
-tests/emu/pfb_emu: tests/emu/emu_main.cpp $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/build.cuh $(CSRC)/dictkeys.cuh $(CSRC)/emit.cuh $(CSRC)/radix.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp $(CSRC)/comm.hpp $(CSRC)/shard.inl $(CSRC)/ingest.cuh $(CSRC)/devio.cuh $(CSRC)/parsekernels.cuh $(CSRC)/scan.cuh
+tests/emu/pfb_emu: tests/emu/emu_main.cpp $(CSRC)/engine.hpp $(CSRC)/pipeline.cuh $(CSRC)/build.cuh $(CSRC)/dictkeys.cuh $(CSRC)/emit.cuh $(CSRC)/radix.cuh $(CSRC)/prim.cuh $(CSRC)/host_io.hpp $(CSRC)/comm.hpp $(CSRC)/shard.inl $(CSRC)/ingest.cuh $(CSRC)/devio.cuh $(CSRC)/parsekernels.cuh $(CSRC)/scan.cuh $(CSRC)/markers.cuh
 	$(CXX) -std=c++17 -O2 -Wall -Wno-unused -I $(CSRC) -o $@ $< -lz -pthread
 
 oracle:

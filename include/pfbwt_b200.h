@@ -148,6 +148,14 @@ int pfb_build_bwt_to_files(pfb_ctx *, const char *prefix, int sa, int rssa, uint
  * reference, so the format is ours): <prefix>.da = one uint32 per BWT position i, the index of the record (line of
  * <prefix>.docs, include/pfbwt_io.hpp:224-231) holding text position SA[i].  Needs store_docs and pfb_build_bwt with sa/rssa. */
 int pfb_write_doc_array(pfb_ctx *, const char *prefix);
+/* The marker-array join of src/mps_to_ma.cpp (write_marker_array, include/marker_array.hpp:137-174, over the rle_window_arr of
+ * include/rle_window_array.hpp:15-51,118-130): <mps> holds runs of text positions with their variant markers
+ * ([first, last, marker..., 2^64-1] as u64 words), the output holds, for every maximal run of BWT positions whose SA[i]
+ * carry the same non-empty marker list, [first i, last i, marker..., 2^64-1].
+ * pfb_write_marker_array joins with the SA pfb_build_bwt (sa or rssa) left on the device - no .sa stream;
+ * pfb_marker_join reads the SA as u64 entries from a file or from stdin ("-"), like the reference's tool (any context will do). */
+int pfb_write_marker_array(pfb_ctx *, const char *mps_path, const char *out_path);
+int pfb_marker_join(pfb_ctx *, const char *mps_path, const char *sa_path_or_dash, const char *out_path);
 /* device bytes a full in-memory pfb_build_bwt needs at its peak (estimate), incl. what the context already holds */
 uint64_t pfb_build_workspace_bytes(const pfb_ctx *, int sa, int rssa);
 /* device bytes available to this context right now (free on the device + held idle by the library's allocator) */

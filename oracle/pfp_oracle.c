@@ -536,3 +536,80 @@ int pfo_merge(pfo_t *out, pfo_t *const *parts, int nparts) {
     free(buf); free(ph); free(last); free(sai);
     return 0;
 }
+
+
+/* ---- marker-array join: src/mps_to_ma.cpp:43-50 -> write_marker_array (include/marker_array.hpp:137-174) over an
+ * rle_window_arr (include/rle_window_array.hpp).  The reference answers at(s) with rank/select on bit vectors of the
+ * run starts and ends (:118-130): "the number of starts <= s is one more than the number of ends < s", i.e. s lies in
+ * the run [first, last] found by a search over the (ascending) starts.  A run that starts or ends at 0 makes the
+ * reference exit (:28-31, rs == re == 0 there); marker lists are compared by content (vec_eq, marker_array.hpp:148). */
+static uint64_t *mj_in; static uint64_t mj_R; static uint64_t *mj_start, *mj_end, *mj_voff;
+static long mj_at(uint64_t s) {
+    if (!mj_R || s < mj_start[0]) return -1;
+    uint64_t lo = 0, hi = mj_R;
+    while (hi - lo > 1) { uint64_t mid = lo + (hi - lo) / 2; if (mj_start[mid] <= s) lo = mid; else hi = mid; }
+    return s <= mj_end[lo] ? (long)lo : -1;
+}
+static int mj_same(long a, long b) {
+    if (a == b) return 1;
+    if (a < 0 || b < 0) return 0;
+    uint64_t ka = mj_voff[a + 1] - mj_voff[a], kb = mj_voff[b + 1] - mj_voff[b];
+    if (ka != kb) return 0;
+    return memcmp(mj_in + mj_voff[a], mj_in + mj_voff[b], ka * 8) == 0;
+}
+int pfo_marker_join(const char *mps_path, const char *sa_path, const char *out_path) {
+    FILE *f = fopen(mps_path, "rb");
+    if (!f) return -1;
+    fseek(f, 0, SEEK_END); long bytes = ftell(f); fseek(f, 0, SEEK_SET);
+    uint64_t nw = (uint64_t)bytes / 8;
+    mj_in = (uint64_t *)malloc((nw + 1) * 8);
+    if (nw && fread(mj_in, 8, nw, f) != nw) { fclose(f); return -1; }
+    fclose(f);
+    mj_R = 0;
+    for (uint64_t i = 0; i < nw; ++i) if (mj_in[i] == ~0ull) ++mj_R;
+    mj_start = (uint64_t *)malloc((mj_R + 1) * 8); mj_end = (uint64_t *)malloc((mj_R + 1) * 8); mj_voff = (uint64_t *)malloc((mj_R + 2) * 8);
+    uint64_t r = 0, b0 = 0;
+    for (uint64_t i = 0; i < nw; ++i) {
+        if (mj_in[i] != ~0ull) continue;
+        if (i - b0 < 3) return -2;                                             /* two keys, at least one marker */
+        mj_start[r] = mj_in[b0]; mj_end[r] = mj_in[b0 + 1]; mj_voff[r] = b0 + 2; /* values stay in place: voff indexes mj_in */
+        if (mj_start[r] == 0 || mj_end[r] == 0) { fprintf(stderr, "warning equal run start at 0 or run end at 0\n"); return 1; }
+        ++r; b0 = i + 1;
+    }
+    /* voff[r+1] - voff[r] must be the value count: keep explicit ends */
+    uint64_t *vend = (uint64_t *)malloc((mj_R + 1) * 8);
+    r = 0; b0 = 0;
+    for (uint64_t i = 0; i < nw; ++i) if (mj_in[i] == ~0ull) { vend[r++] = i; b0 = i + 1; }
+    /* compact the values so that voff is a prefix array */
+    uint64_t *vals = (uint64_t *)malloc((nw + 1) * 8), *voff = (uint64_t *)malloc((mj_R + 2) * 8), t = 0;
+    for (r = 0; r < mj_R; ++r) { voff[r] = t; for (uint64_t j = mj_voff[r]; j < vend[r]; ++j) vals[t++] = mj_in[j]; }
+    voff[mj_R] = t;
+    free(mj_in); free(mj_voff); free(vend);
+    mj_in = vals; mj_voff = voff;
+    FILE *sa = !strcmp(sa_path, "-") ? stdin : fopen(sa_path, "rb");
+    FILE *o = fopen(out_path, "wb");
+    if (!sa || !o) return -1;
+    uint64_t s, i = 0, first = 0, last = 0; const uint64_t delim = ~0ull;
+    long prev = -1;
+    while (fread(&s, 8, 1, sa) == 1) {                                         /* marker_array.hpp:145-163 */
+        long cur = mj_at(s);
+        if (!mj_same(cur, prev)) {
+            if (prev >= 0) {
+                fwrite(&first, 8, 1, o); fwrite(&last, 8, 1, o);
+                fwrite(mj_in + mj_voff[prev], 8, mj_voff[prev + 1] - mj_voff[prev], o);
+                fwrite(&delim, 8, 1, o);
+            }
+            first = i;
+        }
+        last = i; prev = cur; ++i;
+    }
+    if (prev >= 0) {                                                           /* :164-171 */
+        fwrite(&first, 8, 1, o); fwrite(&last, 8, 1, o);
+        fwrite(mj_in + mj_voff[prev], 8, mj_voff[prev + 1] - mj_voff[prev], o);
+        fwrite(&delim, 8, 1, o);
+    }
+    fclose(o);
+    if (sa != stdin) fclose(sa);
+    free(mj_in); free(mj_voff); free(mj_start); free(mj_end);
+    return 0;
+}

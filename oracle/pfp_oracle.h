@@ -76,6 +76,8 @@ int pfo_load_parse(pfo_t *o, const char *prefix);
 int pfo_write_parse_files(const pfo_t *o, const char *prefix, int U, int with_sai);
 int pfo_write_bwt_files(const pfo_t *o, const char *prefix, int U, int sa, int rssa);
 
+/* mps_to_ma (src/mps_to_ma.cpp, include/marker_array.hpp:137-174): 0 ok, 1 = the reference's own refusal, < 0 bad input */
+int pfo_marker_join(const char *mps_path, const char *sa_path, const char *out_path);
 void pfo_init(pfo_t *o, int w, int p, int non_acgt_to_a);
 void pfo_free(pfo_t *o);
 

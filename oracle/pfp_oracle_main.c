@@ -12,6 +12,11 @@
 #include <string.h>
 
 int main(int argc, char **argv) {
+    if (argc == 5 && !strcmp(argv[1], "--marker-join")) {            /* pfp_oracle --marker-join <mps> <sa|-> <out> */
+        int rc = pfo_marker_join(argv[2], argv[3], argv[4]);
+        if (rc < 0) fprintf(stderr, "bad mps / sa input\n");
+        return rc ? 1 : 0;
+    }
     int w = 10, p = 100, sa = 0, rssa = 0, bits = 32, ntoa = 0, parse_only = 0, merge = 0, write_last = 0;
     const char *out = NULL; const char *in[1024]; int nin = 0;
     for (int i = 1; i < argc; ++i) {

@@ -17,7 +17,7 @@ EXPORTS = [
     "pfb_copy_bwt", "pfb_copy_sa", "pfb_copy_ssa", "pfb_copy_esa", "pfb_get_docs", "pfb_upload_text",
     "pfb_run_resident", "pfb_release_text", "pfb_clear",
     "pfb_nccl_unique_id", "pfb_shard_init_nccl", "pfb_shard_init_host", "pfb_get_shard_info", "pfb_get_pending_bases",
-    "pfb_kat_trigger", "pfb_kat_trigger_static", "pfb_add_chunk", "pfb_add_fasta_range", "pfb_save_last_sai", "pfb_build_bwt_to_files", "pfb_build_workspace_bytes", "pfb_write_doc_array", "pfb_device_free_bytes", "pfb_save_parse_async", "pfb_wait_saves",
+    "pfb_kat_trigger", "pfb_kat_trigger_static", "pfb_add_chunk", "pfb_add_fasta_range", "pfb_save_last_sai", "pfb_build_bwt_to_files", "pfb_build_workspace_bytes", "pfb_write_doc_array", "pfb_write_marker_array", "pfb_marker_join", "pfb_device_free_bytes", "pfb_save_parse_async", "pfb_wait_saves",
 ]
 
 
@@ -90,6 +90,8 @@ def load():
     lib.pfb_run_resident.argtypes = [vp, C.c_int, C.c_int]
     lib.pfb_build_bwt_to_files.argtypes = [vp, C.c_char_p, C.c_int, C.c_int, C.c_uint64]
     lib.pfb_write_doc_array.argtypes = [vp, C.c_char_p]
+    lib.pfb_write_marker_array.argtypes = [vp, C.c_char_p, C.c_char_p]
+    lib.pfb_marker_join.argtypes = [vp, C.c_char_p, C.c_char_p, C.c_char_p]
     lib.pfb_device_free_bytes.argtypes = [vp, vp]
     lib.pfb_build_workspace_bytes.restype = C.c_uint64
     lib.pfb_build_workspace_bytes.argtypes = [vp, C.c_int, C.c_int]
@@ -239,6 +241,14 @@ class Context:
 
     def write_doc_array(self, prefix):
         self._ck(self.lib.pfb_write_doc_array(self.h, prefix.encode()))
+
+    def write_marker_array(self, mps_path, out_path):
+        """mps_to_ma with the SA that generate_bwt left on the device"""
+        self._ck(self.lib.pfb_write_marker_array(self.h, mps_path.encode(), out_path.encode()))
+
+    def marker_join(self, mps_path, sa_path, out_path):
+        """mps_to_ma: SA (u64 entries) from a file or '-' (stdin)"""
+        self._ck(self.lib.pfb_marker_join(self.h, mps_path.encode(), sa_path.encode(), out_path.encode()))
 
     def write_bwt(self, prefix, sa=False, rssa=False):
         self._ck(self.lib.pfb_write_bwt(self.h, prefix.encode(), int(sa), int(rssa), None))

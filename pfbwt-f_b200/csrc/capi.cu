@@ -196,6 +196,16 @@ int pfb_write_doc_array(pfb_ctx *c, const char *prefix) {
     if (!prefix) return c->eng.fail(PFB_ERR_ARG, "null prefix");
     return c->eng.write_doc_array(prefix);
 }
+int pfb_write_marker_array(pfb_ctx *c, const char *mps_path, const char *out_path) {
+    CTX_GUARD(c);
+    if (!mps_path || !out_path) return c->eng.fail(PFB_ERR_ARG, "null path");
+    return c->eng.write_marker_array(mps_path, out_path);
+}
+int pfb_marker_join(pfb_ctx *c, const char *mps_path, const char *sa_path_or_dash, const char *out_path) {
+    CTX_GUARD(c);
+    if (!mps_path || !sa_path_or_dash || !out_path) return c->eng.fail(PFB_ERR_ARG, "null path");
+    return c->eng.marker_join(mps_path, sa_path_or_dash, out_path);
+}
 int pfb_device_free_bytes(const pfb_ctx *c, size_t *out) {
     if (!c || !out) return PFB_ERR_ARG;
     cudaSetDevice(c->eng.device);

@@ -11,6 +11,7 @@
 #include "pipeline.cuh"
 #include "ingest.cuh"
 #include "devio.cuh"
+#include "markers.cuh"
 #include <memory>
 #include <thread>
 
@@ -378,6 +379,87 @@ struct Engine {
             std::string e;
             if (dev_file(prefix + ".da", da.get(), len * 4, e)) return fail(PFB_ERR_IO, e);
             return PFB_OK;
+        } catch (const Error &e) { return fail(e.code, e.what()); }
+    }
+
+    // ---- marker array: the join of src/mps_to_ma.cpp / include/marker_array.hpp:137-174 on the device
+    // (markers.cuh).  write_marker_array takes the SA pfb_build_bwt left in HBM - the 8 bytes per base of `--stdout sa` never
+    // leave the device -, marker_join reads a .sa file or stdin ("-") of u64 entries like the reference's tool.
+    static u64 marker_chunk_entries() {
+        u64 c = 1ull << 27;
+        if (const char *e = getenv("PFB_MA_CHUNK")) { const long v = atol(e); if (v > 0) c = (u64)v; }      // test knob
+        return c;
+    }
+    int marker_flush(FILE *f, const DevBuf<u64> &out, u64 nout) {
+        std::string e;
+        if (nout && write_dev_stream(f, out.get(), nout * 8, device, ws.st, e)) return fail(PFB_ERR_IO, e);
+        return PFB_OK;
+    }
+    int write_marker_array(const std::string &mps, const std::string &outp) {
+        try {
+            if (!built || !(built_sa || built_rssa)) return fail(PFB_ERR_ARG, "the marker array needs a BWT built with the suffix array (-s / -r)");
+            if (comm) return fail(PFB_ERR_ARG, "the marker array is a single-GPU output");
+            MarkerRuns mr;
+            int rc = load_marker_runs(mps, mr, device, ws, err);
+            if (rc) return fail(rc, err);
+            FILE *f = fopen(outp.empty() ? "out" : outp.c_str(), "wb");
+            if (!f) return fail(PFB_ERR_IO, "could not open " + outp + " for writing");
+            const u64 len = bwt.len, CH = marker_chunk_entries();
+            const int U = prm.bits / 8;
+            MarkerCarry carry;
+            DevBuf<u64> out;
+            for (u64 c0 = 0; c0 < len && !rc; c0 += CH) {
+                const u64 m = len - c0 < CH ? len - c0 : CH;
+                const bool has_next = c0 + m < len;
+                u64 next = 0, nout = 0;
+                if (U == 4) {
+                    const u32 *sp = reinterpret_cast<const u32 *>(bwt.sa.get()) + c0;
+                    if (has_next) next = read_scalar(sp + m, ws.st);
+                    rc = marker_join_chunk<u32>(mr, sp, m, has_next, next, carry, out, &nout, ws);
+                } else {
+                    const u64 *sp = reinterpret_cast<const u64 *>(bwt.sa.get()) + c0;
+                    if (has_next) next = read_scalar(sp + m, ws.st);
+                    rc = marker_join_chunk<u64>(mr, sp, m, has_next, next, carry, out, &nout, ws);
+                }
+                if (!rc) rc = marker_flush(f, out, nout);
+            }
+            fclose(f);
+            return rc;
+        } catch (const Error &e) { return fail(e.code, e.what()); }
+    }
+    int marker_join(const std::string &mps, const std::string &sa_path, const std::string &outp) {
+        try {
+            MarkerRuns mr;
+            int rc = load_marker_runs(mps, mr, device, ws, err);
+            if (rc) return fail(rc, err);
+            const bool from_stdin = sa_path == "-";
+            FILE *in = from_stdin ? stdin : fopen(sa_path.c_str(), "rb");
+            if (!in) return fail(PFB_ERR_IO, "error opening " + sa_path);
+            FILE *f = fopen(outp.empty() ? "out" : outp.c_str(), "wb");
+            if (!f) { if (!from_stdin) fclose(in); return fail(PFB_ERR_IO, "could not open " + outp + " for writing"); }
+            const u64 CH = marker_chunk_entries();
+            MarkerCarry carry;
+            DevBuf<u64> out, dsa(CH + 1);
+            // the SA goes through the host in chunks of CH entries plus one of look-ahead (a trailing partial entry is
+            // dropped like fread(&s, 8, 1, fp) drops it)
+            std::vector<u64> hbuf(CH + 1);
+            u64 have = fread(hbuf.data(), 8, CH + 1, in);
+            while (have && !rc) {
+                const bool has_next = have == CH + 1;
+                const u64 m = has_next ? CH : have;
+                h2d(dsa.get(), hbuf.data(), have * 8, ws.st);
+                stream_sync(ws.st);
+                const u64 next = has_next ? hbuf[CH] : 0;
+                u64 nout = 0;
+                rc = marker_join_chunk<u64>(mr, dsa.get(), m, has_next, next, carry, out, &nout, ws);
+                if (!rc) rc = marker_flush(f, out, nout);
+                if (!has_next) break;
+                hbuf[0] = next;
+                have = 1 + fread(hbuf.data() + 1, 8, CH, in);
+            }
+            fclose(f);
+            if (!from_stdin) fclose(in);
+            return rc;
         } catch (const Error &e) { return fail(e.code, e.what()); }
     }
 

@@ -17,7 +17,7 @@ static const int BITS = 32;
 #endif
 
 struct Args {
-    std::string in_fname, output, stdout_ext;
+    std::string in_fname, output, stdout_ext, marker_mps;
     size_t w = 10, p = 100;
     int sa = 0, rssa = 0, mmap = 0, parse_only = 0, trim_non_acgt = 0, non_acgt_to_a = 0, pfbwt_only = 0, verbose = 0, print_docs = 0;
     int write_last = 0, write_sai = 0, doc_array = 0;
@@ -62,6 +62,8 @@ static void print_help() {
 "    --print-docs        write <prefix>.docs\n"
 "    --write-last        also write <prefix>.last (last char of every phrase, include/utils.h EXTLST)\n"
 "    --doc-array         also write <prefix>.da: uint32 record index of SA[i] for every BWT position (implies --print-docs, needs -s or -r)\n"
+"    --marker-array <f>  also write <prefix>.ma: the join of the marker runs in <f> (.mps) with the SA, as mps_to_ma writes it from\n"
+"                        `--stdout sa` (needs -s or -r; the SA does not leave the device)\n"
 "    --write-sai         also write <prefix>.sai (end position of every phrase, include/utils.h EXTSAI)\n"
 "    --stdout <ext>      output file ending <ext> will be stdout instead (bwt, sa)\n"
 "    --device <int>      CUDA device ordinal [default: 0]\n"
@@ -82,6 +84,7 @@ static Args parse_args(int argc, char **argv) {
         {"write-last", no_argument, &args.write_last, 1},
         {"write-sai", no_argument, &args.write_sai, 1},
         {"doc-array", no_argument, &args.doc_array, 1},
+        {"marker-array", required_argument, NULL, 'M'},
         {"stdout", required_argument, NULL, 'c'},
         {"verbose", no_argument, &args.verbose, 1},
         {"sa", no_argument, NULL, 's'},
@@ -105,6 +108,7 @@ static Args parse_args(int argc, char **argv) {
         case 'o': args.output.assign(optarg); break;
         case 'c': args.stdout_ext = optarg; break;
         case 'D': args.device = atoi(optarg); break;
+        case 'M': args.marker_mps = optarg; break;
         case '?': fprintf(stderr, "Unknown option. Use -h for help.\n"); exit(1);
         }
     }
@@ -114,6 +118,8 @@ static Args parse_args(int argc, char **argv) {
     if (args.in_fname == "-" && args.output == "") die("if reading from stdin, need a prefix for output files (-o, --output)");
     if (args.in_fname != "-" && args.output == "") args.output = args.in_fname;
     if (args.parse_only && args.pfbwt_only) die("cannot simulatneously do parse_only and pfbwt_only");
+    if (!args.marker_mps.empty() && !args.sa && !args.rssa) { fprintf(stderr, "--marker-array needs the suffix array (-s or -r)\n"); exit(1); }
+    if (!args.marker_mps.empty() && args.mmap) { fprintf(stderr, "--marker-array joins with the SA in device memory: not with -m\n"); exit(1); }
     if (args.doc_array) {
         args.print_docs = 1;
         if (!args.sa && !args.rssa) { fprintf(stderr, "--doc-array needs the suffix array (-s or -r)\n"); exit(1); }
@@ -191,6 +197,7 @@ int main(int argc, char **argv) {
             if (pfb_device_free_bytes(ctx, &fr) == 0 && need > fr) bucketed = true;
         }
         if (bucketed && !args.stdout_ext.empty()) { fprintf(stderr, "--stdout is not available with -m\n"); exit(1); }
+        if (bucketed && !args.marker_mps.empty()) { fprintf(stderr, "--marker-array needs the SA in device memory: the build does not fit (or -m was given)\n"); exit(1); }
         fprintf(stderr, bucketed ? "workspace will be cut into key-range buckets streamed to the output files\n" : "workspace will be contained in HBM\n");
         {
             Timer t(any_sa ? "TASK\tgenerating final BWT w/ full and/or run-length SA\t" : "TASK\tgenerating final BWT w/o SA\t");
@@ -204,6 +211,7 @@ int main(int argc, char **argv) {
                 SubTimer t3("writing BWT files");
                 if (pfb_write_bwt(ctx, args.output.c_str(), args.sa, args.rssa, args.stdout_ext.empty() ? NULL : args.stdout_ext.c_str())) die_ctx(ctx);
                 if (args.doc_array && pfb_write_doc_array(ctx, args.output.c_str())) die_ctx(ctx);
+                if (!args.marker_mps.empty() && pfb_write_marker_array(ctx, args.marker_mps.c_str(), (args.output + ".ma").c_str())) die_ctx(ctx);
             }
         }
         pfb_sizes sz;

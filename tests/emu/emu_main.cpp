@@ -7,6 +7,8 @@
 //
 //   pfb_emu [-w W] [-p P] [-s] [-r] [--bits 32|64] [--non-acgt-to-a] [--parse-only] [-o prefix] in.fa
 //   pfb_emu --merge [-w W] [-p P] [-s] [--bits 64] -o out pfx1 pfx2 ...
+//   pfb_emu --marker-join <mps> <sa file or -> <out>          (mps_to_ma)
+//   pfb_emu ... -s --marker-array <mps> ... in.fa              (also <prefix>.ma from the SA in memory)
 #define PFB_EMU 1
 #include "engine.hpp"
 
@@ -17,8 +19,13 @@ size_t &dev_bytes_peak() { static size_t v = 0; return v; }
 
 int main(int argc, char **argv) {
     int w = 10, p = 100, sa = 0, rssa = 0, bits = 32, ntoa = 0, parse_only = 0, merge = 0, docs = 0, write_last = 0, bucketed = 0;
-    std::string out;
+    std::string out, marker_mps;
     std::vector<std::string> in;
+    if (argc == 5 && std::string(argv[1]) == "--marker-join") {
+        pfb::Engine J;
+        if (J.marker_join(argv[2], argv[3], argv[4])) { fprintf(stderr, "%s\n", J.err.c_str()); return 1; }
+        return 0;
+    }
     for (int i = 1; i < argc; ++i) {
         std::string a = argv[i];
         if (a == "-w") w = atoi(argv[++i]);
@@ -33,6 +40,7 @@ int main(int argc, char **argv) {
         else if (a == "--write-last") write_last = 1;
         else if (a == "-m") bucketed = 1;                 // key-range buckets streamed to the files (PFB_BUCKETS / PFB_HBM_LIMIT)
         else if (a == "-o") out = argv[++i];
+        else if (a == "--marker-array") marker_mps = argv[++i];
         else in.push_back(a);
     }
     if (in.empty()) { fprintf(stderr, "usage: see source header\n"); return 2; }
@@ -60,6 +68,7 @@ int main(int argc, char **argv) {
     if (parse_only) return 0;
     if (bucketed ? E.build_to_files(out, sa, rssa, 0) : (E.build(sa, rssa) || E.write_bwt_files(out, sa, rssa, ""))) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }
     if (bucketed) fprintf(stderr, "buckets: %lu\n", (unsigned long)E.stream_buckets);
+    if (!marker_mps.empty() && E.write_marker_array(marker_mps, out + ".ma")) { fprintf(stderr, "%s\n", E.err.c_str()); return 1; }
     fprintf(stderr, "# easy cases: %lu, # hard cases: %lu\nn: %lu\nr: %lu\nrounds: phrase %u parse_sa %u dict %u\n",
             (unsigned long)E.bwt.easy, (unsigned long)E.bwt.hard, (unsigned long)E.bwt.n, (unsigned long)E.bwt.r,
             E.tm.phrase_sort_rounds, E.tm.parse_sa_rounds, E.tm.dict_sort_rounds);
