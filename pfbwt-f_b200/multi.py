@@ -9,8 +9,10 @@ src/pfbwt-f.cpp:351-367), without the per-part files in between.
 The input files are dealt to the ranks in order, as contiguous groups (rank order = text order).  With fewer files than
 ranks (typically ONE multi-record or single-record FASTA) every file is instead cut into byte ranges, one per rank of its
 share of the ranks (pfb_add_fasta_range: the cuts fall anywhere, also inside a record - the w-overlapping chunk split).  Rank g parses its files on GPU g; the parses are merged over NCCL; every rank builds and writes its
-slice of OUT.bwt (/.sa/.ssa/.esa) at its offset.  Host code only plumbs: all work is in libpfbwt_b200.so
-(include/pfbwt_b200.h, "one job over several GPUs")."""
+slice of OUT.bwt (/.sa/.ssa/.esa) at its offset.  An input that names a PRE-PARSED prefix (<in>.dict and <in>.parse exist, written
+by `pfbwt-f64 --parse-only`) is loaded instead of parsed - exactly merge_pfp's rule (src/merge_pfp.cpp:100-113 load_or_generate_parser):
+`merge_pfp -t N` then is this launcher on N GPUs, each rank holding only ITS parts.  Host code only plumbs: all work is in
+libpfbwt_b200.so (include/pfbwt_b200.h, "one job over several GPUs")."""
 import argparse
 import os
 import sys
@@ -38,7 +40,12 @@ def main():
     B = binding()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    preparsed = [os.path.exists(f + ".dict") and os.path.exists(f + ".parse") for f in a.inputs]
     split = len(a.inputs) < world
+    if split and any(preparsed):
+        if rank == 0:
+            sys.stderr.write("pre-parsed prefixes cannot be cut into byte ranges: give at least one input per rank\n")
+        return 1
     if split and world % len(a.inputs) != 0:
         if rank == 0:
             sys.stderr.write(f"{len(a.inputs)} input files cannot be split evenly over {world} ranks (use 1 file, or a divisor of the ranks)\n")
@@ -62,7 +69,13 @@ def main():
             ctx.add_fasta_range(f, size * k // per, size * (k + 1) // per)
         else:
             for f in mine:
-                ctx.add_fasta(f)
+                if os.path.exists(f + ".dict") and os.path.exists(f + ".parse"):
+                    part = B.Context(device=local_rank, bits=a.bits, w=a.w, p=a.p, get_sai=a.s or a.r, non_acgt_to_a=a.non_acgt_to_a)
+                    part.load_parser(f, False, False)
+                    ctx.append(part)                       # PfParser::operator+= (include/pfparser.hpp:194-263)
+                    part.close()
+                else:
+                    ctx.add_fasta(f)
     except B.PfbError as e:                        # keep going: the failure is agreed on inside finalize()
         sys.stderr.write(f"[rank {rank}] {e.msg}\n")
     try:

@@ -87,7 +87,15 @@ extern "C" int pfb_emu_shard_run(int rank, int world, pfb_allgatherv_fn fn, void
     pfb::HostCallComm *hc = new pfb::HostCallComm();
     hc->rank = rank; hc->world = world; hc->fn = fn; hc->user = user;
     E.comm.reset(hc);
-    int rc = range_end > range_begin ? E.add_fasta_range(fasta, range_begin, range_end) : E.add_fasta(fasta);
+    // a pre-parsed part (<fasta>.dict and <fasta>.parse exist) is loaded instead of parsed: src/merge_pfp.cpp:100-113
+    int rc;
+    const std::string pfx(fasta);
+    if (!(range_end > range_begin) && access((pfx + ".dict").c_str(), R_OK) == 0 && access((pfx + ".parse").c_str(), R_OK) == 0) {
+        pfb::Engine R;
+        R.prm = E.prm;
+        rc = R.load_parse(pfx, false, false);
+        if (rc) E.err = R.err; else rc = E.append_parse_of(R);
+    } else rc = range_end > range_begin ? E.add_fasta_range(fasta, range_begin, range_end) : E.add_fasta(fasta);
     if (rc) fprintf(stderr, "[emu rank %d] %s\n", rank, E.err.c_str());
     // a failed load still has to take part in the collective finalize
     rc = E.finalize();

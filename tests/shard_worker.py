@@ -81,6 +81,11 @@ def main():
         try:
             if rng:
                 ctx.add_fasta_range(fasta, rng[0], rng[1])
+            elif os.path.exists(fasta + ".dict") and os.path.exists(fasta + ".parse"):      # a pre-parsed part: merge_pfp's rule
+                part = b.Context(device=rank if mode == "nccl" else 0, bits=bits, w=w, p=p, get_sai=bool(sa or rssa))
+                part.load_parser(fasta, False, False)
+                ctx.append(part)
+                part.close()
             else:
                 ctx.add_fasta(fasta)
             ctx.finalize()

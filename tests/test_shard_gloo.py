@@ -29,10 +29,11 @@ def free_port():
     return p
 
 
-def run_job(mode, tmp, pieces, w, p, bits, sa, rssa, non_acgt_to_a=False, expect_fail=False, byte_cuts=None, line_width=70):
+def run_job(mode, tmp, pieces, w, p, bits, sa, rssa, non_acgt_to_a=False, expect_fail=False, byte_cuts=None, line_width=70, preparse=None):
     """pieces: list (one per rank) of record lists.  Returns (sharded prefix, reference prefix).
     byte_cuts = (world, [fractions]) instead splits ONE file holding all records by byte ranges (cuts fall anywhere,
-    also inside records and header lines: pfb_add_fasta_range)."""
+    also inside records and header lines: pfb_add_fasta_range).  preparse = a command prefix (e.g. the emulator or bin/pfbwt-f64):
+    every rank's part is parsed to <part>.dict/.parse/... first and the job LOADS the parts (merge_pfp over ranks)."""
     world = len(pieces)
     allrecs = [r for pc in pieces for r in pc]
     whole = os.path.join(tmp, "whole.fa")
@@ -49,6 +50,9 @@ def run_job(mode, tmp, pieces, w, p, bits, sa, rssa, non_acgt_to_a=False, expect
             fa = os.path.join(tmp, f"part{g}.fa")
             write_fasta(fa, pc, line_width=line_width)
             fas.append(fa)
+            if preparse:
+                run(preparse + ["-w", str(w), "-p", str(p), "--parse-only", fa])
+                assert os.path.exists(fa + ".dict") and os.path.exists(fa + ".parse")
     refp = os.path.join(tmp, "ref")
     cmd = [ref_bin("pfbwt-f64" if bits == 64 else "pfbwt-f"), "-w", str(w), "-p", str(p), "-o", refp]
     if sa:
@@ -189,3 +193,13 @@ def test_split_cut_exactly_at_header_and_in_header(tmp_path):
         fr = [(c + 0.25) / size for c in cuts]
         out, refp = run_job("emu", str(sub), [recs], 10, 100, 32, True, False, byte_cuts=(3, fr), line_width=60)
         assert_same_files(out, refp, exts_for(True, False))
+
+
+@pytest.mark.parametrize("world,bits", [(2, 64), (3, 32)])
+def test_preparsed_parts_job(tmp_path, world, bits):
+    """merge_pfp over ranks: every rank LOADS its pre-parsed part (<part>.dict/.parse from --parse-only; the rule of
+    src/merge_pfp.cpp:100-113) instead of parsing a FASTA, the merge and the BWT build are the same collective job"""
+    emu = os.path.join(ROOT, "tests", "emu", "pfb_emu")
+    recs = pangenome_records(5000, 6, 10, seed=17) + [("t", random_bases(900, 3))]
+    out, refp = run_job("emu", str(tmp_path), split_records(recs, world), 10, 100, bits, True, True, preparse=[emu, "--bits", str(bits)])
+    assert_same_files(out, refp, exts_for(True, True))

@@ -144,3 +144,42 @@ def test_multi_launcher_splits_one_file(tmp_path):
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600)
     assert r.returncode == 0, r.stderr.decode(errors="replace")[-3000:]
     assert_same_files(out, refp, exts_for(True, True))
+
+
+# ---- merge_pfp over ranks: every rank loads its pre-parsed parts ---------------------------------------------------------------
+@pytest.mark.parametrize("mode,world", [("cuda", 2), ("nccl", 2)])
+def test_preparsed_parts_job(tmp_path, mode, world):
+    import os
+    from pfp_util import ROOT
+    if mode == "nccl" and ngpu() < world:
+        pytest.skip(f"needs {world} GPUs")
+    recs = pangenome_records(200_000, 6, 200, seed=57) + [("t", random_bases(50_000, 3))]
+    out, refp = run_job(mode, str(tmp_path), split_records(recs, world), 10, 100, 64, True, True,
+                        preparse=[os.path.join(ROOT, "bin", "pfbwt-f64")])
+    assert_same_files(out, refp, exts_for(True, True))
+
+
+def test_multi_launcher_preparsed_parts(tmp_path):
+    """pfbwt-f_b200/multi.py with pre-parsed prefixes as inputs (= merge_pfp + pfbwt-f64 --pfbwt-only in one job); a FASTA
+    and a prefix may be mixed like merge_pfp's inputs"""
+    import os, subprocess, sys
+    from pfp_util import ROOT, write_fasta, run
+    from test_shard_gloo import free_port
+    world = 2 if ngpu() >= 2 else 1
+    recs = pangenome_records(150_000, 6, 150, seed=59)
+    fas = []
+    for g in range(3):
+        fa = os.path.join(str(tmp_path), f"in{g}.fa")
+        write_fasta(fa, recs[2 * g:2 * g + 2], line_width=80)
+        fas.append(fa)
+        if g != 1:
+            run([os.path.join(ROOT, "bin", "pfbwt-f64"), "--parse-only", fa])
+    whole = os.path.join(str(tmp_path), "whole.fa")
+    write_fasta(whole, recs, line_width=80)
+    refp, out = os.path.join(str(tmp_path), "ref"), os.path.join(str(tmp_path), "out")
+    run([ref_bin("pfbwt-f64"), "-s", "-r", "-o", refp, whole])
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", str(free_port()), os.path.join(ROOT, "pfbwt-f_b200", "multi.py"), "-s", "-r", "--save-parse", "-o", out] + fas
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=600)
+    assert r.returncode == 0, r.stderr.decode(errors="replace")[-3000:]
+    assert_same_files(out, refp, exts_for(True, True))
