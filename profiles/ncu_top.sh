@@ -1,7 +1,8 @@
 #!/bin/bash
 # profiles/ncu_top.sh TAG KERNEL_REGEX [KERNEL_REGEX...]   (run under gpurun, one GPU)
 # 1. plain bench run (must exit 0), 2. ncu launch list of the same command, 3. one `ncu --set full`
-# capture of the longest launch of every kernel regex given.  Outputs under gpurun_out/.
+# capture of the longest launch of every kernel regex given (regexes see DEMANGLED names, as the launch list prints them:
+# `for_kernel<...k_fingerprint...>` lambdas can be picked).  Outputs under gpurun_out/.
 set -u
 TAG=$1; shift
 CMD=${NCU_CMD:-"python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e --no-single-job --no-file-leg --no-parity"}
@@ -24,6 +25,6 @@ PY
 )
   NAME=$(echo "$RX" | tr -c 'A-Za-z0-9_' '_')
   echo "profiling $RX invocation $IDX"
-  ncu --set full --clock-control none --import-source on --kernel-id ::regex:"$RX":$IDX -o gpurun_out/${TAG}_${NAME} -f $CMD > gpurun_out/${TAG}_${NAME}.log 2>&1
+  ncu --set full --clock-control none --import-source on --kernel-name-base demangled --kernel-id ::regex:"$RX":$IDX -o gpurun_out/${TAG}_${NAME} -f $CMD > gpurun_out/${TAG}_${NAME}.log 2>&1
 done
 ls -la gpurun_out/ | grep ${TAG}
