@@ -9,11 +9,13 @@
 //      (bytes up to and including their first trigger), rank g appends what it needs to its text;
 //   3. every rank parses its piece (parse_piece: same kernels as the single-GPU path) into a local
 //      sorted dictionary + parse;
-//   4. merge_pfp-style merge (include/pfparser.hpp:194-263, src/merge_pfp.cpp:97-170): the local
-//      dictionaries are all-gathered over NVLink, the union is sorted and deduplicated on every rank
-//      (sort_strings with duplicate groups), local ranks are renamed to global ranks and the renamed
-//      parses / last / sai arrays are all-gathered.  After this every rank holds the whole parse
-//      (dictionary replicated, as the range-partitioned suffix sort of build.cuh needs it).
+//   4. merge_pfp-style merge (include/pfparser.hpp:194-263, src/merge_pfp.cpp:97-170): the distinct words of
+//      the local dictionaries are range-partitioned to owner ranks by one all-to-all over NVLink (contiguous
+//      slices: a local dictionary is sorted), every owner sorts and deduplicates its 1/G of the union
+//      (sort_strings with duplicate groups), the owners return the global ranks (reverse all-to-all) and
+//      all-gather their pieces of the global dictionary; local ranks are renamed and the renamed parses /
+//      last / sai arrays are all-gathered.  After this every rank holds the whole parse (dictionary
+//      replicated, as the range-partitioned suffix sort of build.cuh needs it).
 // Error handling is collective: a rank that fails still takes part in the next exchange and all
 // ranks return an error together.
 
@@ -165,87 +167,181 @@
     }
 
     // ---- 4. merge of the ranks' parses -----------------------------------------------------------------
+    // The distinct words of all ranks are RANGE-PARTITIONED to owner ranks by an all-to-all (the hash-partitioned phrase
+    // exchange of the north star, with an order-preserving key instead of a hash so that an owner's words are one interval
+    // of the global dictionary): key = the first 21 symbols of a word (pack_syms, 63 bits, order preserving; equal keys go to
+    // the same owner).  A local dictionary is sorted, so what a rank sends to owner d is one contiguous slice of its
+    // dictionary image - no scatter.  Every owner sorts and deduplicates 1/G of the union (sort_strings with duplicate
+    // groups) instead of every rank sorting all of it; global rank = words of the owners before + local rank.  The owners
+    // send the ranks back (the reverse all-to-all) and all-gather their piece of the global dictionary, which every rank
+    // needs whole for the range-partitioned suffix sort of build.cuh.
     int shard_merge(DeviceParse &lp, u64 n_total, float &t_x, float &t_m) {
         pfbStream_t st = ws.st;
         const int G = comm->world, g = comm->rank;
         Timer xt(st);
-        u64 sz[3] = {lp.P, lp.Dw, lp.dsize ? lp.dsize - 1 : 0};          // dictionary bytes without the EndOfDict byte
-        std::vector<u64> szs = comm->gather_u64(sz, 3, st);
-        std::vector<u64> cP((size_t)G), cW((size_t)G), cB((size_t)G), oP((size_t)G + 1, 0), oW((size_t)G + 1, 0), oB((size_t)G + 1, 0);
-        for (int r = 0; r < G; ++r) {
-            cP[(size_t)r] = szs[3 * (size_t)r]; cW[(size_t)r] = szs[3 * (size_t)r + 1]; cB[(size_t)r] = szs[3 * (size_t)r + 2];
-            oP[(size_t)r + 1] = oP[(size_t)r] + cP[(size_t)r]; oW[(size_t)r + 1] = oW[(size_t)r] + cW[(size_t)r]; oB[(size_t)r + 1] = oB[(size_t)r] + cB[(size_t)r];
+        const u64 Wl = lp.Dw;                                                   // local distinct words
+        // -- splitters from a sample of every rank's keys
+        const u64 SAMP = 256;
+        DevBuf<u64> kw(Wl + 1);
+        if (Wl) {
+            const u8 *dp = lp.dict.get(); const u64 *wsp = lp.wstart.get(); u64 *kp = kw.get();
+            launch_for(Wl, st, PFB_LAMBDA(u64 j) { kp[j] = pack_syms(dp + wsp[j], wsp[j + 1] - 1 - wsp[j], 0, 21); });
         }
-        const u64 P = oP[(size_t)G], M = oW[(size_t)G], UB = oB[(size_t)G];
+        std::vector<u64> bound((size_t)G + 1, 0);
+        {
+            DevBuf<u64> smp(SAMP), allsmp(SAMP * (u64)G);
+            const u64 *kp = kw.get(); u64 *sp = smp.get();
+            launch_for(SAMP, st, PFB_LAMBDA(u64 i) { sp[i] = Wl ? kp[(2 * i + 1) * Wl / (2 * SAMP)] : ~0ull; });      // Wl < 2^32: no overflow
+            comm->all_gather(smp.get(), allsmp.get(), SAMP * 8, st);
+            std::vector<u64> hs(SAMP * (size_t)G);
+            d2h(hs.data(), allsmp.get(), hs.size() * 8, st);
+            stream_sync(st);
+            std::sort(hs.begin(), hs.end());
+            size_t real = hs.size();
+            while (real && hs[real - 1] == ~0ull) --real;                      // ranks without words sent padding
+            for (int d = 1; d < G; ++d) bound[(size_t)d] = real ? hs[real * (size_t)d / (size_t)G] : ~0ull;
+            bound[(size_t)G] = ~0ull;
+            for (int d = 1; d <= G; ++d) if (bound[(size_t)d] < bound[(size_t)d - 1]) bound[(size_t)d] = bound[(size_t)d - 1];
+        }
+        // -- slice of the local (sorted) dictionary for every owner: words [cut[d], cut[d+1])
+        std::vector<u64> cut((size_t)G + 1, 0), cutb((size_t)G + 1, 0);
+        {
+            DevBuf<u64> db((size_t)G + 1), dc(2 * ((size_t)G + 1));
+            h2d(db.get(), bound.data(), ((size_t)G + 1) * 8, st);
+            const u64 *kp = kw.get(); const u64 *bp = db.get(); const u64 *wsp = lp.wstart.get(); u64 *cp = dc.get();
+            const u64 G1 = (u64)G + 1;
+            launch_for(G1, st, PFB_LAMBDA(u64 d) {
+                u64 lo = 0, hi = Wl;                                            // first word with key >= bound[d] (all words for d = G)
+                if (d + 1 == G1) lo = Wl;
+                else while (lo < hi) { const u64 mid = lo + (hi - lo) / 2; if (kp[mid] < bp[d]) lo = mid + 1; else hi = mid; }
+                cp[d] = lo; cp[G1 + d] = Wl ? wsp[lo] : 0;
+            });
+            std::vector<u64> hc(2 * ((size_t)G + 1));
+            d2h(hc.data(), dc.get(), hc.size() * 8, st);
+            stream_sync(st);
+            for (int d = 0; d <= G; ++d) { cut[(size_t)d] = hc[(size_t)d]; cutb[(size_t)d] = hc[(size_t)G + 1 + (size_t)d]; }
+            cut[0] = 0; cutb[0] = 0;
+        }
+        kw.release();
+        // -- count matrices (words and bytes, source-major) and the phrase counts
+        std::vector<u64> row(2 * (size_t)G + 1);
+        for (int d = 0; d < G; ++d) { row[(size_t)d] = cut[(size_t)d + 1] - cut[(size_t)d]; row[(size_t)G + (size_t)d] = cutb[(size_t)d + 1] - cutb[(size_t)d]; }
+        row[2 * (size_t)G] = lp.P;
+        std::vector<u64> rows = comm->gather_u64(row.data(), 2 * G + 1, st);
+        std::vector<u64> mw((size_t)G * G), mb((size_t)G * G), cP((size_t)G), oP((size_t)G + 1, 0);
+        for (int s_ = 0; s_ < G; ++s_) {
+            for (int d = 0; d < G; ++d) {
+                mw[(size_t)s_ * G + d] = rows[(size_t)s_ * (2 * G + 1) + d];
+                mb[(size_t)s_ * G + d] = rows[(size_t)s_ * (2 * G + 1) + G + d];
+            }
+            cP[(size_t)s_] = rows[(size_t)s_ * (2 * G + 1) + 2 * G];
+            oP[(size_t)s_ + 1] = oP[(size_t)s_] + cP[(size_t)s_];
+        }
+        const u64 P = oP[(size_t)G];
         if (prm.bits == 32 && P > 0x7FFFFFFEull) return fail(PFB_ERR_LIMIT, "Input containing more than 2^31-2 phrases! Please use 64 bit version");
         if (P > 0xFFFFFFFEull) return fail(PFB_ERR_LIMIT, "Input containing more than 2^32-2 phrases! This is currently a hard limit");
-        if (M > 0xFFFFFFF0ull) return fail(PFB_ERR_LIMIT, "more than 2^32 dictionary words across the ranks");
-        // union of the local dictionaries: bytes, word starts, occurrence counts
-        DevBuf<u8> ub(UB + 1);
-        DevBuf<u32> uocc(M + 1);
-        DevBuf<u64> uws(M + 1), ustart(M + 1);
-        auto scaled = [&](const std::vector<u64> &c, u64 k) { std::vector<u64> v(c); for (auto &x : v) x *= k; return v; };
-        comm->all_gather_v(lp.dict.get(), ub.get(), cB.data(), st);
-        comm->all_gather_v(lp.wstart.get(), uws.get(), scaled(cW, 8).data(), st);
-        comm->all_gather_v(lp.occ.get(), uocc.get(), scaled(cW, 4).data(), st);
-        t_x += xt.stop();
-        for (int r = 0; r < G; ++r) {
-            const u64 c = cW[(size_t)r], o = oW[(size_t)r], b = oB[(size_t)r];
-            const u64 *src = uws.get() + o; u64 *dst = ustart.get() + o;
-            launch_for(c, st, PFB_LAMBDA(u64 j) { dst[j] = b + src[j]; });
+        u64 M = 0, MB = 0;                                                      // words / bytes this owner receives
+        for (int s_ = 0; s_ < G; ++s_) { M += mw[(size_t)s_ * G + g]; MB += mb[(size_t)s_ * G + g]; }
+        {
+            u64 tw = 0;
+            for (u64 x : mw) tw += x;
+            if (tw > 0xFFFFFFF0ull) return fail(PFB_ERR_LIMIT, "more than 2^32 dictionary words across the ranks");
         }
-        { u64 *us = ustart.get(); launch_for(1, st, PFB_LAMBDA(u64) { us[M] = UB; }); }
-        // sort the union; groups of identical words collapse into one global word
+        auto scaled = [&](const std::vector<u64> &c, u64 k) { std::vector<u64> v(c); for (auto &x : v) x *= k; return v; };
+        // -- the exchange: bytes, word lengths, occurrence counts
+        DevBuf<u8> ub(MB + 1);
+        DevBuf<u32> ulen(M + 1), uocc(M + 1), slen(Wl + 1);
+        if (Wl) {
+            const u64 *wsp = lp.wstart.get(); u32 *lp_ = slen.get();
+            launch_for(Wl, st, PFB_LAMBDA(u64 j) { lp_[j] = (u32)(wsp[j + 1] - wsp[j]); });      // word + EndOfWord
+        }
+        comm->all_to_all_v(lp.dict.get(), ub.get(), mb.data(), st);
+        comm->all_to_all_v(slen.get(), ulen.get(), scaled(mw, 4).data(), st);
+        comm->all_to_all_v(lp.occ.get(), uocc.get(), scaled(mw, 4).data(), st);
+        slen.release();
+        t_x += xt.stop();
+        // -- this owner's share of the union: sort, groups of identical words collapse into one global word
+        DevBuf<u64> ustart(M + 1);
+        dev_memset(ulen.get() + M, 0, 4, st);
+        exclusive_sum<u32, u64>(ulen.get(), ustart.get(), M + 1, ws.sc, st);
         DevBuf<u32> order(M + 1);
         { u32 *op = order.get(); launch_for(M, st, PFB_LAMBDA(u64 j) { op[j] = (u32)j; }); }
         DevBuf<u8> head;
-        WordStr wsr;
-        wsr.wstart = ustart.get();
-        int rc = sort_strings(ub.get(), wsr, order, M, ws, &tm.phrase_sort_rounds, err, &head);
-        if (rc) return fail(rc, err);
-        DevBuf<u32> gidx(M + 1);
-        const u64 Dw = scan_flags(head.get(), gidx.get(), M, ws);            // gidx[j] + head[j] = 1-based global rank of order[j]
-        DevBuf<u32> map(M + 1), headpos(Dw + 1);
-        parse = DeviceParse();
-        parse.occ.alloc(Dw);
-        dev_memset(parse.occ.get(), 0, Dw * 4, st);
-        {
-            const u32 *op = order.get(); const u32 *gi = gidx.get(); const u8 *hd = head.get(); const u32 *uo = uocc.get();
-            u32 *mp = map.get(); u32 *hp = headpos.get(); u32 *oc = parse.occ.get();
+        u64 Wg = 0;                                                             // distinct words of this owner
+        DevBuf<u32> gidx(M + 1), map(M + 1);
+        if (M) {
+            WordStr wsr;
+            wsr.wstart = ustart.get();
+            int rc = sort_strings(ub.get(), wsr, order, M, ws, &tm.phrase_sort_rounds, err, &head);
+            if (rc) return fail(rc, err);
+            Wg = scan_flags(head.get(), gidx.get(), M, ws);                     // gidx[j] + head[j] = 1-based rank of order[j] inside this owner
+        }
+        DevBuf<u32> headpos(Wg + 1), occg(Wg + 1), leng(Wg + 1);
+        dev_memset(occg.get(), 0, (Wg + 1) * 4, st);
+        if (M) {
+            const u32 *op = order.get(); const u32 *gi = gidx.get(); const u8 *hd = head.get(); const u32 *uo = uocc.get(); const u32 *ul = ulen.get();
+            u32 *mp = map.get(); u32 *hp = headpos.get(); u32 *oc = occg.get(); u32 *lg = leng.get();
             launch_for(M, st, PFB_LAMBDA(u64 j) {
-                u32 r = gi[j] + hd[j];               // 1-based
+                const u32 r = gi[j] + hd[j];               // 1-based
                 mp[op[j]] = r;
-                if (hd[j]) hp[r - 1] = op[j];
+                if (hd[j]) { hp[r - 1] = op[j]; lg[r - 1] = ul[op[j]]; }
                 atomic_add(&oc[r - 1], uo[op[j]]);
             });
         }
-        // global dictionary image (include/pfbwt_io.hpp:71-82)
-        DevBuf<u64> wl(Dw + 1), ws64(Dw + 1);
-        {
-            u64 *wlp = wl.get(); const u32 *hp = headpos.get(); const u64 *us = ustart.get();
-            launch_for(Dw + 1, st, PFB_LAMBDA(u64 r) { wlp[r] = r == Dw ? 0 : us[hp[r] + 1] - us[hp[r]]; });   // word + EndOfWord
-        }
-        exclusive_sum<u64, u64>(wl.get(), ws64.get(), Dw + 1, ws.sc, st);
-        const u64 dsize = read_scalar(ws64.get() + Dw, st) + 1;
-        if (dsize >= DICT_MAX_BYTES) return fail(PFB_ERR_LIMIT, "dictionary larger than 2^40 bytes is not supported");
-        parse.n = n_total; parse.P = P; parse.Dw = Dw; parse.dsize = dsize;
-        parse.wstart = std::move(ws64);
-        parse.dict.alloc(dsize);
-        {
-            const u64 *w64 = parse.wstart.get(); const u32 *hp = headpos.get(); const u64 *us = ustart.get();
-            const u8 *src = ub.get(); u8 *dict = parse.dict.get();
-            launch_for(Dw * 32 + 1, st, PFB_LAMBDA(u64 i) {
-                if (i == Dw * 32) { dict[dsize - 1] = ENDOFDICT; return; }
-                u64 r = i / 32, lane = i % 32;
-                u64 s = us[hp[r]], len = us[hp[r] + 1] - s;          // includes the EndOfWord byte
-                u64 d0 = w64[r];
-                for (u64 j = lane; j < len; j += 32) dict[d0 + j] = src[s + j];
+        // this owner's piece of the global dictionary image (include/pfbwt_io.hpp:71-82)
+        DevBuf<u64> pstart(Wg + 1);
+        dev_memset(leng.get() + Wg, 0, 4, st);
+        exclusive_sum<u32, u64>(leng.get(), pstart.get(), Wg + 1, ws.sc, st);
+        const u64 PB = read_scalar(pstart.get() + Wg, st);                      // bytes of the piece
+        DevBuf<u8> piece(PB + 1);
+        if (Wg) {
+            const u32 *hp = headpos.get(); const u64 *us = ustart.get(); const u64 *ps_ = pstart.get(); const u8 *src = ub.get(); u8 *dst = piece.get();
+            launch_for(Wg * 32, st, PFB_LAMBDA(u64 i) {
+                const u64 r = i / 32, lane = i % 32;
+                const u64 s0 = us[hp[r]], len = us[hp[r] + 1] - s0;             // includes the EndOfWord byte
+                const u64 d0 = ps_[r];
+                for (u64 q = lane; q < len; q += 32) dst[d0 + q] = src[s0 + q];
             });
         }
+        t_m += xt.stop();
+        // -- sizes of the pieces; ranks back to the senders; the pieces to everybody
+        u64 pz[2] = {Wg, PB};
+        std::vector<u64> pzs = comm->gather_u64(pz, 2, st);
+        std::vector<u64> cW((size_t)G), cB((size_t)G), oW((size_t)G + 1, 0), oB((size_t)G + 1, 0);
+        for (int r = 0; r < G; ++r) {
+            cW[(size_t)r] = pzs[2 * (size_t)r]; cB[(size_t)r] = pzs[2 * (size_t)r + 1];
+            oW[(size_t)r + 1] = oW[(size_t)r] + cW[(size_t)r]; oB[(size_t)r + 1] = oB[(size_t)r] + cB[(size_t)r];
+        }
+        const u64 Dw = oW[(size_t)G], dsize = oB[(size_t)G] + 1;
+        if (dsize >= DICT_MAX_BYTES) return fail(PFB_ERR_LIMIT, "dictionary larger than 2^40 bytes is not supported");
+        {
+            u32 *mp = map.get(); const u32 add = (u32)oW[(size_t)g];
+            launch_for(M, st, PFB_LAMBDA(u64 j) { mp[j] += add; });              // global 1-based rank of every received word
+        }
+        DevBuf<u32> gmap(Wl + 1);                                               // global rank of local word j
+        {
+            std::vector<u64> back((size_t)G * G);                               // transposed: owner d sends rank s what s sent d
+            for (int s_ = 0; s_ < G; ++s_) for (int d = 0; d < G; ++d) back[(size_t)d * G + s_] = mw[(size_t)s_ * G + d] * 4;
+            comm->all_to_all_v(map.get(), gmap.get(), back.data(), st);
+        }
+        parse = DeviceParse();
+        parse.n = n_total; parse.P = P; parse.Dw = Dw; parse.dsize = dsize;
+        parse.dict.alloc(dsize);
+        parse.occ.alloc(Dw ? Dw : 1);
+        DevBuf<u32> alllen(Dw + 1);
+        comm->all_gather_v(piece.get(), parse.dict.get(), cB.data(), st);
+        comm->all_gather_v(leng.get(), alllen.get(), scaled(cW, 4).data(), st);
+        comm->all_gather_v(occg.get(), parse.occ.get(), scaled(cW, 4).data(), st);
+        t_x += xt.stop();
+        dev_memset(alllen.get() + Dw, 0, 4, st);
+        parse.wstart.alloc(Dw + 1);
+        exclusive_sum<u32, u64>(alllen.get(), parse.wstart.get(), Dw + 1, ws.sc, st);       // wstart[Dw] = dsize - 1
+        { u8 *dict = parse.dict.get(); launch_for(1, st, PFB_LAMBDA(u64) { dict[dsize - 1] = ENDOFDICT; }); }
+        piece.release(); ub.release(); ustart.release(); order.release(); head.release(); gidx.release(); map.release();
         // local ranks -> global ranks, then the whole parse on every rank
         DevBuf<u32> lp2(lp.P + 1);
         {
-            const u32 *mp = map.get() + oW[(size_t)g]; const u32 *pr = lp.parse.get(); u32 *o = lp2.get();
+            const u32 *mp = gmap.get(); const u32 *pr = lp.parse.get(); u32 *o = lp2.get();
             launch_for(lp.P, st, PFB_LAMBDA(u64 k) { o[k] = mp[pr[k] - 1]; });
         }
         t_m += xt.stop();
