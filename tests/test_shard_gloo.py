@@ -203,3 +203,27 @@ def test_preparsed_parts_job(tmp_path, world, bits):
     recs = pangenome_records(5000, 6, 10, seed=17) + [("t", random_bases(900, 3))]
     out, refp = run_job("emu", str(tmp_path), split_records(recs, world), 10, 100, bits, True, True, preparse=[emu, "--bits", str(bits)])
     assert_same_files(out, refp, exts_for(True, True))
+
+
+def test_skewed_dictionary_owners(tmp_path):
+    """dictionary merge by owner ranks with a skewed key distribution: tandem repeats make most words start with the same 21
+    symbols (one owner gets nearly everything, others nothing) and the same words occur on every rank (deduplicated by their
+    owner); poly-A records add words that are prefixes of each other"""
+    rng = np.random.default_rng(77)
+    unit = random_bases(37, 5)
+    recs = []
+    for i in range(8):
+        s = np.tile(unit, 300).copy()
+        pos = rng.integers(0, len(s), 25)
+        s[pos] = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, 25)]
+        recs.append((f"t{i}", s))
+        recs.append((f"a{i}", np.full(200 + 13 * i, ord("A"), dtype=np.uint8)))
+    out, refp = run_job("emu", str(tmp_path), split_records(recs, 4), 6, 11, 64, True, True)
+    assert_same_files(out, refp, exts_for(True, True))
+
+
+def test_world8_job(tmp_path):
+    """the rank count of the north-star run: 8 ranks (pieces of unequal size, one of them a single tiny record)"""
+    recs = pangenome_records(3000, 9, 10, seed=31) + [("tiny", random_bases(15, 2))] + [(f"r{i}", random_bases(2500 + 31 * i, 40 + i)) for i in range(6)]
+    out, refp = run_job("emu", str(tmp_path), split_records(recs, 8), 10, 100, 64, True, True)
+    assert_same_files(out, refp, exts_for(True, True))
