@@ -152,7 +152,8 @@ int pfb_write_doc_array(pfb_ctx *, const char *prefix);
  * include/rle_window_array.hpp:15-51,118-130): <mps> holds runs of text positions with their variant markers
  * ([first, last, marker..., 2^64-1] as u64 words), the output holds, for every maximal run of BWT positions whose SA[i]
  * carry the same non-empty marker list, [first i, last i, marker..., 2^64-1].
- * pfb_write_marker_array joins with the SA pfb_build_bwt (sa or rssa) left on the device - no .sa stream;
+ * pfb_write_marker_array joins with the SA pfb_build_bwt (sa or rssa) left on the device - no .sa stream; after
+ * pfb_build_bwt_to_files (sa = 1) it joins with the <prefix>.sa file that build wrote (32- or 64-bit entries);
  * pfb_marker_join reads the SA as u64 entries from a file or from stdin ("-"), like the reference's tool (any context will do). */
 int pfb_write_marker_array(pfb_ctx *, const char *mps_path, const char *out_path);
 int pfb_marker_join(pfb_ctx *, const char *mps_path, const char *sa_path_or_dash, const char *out_path);

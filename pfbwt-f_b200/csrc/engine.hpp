@@ -397,8 +397,13 @@ struct Engine {
     }
     int write_marker_array(const std::string &mps, const std::string &outp) {
         try {
-            if (!built || !(built_sa || built_rssa)) return fail(PFB_ERR_ARG, "the marker array needs a BWT built with the suffix array (-s / -r)");
             if (comm) return fail(PFB_ERR_ARG, "the marker array is a single-GPU output");
+            if (streamed && !built) {
+                // the last build went straight to the files (pfb_build_bwt_to_files): join with the .sa file it wrote
+                if (!streamed_sa) return fail(PFB_ERR_ARG, "the marker array after a streamed build needs the .sa file (build with sa)");
+                return prm.bits == 64 ? marker_join_t<u64>(mps, streamed_prefix + ".sa", outp) : marker_join_t<u32>(mps, streamed_prefix + ".sa", outp);
+            }
+            if (!built || !(built_sa || built_rssa)) return fail(PFB_ERR_ARG, "the marker array needs a BWT built with the suffix array (-s / -r)");
             MarkerRuns mr;
             int rc = load_marker_runs(mps, mr, device, ws, err);
             if (rc) return fail(rc, err);
@@ -427,7 +432,10 @@ struct Engine {
             return rc;
         } catch (const Error &e) { return fail(e.code, e.what()); }
     }
-    int marker_join(const std::string &mps, const std::string &sa_path, const std::string &outp) {
+    // SAT = u64: the reference tool's input (`--stdout sa` of pfbwt-f64); u32: the .sa file a 32-bit streamed build left
+    int marker_join(const std::string &mps, const std::string &sa_path, const std::string &outp) { return marker_join_t<u64>(mps, sa_path, outp); }
+    template <class SAT>
+    int marker_join_t(const std::string &mps, const std::string &sa_path, const std::string &outp) {
         try {
             MarkerRuns mr;
             int rc = load_marker_runs(mps, mr, device, ws, err);
@@ -439,23 +447,24 @@ struct Engine {
             if (!f) { if (!from_stdin) fclose(in); return fail(PFB_ERR_IO, "could not open " + outp + " for writing"); }
             const u64 CH = marker_chunk_entries();
             MarkerCarry carry;
-            DevBuf<u64> out, dsa(CH + 1);
+            DevBuf<u64> out;
+            DevBuf<SAT> dsa(CH + 1);
             // the SA goes through the host in chunks of CH entries plus one of look-ahead (a trailing partial entry is
             // dropped like fread(&s, 8, 1, fp) drops it)
-            std::vector<u64> hbuf(CH + 1);
-            u64 have = fread(hbuf.data(), 8, CH + 1, in);
+            std::vector<SAT> hbuf(CH + 1);
+            u64 have = fread(hbuf.data(), sizeof(SAT), CH + 1, in);
             while (have && !rc) {
                 const bool has_next = have == CH + 1;
                 const u64 m = has_next ? CH : have;
-                h2d(dsa.get(), hbuf.data(), have * 8, ws.st);
+                h2d(dsa.get(), hbuf.data(), have * sizeof(SAT), ws.st);
                 stream_sync(ws.st);
-                const u64 next = has_next ? hbuf[CH] : 0;
+                const u64 next = has_next ? (u64)hbuf[CH] : 0;
                 u64 nout = 0;
-                rc = marker_join_chunk<u64>(mr, dsa.get(), m, has_next, next, carry, out, &nout, ws);
+                rc = marker_join_chunk<SAT>(mr, dsa.get(), m, has_next, next, carry, out, &nout, ws);
                 if (!rc) rc = marker_flush(f, out, nout);
                 if (!has_next) break;
-                hbuf[0] = next;
-                have = 1 + fread(hbuf.data() + 1, 8, CH, in);
+                hbuf[0] = (SAT)next;
+                have = 1 + fread(hbuf.data() + 1, sizeof(SAT), CH, in);
             }
             fclose(f);
             if (!from_stdin) fclose(in);
@@ -535,13 +544,14 @@ struct Engine {
                 last.n = out.n; last.r = out.r; last.easy = out.easy; last.hard = out.hard;
             }
             bwt.n = last.n; bwt.r = last.r; bwt.easy = last.easy; bwt.hard = last.hard;      // sizes only: the slices went to the files
-            streamed = true;
+            streamed = true; streamed_sa = sa; streamed_prefix = prefix;
             stream_buckets = B; stream_peak = dev_bytes_peak();
             if (dev_bytes_peak() < peak0) dev_bytes_peak() = peak0;
             return PFB_OK;
         } catch (const Error &e) { return fail(e.code, e.what()); }
     }
     bool streamed = false;            // the last build went straight to files (sizes available, arrays not)
+    bool streamed_sa = false; std::string streamed_prefix;
 
     // drop the text and the staged input (records in HBM from the device reader / add_records, host staging) once the
     // parse exists: only dict/parse are needed downstream.  Parsing again needs pfb_clear + the input once more.

@@ -119,7 +119,6 @@ static Args parse_args(int argc, char **argv) {
     if (args.in_fname != "-" && args.output == "") args.output = args.in_fname;
     if (args.parse_only && args.pfbwt_only) die("cannot simulatneously do parse_only and pfbwt_only");
     if (!args.marker_mps.empty() && !args.sa && !args.rssa) { fprintf(stderr, "--marker-array needs the suffix array (-s or -r)\n"); exit(1); }
-    if (!args.marker_mps.empty() && args.mmap) { fprintf(stderr, "--marker-array joins with the SA in device memory: not with -m\n"); exit(1); }
     if (args.doc_array) {
         args.print_docs = 1;
         if (!args.sa && !args.rssa) { fprintf(stderr, "--doc-array needs the suffix array (-s or -r)\n"); exit(1); }
@@ -197,7 +196,7 @@ int main(int argc, char **argv) {
             if (pfb_device_free_bytes(ctx, &fr) == 0 && need > fr) bucketed = true;
         }
         if (bucketed && !args.stdout_ext.empty()) { fprintf(stderr, "--stdout is not available with -m\n"); exit(1); }
-        if (bucketed && !args.marker_mps.empty()) { fprintf(stderr, "--marker-array needs the SA in device memory: the build does not fit (or -m was given)\n"); exit(1); }
+        if (bucketed && !args.marker_mps.empty() && !args.sa) { fprintf(stderr, "--marker-array with a streamed build (-m, or a build that does not fit the device) joins with <prefix>.sa: add -s\n"); exit(1); }
         fprintf(stderr, bucketed ? "workspace will be cut into key-range buckets streamed to the output files\n" : "workspace will be contained in HBM\n");
         {
             Timer t(any_sa ? "TASK\tgenerating final BWT w/ full and/or run-length SA\t" : "TASK\tgenerating final BWT w/o SA\t");
@@ -206,6 +205,7 @@ int main(int argc, char **argv) {
                 pfb_stats s;
                 pfb_get_stats(ctx, &s);
                 fprintf(stderr, "buckets: %lu, peak device bytes: %lu\n", (unsigned long)s.stream_buckets, (unsigned long)s.stream_peak_bytes);
+                if (!args.marker_mps.empty() && pfb_write_marker_array(ctx, args.marker_mps.c_str(), (args.output + ".ma").c_str())) die_ctx(ctx);
             } else {
                 { SubTimer t2("BWT on device"); if (pfb_build_bwt(ctx, args.sa, args.rssa)) die_ctx(ctx); }
                 SubTimer t3("writing BWT files");

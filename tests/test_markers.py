@@ -132,6 +132,27 @@ def test_emu_join_edge_cases(emu, ref_bins, datadir):
 
 
 @pytest.mark.parametrize("bits", [32, 64])
+def test_emu_marker_array_after_streamed_build(bits, emu, ref_bins, datadir):
+    """-m (key-range buckets streamed to the files) with --marker-array: the join reads the <prefix>.sa file the build wrote,
+    4-byte entries in the 32-bit binary"""
+    fa = os.path.join(datadir, "ma_stream.fa")
+    recs = pangenome_records(20_000, 4, 30, 71)
+    write_fasta(fa, recs, line_width=60)
+    n = sum(len(s) + 10 for _, s in recs)
+    mps = os.path.join(datadir, "ma_stream.mps")
+    random_mps(mps, n, 72)
+    out = os.path.join(datadir, f"ma_stream{bits}")
+    subprocess.run([emu, "--bits", str(bits), "-m", "-s", "--marker-array", mps, "-o", out, fa], check=True,
+                   env=dict(os.environ, PFB_BUCKETS="3", PFB_MA_CHUNK="1001"), stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    sa64 = out + ".sa64"
+    np.fromfile(out + ".sa", dtype=np.uint32 if bits == 32 else np.uint64).astype(np.uint64).tofile(sa64)
+    ref = out + ".ref.ma"
+    reference_join(ref_bins, mps, sa64, ref)
+    assert os.path.getsize(ref) > 0
+    assert open(ref, "rb").read() == open(out + ".ma", "rb").read()
+
+
+@pytest.mark.parametrize("bits", [32, 64])
 def test_emu_marker_array_from_the_build(bits, emu, ref_bins, datadir):
     """pfbwt-f[64] -s --marker-array <mps>: the join with the SA the build left in memory == the reference tool on the .sa file"""
     fa = os.path.join(datadir, "ma_build.fa")
@@ -181,6 +202,10 @@ def test_gpu_marker_array_flag(bits, ref_bins, datadir):
     assert random_mps(mps, n, 63, max_gap=200, max_len=60) > 1000
     out = os.path.join(datadir, f"ma_gpu{bits}")
     run([os.path.join(BIN, "pfbwt-f64" if bits == 64 else "pfbwt-f"), "-s", "--marker-array", mps, "-o", out, fa])
+    if bits == 32:            # the same through a streamed build (-m): the join reads the 4-byte .sa file
+        subprocess.run([os.path.join(BIN, "pfbwt-f"), "-m", "-s", "--marker-array", mps, "-o", out + "_m", fa], check=True,
+                       env=dict(os.environ, PFB_BUCKETS="3"), stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        assert open(out + ".ma", "rb").read() == open(out + "_m.ma", "rb").read()
     sa64 = out + ".sa64"
     np.fromfile(out + ".sa", dtype=np.uint32 if bits == 32 else np.uint64).astype(np.uint64).tofile(sa64)
     ref = out + ".ref.ma"
