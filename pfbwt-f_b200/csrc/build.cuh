@@ -108,6 +108,10 @@ struct RunTableT {
     }
 };
 static const u64 RUN_BLOCK = 256, RUN_MIN = 3 * RUN_BLOCK;
+// All positions inside a single-symbol run are tied with each other after the main sort, so an open list shorter than this at
+// the first pivot round means that no run with open ties is longer than it: every comparison ends within the default cap
+// (2^PIVOT_LBITS symbols) and the scan of the whole dictionary for runs (0.6 ms per GB) is skipped.
+static const u64 RUN_TABLE_MIN_OPEN = 2048;
 
 template <class RT>
 PFB_HD inline u64 pivot_key(const u8 *dict, u64 D, u64 a, u64 p, int lb, const RT &rt) {
@@ -348,7 +352,7 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<DP> &sa, DevB
         }
         if (n_sorted) *n_sorted = N;
         meta.alloc(padded(N) + 64); cnt.alloc(padded(N));
-        dev_memset(meta.get(), M_HEAD, padded(N) + 64, st);
+        dev_memset(meta.get() + padded(N), M_HEAD, 64, st);       // the flags pass below writes every slot of the tiles, padding included
         if (N == 0) { tm.dict_sort_rounds = 0; return PFB_OK; }
         timer.lap("K6 radix sort");
         FlagsArgsT<DP> fa;
@@ -415,6 +419,7 @@ inline int sort_dict_suffixes(const DeviceParse &pp, int w, DevBuf<DP> &sa, DevB
             const u32 *ap = apos.get(); const u32 *cp = cnt.get(); u32 *tc = tcnt.get(); u8 *tm_ = tmeta.get();
             launch_for(m, st, PFB_LAMBDA(u64 a) { const u32 j = ap[a]; tc[a] = cp[j]; tm_[a] = mt[j]; });
         }
+        if (pivot && !have_rt && m < RUN_TABLE_MIN_OPEN) have_rt = true;     // see RUN_TABLE_MIN_OPEN
         if (pivot && !have_rt) {
             u32 R = 0; u64 longest = 0;
             build_run_table<DP>(dict, D, run_s, run_e, &R, &longest, ws);
